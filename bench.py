@@ -1,0 +1,327 @@
+"""bench.py - NSF-HiFiGAN decode throughput (audio-seconds per second) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode fast|fp32]
+
+Workload (BASELINE.json configs[3], the configuration the metric is quoted on): RVC v2 48 kHz decoder,
+30 s padded chunks (T = 3000 frames), 128 chunks per GPU per step - at 8 GPUs that is exactly the
+"1024 x 30 s chunks sharded across 8 B200" case; per-GPU work is fixed as N grows (weak scaling), chunks
+are independent so there is no data-path collective.  Synthetic latents / f0 contours, random-init
+weights of the named architecture (torch.manual_seed(1234), the reference's default init).
+
+One step = one pass of the decoder over this rank's 128 chunks.
+  value : device-resident inputs, CUDA events on the launching stream, barrier + synchronize on both
+          sides, max over ranks.  Inputs of a step are 295 MB (> the 126 MB L2) and every layer streams
+          GBs of activations, so no L2 flush is needed between iterations (stated in config).
+  e2e   : same metric through the host-buffer C-ABI call (rvcdec_forward_host via
+          HiFiGANNSFGenerator.decode_host): pinned host inputs -> device, decode, waveform -> pinned host,
+          every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+SR = 48000
+T_FRAMES = 3000          # 30 s chunks
+CHUNKS_PER_GPU = 128     # 1024 chunks / 8 GPUs
+MMAC_PER_FRAME = 550.760448e6   # SURVEY.md 8a, 48 kHz v2 (algorithmic, biases excluded)
+METRIC = "NSF-HiFiGAN decode audio-sec/sec @48kHz v2"
+
+
+# ------------------------------------------------------------------ distributed helpers
+def rank_units(n_units_per_rank: int, rank: int, world: int):
+    """Global unit ids owned by `rank` (weak scaling: every rank owns n_units_per_rank independent chunks)."""
+    return list(range(rank * n_units_per_rank, (rank + 1) * n_units_per_rank))
+
+
+def _reduce(value: float, device: torch.device, op) -> float:
+    import torch.distributed as dist
+
+    if not (dist.is_available() and dist.is_initialized()):
+        return value
+    t = torch.tensor([value], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=op)
+    return float(t.item())
+
+
+def max_over_ranks(value: float, device: torch.device) -> float:
+    import torch.distributed as dist
+
+    return _reduce(value, device, dist.ReduceOp.MAX)
+
+
+def sum_over_ranks(value: float, device: torch.device) -> float:
+    import torch.distributed as dist
+
+    return _reduce(value, device, dist.ReduceOp.SUM)
+
+
+def barrier():
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        for ln in self.lines:
+            f = [s.strip() for s in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax = float(f[2])
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ model / inputs
+def build_model(device):
+    from oracle.nsf_hifigan_oracle import CONFIG_48K as cfg  # config constants only (no oracle compute)
+    from rvc_b200 import HiFiGANNSFGenerator
+
+    torch.manual_seed(1234)
+    m = HiFiGANNSFGenerator(*cfg.ctor_args(), **cfg.ctor_kwargs()).eval()
+    m.noise_source = "philox"
+    return m, cfg
+
+
+def synth_batch(cfg, B, T, seed, pin):
+    """Synthetic latents / f0 of the named shape, generated on the host (so the e2e leg has real host buffers)."""
+    gen = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, cfg.initial_channel, T, generator=gen)
+    g = torch.randn(B, cfg.gin_channels, 1, generator=gen)
+    t = torch.arange(T, dtype=torch.float32) / 100.0
+    med = 90 + 210 * torch.rand(B, 1, generator=gen)
+    f0 = med * torch.pow(2.0, (0.5 / 12) * torch.sin(2 * 3.14159265 * 5.0 * t + 6.28 * torch.rand(B, 1, generator=gen)))
+    uv = (torch.rand(B, T // 50 + 1, generator=gen) < 0.25).repeat_interleave(50, dim=1)[:, :T]
+    f0 = torch.where(uv, torch.zeros_like(f0), f0).contiguous()
+    if pin:
+        x, g, f0 = x.pin_memory(), g.pin_memory(), f0.pin_memory()
+    return x, f0, g
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+# ------------------------------------------------------------------ arms
+def cpu_reference_throughput(T: int, reps: int, warm: int):
+    """The reference's CPU implementation of the path = the oracle port (torch CPU fp32), all host threads."""
+    from oracle import nsf_hifigan_oracle as O
+
+    cfg = O.CONFIG_48K
+    m, _ = build_model(None)
+    w = O.folded_weights(m.state_dict())
+    x, f0, g, noise = O.synth_inputs(cfg, 1, T, seed=1234)
+    torch.set_num_threads(os.cpu_count() or 1)
+    times = []
+    with torch.no_grad():
+        for i in range(warm + reps):
+            t0 = time.perf_counter()
+            O.decoder_forward(w, cfg, x, f0, g, noise)
+            dt = time.perf_counter() - t0
+            if i >= warm:
+                times.append(dt)
+    return (T / 100.0) / (sum(times) / len(times)), torch.get_num_threads(), sum(times) / len(times)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    T = 1000  # bounded sample of the 30 s-chunk workload: one 10 s chunk per step (same per-frame work)
+    thr, cores, sec = cpu_reference_throughput(T, max(1, args.steps), min(1, args.warmup))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": thr, "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "RVCv2 48kHz HiFiGAN-NSF decoder, 30 s padded chunks (BASELINE configs[3]); CPU arm timed on a bounded "
+                               "sample: one 10 s chunk (T=1000) per step"},
+        "cpu_baseline": {"value": thr, "unit": "audio-s/s", "cores": cores, "kind": "port",
+                         "sample": "oracle port (torch CPU fp32 restatement of hifigan_nsf.py:173-212), B=1, T=1000 frames per step"},
+        "e2e": {"value": thr, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for the product arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    B, T = args.chunks, args.frames
+    model, cfg = build_model(dev)
+    units = rank_units(B, rank, world)
+    x_h, f0_h, g_h = synth_batch(cfg, B, T, seed=1234 + units[0], pin=True)
+    x, f0, g = x_h.to(dev), f0_h.to(dev), g_h.to(dev)
+    n = T * cfg.upp
+    audio_s = B * T / 100.0
+
+    # ---- device-resident timing --------------------------------------------------------
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            y = model(x, f0, g, mode=args.mode)
+        h = model._handle
+        h.profile_enable(True)
+        sampler = ClockSampler(local)
+        torch.cuda.synchronize(); barrier(); torch.cuda.synchronize()
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        launches = 0
+        for _ in range(args.steps):
+            y = model(x, f0, g, mode=args.mode)
+            launches += model.last_launch_count
+        e1.record()
+        torch.cuda.synchronize(); barrier(); torch.cuda.synchronize()
+        clocks = sampler.stop()
+        ms = e0.elapsed_time(e1)
+        prof = h.profile_read()
+        h.profile_enable(False)
+    ms_max = max_over_ranks(ms, dev)
+    total_audio = sum_over_ranks(audio_s * args.steps, dev)
+    value = total_audio / (ms_max / 1e3)
+    assert bool(torch.isfinite(y).all()) and float(y.abs().max()) <= 1.0
+
+    # ---- end-to-end through the host-buffer C ABI --------------------------------------
+    out_h = torch.empty(B, 1, n, dtype=torch.float32, pin_memory=True)
+    for _ in range(1):
+        model.decode_host(x_h, f0_h, g_h, mode=args.mode, out=out_h, device=local)
+    torch.cuda.synchronize(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        model.decode_host(x_h, f0_h, g_h, mode=args.mode, out=out_h, device=local)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0, dev)
+    barrier()
+    e2e_value = total_audio / e2e_s
+    h2d = x_h.numel() * 4 + f0_h.numel() * 4 + g_h.numel() * 4
+    d2h = out_h.numel() * 4
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk, pk_kind = peaks()
+    layers = {}
+    for p in prof:
+        if p["ms"] <= 0:
+            continue
+        layers[p["name"]] = {
+            "ms_per_step": p["ms"] / args.steps, "share": p["ms"] / ms,
+            "tflops": p["flops"] / (p["ms"] * 1e-3) / 1e12, "hbm_gbs": p["bytes"] / (p["ms"] * 1e-3) / 1e9,
+            "tensor_frac": p["flops"] / (p["ms"] * 1e-3) / 1e12 / pk["bf16_tflops_sustained"],
+            "hbm_frac": p["bytes"] / (p["ms"] * 1e-3) / 1e9 / pk["hbm_gbs"],
+        }
+    dom = max((p for p in prof if p["name"].startswith("mrf")), key=lambda p: p["ms"])
+    dom_l = layers[dom["name"]]
+    spans = max(1, dom["spans"])
+    if args.mode == "fp32":
+        roof = {"bound": "tensor", "kernel": f"conv_f32_kernel ({dom['name']})", "achieved": dom_l["tflops"], "peak": pk["bf16_tflops_sustained"],
+                "unit": "TFLOP/s", "frac": dom_l["tensor_frac"], "traffic": None, "peak_kind": pk_kind + " bf16 sustained (fp32 FFMA kernels cannot reach it)"}
+    else:
+        roof = {"bound": "tensor", "kernel": f"conv_mma_kernel ({dom['name']}: the stage's 18 ResBlock convs)", "achieved": dom_l["tflops"],
+                "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": dom_l["tensor_frac"], "traffic": None,
+                "peak_kind": pk_kind + " bf16 sustained (kernel timed inside a long step)",
+                "avg_launch_ms": dom["ms"] / spans, "flops_per_launch": dom["flops"] / spans,
+                "hbm_gbs": dom_l["hbm_gbs"], "hbm_frac": dom_l["hbm_frac"]}
+    total_tflops = 2 * MMAC_PER_FRAME * T * B * args.steps / (ms * 1e-3) / 1e12
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        thr, cores, sec = cpu_reference_throughput(1000, 2, 1)
+        cpu = {"value": thr, "unit": "audio-s/s", "cores": cores, "kind": "port",
+               "sample": f"oracle port (torch CPU fp32), one 10 s chunk (B=1, T=1000), mean of 2 after 1 warm-up, {sec:.2f} s per chunk"}
+    line = {
+        "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.mode == "fp32" else "bf16/f16 operands, f32 accumulate", "data": "synthetic",
+        "config": {"workload": f"RVCv2 48kHz HiFiGAN-NSF decoder, {B} x {T / 100:.0f} s padded chunks per GPU (BASELINE configs[3]: 1024 x 30 s over 8 GPUs), "
+                               f"mode={args.mode}, random-init weights seed 1234, in-kernel Philox source noise",
+                   "chunks_per_gpu": B, "frames_per_chunk": T, "l2": "inputs (295 MB/step) and activations (GBs/layer) exceed the 126 MB L2; no flush needed"},
+        "clocks": clocks, "gpu_launches": launches,
+        "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "roofline": roof, "whole_decoder_tflops": total_tflops, "whole_decoder_tensor_frac": total_tflops / pk["bf16_tflops_sustained"],
+        "layers": layers,
+    }
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="fast", choices=["fast", "fp32", "fast_f16", "fast_bf16"])
+    ap.add_argument("--chunks", type=int, default=CHUNKS_PER_GPU)
+    ap.add_argument("--frames", type=int, default=T_FRAMES)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

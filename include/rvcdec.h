@@ -1,0 +1,162 @@
+/*
+ * rvcdec.h - C ABI of the B200-native NSF-HiFiGAN decoder (librvcdec.so).
+ *
+ * This is the drop-in boundary for ONE path of the reference
+ * (Acelogic/Retrieval-based-Voice-Conversion-MLX): HiFiGANNSFGenerator.forward,
+ * rvc/lib/algorithm/generators/hifigan_nsf.py:173-212, as called from
+ * Synthesizer.infer (rvc/lib/algorithm/synthesizers.py:237-241).  The reference
+ * has no FFI for this path - its boundary is a Python class - so the entry
+ * points below are what a ctypes stub placed in the reference's
+ * rvc/lib/algorithm/generators/ would bind.  Plain C types
+ * only; every pointer documented as "device" is a CUDA device pointer of the
+ * device the handle was created on, every pointer documented as "host" is
+ * ordinary (preferably pinned) host memory.
+ *
+ * All functions return 0 on success and a negative rvcdec_status otherwise;
+ * nothing throws across this boundary.  rvcdec_last_error() returns a
+ * thread-local human-readable message for the last failure.
+ * There is no CPU fallback: every compute entry point fails with
+ * RVCDEC_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef RVCDEC_H_
+#define RVCDEC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RVCDEC_MAX_UPS 8
+#define RVCDEC_MAX_KERNELS 8
+#define RVCDEC_MAX_DILATIONS 8
+
+typedef enum {
+  RVCDEC_OK = 0,
+  RVCDEC_ERR_ARG = -1,         /* bad argument / unsupported configuration */
+  RVCDEC_ERR_CUDA = -2,        /* CUDA runtime error (message has the detail) */
+  RVCDEC_ERR_WEIGHTS = -3,     /* missing / mis-shaped tensor in load_weights */
+  RVCDEC_ERR_WORKSPACE = -4,   /* workspace too small for even one batch item */
+  RVCDEC_ERR_STATE = -5        /* forward before load_weights, etc. */
+} rvcdec_status;
+
+/* Arithmetic of the convolution stack.
+ *   FP32: CUDA-core FFMA kernels, fp32 everywhere (parity mode, <= 2e-3 max-abs).
+ *   FAST: tcgen05 tensor-core implicit GEMMs, 16-bit operands, fp32 accumulate,
+ *         fp32 residual stream (>= 0.999 multi-resolution log-mel correlation). */
+typedef enum { RVCDEC_MODE_FP32 = 0, RVCDEC_MODE_FAST = 1 } rvcdec_mode;
+
+/* The constructor values of the reference class, hifigan_nsf.py:75-86
+ * (checkpointing is training-only and has no counterpart here). */
+typedef struct {
+  int32_t initial_channel;                 /* 192 */
+  int32_t upsample_initial_channel;        /* 512 */
+  int32_t gin_channels;                    /* 256, 0 = no conditioning conv */
+  int32_t sr;                              /* 48000 */
+  int32_t num_upsamples;                   /* 4 */
+  int32_t upsample_rates[RVCDEC_MAX_UPS];          /* 12,10,2,2 (even rates only) */
+  int32_t upsample_kernel_sizes[RVCDEC_MAX_UPS];   /* 24,20,4,4 */
+  int32_t num_kernels;                     /* 3 */
+  int32_t resblock_kernel_sizes[RVCDEC_MAX_KERNELS];   /* 3,7,11 (odd) */
+  int32_t num_dilations;                   /* 3 */
+  int32_t resblock_dilation_sizes[RVCDEC_MAX_KERNELS][RVCDEC_MAX_DILATIONS]; /* 1,3,5 */
+} rvcdec_config;
+
+/* One fp32 tensor of the decoder's state_dict, in HOST memory, named exactly as
+ * the reference names it without the "dec." prefix, e.g. "conv_pre.weight",
+ * "ups.0.parametrizations.weight.original0" or the legacy "ups.0.weight_g"
+ * (rvc/train/utils.py:49-55), "resblocks.3.convs1.2.bias", "m_source.l_linear.weight". */
+typedef struct {
+  const char* name;
+  const float* data;   /* host */
+  int64_t numel;
+} rvcdec_tensor;
+
+typedef struct rvcdec_handle rvcdec_handle;
+
+/* Create a decoder bound to CUDA device `device`.  Replaces
+ * HiFiGANNSFGenerator.__init__ (hifigan_nsf.py:75-171). */
+int rvcdec_create(const rvcdec_config* cfg, int device, rvcdec_handle** out);
+
+/* Fold weight-norm (w = v * g/||v||, hifigan_nsf.py:120, residuals.py:14), repack
+ * every layer into the kernels' layouts and upload.  Replaces
+ * load_state_dict + the per-forward weight-norm recomputation of the reference
+ * (rvc/infer/infer.py:479-488).  May be called again after the weights change. */
+int rvcdec_load_weights(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n);
+
+/* Device scratch bytes for one pass over B items of T frames. Linear in B. */
+size_t rvcdec_workspace_bytes(const rvcdec_handle* h, int32_t B, int32_t T, int32_t mode);
+
+/* forward(x, f0, g) -> waveform, hifigan_nsf.py:173-212, all pointers DEVICE fp32:
+ *   x     (B, initial_channel, T) contiguous
+ *   f0    (B, T) Hz, 0 = unvoiced
+ *   g     (B, gin_channels) or NULL
+ *   noise (B, T*upp) standard-normal draws to inject (what the reference draws at
+ *         hifigan.py:223), or NULL to draw them in-kernel from Philox4x32-10(seed)
+ *   out   (B, T*upp)  (the reference's (B,1,T*upp))
+ * If workspace_bytes is smaller than rvcdec_workspace_bytes(B) the batch is
+ * processed in as many equal passes as needed.  Asynchronous on `stream`
+ * (a cudaStream_t passed as void*). */
+int rvcdec_forward(rvcdec_handle* h, const float* x, const float* f0, const float* g,
+                   const float* noise, uint64_t seed, float* out,
+                   void* workspace, size_t workspace_bytes,
+                   int32_t B, int32_t T, int32_t mode, void* stream);
+
+/* Same call with HOST buffers (pinned memory recommended): copies inputs to the
+ * device, decodes, copies the waveform back, and returns after the copy has
+ * completed.  `noise` may be NULL (in-kernel draws).  Scratch is owned by the
+ * handle and capped at `max_device_bytes` (0 = default cap). This is the call
+ * the reference's pipeline makes per chunk (rvc/infer/pipeline.py:366-371:
+ * net_g.infer(...)[0][0,0].data.cpu().float().numpy()). */
+int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const float* g,
+                        const float* noise, uint64_t seed, float* out,
+                        int32_t B, int32_t T, int32_t mode, size_t max_device_bytes);
+
+/* Number of kernels launched by the last forward on this handle. */
+int64_t rvcdec_last_launch_count(const rvcdec_handle* h);
+
+/* Per-layer timing for bench.py.  While enabled, every forward records a CUDA event on the
+ * launching stream in front of each kernel group; rvcdec_profile_read (which synchronises on the
+ * last event) returns the accumulated device time, algorithmic FLOPs (2 x MAC, biases and
+ * zero-padded polyphase taps excluded) and algorithmic HBM bytes (each operand/result once) per
+ * layer group since the last enable: "source", "prep", "conv_pre", "ups{i}", "noise_add{i}",
+ * "mrf{i}", "conv_post".  Returns the number of entries written. */
+typedef struct {
+  char name[32];
+  double ms;
+  double flops;
+  double bytes;
+  int64_t spans;
+} rvcdec_profile_entry;
+int rvcdec_profile_enable(rvcdec_handle* h, int32_t on);
+int32_t rvcdec_profile_read(rvcdec_handle* h, rvcdec_profile_entry* out, int32_t max_entries);
+
+/* ---- test hooks (used by tests/ only) ------------------------------------- */
+/* Make the next forwards stop early: 0 = run everything, 1 = after the harmonic source,
+ * 2 = after conv_pre, 10+i = after stage i's upsample + noise_conv add, 20+i = after stage i.
+ * rvcdec_debug_read then copies a named intermediate of the LAST pass, converted to plain
+ * (B, C, L) fp32, into a DEVICE buffer.  Names: "har" (B, T*upp); "pre" = leaky_relu(conv_pre
+ * + cond, 0.1); "stage{i}.in" = ups + noise_conv output; "stage{i}.out" = leaky_relu(stage
+ * output, 0.1) for i < last, the raw stage output for the last stage.
+ * Returns the number of floats written, or <0. */
+int rvcdec_debug_set_stop(rvcdec_handle* h, int32_t stop_after);
+int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_t dst_numel,
+                          void* workspace, int32_t B, int32_t T, int32_t mode, void* stream);
+/* Copy a packed host-side weight image for CPU tests (no GPU needed). Layer = reference module
+ * name ("conv_pre", "ups.0", "resblocks.4.convs1.2").  kind 0 = fp32 [tap][ci][n] image, 1 = fp16
+ * tensor-core image, 2 = tap shifts (int32), 3 = tensor-core tap masks (uint32 per N tile),
+ * 4 = bf16 tensor-core image, 5 = int32[8] {Cin, N, cout, up, ntaps, halo, n_tile, kc}, 6 = bias.
+ * dst NULL returns the size in bytes. */
+/* Fold + repack on the host only (no CUDA call), so the images can be inspected without a GPU. */
+int rvcdec_debug_pack_host(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n);
+int64_t rvcdec_debug_packed(const rvcdec_handle* h, const char* layer, int32_t kind, void* dst, int64_t dst_bytes);
+
+void rvcdec_destroy(rvcdec_handle* h);
+const char* rvcdec_last_error(void);
+const char* rvcdec_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RVCDEC_H_ */

@@ -73,9 +73,9 @@ CONFIG_32K = DecoderConfig(upsample_rates=(10, 8, 2, 2), upsample_kernel_sizes=(
 # A narrow decoder with the same topology, small enough to commit its weights as a fixture.
 CONFIG_TINY = DecoderConfig(
     initial_channel=24,
-    upsample_rates=(6, 5, 2, 2),
+    upsample_rates=(6, 4, 2, 2),
     upsample_initial_channel=128,
-    upsample_kernel_sizes=(12, 10, 4, 4),
+    upsample_kernel_sizes=(12, 8, 4, 4),
     gin_channels=16,
     sr=24000,
 )

@@ -1,0 +1,11 @@
+"""rvc_b200 - B200-native NSF-HiFiGAN decoder (drop-in for the reference's HiFiGANNSFGenerator).
+
+Only the decoder hot path lives here; see DESIGN.md for scope.  Importing this package does not
+load the CUDA library; the first ``forward`` (or ``_lib.lib()``) does, and fails loudly if it is
+missing.
+"""
+from .decoder import HiFiGANNSFGenerator, ResBlock, SourceModuleHnNSF  # noqa: F401
+from . import _lib  # noqa: F401
+from . import chunking  # noqa: F401
+
+__all__ = ["HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking"]

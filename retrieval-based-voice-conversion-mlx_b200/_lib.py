@@ -1,0 +1,225 @@
+"""ctypes binding of librvcdec.so (include/rvcdec.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` / ``csrc/build.sh``.
+There is no fallback of any kind: if the shared object is missing or a call
+fails, a ``RuntimeError`` carrying ``rvcdec_last_error()`` is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, Sequence
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librvcdec.so")
+
+MAX_UPS = 8
+MAX_KERNELS = 8
+MAX_DIL = 8
+
+MODE_FP32 = 0
+MODE_FAST = 1          # bf16 operands up to stage 1, fp16 after (default fast plan)
+MODE_FAST_F16 = 2      # fp16 operands everywhere
+MODE_FAST_BF16 = 3     # bf16 operands everywhere
+MODES = {"fp32": MODE_FP32, "fast": MODE_FAST, "fast_f16": MODE_FAST_F16, "fast_bf16": MODE_FAST_BF16}
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("initial_channel", C.c_int32),
+        ("upsample_initial_channel", C.c_int32),
+        ("gin_channels", C.c_int32),
+        ("sr", C.c_int32),
+        ("num_upsamples", C.c_int32),
+        ("upsample_rates", C.c_int32 * MAX_UPS),
+        ("upsample_kernel_sizes", C.c_int32 * MAX_UPS),
+        ("num_kernels", C.c_int32),
+        ("resblock_kernel_sizes", C.c_int32 * MAX_KERNELS),
+        ("num_dilations", C.c_int32),
+        ("resblock_dilation_sizes", (C.c_int32 * MAX_DIL) * MAX_KERNELS),
+    ]
+
+
+class Tensor(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64)]
+
+
+class ProfileEntry(C.Structure):
+    _fields_ = [("name", C.c_char * 32), ("ms", C.c_double), ("flops", C.c_double), ("bytes", C.c_double), ("spans", C.c_int64)]
+
+
+EXPORTS = [
+    "rvcdec_create", "rvcdec_load_weights", "rvcdec_workspace_bytes", "rvcdec_forward", "rvcdec_forward_host",
+    "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
+    "rvcdec_debug_packed", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
+]
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU or PyTorch fallback for the decoder)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, u64, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_size_t
+    L.rvcdec_create.argtypes = [C.POINTER(Config), C.c_int, C.POINTER(vp)]
+    L.rvcdec_create.restype = C.c_int
+    L.rvcdec_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]
+    L.rvcdec_load_weights.restype = C.c_int
+    L.rvcdec_workspace_bytes.argtypes = [vp, i32, i32, i32]
+    L.rvcdec_workspace_bytes.restype = sz
+    L.rvcdec_forward.argtypes = [vp, vp, vp, vp, vp, u64, vp, vp, sz, i32, i32, i32, vp]
+    L.rvcdec_forward.restype = C.c_int
+    L.rvcdec_forward_host.argtypes = [vp, vp, vp, vp, vp, u64, vp, i32, i32, i32, sz]
+    L.rvcdec_forward_host.restype = C.c_int
+    L.rvcdec_last_launch_count.argtypes = [vp]
+    L.rvcdec_last_launch_count.restype = i64
+    L.rvcdec_profile_enable.argtypes = [vp, i32]
+    L.rvcdec_profile_enable.restype = C.c_int
+    L.rvcdec_profile_read.argtypes = [vp, C.POINTER(ProfileEntry), i32]
+    L.rvcdec_profile_read.restype = i32
+    L.rvcdec_debug_set_stop.argtypes = [vp, i32]
+    L.rvcdec_debug_set_stop.restype = C.c_int
+    L.rvcdec_debug_read.argtypes = [vp, C.c_char_p, vp, i64, vp, i32, i32, i32, vp]
+    L.rvcdec_debug_read.restype = i64
+    L.rvcdec_debug_pack_host.argtypes = [vp, C.POINTER(Tensor), i32]
+    L.rvcdec_debug_pack_host.restype = C.c_int
+    L.rvcdec_debug_packed.argtypes = [vp, C.c_char_p, i32, vp, i64]
+    L.rvcdec_debug_packed.restype = i64
+    L.rvcdec_destroy.argtypes = [vp]
+    L.rvcdec_destroy.restype = None
+    L.rvcdec_last_error.argtypes = []
+    L.rvcdec_last_error.restype = C.c_char_p
+    L.rvcdec_version.argtypes = []
+    L.rvcdec_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def last_error() -> str:
+    return (lib().rvcdec_last_error() or b"").decode("utf-8", "replace")
+
+
+def check(rc: int, what: str) -> None:
+    if rc < 0:
+        raise RuntimeError(f"{what} failed ({rc}): {last_error()}")
+
+
+def make_config(initial_channel: int, resblock_kernel_sizes: Sequence[int], resblock_dilation_sizes,
+                upsample_rates: Sequence[int], upsample_initial_channel: int, upsample_kernel_sizes: Sequence[int],
+                gin_channels: int, sr: int) -> Config:
+    if len(upsample_rates) > MAX_UPS or len(resblock_kernel_sizes) > MAX_KERNELS:
+        raise ValueError("too many upsample / resblock stages")
+    nd = {len(d) for d in resblock_dilation_sizes}
+    if len(nd) != 1 or nd.pop() > MAX_DIL:
+        raise ValueError("every resblock must have the same number (<= 8) of dilations")
+    c = Config()
+    c.initial_channel = initial_channel
+    c.upsample_initial_channel = upsample_initial_channel
+    c.gin_channels = gin_channels
+    c.sr = sr
+    c.num_upsamples = len(upsample_rates)
+    for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
+        c.upsample_rates[i] = u
+        c.upsample_kernel_sizes[i] = k
+    c.num_kernels = len(resblock_kernel_sizes)
+    c.num_dilations = len(resblock_dilation_sizes[0])
+    for j, k in enumerate(resblock_kernel_sizes):
+        c.resblock_kernel_sizes[j] = k
+        for m, d in enumerate(resblock_dilation_sizes[j]):
+            c.resblock_dilation_sizes[j][m] = d
+    return c
+
+
+class Handle:
+    """Owns one rvcdec_handle."""
+
+    def __init__(self, cfg: Config, device: int):
+        self._h = C.c_void_p()
+        check(lib().rvcdec_create(C.byref(cfg), int(device), C.byref(self._h)), "rvcdec_create")
+        self.device = int(device)
+        self._keep = None
+
+    @property
+    def ptr(self) -> C.c_void_p:
+        return self._h
+
+    def _tensor_array(self, state: Dict[str, "object"]):
+        import torch
+
+        keep = []
+        arr = (Tensor * len(state))()
+        for i, (k, v) in enumerate(state.items()):
+            t = v.detach().to(device="cpu", dtype=torch.float32).contiguous()
+            name = k.encode()
+            keep.append((t, name))
+            arr[i].name = name
+            arr[i].data = t.data_ptr()
+            arr[i].numel = t.numel()
+        return arr, keep
+
+    def load_weights(self, state: Dict[str, "object"]) -> None:
+        arr, keep = self._tensor_array(state)
+        check(lib().rvcdec_load_weights(self._h, arr, len(state)), "rvcdec_load_weights")
+
+    def pack_host(self, state: Dict[str, "object"]) -> None:
+        arr, keep = self._tensor_array(state)
+        check(lib().rvcdec_debug_pack_host(self._h, arr, len(state)), "rvcdec_debug_pack_host")
+
+    def packed(self, layer: str, kind: int):
+        import numpy as np
+
+        n = lib().rvcdec_debug_packed(self._h, layer.encode(), kind, None, 0)
+        check(n, "rvcdec_debug_packed")
+        dt = {0: np.float32, 1: np.uint16, 2: np.int32, 3: np.uint32, 4: np.uint16, 5: np.int32, 6: np.float32}[kind]
+        out = np.empty(n // np.dtype(dt).itemsize, dtype=dt)
+        check(lib().rvcdec_debug_packed(self._h, layer.encode(), kind, out.ctypes.data, n), "rvcdec_debug_packed")
+        return out
+
+    def workspace_bytes(self, B: int, T: int, mode: int) -> int:
+        return int(lib().rvcdec_workspace_bytes(self._h, B, T, mode))
+
+    def forward(self, x, f0, g, noise, seed, out, workspace, B, T, mode, stream) -> None:
+        check(lib().rvcdec_forward(self._h, x, f0, g, noise, C.c_uint64(seed & (2**64 - 1)), out, workspace.data_ptr(),
+                                   workspace.numel(), B, T, mode, stream), "rvcdec_forward")
+
+    def forward_host(self, x, f0, g, noise, seed, out, B, T, mode, max_device_bytes=0) -> None:
+        check(lib().rvcdec_forward_host(self._h, x, f0, g, noise, C.c_uint64(seed & (2**64 - 1)), out, B, T, mode,
+                                        max_device_bytes), "rvcdec_forward_host")
+
+    def launch_count(self) -> int:
+        return int(lib().rvcdec_last_launch_count(self._h))
+
+    def profile_enable(self, on: bool) -> None:
+        check(lib().rvcdec_profile_enable(self._h, 1 if on else 0), "rvcdec_profile_enable")
+
+    def profile_read(self):
+        arr = (ProfileEntry * 64)()
+        n = lib().rvcdec_profile_read(self._h, arr, 64)
+        check(n, "rvcdec_profile_read")
+        return [dict(name=arr[i].name.decode(), ms=arr[i].ms, flops=arr[i].flops, bytes=arr[i].bytes, spans=arr[i].spans)
+                for i in range(n)]
+
+    def set_stop(self, stop: int) -> None:
+        check(lib().rvcdec_debug_set_stop(self._h, stop), "rvcdec_debug_set_stop")
+
+    def debug_read(self, name: str, dst, workspace, B, T, mode, stream) -> int:
+        n = lib().rvcdec_debug_read(self._h, name.encode(), dst.data_ptr(), dst.numel(), workspace.data_ptr(), B, T, mode, stream)
+        check(n, "rvcdec_debug_read")
+        return int(n)
+
+    def close(self) -> None:
+        if self._h:
+            lib().rvcdec_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,103 @@
+"""Host-side chunk geometry, sharding and stitching around the decoder.
+
+Restates only the arithmetic the reference's pipeline applies around ``net_g.infer``
+(``rvc/infer/pipeline.py``): split a long utterance every ``x_center`` seconds when it is
+longer than ``x_max`` (:441-454), give every chunk ``x_pad`` seconds of context on each side
+(:458, :478-544), decode chunks independently, trim ``t_pad_tgt`` samples per side (:494, :527)
+and concatenate (:545).  Chunks are the unit of data parallelism: they share no state, so they
+are dealt to GPUs with no collective on the data path.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Sequence
+
+import numpy as np
+
+FRAMES_PER_SECOND = 100  # hop = sr/100 at every rate (rvc/configs/*.json "hop_length")
+
+
+@dataclass(frozen=True)
+class Chunk:
+    index: int
+    start: int  # first frame of the padded chunk, in frames of the PADDED utterance
+    stop: int   # one past the last frame
+    trim: int   # frames of context to drop on each side after decoding
+
+    @property
+    def frames(self) -> int:
+        return self.stop - self.start
+
+
+def plan_chunks(n_frames: int, x_pad: int = 1, x_query: int = 6, x_center: int = 38, x_max: int = 41,
+                split_points: Sequence[int] | None = None) -> List[Chunk]:
+    """Chunk plan for an utterance of ``n_frames`` (unpadded) frames.
+
+    The reference pads the utterance by ``t_pad`` on both sides (pipeline.py:458) and, when the
+    padded... unpadded+window signal exceeds ``t_max`` (:443), cuts at ``opt_ts``: one point per
+    ``t_center`` (:446), each moved to the quietest sample within +-``t_query`` (:447-454).  The
+    quietest-sample search needs the waveform; callers that have it pass ``split_points`` (frames,
+    unpadded coordinates).  Without it the nominal multiples of ``t_center`` are used (synthetic
+    latents have no waveform).  Chunk k covers padded frames [s_k, t_k + 2*pad) (:485-487), the last
+    one [t_last, end) (:519-521); every decoded chunk is trimmed by ``pad`` frames per side.
+    """
+    pad = x_pad * FRAMES_PER_SECOND
+    total = n_frames + 2 * pad
+    if split_points is None:
+        split_points = []
+        if n_frames > x_max * FRAMES_PER_SECOND:
+            split_points = list(range(x_center * FRAMES_PER_SECOND, n_frames, x_center * FRAMES_PER_SECOND))
+    chunks: List[Chunk] = []
+    s = 0
+    for k, t in enumerate(split_points):
+        if not (s < t < n_frames):
+            raise ValueError("split points must be increasing and inside the utterance")
+        chunks.append(Chunk(k, s, t + 2 * pad, pad))
+        s = t
+    chunks.append(Chunk(len(chunks), s, total, pad))
+    return chunks
+
+
+def shard_units(lengths: Sequence[int], n_ranks: int) -> List[List[int]]:
+    """Deal independent units (chunks / utterances) to ranks: longest-processing-time first, ties and
+    equal lengths in input order, so equal-length batches become contiguous equal shares."""
+    order = sorted(range(len(lengths)), key=lambda i: (-lengths[i], i))
+    load = [0] * n_ranks
+    out: List[List[int]] = [[] for _ in range(n_ranks)]
+    for i in order:
+        r = min(range(n_ranks), key=lambda q: (load[q], q))
+        out[r].append(i)
+        load[r] += lengths[i]
+    for r in range(n_ranks):
+        out[r].sort()
+    return out
+
+
+def stitch(decoded: Sequence[np.ndarray], trims: Sequence[int], crossfade: int = 0) -> np.ndarray:
+    """Join decoded chunks (1-D sample arrays).  ``trims`` = samples to drop per side.
+
+    crossfade == 0 reproduces the reference exactly: trim then concatenate (pipeline.py:494,:527,:545).
+    crossfade > 0 keeps ``crossfade`` extra samples of context on both sides of every joint and blends
+    them with the reference's only crossfade convention, the sin^2 windows of the realtime path
+    (rvc/realtime/core.py:383-398: fade_in = sin^2(pi/2 * linspace(0,1,N)), fade_out = 1 - fade_in).
+    """
+    if len(decoded) != len(trims):
+        raise ValueError("one trim per chunk")
+    if crossfade == 0:
+        return np.concatenate([d[t: len(d) - t] if t else d for d, t in zip(decoded, trims)])
+    if any(t < crossfade for t in trims[:-1]) or any(t < crossfade for t in trims[1:]):
+        raise ValueError("crossfade longer than the available context")
+    fade_in = np.sin(0.5 * np.pi * np.linspace(0.0, 1.0, 2 * crossfade, dtype=np.float32)) ** 2
+    fade_out = 1.0 - fade_in
+    out = None
+    for k, (d, t) in enumerate(zip(decoded, trims)):
+        lo = t - (crossfade if k > 0 else 0)
+        hi = len(d) - t + (crossfade if k < len(decoded) - 1 else 0)
+        seg = np.array(d[lo:hi], dtype=np.float32, copy=True)
+        if out is None:
+            out = seg
+            continue
+        n = 2 * crossfade
+        out[-n:] = out[-n:] * fade_out + seg[:n] * fade_in
+        out = np.concatenate([out, seg[n:]])
+    return out

@@ -1,0 +1,324 @@
+// Small HBM-bound kernels around the convolution stack: harmonic source, speaker
+// conditioning bias, input packing, pad zeroing, noise_conv add, conv_post + tanh.
+#include <algorithm>
+#include <cstdio>
+#include "common.cuh"
+
+namespace rvcdec {
+
+// ---------------------------------------------------------------------------
+// Harmonic source: SineGenerator.forward (hifigan.py:197-228) + SourceModuleHnNSF
+// merge (hifigan_nsf.py:48-52) in one kernel.
+//   inc[l][k]  = f0[l]/sr * (k+1)
+//   rem[l]     = fmod(inc[l][upp-1] + 0.5, 1) - 0.5          (l < T-1)
+//   C[l]       = sum_{j<l} rem[j]                            (frame-level scan, fp64)
+//   sine       = 0.1 * sin(2*pi*(inc[l][k] + C[l]))
+//   out        = uv ? sine + 0.003*z : (0.1/3)*z ;  har = tanh(w*out + b)
+// Each CTA owns FPB consecutive frames of one item.  The scan is only T (<= a few
+// thousand) elements long, so every CTA re-reduces the prefix of its own span in fp64
+// instead of running a multi-pass device scan: no inter-CTA dependency, one launch.
+// ---------------------------------------------------------------------------
+constexpr int SRC_FPB = 32;
+constexpr int SRC_THREADS = 256;
+
+__device__ __forceinline__ uint32_t mulhilo32(uint32_t a, uint32_t b, uint32_t* hi) {
+  *hi = __umulhi(a, b);
+  return a * b;
+}
+
+// Philox4x32-10 (Salmon et al., SC'11), counter = (c0, c1, 0, 0), key = seed.
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t k0, uint32_t k1) {
+  uint32_t c2 = 0, c3 = 0;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    uint32_t hi0, hi1;
+    const uint32_t lo0 = mulhilo32(0xD2511F53u, c0, &hi0);
+    const uint32_t lo1 = mulhilo32(0xCD9E8D57u, c2, &hi1);
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+
+__device__ __forceinline__ float philox_normal(uint64_t seed, uint64_t idx) {
+  const uint64_t ctr = idx >> 2;
+  const uint4 r = philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), (uint32_t)seed, (uint32_t)(seed >> 32));
+  const int lane = (int)(idx & 3);
+  const uint32_t ua = (lane < 2) ? r.x : r.z, ub = (lane < 2) ? r.y : r.w;
+  const float u1 = ((float)ua + 1.0f) * 2.3283064365386963e-10f;  // (0,1]
+  const float u2 = (float)ub * 2.3283064365386963e-10f;
+  const float rad = sqrtf(-2.0f * __logf(u1));
+  float sn, cs;
+  sincospif(2.0f * u2, &sn, &cs);
+  return (lane & 1) ? rad * sn : rad * cs;
+}
+
+__global__ void __launch_bounds__(SRC_THREADS) source_kernel(SourceParams p) {
+  __shared__ double red[SRC_THREADS / 32];
+  __shared__ double s_prefix;
+  __shared__ double s_C[SRC_FPB];
+  __shared__ double s_finc[SRC_FPB];
+  __shared__ float s_f0[SRC_FPB];
+  const int b = blockIdx.y;
+  const int l0 = blockIdx.x * SRC_FPB;
+  const float* f0 = p.f0 + (size_t)b * p.T;
+  const double inv_sr = 1.0 / (double)p.sr;
+  const double dupp = (double)p.upp;
+
+  // (1) prefix of the wrapped per-frame phase advance over frames [0, l0)
+  double part = 0.0;
+  for (int j = threadIdx.x; j < l0; j += SRC_THREADS) {
+    const double adv = (double)f0[j] * inv_sr * dupp + 0.5;
+    part += (adv - floor(adv)) - 0.5;  // f0 >= 0 so fmod(adv, 1) == adv - floor(adv)
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < SRC_THREADS / 32; ++i) t += red[i];
+    s_prefix = t;
+  }
+  __syncthreads();
+  // (2) scan inside the span (<= 32 frames: one thread per frame, serial partial sums)
+  if (threadIdx.x < SRC_FPB) {
+    const int l = l0 + threadIdx.x;
+    double c = s_prefix;
+    for (int j = l0; j < l && j < p.T; ++j) {
+      const double adv = (double)f0[j] * inv_sr * dupp + 0.5;
+      c += (adv - floor(adv)) - 0.5;
+    }
+    s_C[threadIdx.x] = c - floor(c);  // phase only matters modulo 1
+    const float f = (l < p.T) ? f0[l] : 0.f;
+    s_f0[threadIdx.x] = f;
+    s_finc[threadIdx.x] = (double)f * inv_sr;
+  }
+  __syncthreads();
+  // (3) samples
+  const int nframes = min(SRC_FPB, p.T - l0);
+  const int nsamp = nframes * p.upp;
+  const size_t base = (size_t)b * p.T * p.upp + (size_t)l0 * p.upp;
+  for (int i = threadIdx.x; i < nsamp; i += SRC_THREADS) {
+    const int fr = i / p.upp;
+    const int k = i - fr * p.upp;
+    const double ph = s_finc[fr] * (double)(k + 1) + s_C[fr];
+    const float frac = (float)(ph - floor(ph));
+    const float sine = 0.1f * sinpif(2.0f * frac);
+    const float z = p.noise ? __ldg(p.noise + base + i) : philox_normal(p.seed, base + i);
+    const float v = (s_f0[fr] > 0.f) ? (sine + 0.003f * z) : ((0.1f / 3.0f) * z);
+    p.har[base + i] = tanhf(p.lin_w * v + p.lin_b);
+  }
+}
+
+cudaError_t launch_source(const SourceParams& p, cudaStream_t s) {
+  dim3 grid((p.T + SRC_FPB - 1) / SRC_FPB, p.B);
+  source_kernel<<<grid, SRC_THREADS, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// cond(g) folded into a per-item bias for conv_pre (hifigan_nsf.py:179-182).
+// ---------------------------------------------------------------------------
+__global__ void cond_kernel(const float* __restrict__ g, const float* __restrict__ Wc, const float* __restrict__ bc,
+                            const float* __restrict__ bpre, float* __restrict__ biasB, int B, int gin, int N) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (n >= N) return;
+  float acc = bpre[n];
+  if (g) {
+    acc += bc[n];
+    const float* w = Wc + (size_t)n * gin;
+    const float* gb = g + (size_t)b * gin;
+    for (int c = 0; c < gin; ++c) acc = fmaf(w[c], gb[c], acc);
+  }
+  biasB[(size_t)b * N + n] = acc;
+}
+
+cudaError_t launch_cond(const float* g, const float* Wc, const float* bias_cond, const float* bias_pre, float* biasB,
+                        int B, int gin, int N, cudaStream_t s) {
+  dim3 grid((N + 127) / 128, B);
+  cond_kernel<<<grid, 128, 0, s>>>(g, Wc, bias_cond, bias_pre, biasB, B, gin, N);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ T cvt_act(float v);
+template <> __device__ __forceinline__ float cvt_act<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half cvt_act<__half>(float v) { return __float2half_rn(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt_act<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+template <typename T>
+__global__ void pack_input_kernel(const float* __restrict__ x, T* __restrict__ act, int B, int C, int T_, int Lp) {
+  const size_t total = (size_t)B * (C / 8) * T_;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int t = (int)(i % T_);
+    const size_t bs = i / T_;
+    const int sl = (int)(bs % (C / 8));
+    const int b = (int)(bs / (C / 8));
+    const float* src = x + ((size_t)b * C + sl * 8) * T_ + t;
+    T* dst = act + ((bs * Lp) + PADL + t) * 8;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) dst[c] = cvt_act<T>(src[(size_t)c * T_]);
+  }
+}
+
+cudaError_t launch_pack_input(const float* x, void* act, int fmt, int B, int C, int T, int Lp, cudaStream_t s) {
+  const size_t total = (size_t)B * (C / 8) * T;
+  const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 16));
+  if (fmt == ACT_F32) pack_input_kernel<float><<<blocks, 256, 0, s>>>(x, (float*)act, B, C, T, Lp);
+  else if (fmt == ACT_F16) pack_input_kernel<__half><<<blocks, 256, 0, s>>>(x, (__half*)act, B, C, T, Lp);
+  else pack_input_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(x, (__nv_bfloat16*)act, B, C, T, Lp);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+__global__ void zero_pads_kernel(uint4* a0, uint4* a1, uint4* a2, int chunks_per_row, int L, int Lp) {
+  // one block per (b*slice, tensor); pad rows = [0,PADL) U [PADL+L, Lp)
+  uint4* base = (blockIdx.y == 0 ? a0 : (blockIdx.y == 1 ? a1 : a2));
+  if (!base) return;
+  const int right = Lp - PADL - L;
+  const int total = (PADL + right) * chunks_per_row;
+  uint4* sl = base + (size_t)blockIdx.x * Lp * chunks_per_row;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int r = i / chunks_per_row;
+    const int c = i - r * chunks_per_row;
+    const int row = (r < PADL) ? r : (L + r);  // r >= PADL: PADL + L + (r - PADL)
+    sl[(size_t)row * chunks_per_row + c] = make_uint4(0, 0, 0, 0);
+  }
+}
+
+cudaError_t launch_zero_pads(void* a0, void* a1, void* a2, int elem_bytes, int B, int C, int L, int Lp,
+                             cudaStream_t s) {
+  const int chunks = elem_bytes / 2;  // 16-byte chunks per 8-channel row
+  dim3 grid(B * (C / 8), 3);
+  zero_pads_kernel<<<grid, 256, 0, s>>>((uint4*)a0, (uint4*)a1, (uint4*)a2, chunks, L, Lp);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// x = ups(x) [already in p.x] + noise_convs[i](har)  (hifigan_nsf.py:199), then the
+// activated copy lrelu(x, 0.1) every ResBlock's first conv consumes (residuals.py:74).
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) noise_add_kernel(NoiseAddParams p) {
+  const int nsl = p.C / 8;
+  const size_t total = (size_t)p.B * nsl * p.L;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int row = (int)(i % p.L);
+    const size_t bs = i / p.L;
+    const int sl = (int)(bs % nsl);
+    const int b = (int)(bs / nsl);
+    const size_t off = (bs * p.Lp + PADL + row) * 8;
+    float v[8];
+    {
+      const float4 q0 = *reinterpret_cast<const float4*>(p.x + off);
+      const float4 q1 = *reinterpret_cast<const float4*>(p.x + off + 4);
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + sl * 8));
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + sl * 8 + 4));
+      v[0] = q0.x + b0.x; v[1] = q0.y + b0.y; v[2] = q0.z + b0.z; v[3] = q0.w + b0.w;
+      v[4] = q1.x + b1.x; v[5] = q1.y + b1.y; v[6] = q1.z + b1.z; v[7] = q1.w + b1.w;
+    }
+    const float* hb = p.har + (size_t)b * p.n_src;
+    const int s0 = row * p.stride - p.pad;
+    for (int j = 0; j < p.k; ++j) {
+      const int sidx = s0 + j;
+      if (sidx < 0 || sidx >= p.n_src) continue;
+      const float h = __ldg(hb + sidx);
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(p.w + (size_t)j * p.C + sl * 8));
+      const float4 w1 = __ldg(reinterpret_cast<const float4*>(p.w + (size_t)j * p.C + sl * 8 + 4));
+      v[0] = fmaf(h, w0.x, v[0]); v[1] = fmaf(h, w0.y, v[1]); v[2] = fmaf(h, w0.z, v[2]); v[3] = fmaf(h, w0.w, v[3]);
+      v[4] = fmaf(h, w1.x, v[4]); v[5] = fmaf(h, w1.y, v[5]); v[6] = fmaf(h, w1.z, v[6]); v[7] = fmaf(h, w1.w, v[7]);
+    }
+    *reinterpret_cast<float4*>(p.x + off) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p.x + off + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    T* a = reinterpret_cast<T*>(p.act) + off;
+    if (sizeof(T) == 4) {
+      *reinterpret_cast<float4*>(a) = make_float4(lrelu(v[0], p.slope), lrelu(v[1], p.slope), lrelu(v[2], p.slope), lrelu(v[3], p.slope));
+      *reinterpret_cast<float4*>(a + 4) = make_float4(lrelu(v[4], p.slope), lrelu(v[5], p.slope), lrelu(v[6], p.slope), lrelu(v[7], p.slope));
+    } else {
+      T tmp[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) tmp[c] = cvt_act<T>(lrelu(v[c], p.slope));
+      *reinterpret_cast<uint4*>(a) = *reinterpret_cast<uint4*>(tmp);
+    }
+  }
+}
+
+cudaError_t launch_noise_add(const NoiseAddParams& p, cudaStream_t s) {
+  const size_t total = (size_t)p.B * (p.C / 8) * p.L;
+  const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
+  if (p.act_fmt == ACT_F32) noise_add_kernel<float><<<blocks, 256, 0, s>>>(p);
+  else if (p.act_fmt == ACT_F16) noise_add_kernel<__half><<<blocks, 256, 0, s>>>(p);
+  else noise_add_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// Tail: leaky_relu(x) with the DEFAULT slope 0.01, conv_post (C->1, k=7, no bias), tanh
+// (hifigan_nsf.py:209-210).  One thread per output sample, fp32 throughout.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) post_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                   float* __restrict__ out, int B, int C, int L, int Lp, int k,
+                                                   float slope) {
+  extern __shared__ float sw[];  // [k][C]
+  for (int i = threadIdx.x; i < k * C; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
+  const int nsl = C / 8;
+  const int pad = (k - 1) / 2;
+  const size_t total = (size_t)B * L;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int t = (int)(i % L);
+    const int b = (int)(i / L);
+    float acc = 0.f;
+    for (int sl = 0; sl < nsl; ++sl) {
+      const float* xs = x + (((size_t)b * nsl + sl) * Lp + PADL) * 8;
+      for (int j = 0; j < k; ++j) {
+        const int tt = t + j - pad;
+        if (tt < 0 || tt >= L) continue;
+        const float4 q0 = *reinterpret_cast<const float4*>(xs + (size_t)tt * 8);
+        const float4 q1 = *reinterpret_cast<const float4*>(xs + (size_t)tt * 8 + 4);
+        const float* wj = sw + j * C + sl * 8;
+        acc = fmaf(lrelu(q0.x, slope), wj[0], acc); acc = fmaf(lrelu(q0.y, slope), wj[1], acc);
+        acc = fmaf(lrelu(q0.z, slope), wj[2], acc); acc = fmaf(lrelu(q0.w, slope), wj[3], acc);
+        acc = fmaf(lrelu(q1.x, slope), wj[4], acc); acc = fmaf(lrelu(q1.y, slope), wj[5], acc);
+        acc = fmaf(lrelu(q1.z, slope), wj[6], acc); acc = fmaf(lrelu(q1.w, slope), wj[7], acc);
+      }
+    }
+    out[i] = tanhf(acc);
+  }
+}
+
+cudaError_t launch_post(const float* x, const float* w, float* out, int B, int C, int L, int Lp, int k, float slope,
+                        cudaStream_t s) {
+  const size_t total = (size_t)B * L;
+  const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
+  post_kernel<<<blocks, 256, (size_t)k * C * sizeof(float), s>>>(x, w, out, B, C, L, Lp, k, slope);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+template <typename T>
+__global__ void unpack_kernel(const T* __restrict__ src, float* __restrict__ dst, int B, int C, int L, int Lp) {
+  const size_t total = (size_t)B * C * L;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int t = (int)(i % L);
+    const size_t bc = i / L;
+    const int c = (int)(bc % C);
+    const int b = (int)(bc / C);
+    dst[i] = (float)src[(((size_t)b * (C / 8) + (c >> 3)) * Lp + PADL + t) * 8 + (c & 7)];
+  }
+}
+
+cudaError_t launch_unpack(const void* src, int fmt, float* dst, int B, int C, int L, int Lp, cudaStream_t s) {
+  const size_t total = (size_t)B * C * L;
+  const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
+  if (fmt == ACT_F32) unpack_kernel<float><<<blocks, 256, 0, s>>>((const float*)src, dst, B, C, L, Lp);
+  else if (fmt == ACT_F16) unpack_kernel<__half><<<blocks, 256, 0, s>>>((const __half*)src, dst, B, C, L, Lp);
+  else unpack_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>((const __nv_bfloat16*)src, dst, B, C, L, Lp);
+  return cudaGetLastError();
+}
+
+}  // namespace rvcdec

@@ -1,0 +1,181 @@
+// Shared definitions for the NSF-HiFiGAN decoder kernels (sm_100a).
+//
+// HBM layout of every activation tensor ("blocked-8, time-major"):
+//   element (b, c, t) of a (B, C, L) tensor lives at
+//     ((b * (C/8) + c/8) * Lp + PADL + t) * 8 + (c % 8)
+//   with Lp = PADL + roundup(L, 512) + PADR rows.  A "row" is 8 consecutive
+//   channels of one time step (16 B in 16-bit, 32 B in fp32); the rows of one
+//   channel-slice are contiguous in time.  That makes
+//     * a conv tap a pure row offset (any dilation, no alignment constraint),
+//     * one channel-slice of a time tile a single contiguous run that a 1-D TMA
+//       bulk copy (cp.async.bulk) moves into shared memory,
+//     * the shared-memory image exactly the no-swizzle K-major UMMA operand
+//       layout (8x16B core matrices, SBO = 128 B, LBO = slice stride),
+//     * epilogue stores coalesced: 32 lanes = 32 consecutive rows.
+//   Rows [-PADL, 0) and [L, Lp-PADL) of 16-bit operand tensors are kept zero: they
+//   are the convolutions' zero padding (commons.py:19-27 get_padding).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rvcdec {
+
+constexpr int PADL = 32;
+constexpr int PADR = 32;
+constexpr int ROW_ROUND = 512;
+constexpr int MAX_TAPS = 12;
+constexpr int MAX_NTILES = 64;
+
+__host__ __device__ inline int padded_rows(int L) { return PADL + ((L + ROW_ROUND - 1) / ROW_ROUND) * ROW_ROUND + PADR; }
+
+enum ActFmt : int { ACT_F16 = 0, ACT_BF16 = 1, ACT_F32 = 2 };
+
+__host__ __device__ inline int act_bytes(int fmt) { return fmt == ACT_F32 ? 4 : 2; }
+
+// Epilogue of every convolution kernel (both back-ends):
+//   v = acc + bias[b*bias_bstride + n]
+//   if (res)    v += res[..]
+//   v *= scale
+//   if (sum_in) v += sum_in[..]
+//   if (out_f32) out_f32[..] = v
+//   if (out_act) out_act[..] = cvt(leaky_relu(v, slope))
+// Output column n of input row t maps to channel n % cout and time t*up + n / cout
+// (up > 1 is the polyphase transposed convolution: the phase is folded into N).
+struct Epilogue {
+  const float* bias;
+  const float* res;
+  const float* sum_in;
+  float* out_f32;
+  void* out_act;
+  float scale;
+  float slope;
+  int bias_bstride;
+  int act_fmt;   // format of out_act
+  int up;
+  int cout;      // physical channels of the output tensors
+  int L_out;     // valid rows of the output tensors
+  int Lp_out;    // padded rows of the output tensors
+};
+
+// One convolution as an implicit GEMM:  D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]
+struct ConvParams {
+  const void* act_in;      // blocked-8 input, format act_fmt_in
+  const void* w;           // packed weights (layout depends on the back-end)
+  int act_fmt_in;
+  int B, Cin, L_in, Lp_in;
+  int N_total;             // total GEMM columns (= up * cout)
+  int ntaps;
+  int halo;                // max |shift|
+  int shift[MAX_TAPS];
+  uint32_t tapmask[MAX_NTILES];  // per N tile: bit j set = tap j has non-zero weights
+  int m_tiles, n_tiles;    // tiles per batch item along time, tiles along N
+  Epilogue epi;
+};
+
+__device__ __forceinline__ float lrelu(float v, float slope) { return v > 0.f ? v : v * slope; }
+
+// Apply the epilogue to NV (4 or 8) consecutive GEMM columns n0.. of input row t_in of item b.
+template <int NV>
+__device__ __forceinline__ void epilogue_store(const Epilogue& e, int b, int t_in, int n0, float (&v)[NV]) {
+  const int r = n0 / e.cout;
+  const int co = n0 - r * e.cout;
+  const int row = t_in * e.up + r;
+  if (row >= e.L_out) return;
+  const float* bp = e.bias + (size_t)b * e.bias_bstride + n0;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) v[i] += __ldg(bp + i);
+  const size_t off = (((size_t)b * (e.cout >> 3) + (co >> 3)) * e.Lp_out + PADL + row) * 8 + (co & 7);
+  if (e.res) {
+#pragma unroll
+    for (int i = 0; i < NV; i += 4) {
+      const float4 q = *reinterpret_cast<const float4*>(e.res + off + i);
+      v[i] += q.x; v[i + 1] += q.y; v[i + 2] += q.z; v[i + 3] += q.w;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) v[i] *= e.scale;
+  if (e.sum_in) {
+#pragma unroll
+    for (int i = 0; i < NV; i += 4) {
+      const float4 q = *reinterpret_cast<const float4*>(e.sum_in + off + i);
+      v[i] += q.x; v[i + 1] += q.y; v[i + 2] += q.z; v[i + 3] += q.w;
+    }
+  }
+  if (e.out_f32) {
+#pragma unroll
+    for (int i = 0; i < NV; i += 4)
+      *reinterpret_cast<float4*>(e.out_f32 + off + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+  }
+  if (e.out_act) {
+    if (e.act_fmt == ACT_F32) {
+      float* o = reinterpret_cast<float*>(e.out_act) + off;
+#pragma unroll
+      for (int i = 0; i < NV; i += 4)
+        *reinterpret_cast<float4*>(o + i) = make_float4(lrelu(v[i], e.slope), lrelu(v[i + 1], e.slope),
+                                                        lrelu(v[i + 2], e.slope), lrelu(v[i + 3], e.slope));
+    } else {
+      uint32_t pk[NV / 2];
+      if (e.act_fmt == ACT_F16) {
+#pragma unroll
+        for (int i = 0; i < NV; i += 2) {
+          __half2 h = __floats2half2_rn(lrelu(v[i], e.slope), lrelu(v[i + 1], e.slope));
+          pk[i / 2] = *reinterpret_cast<uint32_t*>(&h);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < NV; i += 2) {
+          __nv_bfloat162 h = __floats2bfloat162_rn(lrelu(v[i], e.slope), lrelu(v[i + 1], e.slope));
+          pk[i / 2] = *reinterpret_cast<uint32_t*>(&h);
+        }
+      }
+      uint16_t* o = reinterpret_cast<uint16_t*>(e.out_act) + off;
+      if (NV == 8) *reinterpret_cast<uint4*>(o) = make_uint4(pk[0], pk[1], pk[NV / 2 - 2], pk[NV / 2 - 1]);
+      else *reinterpret_cast<uint2*>(o) = make_uint2(pk[0], pk[1]);
+    }
+  }
+}
+
+// ---- launchers implemented in the .cu files --------------------------------
+cudaError_t launch_conv_f32(const ConvParams& p, cudaStream_t s);
+// returns cudaErrorInvalidValue when no instantiation fits (N tile / K chunk)
+cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms, cudaStream_t s);
+bool conv_mma_supported(int n_tile, int kc);
+
+struct SourceParams {
+  const float* f0;      // (B, T)
+  const float* noise;   // (B, T*upp) or null
+  float* har;           // (B, T*upp)
+  uint64_t seed;
+  int B, T, upp;
+  float sr, lin_w, lin_b;
+};
+cudaError_t launch_source(const SourceParams& p, cudaStream_t s);
+
+// biasB[b][n] = bias_pre[n] + (g ? bias_cond[n] + sum_c Wc[n][c] g[b][c] : 0)
+cudaError_t launch_cond(const float* g, const float* Wc, const float* bias_cond, const float* bias_pre,
+                        float* biasB, int B, int gin, int N, cudaStream_t s);
+// (B, C, T) fp32 contiguous -> blocked-8 act tensor (format fmt)
+cudaError_t launch_pack_input(const float* x, void* act, int fmt, int B, int C, int T, int Lp, cudaStream_t s);
+// zero the pad rows [-PADL,0) and [L, Lp-PADL) of up to 3 blocked-8 tensors of the same geometry
+cudaError_t launch_zero_pads(void* a0, void* a1, void* a2, int elem_bytes, int B, int C, int L, int Lp, cudaStream_t s);
+// x += noise_conv(har) (+bias); writes x (fp32 blocked) and act = lrelu(x, slope)
+struct NoiseAddParams {
+  const float* har;     // (B, n_src)
+  const float* w;       // [k][C] transposed noise_conv weight
+  const float* bias;    // [C]
+  float* x;             // fp32 blocked (B, C, L)
+  void* act;            // blocked act out
+  int act_fmt;
+  int B, C, L, Lp, n_src, k, stride, pad;
+  float slope;
+};
+cudaError_t launch_noise_add(const NoiseAddParams& p, cudaStream_t s);
+// out[b][t] = tanh(sum_j sum_c w[j][c] * lrelu(x[b][c][t+j-pad], slope))
+cudaError_t launch_post(const float* x, const float* w, float* out, int B, int C, int L, int Lp, int k, float slope,
+                        cudaStream_t s);
+// blocked-8 (fp32 or 16-bit) -> plain (B, C, L) fp32, for tests
+cudaError_t launch_unpack(const void* src, int fmt, float* dst, int B, int C, int L, int Lp, cudaStream_t s);
+
+}  // namespace rvcdec

@@ -1,0 +1,340 @@
+// Tensor-core back-end: every convolution of the decoder as a tcgen05 implicit GEMM (sm_100a).
+//
+//   D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]      (fp32 accumulate in TMEM)
+//
+// CTA = 6 warps, warp-specialised, persistent over (item, time-tile, N-tile):
+//   warp 0   TMA producer   1-D bulk copies (cp.async.bulk, UBLKCP) of activation slices and
+//                           weight blocks into shared memory, completion on mbarriers
+//   warp 1   MMA issuer     one thread issues tcgen05.mma (kind::f16, M=128, N=N_TILE, K=16),
+//                           tcgen05.commit releases smem stages / publishes the accumulator
+//   warps 2-5 epilogue      tcgen05.ld accumulator -> registers -> fused epilogue (bias, residual,
+//                           MRF average, leaky_relu, 16-bit convert) -> coalesced global stores
+//
+// Shared-memory operand layout: NO swizzle, K-major "interleaved" core matrices.  The blocked-8
+// HBM layout ([slice][row][8 ch]) copied verbatim IS that layout: 8 rows x 16 B core matrices,
+// consecutive 8-row groups 128 B apart (SBO), the two K halves of an MMA one slice apart (LBO).
+// A convolution tap is then a +/- n*16 B change of the descriptor start address - any dilation,
+// no 1024 B swizzle-atom alignment to respect - and the tile (+halo) is loaded once per K chunk
+// and reused by every tap.
+//
+// Time tile = MB x 128 rows (MB accumulators side by side in TMEM) so that one weight block
+// fetched from L2 feeds MB MMAs; accumulators are double-buffered in TMEM when they fit
+// (2*MB*N_TILE <= 512 columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include <algorithm>
+#include <cstdio>
+#include "common.cuh"
+
+namespace rvcdec {
+
+// ------------------------------ PTX wrappers -------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded wait: a protocol bug must trap (launch error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  long long t_start = 0;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return;
+    if ((spin & 1023u) == 1023u) {
+      const long long now = clock64();
+      if (t_start == 0) t_start = now;
+      else if (now - t_start > 4000000000LL) {  // ~2 s
+        printf("rvcdec conv_mma: mbarrier timeout (block %d thread %d bar 0x%x parity %u)\n", (int)blockIdx.x,
+               (int)threadIdx.x, bar, parity);
+        __trap();
+      }
+    }
+  }
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor, no swizzle, K-major (PTX ISA "tcgen05 matrix descriptor"):
+//   [0,14) start address >> 4, [16,30) leading-dim byte offset >> 4 (stride between the two
+//   8-element K halves), [32,46) stride-dim byte offset >> 4 (stride between 8-row groups),
+//   [46,48) descriptor version = 1 on sm_100, [61,64) swizzle mode = 0 (none).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | ((uint64_t)1 << 46);
+}
+// Instruction descriptor for kind::f16: D fp32 (bit 4), A/B format (0 = f16, 1 = bf16) at bits 7 / 10,
+// both operands K-major (bits 15, 16 = 0), N >> 3 at bits [17,23), M >> 4 at bits [24,29).
+__host__ __device__ inline uint32_t make_idesc(int fmt, int n) {
+  const uint32_t f = (fmt == ACT_BF16) ? 1u : 0u;
+  return (1u << 4) | (f << 7) | (f << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+// ------------------------------ kernel -------------------------------------
+template <int N_TILE, int MB, int KC, int B_STAGES>
+struct MmaCfg {
+  static constexpr int MT = MB * 128;
+  static constexpr int ACC_STAGES = (2 * MB * N_TILE <= 512) ? 2 : 1;
+  static constexpr int ACC_COLS = ACC_STAGES * MB * N_TILE;
+  static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128 : ACC_COLS <= 256 ? 256 : 512;
+  static constexpr int A_ROWS = MT + 2 * PADL;
+  static constexpr int A_SLICE_BYTES = A_ROWS * 16;
+  static constexpr int A_BUF_BYTES = (KC / 8) * A_SLICE_BYTES;
+  static constexpr int B_SLICE_BYTES = N_TILE * 16;
+  static constexpr int B_STAGE_BYTES = (KC / 8) * B_SLICE_BYTES;
+  static constexpr int NUM_BARS = 2 + 2 + 2 * B_STAGES + 2 * ACC_STAGES;
+  static constexpr int SMEM_BYTES = 128 /*align slack*/ + 2 * A_BUF_BYTES + B_STAGES * B_STAGE_BYTES + NUM_BARS * 8 + 16;
+  static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+};
+
+constexpr int MMA_THREADS = 192;
+
+template <int N_TILE, int MB, int KC, int B_STAGES>
+__global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 127u) & ~127u;
+  const uint32_t a_smem = smem_base;
+  const uint32_t b_smem = a_smem + 2 * Cfg::A_BUF_BYTES;
+  const uint32_t bars = b_smem + B_STAGES * Cfg::B_STAGE_BYTES;
+  const uint32_t a_full = bars, a_empty = bars + 16, b_full = bars + 32, b_empty = b_full + 8 * B_STAGES,
+                 acc_full = b_empty + 8 * B_STAGES, acc_empty = acc_full + 8 * Cfg::ACC_STAGES;
+  const uint32_t tmem_slot = acc_empty + 8 * Cfg::ACC_STAGES;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
+    for (int i = 0; i < B_STAGES; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
+    for (int i = 0; i < Cfg::ACC_STAGES; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, 128); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                 "r"((uint32_t)Cfg::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  const int nkc = p.Cin / KC;
+  const int nsl = p.Cin >> 3;
+  const int tiles_per_item = p.m_tiles * p.n_tiles;
+  const int total_tiles = p.B * tiles_per_item;
+  const int rows = Cfg::MT + 2 * p.halo;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t a_it = 0, b_it = 0;
+      const uint8_t* act = reinterpret_cast<const uint8_t*>(p.act_in);
+      const uint8_t* wgt = reinterpret_cast<const uint8_t*>(p.w);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int b = tile / tiles_per_item;
+        const int rem = tile - b * tiles_per_item;
+        const int m_tile = rem / p.n_tiles;
+        const int n_tile = rem - m_tile * p.n_tiles;
+        const int t0 = m_tile * Cfg::MT;
+        const uint32_t mask = p.tapmask[n_tile];
+        for (int kc = 0; kc < nkc; ++kc) {
+          const uint32_t ab = a_it & 1u;
+          mbar_wait(a_empty + 8 * ab, ((a_it >> 1) & 1u) ^ 1u);
+          mbar_expect_tx(a_full + 8 * ab, (uint32_t)(KC / 8) * rows * 16);
+#pragma unroll
+          for (int sl = 0; sl < KC / 8; ++sl) {
+            const uint8_t* src =
+                act + (((size_t)b * nsl + kc * (KC / 8) + sl) * p.Lp_in + PADL + t0 - p.halo) * 16;
+            bulk_g2s(a_smem + ab * Cfg::A_BUF_BYTES + sl * Cfg::A_SLICE_BYTES, src, (uint32_t)rows * 16,
+                     a_full + 8 * ab);
+          }
+          ++a_it;
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            if (!((mask >> tap) & 1u)) continue;
+            const uint32_t bs = b_it % B_STAGES;
+            mbar_wait(b_empty + 8 * bs, ((b_it / B_STAGES) & 1u) ^ 1u);
+            mbar_expect_tx(b_full + 8 * bs, Cfg::B_STAGE_BYTES);
+            const uint8_t* src = wgt + (((size_t)n_tile * p.ntaps + tap) * nkc + kc) * Cfg::B_STAGE_BYTES;
+            bulk_g2s(b_smem + bs * Cfg::B_STAGE_BYTES, src, Cfg::B_STAGE_BYTES, b_full + 8 * bs);
+            ++b_it;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      uint32_t a_it = 0, b_it = 0, acc_it = 0;
+      const uint32_t idesc = make_idesc(p.act_fmt_in, N_TILE);
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int rem = tile % tiles_per_item;
+        const int n_tile = rem % p.n_tiles;
+        const uint32_t mask = p.tapmask[n_tile];
+        const uint32_t as = acc_it % Cfg::ACC_STAGES;
+        mbar_wait(acc_empty + 8 * as, ((acc_it / Cfg::ACC_STAGES) & 1u) ^ 1u);
+        tc_fence_after();
+        const uint32_t d_base = tmem_base + as * (MB * N_TILE);
+        bool fresh = true;
+        for (int kc = 0; kc < nkc; ++kc) {
+          const uint32_t ab = a_it & 1u;
+          mbar_wait(a_full + 8 * ab, (a_it >> 1) & 1u);
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            if (!((mask >> tap) & 1u)) continue;
+            const uint32_t bs = b_it % B_STAGES;
+            mbar_wait(b_full + 8 * bs, (b_it / B_STAGES) & 1u);
+            tc_fence_after();
+            const uint32_t a_row0 = a_smem + ab * Cfg::A_BUF_BYTES + (uint32_t)(p.halo + p.shift[tap]) * 16;
+            const uint32_t b_row0 = b_smem + bs * Cfg::B_STAGE_BYTES;
+#pragma unroll
+            for (int mb = 0; mb < MB; ++mb) {
+#pragma unroll
+              for (int ks = 0; ks < KC / 16; ++ks) {
+                const uint64_t adesc = make_smem_desc(a_row0 + mb * 128 * 16 + 2 * ks * Cfg::A_SLICE_BYTES,
+                                                      Cfg::A_SLICE_BYTES, 128);
+                const uint64_t bdesc =
+                    make_smem_desc(b_row0 + 2 * ks * Cfg::B_SLICE_BYTES, Cfg::B_SLICE_BYTES, 128);
+                tc_mma_f16(d_base + mb * N_TILE, adesc, bdesc, idesc, (fresh && ks == 0) ? 0u : 1u);
+              }
+            }
+            fresh = false;
+            tc_commit(b_empty + 8 * bs);
+            ++b_it;
+          }
+          tc_commit(a_empty + 8 * ab);
+          ++a_it;
+        }
+        tc_commit(acc_full + 8 * as);
+        ++acc_it;
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================== epilogue warps =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    uint32_t acc_it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int b = tile / tiles_per_item;
+      const int rem = tile - b * tiles_per_item;
+      const int m_tile = rem / p.n_tiles;
+      const int n_tile = rem - m_tile * p.n_tiles;
+      const int t0 = m_tile * Cfg::MT;
+      const uint32_t as = acc_it % Cfg::ACC_STAGES;
+      mbar_wait(acc_full + 8 * as, (acc_it / Cfg::ACC_STAGES) & 1u);
+      tc_fence_after();
+#pragma unroll 1
+      for (int mb = 0; mb < MB; ++mb) {
+        const int t_in = t0 + mb * 128 + q * 32 + lane;
+#pragma unroll 1
+        for (int c0 = 0; c0 < N_TILE; c0 += 32) {
+          uint32_t r[32];
+          tc_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (MB * N_TILE) + mb * N_TILE + c0, r);
+          if (t_in < p.L_in) {
+#pragma unroll
+            for (int s8 = 0; s8 < 4; ++s8) {
+              float v[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[s8 * 8 + i]);
+              epilogue_store<8>(p.epi, b, t_in, n_tile * N_TILE + c0 + s8 * 8, v);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(acc_empty + 8 * as);
+      ++acc_it;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"((uint32_t)Cfg::TMEM_COLS)
+                 : "memory");
+  }
+}
+
+template <int N_TILE, int MB, int KC, int B_STAGES>
+static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s) {
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES>;
+  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES>;
+  {  // per-device attribute; cheap enough to set on every launch
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+  }
+  if (p.Cin % KC != 0 || p.N_total % N_TILE != 0 || p.halo > PADL || p.ntaps > MAX_TAPS) return cudaErrorInvalidValue;
+  ConvParams q = p;
+  q.m_tiles = (p.L_in + Cfg::MT - 1) / Cfg::MT;
+  q.n_tiles = p.N_total / N_TILE;
+  if (q.n_tiles > MAX_NTILES) return cudaErrorInvalidValue;
+  const long long total = (long long)q.B * q.m_tiles * q.n_tiles;
+  if (total <= 0 || total > 0x7fffffffLL) return cudaErrorInvalidValue;
+  const int grid = (int)(total < num_sms ? total : num_sms);
+  kern<<<grid, MMA_THREADS, Cfg::SMEM_BYTES, s>>>(q);
+  return cudaGetLastError();
+}
+
+bool conv_mma_supported(int n_tile, int kc) {
+  return (n_tile == 256 && kc == 64) || (n_tile == 128 && kc == 64) || (n_tile == 64 && kc == 64) ||
+         (n_tile == 32 && kc == 32);
+}
+
+cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms, cudaStream_t s) {
+  if (n_tile == 256 && kc == 64) return launch_inst<256, 2, 64, 4>(p, num_sms, s);
+  if (n_tile == 128 && kc == 64) return launch_inst<128, 2, 64, 6>(p, num_sms, s);
+  if (n_tile == 64 && kc == 64) return launch_inst<64, 4, 64, 4>(p, num_sms, s);
+  if (n_tile == 32 && kc == 32) return launch_inst<32, 4, 32, 4>(p, num_sms, s);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace rvcdec

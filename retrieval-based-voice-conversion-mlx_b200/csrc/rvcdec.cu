@@ -1,0 +1,836 @@
+// librvcdec.so - C ABI (include/rvcdec.h) over the sm_100a decoder kernels.
+// Host side: weight-norm folding and repacking at load time, workspace carving, and the
+// launch sequence of HiFiGANNSFGenerator.forward (reference hifigan_nsf.py:173-212).
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/rvcdec.h"
+#include "common.cuh"
+
+using namespace rvcdec;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CK(expr)                                                                                  \
+  do {                                                                                            \
+    cudaError_t _e = (expr);                                                                      \
+    if (_e != cudaSuccess)                                                                        \
+      return fail(RVCDEC_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+struct ConvLayer {
+  std::string name;
+  int Cin = 0, N_total = 0, cout = 0, up = 1, ntaps = 0, halo = 0;
+  int shift[MAX_TAPS] = {0};
+  double macs_per_row = 0;  // algorithmic MACs per INPUT row (zero-padded polyphase taps not counted)
+  std::vector<float> wf;    // [tap][ci][N_total]
+  std::vector<float> bias;  // [N_total]
+  std::vector<uint32_t> mask_f32;
+  // tensor-core image
+  int n_tile = 0, kc = 0;
+  std::vector<uint32_t> mask_mma;
+  std::vector<uint16_t> wp[2];  // [fmt] f16 / bf16
+  // device copies
+  float* d_wf = nullptr;
+  float* d_bias = nullptr;
+  uint16_t* d_wp[2] = {nullptr, nullptr};
+};
+
+struct NoiseLayer {
+  int C = 0, k = 0, stride = 1, pad = 0;
+  std::vector<float> w, bias;  // w: [k][C]
+  float* d_w = nullptr;
+  float* d_bias = nullptr;
+};
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+struct rvcdec_handle {
+  rvcdec_config cfg{};
+  int device = 0;
+  int num_sms = 148;
+  int upp = 1;
+  int nups = 0, nk = 0, nd = 0;
+  std::vector<int> ch;  // channels after each upsample
+  bool loaded = false;
+  bool fast_ok = false;
+  std::string fast_why;
+  ConvLayer conv_pre;
+  std::vector<ConvLayer> ups;
+  std::vector<ConvLayer> rbconv;  // index ((i*nk + j)*nd + m)*2 + which
+  std::vector<NoiseLayer> noise;
+  std::vector<float> post_w;  // [k][C]
+  std::vector<float> cond_w, cond_b;
+  float lin_w = 1.f, lin_b = 0.f;
+  float* d_post_w = nullptr;
+  float* d_cond_w = nullptr;
+  float* d_cond_b = nullptr;
+  float* d_zero_bias = nullptr;
+  std::vector<void*> dev_allocs;
+  int64_t launches = 0;
+  int debug_stop = 0;
+  // profiling (bench.py): one event before every launch, groups aggregated on read
+  bool prof_on = false;
+  struct ProfMark { int group; double flops; double bytes; cudaEvent_t ev; };
+  std::vector<ProfMark> prof_marks;
+  std::vector<cudaEvent_t> prof_pool;
+  std::vector<std::string> prof_names;
+  std::vector<double> prof_ms, prof_flops, prof_bytes;
+  std::vector<int64_t> prof_launches;
+  // forward_host state
+  cudaStream_t stream = nullptr;
+  void* hbuf = nullptr;
+  size_t hbuf_bytes = 0;
+};
+
+namespace {
+
+struct TensorMap {
+  std::map<std::string, const rvcdec_tensor*> m;
+  const rvcdec_tensor* find(const std::string& n) const {
+    auto it = m.find(n);
+    return it == m.end() ? nullptr : it->second;
+  }
+};
+
+// w = v * (g / ||v||_2 over all dims but 0)  (torch parametrizations.weight_norm, dim=0)
+int get_weight(const TensorMap& tm, const std::string& base, int64_t d0, int64_t rest, std::vector<float>& out) {
+  out.resize((size_t)d0 * rest);
+  if (const rvcdec_tensor* w = tm.find(base + ".weight")) {
+    if (w->numel != d0 * rest) return fail(RVCDEC_ERR_WEIGHTS, "%s.weight: expected %lld elements, got %lld", base.c_str(), (long long)(d0 * rest), (long long)w->numel);
+    memcpy(out.data(), w->data, sizeof(float) * out.size());
+    return 0;
+  }
+  const rvcdec_tensor* g = tm.find(base + ".parametrizations.weight.original0");
+  const rvcdec_tensor* v = tm.find(base + ".parametrizations.weight.original1");
+  if (!g || !v) {
+    g = tm.find(base + ".weight_g");
+    v = tm.find(base + ".weight_v");
+  }
+  if (!g || !v) return fail(RVCDEC_ERR_WEIGHTS, "missing weight for %s (looked for .weight, .parametrizations.weight.original0/1, .weight_g/.weight_v)", base.c_str());
+  if (g->numel != d0 || v->numel != d0 * rest) return fail(RVCDEC_ERR_WEIGHTS, "%s: weight-norm tensors have wrong size", base.c_str());
+  for (int64_t i = 0; i < d0; ++i) {
+    const float* vi = v->data + i * rest;
+    double ss = 0.0;
+    for (int64_t k = 0; k < rest; ++k) ss += (double)vi[k] * (double)vi[k];
+    const float scale = (float)((double)g->data[i] / std::sqrt(ss));
+    for (int64_t k = 0; k < rest; ++k) out[(size_t)(i * rest + k)] = vi[k] * scale;
+  }
+  return 0;
+}
+
+int get_vec(const TensorMap& tm, const std::string& name, int64_t n, std::vector<float>& out) {
+  const rvcdec_tensor* t = tm.find(name);
+  if (!t) return fail(RVCDEC_ERR_WEIGHTS, "missing tensor %s", name.c_str());
+  if (t->numel != n) return fail(RVCDEC_ERR_WEIGHTS, "%s: expected %lld elements, got %lld", name.c_str(), (long long)n, (long long)t->numel);
+  out.assign(t->data, t->data + n);
+  return 0;
+}
+
+// Conv1d weight (Cout, Cin, k), dilation d, "same" zero padding -> taps
+void pack_conv(ConvLayer& L, const std::vector<float>& W, int Cout, int Cin, int k, int d) {
+  L.Cin = Cin; L.N_total = Cout; L.cout = Cout; L.up = 1; L.ntaps = k; L.halo = (k - 1) / 2 * d;
+  L.macs_per_row = (double)Cin * Cout * k;
+  L.wf.assign((size_t)k * Cin * Cout, 0.f);
+  for (int j = 0; j < k; ++j) {
+    L.shift[j] = (j - (k - 1) / 2) * d;
+    for (int ci = 0; ci < Cin; ++ci)
+      for (int co = 0; co < Cout; ++co) L.wf[((size_t)j * Cin + ci) * Cout + co] = W[((size_t)co * Cin + ci) * k + j];
+  }
+}
+
+// ConvTranspose1d weight (Cin, Cout, k), stride u, padding p, output length u*L_in.
+// Polyphase form: y[t*u + r] = sum_m x[t + q_r - m] * w[:, :, r' + m*u],  r' = (r+p) % u, q_r = (r+p) / u.
+// Written as an ordinary convolution over input shifts s = q_r - m with N = u*Cout columns (n = r*Cout + co).
+int pack_ups(ConvLayer& L, const std::vector<float>& W, int Cin, int Cout, int k, int u, int p) {
+  int smin = 1 << 30, smax = -(1 << 30);
+  for (int r = 0; r < u; ++r) {
+    const int rp = (r + p) % u, q = (r + p) / u;
+    for (int m = 0; rp + m * u < k; ++m) { smin = std::min(smin, q - m); smax = std::max(smax, q - m); }
+  }
+  const int nt = smax - smin + 1;
+  if (nt > MAX_TAPS) return fail(RVCDEC_ERR_ARG, "upsample kernel %d / rate %d needs %d input shifts (max %d)", k, u, nt, MAX_TAPS);
+  L.Cin = Cin; L.N_total = u * Cout; L.cout = Cout; L.up = u; L.ntaps = nt;
+  L.macs_per_row = (double)Cin * Cout * k;
+  L.halo = std::max(std::abs(smin), std::abs(smax));
+  L.wf.assign((size_t)nt * Cin * L.N_total, 0.f);
+  for (int t = 0; t < nt; ++t) L.shift[t] = smin + t;
+  for (int r = 0; r < u; ++r) {
+    const int rp = (r + p) % u, q = (r + p) / u;
+    for (int m = 0; rp + m * u < k; ++m) {
+      const int t = (q - m) - smin;
+      for (int ci = 0; ci < Cin; ++ci)
+        for (int co = 0; co < Cout; ++co)
+          L.wf[((size_t)t * Cin + ci) * L.N_total + r * Cout + co] = W[((size_t)ci * Cout + co) * k + rp + m * u];
+    }
+  }
+  return 0;
+}
+
+uint32_t tap_mask(const ConvLayer& L, int col0, int ncols) {
+  uint32_t mask = 0;
+  for (int t = 0; t < L.ntaps; ++t) {
+    bool nz = false;
+    for (int ci = 0; ci < L.Cin && !nz; ++ci) {
+      const float* row = &L.wf[((size_t)t * L.Cin + ci) * L.N_total];
+      for (int n = col0; n < std::min(col0 + ncols, L.N_total); ++n)
+        if (row[n] != 0.f) { nz = true; break; }
+    }
+    if (nz) mask |= 1u << t;
+  }
+  return mask ? mask : 1u;
+}
+
+uint16_t to16(float v, int fmt) {
+  if (fmt == ACT_F16) { __half h = __float2half_rn(v); uint16_t u; memcpy(&u, &h, 2); return u; }
+  __nv_bfloat16 h = __float2bfloat16_rn(v); uint16_t u; memcpy(&u, &h, 2); return u;
+}
+
+void finish_layer(ConvLayer& L, bool want_mma) {
+  L.mask_f32.clear();
+  for (int c0 = 0; c0 < L.N_total; c0 += 64) L.mask_f32.push_back(tap_mask(L, c0, 64));
+  L.n_tile = 0; L.kc = 0;
+  if (!want_mma) return;
+  for (int nt : {256, 128, 64, 32}) {
+    if (L.N_total % nt) continue;
+    const int kc = (nt == 32) ? 32 : 64;
+    if (L.Cin % kc) continue;
+    if (L.N_total / nt > MAX_NTILES) continue;
+    if (!conv_mma_supported(nt, kc)) continue;
+    L.n_tile = nt; L.kc = kc;
+    break;
+  }
+  if (!L.n_tile) return;
+  const int nt = L.n_tile, kc = L.kc, nkc = L.Cin / kc, ntiles = L.N_total / nt;
+  L.mask_mma.clear();
+  for (int i = 0; i < ntiles; ++i) L.mask_mma.push_back(tap_mask(L, i * nt, nt));
+  for (int fmt = 0; fmt < 2; ++fmt) {
+    std::vector<uint16_t>& wp = L.wp[fmt];
+    wp.assign((size_t)L.ntaps * L.Cin * L.N_total, 0);
+    size_t o = 0;
+    for (int tile = 0; tile < ntiles; ++tile)
+      for (int t = 0; t < L.ntaps; ++t)
+        for (int c = 0; c < nkc; ++c)
+          for (int sl = 0; sl < kc / 8; ++sl)
+            for (int n = 0; n < nt; ++n)
+              for (int e = 0; e < 8; ++e)
+                wp[o++] = to16(L.wf[((size_t)t * L.Cin + c * kc + sl * 8 + e) * L.N_total + tile * nt + n], fmt);
+  }
+}
+
+template <typename T>
+int upload(rvcdec_handle* h, const std::vector<T>& v, T** dptr) {
+  if (v.empty()) { *dptr = nullptr; return 0; }
+  void* d = nullptr;
+  CK(cudaMalloc(&d, v.size() * sizeof(T)));
+  h->dev_allocs.push_back(d);
+  CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *dptr = (T*)d;
+  return 0;
+}
+
+int upload_layer(rvcdec_handle* h, ConvLayer& L) {
+  int rc;
+  if ((rc = upload(h, L.wf, &L.d_wf))) return rc;
+  if ((rc = upload(h, L.bias, &L.d_bias))) return rc;
+  for (int f = 0; f < 2; ++f)
+    if ((rc = upload(h, L.wp[f], &L.d_wp[f]))) return rc;
+  return 0;
+}
+
+void free_device(rvcdec_handle* h) {
+  for (void* p : h->dev_allocs) cudaFree(p);
+  h->dev_allocs.clear();
+}
+
+// ---- per-mode formats ------------------------------------------------------
+// mode 0: fp32 everywhere.  mode 1: bf16 operands up to and including stage 1, fp16 after
+// (SURVEY.md 8d numerics probe).  mode 2: fp16 everywhere.  mode 3: bf16 everywhere.
+int fmt_pre(int mode) { return mode == 0 ? ACT_F32 : (mode == 2 ? ACT_F16 : ACT_BF16); }
+int fmt_stage(int mode, int i) {
+  if (mode == 0) return ACT_F32;
+  if (mode == 2) return ACT_F16;
+  if (mode == 3) return ACT_BF16;
+  return i <= 1 ? ACT_BF16 : ACT_F16;
+}
+
+struct Workspace {
+  float* har; float* biasB; void* xin; void* pre;
+  float* xs0; float* xr; float* sum; void* a0; void* a1; void* a2;
+  size_t bytes;
+};
+
+Workspace carve(const rvcdec_handle* h, void* base, int B, int T, int mode) {
+  Workspace w{};
+  size_t off = 0;
+  auto take = [&](size_t n) { size_t o = off; off += align_up(n, 256); return base ? (void*)((uint8_t*)base + o) : (void*)nullptr; };
+  const int C0 = h->cfg.upsample_initial_channel;
+  const int LpT = padded_rows(T);
+  w.har = (float*)take((size_t)B * T * h->upp * 4);
+  w.biasB = (float*)take((size_t)B * C0 * 4);
+  w.xin = take((size_t)B * h->cfg.initial_channel * LpT * act_bytes(fmt_pre(mode)));
+  w.pre = take((size_t)B * C0 * LpT * act_bytes(fmt_pre(mode)));
+  size_t emax = 0;
+  int L = T;
+  for (int i = 0; i < h->nups; ++i) {
+    L *= h->cfg.upsample_rates[i];
+    emax = std::max(emax, (size_t)h->ch[i] * padded_rows(L));
+  }
+  const size_t asz = mode == 0 ? 4 : 2;
+  w.xs0 = (float*)take((size_t)B * emax * 4);
+  w.xr = (float*)take((size_t)B * emax * 4);
+  w.sum = (float*)take((size_t)B * emax * 4);
+  w.a0 = take((size_t)B * emax * asz);
+  w.a1 = take((size_t)B * emax * asz);
+  w.a2 = take((size_t)B * emax * asz);
+  w.bytes = off;
+  return w;
+}
+
+int prof_group(rvcdec_handle* h, const std::string& name) {
+  for (size_t i = 0; i < h->prof_names.size(); ++i)
+    if (h->prof_names[i] == name) return (int)i;
+  h->prof_names.push_back(name);
+  h->prof_ms.push_back(0); h->prof_flops.push_back(0); h->prof_bytes.push_back(0); h->prof_launches.push_back(0);
+  return (int)h->prof_names.size() - 1;
+}
+
+// Record an event in front of the next launch (group < 0 closes the pass).
+int prof_mark(rvcdec_handle* h, const char* group, double flops, double bytes, cudaStream_t s) {
+  if (!h->prof_on) return 0;
+  cudaEvent_t ev;
+  if (!h->prof_pool.empty()) { ev = h->prof_pool.back(); h->prof_pool.pop_back(); }
+  else CK(cudaEventCreate(&ev));
+  CK(cudaEventRecord(ev, s));
+  h->prof_marks.push_back({group ? prof_group(h, group) : -1, flops, bytes, ev});
+  return 0;
+}
+#define MARK(group, flops, bytes) do { int _rc = prof_mark(h, group, flops, bytes, s); if (_rc) return _rc; } while (0)
+
+int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, int fmt_in, const void* act_in, int B,
+             int L_in, const Epilogue& epi, cudaStream_t s) {
+  if (h->prof_on) {
+    const double rows_in = (double)B * L_in, el_out = (double)B * L_in * L.N_total;
+    double bytes = rows_in * L.Cin * act_bytes(fmt_in) + (epi.res ? el_out * 4 : 0) + (epi.sum_in ? el_out * 4 : 0) +
+                   (epi.out_f32 ? el_out * 4 : 0) + (epi.out_act ? el_out * act_bytes(epi.act_fmt) : 0);
+    MARK(group, 2.0 * rows_in * L.macs_per_row, bytes);
+  }
+  ConvParams p{};
+  p.act_in = act_in;
+  p.act_fmt_in = fmt_in;
+  p.B = B; p.Cin = L.Cin; p.L_in = L_in; p.Lp_in = padded_rows(L_in);
+  p.N_total = L.N_total; p.ntaps = L.ntaps; p.halo = L.halo;
+  for (int t = 0; t < L.ntaps; ++t) p.shift[t] = L.shift[t];
+  p.epi = epi;
+  if (mode == 0) {
+    p.w = L.d_wf;
+    for (size_t i = 0; i < L.mask_f32.size() && i < (size_t)MAX_NTILES; ++i) p.tapmask[i] = L.mask_f32[i];
+    CK(launch_conv_f32(p, s));
+  } else {
+    if (!L.n_tile) return fail(RVCDEC_ERR_ARG, "layer %s has no tensor-core tiling (N=%d, Cin=%d)", L.name.c_str(), L.N_total, L.Cin);
+    p.w = L.d_wp[fmt_in == ACT_BF16 ? 1 : 0];
+    for (size_t i = 0; i < L.mask_mma.size(); ++i) p.tapmask[i] = L.mask_mma[i];
+    CK(launch_conv_mma(p, L.n_tile, L.kc, h->num_sms, s));
+  }
+  ++h->launches;
+  return 0;
+}
+
+// One pass over B items (B small enough for the workspace).
+int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float* g, const float* noise, uint64_t seed,
+                 uint64_t item0, float* out, void* wsbase, int B, int T, int mode, cudaStream_t s) {
+  const rvcdec_config& c = h->cfg;
+  Workspace w = carve(h, wsbase, B, T, mode);
+  const int stop = h->debug_stop;
+  const int C0 = c.upsample_initial_channel;
+  const int LpT = padded_rows(T);
+  const int fpre = fmt_pre(mode);
+
+  SourceParams sp{};
+  sp.f0 = f0; sp.noise = noise; sp.har = w.har; sp.seed = seed + 0x9E3779B97F4A7C15ull * item0;
+  sp.B = B; sp.T = T; sp.upp = h->upp; sp.sr = (float)c.sr; sp.lin_w = h->lin_w; sp.lin_b = h->lin_b;
+  MARK("source", 0, (double)B * T * h->upp * (noise ? 8 : 4));
+  CK(launch_source(sp, s)); ++h->launches;
+  if (stop == 1) { MARK(nullptr, 0, 0); return 0; }
+
+  MARK("prep", 0, (double)B * c.initial_channel * T * (4 + act_bytes(fpre)));
+  CK(launch_cond(c.gin_channels ? g : nullptr, h->d_cond_w, h->d_cond_b, h->conv_pre.d_bias, w.biasB, B,
+                 c.gin_channels, C0, s)); ++h->launches;
+  CK(launch_zero_pads(w.xin, nullptr, nullptr, act_bytes(fpre), B, c.initial_channel, T, LpT, s)); ++h->launches;
+  CK(launch_zero_pads(w.pre, nullptr, nullptr, act_bytes(fpre), B, C0, T, LpT, s)); ++h->launches;
+  CK(launch_pack_input(x, w.xin, fpre, B, c.initial_channel, T, LpT, s)); ++h->launches;
+  {
+    Epilogue e{};
+    e.bias = w.biasB; e.bias_bstride = C0; e.scale = 1.f; e.slope = 0.1f;
+    e.out_act = w.pre; e.act_fmt = fpre; e.up = 1; e.cout = C0; e.L_out = T; e.Lp_out = LpT;
+    int rc = run_conv(h, "conv_pre", h->conv_pre, mode, fpre, w.xin, B, T, e, s);
+    if (rc) return rc;
+  }
+  if (stop == 2) { MARK(nullptr, 0, 0); return 0; }
+
+  const void* stage_in = w.pre;
+  int fmt_in = fpre;
+  int L = T;
+  for (int i = 0; i < h->nups; ++i) {
+    const std::string g_ups = "ups" + std::to_string(i), g_noise = "noise_add" + std::to_string(i),
+                      g_mrf = "mrf" + std::to_string(i);
+    const int u = c.upsample_rates[i];
+    const int C = h->ch[i];
+    const int Lo = L * u;
+    const int Lpo = padded_rows(Lo);
+    const int fs = fmt_stage(mode, i);
+    const bool last = (i == h->nups - 1);
+    {  // x = ups[i](leaky_relu(x, 0.1))  (hifigan_nsf.py:185,198); the activation was applied by the producer
+      Epilogue e{};
+      e.bias = h->ups[i].d_bias; e.scale = 1.f; e.slope = 0.1f;
+      e.out_f32 = w.xs0; e.up = u; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
+      int rc = run_conv(h, g_ups.c_str(), h->ups[i], mode, fmt_in, stage_in, B, L, e, s);
+      if (rc) return rc;
+    }
+    MARK(g_noise.c_str(), 2.0 * B * Lo * C * h->noise[i].k, (double)B * Lo * C * (8 + act_bytes(fs)));
+    CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches;
+    {  // x = x + noise_convs[i](har_source)  (:199)
+      const NoiseLayer& nl = h->noise[i];
+      NoiseAddParams np{};
+      np.har = w.har; np.w = nl.d_w; np.bias = nl.d_bias; np.x = w.xs0; np.act = w.a0; np.act_fmt = fs;
+      np.B = B; np.C = C; np.L = Lo; np.Lp = Lpo; np.n_src = T * h->upp; np.k = nl.k; np.stride = nl.stride;
+      np.pad = nl.pad; np.slope = 0.1f;
+      CK(launch_noise_add(np, s)); ++h->launches;
+    }
+    if (stop == 10 + i) { MARK(nullptr, 0, 0); return 0; }
+    // xs = sum_j resblocks[i*nk + j](x) / nk  (:200-207), ResBlock.forward residuals.py:71-80
+    for (int j = 0; j < h->nk; ++j) {
+      for (int m = 0; m < h->nd; ++m) {
+        const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
+        const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
+        {
+          Epilogue e{};
+          e.bias = c1.d_bias; e.scale = 1.f; e.slope = 0.1f;
+          e.out_act = w.a1; e.act_fmt = fs; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
+          int rc = run_conv(h, g_mrf.c_str(), c1, mode, fs, m == 0 ? w.a0 : w.a2, B, Lo, e, s);
+          if (rc) return rc;
+        }
+        {
+          Epilogue e{};
+          e.bias = c2.d_bias; e.slope = 0.1f; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
+          e.res = (m == 0) ? w.xs0 : w.xr;
+          if (m < h->nd - 1) {
+            e.scale = 1.f; e.out_f32 = w.xr; e.out_act = w.a2; e.act_fmt = fs;
+          } else {
+            e.scale = 1.f / (float)h->nk;
+            e.sum_in = (j == 0) ? nullptr : w.sum;
+            if (j < h->nk - 1 || last) e.out_f32 = w.sum;
+            if (j == h->nk - 1 && !last) {
+              // next stage consumes leaky_relu(x, 0.1) in ITS operand format; a0 is dead by now
+              e.out_act = w.a0; e.act_fmt = fmt_stage(mode, i);
+            }
+          }
+          int rc = run_conv(h, g_mrf.c_str(), c2, mode, fs, w.a1, B, Lo, e, s);
+          if (rc) return rc;
+        }
+      }
+    }
+    if (stop == 20 + i) { MARK(nullptr, 0, 0); return 0; }
+    stage_in = w.a0;
+    fmt_in = fs;
+    L = Lo;
+  }
+  // x = tanh(conv_post(leaky_relu(x)))  (:209-210), default slope 0.01
+  MARK("conv_post", 2.0 * B * L * h->ch[h->nups - 1] * 7, (double)B * L * (h->ch[h->nups - 1] * 4 + 4));
+  CK(launch_post(w.sum, h->d_post_w, out, B, h->ch[h->nups - 1], L, padded_rows(L), 7, 0.01f, s)); ++h->launches;
+  MARK(nullptr, 0, 0);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rvcdec_last_error(void) { return g_err.c_str(); }
+const char* rvcdec_version(void) { return "rvcdec 0.1 (sm_100a)"; }
+
+int rvcdec_create(const rvcdec_config* cfg, int device, rvcdec_handle** out) {
+  if (!cfg || !out) return fail(RVCDEC_ERR_ARG, "null argument");
+  *out = nullptr;
+  const rvcdec_config& c = *cfg;
+  if (c.num_upsamples < 1 || c.num_upsamples > RVCDEC_MAX_UPS || c.num_kernels < 1 || c.num_kernels > RVCDEC_MAX_KERNELS ||
+      c.num_dilations < 1 || c.num_dilations > RVCDEC_MAX_DILATIONS)
+    return fail(RVCDEC_ERR_ARG, "bad layer counts");
+  if (c.initial_channel % 8 || c.initial_channel <= 0) return fail(RVCDEC_ERR_ARG, "initial_channel must be a positive multiple of 8");
+  if (c.sr <= 0 || c.gin_channels < 0) return fail(RVCDEC_ERR_ARG, "bad sr / gin_channels");
+  auto h = new rvcdec_handle();
+  h->cfg = c; h->device = device; h->nups = c.num_upsamples; h->nk = c.num_kernels; h->nd = c.num_dilations;
+  h->upp = 1;
+  for (int i = 0; i < h->nups; ++i) {
+    const int u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
+    if (u < 1 || u % 2 || k < u || (k - u) % 2) { delete h; return fail(RVCDEC_ERR_ARG, "upsample %d: rate %d / kernel %d unsupported (even rates with k-u even only)", i, u, k); }
+    const int C = c.upsample_initial_channel >> (i + 1);
+    if (C < 8 || C % 8 || (C << (i + 1)) != c.upsample_initial_channel) { delete h; return fail(RVCDEC_ERR_ARG, "channel count %d at stage %d must be a multiple of 8", C, i); }
+    h->ch.push_back(C);
+    h->upp *= u;
+  }
+  for (int j = 0; j < h->nk; ++j) {
+    const int k = c.resblock_kernel_sizes[j];
+    if (k < 1 || k % 2 == 0 || k > MAX_TAPS) { delete h; return fail(RVCDEC_ERR_ARG, "resblock kernel size %d unsupported (odd, <= %d)", k, MAX_TAPS); }
+    for (int m = 0; m < h->nd; ++m) {
+      const int d = c.resblock_dilation_sizes[j][m];
+      if (d < 1 || (k - 1) / 2 * d > PADL) { delete h; return fail(RVCDEC_ERR_ARG, "resblock halo (k=%d, d=%d) exceeds %d rows", k, d, PADL); }
+    }
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) == cudaSuccess && device >= 0 && device < ndev) {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->num_sms = prop.multiProcessorCount;
+  }
+  *out = h;
+  return 0;
+}
+
+void rvcdec_destroy(rvcdec_handle* h) {
+  if (!h) return;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) == cudaSuccess && h->device < ndev) {
+    cudaSetDevice(h->device);
+    free_device(h);
+    if (h->hbuf) cudaFree(h->hbuf);
+    if (h->stream) cudaStreamDestroy(h->stream);
+  }
+  delete h;
+}
+
+// Host-side fold + repack only (no CUDA): shared by load_weights and the CPU tests.
+static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
+  const rvcdec_config& c = h->cfg;
+  TensorMap tm;
+  for (int i = 0; i < n; ++i) {
+    std::string name = tensors[i].name ? tensors[i].name : "";
+    if (name.rfind("dec.", 0) == 0) name = name.substr(4);
+    tm.m[name] = &tensors[i];
+  }
+  int rc;
+  std::vector<float> W, v;
+  const int C0 = c.upsample_initial_channel;
+  // m_source.l_linear (hifigan_nsf.py:45)
+  if ((rc = get_vec(tm, "m_source.l_linear.weight", 1, v))) return rc;
+  h->lin_w = v[0];
+  if ((rc = get_vec(tm, "m_source.l_linear.bias", 1, v))) return rc;
+  h->lin_b = v[0];
+  // conv_pre (:95-97)
+  if ((rc = get_weight(tm, "conv_pre", C0, (int64_t)c.initial_channel * 7, W))) return rc;
+  h->conv_pre = ConvLayer();
+  h->conv_pre.name = "conv_pre";
+  pack_conv(h->conv_pre, W, C0, c.initial_channel, 7, 1);
+  if ((rc = get_vec(tm, "conv_pre.bias", C0, h->conv_pre.bias))) return rc;
+  // cond (:167-168)
+  h->cond_w.clear(); h->cond_b.clear();
+  if (c.gin_channels) {
+    if ((rc = get_weight(tm, "cond", C0, c.gin_channels, h->cond_w))) return rc;
+    if ((rc = get_vec(tm, "cond.bias", C0, h->cond_b))) return rc;
+  }
+  h->ups.assign(h->nups, ConvLayer());
+  h->noise.assign(h->nups, NoiseLayer());
+  h->rbconv.assign((size_t)h->nups * h->nk * h->nd * 2, ConvLayer());
+  for (int i = 0; i < h->nups; ++i) {
+    const int Cin = C0 >> i, C = h->ch[i], u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
+    const std::string un = "ups." + std::to_string(i);
+    if ((rc = get_weight(tm, un, Cin, (int64_t)C * k, W))) return rc;  // weight-norm dim 0 = C_in
+    h->ups[i].name = un;
+    if ((rc = pack_ups(h->ups[i], W, Cin, C, k, u, (k - u) / 2))) return rc;
+    if ((rc = get_vec(tm, un + ".bias", C, v))) return rc;
+    h->ups[i].bias.resize((size_t)u * C);
+    for (int r = 0; r < u; ++r) memcpy(&h->ups[i].bias[(size_t)r * C], v.data(), sizeof(float) * C);
+    // noise_convs (:142-154): kernel 2s, stride s, pad s/2 (1/1/0 when s == 1)
+    int stride = 1;
+    for (int q = i + 1; q < h->nups; ++q) stride *= c.upsample_rates[q];
+    NoiseLayer& nl = h->noise[i];
+    nl.C = C; nl.stride = stride;
+    nl.k = stride == 1 ? 1 : stride * 2 - stride % 2;
+    nl.pad = stride == 1 ? 0 : (nl.k - stride) / 2;
+    const std::string nn = "noise_convs." + std::to_string(i);
+    if ((rc = get_weight(tm, nn, C, nl.k, W))) return rc;
+    nl.w.resize((size_t)nl.k * C);
+    for (int co = 0; co < C; ++co)
+      for (int j = 0; j < nl.k; ++j) nl.w[(size_t)j * C + co] = W[(size_t)co * nl.k + j];
+    if ((rc = get_vec(tm, nn + ".bias", C, nl.bias))) return rc;
+    for (int j = 0; j < h->nk; ++j)
+      for (int m = 0; m < h->nd; ++m)
+        for (int which = 0; which < 2; ++which) {
+          const int k2 = c.resblock_kernel_sizes[j];
+          const int d = which == 0 ? c.resblock_dilation_sizes[j][m] : 1;
+          const std::string base = "resblocks." + std::to_string(i * h->nk + j) + ".convs" + std::to_string(which + 1) + "." + std::to_string(m);
+          ConvLayer& L = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which];
+          L.name = base;
+          if ((rc = get_weight(tm, base, C, (int64_t)C * k2, W))) return rc;
+          pack_conv(L, W, C, C, k2, d);
+          if ((rc = get_vec(tm, base + ".bias", C, L.bias))) return rc;
+        }
+  }
+  // conv_post (:164): (1, C, 7) no bias -> [j][c]
+  const int Cl = h->ch[h->nups - 1];
+  if ((rc = get_weight(tm, "conv_post", 1, (int64_t)Cl * 7, W))) return rc;
+  h->post_w.resize((size_t)7 * Cl);
+  for (int cc = 0; cc < Cl; ++cc)
+    for (int j = 0; j < 7; ++j) h->post_w[(size_t)j * Cl + cc] = W[(size_t)cc * 7 + j];
+
+  // tilings / 16-bit images
+  h->fast_ok = true; h->fast_why.clear();
+  auto fin = [&](ConvLayer& L) {
+    finish_layer(L, true);
+    if (!L.n_tile && h->fast_ok) { h->fast_ok = false; h->fast_why = L.name + " (N=" + std::to_string(L.N_total) + ", Cin=" + std::to_string(L.Cin) + ")"; }
+  };
+  fin(h->conv_pre);
+  for (auto& L : h->ups) fin(L);
+  for (auto& L : h->rbconv) fin(L);
+  return 0;
+}
+
+int rvcdec_load_weights(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
+  if (!h || !tensors) return fail(RVCDEC_ERR_ARG, "null argument");
+  int rc = pack_all(h, tensors, n);
+  if (rc) return rc;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    // weights are packed on the host (CPU tests can inspect them) but nothing can run
+    h->loaded = false;
+    return fail(RVCDEC_ERR_CUDA, "no CUDA device: %s", cudaGetErrorString(e));
+  }
+  CK(cudaSetDevice(h->device));
+  free_device(h);
+  if ((rc = upload_layer(h, h->conv_pre))) return rc;
+  for (auto& L : h->ups) if ((rc = upload_layer(h, L))) return rc;
+  for (auto& L : h->rbconv) if ((rc = upload_layer(h, L))) return rc;
+  for (auto& nl : h->noise) {
+    if ((rc = upload(h, nl.w, &nl.d_w))) return rc;
+    if ((rc = upload(h, nl.bias, &nl.d_bias))) return rc;
+  }
+  if ((rc = upload(h, h->post_w, &h->d_post_w))) return rc;
+  if ((rc = upload(h, h->cond_w, &h->d_cond_w))) return rc;
+  if ((rc = upload(h, h->cond_b, &h->d_cond_b))) return rc;
+  h->loaded = true;
+  return 0;
+}
+
+size_t rvcdec_workspace_bytes(const rvcdec_handle* h, int32_t B, int32_t T, int32_t mode) {
+  if (!h || B < 1 || T < 1) return 0;
+  return carve(h, nullptr, B, T, mode).bytes;
+}
+
+static int check_forward_args(rvcdec_handle* h, const void* x, const void* f0, const void* g, const void* out, int B,
+                              int T, int mode) {
+  if (!h || !x || !f0 || !out) return fail(RVCDEC_ERR_ARG, "null argument");
+  if (!h->loaded) return fail(RVCDEC_ERR_STATE, "rvcdec_load_weights has not succeeded on this handle");
+  if (B < 1 || T < 1) return fail(RVCDEC_ERR_ARG, "B and T must be >= 1");
+  if (mode < 0 || mode > 3) return fail(RVCDEC_ERR_ARG, "unknown mode %d", mode);
+  if (h->cfg.gin_channels && !g) { /* g=None is legal in the reference: cond is skipped */ }
+  if (mode != 0 && !h->fast_ok) return fail(RVCDEC_ERR_ARG, "fast mode unsupported for this configuration: no tensor-core tiling for %s", h->fast_why.c_str());
+  if ((long long)T * h->upp > 0x7fffffffLL / 8) return fail(RVCDEC_ERR_ARG, "T too large");
+  return 0;
+}
+
+int rvcdec_forward(rvcdec_handle* h, const float* x, const float* f0, const float* g, const float* noise,
+                   uint64_t seed, float* out, void* workspace, size_t workspace_bytes, int32_t B, int32_t T,
+                   int32_t mode, void* stream) {
+  int rc = check_forward_args(h, x, f0, g, out, B, T, mode);
+  if (rc) return rc;
+  if (!workspace) return fail(RVCDEC_ERR_ARG, "null workspace");
+  CK(cudaSetDevice(h->device));
+  const size_t per1 = carve(h, nullptr, 1, T, mode).bytes;
+  if (workspace_bytes < per1) return fail(RVCDEC_ERR_WORKSPACE, "workspace of %zu bytes cannot hold one item (%zu needed)", workspace_bytes, per1);
+  int Bm = B;
+  while (Bm > 1 && carve(h, nullptr, Bm, T, mode).bytes > workspace_bytes) Bm = (Bm + 1) / 2;
+  while (Bm < B && carve(h, nullptr, Bm + 1, T, mode).bytes <= workspace_bytes) ++Bm;
+  h->launches = 0;
+  const size_t n = (size_t)T * h->upp;
+  for (int b0 = 0; b0 < B; b0 += Bm) {
+    const int nb = std::min(Bm, B - b0);
+    rc = forward_pass(h, x + (size_t)b0 * h->cfg.initial_channel * T, f0 + (size_t)b0 * T,
+                      g ? g + (size_t)b0 * h->cfg.gin_channels : nullptr, noise ? noise + b0 * n : nullptr, seed,
+                      (uint64_t)b0, out + b0 * n, workspace, nb, T, mode, (cudaStream_t)stream);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const float* g, const float* noise,
+                        uint64_t seed, float* out, int32_t B, int32_t T, int32_t mode, size_t max_device_bytes) {
+  int rc = check_forward_args(h, x, f0, g, out, B, T, mode);
+  if (rc) return rc;
+  CK(cudaSetDevice(h->device));
+  if (!h->stream) CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  if (max_device_bytes == 0) max_device_bytes = (size_t)24 << 30;
+  const size_t n = (size_t)T * h->upp;
+  const int Cx = h->cfg.initial_channel, G = h->cfg.gin_channels;
+  auto io_bytes = [&](int b) {
+    return align_up((size_t)b * Cx * T * 4, 256) + align_up((size_t)b * T * 4, 256) + align_up((size_t)b * std::max(G, 1) * 4, 256) +
+           (noise ? align_up((size_t)b * n * 4, 256) : 0) + align_up((size_t)b * n * 4, 256);
+  };
+  int Bm = B;
+  while (Bm > 1 && io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes > max_device_bytes) Bm = (Bm + 1) / 2;
+  const size_t need = io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes;
+  if (need > h->hbuf_bytes) {
+    if (h->hbuf) { CK(cudaFree(h->hbuf)); h->hbuf = nullptr; h->hbuf_bytes = 0; }
+    CK(cudaMalloc(&h->hbuf, need));
+    h->hbuf_bytes = need;
+  }
+  uint8_t* p = (uint8_t*)h->hbuf;
+  float* dx = (float*)p; p += align_up((size_t)Bm * Cx * T * 4, 256);
+  float* df0 = (float*)p; p += align_up((size_t)Bm * T * 4, 256);
+  float* dg = (float*)p; p += align_up((size_t)Bm * std::max(G, 1) * 4, 256);
+  float* dnz = nullptr;
+  if (noise) { dnz = (float*)p; p += align_up((size_t)Bm * n * 4, 256); }
+  float* dout = (float*)p; p += align_up((size_t)Bm * n * 4, 256);
+  void* ws = p;
+  h->launches = 0;
+  for (int b0 = 0; b0 < B; b0 += Bm) {
+    const int nb = std::min(Bm, B - b0);
+    CK(cudaMemcpyAsync(dx, x + (size_t)b0 * Cx * T, (size_t)nb * Cx * T * 4, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(df0, f0 + (size_t)b0 * T, (size_t)nb * T * 4, cudaMemcpyHostToDevice, h->stream));
+    if (g && G) CK(cudaMemcpyAsync(dg, g + (size_t)b0 * G, (size_t)nb * G * 4, cudaMemcpyHostToDevice, h->stream));
+    if (noise) CK(cudaMemcpyAsync(dnz, noise + b0 * n, nb * n * 4, cudaMemcpyHostToDevice, h->stream));
+    rc = forward_pass(h, dx, df0, (g && G) ? dg : nullptr, dnz, seed, (uint64_t)b0, dout, ws, nb, T, mode, h->stream);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(out + b0 * n, dout, nb * n * 4, cudaMemcpyDeviceToHost, h->stream));
+  }
+  CK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int64_t rvcdec_last_launch_count(const rvcdec_handle* h) { return h ? h->launches : 0; }
+
+int rvcdec_profile_enable(rvcdec_handle* h, int32_t on) {
+  if (!h) return fail(RVCDEC_ERR_ARG, "null handle");
+  h->prof_on = on != 0;
+  for (auto& m : h->prof_marks) h->prof_pool.push_back(m.ev);
+  h->prof_marks.clear();
+  h->prof_names.clear(); h->prof_ms.clear(); h->prof_flops.clear(); h->prof_bytes.clear(); h->prof_launches.clear();
+  return 0;
+}
+
+int32_t rvcdec_profile_read(rvcdec_handle* h, rvcdec_profile_entry* out, int32_t max_entries) {
+  if (!h || !out) return fail(RVCDEC_ERR_ARG, "null argument");
+  // fold the recorded marks into the per-group totals: a mark's span ends at the next mark
+  if (!h->prof_marks.empty()) {
+    CK(cudaEventSynchronize(h->prof_marks.back().ev));
+    for (size_t i = 0; i + 1 < h->prof_marks.size(); ++i) {
+      const auto& m = h->prof_marks[i];
+      if (m.group < 0) continue;
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, m.ev, h->prof_marks[i + 1].ev));
+      h->prof_ms[m.group] += ms; h->prof_flops[m.group] += m.flops; h->prof_bytes[m.group] += m.bytes;
+      h->prof_launches[m.group] += 1;
+    }
+    for (auto& m : h->prof_marks) h->prof_pool.push_back(m.ev);
+    h->prof_marks.clear();
+  }
+  const int32_t n = std::min<int32_t>(max_entries, (int32_t)h->prof_names.size());
+  for (int32_t i = 0; i < n; ++i) {
+    memset(&out[i], 0, sizeof out[i]);
+    strncpy(out[i].name, h->prof_names[i].c_str(), sizeof(out[i].name) - 1);
+    out[i].ms = h->prof_ms[i]; out[i].flops = h->prof_flops[i]; out[i].bytes = h->prof_bytes[i];
+    out[i].spans = h->prof_launches[i];
+  }
+  return n;
+}
+
+int rvcdec_debug_set_stop(rvcdec_handle* h, int32_t stop_after) {
+  if (!h) return fail(RVCDEC_ERR_ARG, "null handle");
+  h->debug_stop = stop_after;
+  return 0;
+}
+
+int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_t dst_numel, void* workspace,
+                          int32_t B, int32_t T, int32_t mode, void* stream) {
+  if (!h || !name || !dst || !workspace) return fail(RVCDEC_ERR_ARG, "null argument");
+  Workspace w = carve(h, workspace, B, T, mode);
+  const std::string nm = name;
+  cudaStream_t s = (cudaStream_t)stream;
+  auto need = [&](int64_t n) { return n <= dst_numel ? 0 : fail(RVCDEC_ERR_ARG, "destination too small (%lld < %lld)", (long long)dst_numel, (long long)n); };
+  if (nm == "har") {
+    const int64_t n = (int64_t)B * T * h->upp;
+    if (need(n)) return RVCDEC_ERR_ARG;
+    CK(cudaMemcpyAsync(dst, w.har, n * 4, cudaMemcpyDeviceToDevice, s));
+    return n;
+  }
+  if (nm == "pre") {  // leaky_relu(conv_pre(x) + cond(g), 0.1) in the operand format
+    const int C0 = h->cfg.upsample_initial_channel;
+    const int64_t n = (int64_t)B * C0 * T;
+    if (need(n)) return RVCDEC_ERR_ARG;
+    CK(launch_unpack(w.pre, fmt_pre(mode), dst, B, C0, T, padded_rows(T), s));
+    return n;
+  }
+  int L = T;
+  for (int i = 0; i < h->nups; ++i) {
+    L *= h->cfg.upsample_rates[i];
+    const int64_t n = (int64_t)B * h->ch[i] * L;
+    if (nm == "stage" + std::to_string(i) + ".in") {  // ups + noise_conv, fp32
+      if (need(n)) return RVCDEC_ERR_ARG;
+      CK(launch_unpack(w.xs0, ACT_F32, dst, B, h->ch[i], L, padded_rows(L), s));
+      return n;
+    }
+    if (nm == "stage" + std::to_string(i) + ".out") {
+      if (need(n)) return RVCDEC_ERR_ARG;
+      if (i == h->nups - 1) CK(launch_unpack(w.sum, ACT_F32, dst, B, h->ch[i], L, padded_rows(L), s));  // pre-activation
+      else CK(launch_unpack(w.a0, fmt_stage(mode, i), dst, B, h->ch[i], L, padded_rows(L), s));          // leaky_relu(.,0.1)
+      return n;
+    }
+  }
+  return fail(RVCDEC_ERR_ARG, "unknown intermediate '%s'", name);
+}
+
+// Host-only packing for CPU tests: runs fold + repack without touching CUDA.
+int rvcdec_debug_pack_host(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
+  if (!h || !tensors) return fail(RVCDEC_ERR_ARG, "null argument");
+  return pack_all(h, tensors, n);
+}
+
+int64_t rvcdec_debug_packed(const rvcdec_handle* h, const char* layer, int32_t kind, void* dst, int64_t dst_bytes) {
+  if (!h || !layer) return fail(RVCDEC_ERR_ARG, "null argument");
+  const ConvLayer* L = nullptr;
+  const std::string nm = layer;
+  if (nm == h->conv_pre.name) L = &h->conv_pre;
+  for (auto& u : h->ups) if (u.name == nm) L = &u;
+  for (auto& r : h->rbconv) if (r.name == nm) L = &r;
+  if (!L) return fail(RVCDEC_ERR_ARG, "unknown layer '%s'", layer);
+  const void* src = nullptr;
+  int64_t bytes = 0;
+  int32_t meta[8];
+  switch (kind) {
+    case 0: src = L->wf.data(); bytes = (int64_t)L->wf.size() * 4; break;
+    case 1: src = L->wp[0].data(); bytes = (int64_t)L->wp[0].size() * 2; break;
+    case 2: src = L->shift; bytes = (int64_t)L->ntaps * 4; break;
+    case 3: src = L->mask_mma.data(); bytes = (int64_t)L->mask_mma.size() * 4; break;
+    case 4: src = L->wp[1].data(); bytes = (int64_t)L->wp[1].size() * 2; break;
+    case 5:
+      meta[0] = L->Cin; meta[1] = L->N_total; meta[2] = L->cout; meta[3] = L->up; meta[4] = L->ntaps; meta[5] = L->halo;
+      meta[6] = L->n_tile; meta[7] = L->kc;
+      src = meta; bytes = sizeof meta; break;
+    case 6: src = L->bias.data(); bytes = (int64_t)L->bias.size() * 4; break;
+    default: return fail(RVCDEC_ERR_ARG, "unknown kind %d", kind);
+  }
+  if (!dst) return bytes;
+  if (dst_bytes < bytes) return fail(RVCDEC_ERR_ARG, "destination too small");
+  memcpy(dst, src, (size_t)bytes);
+  return bytes;
+}
+
+}  // extern "C"

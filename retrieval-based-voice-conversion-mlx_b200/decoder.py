@@ -1,0 +1,244 @@
+"""Drop-in replacement for the reference's NSF-HiFiGAN decoder.
+
+``HiFiGANNSFGenerator`` mirrors the constructor, parameter names and
+``forward(x, f0, g) -> waveform`` of
+``rvc/lib/algorithm/generators/hifigan_nsf.py:55-235`` so that
+``rvc/lib/algorithm/synthesizers.py:108-118`` can construct it and
+``load_state_dict(cpt["weight"], strict=False)`` (``rvc/infer/infer.py:479-488``)
+fills it unchanged.  The torch submodules below only HOLD parameters: every
+flop of ``forward`` runs in librvcdec.so (hand-written sm_100a CUDA) behind the
+torch custom op ``rvc_b200::nsf_hifigan_decode``.  There is no PyTorch or CPU
+fallback; calling ``forward`` with CPU tensors raises.
+"""
+from __future__ import annotations
+
+import math
+import os
+from typing import Optional
+
+import torch
+from torch.nn.utils.parametrizations import weight_norm
+from torch.nn.utils import parametrize
+
+from . import _lib
+
+LRELU_SLOPE = 0.1  # residuals.py:10
+
+
+def _get_padding(kernel_size: int, dilation: int = 1) -> int:  # commons.py:19-27
+    return int((kernel_size * dilation - dilation) / 2)
+
+
+def _burn_init_weights(m: torch.nn.Module) -> None:
+    """The reference calls ``init_weights`` (commons.py:5-16) on weight-normed convs; on a
+    parametrised module that only re-draws a temporary (``m.weight`` is computed), i.e. it has no
+    effect on the parameters but DOES consume the global RNG.  Same draws here so that
+    ``torch.manual_seed(s); HiFiGANNSFGenerator(...)`` yields bit-identical random-init weights."""
+    if m.__class__.__name__.find("Conv") != -1:
+        m.weight.data.normal_(0.0, 0.01)
+
+
+class SourceModuleHnNSF(torch.nn.Module):
+    """Parameter holder for hifigan_nsf.py:14-52 (``l_linear`` = Linear(1, 1))."""
+
+    def __init__(self, sample_rate: int, harmonic_num: int = 0, sine_amp: float = 0.1, add_noise_std: float = 0.003,
+                 voiced_threshod: float = 0):
+        super().__init__()
+        if harmonic_num != 0:
+            raise ValueError("the NSF decoder uses harmonic_num=0 (hifigan_nsf.py:93)")
+        self.sine_amp = sine_amp
+        self.noise_std = add_noise_std
+        self.sampling_rate = sample_rate
+        self.l_linear = torch.nn.Linear(harmonic_num + 1, 1)
+        self.l_tanh = torch.nn.Tanh()
+
+
+class ResBlock(torch.nn.Module):
+    """Parameter holder for residuals.py:34-84."""
+
+    def __init__(self, channels: int, kernel_size: int = 3, dilations=(1, 3, 5)):
+        super().__init__()
+        self.convs1 = self._create_convs(channels, kernel_size, dilations)
+        self.convs2 = self._create_convs(channels, kernel_size, [1] * len(dilations))
+
+    @staticmethod
+    def _create_convs(channels, kernel_size, dilations):
+        layers = torch.nn.ModuleList([
+            weight_norm(torch.nn.Conv1d(channels, channels, kernel_size, 1, dilation=d, padding=_get_padding(kernel_size, d)))
+            for d in dilations
+        ])
+        layers.apply(_burn_init_weights)
+        return layers
+
+
+def _strip(module: torch.nn.Module) -> None:
+    if parametrize.is_parametrized(module, "weight"):
+        parametrize.remove_parametrizations(module, "weight", leave_parametrized=True)
+
+
+class HiFiGANNSFGenerator(torch.nn.Module):
+    """B200-native NSF-HiFiGAN generator with the reference's interface (hifigan_nsf.py:75-86).
+
+    Extra, optional, keyword-only arguments of ``forward``:
+      noise  (B, T*upp) or (B, T*upp, 1) standard-normal draws to inject; default = drawn with the torch
+             generator of x's device in the reference's order (``rand(1,1,1)`` then ``randn(B, T*upp, 1)``,
+             hifigan.py:189,223), so a seeded call reproduces the reference's noise on the same device.
+             "philox" draws them inside the source kernel instead (no noise tensor in HBM).
+      mode   "fp32" | "fast" | "fast_f16" | "fast_bf16"; default ``self.mode`` ("fast", or $RVC_B200_MODE).
+    """
+
+    def __init__(self, initial_channel: int, resblock_kernel_sizes: list, resblock_dilation_sizes: list,
+                 upsample_rates: list, upsample_initial_channel: int, upsample_kernel_sizes: list, gin_channels: int,
+                 sr: int, checkpointing: bool = False):
+        super().__init__()
+        self.num_kernels = len(resblock_kernel_sizes)
+        self.num_upsamples = len(upsample_rates)
+        self.checkpointing = checkpointing  # training-only in the reference; accepted and ignored
+        self.f0_upsamp = torch.nn.Upsample(scale_factor=math.prod(upsample_rates))
+        self.m_source = SourceModuleHnNSF(sample_rate=sr, harmonic_num=0)
+        self.conv_pre = torch.nn.Conv1d(initial_channel, upsample_initial_channel, 7, 1, padding=3)
+        self.ups = torch.nn.ModuleList()
+        self.noise_convs = torch.nn.ModuleList()
+        channels = [upsample_initial_channel // (2 ** (i + 1)) for i in range(len(upsample_rates))]
+        stride_f0s = [math.prod(upsample_rates[i + 1:]) if i + 1 < len(upsample_rates) else 1
+                      for i in range(len(upsample_rates))]
+        for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
+            if u % 2 != 0:
+                raise ValueError("odd upsample rates are not supported by the B200 decoder (32k/40k/48k are all even)")
+            self.ups.append(weight_norm(torch.nn.ConvTranspose1d(upsample_initial_channel // (2 ** i), channels[i], k, u,
+                                                                 padding=(k - u) // 2, output_padding=0)))
+            stride = stride_f0s[i]
+            kernel = 1 if stride == 1 else stride * 2 - stride % 2
+            padding = 0 if stride == 1 else (kernel - stride) // 2
+            self.noise_convs.append(torch.nn.Conv1d(1, channels[i], kernel_size=kernel, stride=stride, padding=padding))
+        self.resblocks = torch.nn.ModuleList([
+            ResBlock(channels[i], k, d)
+            for i in range(len(self.ups))
+            for k, d in zip(resblock_kernel_sizes, resblock_dilation_sizes)
+        ])
+        self.conv_post = torch.nn.Conv1d(channels[-1], 1, 7, 1, padding=3, bias=False)
+        self.ups.apply(_burn_init_weights)
+        if gin_channels != 0:
+            self.cond = torch.nn.Conv1d(gin_channels, upsample_initial_channel, 1)
+        self.upp = math.prod(upsample_rates)
+        self.lrelu_slope = LRELU_SLOPE
+
+        self.mode = os.environ.get("RVC_B200_MODE", "fast")
+        self.noise_source = os.environ.get("RVC_B200_NOISE", "torch")  # "torch" | "philox"
+        self.max_workspace_bytes = int(os.environ.get("RVC_B200_MAX_WORKSPACE", str(32 << 30)))
+        self._cfg_args = (initial_channel, list(resblock_kernel_sizes), [list(d) for d in resblock_dilation_sizes],
+                          list(upsample_rates), upsample_initial_channel, list(upsample_kernel_sizes), gin_channels, sr)
+        self._gin = gin_channels
+        self._cin = initial_channel
+        self._handle: Optional[_lib.Handle] = None
+        self._packed_key = None
+        self._workspace: Optional[torch.Tensor] = None
+        self.last_launch_count = 0
+
+    # -- reference protocol ------------------------------------------------
+    def remove_weight_norm(self):
+        """Fold weight-norm into plain weights (the reference's version raises on parametrised
+        modules, hifigan_nsf.py:214-218; rvc/realtime/pipeline.py:405-415 shows the intent)."""
+        for l in self.ups:
+            _strip(l)
+        for rb in self.resblocks:
+            for l in list(rb.convs1) + list(rb.convs2):
+                _strip(l)
+
+    def __prepare_scriptable__(self):
+        return self
+
+    # -- packed weights ----------------------------------------------------
+    def _weights_key(self):
+        return tuple((p.data_ptr(), p._version, p.device.index) for p in self.parameters())
+
+    def _ensure_handle(self, device: torch.device) -> _lib.Handle:
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        if self._handle is not None and self._handle.device != idx:
+            self._handle.close()
+            self._handle = None
+        if self._handle is None:
+            self._handle = _lib.Handle(_lib.make_config(*self._cfg_args), idx)
+            self._packed_key = None
+        key = self._weights_key()
+        if key != self._packed_key:
+            self._handle.load_weights(self.state_dict())
+            self._packed_key = key
+        return self._handle
+
+    def _get_workspace(self, nbytes: int, device: torch.device) -> torch.Tensor:
+        ws = self._workspace
+        if ws is None or ws.device != device or ws.numel() < nbytes:
+            self._workspace = None
+            ws = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            self._workspace = ws
+        return ws
+
+    # -- forward -----------------------------------------------------------
+    def forward(self, x: torch.Tensor, f0: torch.Tensor, g: Optional[torch.Tensor] = None, *,
+                noise: Optional[torch.Tensor] = None, mode: Optional[str] = None):
+        from . import ops  # registers the custom op
+
+        if not x.is_cuda:
+            raise RuntimeError("rvc_b200.HiFiGANNSFGenerator runs only on a CUDA (sm_100a) device; there is no CPU fallback")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and self.training:
+            raise RuntimeError("the B200 decoder is inference-only (call .eval() / use torch.no_grad())")
+        B, Cx, T = x.shape
+        if Cx != self._cin or f0.shape != (B, T):
+            raise ValueError(f"expected x (B,{self._cin},T) and f0 (B,T); got {tuple(x.shape)} and {tuple(f0.shape)}")
+        m = _lib.MODES[mode or self.mode]
+        h = self._ensure_handle(x.device)
+        n = T * self.upp
+        seed = 0
+        if noise is None:
+            noise = self.noise_source
+        if isinstance(noise, str):
+            if noise == "torch":
+                # reference draw order on this device's generator: hifigan.py:189 then :223
+                torch.rand(1, 1, 1, device=x.device)
+                noise = torch.randn(B, n, 1, device=x.device, dtype=torch.float32)
+            elif noise == "philox":
+                # in-kernel draws: one 63-bit key from the torch CPU generator per call
+                noise = None
+                seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            else:
+                raise ValueError("noise must be a tensor, 'torch' or 'philox'")
+        if noise is not None:
+            noise = noise.reshape(B, n).contiguous().float()
+        if g is not None:
+            if self._gin == 0:
+                g = None
+            else:
+                g = g.reshape(B, self._gin).contiguous().float()
+        need = h.workspace_bytes(B, T, m)
+        ws = self._get_workspace(min(need, max(self.max_workspace_bytes, h.workspace_bytes(1, T, m))), x.device)
+        out = ops.nsf_hifigan_decode(x.contiguous().float(), f0.contiguous().float(), g, noise, ws, h.ptr.value, m, self.upp, seed)
+        self.last_launch_count = h.launch_count()
+        return out.unsqueeze(1)
+
+    def decode_host(self, x: torch.Tensor, f0: torch.Tensor, g: Optional[torch.Tensor] = None, *,
+                    mode: Optional[str] = None, out: Optional[torch.Tensor] = None, device: Optional[int] = None,
+                    max_device_bytes: int = 0) -> torch.Tensor:
+        """Host-buffer entry point (``rvcdec_forward_host``): x, f0, g are CPU tensors (pinned memory
+        recommended); copies in, decodes with in-kernel noise, copies the waveform back into ``out``
+        (CPU, (B,1,T*upp)) and returns it.  This is the per-chunk call of the reference's pipeline
+        (rvc/infer/pipeline.py:366-371) with the host<->device hops inside."""
+        if x.is_cuda or f0.is_cuda:
+            raise ValueError("decode_host takes CPU tensors; use forward() for device tensors")
+        B, Cx, T = x.shape
+        m = _lib.MODES[mode or self.mode]
+        dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        h = self._ensure_handle(dev)
+        x = x.contiguous().float()
+        f0 = f0.contiguous().float()
+        gp = None
+        if g is not None and self._gin:
+            g = g.reshape(B, self._gin).contiguous().float()
+            gp = g.data_ptr()
+        n = T * self.upp
+        if out is None:
+            out = torch.empty(B, 1, n, dtype=torch.float32, pin_memory=True)
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        h.forward_host(x.data_ptr(), f0.data_ptr(), gp, None, seed, out.data_ptr(), B, T, m, max_device_bytes)
+        self.last_launch_count = h.launch_count()
+        return out

@@ -1,0 +1,270 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called through the drop-in module
+-> torch custom op -> C ABI, against the CPU oracle and the reference-generated golden fixtures.
+
+Bars (BASELINE.json north_star): fp32 mode max-abs <= 2e-3; fast mode multi-resolution log-mel
+correlation (min over the 7 resolutions) >= 0.999.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import nsf_hifigan_oracle as O
+from helpers import build_module, golden_state, load_golden, tensors
+
+pytestmark = pytest.mark.gpu
+
+FP32_BAR = 2e-3
+FAST_BAR = 0.999
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "GPU tests need CUDA"
+    return torch.device("cuda", 0)
+
+
+def _module_for(name, dev):
+    d, cfg = load_golden(name)
+    m = build_module(cfg, int(d["init_seed"]))
+    sd = golden_state(d, cfg)
+    m.load_state_dict(sd)
+    return d, cfg, m.to(dev), O.folded_weights(sd)
+
+
+def layer_taps(m, cfg, x, f0, g, noise, mode):
+    """Run the CUDA path with early stops and fetch the intermediates the C ABI exposes."""
+    from rvc_b200 import _lib
+
+    dev = x.device
+    B, _, T = x.shape
+    mm = _lib.MODES[mode]
+    out = {}
+    with torch.no_grad():
+        m(x, f0, g, noise=noise, mode=mode)  # builds handle / workspace
+    h, ws = m._handle, m._workspace
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    L = T
+    plan = [(1, "har", (B, T * cfg.upp)), (2, "pre", (B, cfg.upsample_initial_channel, T))]
+    for i, u in enumerate(cfg.upsample_rates):
+        L *= u
+        C = cfg.upsample_initial_channel >> (i + 1)
+        plan += [(10 + i, f"stage{i}.in", (B, C, L)), (20 + i, f"stage{i}.out", (B, C, L))]
+    try:
+        for stop, name, shape in plan:
+            h.set_stop(stop)
+            with torch.no_grad():
+                m(x, f0, g, noise=noise, mode=mode)
+            dst = torch.empty(shape, dtype=torch.float32, device=dev)
+            n = h.debug_read(name, dst, ws, B, T, mm, stream)
+            assert n == dst.numel()
+            torch.cuda.synchronize()
+            out[name] = dst.cpu()
+    finally:
+        h.set_stop(0)
+    return out
+
+
+def oracle_taps(w, cfg, x, f0, g, noise):
+    taps = {}
+    y = O.decoder_forward(w, cfg, x, f0, g, noise, taps=taps)
+    last = len(cfg.upsample_rates) - 1
+    exp = {"har": taps["har"], "pre": F.leaky_relu(taps["pre"], 0.1)}
+    for i in range(last + 1):
+        exp[f"stage{i}.in"] = taps[f"stage{i}.in"]
+        exp[f"stage{i}.out"] = taps[f"stage{i}.out"] if i == last else F.leaky_relu(taps[f"stage{i}.out"], 0.1)
+    return exp, y
+
+
+def layer_errors(name, mode, dev):
+    d, cfg, m, w = _module_for(name, dev)
+    x, f0, g, noise, y = tensors(d)
+    got = layer_taps(m, cfg, x.to(dev), f0.to(dev), g.to(dev), noise.to(dev), mode)
+    exp, _ = oracle_taps(w, cfg, x, f0, g, noise)
+    errs = {}
+    for k in exp:
+        scale = float(exp[k].abs().max()) + 1e-12
+        errs[k] = (float((got[k] - exp[k]).abs().max()), scale)
+    return errs
+
+
+def test_source_kernel_matches_oracle(dev):
+    """One kernel: f0 upsample + fp64 phase scan + sine + injected noise + Linear + tanh, vs SineGenerator."""
+    d, cfg, m, w = _module_for("v2_48k_B2_T24", dev)
+    gen = torch.Generator().manual_seed(3)
+    f0 = O.synth_f0(3, 333, gen)
+    f0[2] = 0.0  # fully unvoiced item
+    noise = torch.randn(3, 333 * cfg.upp, generator=gen)
+    x = torch.zeros(3, cfg.initial_channel, 333)
+    got = layer_taps(m, cfg, x.to(dev), f0.to(dev), None, noise.to(dev), "fp32")["har"]
+    s = O.sine_source(f0, cfg.upp, cfg.sr, noise, dtype=torch.float64)
+    exp = torch.tanh(s * w["m_source.l_linear.weight"].reshape(()) + w["m_source.l_linear.bias"].reshape(()))
+    assert float((got - exp).abs().max()) <= 2e-5
+    # and against the reference's own fp32 phase accumulation (its cumsum error is the difference)
+    s32 = O.sine_source(f0, cfg.upp, cfg.sr, noise)
+    exp32 = torch.tanh(s32 * w["m_source.l_linear.weight"].reshape(()) + w["m_source.l_linear.bias"].reshape(()))
+    assert float((got - exp32).abs().max()) <= 1e-4
+
+
+@pytest.mark.parametrize("name", ["tiny_24k_B2_T40", "v2_48k_B2_T24", "v2_40k_B1_T32", "v2_32k_B1_T16"])
+def test_fp32_mode_matches_reference_golden(dev, name):
+    d, cfg, m, w = _module_for(name, dev)
+    x, f0, g, noise, y = tensors(d)
+    with torch.no_grad():
+        got = m(x.to(dev), f0.to(dev), g.to(dev), noise=noise.to(dev), mode="fp32").cpu()
+    assert got.shape == y.shape
+    err = float((got - y).abs().max())
+    assert err <= FP32_BAR, err
+    assert err <= 5e-5, f"fp32 path should be at rounding level, got {err}"
+
+
+@pytest.mark.parametrize("name", ["tiny_24k_B2_T40", "v2_48k_B2_T24"])
+def test_fp32_mode_layer_by_layer(dev, name):
+    errs = layer_errors(name, "fp32", dev)
+    for k, (e, scale) in errs.items():
+        assert e <= 2e-5 * max(1.0, scale), (k, e, scale)
+
+
+def test_fast_mode_layer_by_layer(dev):
+    errs = layer_errors("v2_48k_B2_T24", "fast", dev)
+    for k, (e, scale) in errs.items():
+        tol = 2e-5 if k == "har" else 3e-2 * max(1.0, scale)
+        assert e <= tol, (k, e, scale)
+
+
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 1), ("48k", 1, 257, 2), ("40k", 2, 120, 3), ("32k", 1, 100, 4)])
+@pytest.mark.parametrize("mode", ["fp32", "fast"])
+def test_against_oracle_on_seeded_inputs(dev, cfg_name, B, T, seed, mode):
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K, "32k": O.CONFIG_32K}[cfg_name]
+    m = build_module(cfg, 1000 + seed)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    with torch.no_grad():
+        y = m(x.to(dev), f0.to(dev), g.to(dev), noise=noise.to(dev), mode=mode).cpu()
+    assert y.shape == (B, 1, T * cfg.upp)
+    err = float((y - y_ref).abs().max())
+    if mode == "fp32":
+        assert err <= FP32_BAR, err
+    else:
+        corr = O.multires_logmel_corr(y, y_ref, cfg.sr)
+        assert corr["min"] >= FAST_BAR, (corr, err)
+        assert err <= 2e-2, err
+
+
+def test_readme_shape_both_modes(dev):
+    """BASELINE configs[2]: 13.5 s at the README benchmark shape (T=1350), real RMVPE-like contour shape."""
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 1234)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, 1, 1350, seed=1234)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    with torch.no_grad():
+        y32 = m(x.to(dev), f0.to(dev), g.to(dev), noise=noise.to(dev), mode="fp32").cpu()
+        yf = m(x.to(dev), f0.to(dev), g.to(dev), noise=noise.to(dev), mode="fast").cpu()
+    assert y32.shape == (1, 1, 648000)
+    assert float((y32 - y_ref).abs().max()) <= FP32_BAR
+    assert O.multires_logmel_corr(yf, y_ref, cfg.sr)["min"] >= FAST_BAR
+
+
+@pytest.mark.parametrize("mode", ["fp32", "fast"])
+def test_size_independent_properties(dev, mode):
+    """Batch items are independent; ragged tile edges, micro-batching and g=None behave; output is bounded."""
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 7).to(dev)
+    x, f0, g, noise = (t.to(dev) for t in O.synth_inputs(cfg, 3, 77, seed=9))
+    with torch.no_grad():
+        y = m(x, f0, g, noise=noise, mode=mode)
+        y1 = m(x[1:2], f0[1:2], g[1:2], noise=noise[1:2], mode=mode)
+        assert torch.equal(y[1:2], y1), "batch items must not influence each other"
+        y_again = m(x, f0, g, noise=noise, mode=mode)
+        assert torch.equal(y, y_again), "deterministic for fixed noise"
+        # micro-batching: a workspace that only fits one item gives the same result
+        full = m.max_workspace_bytes
+        try:
+            m.max_workspace_bytes = 1
+            m._workspace = None
+            y_mb = m(x, f0, g, noise=noise, mode=mode)
+        finally:
+            m.max_workspace_bytes = full
+            m._workspace = None
+        assert torch.equal(y, y_mb)
+        y_nog = m(x, f0, None, noise=noise, mode=mode)
+        assert y_nog.shape == y.shape and not torch.equal(y_nog, y)
+        assert float(y.abs().max()) <= 1.0 and bool(torch.isfinite(y).all())
+        # causality of the zero padding: a longer input with the same prefix only changes the tail region
+        xl = torch.cat([x, torch.randn(3, cfg.initial_channel, 23, device=dev)], dim=2)
+        f0l = torch.cat([f0, f0[:, :23]], dim=1)
+        nl = torch.cat([noise, noise[:, : 23 * cfg.upp]], dim=1)
+        yl = m(xl, f0l, g, noise=nl, mode=mode)
+        keep = (77 - 12) * cfg.upp  # receptive field is ~11 frames
+        assert float((yl[:, :, :keep] - y[:, :, :keep]).abs().max()) <= 1e-5
+
+
+def test_saturation_and_bounds(dev):
+    """Scaled weights drive tanh into saturation (random-init outputs never get near 1)."""
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 11)
+    with torch.no_grad():
+        m.conv_post.weight.mul_(200.0)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, 1, 40, seed=2)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    with torch.no_grad():
+        y = m(x.to(dev), f0.to(dev), g.to(dev), noise=noise.to(dev), mode="fp32").cpu()
+    assert float(y_ref.abs().max()) > 0.99
+    assert float(y.abs().max()) <= 1.0
+    assert float((y - y_ref).abs().max()) <= FP32_BAR
+
+
+def test_reference_noise_order_and_host_entry(dev):
+    """Default noise = torch generator draws in the reference's order; decode_host == forward(philox) for one seed."""
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 5).to(dev)
+    x, f0, g, _ = O.synth_inputs(cfg, 2, 30, seed=4)
+    xd, fd, gd = x.to(dev), f0.to(dev), g.to(dev)
+    with torch.no_grad():
+        torch.manual_seed(77)
+        y_default = m(xd, fd, gd, mode="fp32")
+        torch.manual_seed(77)
+        torch.rand(1, 1, 1, device=dev)
+        nz = torch.randn(2, 30 * cfg.upp, 1, device=dev)
+        y_explicit = m(xd, fd, gd, noise=nz, mode="fp32")
+        assert torch.equal(y_default, y_explicit)
+        torch.manual_seed(5)
+        y_ph = m(xd, fd, gd, noise="philox", mode="fast")
+        torch.manual_seed(5)
+        y_host = m.decode_host(x, f0, g, mode="fast")
+        assert y_host.shape == (2, 1, 30 * cfg.upp) and not y_host.is_cuda
+        assert torch.equal(y_ph.cpu(), y_host)
+        # Philox draws are standard normal: unvoiced-only input isolates them (har = tanh(w*(0.1/3)z + b))
+        assert m.last_launch_count > 80
+
+
+def test_long_form_chunked_decode_matches_reference_stitching(dev):
+    """BASELINE configs[4] in miniature: t_pad-overlap chunks decoded independently, trimmed and concatenated
+    equal the oracle run chunk by chunk (the reference restarts the sine phase per chunk too)."""
+    from rvc_b200 import chunking as ch
+
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 21)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    n_frames = 260
+    chunks = ch.plan_chunks(n_frames, split_points=[90, 170])
+    total = n_frames + 200
+    x, f0, g, _ = O.synth_inputs(cfg, 1, total, seed=8)
+    outs, refs = [], []
+    for c in chunks:
+        xs, fs = x[:, :, c.start:c.stop], f0[:, c.start:c.stop]
+        nz = torch.randn(1, c.frames * cfg.upp, generator=torch.Generator().manual_seed(c.index))
+        refs.append(O.decoder_forward(w, cfg, xs, fs, g, nz)[0, 0].numpy())
+        with torch.no_grad():
+            outs.append(m(xs.to(dev).contiguous(), fs.to(dev).contiguous(), g.to(dev), noise=nz.to(dev), mode="fp32")[0, 0].cpu().numpy())
+    trims = [c.trim * cfg.upp for c in chunks]
+    y, y_ref = ch.stitch(outs, trims), ch.stitch(refs, trims)
+    assert y.shape == (n_frames * cfg.upp,)
+    assert float(np.abs(y - y_ref).max()) <= FP32_BAR

@@ -1,0 +1,200 @@
+"""CPU tests of the host side: C-ABI exports, weight folding/packing images, polyphase
+decomposition, chunk geometry, sharding (incl. a world_size-2 gloo run).  No kernel is launched."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import nsf_hifigan_oracle as O
+from helpers import build_module, golden_state, load_golden
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_abi_exports_every_declared_symbol(built_lib):
+    from rvc_b200 import _lib
+
+    hdr = open(os.path.join(ROOT, "include", "rvcdec.h")).read()
+    declared = set(re.findall(r"\b(rvcdec_[a-z_0-9]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.EXPORTS)
+    for sym in declared:
+        assert getattr(built_lib, sym) is not None
+    assert b"sm_100a" in built_lib.rvcdec_version()
+
+
+def test_module_state_dict_matches_reference_naming():
+    d, cfg = load_golden("v2_48k_B2_T24")
+    m = build_module(cfg, int(d["init_seed"]))
+    sd = m.state_dict()
+    assert len(sd) == 243  # 2 + 2 + 4*3 + 4*2 + 12*6*3 + 1 + 2
+    assert {k[4:] for k in d.files if k.startswith("ck::")} == set(sd.keys())
+    assert m.upp == 480 and m.num_kernels == 3 and m.num_upsamples == 4
+    assert len(m.ups) == 4 and len(m.noise_convs) == 4 and len(m.resblocks) == 12
+    # legacy checkpoint naming (weight_g / weight_v) loads, as rvc/infer/infer.py:485 relies on
+    legacy = {k.replace(".parametrizations.weight.original0", ".weight_g").replace(".parametrizations.weight.original1", ".weight_v"): v for k, v in sd.items()}
+    m2 = build_module(cfg, 1)
+    res = m2.load_state_dict(legacy, strict=False)
+    assert not res.missing_keys and not res.unexpected_keys
+    assert torch.equal(m2.ups[0].weight, m.ups[0].weight)
+    m2.remove_weight_norm()  # must not raise (the reference's does)
+    assert "ups.0.weight" in m2.state_dict()
+    assert torch.allclose(m2.ups[0].weight, m.ups[0].weight, atol=1e-7)
+
+
+def test_forward_without_cuda_fails_loudly():
+    d, cfg = load_golden("tiny_24k_B2_T40")
+    m = build_module(cfg, 0)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m(torch.zeros(1, cfg.initial_channel, 4), torch.zeros(1, 4))
+
+
+def _conv_from_image(x, wf, shifts, up, cout):
+    """Evaluate a packed layer image exactly as the kernels do: D[t,n] = sum_tap x[t+shift] @ wf[tap]."""
+    B, Cin, L = x.shape
+    halo = int(max(abs(int(s)) for s in shifts))
+    xp = F.pad(x, (halo, halo)).double()
+    N = wf.shape[2]
+    D = torch.zeros(B, L, N, dtype=torch.float64)
+    for tap, s in enumerate(shifts):
+        D += xp[:, :, halo + int(s): halo + int(s) + L].transpose(1, 2) @ torch.from_numpy(wf[tap]).double()
+    return D.reshape(B, L, up, cout).permute(0, 3, 1, 2).reshape(B, cout, L * up)
+
+
+def _decode16(img, fmt):
+    if fmt == "f16":
+        return torch.from_numpy(img.view(np.float16).astype(np.float32))
+    return (torch.from_numpy(img.astype(np.int32)) << 16).view(torch.float32)
+
+
+@pytest.mark.parametrize("name", ["tiny_24k_B2_T40", "v2_40k_B1_T32"])
+def test_packed_images_reproduce_the_layers(built_lib, name):
+    from rvc_b200 import _lib
+
+    d, cfg = load_golden(name)
+    sd = golden_state(d, cfg)
+    w = O.folded_weights(sd)
+    h = _lib.Handle(_lib.make_config(*cfg.ctor_args(), cfg.gin_channels, cfg.sr), 0)
+    h.pack_host(sd)
+    gen = torch.Generator().manual_seed(0)
+    layers = ["conv_pre", "ups.0", "ups.1", "ups.2", "ups.3", "resblocks.0.convs1.2", "resblocks.4.convs1.1",
+              "resblocks.8.convs2.0", "resblocks.11.convs1.2"]
+    for layer in layers:
+        meta = h.packed(layer, 5)
+        Cin, N, cout, up, ntaps, halo, n_tile, kc = (int(v) for v in meta)
+        wf = h.packed(layer, 0).reshape(ntaps, Cin, N)
+        shifts = h.packed(layer, 2)
+        bias = torch.from_numpy(h.packed(layer, 6)).double()
+        x = torch.randn(2, Cin, 37, generator=gen)
+        got = _conv_from_image(x, wf, shifts, up, cout) + bias.reshape(up, cout)[0].reshape(1, -1, 1)
+        if layer == "conv_pre":
+            exp = F.conv1d(x.double(), w["conv_pre.weight"].double(), w["conv_pre.bias"].double(), padding=3)
+        elif layer.startswith("ups."):
+            i = int(layer[4:])
+            u, k = cfg.upsample_rates[i], cfg.upsample_kernel_sizes[i]
+            exp = F.conv_transpose1d(x.double(), w[layer + ".weight"].double(), w[layer + ".bias"].double(), stride=u, padding=(k - u) // 2)
+        else:
+            j = int(layer.split(".")[1]) % 3
+            m = int(layer.split(".")[3])
+            k = cfg.resblock_kernel_sizes[j]
+            dil = cfg.resblock_dilation_sizes[j][m] if ".convs1." in layer else 1
+            exp = F.conv1d(x.double(), w[layer + ".weight"].double(), w[layer + ".bias"].double(), dilation=dil, padding=O.get_padding(k, dil))
+        assert got.shape == exp.shape, layer
+        assert float((got - exp).abs().max()) < 2e-6, layer  # fp32 weight-norm fold rounding only
+        # tensor-core image: [n_tile][tap][kchunk][slice][n][8], equal to the fp32 image rounded to 16 bits
+        if n_tile:
+            for kind, fmt in ((1, "f16"), (4, "bf16")):
+                img = _decode16(h.packed(layer, kind), fmt).reshape(N // n_tile, ntaps, Cin // kc, kc // 8, n_tile, 8)
+                back = img.permute(1, 2, 3, 5, 0, 4).reshape(ntaps, Cin, N)
+                ref16 = torch.from_numpy(wf)
+                ref16 = ref16.half().float() if fmt == "f16" else ref16.bfloat16().float()
+                assert torch.equal(back, ref16), (layer, fmt)
+            masks = h.packed(layer, 3)
+            for t in range(N // n_tile):
+                for tap in range(ntaps):
+                    nz = bool(np.any(wf[tap][:, t * n_tile:(t + 1) * n_tile] != 0))
+                    assert bool((int(masks[t]) >> tap) & 1) == nz, (layer, t, tap)
+        elif name.startswith("v2_"):
+            pytest.fail(f"{layer}: v2 layer without a tensor-core tiling")
+    h.close()
+
+
+def test_v2_48k_tilings(built_lib):
+    """Every conv of the 48 kHz v2 decoder gets a tcgen05 tiling; ups0 skips its all-zero tap blocks."""
+    from rvc_b200 import _lib
+
+    d, cfg = load_golden("v2_48k_B2_T24")
+    sd = golden_state(d, cfg)
+    h = _lib.Handle(_lib.make_config(*cfg.ctor_args(), cfg.gin_channels, cfg.sr), 0)
+    h.pack_host(sd)
+    expect = {"conv_pre": (192, 512, 256, 64), "ups.0": (512, 3072, 256, 64), "ups.1": (256, 1280, 256, 64),
+              "ups.2": (128, 128, 128, 64), "ups.3": (64, 64, 64, 64), "resblocks.0.convs1.0": (256, 256, 256, 64),
+              "resblocks.3.convs1.0": (128, 128, 128, 64), "resblocks.6.convs2.1": (64, 64, 64, 64),
+              "resblocks.9.convs1.2": (32, 32, 32, 32)}
+    for layer, (Cin, N, nt, kc) in expect.items():
+        meta = h.packed(layer, 5)
+        assert (int(meta[0]), int(meta[1]), int(meta[6]), int(meta[7])) == (Cin, N, nt, kc), layer
+    m0 = h.packed("ups.0", 3)
+    assert len(m0) == 12 and all(bin(int(v)).count("1") == 2 for v in m0)  # exactly 2 of 3 shifts per phase
+    h.close()
+
+
+def test_chunk_plan_matches_reference_geometry():
+    from rvc_b200 import chunking as ch
+
+    # 5 min @ 100 frames/s with (x_pad,x_query,x_center,x_max) = (1,6,38,41): 7 split points, 8 chunks
+    chunks = ch.plan_chunks(30000)
+    assert len(chunks) == 8
+    assert chunks[0].start == 0 and chunks[0].stop == 3800 + 200 and chunks[-1].stop == 30000 + 200
+    covered = 0
+    for c in chunks:
+        assert c.trim == 100
+        covered += c.frames - 2 * c.trim
+    assert covered == 30000
+    assert len(ch.plan_chunks(4100)) == 1 and len(ch.plan_chunks(4101)) == 2
+    # trim + concat of per-chunk "decodes" of an identity signal reconstructs the signal
+    sig = np.arange(30000 * 4, dtype=np.float32)
+    padded = np.pad(sig, (400, 400), mode="reflect")
+    dec = [padded[c.start * 4: c.stop * 4] for c in chunks]
+    out = ch.stitch(dec, [c.trim * 4 for c in chunks])
+    assert np.array_equal(out, sig)
+    out_cf = ch.stitch(dec, [c.trim * 4 for c in chunks], crossfade=64)
+    assert out_cf.shape == sig.shape and np.allclose(out_cf, sig, rtol=1e-6, atol=0.05)
+
+
+def test_shard_units_balanced():
+    from rvc_b200 import chunking as ch
+
+    shards = ch.shard_units([3000] * 1024, 8)
+    assert all(len(s) == 128 for s in shards)
+    assert sorted(i for s in shards for i in s) == list(range(1024))
+    shards = ch.shard_units([4000, 4000, 4000, 4000, 4000, 4000, 4000, 2200], 4)
+    assert sorted(i for s in shards for i in s) == list(range(8))
+    assert max(len(s) for s in shards) == 2
+
+
+def test_gloo_world2_sharding(tmp_path):
+    """The N>1 host path of bench.py (sharding + max-over-ranks reduction) on CPU with gloo."""
+    script = tmp_path / "w.py"
+    script.write_text(
+        "import os, sys, torch, torch.distributed as dist\n"
+        f"sys.path.insert(0, {ROOT!r})\n"
+        "import bench\n"
+        "dist.init_process_group('gloo')\n"
+        "r, w = dist.get_rank(), dist.get_world_size()\n"
+        "mine = bench.rank_units(10, r, w)\n"
+        "t = bench.max_over_ranks(float(r + 1), torch.device('cpu'))\n"
+        "tot = bench.sum_over_ranks(float(len(mine)), torch.device('cpu'))\n"
+        "assert t == float(w) and tot == 10.0 * w and mine[0] == 10 * r, (t, tot, mine)\n"
+        "print('ok', r, mine)\n"
+    )
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29533", str(script)], capture_output=True, text=True, env=env, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert p.stdout.count("ok") == 2

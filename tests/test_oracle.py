@@ -1,0 +1,90 @@
+"""The oracle against the golden vectors produced by the reference (oracle/make_golden.py), and
+against the live reference module when /root/reference is present (build container only)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nsf_hifigan_oracle as O
+from helpers import golden_state, load_golden, tensors
+
+CASES = ["tiny_24k_B2_T40", "v2_48k_B2_T24", "v2_40k_B1_T32", "v2_32k_B1_T16"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_oracle_matches_golden(name):
+    d, cfg = load_golden(name)
+    x, f0, g, noise, y = tensors(d)
+    w = O.folded_weights(golden_state(d, cfg))
+    got = O.decoder_forward(w, cfg, x, f0, g, noise)
+    assert got.shape == y.shape == (x.shape[0], 1, x.shape[2] * cfg.upp)
+    assert float((got - y).abs().max()) <= 2e-6  # fp32 reference vs fp32 oracle: summation-order noise only
+
+
+def test_oracle_fp64_close_to_fp32():
+    d, cfg = load_golden("tiny_24k_B2_T40")
+    x, f0, g, noise, y = tensors(d)
+    w = O.folded_weights(golden_state(d, cfg))
+    got = O.decoder_forward(w, cfg, x, f0, g, noise, dtype=torch.float64, source_dtype=torch.float64)
+    assert float((got - y).abs().max()) <= 2e-5
+
+
+def test_sine_source_matches_golden():
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "sine_48k.npz"))
+    for f0k, nk, sk in (("f0", "noise", "sine"), ("f0_real", "noise_real", "sine_real")):
+        f0 = torch.from_numpy(d[f0k]).reshape(-1, d[f0k].shape[-1])
+        noise = torch.from_numpy(d[nk].astype(np.float32))
+        exp = torch.from_numpy(d[sk]).reshape(f0.shape[0], -1)
+        got = O.sine_source(f0, 480, 48000, noise)
+        assert float((got - exp).abs().max()) <= 1e-6
+        # the fp64 phase accumulation (what the CUDA kernel does) stays within the fp32 scan's own error
+        got64 = O.sine_source(f0, 480, 48000, noise, dtype=torch.float64)
+        assert float((got64 - exp).abs().max()) <= 5e-5
+
+
+def test_weight_norm_fold_both_namings():
+    d, cfg = load_golden("tiny_24k_B2_T40")
+    sd = golden_state(d, cfg)
+    legacy = {}
+    for k, v in sd.items():
+        legacy[k.replace(".parametrizations.weight.original0", ".weight_g").replace(".parametrizations.weight.original1", ".weight_v")] = v
+    a, b = O.folded_weights(sd), O.folded_weights(legacy)
+    assert a.keys() == b.keys()
+    for k in a:
+        assert torch.equal(a[k], b[k])
+    v, g_ = sd["ups.0.parametrizations.weight.original1"], sd["ups.0.parametrizations.weight.original0"]
+    assert torch.allclose(a["ups.0.weight"].reshape(v.shape[0], -1).norm(dim=1), g_.flatten(), rtol=1e-5)
+
+
+def test_property_shapes_and_bounds():
+    """Properties the reference's own unit tests check (tests/unit/test_generators.py:102-190)."""
+    d, cfg = load_golden("tiny_24k_B2_T40")
+    x, f0, g, noise, y = tensors(d)
+    w = O.folded_weights(golden_state(d, cfg))
+    assert cfg.upp == int(np.prod(cfg.upsample_rates))
+    y_nog = O.decoder_forward(w, cfg, x, f0, None, noise)
+    assert y_nog.shape == y.shape
+    assert float(y.abs().max()) <= 1.0 and float(y_nog.abs().max()) <= 1.0
+    # voiced mask semantics: unvoiced frames carry only the (larger) noise floor
+    f = torch.tensor([[0.0, 220.0]])
+    s = O.sine_source(f, cfg.upp, cfg.sr, torch.zeros(1, 2 * cfg.upp))
+    assert float(s[0, : cfg.upp].abs().max()) == 0.0 and float(s[0, cfg.upp :].abs().max()) > 0.05
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/rvc"), reason="reference checkout not present (GPU box)")
+def test_oracle_matches_live_reference():
+    sys.path.insert(0, "/root/reference")
+    from rvc.lib.algorithm.generators.hifigan_nsf import HiFiGANNSFGenerator as Ref
+
+    cfg = O.CONFIG_40K
+    torch.manual_seed(99)
+    ref = Ref(*cfg.ctor_args(), **cfg.ctor_kwargs()).eval()
+    x, f0, g, _ = O.synth_inputs(cfg, 1, 20, seed=3)
+    torch.manual_seed(5)
+    with torch.no_grad():
+        y = ref(x, f0, g=g)
+    noise = O.draw_reference_noise(5, 1, 20 * cfg.upp)
+    got = O.decoder_forward(O.folded_weights(ref.state_dict()), cfg, x, f0, g, noise)
+    assert float((got - y).abs().max()) <= 2e-6
