@@ -2,12 +2,12 @@
 //
 //   D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]      (fp32 accumulate in TMEM)
 //
-// CTA = 6 warps, warp-specialised, persistent over (item, time-tile, N-tile):
+// CTA = 10 warps, warp-specialised, persistent over (item, time-tile, N-tile):
 //   warp 0   TMA producer   1-D bulk copies (cp.async.bulk, UBLKCP) of activation slices and
 //                           weight blocks into shared memory, completion on mbarriers
 //   warp 1   MMA issuer     one thread issues tcgen05.mma (kind::f16, M=128, N=N_TILE, K=16),
 //                           tcgen05.commit releases smem stages / publishes the accumulator
-//   warps 2-5 epilogue      tcgen05.ld accumulator -> registers -> fused epilogue (bias, residual,
+//   warps 2-9 epilogue      tcgen05.ld accumulator -> registers -> fused epilogue (bias, residual,
 //                           MRF average, leaky_relu, 16-bit convert) -> coalesced global stores
 //
 // Shared-memory operand layout: NO swizzle, K-major "interleaved" core matrices.  The blocked-8
@@ -128,7 +128,7 @@ struct MmaCfg {
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
-constexpr int MMA_THREADS = 192;
+constexpr int MMA_THREADS = 320;  // producer warp + MMA warp + 2 epilogue warpgroups
 
 template <int N_TILE, int MB, int KC, int B_STAGES>
 __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
   if (threadIdx.x == 0) {
     for (int i = 0; i < 2; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
     for (int i = 0; i < B_STAGES; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
-    for (int i = 0; i < Cfg::ACC_STAGES; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, 128); }
+    for (int i = 0; i < Cfg::ACC_STAGES; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, MMA_THREADS - 64); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -258,8 +258,14 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
     }
     __syncwarp();
   } else {
-    // ===================== epilogue warps =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    // ===================== epilogue warps (2 warpgroups) =====================
+    const int q = warp & 3;          // TMEM lane quarter this warp may access
+    const int wg = (warp - 2) >> 2;  // work items (mb, 32-column chunk) alternate between the warpgroups
+    constexpr int CH = N_TILE / 32;
+    constexpr int ITEMS = MB * CH;
+    const Epilogue& e = p.epi;
+    const bool fast = (e.up == 1);
+    const size_t slice_stride = (size_t)e.Lp_out * 8;
     uint32_t acc_it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int b = tile / tiles_per_item;
@@ -270,20 +276,91 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
       const uint32_t as = acc_it % Cfg::ACC_STAGES;
       mbar_wait(acc_full + 8 * as, (acc_it / Cfg::ACC_STAGES) & 1u);
       tc_fence_after();
+      const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (MB * N_TILE);
 #pragma unroll 1
-      for (int mb = 0; mb < MB; ++mb) {
+      for (int item = wg; item < ITEMS; item += 2) {
+        const int mb = item / CH;
+        const int c0 = (item - mb * CH) * 32;
         const int t_in = t0 + mb * 128 + q * 32 + lane;
-#pragma unroll 1
-        for (int c0 = 0; c0 < N_TILE; c0 += 32) {
-          uint32_t r[32];
-          tc_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + as * (MB * N_TILE) + mb * N_TILE + c0, r);
-          if (t_in < p.L_in) {
+        const bool valid = t_in < p.L_in;
+        uint32_t r[32];
+        if (fast) {
+          // ---- lean path (every ordinary conv): up == 1, output row == input row ----
+          const int n0 = n_tile * N_TILE + c0;
+          const size_t off = (((size_t)b * (e.cout >> 3) + (n0 >> 3)) * e.Lp_out + PADL + t_in) * 8;
+          float4 rr[8], sm[8];
+          if (e.res && valid) {  // issue the residual loads before waiting on TMEM
 #pragma unroll
+            for (int s8 = 0; s8 < 4; ++s8) {
+              rr[2 * s8] = *reinterpret_cast<const float4*>(e.res + off + s8 * slice_stride);
+              rr[2 * s8 + 1] = *reinterpret_cast<const float4*>(e.res + off + s8 * slice_stride + 4);
+            }
+          }
+          if (e.sum_in && valid) {
+#pragma unroll
+            for (int s8 = 0; s8 < 4; ++s8) {
+              sm[2 * s8] = *reinterpret_cast<const float4*>(e.sum_in + off + s8 * slice_stride);
+              sm[2 * s8 + 1] = *reinterpret_cast<const float4*>(e.sum_in + off + s8 * slice_stride + 4);
+            }
+          }
+          tc_ld32(t_acc + mb * N_TILE + c0, r);
+          if (valid) {
+            const float4* bp = reinterpret_cast<const float4*>(e.bias + (size_t)b * e.bias_bstride + n0);
+#pragma unroll
+            for (int s8 = 0; s8 < 4; ++s8) {
+              float v[8];
+              const float4 b0 = __ldg(bp + 2 * s8), b1 = __ldg(bp + 2 * s8 + 1);
+              v[0] = __uint_as_float(r[s8 * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[s8 * 8 + 1]) + b0.y;
+              v[2] = __uint_as_float(r[s8 * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[s8 * 8 + 3]) + b0.w;
+              v[4] = __uint_as_float(r[s8 * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[s8 * 8 + 5]) + b1.y;
+              v[6] = __uint_as_float(r[s8 * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[s8 * 8 + 7]) + b1.w;
+              if (e.res) {
+                v[0] += rr[2 * s8].x; v[1] += rr[2 * s8].y; v[2] += rr[2 * s8].z; v[3] += rr[2 * s8].w;
+                v[4] += rr[2 * s8 + 1].x; v[5] += rr[2 * s8 + 1].y; v[6] += rr[2 * s8 + 1].z; v[7] += rr[2 * s8 + 1].w;
+              }
+              if (e.scale != 1.f) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] *= e.scale;
+              }
+              if (e.sum_in) {
+                v[0] += sm[2 * s8].x; v[1] += sm[2 * s8].y; v[2] += sm[2 * s8].z; v[3] += sm[2 * s8].w;
+                v[4] += sm[2 * s8 + 1].x; v[5] += sm[2 * s8 + 1].y; v[6] += sm[2 * s8 + 1].z; v[7] += sm[2 * s8 + 1].w;
+              }
+              const size_t o = off + s8 * slice_stride;
+              if (e.out_f32) {
+                *reinterpret_cast<float4*>(e.out_f32 + o) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(e.out_f32 + o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+              }
+              if (e.out_act) {
+                // leaky_relu(v) = max(v, slope*v) for 0 < slope < 1
+                uint32_t pk[4];
+                if (e.act_fmt == ACT_F16) {
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    __half2 hh = __floats2half2_rn(fmaxf(v[2 * i], v[2 * i] * e.slope), fmaxf(v[2 * i + 1], v[2 * i + 1] * e.slope));
+                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                  }
+                } else {
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    __nv_bfloat162 hh = __floats2bfloat162_rn(fmaxf(v[2 * i], v[2 * i] * e.slope), fmaxf(v[2 * i + 1], v[2 * i + 1] * e.slope));
+                    pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+                  }
+                }
+                *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(e.out_act) + o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              }
+            }
+          }
+        } else {
+          // ---- generic path (polyphase upsample: phase scatter) ----
+          tc_ld32(t_acc + mb * N_TILE + c0, r);
+          if (valid) {
+#pragma unroll 1
             for (int s8 = 0; s8 < 4; ++s8) {
               float v[8];
 #pragma unroll
               for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[s8 * 8 + i]);
-              epilogue_store<8>(p.epi, b, t_in, n_tile * N_TILE + c0 + s8 * 8, v);
+              epilogue_store<8>(e, b, t_in, n_tile * N_TILE + c0 + s8 * 8, v);
             }
           }
         }
