@@ -67,6 +67,11 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                "l"(src), "r"(bytes), "r"(bar)
                : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -92,6 +97,14 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr)
       : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tc_ld8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
@@ -173,90 +186,97 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
   const int rows = Cfg::MT + 2 * p.halo;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      uint32_t a_it = 0, b_it = 0;
-      const uint8_t* act = reinterpret_cast<const uint8_t*>(p.act_in);
-      const uint8_t* wgt = reinterpret_cast<const uint8_t*>(p.w);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int b = tile / tiles_per_item;
-        const int rem = tile - b * tiles_per_item;
-        const int m_tile = rem / p.n_tiles;
-        const int n_tile = rem - m_tile * p.n_tiles;
-        const int t0 = m_tile * Cfg::MT;
-        const uint32_t mask = p.tapmask[n_tile];
-        for (int kc = 0; kc < nkc; ++kc) {
-          const uint32_t ab = a_it & 1u;
-          mbar_wait(a_empty + 8 * ab, ((a_it >> 1) & 1u) ^ 1u);
-          mbar_expect_tx(a_full + 8 * ab, (uint32_t)(KC / 8) * rows * 16);
+    // ===================== TMA producer (converged warp, one elected lane issues) =====================
+    uint32_t a_stage = 0, a_phase = 0, b_stage = 0, b_phase = 0;
+    const uint8_t* act = reinterpret_cast<const uint8_t*>(p.act_in);
+    const uint8_t* wgt = reinterpret_cast<const uint8_t*>(p.w);
+    const int n_tiles = p.n_tiles, ntaps = p.ntaps;
+    const uint32_t a_bytes = (uint32_t)rows * 16;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int b = tile / tiles_per_item;
+      const int rem = tile - b * tiles_per_item;
+      const int m_tile = rem / n_tiles;
+      const int n_tile = rem - m_tile * n_tiles;
+      const int t0 = m_tile * Cfg::MT;
+      const uint32_t mask = p.tapmask[n_tile];
+      const uint8_t* a_src = act + (((size_t)b * nsl) * p.Lp_in + PADL + t0 - p.halo) * 16;
+      const uint8_t* w_src = wgt + (size_t)n_tile * ntaps * nkc * Cfg::B_STAGE_BYTES;
+      for (int kc = 0; kc < nkc; ++kc) {
+        mbar_wait(a_empty + 8 * a_stage, a_phase ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(a_full + 8 * a_stage, (uint32_t)(KC / 8) * a_bytes);
 #pragma unroll
-          for (int sl = 0; sl < KC / 8; ++sl) {
-            const uint8_t* src =
-                act + (((size_t)b * nsl + kc * (KC / 8) + sl) * p.Lp_in + PADL + t0 - p.halo) * 16;
-            bulk_g2s(a_smem + ab * Cfg::A_BUF_BYTES + sl * Cfg::A_SLICE_BYTES, src, (uint32_t)rows * 16,
-                     a_full + 8 * ab);
+          for (int sl = 0; sl < KC / 8; ++sl)
+            bulk_g2s(a_smem + a_stage * Cfg::A_BUF_BYTES + sl * Cfg::A_SLICE_BYTES,
+                     a_src + (size_t)(kc * (KC / 8) + sl) * p.Lp_in * 16, a_bytes, a_full + 8 * a_stage);
+        }
+        __syncwarp();
+        a_stage ^= 1u;
+        if (a_stage == 0) a_phase ^= 1u;
+        for (int tap = 0; tap < ntaps; ++tap) {
+          if (!((mask >> tap) & 1u)) continue;
+          mbar_wait(b_empty + 8 * b_stage, b_phase ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(b_full + 8 * b_stage, Cfg::B_STAGE_BYTES);
+            bulk_g2s(b_smem + b_stage * Cfg::B_STAGE_BYTES, w_src + (size_t)(tap * nkc + kc) * Cfg::B_STAGE_BYTES,
+                     Cfg::B_STAGE_BYTES, b_full + 8 * b_stage);
           }
-          ++a_it;
-          for (int tap = 0; tap < p.ntaps; ++tap) {
-            if (!((mask >> tap) & 1u)) continue;
-            const uint32_t bs = b_it % B_STAGES;
-            mbar_wait(b_empty + 8 * bs, ((b_it / B_STAGES) & 1u) ^ 1u);
-            mbar_expect_tx(b_full + 8 * bs, Cfg::B_STAGE_BYTES);
-            const uint8_t* src = wgt + (((size_t)n_tile * p.ntaps + tap) * nkc + kc) * Cfg::B_STAGE_BYTES;
-            bulk_g2s(b_smem + bs * Cfg::B_STAGE_BYTES, src, Cfg::B_STAGE_BYTES, b_full + 8 * bs);
-            ++b_it;
-          }
+          __syncwarp();
+          if (++b_stage == B_STAGES) { b_stage = 0; b_phase ^= 1u; }
         }
       }
     }
-    __syncwarp();
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      uint32_t a_it = 0, b_it = 0, acc_it = 0;
-      const uint32_t idesc = make_idesc(p.act_fmt_in, N_TILE);
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int rem = tile % tiles_per_item;
-        const int n_tile = rem % p.n_tiles;
-        const uint32_t mask = p.tapmask[n_tile];
-        const uint32_t as = acc_it % Cfg::ACC_STAGES;
-        mbar_wait(acc_empty + 8 * as, ((acc_it / Cfg::ACC_STAGES) & 1u) ^ 1u);
-        tc_fence_after();
-        const uint32_t d_base = tmem_base + as * (MB * N_TILE);
-        bool fresh = true;
-        for (int kc = 0; kc < nkc; ++kc) {
-          const uint32_t ab = a_it & 1u;
-          mbar_wait(a_full + 8 * ab, (a_it >> 1) & 1u);
-          for (int tap = 0; tap < p.ntaps; ++tap) {
-            if (!((mask >> tap) & 1u)) continue;
-            const uint32_t bs = b_it % B_STAGES;
-            mbar_wait(b_full + 8 * bs, (b_it / B_STAGES) & 1u);
-            tc_fence_after();
-            const uint32_t a_row0 = a_smem + ab * Cfg::A_BUF_BYTES + (uint32_t)(p.halo + p.shift[tap]) * 16;
-            const uint32_t b_row0 = b_smem + bs * Cfg::B_STAGE_BYTES;
+    // The whole warp runs the loop converged (so every descriptor stays in uniform registers and
+    // ptxas emits no per-MMA "elect" waterfall); one elected lane issues the MMAs and the commits.
+    // ncu r1c: the former `if (lane == 0)` form spent ~120 clk of issue overhead per MMA and was the
+    // bottleneck of every convolution (the tensor pipe needs one N=128 MMA per 64 clk).
+    uint32_t a_stage = 0, a_phase = 0, b_stage = 0, b_phase = 0, acc_stage = 0, acc_phase = 0;
+    const uint32_t idesc = make_idesc(p.act_fmt_in, N_TILE);
+    const uint64_t a_desc0 = make_smem_desc(a_smem, Cfg::A_SLICE_BYTES, 128);
+    const uint64_t b_desc0 = make_smem_desc(b_smem, Cfg::B_SLICE_BYTES, 128);
+    const int n_tiles = p.n_tiles, ntaps = p.ntaps;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const uint32_t mask = p.tapmask[tile % n_tiles];
+      mbar_wait(acc_empty + 8 * acc_stage, acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_base = tmem_base + acc_stage * (MB * N_TILE);
+      uint32_t fresh = 0u;  // 0 for the very first MMA of the tile (overwrite), 1 afterwards
+      for (int kc = 0; kc < nkc; ++kc) {
+        mbar_wait(a_full + 8 * a_stage, a_phase);
+        const uint64_t a_kc = a_desc0 + (uint64_t)((a_stage * Cfg::A_BUF_BYTES) >> 4) + (uint64_t)p.halo;
+        for (int tap = 0; tap < ntaps; ++tap) {
+          if (!((mask >> tap) & 1u)) continue;
+          mbar_wait(b_full + 8 * b_stage, b_phase);
+          tc_fence_after();
+          if (elect_one()) {
+            // one row of the blocked layout is 16 B, so a tap shift is +shift in descriptor units
+            const uint64_t a_tap = a_kc + (uint64_t)(int64_t)p.shift[tap];
+            const uint64_t b_st = b_desc0 + (uint64_t)((b_stage * Cfg::B_STAGE_BYTES) >> 4);
 #pragma unroll
             for (int mb = 0; mb < MB; ++mb) {
 #pragma unroll
               for (int ks = 0; ks < KC / 16; ++ks) {
-                const uint64_t adesc = make_smem_desc(a_row0 + mb * 128 * 16 + 2 * ks * Cfg::A_SLICE_BYTES,
-                                                      Cfg::A_SLICE_BYTES, 128);
-                const uint64_t bdesc =
-                    make_smem_desc(b_row0 + 2 * ks * Cfg::B_SLICE_BYTES, Cfg::B_SLICE_BYTES, 128);
-                tc_mma_f16(d_base + mb * N_TILE, adesc, bdesc, idesc, (fresh && ks == 0) ? 0u : 1u);
+                tc_mma_f16(d_base + mb * N_TILE, a_tap + (uint64_t)((mb * 128 * 16 + 2 * ks * Cfg::A_SLICE_BYTES) >> 4),
+                           b_st + (uint64_t)((2 * ks * Cfg::B_SLICE_BYTES) >> 4), idesc, (ks == 0) ? fresh : 1u);
               }
             }
-            fresh = false;
-            tc_commit(b_empty + 8 * bs);
-            ++b_it;
+            tc_commit(b_empty + 8 * b_stage);
           }
-          tc_commit(a_empty + 8 * ab);
-          ++a_it;
+          __syncwarp();
+          fresh = 1u;
+          if (++b_stage == B_STAGES) { b_stage = 0; b_phase ^= 1u; }
         }
-        tc_commit(acc_full + 8 * as);
-        ++acc_it;
+        if (elect_one()) tc_commit(a_empty + 8 * a_stage);
+        __syncwarp();
+        a_stage ^= 1u;
+        if (a_stage == 0) a_phase ^= 1u;
       }
+      if (elect_one()) tc_commit(acc_full + 8 * acc_stage);
+      __syncwarp();
+      if (++acc_stage == Cfg::ACC_STAGES) { acc_stage = 0; acc_phase ^= 1u; }
     }
-    __syncwarp();
   } else {
     // ===================== epilogue warps (2 warpgroups) =====================
     const int q = warp & 3;          // TMEM lane quarter this warp may access
@@ -283,8 +303,8 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
         const int c0 = (item - mb * CH) * 32;
         const int t_in = t0 + mb * 128 + q * 32 + lane;
         const bool valid = t_in < p.L_in;
-        uint32_t r[32];
         if (fast) {
+          uint32_t r[32];
           // ---- lean path (every ordinary conv): up == 1, output row == input row ----
           const int n0 = n_tile * N_TILE + c0;
           const size_t off = (((size_t)b * (e.cout >> 3) + (n0 >> 3)) * e.Lp_out + PADL + t_in) * 8;
@@ -353,13 +373,16 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
           }
         } else {
           // ---- generic path (polyphase upsample: phase scatter) ----
-          tc_ld32(t_acc + mb * N_TILE + c0, r);
-          if (valid) {
+          // 8 columns per TMEM load so the accumulator registers are indexed statically (a 32-wide
+          // array indexed by the s8 loop variable lived in local memory: STL/LDL in the r1c capture).
 #pragma unroll 1
-            for (int s8 = 0; s8 < 4; ++s8) {
+          for (int s8 = 0; s8 < 4; ++s8) {
+            uint32_t r8[8];
+            tc_ld8(t_acc + mb * N_TILE + c0 + s8 * 8, r8);
+            if (valid) {
               float v[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[s8 * 8 + i]);
+              for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r8[i]);
               epilogue_store<8>(e, b, t_in, n_tile * N_TILE + c0 + s8 * 8, v);
             }
           }
