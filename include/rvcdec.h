@@ -113,6 +113,13 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
                         const float* noise, uint64_t seed, float* out,
                         int32_t B, int32_t T, int32_t mode, size_t max_device_bytes);
 
+/* Tuning knobs of the fast mode (results stay within the fast-mode tolerance for every setting):
+ *   "fused_mrf"  0 = every ResBlock convolution is its own kernel on every stage;
+ *                1 = (default) the 64/32-channel stages run the fused ResBlock-chain kernel, one launch
+ *                    per ResBlock (residuals.py:71-80 kept on chip: residual in TMEM, operands in smem);
+ *                2 = same kernel, one launch per stage (all ResBlocks of the MRF over one tile). */
+int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value);
+
 /* Number of kernels launched by the last forward on this handle. */
 int64_t rvcdec_last_launch_count(const rvcdec_handle* h);
 
@@ -143,6 +150,11 @@ int32_t rvcdec_profile_read(rvcdec_handle* h, rvcdec_profile_entry* out, int32_t
 int rvcdec_debug_set_stop(rvcdec_handle* h, int32_t stop_after);
 int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_t dst_numel,
                           void* workspace, int32_t B, int32_t T, int32_t mode, void* stream);
+/* Instrumented twin of the fused ResBlock kernel: after rvcdec_set_option(h, "fused_timing", 1) every
+ * fused launch (up to 32) records, per SM, clock64 spans {MMA warp: wait operand rows, wait acc1 drained,
+ * wait weights, total, -,-,-,-; epilogue warp: wait conv1 accumulator, wait conv2 accumulator, stage-input
+ * load, total, ...} (16 int64 per SM).  Returns the number of launches recorded. */
+int64_t rvcdec_debug_fused_timing(rvcdec_handle* h, int64_t* dst, int64_t dst_numel);
 /* Copy a packed host-side weight image for CPU tests (no GPU needed). Layer = reference module
  * name ("conv_pre", "ups.0", "resblocks.4.convs1.2").  kind 0 = fp32 [tap][ci][n] image, 1 = fp16
  * tensor-core image, 2 = tap shifts (int32), 3 = tensor-core tap masks (uint32 per N tile),

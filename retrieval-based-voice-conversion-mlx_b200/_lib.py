@@ -50,8 +50,8 @@ class ProfileEntry(C.Structure):
 
 EXPORTS = [
     "rvcdec_create", "rvcdec_load_weights", "rvcdec_workspace_bytes", "rvcdec_forward", "rvcdec_forward_host",
-    "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
-    "rvcdec_debug_packed", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
+    "rvcdec_set_option", "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
+    "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
 ]
 
 _lib = None
@@ -77,6 +77,8 @@ def lib() -> C.CDLL:
     L.rvcdec_forward.restype = C.c_int
     L.rvcdec_forward_host.argtypes = [vp, vp, vp, vp, vp, u64, vp, i32, i32, i32, sz]
     L.rvcdec_forward_host.restype = C.c_int
+    L.rvcdec_set_option.argtypes = [vp, C.c_char_p, i64]
+    L.rvcdec_set_option.restype = C.c_int
     L.rvcdec_last_launch_count.argtypes = [vp]
     L.rvcdec_last_launch_count.restype = i64
     L.rvcdec_profile_enable.argtypes = [vp, i32]
@@ -91,6 +93,8 @@ def lib() -> C.CDLL:
     L.rvcdec_debug_pack_host.restype = C.c_int
     L.rvcdec_debug_packed.argtypes = [vp, C.c_char_p, i32, vp, i64]
     L.rvcdec_debug_packed.restype = i64
+    L.rvcdec_debug_fused_timing.argtypes = [vp, vp, i64]
+    L.rvcdec_debug_fused_timing.restype = i64
     L.rvcdec_destroy.argtypes = [vp]
     L.rvcdec_destroy.restype = None
     L.rvcdec_last_error.argtypes = []
@@ -191,6 +195,17 @@ class Handle:
     def forward_host(self, x, f0, g, noise, seed, out, B, T, mode, max_device_bytes=0) -> None:
         check(lib().rvcdec_forward_host(self._h, x, f0, g, noise, C.c_uint64(seed & (2**64 - 1)), out, B, T, mode,
                                         max_device_bytes), "rvcdec_forward_host")
+
+    def set_option(self, key: str, value: int) -> None:
+        check(lib().rvcdec_set_option(self._h, key.encode(), int(value)), "rvcdec_set_option")
+
+    def fused_timing(self, num_sms: int = 148):
+        import numpy as np
+
+        buf = np.zeros(32 * num_sms * 16, dtype=np.int64)
+        n = lib().rvcdec_debug_fused_timing(self._h, buf.ctypes.data, buf.size)
+        check(n, "rvcdec_debug_fused_timing")
+        return buf[: n * num_sms * 16].reshape(n, num_sms, 16)
 
     def launch_count(self) -> int:
         return int(lib().rvcdec_last_launch_count(self._h))

@@ -143,6 +143,43 @@ cudaError_t launch_conv_f32(const ConvParams& p, cudaStream_t s);
 cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms, cudaStream_t s);
 bool conv_mma_supported(int n_tile, int kc);
 
+// ---- fused ResBlock chain (mrf_fused.cu) ------------------------------------
+// One ResBlock (residuals.py:71-80) = nd x [ xt = conv1_d(lrelu(x)); xt = conv2(lrelu(xt)); x = xt + x ].
+// The kernel keeps x (fp32) in TMEM for the whole chain and the two 16-bit operand tiles in shared
+// memory; only the stage input is read from HBM and only the MRF sum / stage output is written.
+constexpr int FUSED_MAX_D = 4;   // dilations per ResBlock
+constexpr int FUSED_MAX_RB = 4;  // ResBlocks per launch
+struct FusedConv {
+  const void* w;      // tensor-core image of the conv: [tap][C/8][C][8] 16-bit, one tap block = C*C*2 bytes
+  const float* bias;  // conv1: its bias; conv2: CUMULATIVE bias b2[0]+..+b2[m] (x stays un-biased in TMEM)
+  int ntaps, dil;
+};
+struct FusedRB {
+  FusedConv c1[FUSED_MAX_D], c2[FUSED_MAX_D];
+  int sum_in;   // 1: add the running MRF sum (p.sum) to this ResBlock's output
+  int is_last;  // 1: this ResBlock completes the MRF average -> write out_f32 / out_act; 0: write p.sum
+};
+struct FusedParams {
+  const float* x_in;  // stage input, fp32 blocked-8 (B, C, L)
+  float* sum;         // MRF accumulator, fp32 blocked-8
+  float* out_f32;     // stage output (average), fp32 blocked-8, or null
+  void* out_act;      // leaky_relu(stage output, out_slope) in out_fmt, blocked-8, or null
+  int fmt;            // operand format of this stage (ACT_F16 / ACT_BF16)
+  int out_fmt;
+  float scale;        // 1 / num_kernels
+  float slope;        // 0.1 inside the ResBlocks
+  float out_slope;
+  int B, L, Lp, C;
+  int nd, n_rb;
+  int margin;         // rows at each tile edge that are recomputed by the neighbouring tile
+  int tiles_per_item;
+  long long* timing;  // null, or [gridDim.x][16] clock64 spans (instrumented kernel twin)
+  FusedRB rb[FUSED_MAX_RB];
+};
+bool mrf_fused_supported(int C, int max_taps, int max_halo);
+int mrf_fused_tile_rows(int C);
+cudaError_t launch_mrf_fused(const FusedParams& p, int num_sms, cudaStream_t s);
+
 struct SourceParams {
   const float* f0;      // (B, T)
   const float* noise;   // (B, T*upp) or null

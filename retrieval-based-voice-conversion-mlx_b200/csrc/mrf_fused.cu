@@ -1,0 +1,512 @@
+// Fused multi-receptive-field stage for the low-channel, high-rate stages (C = 64, 32):
+// a whole ResBlock chain (residuals.py:71-80; 3 x [lrelu -> dilated conv1 -> lrelu -> conv2 -> +x])
+// runs inside one CTA per time tile, with the MRF average (hifigan_nsf.py:200-207) folded into the
+// last write.  HBM sees the stage input once per ResBlock and the running MRF sum; the ~7 tensors
+// per conv pair the un-fused path streams through HBM (SURVEY 8a "activation volume") stay on chip:
+//
+//   TMEM   x[MB][128 x C] fp32   the residual stream; conv2 ACCUMULATES into it (the "+x" is free)
+//          acc1[2][128 x C] fp32 conv1 accumulators, double-buffered per 128-row block
+//   smem   A0, A1                16-bit operand tiles (MB*128 + 2*32 pad rows) x C, blocked-8 K-major
+//                                = the no-swizzle UMMA layout, a tap / dilation is a row offset
+//          W ring                S tap blocks (C x C 16-bit); a conv's k taps stay resident while the
+//                                MB row blocks pass over them, so L2 -> smem weight traffic is per tile
+//
+// Tiles overlap by `margin` rows per side (the chain's receptive field); every conv is computed on
+// all MB*128 rows and the rows whose inputs fell outside the tile are simply never stored.
+//
+// Warp roles (320 threads): warp 0 = TMA weight producer, warp 1 = tcgen05.mma issuer,
+// warps 2-9 = epilogue (TMEM -> bias/lrelu/convert -> smem operand; stage input load; final store).
+#include <algorithm>
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace rvcdec {
+
+constexpr int FUSED_THREADS = 320;
+constexpr int FUSED_EPI_WARPS = 8;
+
+template <int C, int MB, int S>
+struct FusedCfg {
+  static constexpr int MT = MB * 128;
+  static constexpr int PAD = 32;
+  static constexpr int ROWS = MT + 2 * PAD;
+  static constexpr int NSL = C / 8;
+  static constexpr int A_SLICE = ROWS * 16;
+  static constexpr int A_BUF = NSL * A_SLICE;
+  static constexpr int W_SLOT = C * C * 2;
+  static constexpr int B_SLICE = C * 16;
+  static constexpr int X_COLS = MB * C;
+  static constexpr int ACC1_COL0 = X_COLS;
+  static constexpr int USED_COLS = X_COLS + 2 * C;
+  static constexpr int TMEM_COLS = USED_COLS <= 128 ? 128 : USED_COLS <= 256 ? 256 : 512;
+  static constexpr int NUM_BARS = 2 * S + 4 + 3 * MB;
+  static constexpr int SMEM_BYTES = 128 + 2 * A_BUF + S * W_SLOT + NUM_BARS * 8 + 16;
+  static_assert(USED_COLS <= 512, "TMEM budget");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+  static_assert(C == 32 || C == 64, "column split below assumes 16 or 32 columns per epilogue warp");
+};
+
+__device__ __forceinline__ uint32_t uni(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+
+__device__ __forceinline__ uint32_t pack2(float a, float b, int fmt) {
+  if (fmt == ACT_F16) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// packed fp32x2 arithmetic (sm_100 FADD2 / FMUL2): halves the epilogue's instruction count
+__device__ __forceinline__ uint64_t f2_pack_u(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) { return f2_pack_u(__float_as_uint(lo), __float_as_uint(hi)); }
+__device__ __forceinline__ uint64_t f2_splat(float v) { return f2_pack(v, v); }
+__device__ __forceinline__ float2 f2_unpack(uint64_t v) {
+  uint32_t lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
+  return make_float2(__uint_as_float(lo), __uint_as_float(hi));
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// 16-bit pair of leaky_relu(v) = max(v, slope * v), 0 < slope < 1
+template <bool BF16>
+__device__ __forceinline__ uint32_t lrelu_pack(uint64_t v, uint64_t slope2) {
+  const float2 a = f2_unpack(v), m = f2_unpack(f2_mul(v, slope2));
+  return pack2(fmaxf(a.x, m.x), fmaxf(a.y, m.y), BF16 ? ACT_BF16 : ACT_F16);
+}
+
+template <int NC>
+__device__ __forceinline__ void tmem_load_cols(uint32_t taddr, uint32_t (&r)[NC]);
+template <>
+__device__ __forceinline__ void tmem_load_cols<16>(uint32_t taddr, uint32_t (&r)[16]) { tc_ld16(taddr, r); }
+template <>
+__device__ __forceinline__ void tmem_load_cols<32>(uint32_t taddr, uint32_t (&r)[32]) { tc_ld32(taddr, r); }
+
+// TIMING = true compiles the instrumented twin used by tools/fused_timing.py: the MMA warp and one
+// epilogue warp accumulate clock64() spans around every wait into p.timing[blockIdx.x][16].
+#define TWAIT(slot_, ...)                                  \
+  do {                                                     \
+    if (TIMING) {                                          \
+      const long long _t = clock64();                      \
+      __VA_ARGS__;                                         \
+      tacc[slot_] += clock64() - _t;                       \
+    } else {                                               \
+      __VA_ARGS__;                                         \
+    }                                                      \
+  } while (0)
+
+template <int C, int MB, int S, bool BF16, bool TIMING>
+__global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __grid_constant__ FusedParams p) {
+  using Cfg = FusedCfg<C, MB, S>;
+  long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const long long t_begin = TIMING ? clock64() : 0;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 127u) & ~127u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t a0_smem = smem_base;
+  const uint32_t a1_smem = a0_smem + Cfg::A_BUF;
+  const uint32_t w_smem = a1_smem + Cfg::A_BUF;
+  const uint32_t bars = w_smem + S * Cfg::W_SLOT;
+  const uint32_t w_full = bars, w_empty = w_full + 8 * S, acc1_full = w_empty + 8 * S, acc1_empty = acc1_full + 16,
+                 x_full = acc1_empty + 16, a0_ready = x_full + 8 * MB, a1_ready = a0_ready + 8 * MB;
+  const uint32_t tmem_slot = a1_ready + 8 * MB;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);  // provably warp-uniform role index
+  const int lane = threadIdx.x & 31;
+
+  // operand tiles start as zeros: the pad rows are the convolutions' zero padding at the tile edges
+  for (int i = threadIdx.x; i < 2 * Cfg::A_BUF / 16; i += FUSED_THREADS)
+    reinterpret_cast<uint4*>(smem_gen)[i] = make_uint4(0, 0, 0, 0);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < S; ++i) { mbar_init(w_full + 8 * i, 1); mbar_init(w_empty + 8 * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(acc1_full + 8 * i, 1); mbar_init(acc1_empty + 8 * i, FUSED_EPI_WARPS); }
+    for (int i = 0; i < MB; ++i) {
+      mbar_init(x_full + 8 * i, 1);
+      mbar_init(a0_ready + 8 * i, FUSED_EPI_WARPS);
+      mbar_init(a1_ready + 8 * i, FUSED_EPI_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  fence_proxy_async();
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                 "r"((uint32_t)Cfg::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  const int nd = p.nd, n_rb = p.n_rb;
+  const int total_work = p.B * p.tiles_per_item;
+
+  if (warp == 0) {
+    // ===================== weight producer =====================
+    uint32_t slot = 0, ph = 0;
+    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+      for (int rb = 0; rb < n_rb; ++rb) {
+        for (int m = 0; m < nd; ++m) {
+#pragma unroll 1
+          for (int which = 0; which < 2; ++which) {
+            const FusedConv& cv = which ? p.rb[rb].c2[m] : p.rb[rb].c1[m];
+            const uint8_t* src = reinterpret_cast<const uint8_t*>(cv.w);
+            const int ntaps = cv.ntaps;
+            for (int tap = 0; tap < ntaps; ++tap) {
+              mbar_wait(w_empty + 8 * slot, ph ^ 1u);
+              if (elect_one()) {
+                mbar_expect_tx(w_full + 8 * slot, Cfg::W_SLOT);
+                bulk_g2s(w_smem + slot * Cfg::W_SLOT, src + (size_t)tap * Cfg::W_SLOT, Cfg::W_SLOT, w_full + 8 * slot);
+              }
+              __syncwarp();
+              if (++slot == S) { slot = 0; ph ^= 1u; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (converged warp, elected lane issues) =====================
+    const uint32_t idesc = make_idesc(p.fmt, C);
+    const uint64_t a0_desc = make_smem_desc(a0_smem, Cfg::A_SLICE, 128) + (uint64_t)Cfg::PAD;
+    const uint64_t a1_desc = make_smem_desc(a1_smem, Cfg::A_SLICE, 128) + (uint64_t)Cfg::PAD;
+    const uint64_t w_desc = make_smem_desc(w_smem, Cfg::B_SLICE, 128);
+    const uint32_t leader = elect_one() ? 1u : 0u;
+    uint32_t slot0 = 0, ph0 = 0;  // ring position of tap 0 of the current conv
+    uint32_t a1cnt = 0;           // conv1 accumulator blocks produced so far
+    uint32_t seq = 0;             // (tile, ResBlock) pairs processed so far
+    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+      for (int rb = 0; rb < n_rb; ++rb, ++seq) {
+        for (int m = 0; m < nd; ++m) {
+          const uint32_t par = (seq * (uint32_t)nd + (uint32_t)m) & 1u;
+#pragma unroll 1
+          for (int which = 0; which < 2; ++which) {
+            const FusedConv& cv = which ? p.rb[rb].c2[m] : p.rb[rb].c1[m];
+            const int ntaps = cv.ntaps, dil = cv.dil;
+            const int shift0 = -((ntaps - 1) / 2) * dil;
+            const uint32_t in_ready = which ? a1_ready : a0_ready;
+            const uint64_t in_desc = which ? a1_desc : a0_desc;
+#pragma unroll 1
+            for (int mb = 0; mb < MB; ++mb) {
+              // operand rows of blocks mb-1 .. mb+1 must have been written by the epilogue
+              TWAIT(0, if (mb == 0) mbar_wait(in_ready, par); if (mb + 1 < MB) mbar_wait(in_ready + 8 * (mb + 1), par));
+              uint32_t d_tmem;
+              uint32_t buf = 0;
+              if (!which) {
+                buf = a1cnt & 1u;
+                TWAIT(1, mbar_wait(acc1_empty + 8 * buf, ((a1cnt >> 1) & 1u) ^ 1u));
+                d_tmem = tmem_base + Cfg::ACC1_COL0 + buf * C;
+              } else {
+                d_tmem = tmem_base + mb * C;
+              }
+              // weights of this conv: lane t waits for tap t (one barrier latency for all taps)
+              if (mb == 0) {
+                uint32_t sl = slot0 + (uint32_t)lane, pz = ph0;
+                if (sl >= S) { sl -= S; pz ^= 1u; }
+                const uint32_t my_bar = w_full + 8 * sl;
+                const bool mine = lane < ntaps;
+                const long long t_w = TIMING ? clock64() : 0;
+                for (uint32_t spin = 0;; ++spin) {  // uniform exit (vote), so the warp stays provably converged
+                  const uint32_t ok = mine ? mbar_try(my_bar, pz) : 1u;
+                  if (__all_sync(0xffffffffu, ok)) break;
+                  if (spin > (1u << 24)) { printf("rvcdec mrf_fused: weight barrier timeout (block %d)\n", (int)blockIdx.x); __trap(); }
+                }
+                if (TIMING) tacc[2] += clock64() - t_w;
+              }
+              tc_fence_after();
+              // Warp-uniform tap loop; the MMAs / commits are predicated on the elected lane.
+              // (the shuffles only tell ptxas that these loop inputs are warp-uniform, so that the loop
+              //  below runs on the uniform datapath)
+              const uint64_t a_blk = in_desc + (uint64_t)(int64_t)(mb * 128 + shift0);
+              uint64_t a_tap = ((uint64_t)uni((uint32_t)(a_blk >> 32)) << 32) | (uint64_t)uni((uint32_t)a_blk);
+              uint32_t slot = uni(slot0), ph = ph0;
+              const uint32_t rel = (uni((uint32_t)mb) == MB - 1) ? leader : 0u;  // last block releases the weight slots
+              uint32_t acc = uni(which ? 1u : 0u);
+              d_tmem = uni(d_tmem);
+              const int ntaps_u = (int)uni((uint32_t)ntaps), dil_u = (int)uni((uint32_t)dil);
+#pragma unroll 1
+              for (int tap = 0; tap < ntaps_u; ++tap) {
+                const uint64_t b_tap = w_desc + (uint64_t)(slot * (Cfg::W_SLOT >> 4));
+#pragma unroll
+                for (int ks = 0; ks < C / 16; ++ks)
+                  tc_mma_f16_pred(d_tmem, a_tap + (uint64_t)((2 * ks * Cfg::A_SLICE) >> 4),
+                                  b_tap + (uint64_t)((2 * ks * Cfg::B_SLICE) >> 4), idesc, ks == 0 ? acc : 1u, leader);
+                acc = 1u;
+                tc_commit_pred(w_empty + 8 * slot, rel);
+                a_tap += (uint64_t)(int64_t)dil_u;
+                if (++slot == S) slot = 0;
+              }
+              slot = slot0 + (uint32_t)ntaps;
+              if (slot >= S) { slot -= S; ph ^= 1u; }
+              tc_commit_pred(which ? (x_full + 8 * mb) : (acc1_full + 8 * buf), leader);
+              if (!which) ++a1cnt;
+              if (mb == MB - 1) { slot0 = slot; ph0 = ph; }
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps =====================
+    constexpr int NC = C / 2;        // accumulator columns handled by this warp
+    constexpr int NS8 = NC / 8;      // = 8-channel slices handled by this warp
+    const int q = warp & 3;          // TMEM lane quarter this warp may access
+    const int hh = (warp - 2) >> 2;  // column half
+    const int r_in_blk = q * 32 + lane;
+    const int sl0 = hh * NS8;        // first slice of this warp
+    const uint64_t slope2 = f2_splat(p.slope);
+    const int valid_rows = Cfg::MT - 2 * p.margin;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint32_t a1cnt = 0, seq = 0;
+
+    // make this warp's smem / TMEM writes visible to the MMA (async proxy) and signal `bar`
+    auto publish = [&](uint32_t bar) {
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar);
+    };
+    // 16-bit row of this warp's slices -> operand tile
+    auto store_row = [&](uint32_t a_smem, int r, const uint32_t (&pk)[NC / 2]) {
+#pragma unroll
+      for (int s8 = 0; s8 < NS8; ++s8) {
+        const uint32_t dst = a_smem + (uint32_t)(sl0 + s8) * Cfg::A_SLICE + (uint32_t)(Cfg::PAD + r) * 16;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk[4 * s8]), "r"(pk[4 * s8 + 1]),
+                     "r"(pk[4 * s8 + 2]), "r"(pk[4 * s8 + 3])
+                     : "memory");
+      }
+    };
+    auto load_x = [&](float4 (&dst)[NC / 4], size_t item_base, int t, bool ok) {
+#pragma unroll
+      for (int s8 = 0; s8 < NS8; ++s8) {
+        dst[2 * s8] = make_float4(0.f, 0.f, 0.f, 0.f);
+        dst[2 * s8 + 1] = dst[2 * s8];
+        if (ok) {
+          const float* src = p.x_in + ((item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8;
+          dst[2 * s8] = *reinterpret_cast<const float4*>(src);
+          dst[2 * s8 + 1] = *reinterpret_cast<const float4*>(src + 4);
+        }
+      }
+    };
+
+    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
+      const int b = work / p.tiles_per_item;
+      const int tile = work - b * p.tiles_per_item;
+      const int t0 = tile * valid_rows - p.margin;
+      const size_t item_base = (size_t)b * Cfg::NSL * p.Lp;
+      const bool interior = (t0 >= 0) && (t0 + Cfg::MT <= p.L);  // no row of this tile needs zero padding
+      for (int rb = 0; rb < n_rb; ++rb, ++seq) {
+        const FusedRB& R = p.rb[rb];
+        // ---- stage input: x -> TMEM (fp32 residual stream) and lrelu(x) -> A0; the loads of block
+        //      mb+1 are in flight while block mb is converted ----
+        const long long t_xl = TIMING ? clock64() : 0;
+        {
+          float4 cur[NC / 4], nxt[NC / 4];
+          load_x(cur, item_base, t0 + r_in_blk, interior || (t0 + r_in_blk >= 0 && t0 + r_in_blk < p.L));
+#pragma unroll 1
+          for (int mb = 0; mb < MB; ++mb) {
+            const int r = mb * 128 + r_in_blk;
+            if (mb + 1 < MB) {
+              const int tn = t0 + r + 128;
+              load_x(nxt, item_base, tn, interior || (tn >= 0 && tn < p.L));
+            }
+            uint32_t pk[NC / 2];
+#pragma unroll
+            for (int i = 0; i < NC / 4; ++i) {
+              const uint64_t v0 = f2_pack(cur[i].x, cur[i].y), v1 = f2_pack(cur[i].z, cur[i].w);
+              pk[2 * i] = lrelu_pack<BF16>(v0, slope2);
+              pk[2 * i + 1] = lrelu_pack<BF16>(v1, slope2);
+            }
+#pragma unroll
+            for (int s8 = 0; s8 < NS8; ++s8) {
+              uint32_t r8[8] = {__float_as_uint(cur[2 * s8].x), __float_as_uint(cur[2 * s8].y), __float_as_uint(cur[2 * s8].z),
+                                __float_as_uint(cur[2 * s8].w), __float_as_uint(cur[2 * s8 + 1].x), __float_as_uint(cur[2 * s8 + 1].y),
+                                __float_as_uint(cur[2 * s8 + 1].z), __float_as_uint(cur[2 * s8 + 1].w)};
+              tc_st8(t_lane + mb * C + hh * NC + s8 * 8, r8);
+            }
+            store_row(a0_smem, r, pk);  // rows outside the sequence were loaded as zeros
+            tc_wait_st();
+            publish(a0_ready + 8 * mb);
+#pragma unroll
+            for (int i = 0; i < NC / 4; ++i) cur[i] = nxt[i];
+          }
+        }
+        if (TIMING) tacc[2] += clock64() - t_xl;
+        for (int m = 0; m < nd; ++m) {
+          const uint32_t par = (seq * (uint32_t)nd + (uint32_t)m) & 1u;
+          // biases of this conv pair, as fp32x2 pairs in registers
+          uint64_t b1[NC / 2], b2[NC / 2];
+          {
+            const uint64_t* g1 = reinterpret_cast<const uint64_t*>(R.c1[m].bias + hh * NC);
+            const uint64_t* g2 = reinterpret_cast<const uint64_t*>(R.c2[m].bias + hh * NC);
+#pragma unroll
+            for (int i = 0; i < NC / 2; ++i) { b1[i] = __ldg(g1 + i); b2[i] = __ldg(g2 + i); }
+          }
+          // ---- conv1 epilogue: A1 = lrelu(acc1 + b1) ----
+#pragma unroll 1
+          for (int mb = 0; mb < MB; ++mb) {
+            const int r = mb * 128 + r_in_blk;
+            const uint32_t buf = a1cnt & 1u;
+            TWAIT(0, mbar_wait(acc1_full + 8 * buf, (a1cnt >> 1) & 1u));
+            tc_fence_after();
+            uint32_t rr[NC];
+            TWAIT(3, tmem_load_cols<NC>(t_lane + Cfg::ACC1_COL0 + buf * C + hh * NC, rr));
+            const long long t_c = TIMING ? clock64() : 0;
+            uint32_t pk[NC / 2];
+#pragma unroll
+            for (int i = 0; i < NC / 2; ++i) pk[i] = lrelu_pack<BF16>(f2_add(f2_pack_u(rr[2 * i], rr[2 * i + 1]), b1[i]), slope2);
+            if (!interior) {
+              const int t = t0 + r;
+              if (t < 0 || t >= p.L) {
+#pragma unroll
+                for (int i = 0; i < NC / 2; ++i) pk[i] = 0u;
+              }
+            }
+            store_row(a1_smem, r, pk);
+            if (TIMING) tacc[4] += clock64() - t_c;
+            TWAIT(5, fence_proxy_async(); tc_fence_before(); __syncwarp();
+                  if (lane == 0) { mbar_arrive(a1_ready + 8 * mb); mbar_arrive(acc1_empty + 8 * buf); });
+            ++a1cnt;
+          }
+          // ---- conv2 epilogue: x (TMEM) now holds x + conv2(...) without the biases ----
+          const bool final_m = (m == nd - 1);
+#pragma unroll 1
+          for (int mb = 0; mb < MB; ++mb) {
+            const int r = mb * 128 + r_in_blk;
+            const int t = t0 + r;
+            const bool ok = interior || ((t >= 0) && (t < p.L));
+            const bool store_out = final_m && ok && r >= p.margin && r < Cfg::MT - p.margin;
+            float4 sm[NC / 4];
+            if (store_out && R.sum_in) {  // issue the MRF-sum loads before waiting on the accumulator
+#pragma unroll
+              for (int s8 = 0; s8 < NS8; ++s8) {
+                const float* src = p.sum + ((item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8;
+                sm[2 * s8] = *reinterpret_cast<const float4*>(src);
+                sm[2 * s8 + 1] = *reinterpret_cast<const float4*>(src + 4);
+              }
+            }
+            TWAIT(1, mbar_wait(x_full + 8 * mb, par));
+            tc_fence_after();
+            uint32_t rr[NC];
+            tmem_load_cols<NC>(t_lane + mb * C + hh * NC, rr);
+            if (!final_m) {
+              uint32_t pk[NC / 2];
+#pragma unroll
+              for (int i = 0; i < NC / 2; ++i) pk[i] = lrelu_pack<BF16>(f2_add(f2_pack_u(rr[2 * i], rr[2 * i + 1]), b2[i]), slope2);
+              if (!ok) {
+#pragma unroll
+                for (int i = 0; i < NC / 2; ++i) pk[i] = 0u;
+              }
+              store_row(a0_smem, r, pk);
+              publish(a0_ready + 8 * mb);
+            } else if (store_out) {
+              // ---- ResBlock output -> MRF sum / stage output ----
+#pragma unroll
+              for (int s8 = 0; s8 < NS8; ++s8) {
+                const size_t off = ((item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8;
+                float o[8];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float2 bb = f2_unpack(b2[4 * s8 + i]);
+                  o[2 * i] = (__uint_as_float(rr[8 * s8 + 2 * i]) + bb.x) * p.scale;
+                  o[2 * i + 1] = (__uint_as_float(rr[8 * s8 + 2 * i + 1]) + bb.y) * p.scale;
+                }
+                if (R.sum_in) {
+                  o[0] += sm[2 * s8].x; o[1] += sm[2 * s8].y; o[2] += sm[2 * s8].z; o[3] += sm[2 * s8].w;
+                  o[4] += sm[2 * s8 + 1].x; o[5] += sm[2 * s8 + 1].y; o[6] += sm[2 * s8 + 1].z; o[7] += sm[2 * s8 + 1].w;
+                }
+                if (!R.is_last) {
+                  *reinterpret_cast<float4*>(p.sum + off) = make_float4(o[0], o[1], o[2], o[3]);
+                  *reinterpret_cast<float4*>(p.sum + off + 4) = make_float4(o[4], o[5], o[6], o[7]);
+                } else {
+                  if (p.out_f32) {
+                    *reinterpret_cast<float4*>(p.out_f32 + off) = make_float4(o[0], o[1], o[2], o[3]);
+                    *reinterpret_cast<float4*>(p.out_f32 + off + 4) = make_float4(o[4], o[5], o[6], o[7]);
+                  }
+                  if (p.out_act) {
+                    uint32_t pk[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                      pk[i] = pack2(fmaxf(o[2 * i], o[2 * i] * p.out_slope), fmaxf(o[2 * i + 1], o[2 * i + 1] * p.out_slope), p.out_fmt);
+                    *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out_act) + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                  }
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  if (TIMING && p.timing && (threadIdx.x == 32 || threadIdx.x == 64)) {
+    // [0..3] MMA warp: wait operand rows, wait acc1 drained, wait weights, total; [8..11] epilogue warp 2:
+    // wait acc1_full, wait x_full, stage-input load, total
+    long long* o = p.timing + (size_t)blockIdx.x * 16 + (threadIdx.x == 32 ? 0 : 8);
+    o[0] = tacc[0]; o[1] = tacc[1]; o[2] = tacc[2]; o[3] = clock64() - t_begin;
+    o[4] = tacc[3]; o[5] = tacc[4]; o[6] = tacc[5];
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)Cfg::TMEM_COLS)
+                 : "memory");
+  }
+}
+
+// ------------------------------ host side ----------------------------------
+template <int C, int MB, int S>
+static cudaError_t launch_fused_inst(const FusedParams& p, int num_sms, cudaStream_t s) {
+  using Cfg = FusedCfg<C, MB, S>;
+  auto kern = p.timing ? (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, true, true> : mrf_fused_kernel<C, MB, S, false, true>)
+                       : (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, true, false> : mrf_fused_kernel<C, MB, S, false, false>);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+  if (e != cudaSuccess) return e;
+  FusedParams q = p;
+  const int valid = Cfg::MT - 2 * p.margin;
+  if (valid < 128 || p.nd < 1 || p.nd > FUSED_MAX_D || p.n_rb < 1 || p.n_rb > FUSED_MAX_RB) return cudaErrorInvalidValue;
+  for (int r = 0; r < p.n_rb; ++r)
+    for (int m = 0; m < p.nd; ++m) {
+      const FusedConv* cs[2] = {&p.rb[r].c1[m], &p.rb[r].c2[m]};
+      for (const FusedConv* c : cs)
+        if (c->ntaps < 1 || c->ntaps > S || (c->ntaps - 1) / 2 * c->dil > Cfg::PAD) return cudaErrorInvalidValue;
+    }
+  q.tiles_per_item = (p.L + valid - 1) / valid;
+  const long long total = (long long)q.B * q.tiles_per_item;
+  if (total <= 0 || total > 0x7fffffffLL) return cudaErrorInvalidValue;
+  const int grid = (int)(total < num_sms ? total : num_sms);
+  kern<<<grid, FUSED_THREADS, Cfg::SMEM_BYTES, s>>>(q);
+  return cudaGetLastError();
+}
+
+// (C, MB, S): C = 64 -> 3 x 128-row blocks, 13 tap slots (221 KB smem); C = 32 -> 8 blocks, 24 slots (188 KB)
+bool mrf_fused_supported(int C, int max_taps, int max_halo) {
+  if (max_halo > 32) return false;
+  if (C == 64) return max_taps <= 13;
+  if (C == 32) return max_taps <= 24;
+  return false;
+}
+int mrf_fused_tile_rows(int C) { return C == 64 ? 3 * 128 : C == 32 ? 8 * 128 : 0; }
+
+cudaError_t launch_mrf_fused(const FusedParams& p, int num_sms, cudaStream_t s) {
+  if (p.C == 64) return launch_fused_inst<64, 3, 13>(p, num_sms, s);
+  if (p.C == 32) return launch_fused_inst<32, 8, 24>(p, num_sms, s);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace rvcdec

@@ -51,6 +51,9 @@ struct ConvLayer {
   float* d_wf = nullptr;
   float* d_bias = nullptr;
   uint16_t* d_wp[2] = {nullptr, nullptr};
+  // conv2 of a ResBlock only: b2[0] + .. + b2[m] (the fused kernel keeps x un-biased in TMEM)
+  std::vector<float> cbias;
+  float* d_cbias = nullptr;
 };
 
 struct NoiseLayer {
@@ -88,6 +91,12 @@ struct rvcdec_handle {
   std::vector<void*> dev_allocs;
   int64_t launches = 0;
   int debug_stop = 0;
+  // instrumented fused kernel (tools/fused_timing.py): [launch][sm][16] clock64 spans
+  long long* d_timing = nullptr;
+  int timing_launches = 0;
+  static constexpr int kTimingMaxLaunches = 32;
+  int fused_mrf = 1;  // 0 = one kernel per conv everywhere, 1 = fused ResBlock kernel (one launch per ResBlock) on
+                      // the 64/32-channel stages, 2 = one launch per stage (all ResBlocks, common margin)
   // profiling (bench.py): one event before every launch, groups aggregated on read
   bool prof_on = false;
   struct ProfMark { int group; double flops; double bytes; cudaEvent_t ev; };
@@ -254,6 +263,7 @@ int upload_layer(rvcdec_handle* h, ConvLayer& L) {
   if ((rc = upload(h, L.bias, &L.d_bias))) return rc;
   for (int f = 0; f < 2; ++f)
     if ((rc = upload(h, L.wp[f], &L.d_wp[f]))) return rc;
+  if ((rc = upload(h, L.cbias, &L.d_cbias))) return rc;
   return 0;
 }
 
@@ -355,6 +365,90 @@ int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, 
   return 0;
 }
 
+
+// The fused ResBlock-chain kernel (mrf_fused.cu) serves the stages whose channel count makes the
+// per-conv kernels HBM-bound (C = 64, 32).
+bool use_fused_mrf(const rvcdec_handle* h, int mode, int i) {
+  if (mode == 0 || h->fused_mrf == 0) return false;
+  if (h->nd > FUSED_MAX_D || h->nk > FUSED_MAX_RB) return false;
+  int max_taps = 0, max_halo = 0;
+  for (int j = 0; j < h->nk; ++j)
+    for (int m = 0; m < h->nd; ++m)
+      for (int which = 0; which < 2; ++which) {
+        const ConvLayer& L = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which];
+        max_taps = std::max(max_taps, L.ntaps);
+        max_halo = std::max(max_halo, L.halo);
+        if (L.n_tile != h->ch[i]) return false;  // needs the single-N-tile weight image ([tap][C/8][C][8])
+      }
+  if (!mrf_fused_supported(h->ch[i], max_taps, max_halo)) return false;
+  // the chain's receptive field must leave a useful tile interior
+  int margin = 0;
+  for (int j = 0; j < h->nk; ++j) {
+    int mj = 0;
+    for (int m = 0; m < h->nd; ++m)
+      for (int which = 0; which < 2; ++which) mj += h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which].halo;
+    margin = std::max(margin, mj);
+  }
+  return mrf_fused_tile_rows(h->ch[i]) - 2 * margin >= 128;
+}
+
+int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w, int B, int Lo, int Lpo, int fs,
+                  bool last, cudaStream_t s) {
+  const int C = h->ch[i];
+  auto layer = [&](int j, int m, int which) -> const ConvLayer& {
+    return h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which];
+  };
+  auto fill_rb = [&](FusedRB& R, int j) {
+    int margin = 0;
+    for (int m = 0; m < h->nd; ++m) {
+      const ConvLayer& c1 = layer(j, m, 0);
+      const ConvLayer& c2 = layer(j, m, 1);
+      const int d1 = c1.ntaps > 1 ? c1.shift[1] - c1.shift[0] : 1, d2 = c2.ntaps > 1 ? c2.shift[1] - c2.shift[0] : 1;
+      R.c1[m] = FusedConv{c1.d_wp[fs == ACT_BF16 ? 1 : 0], c1.d_bias, c1.ntaps, d1};
+      R.c2[m] = FusedConv{c2.d_wp[fs == ACT_BF16 ? 1 : 0], c2.d_cbias, c2.ntaps, d2};
+      margin += c1.halo + c2.halo;
+    }
+    R.sum_in = (j > 0);
+    R.is_last = (j == h->nk - 1);
+    return margin;
+  };
+  FusedParams p{};
+  auto next_timing = [&]() -> long long* {
+    if (!h->d_timing || h->timing_launches >= rvcdec_handle::kTimingMaxLaunches) return nullptr;
+    return h->d_timing + (size_t)(h->timing_launches++) * h->num_sms * 16;
+  };
+  p.x_in = w.xs0; p.sum = w.sum;
+  p.out_f32 = last ? w.sum : nullptr;  // the last stage hands its fp32 average to conv_post in `sum`
+  p.out_act = last ? nullptr : w.a0;   // the next stage consumes leaky_relu(x, 0.1) in this stage's format
+  p.fmt = fs; p.out_fmt = fs;
+  p.scale = 1.f / (float)h->nk; p.slope = 0.1f; p.out_slope = 0.1f;
+  p.B = B; p.L = Lo; p.Lp = Lpo; p.C = C; p.nd = h->nd;
+  const double el = (double)B * Lo * C;
+  auto flops_rb = [&](int j) {
+    double f = 0;
+    for (int m = 0; m < h->nd; ++m) f += 2.0 * B * Lo * (layer(j, m, 0).macs_per_row + layer(j, m, 1).macs_per_row);
+    return f;
+  };
+  if (h->fused_mrf == 2) {
+    double fl = 0;
+    p.n_rb = h->nk; p.margin = 0;
+    for (int j = 0; j < h->nk; ++j) { p.margin = std::max(p.margin, fill_rb(p.rb[j], j)); fl += flops_rb(j); }
+    MARK(group, fl, el * (4 + (last ? 4 : act_bytes(fs))));
+    p.timing = next_timing();
+    CK(launch_mrf_fused(p, h->num_sms, s)); ++h->launches;
+  } else {
+    for (int j = 0; j < h->nk; ++j) {
+      p.n_rb = 1;
+      p.margin = fill_rb(p.rb[0], j);
+      const bool fin = (j == h->nk - 1);
+      MARK(group, flops_rb(j), el * (4 + (j > 0 ? 4 : 0) + (fin ? (last ? 4 : act_bytes(fs)) : 4)));
+      p.timing = next_timing();
+      CK(launch_mrf_fused(p, h->num_sms, s)); ++h->launches;
+    }
+  }
+  return 0;
+}
+
 // One pass over B items (B small enough for the workspace).
 int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float* g, const float* noise, uint64_t seed,
                  uint64_t item0, float* out, void* wsbase, int B, int T, int mode, cudaStream_t s) {
@@ -418,6 +512,10 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     }
     if (stop == 10 + i) { MARK(nullptr, 0, 0); return 0; }
     // xs = sum_j resblocks[i*nk + j](x) / nk  (:200-207), ResBlock.forward residuals.py:71-80
+    if (use_fused_mrf(h, mode, i)) {
+      int rc = run_fused_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, s);
+      if (rc) return rc;
+    } else
     for (int j = 0; j < h->nk; ++j) {
       for (int m = 0; m < h->nd; ++m) {
         const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
@@ -511,6 +609,7 @@ void rvcdec_destroy(rvcdec_handle* h) {
   if (cudaGetDeviceCount(&ndev) == cudaSuccess && h->device < ndev) {
     cudaSetDevice(h->device);
     free_device(h);
+    if (h->d_timing) cudaFree(h->d_timing);
     if (h->hbuf) cudaFree(h->hbuf);
     if (h->stream) cudaStreamDestroy(h->stream);
   }
@@ -584,6 +683,15 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
           if ((rc = get_vec(tm, base + ".bias", C, L.bias))) return rc;
         }
   }
+  for (int i = 0; i < h->nups; ++i)
+    for (int j = 0; j < h->nk; ++j) {
+      std::vector<float> run(h->ch[i], 0.f);
+      for (int m = 0; m < h->nd; ++m) {
+        ConvLayer& L2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
+        for (int cc = 0; cc < h->ch[i]; ++cc) run[cc] += L2.bias[cc];
+        L2.cbias = run;
+      }
+    }
   // conv_post (:164): (1, C, 7) no bias -> [j][c]
   const int Cl = h->ch[h->nups - 1];
   if ((rc = get_weight(tm, "conv_post", 1, (int64_t)Cl * 7, W))) return rc;
@@ -752,6 +860,27 @@ int32_t rvcdec_profile_read(rvcdec_handle* h, rvcdec_profile_entry* out, int32_t
   return n;
 }
 
+int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
+  if (!h || !key) return fail(RVCDEC_ERR_ARG, "null argument");
+  const std::string k = key;
+  if (k == "fused_timing") {  // allocate / reset the timing buffer of the instrumented fused kernel
+    if (value && !h->d_timing) {
+      CK(cudaSetDevice(h->device));
+      CK(cudaMalloc(&h->d_timing, sizeof(long long) * rvcdec_handle::kTimingMaxLaunches * h->num_sms * 16));
+    }
+    if (!value && h->d_timing) { cudaFree(h->d_timing); h->d_timing = nullptr; }
+    if (h->d_timing) CK(cudaMemset(h->d_timing, 0, sizeof(long long) * rvcdec_handle::kTimingMaxLaunches * h->num_sms * 16));
+    h->timing_launches = 0;
+    return 0;
+  }
+  if (k == "fused_mrf") {
+    if (value < 0 || value > 2) return fail(RVCDEC_ERR_ARG, "fused_mrf must be 0, 1 or 2");
+    h->fused_mrf = (int)value;
+    return 0;
+  }
+  return fail(RVCDEC_ERR_ARG, "unknown option '%s'", key);
+}
+
 int rvcdec_debug_set_stop(rvcdec_handle* h, int32_t stop_after) {
   if (!h) return fail(RVCDEC_ERR_ARG, "null handle");
   h->debug_stop = stop_after;
@@ -795,6 +924,18 @@ int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_
     }
   }
   return fail(RVCDEC_ERR_ARG, "unknown intermediate '%s'", name);
+}
+
+// Copies the instrumented fused kernel's spans (see "fused_timing") to the host: returns the number of
+// launches recorded; dst gets launches * num_sms * 16 int64 values.
+int64_t rvcdec_debug_fused_timing(rvcdec_handle* h, int64_t* dst, int64_t dst_numel) {
+  if (!h || !dst) return fail(RVCDEC_ERR_ARG, "null argument");
+  if (!h->d_timing) return 0;
+  const int64_t n = (int64_t)h->timing_launches * h->num_sms * 16;
+  if (dst_numel < n) return fail(RVCDEC_ERR_ARG, "destination too small");
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(dst, h->d_timing, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost));
+  return h->timing_launches;
 }
 
 // Host-only packing for CPU tests: runs fold + repack without touching CUDA.

@@ -130,6 +130,9 @@ class HiFiGANNSFGenerator(torch.nn.Module):
                           list(upsample_rates), upsample_initial_channel, list(upsample_kernel_sizes), gin_channels, sr)
         self._gin = gin_channels
         self._cin = initial_channel
+        # fast-mode tuning knob (rvcdec_set_option "fused_mrf"): None = library default
+        self.fused_mrf: Optional[int] = int(os.environ["RVC_B200_FUSED_MRF"]) if "RVC_B200_FUSED_MRF" in os.environ else None
+        self._applied_fused = None
         self._handle: Optional[_lib.Handle] = None
         self._packed_key = None
         self._workspace: Optional[torch.Tensor] = None
@@ -160,6 +163,10 @@ class HiFiGANNSFGenerator(torch.nn.Module):
         if self._handle is None:
             self._handle = _lib.Handle(_lib.make_config(*self._cfg_args), idx)
             self._packed_key = None
+            self._applied_fused = None
+        if self.fused_mrf is not None and self.fused_mrf != self._applied_fused:
+            self._handle.set_option("fused_mrf", self.fused_mrf)
+            self._applied_fused = self.fused_mrf
         key = self._weights_key()
         if key != self._packed_key:
             self._handle.load_weights(self.state_dict())

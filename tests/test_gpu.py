@@ -153,6 +153,34 @@ def test_against_oracle_on_seeded_inputs(dev, cfg_name, B, T, seed, mode):
         assert err <= 2e-2, err
 
 
+@pytest.mark.parametrize("fused", [0, 1, 2])
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 11), ("40k", 1, 97, 12)])
+def test_fused_mrf_variants_agree(dev, fused, cfg_name, B, T, seed):
+    """rvcdec_set_option("fused_mrf"): per-conv kernels (0), fused ResBlock kernel per ResBlock (1) and per
+    stage (2) compute the same decoder; each meets the fast bar and they agree closely with one another
+    (same operand rounding, different accumulation order).  Tile edges: T*upp/4 rows is not a multiple of
+    the fused tile interior, and several tiles per item are exercised."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K}[cfg_name]
+    m = build_module(cfg, 2000 + seed)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        m.fused_mrf = 0
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        m.fused_mrf = fused
+        y = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+    if fused:
+        assert n1 < n0, (n0, n1)
+    corr = O.multires_logmel_corr(y, y_ref, cfg.sr)
+    assert corr["min"] >= FAST_BAR, corr
+    assert float((y - y0).abs().max()) <= 2e-3, float((y - y0).abs().max())
+
+
 def test_readme_shape_both_modes(dev):
     """BASELINE configs[2]: 13.5 s at the README benchmark shape (T=1350), real RMVPE-like contour shape."""
     cfg = O.CONFIG_48K
@@ -241,7 +269,7 @@ def test_reference_noise_order_and_host_entry(dev):
         assert y_host.shape == (2, 1, 30 * cfg.upp) and not y_host.is_cuda
         assert torch.equal(y_ph.cpu(), y_host)
         # Philox draws are standard normal: unvoiced-only input isolates them (har = tanh(w*(0.1/3)z + b))
-        assert m.last_launch_count > 80
+        assert m.last_launch_count > 40
 
 
 def test_long_form_chunked_decode_matches_reference_stitching(dev):
