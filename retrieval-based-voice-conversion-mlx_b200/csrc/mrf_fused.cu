@@ -39,7 +39,7 @@ struct FusedCfg {
   static constexpr int ACC1_COL0 = X_COLS;
   static constexpr int USED_COLS = X_COLS + 2 * C;
   static constexpr int TMEM_COLS = USED_COLS <= 128 ? 128 : USED_COLS <= 256 ? 256 : 512;
-  static constexpr int NUM_BARS = 2 * S + 4 + 3 * MB;
+  static constexpr int NUM_BARS = 2 * S + 4 + 3 * MB + 1;
   static constexpr int SMEM_BYTES = 128 + 2 * A_BUF + S * W_SLOT + NUM_BARS * 8 + 16;
   static_assert(USED_COLS <= 512, "TMEM budget");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
   const uint32_t bars = w_smem + S * Cfg::W_SLOT;
   const uint32_t w_full = bars, w_empty = w_full + 8 * S, acc1_full = w_empty + 8 * S, acc1_empty = acc1_full + 16,
                  x_full = acc1_empty + 16, a0_ready = x_full + 8 * MB, a1_ready = a0_ready + 8 * MB;
-  const uint32_t tmem_slot = a1_ready + 8 * MB;
+  const uint32_t dummy_bar = a1_ready + 8 * MB;  // sink for commits that release nothing
+  const uint32_t tmem_slot = dummy_bar + 8;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);  // provably warp-uniform role index
@@ -138,6 +139,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
       mbar_init(a0_ready + 8 * i, FUSED_EPI_WARPS);
       mbar_init(a1_ready + 8 * i, FUSED_EPI_WARPS);
     }
+    mbar_init(dummy_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   fence_proxy_async();
@@ -203,12 +205,12 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
 #pragma unroll 1
             for (int mb = 0; mb < MB; ++mb) {
               // operand rows of blocks mb-1 .. mb+1 must have been written by the epilogue
-              TWAIT(0, if (mb == 0) mbar_wait(in_ready, par); if (mb + 1 < MB) mbar_wait(in_ready + 8 * (mb + 1), par));
+              TWAIT((which ? 3 : 0) + (mb < 2 ? mb : 2), if (mb == 0) mbar_wait(in_ready, par); if (mb + 1 < MB) mbar_wait(in_ready + 8 * (mb + 1), par));
               uint32_t d_tmem;
               uint32_t buf = 0;
               if (!which) {
                 buf = a1cnt & 1u;
-                TWAIT(1, mbar_wait(acc1_empty + 8 * buf, ((a1cnt >> 1) & 1u) ^ 1u));
+                TWAIT(6, mbar_wait(acc1_empty + 8 * buf, ((a1cnt >> 1) & 1u) ^ 1u));
                 d_tmem = tmem_base + Cfg::ACC1_COL0 + buf * C;
               } else {
                 d_tmem = tmem_base + mb * C;
@@ -225,29 +227,33 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                   if (__all_sync(0xffffffffu, ok)) break;
                   if (spin > (1u << 24)) { printf("rvcdec mrf_fused: weight barrier timeout (block %d)\n", (int)blockIdx.x); __trap(); }
                 }
-                if (TIMING) tacc[2] += clock64() - t_w;
+                if (TIMING) tacc[7] += clock64() - t_w;
               }
               tc_fence_after();
               // Warp-uniform tap loop; the MMAs / commits are predicated on the elected lane.
               // (the shuffles only tell ptxas that these loop inputs are warp-uniform, so that the loop
               //  below runs on the uniform datapath)
-              const uint64_t a_blk = in_desc + (uint64_t)(int64_t)(mb * 128 + shift0);
-              uint64_t a_tap = ((uint64_t)uni((uint32_t)(a_blk >> 32)) << 32) | (uint64_t)uni((uint32_t)a_blk);
+              // 32-bit descriptor arithmetic: only the start-address field (low word) changes
+              uint32_t a_lo = uni((uint32_t)in_desc + (uint32_t)(mb * 128 + shift0));
+              const uint32_t a_hi = (uint32_t)(in_desc >> 32), w_lo = (uint32_t)w_desc, w_hi = (uint32_t)(w_desc >> 32);
               uint32_t slot = uni(slot0), ph = ph0;
-              const uint32_t rel = (uni((uint32_t)mb) == MB - 1) ? leader : 0u;  // last block releases the weight slots
+              // the last block releases each weight slot; the other blocks "release" a dummy barrier so
+              // that the commit stays unconditional (no divergent branch in the loop)
+              const uint32_t rel_base = uni((mb == MB - 1) ? w_empty : dummy_bar);
+              const uint32_t rel_step = uni((mb == MB - 1) ? 8u : 0u);
               uint32_t acc = uni(which ? 1u : 0u);
               d_tmem = uni(d_tmem);
               const int ntaps_u = (int)uni((uint32_t)ntaps), dil_u = (int)uni((uint32_t)dil);
 #pragma unroll 1
               for (int tap = 0; tap < ntaps_u; ++tap) {
-                const uint64_t b_tap = w_desc + (uint64_t)(slot * (Cfg::W_SLOT >> 4));
+                const uint32_t b_lo = w_lo + slot * (uint32_t)(Cfg::W_SLOT >> 4);
 #pragma unroll
                 for (int ks = 0; ks < C / 16; ++ks)
-                  tc_mma_f16_pred(d_tmem, a_tap + (uint64_t)((2 * ks * Cfg::A_SLICE) >> 4),
-                                  b_tap + (uint64_t)((2 * ks * Cfg::B_SLICE) >> 4), idesc, ks == 0 ? acc : 1u, leader);
+                  tc_mma_f16_pred_lh(d_tmem, a_lo + (uint32_t)((2 * ks * Cfg::A_SLICE) >> 4), a_hi,
+                                     b_lo + (uint32_t)((2 * ks * Cfg::B_SLICE) >> 4), w_hi, idesc, ks == 0 ? acc : 1u, leader);
                 acc = 1u;
-                tc_commit_pred(w_empty + 8 * slot, rel);
-                a_tap += (uint64_t)(int64_t)dil_u;
+                tc_commit_pred(rel_base + rel_step * slot, leader);
+                a_lo += (uint32_t)dil_u;
                 if (++slot == S) slot = 0;
               }
               slot = slot0 + (uint32_t)ntaps;
@@ -303,60 +309,74 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
       }
     };
 
-    for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
-      const int b = work / p.tiles_per_item;
-      const int tile = work - b * p.tiles_per_item;
-      const int t0 = tile * valid_rows - p.margin;
-      const size_t item_base = (size_t)b * Cfg::NSL * p.Lp;
-      const bool interior = (t0 >= 0) && (t0 + Cfg::MT <= p.L);  // no row of this tile needs zero padding
-      for (int rb = 0; rb < n_rb; ++rb, ++seq) {
-        const FusedRB& R = p.rb[rb];
-        // ---- stage input: x -> TMEM (fp32 residual stream) and lrelu(x) -> A0; the loads of block
-        //      mb+1 are in flight while block mb is converted ----
-        const long long t_xl = TIMING ? clock64() : 0;
-        {
-          float4 cur[NC / 4], nxt[NC / 4];
-          load_x(cur, item_base, t0 + r_in_blk, interior || (t0 + r_in_blk >= 0 && t0 + r_in_blk < p.L));
+    // A unit = one ResBlock over one tile.  The stage input of unit n+1 is loaded block by block
+    // inside the final epilogue of unit n (as soon as a block's residual has been read out of TMEM its
+    // columns and operand rows are free), so the MMA warp finds the first blocks of the next unit ready
+    // while the last block of this one is still in the tensor pipe.
+    struct Unit { int work, rb, t0; size_t item_base; bool interior, valid; };
+    auto make_unit = [&](int work, int rb) {
+      Unit u;
+      u.work = work; u.rb = rb; u.valid = work < total_work;
+      const int bb = work / p.tiles_per_item;
+      const int tile = work - bb * p.tiles_per_item;
+      u.t0 = tile * valid_rows - p.margin;
+      u.item_base = (size_t)bb * Cfg::NSL * p.Lp;
+      u.interior = (u.t0 >= 0) && (u.t0 + Cfg::MT <= p.L);  // no row of this tile needs zero padding
+      return u;
+    };
+    auto load_unit_x = [&](float4 (&dst)[NC / 4], const Unit& u, int r) {
+      const int t = u.t0 + r;
+      load_x(dst, u.item_base, t, u.interior || (t >= 0 && t < p.L));
+    };
+    // x block (registers) -> TMEM residual + lrelu(x) operand rows, then signal the MMA warp
+    auto store_unit_x = [&](const float4 (&cur)[NC / 4], int mb) {
+      const int r = mb * 128 + r_in_blk;
+      uint32_t pk[NC / 2];
+#pragma unroll
+      for (int i = 0; i < NC / 4; ++i) {
+        pk[2 * i] = lrelu_pack<BF16>(f2_pack(cur[i].x, cur[i].y), slope2);
+        pk[2 * i + 1] = lrelu_pack<BF16>(f2_pack(cur[i].z, cur[i].w), slope2);
+      }
+#pragma unroll
+      for (int s8 = 0; s8 < NS8; ++s8) {
+        uint32_t r8[8] = {__float_as_uint(cur[2 * s8].x), __float_as_uint(cur[2 * s8].y), __float_as_uint(cur[2 * s8].z),
+                          __float_as_uint(cur[2 * s8].w), __float_as_uint(cur[2 * s8 + 1].x), __float_as_uint(cur[2 * s8 + 1].y),
+                          __float_as_uint(cur[2 * s8 + 1].z), __float_as_uint(cur[2 * s8 + 1].w)};
+        tc_st8(t_lane + mb * C + hh * NC + s8 * 8, r8);
+      }
+      store_row(a0_smem, r, pk);  // rows outside the sequence were loaded as zeros
+      tc_wait_st();
+      publish(a0_ready + 8 * mb);
+    };
+
+    Unit u = make_unit(blockIdx.x, 0);
+    if (u.valid) {  // the first unit of this CTA has nothing to hide behind
+      const long long t_xl = TIMING ? clock64() : 0;
+      float4 cur[NC / 4], nxt[NC / 4];
+      load_unit_x(cur, u, r_in_blk);
 #pragma unroll 1
-          for (int mb = 0; mb < MB; ++mb) {
-            const int r = mb * 128 + r_in_blk;
-            if (mb + 1 < MB) {
-              const int tn = t0 + r + 128;
-              load_x(nxt, item_base, tn, interior || (tn >= 0 && tn < p.L));
-            }
-            uint32_t pk[NC / 2];
+      for (int mb = 0; mb < MB; ++mb) {
+        if (mb + 1 < MB) load_unit_x(nxt, u, (mb + 1) * 128 + r_in_blk);
+        store_unit_x(cur, mb);
 #pragma unroll
-            for (int i = 0; i < NC / 4; ++i) {
-              const uint64_t v0 = f2_pack(cur[i].x, cur[i].y), v1 = f2_pack(cur[i].z, cur[i].w);
-              pk[2 * i] = lrelu_pack<BF16>(v0, slope2);
-              pk[2 * i + 1] = lrelu_pack<BF16>(v1, slope2);
-            }
+        for (int i = 0; i < NC / 4; ++i) cur[i] = nxt[i];
+      }
+      if (TIMING) tacc[2] += clock64() - t_xl;
+    }
+    while (u.valid) {
+      Unit nx = (u.rb + 1 < n_rb) ? make_unit(u.work, u.rb + 1) : make_unit(u.work + (int)gridDim.x, 0);
+      const FusedRB& R = p.rb[u.rb];
+      const int t0 = u.t0;
+      const size_t item_base = u.item_base;
+      const bool interior = u.interior;
+      for (int m = 0; m < nd; ++m) {
+        const uint32_t par = (seq * (uint32_t)nd + (uint32_t)m) & 1u;
+        // ---- conv1 epilogue: A1 = lrelu(acc1 + b1) ----
+        {
+          uint64_t b1[NC / 2];  // bias as fp32x2 pairs in registers
+          const uint64_t* g1 = reinterpret_cast<const uint64_t*>(R.c1[m].bias + hh * NC);
 #pragma unroll
-            for (int s8 = 0; s8 < NS8; ++s8) {
-              uint32_t r8[8] = {__float_as_uint(cur[2 * s8].x), __float_as_uint(cur[2 * s8].y), __float_as_uint(cur[2 * s8].z),
-                                __float_as_uint(cur[2 * s8].w), __float_as_uint(cur[2 * s8 + 1].x), __float_as_uint(cur[2 * s8 + 1].y),
-                                __float_as_uint(cur[2 * s8 + 1].z), __float_as_uint(cur[2 * s8 + 1].w)};
-              tc_st8(t_lane + mb * C + hh * NC + s8 * 8, r8);
-            }
-            store_row(a0_smem, r, pk);  // rows outside the sequence were loaded as zeros
-            tc_wait_st();
-            publish(a0_ready + 8 * mb);
-#pragma unroll
-            for (int i = 0; i < NC / 4; ++i) cur[i] = nxt[i];
-          }
-        }
-        if (TIMING) tacc[2] += clock64() - t_xl;
-        for (int m = 0; m < nd; ++m) {
-          const uint32_t par = (seq * (uint32_t)nd + (uint32_t)m) & 1u;
-          // biases of this conv pair, as fp32x2 pairs in registers
-          uint64_t b1[NC / 2], b2[NC / 2];
-          {
-            const uint64_t* g1 = reinterpret_cast<const uint64_t*>(R.c1[m].bias + hh * NC);
-            const uint64_t* g2 = reinterpret_cast<const uint64_t*>(R.c2[m].bias + hh * NC);
-#pragma unroll
-            for (int i = 0; i < NC / 2; ++i) { b1[i] = __ldg(g1 + i); b2[i] = __ldg(g2 + i); }
-          }
-          // ---- conv1 epilogue: A1 = lrelu(acc1 + b1) ----
+          for (int i = 0; i < NC / 2; ++i) b1[i] = __ldg(g1 + i);
 #pragma unroll 1
           for (int mb = 0; mb < MB; ++mb) {
             const int r = mb * 128 + r_in_blk;
@@ -382,39 +402,48 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                   if (lane == 0) { mbar_arrive(a1_ready + 8 * mb); mbar_arrive(acc1_empty + 8 * buf); });
             ++a1cnt;
           }
-          // ---- conv2 epilogue: x (TMEM) now holds x + conv2(...) without the biases ----
-          const bool final_m = (m == nd - 1);
+        }
+        // ---- conv2 epilogue: x (TMEM) now holds x + conv2(...) without the biases ----
+        uint64_t b2[NC / 2];
+        {
+          const uint64_t* g2 = reinterpret_cast<const uint64_t*>(R.c2[m].bias + hh * NC);
+#pragma unroll
+          for (int i = 0; i < NC / 2; ++i) b2[i] = __ldg(g2 + i);
+        }
+        if (m < nd - 1) {
+#pragma unroll 1
+          for (int mb = 0; mb < MB; ++mb) {
+            const int r = mb * 128 + r_in_blk;
+            const int t = t0 + r;
+            TWAIT(1, mbar_wait(x_full + 8 * mb, par));
+            tc_fence_after();
+            uint32_t rr[NC];
+            tmem_load_cols<NC>(t_lane + mb * C + hh * NC, rr);
+            uint32_t pk[NC / 2];
+#pragma unroll
+            for (int i = 0; i < NC / 2; ++i) pk[i] = lrelu_pack<BF16>(f2_add(f2_pack_u(rr[2 * i], rr[2 * i + 1]), b2[i]), slope2);
+            if (!interior && (t < 0 || t >= p.L)) {
+#pragma unroll
+              for (int i = 0; i < NC / 2; ++i) pk[i] = 0u;
+            }
+            store_row(a0_smem, r, pk);
+            publish(a0_ready + 8 * mb);
+          }
+        } else {
+          // ---- ResBlock output -> MRF sum / stage output, interleaved with the next unit's input ----
 #pragma unroll 1
           for (int mb = 0; mb < MB; ++mb) {
             const int r = mb * 128 + r_in_blk;
             const int t = t0 + r;
             const bool ok = interior || ((t >= 0) && (t < p.L));
-            const bool store_out = final_m && ok && r >= p.margin && r < Cfg::MT - p.margin;
-            float4 sm[NC / 4];
-            if (store_out && R.sum_in) {  // issue the MRF-sum loads before waiting on the accumulator
-#pragma unroll
-              for (int s8 = 0; s8 < NS8; ++s8) {
-                const float* src = p.sum + ((item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8;
-                sm[2 * s8] = *reinterpret_cast<const float4*>(src);
-                sm[2 * s8 + 1] = *reinterpret_cast<const float4*>(src + 4);
-              }
-            }
+            const bool store_out = ok && r >= p.margin && r < Cfg::MT - p.margin;
+            float4 xn[NC / 4];
+            if (nx.valid) load_unit_x(xn, nx, r);  // in flight while we wait for the accumulator
             TWAIT(1, mbar_wait(x_full + 8 * mb, par));
             tc_fence_after();
             uint32_t rr[NC];
             tmem_load_cols<NC>(t_lane + mb * C + hh * NC, rr);
-            if (!final_m) {
-              uint32_t pk[NC / 2];
-#pragma unroll
-              for (int i = 0; i < NC / 2; ++i) pk[i] = lrelu_pack<BF16>(f2_add(f2_pack_u(rr[2 * i], rr[2 * i + 1]), b2[i]), slope2);
-              if (!ok) {
-#pragma unroll
-                for (int i = 0; i < NC / 2; ++i) pk[i] = 0u;
-              }
-              store_row(a0_smem, r, pk);
-              publish(a0_ready + 8 * mb);
-            } else if (store_out) {
-              // ---- ResBlock output -> MRF sum / stage output ----
+            if (store_out) {
 #pragma unroll
               for (int s8 = 0; s8 < NS8; ++s8) {
                 const size_t off = ((item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8;
@@ -426,8 +455,10 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                   o[2 * i + 1] = (__uint_as_float(rr[8 * s8 + 2 * i + 1]) + bb.y) * p.scale;
                 }
                 if (R.sum_in) {
-                  o[0] += sm[2 * s8].x; o[1] += sm[2 * s8].y; o[2] += sm[2 * s8].z; o[3] += sm[2 * s8].w;
-                  o[4] += sm[2 * s8 + 1].x; o[5] += sm[2 * s8 + 1].y; o[6] += sm[2 * s8 + 1].z; o[7] += sm[2 * s8 + 1].w;
+                  const float4 s0 = *reinterpret_cast<const float4*>(p.sum + off);
+                  const float4 s1 = *reinterpret_cast<const float4*>(p.sum + off + 4);
+                  o[0] += s0.x; o[1] += s0.y; o[2] += s0.z; o[3] += s0.w;
+                  o[4] += s1.x; o[5] += s1.y; o[6] += s1.z; o[7] += s1.w;
                 }
                 if (!R.is_last) {
                   *reinterpret_cast<float4*>(p.sum + off) = make_float4(o[0], o[1], o[2], o[3]);
@@ -447,9 +478,12 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                 }
               }
             }
+            if (nx.valid) store_unit_x(xn, mb);
           }
         }
       }
+      u = nx;
+      ++seq;
     }
   }
 
@@ -457,8 +491,15 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
     // [0..3] MMA warp: wait operand rows, wait acc1 drained, wait weights, total; [8..11] epilogue warp 2:
     // wait acc1_full, wait x_full, stage-input load, total
     long long* o = p.timing + (size_t)blockIdx.x * 16 + (threadIdx.x == 32 ? 0 : 8);
-    o[0] = tacc[0]; o[1] = tacc[1]; o[2] = tacc[2]; o[3] = clock64() - t_begin;
-    o[4] = tacc[3]; o[5] = tacc[4]; o[6] = tacc[5];
+    if (threadIdx.x == 32) {
+      o[0] = tacc[0] + tacc[1] + tacc[2] + tacc[3] + tacc[4] + tacc[5]; o[1] = tacc[6]; o[2] = tacc[7];
+      o[3] = clock64() - t_begin;
+      // operand-row waits by position: conv1 block 0, conv1 blocks >= 1, conv2 block 0, conv2 blocks >= 1
+      o[4] = tacc[0]; o[5] = tacc[1] + tacc[2]; o[6] = tacc[3]; o[7] = tacc[4] + tacc[5];
+    } else {
+      o[0] = tacc[0]; o[1] = tacc[1]; o[2] = tacc[2]; o[3] = clock64() - t_begin;
+      o[4] = tacc[3]; o[5] = tacc[4]; o[6] = tacc[5];
+    }
   }
   tc_fence_before();
   __syncthreads();

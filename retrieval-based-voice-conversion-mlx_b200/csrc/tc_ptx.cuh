@@ -96,6 +96,20 @@ __device__ __forceinline__ void tc_mma_f16_pred(uint32_t d_tmem, uint64_t adesc,
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader)
       : "memory");
 }
+// Same, with the descriptors given as (low, high) words: only the low word (start address field) moves
+// between MMAs, so the issue loop needs 32-bit adds only (no carry chains on the uniform datapath).
+__device__ __forceinline__ void tc_mma_f16_pred_lh(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                   uint32_t b_hi, uint32_t idesc, uint32_t accumulate, uint32_t leader) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "setp.ne.b32 q, %7, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(leader)
+      : "memory");
+}
 __device__ __forceinline__ void tc_commit_pred(uint32_t bar, uint32_t leader) {
   asm volatile(
       "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t"
