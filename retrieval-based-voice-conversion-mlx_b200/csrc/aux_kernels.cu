@@ -247,7 +247,106 @@ __global__ void __launch_bounds__(256) noise_add_kernel(NoiseAddParams p) {
   }
 }
 
+// Long noise convs (stage 0: 80 taps, stride 40, 256 channels): weights and the har span of a row tile
+// are staged in shared memory and every thread keeps 8 rows x 8 channels in registers, so one weight
+// fetch feeds 8 rows (the generic kernel above re-read the weights from L1 for every row: 30 ms at the
+// bench shape; this one is FMA-bound at ~3 ms).
+constexpr int NZB_ROWS_PER_THREAD = 8;
+template <typename T>
+__global__ void __launch_bounds__(256) noise_add_big_kernel(NoiseAddParams p, int tiles_per_item, int rows_per_tile) {
+  extern __shared__ float nz_smem[];
+  float* sw = nz_smem;                 // [k][C]
+  float* sh = nz_smem + p.k * p.C;     // har span of the tile
+  const int nsl = p.C / 8;
+  const int rgroups = 256 / nsl;       // row groups per block
+  const int sl = threadIdx.x % nsl;
+  const int rg = threadIdx.x / nsl;
+  for (int i = threadIdx.x; i < p.k * p.C; i += 256) sw[i] = p.w[i];
+  const int span = (rows_per_tile - 1) * p.stride + p.k;
+  const int total = p.B * tiles_per_item;
+  for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    const int b = tile / tiles_per_item;
+    const int row0 = (tile - b * tiles_per_item) * rows_per_tile;
+    const float* hb = p.har + (size_t)b * p.n_src;
+    const int s_base = row0 * p.stride - p.pad;
+    __syncthreads();  // previous tile's readers done (also covers the weight staging on the first pass)
+    for (int i = threadIdx.x; i < span; i += 256) {
+      const int sidx = s_base + i;
+      sh[i] = (sidx >= 0 && sidx < p.n_src) ? __ldg(hb + sidx) : 0.f;
+    }
+    __syncthreads();
+    if (rg < rgroups) {
+      float acc[NZB_ROWS_PER_THREAD][8];
+#pragma unroll
+      for (int r = 0; r < NZB_ROWS_PER_THREAD; ++r)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[r][c] = 0.f;
+      const float* hrow = sh + rg * NZB_ROWS_PER_THREAD * p.stride;
+      for (int j = 0; j < p.k; ++j) {
+        const float4 w0 = *reinterpret_cast<const float4*>(sw + j * p.C + sl * 8);
+        const float4 w1 = *reinterpret_cast<const float4*>(sw + j * p.C + sl * 8 + 4);
+#pragma unroll
+        for (int r = 0; r < NZB_ROWS_PER_THREAD; ++r) {
+          const float hv = hrow[r * p.stride + j];
+          acc[r][0] = fmaf(hv, w0.x, acc[r][0]); acc[r][1] = fmaf(hv, w0.y, acc[r][1]);
+          acc[r][2] = fmaf(hv, w0.z, acc[r][2]); acc[r][3] = fmaf(hv, w0.w, acc[r][3]);
+          acc[r][4] = fmaf(hv, w1.x, acc[r][4]); acc[r][5] = fmaf(hv, w1.y, acc[r][5]);
+          acc[r][6] = fmaf(hv, w1.z, acc[r][6]); acc[r][7] = fmaf(hv, w1.w, acc[r][7]);
+        }
+      }
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + sl * 8));
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + sl * 8 + 4));
+#pragma unroll
+      for (int r = 0; r < NZB_ROWS_PER_THREAD; ++r) {
+        const int row = row0 + rg * NZB_ROWS_PER_THREAD + r;
+        if (row >= p.L) break;
+        const size_t off = (((size_t)b * nsl + sl) * p.Lp + PADL + row) * 8;
+        const float4 q0 = *reinterpret_cast<const float4*>(p.x + off);
+        const float4 q1 = *reinterpret_cast<const float4*>(p.x + off + 4);
+        float v[8] = {q0.x + b0.x + acc[r][0], q0.y + b0.y + acc[r][1], q0.z + b0.z + acc[r][2], q0.w + b0.w + acc[r][3],
+                      q1.x + b1.x + acc[r][4], q1.y + b1.y + acc[r][5], q1.z + b1.z + acc[r][6], q1.w + b1.w + acc[r][7]};
+        *reinterpret_cast<float4*>(p.x + off) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(p.x + off + 4) = make_float4(v[4], v[5], v[6], v[7]);
+        T* a = reinterpret_cast<T*>(p.act) + off;
+        if (sizeof(T) == 4) {
+          *reinterpret_cast<float4*>(a) = make_float4(lrelu(v[0], p.slope), lrelu(v[1], p.slope), lrelu(v[2], p.slope), lrelu(v[3], p.slope));
+          *reinterpret_cast<float4*>(a + 4) = make_float4(lrelu(v[4], p.slope), lrelu(v[5], p.slope), lrelu(v[6], p.slope), lrelu(v[7], p.slope));
+        } else {
+          T tmp[8];
+#pragma unroll
+          for (int c = 0; c < 8; ++c) tmp[c] = cvt_act<T>(lrelu(v[c], p.slope));
+          *reinterpret_cast<uint4*>(a) = *reinterpret_cast<uint4*>(tmp);
+        }
+      }
+    }
+  }
+}
+
+template <typename T>
+static cudaError_t launch_noise_add_big(const NoiseAddParams& p, cudaStream_t s) {
+  const int nsl = p.C / 8;
+  const int rows_per_tile = (256 / nsl) * NZB_ROWS_PER_THREAD;
+  const int span = (rows_per_tile - 1) * p.stride + p.k;
+  const size_t smem = ((size_t)p.k * p.C + span) * sizeof(float);
+  auto kern = noise_add_big_kernel<T>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const int tiles_per_item = (p.L + rows_per_tile - 1) / rows_per_tile;
+  const long long total = (long long)p.B * tiles_per_item;
+  const int blocks = (int)std::min<long long>(total, 148 * 2);
+  kern<<<blocks, 256, smem, s>>>(p, tiles_per_item, rows_per_tile);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_noise_add(const NoiseAddParams& p, cudaStream_t s) {
+  // long kernels: smem-staged register-tiled variant (needs C/8 to divide 256 and the image to fit)
+  const int nsl = p.C / 8;
+  if (p.k >= 16 && nsl <= 256 && 256 % nsl == 0 &&
+      ((size_t)p.k * p.C + (size_t)((256 / nsl) * NZB_ROWS_PER_THREAD - 1) * p.stride + p.k) * 4 <= 200 * 1024) {
+    if (p.act_fmt == ACT_F32) return launch_noise_add_big<float>(p, s);
+    if (p.act_fmt == ACT_F16) return launch_noise_add_big<__half>(p, s);
+    return launch_noise_add_big<__nv_bfloat16>(p, s);
+  }
   const size_t total = (size_t)p.B * (p.C / 8) * p.L;
   const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
   if (p.act_fmt == ACT_F32) noise_add_kernel<float><<<blocks, 256, 0, s>>>(p);
@@ -291,8 +390,63 @@ __global__ void __launch_bounds__(256) post_kernel(const float* __restrict__ x, 
   }
 }
 
+// k = 7 specialisation: every thread produces 4 consecutive samples from a 10-row window, so each
+// input row is fetched 2.5x instead of 7x per output (the generic kernel above is L1-bandwidth bound).
+__global__ void __launch_bounds__(256) post7_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                    float* __restrict__ out, int B, int C, int L, int Lp, float slope) {
+  extern __shared__ float sw[];  // [7][C]
+  for (int i = threadIdx.x; i < 7 * C; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
+  const int nsl = C / 8;
+  const int groups_per_item = (L + 3) / 4;
+  const size_t total = (size_t)B * groups_per_item;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int gq = (int)(i % groups_per_item);
+    const int b = (int)(i / groups_per_item);
+    const int t0 = gq * 4;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int sl = 0; sl < nsl; ++sl) {
+      const float* xs = x + (((size_t)b * nsl + sl) * Lp + PADL) * 8;
+      const float* ws = sw + sl * 8;
+#pragma unroll
+      for (int r = 0; r < 10; ++r) {
+        const int tt = t0 + r - 3;
+        if (tt < 0 || tt >= L) continue;  // zero padding of conv_post
+        const float4 q0 = *reinterpret_cast<const float4*>(xs + (size_t)tt * 8);
+        const float4 q1 = *reinterpret_cast<const float4*>(xs + (size_t)tt * 8 + 4);
+        const float v[8] = {lrelu(q0.x, slope), lrelu(q0.y, slope), lrelu(q0.z, slope), lrelu(q0.w, slope),
+                            lrelu(q1.x, slope), lrelu(q1.y, slope), lrelu(q1.z, slope), lrelu(q1.w, slope)};
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+          const int j = r - o;  // tap index of row r for output t0 + o
+          if (j < 0 || j >= 7) continue;
+          const float4 w0 = *reinterpret_cast<const float4*>(ws + j * C);
+          const float4 w1 = *reinterpret_cast<const float4*>(ws + j * C + 4);
+          acc[o] = fmaf(v[0], w0.x, acc[o]); acc[o] = fmaf(v[1], w0.y, acc[o]); acc[o] = fmaf(v[2], w0.z, acc[o]);
+          acc[o] = fmaf(v[3], w0.w, acc[o]); acc[o] = fmaf(v[4], w1.x, acc[o]); acc[o] = fmaf(v[5], w1.y, acc[o]);
+          acc[o] = fmaf(v[6], w1.z, acc[o]); acc[o] = fmaf(v[7], w1.w, acc[o]);
+        }
+      }
+    }
+    float* o = out + (size_t)b * L + t0;
+    if (t0 + 3 < L && ((((size_t)b * L + t0) & 3) == 0)) {
+      *reinterpret_cast<float4*>(o) = make_float4(tanhf(acc[0]), tanhf(acc[1]), tanhf(acc[2]), tanhf(acc[3]));
+    } else {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (t0 + q < L) o[q] = tanhf(acc[q]);
+    }
+  }
+}
+
 cudaError_t launch_post(const float* x, const float* w, float* out, int B, int C, int L, int Lp, int k, float slope,
                         cudaStream_t s) {
+  if (k == 7) {
+    const size_t total = (size_t)B * ((L + 3) / 4);
+    const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
+    post7_kernel<<<blocks, 256, (size_t)7 * C * sizeof(float), s>>>(x, w, out, B, C, L, Lp, slope);
+    return cudaGetLastError();
+  }
   const size_t total = (size_t)B * L;
   const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
   post_kernel<<<blocks, 256, (size_t)k * C * sizeof(float), s>>>(x, w, out, B, C, L, Lp, k, slope);

@@ -57,6 +57,12 @@ struct Epilogue {
   int cout;      // physical channels of the output tensors
   int L_out;     // valid rows of the output tensors
   int Lp_out;    // padded rows of the output tensors
+  // optional fused noise_convs[i] (hifigan_nsf.py:199): v += nz_bias[co] + sum_j har[b][row*stride - pad + j] * nz_w[j][co]
+  // (applied before res / scale; used by the upsample layers whose noise conv has <= 8 taps)
+  const float* nz_har;   // (B, nz_src) or null
+  const float* nz_w;     // [k][cout]
+  const float* nz_bias;  // [cout]
+  int nz_k, nz_stride, nz_pad, nz_src;
 };
 
 // One convolution as an implicit GEMM:  D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]
@@ -85,7 +91,29 @@ __device__ __forceinline__ void epilogue_store(const Epilogue& e, int b, int t_i
   if (row >= e.L_out) return;
   const float* bp = e.bias + (size_t)b * e.bias_bstride + n0;
 #pragma unroll
-  for (int i = 0; i < NV; ++i) v[i] += __ldg(bp + i);
+  for (int i = 0; i < NV; i += 4) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(bp + i));
+    v[i] += q.x; v[i + 1] += q.y; v[i + 2] += q.z; v[i + 3] += q.w;
+  }
+  if (e.nz_har) {
+#pragma unroll
+    for (int i = 0; i < NV; i += 4) {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(e.nz_bias + co + i));
+      v[i] += q.x; v[i + 1] += q.y; v[i + 2] += q.z; v[i + 3] += q.w;
+    }
+    const float* hb = e.nz_har + (size_t)b * e.nz_src;
+    const int s0 = row * e.nz_stride - e.nz_pad;
+    for (int j = 0; j < e.nz_k; ++j) {
+      const int sidx = s0 + j;
+      if (sidx < 0 || sidx >= e.nz_src) continue;
+      const float h = __ldg(hb + sidx);
+#pragma unroll
+      for (int i = 0; i < NV; i += 4) {
+        const float4 q = __ldg(reinterpret_cast<const float4*>(e.nz_w + (size_t)j * e.cout + co + i));
+        v[i] = fmaf(h, q.x, v[i]); v[i + 1] = fmaf(h, q.y, v[i + 1]); v[i + 2] = fmaf(h, q.z, v[i + 2]); v[i + 3] = fmaf(h, q.w, v[i + 3]);
+      }
+    }
+  }
   const size_t off = (((size_t)b * (e.cout >> 3) + (co >> 3)) * e.Lp_out + PADL + row) * 8 + (co & 7);
   if (e.res) {
 #pragma unroll

@@ -493,17 +493,27 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     const int Lpo = padded_rows(Lo);
     const int fs = fmt_stage(mode, i);
     const bool last = (i == h->nups - 1);
+    const NoiseLayer& nl = h->noise[i];
+    // Short noise convs ride in the upsample epilogue when the stage runs the fused MRF kernel (which
+    // reads the fp32 stage input only, so no activated 16-bit copy is needed).
+    const bool fuse_noise = nl.k <= 8 && use_fused_mrf(h, mode, i);
     {  // x = ups[i](leaky_relu(x, 0.1))  (hifigan_nsf.py:185,198); the activation was applied by the producer
       Epilogue e{};
       e.bias = h->ups[i].d_bias; e.scale = 1.f; e.slope = 0.1f;
       e.out_f32 = w.xs0; e.up = u; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
+      if (fuse_noise) {  // ... + noise_convs[i](har_source)  (:199)
+        e.nz_har = w.har; e.nz_w = nl.d_w; e.nz_bias = nl.d_bias;
+        e.nz_k = nl.k; e.nz_stride = nl.stride; e.nz_pad = nl.pad; e.nz_src = T * h->upp;
+      }
       int rc = run_conv(h, g_ups.c_str(), h->ups[i], mode, fmt_in, stage_in, B, L, e, s);
       if (rc) return rc;
     }
-    MARK(g_noise.c_str(), 2.0 * B * Lo * C * h->noise[i].k, (double)B * Lo * C * (8 + act_bytes(fs)));
-    CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches;
-    {  // x = x + noise_convs[i](har_source)  (:199)
-      const NoiseLayer& nl = h->noise[i];
+    // (after the upsample has read the previous stage's tensor out of a0: new geometry, new pad rows)
+    if (fuse_noise) { CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
+    if (!fuse_noise) {
+      MARK(g_noise.c_str(), 2.0 * B * Lo * C * nl.k, (double)B * Lo * C * (8 + act_bytes(fs)));
+      CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches;
+      // x = x + noise_convs[i](har_source)  (:199)
       NoiseAddParams np{};
       np.har = w.har; np.w = nl.d_w; np.bias = nl.d_bias; np.x = w.xs0; np.act = w.a0; np.act_fmt = fs;
       np.B = B; np.C = C; np.L = Lo; np.Lp = Lpo; np.n_src = T * h->upp; np.k = nl.k; np.stride = nl.stride;
