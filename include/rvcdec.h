@@ -117,7 +117,10 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *   "fused_mrf"  0 = every ResBlock convolution is its own kernel on every stage;
  *                1 = (default) the 64/32-channel stages run the fused ResBlock-chain kernel, one launch
  *                    per ResBlock (residuals.py:71-80 kept on chip: residual in TMEM, operands in smem);
- *                2 = same kernel, one launch per stage (all ResBlocks of the MRF over one tile). */
+ *                2 = same kernel, one launch per stage (all ResBlocks of the MRF over one tile).
+ *   "zero_stuff" 1 = (default) a stride-2 upsample that feeds a fused-MRF stage runs as an ordinary convolution
+ *                    over a zero-stuffed copy of its input (written by the previous stage's last kernel);
+ *                0 = polyphase form everywhere. */
 int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value);
 
 /* Number of kernels launched by the last forward on this handle. */

@@ -455,23 +455,23 @@ cudaError_t launch_post(const float* x, const float* w, float* out, int B, int C
 
 // ---------------------------------------------------------------------------
 template <typename T>
-__global__ void unpack_kernel(const T* __restrict__ src, float* __restrict__ dst, int B, int C, int L, int Lp) {
+__global__ void unpack_kernel(const T* __restrict__ src, float* __restrict__ dst, int B, int C, int L, int Lp, int rs) {
   const size_t total = (size_t)B * C * L;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int t = (int)(i % L);
     const size_t bc = i / L;
     const int c = (int)(bc % C);
     const int b = (int)(bc / C);
-    dst[i] = (float)src[(((size_t)b * (C / 8) + (c >> 3)) * Lp + PADL + t) * 8 + (c & 7)];
+    dst[i] = (float)src[(((size_t)b * (C / 8) + (c >> 3)) * Lp + PADL + (size_t)t * rs) * 8 + (c & 7)];
   }
 }
 
-cudaError_t launch_unpack(const void* src, int fmt, float* dst, int B, int C, int L, int Lp, cudaStream_t s) {
+cudaError_t launch_unpack(const void* src, int fmt, float* dst, int B, int C, int L, int Lp, cudaStream_t s, int rs) {
   const size_t total = (size_t)B * C * L;
   const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
-  if (fmt == ACT_F32) unpack_kernel<float><<<blocks, 256, 0, s>>>((const float*)src, dst, B, C, L, Lp);
-  else if (fmt == ACT_F16) unpack_kernel<__half><<<blocks, 256, 0, s>>>((const __half*)src, dst, B, C, L, Lp);
-  else unpack_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>((const __nv_bfloat16*)src, dst, B, C, L, Lp);
+  if (fmt == ACT_F32) unpack_kernel<float><<<blocks, 256, 0, s>>>((const float*)src, dst, B, C, L, Lp, rs);
+  else if (fmt == ACT_F16) unpack_kernel<__half><<<blocks, 256, 0, s>>>((const __half*)src, dst, B, C, L, Lp, rs);
+  else unpack_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>((const __nv_bfloat16*)src, dst, B, C, L, Lp, rs);
   return cudaGetLastError();
 }
 

@@ -63,6 +63,12 @@ struct Epilogue {
   const float* nz_w;     // [k][cout]
   const float* nz_bias;  // [cout]
   int nz_k, nz_stride, nz_pad, nz_src;
+  // optional zero-stuffed 16-bit output: out_act row t goes to row t*act_zs of a tensor with Lp_act padded
+  // rows, rows t*act_zs+1 .. are written as zeros.  A following stride-2 transposed convolution then is an
+  // ordinary convolution over that tensor (ConvTranspose1d == conv over the zero-stuffed input with the
+  // flipped kernel), which gives it the coalesced "output row == accumulator row" epilogue.
+  int act_zs;   // 0 / 1 = dense
+  int Lp_act;   // padded rows of out_act when act_zs > 1
 };
 
 // One convolution as an implicit GEMM:  D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]
@@ -194,6 +200,8 @@ struct FusedParams {
   void* out_act;      // leaky_relu(stage output, out_slope) in out_fmt, blocked-8, or null
   int fmt;            // operand format of this stage (ACT_F16 / ACT_BF16)
   int out_fmt;
+  int out_zs;         // > 1: out_act is zero-stuffed (row t -> t*out_zs, see Epilogue::act_zs), Lp_out_act padded rows
+  int Lp_out_act;
   float scale;        // 1 / num_kernels
   float slope;        // 0.1 inside the ResBlocks
   float out_slope;
@@ -241,6 +249,6 @@ cudaError_t launch_noise_add(const NoiseAddParams& p, cudaStream_t s);
 cudaError_t launch_post(const float* x, const float* w, float* out, int B, int C, int L, int Lp, int k, float slope,
                         cudaStream_t s);
 // blocked-8 (fp32 or 16-bit) -> plain (B, C, L) fp32, for tests
-cudaError_t launch_unpack(const void* src, int fmt, float* dst, int B, int C, int L, int Lp, cudaStream_t s);
+cudaError_t launch_unpack(const void* src, int fmt, float* dst, int B, int C, int L, int Lp, cudaStream_t s, int row_stride = 1);
 
 }  // namespace rvcdec

@@ -227,6 +227,16 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
               sm[2 * s8 + 1] = *reinterpret_cast<const float4*>(e.sum_in + off + s8 * slice_stride + 4);
             }
           }
+          float hv[8];  // har samples under this row's (<= 8-tap) noise conv, loaded before the TMEM wait
+          if (e.nz_har) {
+            const float* hb = e.nz_har + (size_t)b * e.nz_src;
+            const int s0 = t_in * e.nz_stride - e.nz_pad;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int sidx = s0 + j;
+              hv[j] = (valid && j < e.nz_k && sidx >= 0 && sidx < e.nz_src) ? __ldg(hb + sidx) : 0.f;
+            }
+          }
           tc_ld32(t_acc + mb * N_TILE + c0, r);
           if (valid) {
             const float4* bp = reinterpret_cast<const float4*>(e.bias + (size_t)b * e.bias_bstride + n0);
@@ -241,6 +251,22 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
               if (e.res) {
                 v[0] += rr[2 * s8].x; v[1] += rr[2 * s8].y; v[2] += rr[2 * s8].z; v[3] += rr[2 * s8].w;
                 v[4] += rr[2 * s8 + 1].x; v[5] += rr[2 * s8 + 1].y; v[6] += rr[2 * s8 + 1].z; v[7] += rr[2 * s8 + 1].w;
+              }
+              if (e.nz_har) {  // fused noise_convs[i](har_source), hifigan_nsf.py:199 (har values hoisted above)
+                const int co = n0 + s8 * 8;
+                const float4 nb0 = __ldg(reinterpret_cast<const float4*>(e.nz_bias + co));
+                const float4 nb1 = __ldg(reinterpret_cast<const float4*>(e.nz_bias + co + 4));
+                v[0] += nb0.x; v[1] += nb0.y; v[2] += nb0.z; v[3] += nb0.w;
+                v[4] += nb1.x; v[5] += nb1.y; v[6] += nb1.z; v[7] += nb1.w;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  if (j < e.nz_k) {
+                    const float4 w0 = __ldg(reinterpret_cast<const float4*>(e.nz_w + (size_t)j * e.cout + co));
+                    const float4 w1 = __ldg(reinterpret_cast<const float4*>(e.nz_w + (size_t)j * e.cout + co + 4));
+                    v[0] = fmaf(hv[j], w0.x, v[0]); v[1] = fmaf(hv[j], w0.y, v[1]); v[2] = fmaf(hv[j], w0.z, v[2]); v[3] = fmaf(hv[j], w0.w, v[3]);
+                    v[4] = fmaf(hv[j], w1.x, v[4]); v[5] = fmaf(hv[j], w1.y, v[5]); v[6] = fmaf(hv[j], w1.z, v[6]); v[7] = fmaf(hv[j], w1.w, v[7]);
+                  }
+                }
               }
               if (e.scale != 1.f) {
 #pragma unroll
@@ -271,7 +297,14 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
                     pk[i] = *reinterpret_cast<uint32_t*>(&hh);
                   }
                 }
-                *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(e.out_act) + o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                if (e.act_zs > 1) {  // zero-stuffed rows for the next stage's stride-act_zs transposed conv
+                  uint16_t* oa = reinterpret_cast<uint16_t*>(e.out_act) +
+                                 ((((size_t)b * (e.cout >> 3) + (n0 >> 3) + s8) * e.Lp_act + PADL) + (size_t)t_in * e.act_zs) * 8;
+                  *reinterpret_cast<uint4*>(oa) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                  for (int z = 1; z < e.act_zs; ++z) *reinterpret_cast<uint4*>(oa + z * 8) = make_uint4(0, 0, 0, 0);
+                } else {
+                  *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(e.out_act) + o) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                }
               }
             }
           }

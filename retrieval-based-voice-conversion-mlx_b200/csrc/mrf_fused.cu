@@ -473,7 +473,14 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
                       pk[i] = pack2(fmaxf(o[2 * i], o[2 * i] * p.out_slope), fmaxf(o[2 * i + 1], o[2 * i + 1] * p.out_slope), p.out_fmt);
-                    *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out_act) + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    if (p.out_zs > 1) {
+                      uint16_t* oa = reinterpret_cast<uint16_t*>(p.out_act) +
+                                     (((size_t)(item_base / p.Lp) + (size_t)(sl0 + s8)) * p.Lp_out_act + PADL + (size_t)t * p.out_zs) * 8;
+                      *reinterpret_cast<uint4*>(oa) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                      for (int z = 1; z < p.out_zs; ++z) *reinterpret_cast<uint4*>(oa + z * 8) = make_uint4(0, 0, 0, 0);
+                    } else {
+                      *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out_act) + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    }
                   }
                 }
               }

@@ -79,6 +79,7 @@ struct rvcdec_handle {
   std::string fast_why;
   ConvLayer conv_pre;
   std::vector<ConvLayer> ups;
+  std::vector<ConvLayer> ups_zs;  // stride-2 upsamples as ordinary convs over a zero-stuffed input (n_tile == 0: unused)
   std::vector<ConvLayer> rbconv;  // index ((i*nk + j)*nd + m)*2 + which
   std::vector<NoiseLayer> noise;
   std::vector<float> post_w;  // [k][C]
@@ -95,6 +96,7 @@ struct rvcdec_handle {
   long long* d_timing = nullptr;
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
+  int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
   int fused_mrf = 1;  // 0 = one kernel per conv everywhere, 1 = fused ResBlock kernel (one launch per ResBlock) on
                       // the 64/32-channel stages, 2 = one launch per stage (all ResBlocks, common margin)
   // profiling (bench.py): one event before every launch, groups aggregated on read
@@ -283,6 +285,13 @@ int fmt_stage(int mode, int i) {
   return i <= 1 ? ACT_BF16 : ACT_F16;
 }
 
+bool use_fused_mrf(const rvcdec_handle* h, int mode, int i);
+// Stage i writes its 16-bit output zero-stuffed when stage i+1 is a stride-2 upsample feeding a fused MRF stage.
+bool zs_out_stage(const rvcdec_handle* h, int mode, int i) {
+  if (mode == 0 || !h->zero_stuff || i + 1 >= h->nups) return false;
+  return h->cfg.upsample_rates[i + 1] == 2 && h->ups_zs[i + 1].n_tile != 0 && use_fused_mrf(h, mode, i + 1);
+}
+
 struct Workspace {
   float* har; float* biasB; void* xin; void* pre;
   float* xs0; float* xr; float* sum; void* a0; void* a1; void* a2;
@@ -299,17 +308,19 @@ Workspace carve(const rvcdec_handle* h, void* base, int B, int T, int mode) {
   w.biasB = (float*)take((size_t)B * C0 * 4);
   w.xin = take((size_t)B * h->cfg.initial_channel * LpT * act_bytes(fmt_pre(mode)));
   w.pre = take((size_t)B * C0 * LpT * act_bytes(fmt_pre(mode)));
-  size_t emax = 0;
+  size_t emax = 0, emax_a0 = 0;
   int L = T;
   for (int i = 0; i < h->nups; ++i) {
     L *= h->cfg.upsample_rates[i];
     emax = std::max(emax, (size_t)h->ch[i] * padded_rows(L));
+    if (h->loaded && zs_out_stage(h, mode, i)) emax_a0 = std::max(emax_a0, (size_t)h->ch[i] * padded_rows(2 * L));
   }
+  emax_a0 = std::max(emax_a0, emax);
   const size_t asz = mode == 0 ? 4 : 2;
   w.xs0 = (float*)take((size_t)B * emax * 4);
   w.xr = (float*)take((size_t)B * emax * 4);
   w.sum = (float*)take((size_t)B * emax * 4);
-  w.a0 = take((size_t)B * emax * asz);
+  w.a0 = take((size_t)B * emax_a0 * asz);
   w.a1 = take((size_t)B * emax * asz);
   w.a2 = take((size_t)B * emax * asz);
   w.bytes = off;
@@ -393,7 +404,7 @@ bool use_fused_mrf(const rvcdec_handle* h, int mode, int i) {
 }
 
 int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w, int B, int Lo, int Lpo, int fs,
-                  bool last, cudaStream_t s) {
+                  bool last, bool zs_out, cudaStream_t s) {
   const int C = h->ch[i];
   auto layer = [&](int j, int m, int which) -> const ConvLayer& {
     return h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which];
@@ -421,6 +432,7 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
   p.out_f32 = last ? w.sum : nullptr;  // the last stage hands its fp32 average to conv_post in `sum`
   p.out_act = last ? nullptr : w.a0;   // the next stage consumes leaky_relu(x, 0.1) in this stage's format
   p.fmt = fs; p.out_fmt = fs;
+  p.out_zs = zs_out ? 2 : 1; p.Lp_out_act = padded_rows(2 * Lo);
   p.scale = 1.f / (float)h->nk; p.slope = 0.1f; p.out_slope = 0.1f;
   p.B = B; p.L = Lo; p.Lp = Lpo; p.C = C; p.nd = h->nd;
   const double el = (double)B * Lo * C;
@@ -484,6 +496,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   const void* stage_in = w.pre;
   int fmt_in = fpre;
   int L = T;
+  bool zs_in = false;  // stage_in is zero-stuffed (rows 2t hold the data)
   for (int i = 0; i < h->nups; ++i) {
     const std::string g_ups = "ups" + std::to_string(i), g_noise = "noise_add" + std::to_string(i),
                       g_mrf = "mrf" + std::to_string(i);
@@ -497,6 +510,20 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     // Short noise convs ride in the upsample epilogue when the stage runs the fused MRF kernel (which
     // reads the fp32 stage input only, so no activated 16-bit copy is needed).
     const bool fuse_noise = nl.k <= 8 && use_fused_mrf(h, mode, i);
+    const bool zs_out = zs_out_stage(h, mode, i);
+    if (zs_in) {
+      // x = ups[i](...) as an ordinary convolution over the zero-stuffed tensor the previous stage wrote
+      CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fmt_in), B, h->ch[i - 1], Lo, Lpo, s)); ++h->launches;
+      Epilogue e{};
+      e.bias = h->ups_zs[i].d_bias; e.scale = 1.f; e.slope = 0.1f;
+      e.out_f32 = w.xs0; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
+      if (nl.k <= 8) {  // the coalesced epilogue carries noise convs of up to 8 taps
+        e.nz_har = w.har; e.nz_w = nl.d_w; e.nz_bias = nl.d_bias;
+        e.nz_k = nl.k; e.nz_stride = nl.stride; e.nz_pad = nl.pad; e.nz_src = T * h->upp;
+      }
+      int rc = run_conv(h, g_ups.c_str(), h->ups_zs[i], mode, fmt_in, stage_in, B, Lo, e, s);
+      if (rc) return rc;
+    } else
     {  // x = ups[i](leaky_relu(x, 0.1))  (hifigan_nsf.py:185,198); the activation was applied by the producer
       Epilogue e{};
       e.bias = h->ups[i].d_bias; e.scale = 1.f; e.slope = 0.1f;
@@ -509,8 +536,8 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
       if (rc) return rc;
     }
     // (after the upsample has read the previous stage's tensor out of a0: new geometry, new pad rows)
-    if (fuse_noise) { CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
-    if (!fuse_noise) {
+    if ((fuse_noise || (zs_in && nl.k <= 8)) && !zs_out) { CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
+    if (!fuse_noise && !(zs_in && nl.k <= 8)) {
       MARK(g_noise.c_str(), 2.0 * B * Lo * C * nl.k, (double)B * Lo * C * (8 + act_bytes(fs)));
       CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches;
       // x = x + noise_convs[i](har_source)  (:199)
@@ -523,7 +550,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     if (stop == 10 + i) { MARK(nullptr, 0, 0); return 0; }
     // xs = sum_j resblocks[i*nk + j](x) / nk  (:200-207), ResBlock.forward residuals.py:71-80
     if (use_fused_mrf(h, mode, i)) {
-      int rc = run_fused_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, s);
+      int rc = run_fused_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, zs_out, s);
       if (rc) return rc;
     } else
     for (int j = 0; j < h->nk; ++j) {
@@ -550,6 +577,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
             if (j == h->nk - 1 && !last) {
               // next stage consumes leaky_relu(x, 0.1) in ITS operand format; a0 is dead by now
               e.out_act = w.a0; e.act_fmt = fmt_stage(mode, i);
+              if (zs_out) { e.act_zs = 2; e.Lp_act = padded_rows(2 * Lo); }
             }
           }
           int rc = run_conv(h, g_mrf.c_str(), c2, mode, fs, w.a1, B, Lo, e, s);
@@ -561,6 +589,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     stage_in = w.a0;
     fmt_in = fs;
     L = Lo;
+    zs_in = zs_out;
   }
   // x = tanh(conv_post(leaky_relu(x)))  (:209-210), default slope 0.01
   MARK("conv_post", 2.0 * B * L * h->ch[h->nups - 1] * 7, (double)B * L * (h->ch[h->nups - 1] * 4 + 4));
@@ -656,6 +685,7 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
     if ((rc = get_vec(tm, "cond.bias", C0, h->cond_b))) return rc;
   }
   h->ups.assign(h->nups, ConvLayer());
+  h->ups_zs.assign(h->nups, ConvLayer());
   h->noise.assign(h->nups, NoiseLayer());
   h->rbconv.assign((size_t)h->nups * h->nk * h->nd * 2, ConvLayer());
   for (int i = 0; i < h->nups; ++i) {
@@ -665,6 +695,24 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
     h->ups[i].name = un;
     if ((rc = pack_ups(h->ups[i], W, Cin, C, k, u, (k - u) / 2))) return rc;
     if ((rc = get_vec(tm, un + ".bias", C, v))) return rc;
+    h->ups_zs[i] = ConvLayer();
+    if (u == 2 && k <= MAX_TAPS) {
+      // ConvTranspose1d(k, stride u, padding p) == Conv1d over the zero-stuffed input z[i*u] = x[i] with the
+      // flipped kernel: y[o] = b + sum_j z[o - (k-1-p) + j] * w[:, :, k-1-j]
+      ConvLayer& Z = h->ups_zs[i];
+      const int p0 = (k - u) / 2;
+      Z.name = un + "(zero-stuffed)";
+      Z.Cin = Cin; Z.N_total = C; Z.cout = C; Z.up = 1; Z.ntaps = k; Z.halo = 0;
+      Z.macs_per_row = (double)Cin * C * k / u;  // algorithmic MACs per OUTPUT row
+      Z.wf.assign((size_t)k * Cin * C, 0.f);
+      for (int j = 0; j < k; ++j) {
+        Z.shift[j] = j - (k - 1 - p0);
+        Z.halo = std::max(Z.halo, std::abs(Z.shift[j]));
+        for (int ci = 0; ci < Cin; ++ci)
+          for (int co = 0; co < C; ++co) Z.wf[((size_t)j * Cin + ci) * C + co] = W[((size_t)ci * C + co) * k + (k - 1 - j)];
+      }
+      Z.bias = v;
+    }
     h->ups[i].bias.resize((size_t)u * C);
     for (int r = 0; r < u; ++r) memcpy(&h->ups[i].bias[(size_t)r * C], v.data(), sizeof(float) * C);
     // noise_convs (:142-154): kernel 2s, stride s, pad s/2 (1/1/0 when s == 1)
@@ -717,6 +765,7 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   };
   fin(h->conv_pre);
   for (auto& L : h->ups) fin(L);
+  for (auto& L : h->ups_zs) if (L.ntaps) finish_layer(L, true);
   for (auto& L : h->rbconv) fin(L);
   return 0;
 }
@@ -736,6 +785,7 @@ int rvcdec_load_weights(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t 
   free_device(h);
   if ((rc = upload_layer(h, h->conv_pre))) return rc;
   for (auto& L : h->ups) if ((rc = upload_layer(h, L))) return rc;
+  for (auto& L : h->ups_zs) if (L.ntaps && (rc = upload_layer(h, L))) return rc;
   for (auto& L : h->rbconv) if ((rc = upload_layer(h, L))) return rc;
   for (auto& nl : h->noise) {
     if ((rc = upload(h, nl.w, &nl.d_w))) return rc;
@@ -883,6 +933,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     h->timing_launches = 0;
     return 0;
   }
+  if (k == "zero_stuff") {
+    if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "zero_stuff must be 0 or 1");
+    h->zero_stuff = (int)value;
+    return 0;
+  }
   if (k == "fused_mrf") {
     if (value < 0 || value > 2) return fail(RVCDEC_ERR_ARG, "fused_mrf must be 0, 1 or 2");
     h->fused_mrf = (int)value;
@@ -929,6 +984,7 @@ int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_
     if (nm == "stage" + std::to_string(i) + ".out") {
       if (need(n)) return RVCDEC_ERR_ARG;
       if (i == h->nups - 1) CK(launch_unpack(w.sum, ACT_F32, dst, B, h->ch[i], L, padded_rows(L), s));  // pre-activation
+      else if (zs_out_stage(h, mode, i)) CK(launch_unpack(w.a0, fmt_stage(mode, i), dst, B, h->ch[i], L, padded_rows(2 * L), s, 2));  // zero-stuffed rows
       else CK(launch_unpack(w.a0, fmt_stage(mode, i), dst, B, h->ch[i], L, padded_rows(L), s));          // leaky_relu(.,0.1)
       return n;
     }

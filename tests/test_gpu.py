@@ -153,9 +153,9 @@ def test_against_oracle_on_seeded_inputs(dev, cfg_name, B, T, seed, mode):
         assert err <= 2e-2, err
 
 
-@pytest.mark.parametrize("fused", [0, 1, 2])
+@pytest.mark.parametrize("fused,zs", [(0, 1), (1, 1), (2, 1), (1, 0)])
 @pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 11), ("40k", 1, 97, 12)])
-def test_fused_mrf_variants_agree(dev, fused, cfg_name, B, T, seed):
+def test_fused_mrf_variants_agree(dev, fused, zs, cfg_name, B, T, seed):
     """rvcdec_set_option("fused_mrf"): per-conv kernels (0), fused ResBlock kernel per ResBlock (1) and per
     stage (2) compute the same decoder; each meets the fast bar and they agree closely with one another
     (same operand rounding, different accumulation order).  Tile edges: T*upp/4 rows is not a multiple of
@@ -172,6 +172,7 @@ def test_fused_mrf_variants_agree(dev, fused, cfg_name, B, T, seed):
         y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
         n0 = m.last_launch_count
         m.fused_mrf = fused
+        m._handle.set_option("zero_stuff", zs)  # stride-2 upsamples: zero-stuffed conv (1) or polyphase (0)
         y = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
         n1 = m.last_launch_count
     if fused:
