@@ -22,7 +22,8 @@
 
 namespace rvcdec {
 
-constexpr int FUSED_THREADS = 320;
+constexpr int FUSED_THREADS = 352;
+constexpr int FUSED_MMA_WARP_B = 10;  // second MMA issuer (warp 1 is the first); 10 % 4 = 2: another scheduler
 constexpr int FUSED_EPI_WARPS = 8;
 
 template <int C, int MB, int S>
@@ -111,6 +112,7 @@ template <int C, int MB, int S, bool BF16, bool TIMING>
 __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __grid_constant__ FusedParams p) {
   using Cfg = FusedCfg<C, MB, S>;
   long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long t_taps = 0;  // MMA warp: time inside the tap loops (issue + queue back-pressure)
   const long long t_begin = TIMING ? clock64() : 0;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 127u) & ~127u;
@@ -132,7 +134,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
   for (int i = threadIdx.x; i < 2 * Cfg::A_BUF / 16; i += FUSED_THREADS)
     reinterpret_cast<uint4*>(smem_gen)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x == 0) {
-    for (int i = 0; i < S; ++i) { mbar_init(w_full + 8 * i, 1); mbar_init(w_empty + 8 * i, 1); }
+    for (int i = 0; i < S; ++i) { mbar_init(w_full + 8 * i, 1); mbar_init(w_empty + 8 * i, MB > 1 ? 2 : 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(acc1_full + 8 * i, 1); mbar_init(acc1_empty + 8 * i, FUSED_EPI_WARPS); }
     for (int i = 0; i < MB; ++i) {
       mbar_init(x_full + 8 * i, 1);
@@ -181,15 +183,20 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (converged warp, elected lane issues) =====================
+  } else if (warp == 1 || warp == FUSED_MMA_WARP_B) {
+    // ===================== MMA issuers (two converged warps on different schedulers) =====================
+    // The issue path (barrier probes + ~9 uniform instructions per MMA) costs about as much time as the
+    // tensor pipe needs to execute an N = 64 / 32 MMA (timing twin, r1g: 48 clk per MMA in the tap loop +
+    // ~600 clk per 128-row block), so one issuing thread cannot keep the pipe busy.  Blocks alternate
+    // between two issuers; all ordering between them goes through the operand / accumulator barriers.
+    const uint32_t issuer = (warp == 1) ? 0u : 1u;
     const uint32_t idesc = make_idesc(p.fmt, C);
     const uint64_t a0_desc = make_smem_desc(a0_smem, Cfg::A_SLICE, 128) + (uint64_t)Cfg::PAD;
     const uint64_t a1_desc = make_smem_desc(a1_smem, Cfg::A_SLICE, 128) + (uint64_t)Cfg::PAD;
     const uint64_t w_desc = make_smem_desc(w_smem, Cfg::B_SLICE, 128);
     const uint32_t leader = elect_one() ? 1u : 0u;
     uint32_t slot0 = 0, ph0 = 0;  // ring position of tap 0 of the current conv
-    uint32_t a1cnt = 0;           // conv1 accumulator blocks produced so far
+    uint32_t cnt[2] = {0, 0};     // conv1 / conv2 blocks issued so far (by both issuers); parity = owner
     uint32_t seq = 0;             // (tile, ResBlock) pairs processed so far
     for (int work = blockIdx.x; work < total_work; work += gridDim.x) {
       for (int rb = 0; rb < n_rb; ++rb, ++seq) {
@@ -202,48 +209,52 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
             const int shift0 = -((ntaps - 1) / 2) * dil;
             const uint32_t in_ready = which ? a1_ready : a0_ready;
             const uint64_t in_desc = which ? a1_desc : a0_desc;
+            const uint32_t cnt0 = cnt[which];
+            // blocks of this conv owned by this issuer: mb with ((cnt0 + mb) & 1) == issuer
+            const int first_own = ((cnt0 & 1u) == issuer) ? 0 : 1;
+            const int last_own = (((cnt0 + MB - 1) & 1u) == issuer) ? MB - 1 : MB - 2;
 #pragma unroll 1
-            for (int mb = 0; mb < MB; ++mb) {
-              // operand rows of blocks mb-1 .. mb+1 must have been written by the epilogue
-              TWAIT((which ? 3 : 0) + (mb < 2 ? mb : 2), if (mb == 0) mbar_wait(in_ready, par); if (mb + 1 < MB) mbar_wait(in_ready + 8 * (mb + 1), par));
-              uint32_t d_tmem;
-              uint32_t buf = 0;
-              if (!which) {
-                buf = a1cnt & 1u;
-                TWAIT(6, mbar_wait(acc1_empty + 8 * buf, ((a1cnt >> 1) & 1u) ^ 1u));
-                d_tmem = tmem_base + Cfg::ACC1_COL0 + buf * C;
-              } else {
-                d_tmem = tmem_base + mb * C;
-              }
-              // weights of this conv: lane t waits for tap t (one barrier latency for all taps)
-              if (mb == 0) {
-                uint32_t sl = slot0 + (uint32_t)lane, pz = ph0;
-                if (sl >= S) { sl -= S; pz ^= 1u; }
-                const uint32_t my_bar = w_full + 8 * sl;
-                const bool mine = lane < ntaps;
+            for (int mb = first_own; mb < MB; mb += 2) {
+              const uint32_t bcnt = cnt0 + (uint32_t)mb;
+              const uint32_t buf = issuer;  // conv1 accumulator buffer == owner (bcnt & 1)
+              uint32_t d_tmem = which ? (tmem_base + mb * C) : (tmem_base + Cfg::ACC1_COL0 + buf * C);
+              // ---- every barrier this block depends on, probed by one lane each, one vote ----
+              {
+                uint32_t my_bar = 0, my_par = 0;
+                bool mine = false;
+                if (lane == 0 && mb > 0) { mine = true; my_bar = in_ready + 8 * (mb - 1); my_par = par; }
+                if (lane == 1) { mine = true; my_bar = in_ready + 8 * mb; my_par = par; }
+                if (lane == 2 && mb + 1 < MB) { mine = true; my_bar = in_ready + 8 * (mb + 1); my_par = par; }
+                if (lane == 3 && !which) { mine = true; my_bar = acc1_empty + 8 * buf; my_par = (((bcnt >> 1) & 1u) ^ 1u); }
+                if (mb == first_own && lane >= 4 && lane < 4 + ntaps) {  // weights of this conv: lane 4+t waits for tap t
+                  uint32_t sl = slot0 + (uint32_t)(lane - 4), pz = ph0;
+                  if (sl >= S) { sl -= S; pz ^= 1u; }
+                  mine = true; my_bar = w_full + 8 * sl; my_par = pz;
+                }
                 const long long t_w = TIMING ? clock64() : 0;
                 for (uint32_t spin = 0;; ++spin) {  // uniform exit (vote), so the warp stays provably converged
-                  const uint32_t ok = mine ? mbar_try(my_bar, pz) : 1u;
+                  const uint32_t ok = mine ? mbar_try(my_bar, my_par) : 1u;
                   if (__all_sync(0xffffffffu, ok)) break;
-                  if (spin > (1u << 24)) { printf("rvcdec mrf_fused: weight barrier timeout (block %d)\n", (int)blockIdx.x); __trap(); }
+                  if (spin > (1u << 24)) { printf("rvcdec mrf_fused: barrier timeout (block %d issuer %u)\n", (int)blockIdx.x, issuer); __trap(); }
                 }
-                if (TIMING) tacc[7] += clock64() - t_w;
+                if (TIMING) tacc[0] += clock64() - t_w;
               }
               tc_fence_after();
               // Warp-uniform tap loop; the MMAs / commits are predicated on the elected lane.
               // (the shuffles only tell ptxas that these loop inputs are warp-uniform, so that the loop
-              //  below runs on the uniform datapath)
-              // 32-bit descriptor arithmetic: only the start-address field (low word) changes
+              //  below runs on the uniform datapath).  32-bit descriptor arithmetic: only the
+              // start-address field (low word) changes.
               uint32_t a_lo = uni((uint32_t)in_desc + (uint32_t)(mb * 128 + shift0));
               const uint32_t a_hi = (uint32_t)(in_desc >> 32), w_lo = (uint32_t)w_desc, w_hi = (uint32_t)(w_desc >> 32);
-              uint32_t slot = uni(slot0), ph = ph0;
-              // the last block releases each weight slot; the other blocks "release" a dummy barrier so
-              // that the commit stays unconditional (no divergent branch in the loop)
-              const uint32_t rel_base = uni((mb == MB - 1) ? w_empty : dummy_bar);
-              const uint32_t rel_step = uni((mb == MB - 1) ? 8u : 0u);
+              uint32_t slot = uni(slot0);
+              // this issuer's last block of the conv releases each weight slot (w_empty counts both issuers);
+              // its other blocks "release" a dummy barrier so that the commit stays unconditional
+              const uint32_t rel_base = uni((mb == last_own) ? w_empty : dummy_bar);
+              const uint32_t rel_step = uni((mb == last_own) ? 8u : 0u);
               uint32_t acc = uni(which ? 1u : 0u);
               d_tmem = uni(d_tmem);
               const int ntaps_u = (int)uni((uint32_t)ntaps), dil_u = (int)uni((uint32_t)dil);
+              const long long t_loop = TIMING ? clock64() : 0;
 #pragma unroll 1
               for (int tap = 0; tap < ntaps_u; ++tap) {
                 const uint32_t b_lo = w_lo + slot * (uint32_t)(Cfg::W_SLOT >> 4);
@@ -256,12 +267,12 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                 a_lo += (uint32_t)dil_u;
                 if (++slot == S) slot = 0;
               }
-              slot = slot0 + (uint32_t)ntaps;
-              if (slot >= S) { slot -= S; ph ^= 1u; }
+              if (TIMING) t_taps += clock64() - t_loop;
               tc_commit_pred(which ? (x_full + 8 * mb) : (acc1_full + 8 * buf), leader);
-              if (!which) ++a1cnt;
-              if (mb == MB - 1) { slot0 = slot; ph0 = ph; }
             }
+            cnt[which] = cnt0 + MB;
+            slot0 += (uint32_t)ntaps;
+            if (slot0 >= S) { slot0 -= S; ph0 ^= 1u; }
           }
         }
       }
@@ -499,10 +510,10 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
     // wait acc1_full, wait x_full, stage-input load, total
     long long* o = p.timing + (size_t)blockIdx.x * 16 + (threadIdx.x == 32 ? 0 : 8);
     if (threadIdx.x == 32) {
-      o[0] = tacc[0] + tacc[1] + tacc[2] + tacc[3] + tacc[4] + tacc[5]; o[1] = tacc[6]; o[2] = tacc[7];
+      o[0] = tacc[0]; o[1] = 0; o[2] = 0;
       o[3] = clock64() - t_begin;
       // operand-row waits by position: conv1 block 0, conv1 blocks >= 1, conv2 block 0, conv2 blocks >= 1
-      o[4] = tacc[0]; o[5] = tacc[1] + tacc[2]; o[6] = tacc[3]; o[7] = tacc[4] + tacc[5];
+      o[4] = 0; o[5] = 0; o[6] = t_taps; o[7] = 0;
     } else {
       o[0] = tacc[0]; o[1] = tacc[1]; o[2] = tacc[2]; o[3] = clock64() - t_begin;
       o[4] = tacc[3]; o[5] = tacc[4]; o[6] = tacc[5];

@@ -17,6 +17,8 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// (A non-zero suspendTimeHint on try_wait faulted with 'illegal memory access' on this driver in the
+// lane-parallel probe loops of mrf_fused.cu, r1j; the plain form is used everywhere.)
 // Bounded wait: a protocol bug must trap (launch error) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;

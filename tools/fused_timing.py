@@ -19,7 +19,7 @@ with torch.no_grad():
     m._handle.set_option("fused_timing", 1)
     m(x, f0, g, mode="fast")
     t = m._handle.fused_timing()
-names = ["mma:wait_rows", "mma:wait_acc1", "mma:wait_w", "mma:total", "rows:c1b0", "rows:c1b1+", "rows:c2b0", "rows:c2b1+",
+names = ["mma:wait_rows", "mma:wait_acc1", "mma:wait_w", "mma:total", "rows:c1b0", "rows:c1b1+", "mma:tap_loops", "rows:c2",
          "epi:wait_acc1", "epi:wait_x", "epi:xload", "epi:total", "epi1:tmem_ld", "epi1:math+sts", "epi1:fence+arrive", ""]
 for i in range(t.shape[0]):
     a = t[i].astype(float).mean(axis=0)
