@@ -152,6 +152,20 @@ def peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+def measured_traffic(B, T):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+    (profiles/roofline_traffic.json, written by tools/launch_share.py --traffic).  The capture runs fewer chunks
+    than the bench (ncu replays every kernel ~40x); traffic of these kernels is linear in the number of rows,
+    so it is scaled by rows(bench) / rows(capture) and the note says so."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))
+        scale = (B * T) / float(t["chunks"] * t["frames_per_chunk"])
+        return t["dram_bytes_per_launch"] * scale, (f"ncu dram__bytes_read+write per launch, {t['source']} ({t['chunks']} chunks), "
+                                                    f"x{scale:g} rows")
+    except Exception as e:  # noqa: BLE001
+        return None, f"no capture: {e}"
+
+
 # ------------------------------------------------------------------ arms
 def cpu_reference_throughput(T: int, reps: int, warm: int):
     """The reference's CPU implementation of the path = the oracle port (torch CPU fp32), all host threads."""
@@ -281,6 +295,9 @@ def run_ours(args):
                 "peak_kind": pk_kind + " bf16 sustained (kernel timed inside a long step)",
                 "avg_launch_ms": dom["ms"] / spans, "flops_per_launch": dom["flops"] / spans,
                 "hbm_gbs": dom_l["hbm_gbs"], "hbm_frac": dom_l["hbm_frac"]}
+    if args.mode != "fp32":
+        roof["traffic"], roof["traffic_note"] = measured_traffic(B, T)
+        roof["algorithmic_bytes_per_launch"] = dom["bytes"] / spans
     total_tflops = 2 * MMAC_PER_FRAME * T * B * args.steps / (ms * 1e-3) / 1e12
     cpu = None
     if world == 1 and not args.no_cpu:

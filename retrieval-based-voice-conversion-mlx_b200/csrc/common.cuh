@@ -210,9 +210,16 @@ struct FusedParams {
   int margin;         // rows at each tile edge that are recomputed by the neighbouring tile
   int tiles_per_item;
   long long* timing;  // null, or [gridDim.x][16] clock64 spans (instrumented kernel twin)
+  // optional fused tail (last stage, C = 32, 7 taps): post_out[b][t] = tanh(conv_post(leaky_relu(avg, post_slope)))
+  // (hifigan_nsf.py:209-210) computed from the last ResBlock's epilogue instead of writing the fp32 average to HBM;
+  // `margin` must then include the 3 extra rows per side that conv_post reads.
+  const float* post_w;  // [7][C], or null
+  float* post_out;      // (B, L)
+  float post_slope;
   FusedRB rb[FUSED_MAX_RB];
 };
 bool mrf_fused_supported(int C, int max_taps, int max_halo);
+bool mrf_fused_post_supported(int C, int post_k);
 int mrf_fused_tile_rows(int C);
 cudaError_t launch_mrf_fused(const FusedParams& p, int num_sms, cudaStream_t s);
 

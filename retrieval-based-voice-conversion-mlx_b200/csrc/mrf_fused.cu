@@ -41,7 +41,12 @@ struct FusedCfg {
   static constexpr int USED_COLS = X_COLS + 2 * C;
   static constexpr int TMEM_COLS = USED_COLS <= 128 ? 128 : USED_COLS <= 256 ? 256 : 512;
   static constexpr int NUM_BARS = 2 * S + 4 + 3 * MB + 1;
-  static constexpr int SMEM_BYTES = 128 + 2 * A_BUF + S * W_SLOT + NUM_BARS * 8 + 16;
+  // fused conv_post (last stage only, C = 32): ring of 3 blocks x 2 column halves x 7 taps x 128 rows of partial
+  // dot products + the [7][C] conv_post weights
+  static constexpr int POST_TAPS = 7;
+  static constexpr int POST_RING = 3;
+  static constexpr int POST_BYTES = (C == 32) ? (POST_RING * 2 * POST_TAPS * 128 * 4 + POST_TAPS * C * 4) : 0;
+  static constexpr int SMEM_BYTES = 128 + 2 * A_BUF + S * W_SLOT + NUM_BARS * 8 + 16 + 16 + POST_BYTES;
   static_assert(USED_COLS <= 512, "TMEM budget");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
   static_assert(C == 32 || C == 64, "column split below assumes 16 or 32 columns per epilogue warp");
@@ -126,6 +131,12 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
   const uint32_t dummy_bar = a1_ready + 8 * MB;  // sink for commits that release nothing
   const uint32_t tmem_slot = dummy_bar + 8;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+  const uint32_t post_s = (tmem_slot + 16 + 15) & ~15u;  // partial-sum ring, then the conv_post weights
+  float* post_ring = reinterpret_cast<float*>(smem_gen + (post_s - smem_base));
+  float* post_wsm = post_ring + Cfg::POST_RING * 2 * Cfg::POST_TAPS * 128;
+  const bool do_post_any = Cfg::POST_BYTES > 0 && p.post_w != nullptr;
+  if (do_post_any)
+    for (int i = threadIdx.x; i < Cfg::POST_TAPS * C; i += FUSED_THREADS) post_wsm[i] = p.post_w[i];
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);  // provably warp-uniform role index
   const int lane = threadIdx.x & 31;
@@ -324,13 +335,14 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
     // inside the final epilogue of unit n (as soon as a block's residual has been read out of TMEM its
     // columns and operand rows are free), so the MMA warp finds the first blocks of the next unit ready
     // while the last block of this one is still in the tensor pipe.
-    struct Unit { int work, rb, t0; size_t item_base; bool interior, valid; };
+    struct Unit { int work, rb, t0, item; size_t item_base; bool interior, valid; };
     auto make_unit = [&](int work, int rb) {
       Unit u;
       u.work = work; u.rb = rb; u.valid = work < total_work;
       const int bb = work / p.tiles_per_item;
       const int tile = work - bb * p.tiles_per_item;
       u.t0 = tile * valid_rows - p.margin;
+      u.item = bb;
       u.item_base = (size_t)bb * Cfg::NSL * p.Lp;
       u.interior = (u.t0 >= 0) && (u.t0 + Cfg::MT <= p.L);  // no row of this tile needs zero padding
       return u;
@@ -338,6 +350,24 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
     auto load_unit_x = [&](float4 (&dst)[NC / 4], const Unit& u, int r) {
       const int t = u.t0 + r;
       load_x(dst, u.item_base, t, u.interior || (t >= 0 && t < p.L));
+    };
+    // L2 prefetch of what the final epilogue of this unit will read for row r: the running MRF sum and the
+    // next unit's stage input.  Issued one convolution ahead (from the last conv1 epilogue), so the
+    // final epilogue's loads hit L2 instead of paying an HBM round trip per block on the critical path
+    // between two units (timing twin r1k: ~15k clk per unit were spent there).
+    auto prefetch_final = [&](const Unit& u, const Unit& nx, int r, bool sum_in) {
+      const int t = u.t0 + r;
+      if (sum_in && r >= p.margin && r < Cfg::MT - p.margin && t >= 0 && t < p.L) {
+#pragma unroll
+        for (int s8 = 0; s8 < NS8; ++s8)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.sum + ((u.item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8));
+      }
+      const int tn = nx.t0 + r;
+      if (nx.valid && tn >= 0 && tn < p.L) {
+#pragma unroll
+        for (int s8 = 0; s8 < NS8; ++s8)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.x_in + ((nx.item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + tn) * 8));
+      }
     };
     // x block (registers) -> TMEM residual + lrelu(x) operand rows, then signal the MMA warp
     auto store_unit_x = [&](const float4 (&cur)[NC / 4], int mb) {
@@ -412,6 +442,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
             TWAIT(5, fence_proxy_async(); tc_fence_before(); __syncwarp();
                   if (lane == 0) { mbar_arrive(a1_ready + 8 * mb); mbar_arrive(acc1_empty + 8 * buf); });
             ++a1cnt;
+            if (m == nd - 1) prefetch_final(u, nx, r, R.sum_in != 0);
           }
         }
         // ---- conv2 epilogue: x (TMEM) now holds x + conv2(...) without the biases ----
@@ -447,13 +478,28 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
             const int r = mb * 128 + r_in_blk;
             const int t = t0 + r;
             const bool ok = interior || ((t >= 0) && (t < p.L));
-            const bool store_out = ok && r >= p.margin && r < Cfg::MT - p.margin;
+            // fused conv_post consumes rows up to 3 beyond the rows this tile writes (p.margin includes them)
+            const bool do_post = do_post_any && R.is_last;
+            const int extra = do_post ? (Cfg::POST_TAPS - 1) / 2 : 0;
+            const bool store_out = ok && r >= p.margin - extra && r < Cfg::MT - p.margin + extra;
             float4 xn[NC / 4];
             if (nx.valid) load_unit_x(xn, nx, r);  // in flight while we wait for the accumulator
+            float4 sm[NC / 4];                      // running MRF sum of this row: all loads before any store
+            if (R.sum_in && store_out) {
+#pragma unroll
+              for (int s8 = 0; s8 < NS8; ++s8) {
+                const float* sp = p.sum + ((item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8;
+                sm[2 * s8] = *reinterpret_cast<const float4*>(sp);
+                sm[2 * s8 + 1] = *reinterpret_cast<const float4*>(sp + 4);
+              }
+            }
             TWAIT(1, mbar_wait(x_full + 8 * mb, par));
             tc_fence_after();
             uint32_t rr[NC];
             tmem_load_cols<NC>(t_lane + mb * C + hh * NC, rr);
+            float pj[Cfg::POST_TAPS];  // conv_post partial dot products of this row over this warp's channels
+#pragma unroll
+            for (int j = 0; j < Cfg::POST_TAPS; ++j) pj[j] = 0.f;
             if (store_out) {
 #pragma unroll
               for (int s8 = 0; s8 < NS8; ++s8) {
@@ -466,14 +512,26 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                   o[2 * i + 1] = (__uint_as_float(rr[8 * s8 + 2 * i + 1]) + bb.y) * p.scale;
                 }
                 if (R.sum_in) {
-                  const float4 s0 = *reinterpret_cast<const float4*>(p.sum + off);
-                  const float4 s1 = *reinterpret_cast<const float4*>(p.sum + off + 4);
+                  const float4 s0 = sm[2 * s8], s1 = sm[2 * s8 + 1];
                   o[0] += s0.x; o[1] += s0.y; o[2] += s0.z; o[3] += s0.w;
                   o[4] += s1.x; o[5] += s1.y; o[6] += s1.z; o[7] += s1.w;
                 }
                 if (!R.is_last) {
                   *reinterpret_cast<float4*>(p.sum + off) = make_float4(o[0], o[1], o[2], o[3]);
                   *reinterpret_cast<float4*>(p.sum + off + 4) = make_float4(o[4], o[5], o[6], o[7]);
+                } else if (do_post) {
+                  // leaky_relu(x, 0.01) . conv_post weights (hifigan_nsf.py:209-210): tap j of this row feeds sample t - j + 3
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], o[i] * p.post_slope);
+#pragma unroll
+                  for (int j = 0; j < Cfg::POST_TAPS; ++j) {
+                    const float4 w0 = *reinterpret_cast<const float4*>(post_wsm + j * C + (sl0 + s8) * 8);
+                    const float4 w1 = *reinterpret_cast<const float4*>(post_wsm + j * C + (sl0 + s8) * 8 + 4);
+                    float a = pj[j];
+                    a = fmaf(o[0], w0.x, a); a = fmaf(o[1], w0.y, a); a = fmaf(o[2], w0.z, a); a = fmaf(o[3], w0.w, a);
+                    a = fmaf(o[4], w1.x, a); a = fmaf(o[5], w1.y, a); a = fmaf(o[6], w1.z, a); a = fmaf(o[7], w1.w, a);
+                    pj[j] = a;
+                  }
                 } else {
                   if (p.out_f32) {
                     *reinterpret_cast<float4*>(p.out_f32 + off) = make_float4(o[0], o[1], o[2], o[3]);
@@ -493,6 +551,29 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                       *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out_act) + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                     }
                   }
+                }
+              }
+            }
+            if (do_post) {
+              // stage the partial sums of this block, then (column-half 0 warps) finish the samples whose 7-row
+              // windows are complete: tile rows [mb*128 - 3, mb*128 + 125).  The ring keeps 3 blocks, so the one
+              // barrier per block also orders these reads against the overwrite two blocks later.
+              float* ring = post_ring + ((mb % Cfg::POST_RING) * 2 + hh) * Cfg::POST_TAPS * 128 + r_in_blk;
+#pragma unroll
+              for (int j = 0; j < Cfg::POST_TAPS; ++j) ring[j * 128] = pj[j];
+              asm volatile("bar.sync 1, 256;" ::: "memory");
+              if (hh == 0) {
+                const int ro = r - extra;
+                const int to = t0 + ro;
+                if (ro >= p.margin && ro < Cfg::MT - p.margin && to >= 0 && to < p.L) {
+                  float acc = 0.f;
+#pragma unroll
+                  for (int j = 0; j < Cfg::POST_TAPS; ++j) {
+                    const int src = ro + j - extra;  // the row whose tap-j product feeds sample ro
+                    const float* q = post_ring + (((src >> 7) % Cfg::POST_RING) * 2) * Cfg::POST_TAPS * 128 + j * 128 + (src & 127);
+                    acc += q[0] + q[Cfg::POST_TAPS * 128];
+                  }
+                  p.post_out[(size_t)u.item * p.L + to] = tanhf(acc);
                 }
               }
             }
@@ -538,6 +619,9 @@ static cudaError_t launch_fused_inst(const FusedParams& p, int num_sms, cudaStre
   if (e != cudaSuccess) return e;
   FusedParams q = p;
   const int valid = Cfg::MT - 2 * p.margin;
+  // (one ResBlock per launch only: the tail reads the running MRF sum 3 rows beyond the rows this tile owns, which
+  //  must come from an earlier launch, not from a neighbouring CTA of this one)
+  if (p.post_w && (Cfg::POST_BYTES == 0 || p.margin < 3 || !p.post_out || p.n_rb != 1)) return cudaErrorInvalidValue;
   if (valid < 128 || p.nd < 1 || p.nd > FUSED_MAX_D || p.n_rb < 1 || p.n_rb > FUSED_MAX_RB) return cudaErrorInvalidValue;
   for (int r = 0; r < p.n_rb; ++r)
     for (int m = 0; m < p.nd; ++m) {
@@ -560,6 +644,7 @@ bool mrf_fused_supported(int C, int max_taps, int max_halo) {
   if (C == 32) return max_taps <= 24;
   return false;
 }
+bool mrf_fused_post_supported(int C, int post_k) { return C == 32 && post_k == 7; }
 int mrf_fused_tile_rows(int C) { return C == 64 ? 3 * 128 : C == 32 ? 8 * 128 : 0; }
 
 cudaError_t launch_mrf_fused(const FusedParams& p, int num_sms, cudaStream_t s) {

@@ -97,6 +97,7 @@ struct rvcdec_handle {
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
+  int fused_post = 1; // 1 = conv_post + tanh fused into the last stage's final fused-MRF launch (C = 32, 7 taps)
   int fused_mrf = 1;  // 0 = one kernel per conv everywhere, 1 = fused ResBlock kernel (one launch per ResBlock) on
                       // the 64/32-channel stages, 2 = one launch per stage (all ResBlocks, common margin)
   // profiling (bench.py): one event before every launch, groups aggregated on read
@@ -379,6 +380,17 @@ int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, 
 
 // The fused ResBlock-chain kernel (mrf_fused.cu) serves the stages whose channel count makes the
 // per-conv kernels HBM-bound (C = 64, 32).
+// largest receptive-field margin (rows per side) of stage i's ResBlock chains
+int fused_margin(const rvcdec_handle* h, int i) {
+  int margin = 0;
+  for (int j = 0; j < h->nk; ++j) {
+    int mj = 0;
+    for (int m = 0; m < h->nd; ++m)
+      for (int which = 0; which < 2; ++which) mj += h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which].halo;
+    margin = std::max(margin, mj);
+  }
+  return margin;
+}
 bool use_fused_mrf(const rvcdec_handle* h, int mode, int i) {
   if (mode == 0 || h->fused_mrf == 0) return false;
   if (h->nd > FUSED_MAX_D || h->nk > FUSED_MAX_RB) return false;
@@ -393,18 +405,20 @@ bool use_fused_mrf(const rvcdec_handle* h, int mode, int i) {
       }
   if (!mrf_fused_supported(h->ch[i], max_taps, max_halo)) return false;
   // the chain's receptive field must leave a useful tile interior
-  int margin = 0;
-  for (int j = 0; j < h->nk; ++j) {
-    int mj = 0;
-    for (int m = 0; m < h->nd; ++m)
-      for (int which = 0; which < 2; ++which) mj += h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which].halo;
-    margin = std::max(margin, mj);
-  }
-  return mrf_fused_tile_rows(h->ch[i]) - 2 * margin >= 128;
+  return mrf_fused_tile_rows(h->ch[i]) - 2 * fused_margin(h, i) >= 128;
 }
 
+// conv_post + tanh can ride in the final fused-MRF launch of the last stage (not while a debug tap wants the
+// stage output in HBM).
+bool fuse_post(const rvcdec_handle* h, int mode, int i) {
+  return h->fused_post && h->fused_mrf == 1 && h->debug_stop == 0 && i == h->nups - 1 && use_fused_mrf(h, mode, i) &&
+         mrf_fused_post_supported(h->ch[i], 7) &&
+         mrf_fused_tile_rows(h->ch[i]) - 2 * (fused_margin(h, i) + 3) >= 128;
+}
+
+// `post_out` non-null: conv_post + tanh ride in the last ResBlock's epilogue (the caller checked fuse_post()).
 int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w, int B, int Lo, int Lpo, int fs,
-                  bool last, bool zs_out, cudaStream_t s) {
+                  bool last, bool zs_out, float* post_out, cudaStream_t s) {
   const int C = h->ch[i];
   auto layer = [&](int j, int m, int which) -> const ConvLayer& {
     return h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + which];
@@ -441,11 +455,16 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
     for (int m = 0; m < h->nd; ++m) f += 2.0 * B * Lo * (layer(j, m, 0).macs_per_row + layer(j, m, 1).macs_per_row);
     return f;
   };
+  const double post_fl = post_out ? 2.0 * B * Lo * C * 7 : 0.0;
+  auto arm_post = [&]() {  // the launch that completes the MRF average also produces the waveform
+    p.post_w = h->d_post_w; p.post_out = post_out; p.post_slope = 0.01f; p.out_f32 = nullptr; p.margin += 3;
+  };
   if (h->fused_mrf == 2) {
     double fl = 0;
     p.n_rb = h->nk; p.margin = 0;
     for (int j = 0; j < h->nk; ++j) { p.margin = std::max(p.margin, fill_rb(p.rb[j], j)); fl += flops_rb(j); }
-    MARK(group, fl, el * (4 + (last ? 4 : act_bytes(fs))));
+    if (post_out) arm_post();
+    MARK(group, fl + post_fl, el * (4 + (last ? (post_out ? 0 : 4) : act_bytes(fs))) + (post_out ? 4.0 * B * Lo : 0.0));
     p.timing = next_timing();
     CK(launch_mrf_fused(p, h->num_sms, s)); ++h->launches;
   } else {
@@ -453,7 +472,9 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
       p.n_rb = 1;
       p.margin = fill_rb(p.rb[0], j);
       const bool fin = (j == h->nk - 1);
-      MARK(group, flops_rb(j), el * (4 + (j > 0 ? 4 : 0) + (fin ? (last ? 4 : act_bytes(fs)) : 4)));
+      if (fin && post_out) arm_post();
+      MARK(group, flops_rb(j) + (fin ? post_fl : 0.0),
+           el * (4 + (j > 0 ? 4 : 0) + (fin ? (last ? (post_out ? 0 : 4) : act_bytes(fs)) : 4)) + (fin && post_out ? 4.0 * B * Lo : 0.0));
       p.timing = next_timing();
       CK(launch_mrf_fused(p, h->num_sms, s)); ++h->launches;
     }
@@ -467,6 +488,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   const rvcdec_config& c = h->cfg;
   Workspace w = carve(h, wsbase, B, T, mode);
   const int stop = h->debug_stop;
+  bool post_fused = false;
   const int C0 = c.upsample_initial_channel;
   const int LpT = padded_rows(T);
   const int fpre = fmt_pre(mode);
@@ -550,7 +572,8 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     if (stop == 10 + i) { MARK(nullptr, 0, 0); return 0; }
     // xs = sum_j resblocks[i*nk + j](x) / nk  (:200-207), ResBlock.forward residuals.py:71-80
     if (use_fused_mrf(h, mode, i)) {
-      int rc = run_fused_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, zs_out, s);
+      post_fused = last && fuse_post(h, mode, i);
+      int rc = run_fused_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, zs_out, post_fused ? out : nullptr, s);
       if (rc) return rc;
     } else
     for (int j = 0; j < h->nk; ++j) {
@@ -592,8 +615,10 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     zs_in = zs_out;
   }
   // x = tanh(conv_post(leaky_relu(x)))  (:209-210), default slope 0.01
-  MARK("conv_post", 2.0 * B * L * h->ch[h->nups - 1] * 7, (double)B * L * (h->ch[h->nups - 1] * 4 + 4));
-  CK(launch_post(w.sum, h->d_post_w, out, B, h->ch[h->nups - 1], L, padded_rows(L), 7, 0.01f, s)); ++h->launches;
+  if (!post_fused) {
+    MARK("conv_post", 2.0 * B * L * h->ch[h->nups - 1] * 7, (double)B * L * (h->ch[h->nups - 1] * 4 + 4));
+    CK(launch_post(w.sum, h->d_post_w, out, B, h->ch[h->nups - 1], L, padded_rows(L), 7, 0.01f, s)); ++h->launches;
+  }
   MARK(nullptr, 0, 0);
   return 0;
 }
@@ -938,6 +963,7 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     h->zero_stuff = (int)value;
     return 0;
   }
+  if (k == "fused_post") { h->fused_post = value ? 1 : 0; return RVCDEC_OK; }
   if (k == "fused_mrf") {
     if (value < 0 || value > 2) return fail(RVCDEC_ERR_ARG, "fused_mrf must be 0, 1 or 2");
     h->fused_mrf = (int)value;

@@ -182,6 +182,30 @@ def test_fused_mrf_variants_agree(dev, fused, zs, cfg_name, B, T, seed):
     assert float((y - y0).abs().max()) <= 2e-3, float((y - y0).abs().max())
 
 
+@pytest.mark.parametrize("fused", [1])
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 21), ("40k", 1, 97, 22), ("48k", 1, 3, 23), ("32k", 3, 61, 24)])
+def test_fused_conv_post_matches_separate_kernel(dev, fused, cfg_name, B, T, seed):
+    """rvcdec_set_option("fused_post"): conv_post + tanh computed inside the last fused-MRF launch (tile
+    margins widened by conv_post's 3 rows) vs the stand-alone post kernel on the same stage output.  Same
+    fp32 products, different summation order: the waveforms agree to a few ulp of the pre-tanh sum.  Covers
+    sequence ends (zero padding of conv_post), items shorter than one tile and several tiles per item."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K, "32k": O.CONFIG_32K}[cfg_name]
+    m = build_module(cfg, 3000 + seed).to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        m.fused_mrf = fused
+        m._ensure_handle(dev).set_option("fused_post", 0)
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        m._handle.set_option("fused_post", 1)
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+    assert n1 == n0 - 1, (n0, n1)
+    assert y1.shape == y0.shape
+    assert float((y1 - y0).abs().max()) <= 2e-5, float((y1 - y0).abs().max())
+
+
 def test_readme_shape_both_modes(dev):
     """BASELINE configs[2]: 13.5 s at the README benchmark shape (T=1350), real RMVPE-like contour shape."""
     cfg = O.CONFIG_48K
