@@ -209,6 +209,7 @@ struct FusedParams {
   int nd, n_rb;
   int margin;         // rows at each tile edge that are recomputed by the neighbouring tile
   int tiles_per_item;
+  int epi_warps;      // 8 or 16 epilogue warps (anything else = 16)
   long long* timing;  // null, or [gridDim.x][16] clock64 spans (instrumented kernel twin)
   // optional fused tail (last stage, C = 32, 7 taps): post_out[b][t] = tanh(conv_post(leaky_relu(avg, post_slope)))
   // (hifigan_nsf.py:209-210) computed from the last ResBlock's epilogue instead of writing the fp32 average to HBM;
@@ -222,6 +223,31 @@ bool mrf_fused_supported(int C, int max_taps, int max_halo);
 bool mrf_fused_post_supported(int C, int post_k);
 int mrf_fused_tile_rows(int C);
 cudaError_t launch_mrf_fused(const FusedParams& p, int num_sms, cudaStream_t s);
+
+// ---- fused ResBlock pair for the 128-channel stage (mrf_pair.cu) --------------
+//   v = x + conv2(lrelu(conv1(lrelu(x)) + b1)) + b2 ;  o = v * scale (+ sum_in) ;  out_f32 = o ; out_act = cvt(lrelu(o, out_slope))
+struct PairParams {
+  const float* x_in;          // fp32 blocked-8 (B, 128, L); must not alias out_f32 (tiles read their neighbours' rows)
+  const void* w1;             // conv_mma weight images, N tile 128 / K chunk 64: [tap][chunk][slice 8][n 128][8] 16-bit
+  const void* w2;
+  const float* b1;
+  const float* b2;
+  int k1, d1, k2, d2;         // taps / dilation of conv1, conv2
+  int fmt;                    // operand format (ACT_F16 / ACT_BF16)
+  float slope;                // 0.1 inside the ResBlocks
+  int B, L, Lp;
+  int margin;                 // halo(conv1) + halo(conv2): rows per tile edge recomputed by the neighbouring tile
+  int tiles_per_item;
+  float scale;                // 1 (inner pairs) or 1 / num_kernels (last pair of a ResBlock)
+  const float* sum_in;        // running MRF sum to add, or null
+  float* out_f32;             // residual stream for the next pair / running MRF sum / stage output, or null
+  void* out_act;              // leaky_relu(o, out_slope) as the next stage's 16-bit operand, or null
+  int out_fmt, out_zs, Lp_out_act;
+  float out_slope;
+  long long* timing;          // null, or [gridDim.x][16] clock64 spans (instrumented twin)
+};
+bool mrf_pair_supported(int C, int halo1, int halo2);
+cudaError_t launch_mrf_pair(const PairParams& p, int num_sms, cudaStream_t s);
 
 struct SourceParams {
   const float* f0;      // (B, T)

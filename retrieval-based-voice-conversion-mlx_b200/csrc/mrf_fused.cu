@@ -22,9 +22,9 @@
 
 namespace rvcdec {
 
-constexpr int FUSED_THREADS = 352;
-constexpr int FUSED_MMA_WARP_B = 10;  // second MMA issuer (warp 1 is the first); 10 % 4 = 2: another scheduler
-constexpr int FUSED_EPI_WARPS = 8;
+// EW = epilogue warps (8 or 16): EW / 4 column groups x 4 TMEM lane quarters.  Warps: 0 = weight producer,
+// 1 = MMA issuer A, 2 .. EW+1 = epilogue, EW+2 = MMA issuer B ((EW + 2) % 4 = 2: another scheduler than warp 1).
+__host__ __device__ constexpr int fused_threads(int ew) { return 32 * (ew + 3); }
 
 template <int C, int MB, int S>
 struct FusedCfg {
@@ -44,12 +44,14 @@ struct FusedCfg {
   // fused conv_post (last stage only, C = 32): ring of 3 blocks x 2 column halves x 7 taps x 128 rows of partial
   // dot products + the [7][C] conv_post weights
   static constexpr int POST_TAPS = 7;
-  static constexpr int POST_RING = 3;
-  static constexpr int POST_BYTES = (C == 32) ? (POST_RING * 2 * POST_TAPS * 128 * 4 + POST_TAPS * C * 4) : 0;
+  // partial sums: double-buffered block [2][4 column groups][7][128] + the last 8 rows of the previous blocks [3][4][7][8]
+  static constexpr int POST_MAIN = 2 * 4 * POST_TAPS * 128;
+  static constexpr int POST_TAIL = 3 * 4 * POST_TAPS * 8;
+  static constexpr int POST_BYTES = (C == 32) ? ((POST_MAIN + POST_TAIL) * 4 + POST_TAPS * C * 4) : 0;
   static constexpr int SMEM_BYTES = 128 + 2 * A_BUF + S * W_SLOT + NUM_BARS * 8 + 16 + 16 + POST_BYTES;
   static_assert(USED_COLS <= 512, "TMEM budget");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
-  static_assert(C == 32 || C == 64, "column split below assumes 16 or 32 columns per epilogue warp");
+  static_assert(C == 32 || C == 64, "column split below assumes 8, 16 or 32 columns per epilogue warp");
 };
 
 __device__ __forceinline__ uint32_t uni(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
@@ -96,6 +98,8 @@ __device__ __forceinline__ uint32_t lrelu_pack(uint64_t v, uint64_t slope2) {
 template <int NC>
 __device__ __forceinline__ void tmem_load_cols(uint32_t taddr, uint32_t (&r)[NC]);
 template <>
+__device__ __forceinline__ void tmem_load_cols<8>(uint32_t taddr, uint32_t (&r)[8]) { tc_ld8(taddr, r); }
+template <>
 __device__ __forceinline__ void tmem_load_cols<16>(uint32_t taddr, uint32_t (&r)[16]) { tc_ld16(taddr, r); }
 template <>
 __device__ __forceinline__ void tmem_load_cols<32>(uint32_t taddr, uint32_t (&r)[32]) { tc_ld32(taddr, r); }
@@ -113,9 +117,13 @@ __device__ __forceinline__ void tmem_load_cols<32>(uint32_t taddr, uint32_t (&r)
     }                                                      \
   } while (0)
 
-template <int C, int MB, int S, bool BF16, bool TIMING>
-__global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __grid_constant__ FusedParams p) {
+template <int C, int MB, int S, int EW, bool BF16, bool TIMING>
+__global__ void __launch_bounds__(fused_threads(EW), 1) mrf_fused_kernel(const __grid_constant__ FusedParams p) {
   using Cfg = FusedCfg<C, MB, S>;
+  constexpr int FUSED_THREADS = fused_threads(EW);
+  constexpr int FUSED_EPI_WARPS = EW;
+  constexpr int FUSED_MMA_WARP_B = EW + 2;
+  static_assert(EW == 8 || EW == 16, "epilogue warps");
   long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long t_taps = 0;  // MMA warp: time inside the tap loops (issue + queue back-pressure)
   const long long t_begin = TIMING ? clock64() : 0;
@@ -133,7 +141,8 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
   const uint32_t post_s = (tmem_slot + 16 + 15) & ~15u;  // partial-sum ring, then the conv_post weights
   float* post_ring = reinterpret_cast<float*>(smem_gen + (post_s - smem_base));
-  float* post_wsm = post_ring + Cfg::POST_RING * 2 * Cfg::POST_TAPS * 128;
+  float* post_tail = post_ring + Cfg::POST_MAIN;
+  float* post_wsm = post_tail + Cfg::POST_TAIL;
   const bool do_post_any = Cfg::POST_BYTES > 0 && p.post_w != nullptr;
   if (do_post_any)
     for (int i = threadIdx.x; i < Cfg::POST_TAPS * C; i += FUSED_THREADS) post_wsm[i] = p.post_w[i];
@@ -290,10 +299,11 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
     }
   } else {
     // ===================== epilogue warps =====================
-    constexpr int NC = C / 2;        // accumulator columns handled by this warp
+    constexpr int CG = EW / 4;       // column groups
+    constexpr int NC = C / CG;       // accumulator columns handled by this warp
     constexpr int NS8 = NC / 8;      // = 8-channel slices handled by this warp
     const int q = warp & 3;          // TMEM lane quarter this warp may access
-    const int hh = (warp - 2) >> 2;  // column half
+    const int hh = (warp - 2) >> 2;  // column group
     const int r_in_blk = q * 32 + lane;
     const int sl0 = hh * NS8;        // first slice of this warp
     const uint64_t slope2 = f2_splat(p.slope);
@@ -497,6 +507,9 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
             tc_fence_after();
             uint32_t rr[NC];
             tmem_load_cols<NC>(t_lane + mb * C + hh * NC, rr);
+            // The next unit's operand rows are published BEFORE this block's global stores are issued: the proxy
+            // fence in publish() waits for the thread's outstanding global stores (timing twin of mrf_pair.cu, r1q/r1s).
+            if (nx.valid) store_unit_x(xn, mb);
             float pj[Cfg::POST_TAPS];  // conv_post partial dot products of this row over this warp's channels
 #pragma unroll
             for (int j = 0; j < Cfg::POST_TAPS; ++j) pj[j] = 0.f;
@@ -558,10 +571,15 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
               // stage the partial sums of this block, then (column-half 0 warps) finish the samples whose 7-row
               // windows are complete: tile rows [mb*128 - 3, mb*128 + 125).  The ring keeps 3 blocks, so the one
               // barrier per block also orders these reads against the overwrite two blocks later.
-              float* ring = post_ring + ((mb % Cfg::POST_RING) * 2 + hh) * Cfg::POST_TAPS * 128 + r_in_blk;
+              float* ring = post_ring + (((mb & 1) * 4 + hh) * Cfg::POST_TAPS) * 128 + r_in_blk;
 #pragma unroll
               for (int j = 0; j < Cfg::POST_TAPS; ++j) ring[j * 128] = pj[j];
-              asm volatile("bar.sync 1, 256;" ::: "memory");
+              if (r_in_blk >= 120) {  // the next block's first samples read these rows after `main` has moved on
+                float* tl = post_tail + (((mb % 3) * 4 + hh) * Cfg::POST_TAPS) * 8 + (r_in_blk - 120);
+#pragma unroll
+                for (int j = 0; j < Cfg::POST_TAPS; ++j) tl[j * 8] = pj[j];
+              }
+              asm volatile("bar.sync 1, %0;" ::"n"(32 * EW) : "memory");
               if (hh == 0) {
                 const int ro = r - extra;
                 const int to = t0 + ro;
@@ -569,15 +587,17 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
                   float acc = 0.f;
 #pragma unroll
                   for (int j = 0; j < Cfg::POST_TAPS; ++j) {
-                    const int src = ro + j - extra;  // the row whose tap-j product feeds sample ro
-                    const float* q = post_ring + (((src >> 7) % Cfg::POST_RING) * 2) * Cfg::POST_TAPS * 128 + j * 128 + (src & 127);
-                    acc += q[0] + q[Cfg::POST_TAPS * 128];
+                    const int src = ro + j - extra - mb * 128;  // block-relative row whose tap-j product feeds sample ro
+                    const float* q = (src >= 0) ? post_ring + (((mb & 1) * 4) * Cfg::POST_TAPS + j) * 128 + src
+                                                : post_tail + ((((mb + 2) % 3) * 4) * Cfg::POST_TAPS + j) * 8 + (src + 8);
+                    const int cg_stride = (src >= 0) ? Cfg::POST_TAPS * 128 : Cfg::POST_TAPS * 8;
+#pragma unroll
+                    for (int c = 0; c < CG; ++c) acc += q[c * cg_stride];
                   }
                   p.post_out[(size_t)u.item * p.L + to] = tanhf(acc);
                 }
               }
             }
-            if (nx.valid) store_unit_x(xn, mb);
           }
         }
       }
@@ -610,11 +630,11 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) mrf_fused_kernel(const __gri
 }
 
 // ------------------------------ host side ----------------------------------
-template <int C, int MB, int S>
+template <int C, int MB, int S, int EW>
 static cudaError_t launch_fused_inst(const FusedParams& p, int num_sms, cudaStream_t s) {
   using Cfg = FusedCfg<C, MB, S>;
-  auto kern = p.timing ? (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, true, true> : mrf_fused_kernel<C, MB, S, false, true>)
-                       : (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, true, false> : mrf_fused_kernel<C, MB, S, false, false>);
+  auto kern = p.timing ? (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, EW, true, true> : mrf_fused_kernel<C, MB, S, EW, false, true>)
+                       : (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, EW, true, false> : mrf_fused_kernel<C, MB, S, EW, false, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
   if (e != cudaSuccess) return e;
   FusedParams q = p;
@@ -633,7 +653,7 @@ static cudaError_t launch_fused_inst(const FusedParams& p, int num_sms, cudaStre
   const long long total = (long long)q.B * q.tiles_per_item;
   if (total <= 0 || total > 0x7fffffffLL) return cudaErrorInvalidValue;
   const int grid = (int)(total < num_sms ? total : num_sms);
-  kern<<<grid, FUSED_THREADS, Cfg::SMEM_BYTES, s>>>(q);
+  kern<<<grid, fused_threads(EW), Cfg::SMEM_BYTES, s>>>(q);
   return cudaGetLastError();
 }
 
@@ -648,8 +668,8 @@ bool mrf_fused_post_supported(int C, int post_k) { return C == 32 && post_k == 7
 int mrf_fused_tile_rows(int C) { return C == 64 ? 3 * 128 : C == 32 ? 8 * 128 : 0; }
 
 cudaError_t launch_mrf_fused(const FusedParams& p, int num_sms, cudaStream_t s) {
-  if (p.C == 64) return launch_fused_inst<64, 3, 13>(p, num_sms, s);
-  if (p.C == 32) return launch_fused_inst<32, 8, 24>(p, num_sms, s);
+  if (p.C == 64) return p.epi_warps == 8 ? launch_fused_inst<64, 3, 13, 8>(p, num_sms, s) : launch_fused_inst<64, 3, 13, 16>(p, num_sms, s);
+  if (p.C == 32) return p.epi_warps == 8 ? launch_fused_inst<32, 8, 24, 8>(p, num_sms, s) : launch_fused_inst<32, 8, 24, 16>(p, num_sms, s);
   return cudaErrorInvalidValue;
 }
 

@@ -97,6 +97,9 @@ struct rvcdec_handle {
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
+  int pair_noise = 0;  // 1 = the pair stage's short noise conv rides in its upsample's epilogue (no noise_add launch)
+  int pair_mrf = 0;  // 1 = fused conv1+conv2 pair kernel (mrf_pair.cu) on the 128-channel stage (r1z: on par with the per-conv path, so off)
+  int fused_epi_warps = 8;   // epilogue warps of the fused ResBlock kernel (8 or 16)
   int fused_post = 1; // 1 = conv_post + tanh fused into the last stage's final fused-MRF launch (C = 32, 7 taps)
   int fused_mrf = 1;  // 0 = one kernel per conv everywhere, 1 = fused ResBlock kernel (one launch per ResBlock) on
                       // the 64/32-channel stages, 2 = one launch per stage (all ResBlocks, common margin)
@@ -287,6 +290,7 @@ int fmt_stage(int mode, int i) {
 }
 
 bool use_fused_mrf(const rvcdec_handle* h, int mode, int i);
+bool use_pair_mrf(const rvcdec_handle* h, int mode, int i);
 // Stage i writes its 16-bit output zero-stuffed when stage i+1 is a stride-2 upsample feeding a fused MRF stage.
 bool zs_out_stage(const rvcdec_handle* h, int mode, int i) {
   if (mode == 0 || !h->zero_stuff || i + 1 >= h->nups) return false;
@@ -322,8 +326,10 @@ Workspace carve(const rvcdec_handle* h, void* base, int B, int T, int mode) {
   w.xr = (float*)take((size_t)B * emax * 4);
   w.sum = (float*)take((size_t)B * emax * 4);
   w.a0 = take((size_t)B * emax_a0 * asz);
-  w.a1 = take((size_t)B * emax * asz);
-  w.a2 = take((size_t)B * emax * asz);
+  // a1 and a2 are adjacent: together they also serve as one fp32 tensor (the second residual buffer of the
+  // fused-pair path, run_pair_mrf)
+  w.a1 = take(2 * (size_t)B * emax * asz);
+  w.a2 = w.a1 ? (void*)((uint8_t*)w.a1 + (size_t)B * emax * asz) : nullptr;
   w.bytes = off;
   return w;
 }
@@ -408,6 +414,60 @@ bool use_fused_mrf(const rvcdec_handle* h, int mode, int i) {
   return mrf_fused_tile_rows(h->ch[i]) - 2 * fused_margin(h, i) >= 128;
 }
 
+// The fused-pair kernel (mrf_pair.cu) serves the 128-channel stage, where the per-conv path is HBM-bound.
+bool use_pair_mrf(const rvcdec_handle* h, int mode, int i) {
+  if (mode == 0 || !h->pair_mrf || h->ch[i] != 128) return false;
+  for (int j = 0; j < h->nk; ++j)
+    for (int m = 0; m < h->nd; ++m) {
+      const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
+      const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
+      if (c1.n_tile != 128 || c1.kc != 64 || c2.n_tile != 128 || c2.kc != 64) return false;  // weight image it streams
+      if (!mrf_pair_supported(h->ch[i], c1.halo, c2.halo)) return false;
+    }
+  return true;
+}
+
+// xs = sum_j ResBlock_j(x) / nk with one launch per (conv1, conv2) pair.  The fp32 residual stream ping-pongs
+// between xr and the a1|a2 region (a launch must not write the tensor its neighbouring tiles still read).
+int run_pair_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w, int B, int Lo, int Lpo, int fs,
+                 bool last, bool zs_out, cudaStream_t s) {
+  const int C = h->ch[i];
+  float* buf[2] = {w.xr, (float*)w.a1};
+  const double el = (double)B * Lo * C;
+  for (int j = 0; j < h->nk; ++j)
+    for (int m = 0; m < h->nd; ++m) {
+      const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
+      const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
+      PairParams p{};
+      p.x_in = (m == 0) ? w.xs0 : buf[(m - 1) & 1];
+      p.w1 = c1.d_wp[fs == ACT_BF16 ? 1 : 0]; p.w2 = c2.d_wp[fs == ACT_BF16 ? 1 : 0];
+      p.b1 = c1.d_bias; p.b2 = c2.d_bias;
+      p.k1 = c1.ntaps; p.d1 = c1.ntaps > 1 ? c1.shift[1] - c1.shift[0] : 1;
+      p.k2 = c2.ntaps; p.d2 = c2.ntaps > 1 ? c2.shift[1] - c2.shift[0] : 1;
+      p.fmt = fs; p.slope = 0.1f; p.B = B; p.L = Lo; p.Lp = Lpo; p.margin = c1.halo + c2.halo;
+      p.scale = 1.f; p.out_slope = 0.1f; p.out_fmt = fs; p.out_zs = 1; p.Lp_out_act = Lpo;
+      double bytes = el * 8;
+      if (m < h->nd - 1) {
+        p.out_f32 = buf[m & 1];
+      } else {
+        p.scale = 1.f / (float)h->nk;
+        p.sum_in = (j == 0) ? nullptr : w.sum;
+        if (j > 0) bytes += el * 4;
+        if (j < h->nk - 1 || last) p.out_f32 = w.sum; else bytes -= el * 4;
+        if (j == h->nk - 1 && !last) {
+          p.out_act = w.a0;  // the next stage consumes leaky_relu(x, 0.1) in this stage's operand format
+          if (zs_out) { p.out_zs = 2; p.Lp_out_act = padded_rows(2 * Lo); }
+          bytes += el * act_bytes(fs);
+        }
+      }
+      MARK(group, 2.0 * B * Lo * (c1.macs_per_row + c2.macs_per_row), bytes);
+      if (h->d_timing && h->timing_launches < rvcdec_handle::kTimingMaxLaunches)
+        p.timing = h->d_timing + (size_t)(h->timing_launches++) * h->num_sms * 16;
+      CK(launch_mrf_pair(p, h->num_sms, s)); ++h->launches;
+    }
+  return 0;
+}
+
 // conv_post + tanh can ride in the final fused-MRF launch of the last stage (not while a debug tap wants the
 // stage output in HBM).
 bool fuse_post(const rvcdec_handle* h, int mode, int i) {
@@ -442,7 +502,7 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
     if (!h->d_timing || h->timing_launches >= rvcdec_handle::kTimingMaxLaunches) return nullptr;
     return h->d_timing + (size_t)(h->timing_launches++) * h->num_sms * 16;
   };
-  p.x_in = w.xs0; p.sum = w.sum;
+  p.x_in = w.xs0; p.sum = w.sum; p.epi_warps = h->fused_epi_warps;
   p.out_f32 = last ? w.sum : nullptr;  // the last stage hands its fp32 average to conv_post in `sum`
   p.out_act = last ? nullptr : w.a0;   // the next stage consumes leaky_relu(x, 0.1) in this stage's format
   p.fmt = fs; p.out_fmt = fs;
@@ -531,7 +591,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     const NoiseLayer& nl = h->noise[i];
     // Short noise convs ride in the upsample epilogue when the stage runs the fused MRF kernel (which
     // reads the fp32 stage input only, so no activated 16-bit copy is needed).
-    const bool fuse_noise = nl.k <= 8 && use_fused_mrf(h, mode, i);
+    const bool fuse_noise = nl.k <= 8 && (use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i)));
     const bool zs_out = zs_out_stage(h, mode, i);
     if (zs_in) {
       // x = ups[i](...) as an ordinary convolution over the zero-stuffed tensor the previous stage wrote
@@ -574,6 +634,9 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     if (use_fused_mrf(h, mode, i)) {
       post_fused = last && fuse_post(h, mode, i);
       int rc = run_fused_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, zs_out, post_fused ? out : nullptr, s);
+      if (rc) return rc;
+    } else if (use_pair_mrf(h, mode, i)) {
+      int rc = run_pair_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, zs_out, s);
       if (rc) return rc;
     } else
     for (int j = 0; j < h->nk; ++j) {
@@ -962,6 +1025,13 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "zero_stuff must be 0 or 1");
     h->zero_stuff = (int)value;
     return 0;
+  }
+  if (k == "pair_noise") { h->pair_noise = value ? 1 : 0; return RVCDEC_OK; }
+  if (k == "pair_mrf") { h->pair_mrf = value ? 1 : 0; return RVCDEC_OK; }
+  if (k == "fused_epi_warps") {
+    if (value != 8 && value != 16) return fail(RVCDEC_ERR_ARG, "fused_epi_warps must be 8 or 16");
+    h->fused_epi_warps = (int)value;
+    return RVCDEC_OK;
   }
   if (k == "fused_post") { h->fused_post = value ? 1 : 0; return RVCDEC_OK; }
   if (k == "fused_mrf") {

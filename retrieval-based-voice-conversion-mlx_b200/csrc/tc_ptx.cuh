@@ -159,6 +159,28 @@ __device__ __forceinline__ void tc_st8(uint32_t taddr, const uint32_t (&r)[8]) {
                : "memory");
 }
 
+// ---- coalesced fp32 row stores ------------------------------------------------------------------
+// In the blocked-8 fp32 layout one row of a channel slice is 32 B, and an epilogue thread owns one row (TMEM
+// lane = row).  Storing it as two float4 per lane makes every STG.128 touch 32 half sectors at a 32 B stride;
+// tools/stg_bench.cu (r1u) measures 3.5 TB/s for that pattern against 5.8 TB/s when each STG.128 writes 512
+// contiguous bytes, and the epilogues of the fused kernels spent ~3.7k clk per 64 KB block in such stores.
+// Here the warp re-distributes its 32 rows first (lane l takes half l&1 of rows l>>1 and 16 + l>>1), so the two
+// stores of a slice cover rows 0-15 and 16-31 as contiguous 512 B runs.  Must be called by all 32 lanes;
+// `row0` points at the slice's row of lane 0, `ok` tells whether this lane's row is to be stored.
+__device__ __forceinline__ float4 shfl_f4(float4 v, int src) {
+  return make_float4(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src),
+                     __shfl_sync(0xffffffffu, v.z, src), __shfl_sync(0xffffffffu, v.w, src));
+}
+__device__ __forceinline__ void warp_store_rows_f32(float* row0, float4 lo, float4 hi, bool ok) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t m = __ballot_sync(0xffffffffu, ok);
+  const int sa = lane >> 1, sb = 16 + (lane >> 1);
+  const float4 alo = shfl_f4(lo, sa), ahi = shfl_f4(hi, sa), blo = shfl_f4(lo, sb), bhi = shfl_f4(hi, sb);
+  float* p = row0 + lane * 4;
+  if ((m >> sa) & 1u) *reinterpret_cast<float4*>(p) = (lane & 1) ? ahi : alo;
+  if ((m >> sb) & 1u) *reinterpret_cast<float4*>(p + 128) = (lane & 1) ? bhi : blo;
+}
+
 // Shared-memory matrix descriptor, no swizzle, K-major (PTX ISA "tcgen05 matrix descriptor"):
 //   [0,14) start address >> 4, [16,30) leading-dim byte offset >> 4 (stride between the two
 //   8-element K halves), [32,46) stride-dim byte offset >> 4 (stride between 8-row groups),

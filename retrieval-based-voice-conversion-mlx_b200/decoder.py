@@ -164,6 +164,10 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             self._handle = _lib.Handle(_lib.make_config(*self._cfg_args), idx)
             self._packed_key = None
             self._applied_fused = None
+            # tuning knobs for A/B runs: RVC_B200_OPTS="fused_epi_warps=8,fused_post=0" -> rvcdec_set_option
+            for kv in filter(None, os.environ.get("RVC_B200_OPTS", "").split(",")):
+                k, v = kv.split("=")
+                self._handle.set_option(k.strip(), int(v))
         if self.fused_mrf is not None and self.fused_mrf != self._applied_fused:
             self._handle.set_option("fused_mrf", self.fused_mrf)
             self._applied_fused = self.fused_mrf

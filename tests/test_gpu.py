@@ -206,6 +206,48 @@ def test_fused_conv_post_matches_separate_kernel(dev, fused, cfg_name, B, T, see
     assert float((y1 - y0).abs().max()) <= 2e-5, float((y1 - y0).abs().max())
 
 
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 41), ("40k", 1, 97, 42), ("48k", 3, 2, 43), ("32k", 2, 61, 44)])
+def test_fused_pair_kernel_matches_per_conv_path(dev, cfg_name, B, T, seed):
+    """rvcdec_set_option("pair_mrf"): the 128-channel stage as one launch per (conv1, conv2) pair (fp32 residual
+    in TMEM, operands in shared memory) vs one launch per conv.  Same operand rounding and fp32 accumulation;
+    only the order in which bias / residual enter the sums differs.  Covers items shorter than one tile, several
+    tiles per item and ragged tile ends."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K, "32k": O.CONFIG_32K}[cfg_name]
+    m = build_module(cfg, 5000 + seed)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        m._ensure_handle(dev).set_option("pair_mrf", 0)
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        m._handle.set_option("pair_mrf", 1)
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+    assert n1 <= n0 - 9, (n0, n1)  # 18 conv launches -> 9 pair launches (and no separate noise_add)
+    assert float((y1 - y0).abs().max()) <= 2e-3, float((y1 - y0).abs().max())
+    if T >= 50:
+        assert O.multires_logmel_corr(y1, y_ref, cfg.sr)["min"] >= FAST_BAR
+
+
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 31), ("40k", 1, 97, 32)])
+def test_fused_epilogue_warp_counts_agree(dev, cfg_name, B, T, seed):
+    """rvcdec_set_option("fused_epi_warps"): 8 or 16 epilogue warps split the accumulator columns differently
+    but compute every element with the same arithmetic; only conv_post's partial-sum order differs."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K}[cfg_name]
+    m = build_module(cfg, 4000 + seed).to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    ys = []
+    with torch.no_grad():
+        for ew in (8, 16):
+            m._ensure_handle(dev).set_option("fused_epi_warps", ew)
+            ys.append(m(xd, fd, gd, noise=nd_, mode="fast").cpu())
+    assert float((ys[0] - ys[1]).abs().max()) <= 2e-6, float((ys[0] - ys[1]).abs().max())
+
+
 def test_readme_shape_both_modes(dev):
     """BASELINE configs[2]: 13.5 s at the README benchmark shape (T=1350), real RMVPE-like contour shape."""
     cfg = O.CONFIG_48K

@@ -13,6 +13,8 @@ fm = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 dev = torch.device("cuda", 0)
 m, cfg = build_model(dev)
 m.fused_mrf = fm
+if len(sys.argv) > 4:
+    m._ensure_handle(dev).set_option("fused_epi_warps", int(sys.argv[4]))
 x, f0, g = (t.to(dev) for t in synth_batch(cfg, B, T, 1234, False))
 with torch.no_grad():
     m(x, f0, g, mode="fast")
