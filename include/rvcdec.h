@@ -120,7 +120,14 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *                2 = same kernel, one launch per stage (all ResBlocks of the MRF over one tile).
  *   "zero_stuff" 1 = (default) a stride-2 upsample that feeds a fused-MRF stage runs as an ordinary convolution
  *                    over a zero-stuffed copy of its input (written by the previous stage's last kernel);
- *                0 = polyphase form everywhere. */
+ *                0 = polyphase form everywhere.
+ *   "fused_post" 1 = (default) conv_post + tanh (hifigan_nsf.py:209-210) are computed in the epilogue of the last
+ *                    stage's final fused-MRF launch (32-channel last stage, 7 taps, "fused_mrf" 1); 0 = own kernel.
+ *   "fused_epi_warps" 8 (default) or 16 epilogue warps in the fused ResBlock kernel.
+ *   "pair_mrf"   1 = the 128-channel stage runs one launch per (conv1, conv2) pair (mrf_pair.cu: fp32 residual in
+ *                    TMEM, operand tile in smem, half the HBM traffic); 0 = (default) one launch per conv - the two
+ *                    measure the same on B200 (profiles/r1z_*), see DESIGN.md section 3.
+ *   "pair_noise" 1 = with "pair_mrf", the stage's short noise conv rides in its upsample's epilogue; 0 = (default). */
 int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value);
 
 /* Number of kernels launched by the last forward on this handle. */

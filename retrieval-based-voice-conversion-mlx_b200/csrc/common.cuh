@@ -215,6 +215,8 @@ struct FusedParams {
   // (hifigan_nsf.py:209-210) computed from the last ResBlock's epilogue instead of writing the fp32 average to HBM;
   // `margin` must then include the 3 extra rows per side that conv_post reads.
   const float* post_w;  // [7][C], or null
+  float post_wc[7 * 32]; // the same weights in the kernel's constant bank (filled by the launcher): the tail's FMAs read
+                         // them as constant operands instead of taking shared-memory bandwidth from the MMAs
   float* post_out;      // (B, L)
   float post_slope;
   FusedRB rb[FUSED_MAX_RB];

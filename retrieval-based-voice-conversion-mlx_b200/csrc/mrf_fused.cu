@@ -47,7 +47,7 @@ struct FusedCfg {
   // partial sums: double-buffered block [2][4 column groups][7][128] + the last 8 rows of the previous blocks [3][4][7][8]
   static constexpr int POST_MAIN = 2 * 4 * POST_TAPS * 128;
   static constexpr int POST_TAIL = 3 * 4 * POST_TAPS * 8;
-  static constexpr int POST_BYTES = (C == 32) ? ((POST_MAIN + POST_TAIL) * 4 + POST_TAPS * C * 4) : 0;
+  static constexpr int POST_BYTES = (C == 32) ? (POST_MAIN + POST_TAIL) * 4 : 0;
   static constexpr int SMEM_BYTES = 128 + 2 * A_BUF + S * W_SLOT + NUM_BARS * 8 + 16 + 16 + POST_BYTES;
   static_assert(USED_COLS <= 512, "TMEM budget");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
@@ -139,13 +139,10 @@ __global__ void __launch_bounds__(fused_threads(EW), 1) mrf_fused_kernel(const _
   const uint32_t dummy_bar = a1_ready + 8 * MB;  // sink for commits that release nothing
   const uint32_t tmem_slot = dummy_bar + 8;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
-  const uint32_t post_s = (tmem_slot + 16 + 15) & ~15u;  // partial-sum ring, then the conv_post weights
+  const uint32_t post_s = (tmem_slot + 16 + 15) & ~15u;  // partial-sum ring of the fused conv_post
   float* post_ring = reinterpret_cast<float*>(smem_gen + (post_s - smem_base));
   float* post_tail = post_ring + Cfg::POST_MAIN;
-  float* post_wsm = post_tail + Cfg::POST_TAIL;
   const bool do_post_any = Cfg::POST_BYTES > 0 && p.post_w != nullptr;
-  if (do_post_any)
-    for (int i = threadIdx.x; i < Cfg::POST_TAPS * C; i += FUSED_THREADS) post_wsm[i] = p.post_w[i];
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);  // provably warp-uniform role index
   const int lane = threadIdx.x & 31;
@@ -538,11 +535,10 @@ __global__ void __launch_bounds__(fused_threads(EW), 1) mrf_fused_kernel(const _
                   for (int i = 0; i < 8; ++i) o[i] = fmaxf(o[i], o[i] * p.post_slope);
 #pragma unroll
                   for (int j = 0; j < Cfg::POST_TAPS; ++j) {
-                    const float4 w0 = *reinterpret_cast<const float4*>(post_wsm + j * C + (sl0 + s8) * 8);
-                    const float4 w1 = *reinterpret_cast<const float4*>(post_wsm + j * C + (sl0 + s8) * 8 + 4);
+                    const float* wc = p.post_wc + (j * C + (sl0 + s8) * 8) % (7 * 32);  // constant bank (C == 32 here)
                     float a = pj[j];
-                    a = fmaf(o[0], w0.x, a); a = fmaf(o[1], w0.y, a); a = fmaf(o[2], w0.z, a); a = fmaf(o[3], w0.w, a);
-                    a = fmaf(o[4], w1.x, a); a = fmaf(o[5], w1.y, a); a = fmaf(o[6], w1.z, a); a = fmaf(o[7], w1.w, a);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) a = fmaf(o[i], wc[i], a);
                     pj[j] = a;
                   }
                 } else {

@@ -97,6 +97,7 @@ struct rvcdec_handle {
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
+  int max_ntile = 128;  // (r1ab: N = 128 tiles keep the accumulators double-buffered in TMEM; 256-wide tiles serialise MMA and epilogue) largest GEMM N tile the weight images are built for (takes effect at the next rvcdec_load_weights)
   int pair_noise = 0;  // 1 = the pair stage's short noise conv rides in its upsample's epilogue (no noise_add launch)
   int pair_mrf = 0;  // 1 = fused conv1+conv2 pair kernel (mrf_pair.cu) on the 128-channel stage (r1z: on par with the per-conv path, so off)
   int fused_epi_warps = 8;   // epilogue warps of the fused ResBlock kernel (8 or 16)
@@ -220,13 +221,13 @@ uint16_t to16(float v, int fmt) {
   __nv_bfloat16 h = __float2bfloat16_rn(v); uint16_t u; memcpy(&u, &h, 2); return u;
 }
 
-void finish_layer(ConvLayer& L, bool want_mma) {
+void finish_layer(ConvLayer& L, bool want_mma, int max_ntile = 256) {
   L.mask_f32.clear();
   for (int c0 = 0; c0 < L.N_total; c0 += 64) L.mask_f32.push_back(tap_mask(L, c0, 64));
   L.n_tile = 0; L.kc = 0;
   if (!want_mma) return;
   for (int nt : {256, 128, 64, 32}) {
-    if (L.N_total % nt) continue;
+    if (nt > max_ntile || L.N_total % nt) continue;
     const int kc = (nt == 32) ? 32 : 64;
     if (L.Cin % kc) continue;
     if (L.N_total / nt > MAX_NTILES) continue;
@@ -518,6 +519,7 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
   const double post_fl = post_out ? 2.0 * B * Lo * C * 7 : 0.0;
   auto arm_post = [&]() {  // the launch that completes the MRF average also produces the waveform
     p.post_w = h->d_post_w; p.post_out = post_out; p.post_slope = 0.01f; p.out_f32 = nullptr; p.margin += 3;
+    for (size_t q = 0; q < h->post_w.size() && q < sizeof(p.post_wc) / sizeof(float); ++q) p.post_wc[q] = h->post_w[q];
   };
   if (h->fused_mrf == 2) {
     double fl = 0;
@@ -848,7 +850,7 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   // tilings / 16-bit images
   h->fast_ok = true; h->fast_why.clear();
   auto fin = [&](ConvLayer& L) {
-    finish_layer(L, true);
+    finish_layer(L, true, h->max_ntile);
     if (!L.n_tile && h->fast_ok) { h->fast_ok = false; h->fast_why = L.name + " (N=" + std::to_string(L.N_total) + ", Cin=" + std::to_string(L.Cin) + ")"; }
   };
   fin(h->conv_pre);
@@ -1025,6 +1027,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "zero_stuff must be 0 or 1");
     h->zero_stuff = (int)value;
     return 0;
+  }
+  if (k == "max_ntile") {
+    if (value != 256 && value != 128) return fail(RVCDEC_ERR_ARG, "max_ntile must be 128 or 256");
+    h->max_ntile = (int)value;
+    return RVCDEC_OK;
   }
   if (k == "pair_noise") { h->pair_noise = value ? 1 : 0; return RVCDEC_OK; }
   if (k == "pair_mrf") { h->pair_mrf = value ? 1 : 0; return RVCDEC_OK; }
