@@ -83,6 +83,7 @@ struct ConvParams {
   int shift[MAX_TAPS];
   uint32_t tapmask[MAX_NTILES];  // per N tile: bit j set = tap j has non-zero weights
   int m_tiles, n_tiles;    // tiles per batch item along time, tiles along N
+  int a_stages;            // activation ring depth of the 128-wide tensor-core tiling (3; anything else = 2)
   Epilogue epi;
 };
 

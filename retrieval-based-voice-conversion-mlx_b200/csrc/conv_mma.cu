@@ -28,7 +28,7 @@
 namespace rvcdec {
 
 // ------------------------------ kernel -------------------------------------
-template <int N_TILE, int MB, int KC, int B_STAGES>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2>
 struct MmaCfg {
   static constexpr int MT = MB * 128;
   static constexpr int ACC_STAGES = (2 * MB * N_TILE <= 512) ? 2 : 1;
@@ -39,23 +39,23 @@ struct MmaCfg {
   static constexpr int A_BUF_BYTES = (KC / 8) * A_SLICE_BYTES;
   static constexpr int B_SLICE_BYTES = N_TILE * 16;
   static constexpr int B_STAGE_BYTES = (KC / 8) * B_SLICE_BYTES;
-  static constexpr int NUM_BARS = 2 + 2 + 2 * B_STAGES + 2 * ACC_STAGES;
-  static constexpr int SMEM_BYTES = 128 /*align slack*/ + 2 * A_BUF_BYTES + B_STAGES * B_STAGE_BYTES + NUM_BARS * 8 + 16;
+  static constexpr int NUM_BARS = 2 * A_STAGES + 2 * B_STAGES + 2 * ACC_STAGES;
+  static constexpr int SMEM_BYTES = 128 /*align slack*/ + A_STAGES * A_BUF_BYTES + B_STAGES * B_STAGE_BYTES + NUM_BARS * 8 + 16;
   static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
 constexpr int MMA_THREADS = 320;  // producer warp + MMA warp + 2 epilogue warpgroups
 
-template <int N_TILE, int MB, int KC, int B_STAGES>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES>
 __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES>;
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 127u) & ~127u;
   const uint32_t a_smem = smem_base;
-  const uint32_t b_smem = a_smem + 2 * Cfg::A_BUF_BYTES;
+  const uint32_t b_smem = a_smem + A_STAGES * Cfg::A_BUF_BYTES;
   const uint32_t bars = b_smem + B_STAGES * Cfg::B_STAGE_BYTES;
-  const uint32_t a_full = bars, a_empty = bars + 16, b_full = bars + 32, b_empty = b_full + 8 * B_STAGES,
+  const uint32_t a_full = bars, a_empty = bars + 8 * A_STAGES, b_full = bars + 16 * A_STAGES, b_empty = b_full + 8 * B_STAGES,
                  acc_full = b_empty + 8 * B_STAGES, acc_empty = acc_full + 8 * Cfg::ACC_STAGES;
   const uint32_t tmem_slot = acc_empty + 8 * Cfg::ACC_STAGES;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < 2; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
+    for (int i = 0; i < A_STAGES; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
     for (int i = 0; i < B_STAGES; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
     for (int i = 0; i < Cfg::ACC_STAGES; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, MMA_THREADS - 64); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -115,8 +115,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
                      a_src + (size_t)(kc * (KC / 8) + sl) * p.Lp_in * 16, a_bytes, a_full + 8 * a_stage);
         }
         __syncwarp();
-        a_stage ^= 1u;
-        if (a_stage == 0) a_phase ^= 1u;
+        if (++a_stage == A_STAGES) { a_stage = 0; a_phase ^= 1u; }
         for (int tap = 0; tap < ntaps; ++tap) {
           if (!((mask >> tap) & 1u)) continue;
           mbar_wait(b_empty + 8 * b_stage, b_phase ^ 1u);
@@ -174,8 +173,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
         }
         if (elect_one()) tc_commit(a_empty + 8 * a_stage);
         __syncwarp();
-        a_stage ^= 1u;
-        if (a_stage == 0) a_phase ^= 1u;
+        if (++a_stage == A_STAGES) { a_stage = 0; a_phase ^= 1u; }
       }
       if (elect_one()) tc_commit(acc_full + 8 * acc_stage);
       __syncwarp();
@@ -341,10 +339,10 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
   }
 }
 
-template <int N_TILE, int MB, int KC, int B_STAGES>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2>
 static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s) {
-  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES>;
-  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES>;
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES>;
+  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES>;
   {  // per-device attribute; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) return e;
@@ -368,7 +366,9 @@ bool conv_mma_supported(int n_tile, int kc) {
 
 cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms, cudaStream_t s) {
   if (n_tile == 256 && kc == 64) return launch_inst<256, 2, 64, 4>(p, num_sms, s);
-  if (n_tile == 128 && kc == 64) return launch_inst<128, 2, 64, 6>(p, num_sms, s);
+  // 128-wide tiles: option a_stages = 3 adds a third 40 KB activation stage.  Measured (profiles/r1af_*): the
+  // 128-channel stage gets 7 % SLOWER with it (229 vs 214 ms), so two stages stay the default.
+  if (n_tile == 128 && kc == 64) return p.a_stages == 3 ? launch_inst<128, 2, 64, 6, 3>(p, num_sms, s) : launch_inst<128, 2, 64, 6, 2>(p, num_sms, s);
   if (n_tile == 64 && kc == 64) return launch_inst<64, 4, 64, 4>(p, num_sms, s);
   if (n_tile == 32 && kc == 32) return launch_inst<32, 4, 32, 4>(p, num_sms, s);
   return cudaErrorInvalidValue;

@@ -98,6 +98,7 @@ struct rvcdec_handle {
   static constexpr int kTimingMaxLaunches = 32;
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
   int max_ntile = 128;  // (r1ab: N = 128 tiles keep the accumulators double-buffered in TMEM; 256-wide tiles serialise MMA and epilogue) largest GEMM N tile the weight images are built for (takes effect at the next rvcdec_load_weights)
+  int a_stages = 2;  // activation ring depth of the 128-wide conv_mma tiling (r1af: a third stage costs 7 % on the 128-channel stage)
   int pair_noise = 0;  // 1 = the pair stage's short noise conv rides in its upsample's epilogue (no noise_add launch)
   int pair_mrf = 0;  // 1 = fused conv1+conv2 pair kernel (mrf_pair.cu) on the 128-channel stage (r1z: on par with the per-conv path, so off)
   int fused_epi_warps = 8;   // epilogue warps of the fused ResBlock kernel (8 or 16)
@@ -370,6 +371,7 @@ int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, 
   p.N_total = L.N_total; p.ntaps = L.ntaps; p.halo = L.halo;
   for (int t = 0; t < L.ntaps; ++t) p.shift[t] = L.shift[t];
   p.epi = epi;
+  p.a_stages = h->a_stages;
   if (mode == 0) {
     p.w = L.d_wf;
     for (size_t i = 0; i < L.mask_f32.size() && i < (size_t)MAX_NTILES; ++i) p.tapmask[i] = L.mask_f32[i];
@@ -1031,6 +1033,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
   if (k == "max_ntile") {
     if (value != 256 && value != 128) return fail(RVCDEC_ERR_ARG, "max_ntile must be 128 or 256");
     h->max_ntile = (int)value;
+    return RVCDEC_OK;
+  }
+  if (k == "a_stages") {
+    if (value != 2 && value != 3) return fail(RVCDEC_ERR_ARG, "a_stages must be 2 or 3");
+    h->a_stages = (int)value;
     return RVCDEC_OK;
   }
   if (k == "pair_noise") { h->pair_noise = value ? 1 : 0; return RVCDEC_OK; }
