@@ -127,7 +127,13 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *   "pair_mrf"   1 = the 128-channel stage runs one launch per (conv1, conv2) pair (mrf_pair.cu: fp32 residual in
  *                    TMEM, operand tile in smem, half the HBM traffic); 0 = (default) one launch per conv - the two
  *                    measure the same on B200 (profiles/r1z_*), see DESIGN.md section 3.
- *   "pair_noise" 1 = with "pair_mrf", the stage's short noise conv rides in its upsample's epilogue; 0 = (default). */
+ *   "pair_noise" 1 = with "pair_mrf", the stage's short noise conv rides in its upsample's epilogue; 0 = (default).
+ *   "max_ntile"  128 (default) or 256: widest GEMM N tile of the tensor-core weight images; takes effect at the next
+ *                    rvcdec_load_weights.  128 keeps the accumulators double-buffered in TMEM (profiles/r1ab_*).
+ *   "a_stages"   2 (default) or 3 activation stages in the 128-wide tiling (3 measured slower, profiles/r1af_*).
+ *   "mrf_items"  0 (default) = every launch of a per-conv MRF stage covers all items; N > 0 = launches run over groups
+ *                    of items whose 16-bit hand-off tensor stays under N MiB (bit-identical results; measured slower on
+ *                    30 s chunks, profiles/r1ag_*). */
 int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value);
 
 /* Number of kernels launched by the last forward on this handle. */

@@ -99,6 +99,8 @@ struct rvcdec_handle {
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
   int max_ntile = 128;  // (r1ab: N = 128 tiles keep the accumulators double-buffered in TMEM; 256-wide tiles serialise MMA and epilogue) largest GEMM N tile the weight images are built for (takes effect at the next rvcdec_load_weights)
   int a_stages = 2;  // activation ring depth of the 128-wide conv_mma tiling (r1af: a third stage costs 7 % on the 128-channel stage)
+  int mrf_items = 0;  // > 0: the per-conv MRF path runs its launches over groups of items whose 16-bit hand-off tensor
+                      // stays under this many MiB (L2 reuse between consecutive launches); 0 = all items at once
   int pair_noise = 0;  // 1 = the pair stage's short noise conv rides in its upsample's epilogue (no noise_add launch)
   int pair_mrf = 0;  // 1 = fused conv1+conv2 pair kernel (mrf_pair.cu) on the 128-channel stage (r1z: on par with the per-conv path, so off)
   int fused_epi_warps = 8;   // epilogue warps of the fused ResBlock kernel (8 or 16)
@@ -642,36 +644,58 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     } else if (use_pair_mrf(h, mode, i)) {
       int rc = run_pair_mrf(h, g_mrf.c_str(), i, w, B, Lo, Lpo, fs, last, zs_out, s);
       if (rc) return rc;
-    } else
-    for (int j = 0; j < h->nk; ++j) {
-      for (int m = 0; m < h->nd; ++m) {
-        const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
-        const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
-        {
-          Epilogue e{};
-          e.bias = c1.d_bias; e.scale = 1.f; e.slope = 0.1f;
-          e.out_act = w.a1; e.act_fmt = fs; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
-          int rc = run_conv(h, g_mrf.c_str(), c1, mode, fs, m == 0 ? w.a0 : w.a2, B, Lo, e, s);
-          if (rc) return rc;
-        }
-        {
-          Epilogue e{};
-          e.bias = c2.d_bias; e.slope = 0.1f; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
-          e.res = (m == 0) ? w.xs0 : w.xr;
-          if (m < h->nd - 1) {
-            e.scale = 1.f; e.out_f32 = w.xr; e.out_act = w.a2; e.act_fmt = fs;
-          } else {
-            e.scale = 1.f / (float)h->nk;
-            e.sum_in = (j == 0) ? nullptr : w.sum;
-            if (j < h->nk - 1 || last) e.out_f32 = w.sum;
-            if (j == h->nk - 1 && !last) {
-              // next stage consumes leaky_relu(x, 0.1) in ITS operand format; a0 is dead by now
-              e.out_act = w.a0; e.act_fmt = fmt_stage(mode, i);
-              if (zs_out) { e.act_zs = 2; e.Lp_act = padded_rows(2 * Lo); }
+    } else {
+      // Per-conv path.  With "mrf_items" = G > 0 (fast mode) the 18 launches run over G items at a time, so the
+      // 16-bit tensors handed from one launch to the next (conv1 -> conv2 -> next conv1) are small enough to be
+      // re-read out of L2 instead of HBM.  Groups go in DESCENDING item order: the last launch of a group writes
+      // the stage output into a0, possibly in the wider zero-stuffed geometry, i.e. over the a0 inputs of
+      // higher-numbered items only - which are consumed by then.
+      const size_t ab = act_bytes(mode == 0 ? ACT_F32 : fs);
+      const size_t item_el = (size_t)C * Lpo;
+      int G = B;  // "mrf_items" = budget in MiB for one 16-bit hand-off tensor of a group
+      if (mode != 0 && h->mrf_items > 0)
+        G = (int)std::min<size_t>((size_t)B, std::max<size_t>(1, ((size_t)h->mrf_items << 20) / (item_el * ab)));
+      const int Lp_zs = padded_rows(2 * Lo);
+      for (int b0 = ((B - 1) / G) * G; b0 >= 0; b0 -= G) {
+        const int nb = std::min(G, B - b0);
+        auto A = [&](void* p_) { return (void*)((uint8_t*)p_ + (size_t)b0 * item_el * ab); };
+        auto F = [&](float* p_) { return p_ + (size_t)b0 * item_el; };
+        for (int j = 0; j < h->nk; ++j) {
+          for (int m = 0; m < h->nd; ++m) {
+            const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
+            const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
+            {
+              Epilogue e{};
+              e.bias = c1.d_bias; e.scale = 1.f; e.slope = 0.1f;
+              e.out_act = A(w.a1); e.act_fmt = fs; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
+              int rc = run_conv(h, g_mrf.c_str(), c1, mode, fs, m == 0 ? A(w.a0) : A(w.a2), nb, Lo, e, s);
+              if (rc) return rc;
+            }
+            {
+              Epilogue e{};
+              e.bias = c2.d_bias; e.slope = 0.1f; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
+              e.res = (m == 0) ? F(w.xs0) : F(w.xr);
+              if (m < h->nd - 1) {
+                e.scale = 1.f; e.out_f32 = F(w.xr); e.out_act = A(w.a2); e.act_fmt = fs;
+              } else {
+                e.scale = 1.f / (float)h->nk;
+                e.sum_in = (j == 0) ? nullptr : F(w.sum);
+                if (j < h->nk - 1 || last) e.out_f32 = F(w.sum);
+                if (j == h->nk - 1 && !last) {
+                  // next stage consumes leaky_relu(x, 0.1) in ITS operand format; a0 is dead by now
+                  e.act_fmt = fmt_stage(mode, i);
+                  if (zs_out) {
+                    e.act_zs = 2; e.Lp_act = Lp_zs;
+                    e.out_act = (uint8_t*)w.a0 + (size_t)b0 * C * Lp_zs * ab;
+                  } else {
+                    e.out_act = A(w.a0);
+                  }
+                }
+              }
+              int rc = run_conv(h, g_mrf.c_str(), c2, mode, fs, A(w.a1), nb, Lo, e, s);
+              if (rc) return rc;
             }
           }
-          int rc = run_conv(h, g_mrf.c_str(), c2, mode, fs, w.a1, B, Lo, e, s);
-          if (rc) return rc;
         }
       }
     }
@@ -1038,6 +1062,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
   if (k == "a_stages") {
     if (value != 2 && value != 3) return fail(RVCDEC_ERR_ARG, "a_stages must be 2 or 3");
     h->a_stages = (int)value;
+    return RVCDEC_OK;
+  }
+  if (k == "mrf_items") {
+    if (value < 0 || value > (1 << 20)) return fail(RVCDEC_ERR_ARG, "mrf_items out of range");
+    h->mrf_items = (int)value;
     return RVCDEC_OK;
   }
   if (k == "pair_noise") { h->pair_noise = value ? 1 : 0; return RVCDEC_OK; }

@@ -232,6 +232,28 @@ def test_fused_pair_kernel_matches_per_conv_path(dev, cfg_name, B, T, seed):
         assert O.multires_logmel_corr(y1, y_ref, cfg.sr)["min"] >= FAST_BAR
 
 
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 5, 60, 51), ("40k", 3, 97, 52)])
+def test_item_grouped_launches_are_bit_identical(dev, cfg_name, B, T, seed):
+    """rvcdec_set_option("mrf_items"): the per-conv MRF stages launched over groups of items (descending order, so
+    the stage output written into a0 - zero-stuffed on the way into a stride-2 upsample - never lands on an input
+    that is still to be read) compute exactly what one launch over all items computes."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K}[cfg_name]
+    m = build_module(cfg, 6000 + seed).to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        h = m._ensure_handle(dev)
+        h.set_option("mrf_items", 0)
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        h.set_option("mrf_items", 1)  # 1 MiB budget: groups of 1-2 items at these sizes
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+        h.set_option("mrf_items", 0)
+    assert n1 > n0, (n0, n1)
+    assert torch.equal(y0, y1)
+
+
 @pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 31), ("40k", 1, 97, 32)])
 def test_fused_epilogue_warp_counts_agree(dev, cfg_name, B, T, seed):
     """rvcdec_set_option("fused_epi_warps"): 8 or 16 epilogue warps split the accumulator columns differently
