@@ -132,15 +132,25 @@ def test_v2_48k_tilings(built_lib):
     sd = golden_state(d, cfg)
     h = _lib.Handle(_lib.make_config(*cfg.ctor_args(), cfg.gin_channels, cfg.sr), 0)
     h.pack_host(sd)
-    expect = {"conv_pre": (192, 512, 256, 64), "ups.0": (512, 3072, 256, 64), "ups.1": (256, 1280, 256, 64),
-              "ups.2": (128, 128, 128, 64), "ups.3": (64, 64, 64, 64), "resblocks.0.convs1.0": (256, 256, 256, 64),
+    # default: 128-wide N tiles (accumulators double-buffered in TMEM)
+    expect = {"conv_pre": (192, 512, 128, 64), "ups.0": (512, 3072, 128, 64), "ups.1": (256, 1280, 128, 64),
+              "ups.2": (128, 128, 128, 64), "ups.3": (64, 64, 64, 64), "resblocks.0.convs1.0": (256, 256, 128, 64),
               "resblocks.3.convs1.0": (128, 128, 128, 64), "resblocks.6.convs2.1": (64, 64, 64, 64),
               "resblocks.9.convs1.2": (32, 32, 32, 32)}
     for layer, (Cin, N, nt, kc) in expect.items():
         meta = h.packed(layer, 5)
         assert (int(meta[0]), int(meta[1]), int(meta[6]), int(meta[7])) == (Cin, N, nt, kc), layer
     m0 = h.packed("ups.0", 3)
-    assert len(m0) == 12 and all(bin(int(v)).count("1") == 2 for v in m0)  # exactly 2 of 3 shifts per phase
+    assert len(m0) == 24 and all(bin(int(v)).count("1") == 2 for v in m0)  # exactly 2 of 3 shifts per phase half
+    # option max_ntile = 256 (takes effect at the next pack): the widest tiles the kernels support
+    h.set_option("max_ntile", 256)
+    h.pack_host(sd)
+    for layer, (Cin, N, nt, kc) in {"conv_pre": (192, 512, 256, 64), "ups.0": (512, 3072, 256, 64),
+                                     "resblocks.0.convs1.0": (256, 256, 256, 64), "resblocks.3.convs1.0": (128, 128, 128, 64)}.items():
+        meta = h.packed(layer, 5)
+        assert (int(meta[0]), int(meta[1]), int(meta[6]), int(meta[7])) == (Cin, N, nt, kc), layer
+    m0 = h.packed("ups.0", 3)
+    assert len(m0) == 12 and all(bin(int(v)).count("1") == 2 for v in m0)
     h.close()
 
 
