@@ -152,16 +152,18 @@ def peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
-def measured_traffic(B, T):
+def measured_traffic(B, T, steps, spans):
     """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
     (profiles/roofline_traffic.json, written by tools/launch_share.py --traffic).  The capture runs fewer chunks
-    than the bench (ncu replays every kernel ~40x); traffic of these kernels is linear in the number of rows,
-    so it is scaled by rows(bench) / rows(capture) and the note says so."""
+    than a bench launch covers (ncu replays every kernel ~40x); traffic of these kernels is linear in the number of
+    rows, so it is scaled by frames per launch (bench) / frames per launch (capture).  A bench step may take several
+    passes over the batch (workspace cap), hence frames per launch = B*T*steps*launches_per_pass / launches timed."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))
-        scale = (B * T) / float(t["chunks"] * t["frames_per_chunk"])
-        return t["dram_bytes_per_launch"] * scale, (f"ncu dram__bytes_read+write per launch, {t['source']} ({t['chunks']} chunks), "
-                                                    f"x{scale:g} rows")
+        frames_per_launch = B * T * steps * t["launches"] / float(spans)
+        scale = frames_per_launch / float(t["chunks"] * t["frames_per_chunk"])
+        return t["dram_bytes_per_launch"] * scale, (f"ncu dram__bytes_read+write per launch, {t['source']} ({t['chunks']} chunks per launch), "
+                                                    f"x{scale:.3g} ({frames_per_launch:.0f} frames per launch here)")
     except Exception as e:  # noqa: BLE001
         return None, f"no capture: {e}"
 
@@ -299,7 +301,7 @@ def run_ours(args):
                 "avg_launch_ms": dom["ms"] / spans, "flops_per_launch": dom["flops"] / spans,
                 "hbm_gbs": dom_l["hbm_gbs"], "hbm_frac": dom_l["hbm_frac"]}
     if args.mode != "fp32":
-        roof["traffic"], roof["traffic_note"] = measured_traffic(B, T)
+        roof["traffic"], roof["traffic_note"] = measured_traffic(B, T, args.steps, spans)
         roof["algorithmic_bytes_per_launch"] = dom["bytes"] / spans
     total_tflops = 2 * MMAC_PER_FRAME * T * B * args.steps / (ms * 1e-3) / 1e12
     cpu = None
