@@ -106,7 +106,9 @@ int rvcdec_forward(rvcdec_handle* h, const float* x, const float* f0, const floa
 /* Same call with HOST buffers (pinned memory recommended): copies inputs to the
  * device, decodes, copies the waveform back, and returns after the copy has
  * completed.  `noise` may be NULL (in-kernel draws).  Scratch is owned by the
- * handle and capped at `max_device_bytes` (0 = default cap). This is the call
+ * handle and capped at `max_device_bytes` (0 = automatic: 60 % of the free device memory, and a large batch is
+ * cut into at least three passes so that the copies of one pass overlap the kernels of its neighbours: inputs
+ * and waveform are double-buffered on two copy streams). This is the call
  * the reference's pipeline makes per chunk (rvc/infer/pipeline.py:366-371:
  * net_g.infer(...)[0][0,0].data.cpu().float().numpy()). */
 int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const float* g,

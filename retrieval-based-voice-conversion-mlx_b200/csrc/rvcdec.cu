@@ -117,6 +117,9 @@ struct rvcdec_handle {
   std::vector<int64_t> prof_launches;
   // forward_host state
   cudaStream_t stream = nullptr;
+  // host-buffer entry point: copies of pass i+1 / i-1 overlap the kernels of pass i
+  cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
   void* hbuf = nullptr;
   size_t hbuf_bytes = 0;
 };
@@ -767,6 +770,11 @@ void rvcdec_destroy(rvcdec_handle* h) {
     if (h->d_timing) cudaFree(h->d_timing);
     if (h->hbuf) cudaFree(h->hbuf);
     if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
+    if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
+    for (int i = 0; i < 2; ++i)
+      for (cudaEvent_t e : {h->ev_in[i], h->ev_comp[i], h->ev_out[i]})
+        if (e) cudaEventDestroy(e);
   }
   delete h;
 }
@@ -961,40 +969,74 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
   if (rc) return rc;
   CK(cudaSetDevice(h->device));
   if (!h->stream) CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  if (max_device_bytes == 0) max_device_bytes = (size_t)24 << 30;
+  if (!h->h2d_stream) {
+    CK(cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      CK(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&h->ev_comp[i], cudaEventDisableTiming));
+      CK(cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming));
+    }
+  }
+  const bool auto_cap = (max_device_bytes == 0);
+  if (auto_cap) {  // 60 % of what is free now (plus what this handle already holds)
+    size_t free_b = 0, total_b = 0;
+    CK(cudaMemGetInfo(&free_b, &total_b));
+    max_device_bytes = (size_t)(0.6 * (double)(free_b + h->hbuf_bytes));
+  }
   const size_t n = (size_t)T * h->upp;
   const int Cx = h->cfg.initial_channel, G = h->cfg.gin_channels;
+  // two sets of input / output staging buffers (double buffering across passes) + one workspace
   auto io_bytes = [&](int b) {
     return align_up((size_t)b * Cx * T * 4, 256) + align_up((size_t)b * T * 4, 256) + align_up((size_t)b * std::max(G, 1) * 4, 256) +
            (noise ? align_up((size_t)b * n * 4, 256) : 0) + align_up((size_t)b * n * 4, 256);
   };
   int Bm = B;
-  while (Bm > 1 && io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes > max_device_bytes) Bm = (Bm + 1) / 2;
-  const size_t need = io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes;
+  // at least three passes on a large batch, so that most of the host<->device traffic hides behind kernels
+  if (auto_cap && B >= 6) Bm = (B + 2) / 3;
+  while (Bm > 1 && 2 * io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes > max_device_bytes) Bm = (Bm + 1) / 2;
+  while (Bm < B && !(auto_cap && B >= 6 && Bm >= (B + 2) / 3) &&
+         2 * io_bytes(Bm + 1) + carve(h, nullptr, Bm + 1, T, mode).bytes <= max_device_bytes) ++Bm;
+  const size_t need = 2 * io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes;
   if (need > h->hbuf_bytes) {
-    if (h->hbuf) { CK(cudaFree(h->hbuf)); h->hbuf = nullptr; h->hbuf_bytes = 0; }
+    if (h->hbuf) { CK(cudaDeviceSynchronize()); CK(cudaFree(h->hbuf)); h->hbuf = nullptr; h->hbuf_bytes = 0; }
     CK(cudaMalloc(&h->hbuf, need));
     h->hbuf_bytes = need;
   }
   uint8_t* p = (uint8_t*)h->hbuf;
-  float* dx = (float*)p; p += align_up((size_t)Bm * Cx * T * 4, 256);
-  float* df0 = (float*)p; p += align_up((size_t)Bm * T * 4, 256);
-  float* dg = (float*)p; p += align_up((size_t)Bm * std::max(G, 1) * 4, 256);
-  float* dnz = nullptr;
-  if (noise) { dnz = (float*)p; p += align_up((size_t)Bm * n * 4, 256); }
-  float* dout = (float*)p; p += align_up((size_t)Bm * n * 4, 256);
+  float *dx[2], *df0[2], *dg[2], *dnz[2] = {nullptr, nullptr}, *dout[2];
+  for (int s2 = 0; s2 < 2; ++s2) {
+    dx[s2] = (float*)p; p += align_up((size_t)Bm * Cx * T * 4, 256);
+    df0[s2] = (float*)p; p += align_up((size_t)Bm * T * 4, 256);
+    dg[s2] = (float*)p; p += align_up((size_t)Bm * std::max(G, 1) * 4, 256);
+    if (noise) { dnz[s2] = (float*)p; p += align_up((size_t)Bm * n * 4, 256); }
+    dout[s2] = (float*)p; p += align_up((size_t)Bm * n * 4, 256);
+  }
   void* ws = p;
   h->launches = 0;
-  for (int b0 = 0; b0 < B; b0 += Bm) {
+  int pass = 0;
+  for (int b0 = 0; b0 < B; b0 += Bm, ++pass) {
     const int nb = std::min(Bm, B - b0);
-    CK(cudaMemcpyAsync(dx, x + (size_t)b0 * Cx * T, (size_t)nb * Cx * T * 4, cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemcpyAsync(df0, f0 + (size_t)b0 * T, (size_t)nb * T * 4, cudaMemcpyHostToDevice, h->stream));
-    if (g && G) CK(cudaMemcpyAsync(dg, g + (size_t)b0 * G, (size_t)nb * G * 4, cudaMemcpyHostToDevice, h->stream));
-    if (noise) CK(cudaMemcpyAsync(dnz, noise + b0 * n, nb * n * 4, cudaMemcpyHostToDevice, h->stream));
-    rc = forward_pass(h, dx, df0, (g && G) ? dg : nullptr, dnz, seed, (uint64_t)b0, dout, ws, nb, T, mode, h->stream);
+    const int s2 = pass & 1;
+    // inputs of this pass: the staging set is free once the pass that used it two passes ago has run
+    if (pass >= 2) CK(cudaStreamWaitEvent(h->h2d_stream, h->ev_comp[s2], 0));
+    CK(cudaMemcpyAsync(dx[s2], x + (size_t)b0 * Cx * T, (size_t)nb * Cx * T * 4, cudaMemcpyHostToDevice, h->h2d_stream));
+    CK(cudaMemcpyAsync(df0[s2], f0 + (size_t)b0 * T, (size_t)nb * T * 4, cudaMemcpyHostToDevice, h->h2d_stream));
+    if (g && G) CK(cudaMemcpyAsync(dg[s2], g + (size_t)b0 * G, (size_t)nb * G * 4, cudaMemcpyHostToDevice, h->h2d_stream));
+    if (noise) CK(cudaMemcpyAsync(dnz[s2], noise + b0 * n, nb * n * 4, cudaMemcpyHostToDevice, h->h2d_stream));
+    CK(cudaEventRecord(h->ev_in[s2], h->h2d_stream));
+    // kernels: need the inputs, and the output staging buffer drained by the copy of two passes ago
+    CK(cudaStreamWaitEvent(h->stream, h->ev_in[s2], 0));
+    if (pass >= 2) CK(cudaStreamWaitEvent(h->stream, h->ev_out[s2], 0));
+    rc = forward_pass(h, dx[s2], df0[s2], (g && G) ? dg[s2] : nullptr, dnz[s2], seed, (uint64_t)b0, dout[s2], ws, nb, T, mode, h->stream);
     if (rc) return rc;
-    CK(cudaMemcpyAsync(out + b0 * n, dout, nb * n * 4, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaEventRecord(h->ev_comp[s2], h->stream));
+    // waveform of this pass back to the host while the next pass computes
+    CK(cudaStreamWaitEvent(h->d2h_stream, h->ev_comp[s2], 0));
+    CK(cudaMemcpyAsync(out + b0 * n, dout[s2], nb * n * 4, cudaMemcpyDeviceToHost, h->d2h_stream));
+    CK(cudaEventRecord(h->ev_out[s2], h->d2h_stream));
   }
+  CK(cudaStreamSynchronize(h->d2h_stream));
   CK(cudaStreamSynchronize(h->stream));
   return 0;
 }

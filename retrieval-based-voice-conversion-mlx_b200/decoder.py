@@ -125,7 +125,9 @@ class HiFiGANNSFGenerator(torch.nn.Module):
 
         self.mode = os.environ.get("RVC_B200_MODE", "fast")
         self.noise_source = os.environ.get("RVC_B200_NOISE", "torch")  # "torch" | "philox"
-        self.max_workspace_bytes = int(os.environ.get("RVC_B200_MAX_WORKSPACE", str(32 << 30)))
+        # scratch cap per forward; 0 = automatic: 70 % of the device memory that is free when the scratch is (re)allocated,
+        # so a batch that fits runs in ONE pass (4 passes over 128 x 30 s chunks cost 2 %, profiles/r1am_*)
+        self.max_workspace_bytes = int(os.environ.get("RVC_B200_MAX_WORKSPACE", "0"))
         self._cfg_args = (initial_channel, list(resblock_kernel_sizes), [list(d) for d in resblock_dilation_sizes],
                           list(upsample_rates), upsample_initial_channel, list(upsample_kernel_sizes), gin_channels, sr)
         self._gin = gin_channels
@@ -222,7 +224,11 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             else:
                 g = g.reshape(B, self._gin).contiguous().float()
         need = h.workspace_bytes(B, T, m)
-        ws = self._get_workspace(min(need, max(self.max_workspace_bytes, h.workspace_bytes(1, T, m))), x.device)
+        cap = self.max_workspace_bytes
+        if cap <= 0:
+            have = self._workspace.numel() if (self._workspace is not None and self._workspace.device == x.device) else 0
+            cap = need if have >= need else int(0.7 * (torch.cuda.mem_get_info(x.device)[0] + have))
+        ws = self._get_workspace(min(need, max(cap, h.workspace_bytes(1, T, m))), x.device)
         out = ops.nsf_hifigan_decode(x.contiguous().float(), f0.contiguous().float(), g, noise, ws, h.ptr.value, m, self.upp, seed)
         self.last_launch_count = h.launch_count()
         return out.unsqueeze(1)
