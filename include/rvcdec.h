@@ -130,6 +130,9 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *                    TMEM, operand tile in smem, half the HBM traffic); 0 = (default) one launch per conv - the two
  *                    measure the same on B200 (profiles/r1z_*), see DESIGN.md section 3.
  *   "pair_noise" 1 = with "pair_mrf", the stage's short noise conv rides in its upsample's epilogue; 0 = (default).
+ *   "fused_split_k" fused ResBlock chains as two launches (dilations 1,3 -> fp32 -> dilation 5), which halves the rows
+ *                    recomputed at tile edges: N > 0 = chains with kernel size >= N; 0 = (default) chains whose recompute
+ *                    exceeds a quarter of the tile (the k = 11 chain of the 64-channel stage); -1 = never.
  *   "max_ntile"  128 (default) or 256: widest GEMM N tile of the tensor-core weight images; takes effect at the next
  *                    rvcdec_load_weights.  128 keeps the accumulators double-buffered in TMEM (profiles/r1ab_*).
  *   "a_stages"   2 (default) or 3 activation stages in the 128-wide tiling (3 measured slower, profiles/r1af_*).

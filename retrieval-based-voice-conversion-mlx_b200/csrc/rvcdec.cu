@@ -101,6 +101,8 @@ struct rvcdec_handle {
   int a_stages = 2;  // activation ring depth of the 128-wide conv_mma tiling (r1af: a third stage costs 7 % on the 128-channel stage)
   int mrf_items = 0;  // > 0: the per-conv MRF path runs its launches over groups of items whose 16-bit hand-off tensor
                       // stays under this many MiB (L2 reuse between consecutive launches); 0 = all items at once
+  int fused_split_k = 0;  // fused ResBlock chains as two launches (less tile-edge recompute): > 0 = those with kernel size >= this,
+                          // 0 = automatic (chains whose recompute exceeds a quarter of the tile), -1 = never
   int pair_noise = 0;  // 1 = the pair stage's short noise conv rides in its upsample's epilogue (no noise_add launch)
   int pair_mrf = 0;  // 1 = fused conv1+conv2 pair kernel (mrf_pair.cu) on the 128-channel stage (r1z: on par with the per-conv path, so off)
   int fused_epi_warps = 8;   // epilogue warps of the fused ResBlock kernel (8 or 16)
@@ -539,8 +541,55 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
   } else {
     for (int j = 0; j < h->nk; ++j) {
       p.n_rb = 1;
-      p.margin = fill_rb(p.rb[0], j);
       const bool fin = (j == h->nk - 1);
+      // split when asked for by kernel size ("fused_split_k"), or by default when the chain's tile-edge recompute
+      // exceeds a quarter of the tile (64-channel stage, k = 11: 120 of 384 rows; A/B profiles/r1ap_*)
+      int chain_margin = 0;
+      for (int m = 0; m < h->nd; ++m) chain_margin += layer(j, m, 0).halo + layer(j, m, 1).halo;
+      const bool split = h->nd >= 2 && (h->fused_split_k > 0 ? h->cfg.resblock_kernel_sizes[j] >= h->fused_split_k
+                                                             : (h->fused_split_k == 0 && 8 * chain_margin > mrf_fused_tile_rows(C)));
+      if (split) {
+        // Long chains in two launches: dilations [0, nd-1) -> xr (fp32), then the last dilation.  Each launch
+        // recomputes only its own receptive field at the tile edges (k = 11: 30 + 30 rows instead of 60 per side,
+        // i.e. 84 % instead of 69 % useful rows at 384-row tiles) for one extra fp32 round trip through HBM.
+        const int ndA = h->nd - 1;
+        double flA = 0, flB = 0;
+        int marginA = 0;
+        for (int m = 0; m < ndA; ++m) {
+          const ConvLayer& c1 = layer(j, m, 0);
+          const ConvLayer& c2 = layer(j, m, 1);
+          const int d1 = c1.ntaps > 1 ? c1.shift[1] - c1.shift[0] : 1, d2 = c2.ntaps > 1 ? c2.shift[1] - c2.shift[0] : 1;
+          p.rb[0].c1[m] = FusedConv{c1.d_wp[fs == ACT_BF16 ? 1 : 0], c1.d_bias, c1.ntaps, d1};
+          p.rb[0].c2[m] = FusedConv{c2.d_wp[fs == ACT_BF16 ? 1 : 0], c2.d_cbias, c2.ntaps, d2};  // cumulative over m
+          marginA += c1.halo + c2.halo;
+          flA += 2.0 * B * Lo * (c1.macs_per_row + c2.macs_per_row);
+        }
+        FusedParams q = p;
+        q.nd = ndA; q.margin = marginA; q.rb[0].sum_in = 0; q.rb[0].is_last = 0;
+        q.x_in = w.xs0; q.sum = w.xr; q.scale = 1.f; q.post_w = nullptr;
+        MARK(group, flA, el * 8);
+        q.timing = next_timing();
+        CK(launch_mrf_fused(q, h->num_sms, s)); ++h->launches;
+        {
+          const ConvLayer& c1 = layer(j, ndA, 0);
+          const ConvLayer& c2 = layer(j, ndA, 1);
+          const int d1 = c1.ntaps > 1 ? c1.shift[1] - c1.shift[0] : 1, d2 = c2.ntaps > 1 ? c2.shift[1] - c2.shift[0] : 1;
+          p.rb[0].c1[0] = FusedConv{c1.d_wp[fs == ACT_BF16 ? 1 : 0], c1.d_bias, c1.ntaps, d1};
+          p.rb[0].c2[0] = FusedConv{c2.d_wp[fs == ACT_BF16 ? 1 : 0], c2.d_bias, c2.ntaps, d2};  // xr already carries the earlier biases
+          p.margin = c1.halo + c2.halo;
+          flB = 2.0 * B * Lo * (c1.macs_per_row + c2.macs_per_row);
+        }
+        p.nd = 1; p.rb[0].sum_in = (j > 0); p.rb[0].is_last = fin;
+        p.x_in = w.xr;
+        if (fin && post_out) arm_post();
+        MARK(group, flB + (fin ? post_fl : 0.0),
+             el * (4 + (j > 0 ? 4 : 0) + (fin ? (last ? (post_out ? 0 : 4) : act_bytes(fs)) : 4)) + (fin && post_out ? 4.0 * B * Lo : 0.0));
+        p.timing = next_timing();
+        CK(launch_mrf_fused(p, h->num_sms, s)); ++h->launches;
+        p.nd = h->nd; p.x_in = w.xs0;
+        continue;
+      }
+      p.margin = fill_rb(p.rb[0], j);
       if (fin && post_out) arm_post();
       MARK(group, flops_rb(j) + (fin ? post_fl : 0.0),
            el * (4 + (j > 0 ? 4 : 0) + (fin ? (last ? (post_out ? 0 : 4) : act_bytes(fs)) : 4)) + (fin && post_out ? 4.0 * B * Lo : 0.0));
@@ -1109,6 +1158,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
   if (k == "mrf_items") {
     if (value < 0 || value > (1 << 20)) return fail(RVCDEC_ERR_ARG, "mrf_items out of range");
     h->mrf_items = (int)value;
+    return RVCDEC_OK;
+  }
+  if (k == "fused_split_k") {
+    if (value < -1 || value > 64) return fail(RVCDEC_ERR_ARG, "fused_split_k out of range");
+    h->fused_split_k = (int)value;
     return RVCDEC_OK;
   }
   if (k == "pair_noise") { h->pair_noise = value ? 1 : 0; return RVCDEC_OK; }

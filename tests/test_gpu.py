@@ -254,6 +254,29 @@ def test_item_grouped_launches_are_bit_identical(dev, cfg_name, B, T, seed):
     assert torch.equal(y0, y1)
 
 
+@pytest.mark.parametrize("split_k", [7, 11])
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 61), ("40k", 1, 97, 62), ("48k", 1, 2, 63)])
+def test_split_fused_chains_agree(dev, split_k, cfg_name, B, T, seed):
+    """rvcdec_set_option("fused_split_k"): ResBlock chains of the fused stages with kernel size >= split_k run as two
+    launches (dilations 1,3 -> fp32 -> dilation 5) instead of one.  Same operands, same fp32 accumulation; only the
+    point at which the conv2 biases enter the residual differs."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K}[cfg_name]
+    m = build_module(cfg, 7000 + seed).to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        h = m._ensure_handle(dev)
+        h.set_option("fused_split_k", -1)  # never split
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        h.set_option("fused_split_k", split_k)
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+        h.set_option("fused_split_k", 0)  # default: automatic
+    assert n1 == n0 + (2 if split_k == 11 else 4), (n0, n1)  # two fused stages x ResBlocks with k >= split_k
+    assert float((y1 - y0).abs().max()) <= 2e-3, float((y1 - y0).abs().max())
+
+
 @pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 31), ("40k", 1, 97, 32)])
 def test_fused_epilogue_warp_counts_agree(dev, cfg_name, B, T, seed):
     """rvcdec_set_option("fused_epi_warps"): 8 or 16 epilogue warps split the accumulator columns differently
