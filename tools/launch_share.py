@@ -2,7 +2,8 @@
 decoder pass, and (optionally) turn an ncu --set full summary (tools/ncu_summary.py) into the per-launch DRAM
 traffic record bench.py reports as roofline.traffic.
     python tools/launch_share.py gpurun_out/x_launches.csv > profiles/x_launch_share.csv
-    python tools/launch_share.py --traffic profiles/x_summary.csv 'conv_mma_kernel<128' CHUNKS > profiles/roofline_traffic.json"""
+    python tools/launch_share.py --traffic profiles/x_summary.csv 'conv_mma_kernel<128' CHUNKS [FIRST_ID LAST_ID] > profiles/roofline_traffic.json
+(the id range picks the launches of one layer group, e.g. 21 38 = the 18 ResBlock convs of the 128-channel stage)"""
 import csv, json, re, sys
 from collections import OrderedDict
 
@@ -28,9 +29,9 @@ def shares(path):
     w.writerow(["TOTAL", len(rows), f"{tot:.3f}", "1.0"])
 
 
-def traffic(path, pat, chunks):
+def traffic(path, pat, chunks, first=None, last=None):
     rows = list(csv.DictReader(open(path)))
-    sel = [r for r in rows if pat in r["kernel"]]
+    sel = [r for r in rows if pat in r["kernel"] and (first is None or first <= int(r["id"]) <= last)]
     b = [(float(r["dram_rd_MB"]) + float(r["dram_wr_MB"])) * 1e6 for r in sel]
     print(json.dumps({"kernel": pat, "launches": len(sel), "chunks": int(chunks), "frames_per_chunk": 3000,
                       "dram_bytes_per_launch": sum(b) / len(b), "ms_per_launch_under_ncu": sum(float(r["ms"]) for r in sel) / len(sel),
@@ -39,6 +40,6 @@ def traffic(path, pat, chunks):
 
 if __name__ == "__main__":
     if sys.argv[1] == "--traffic":
-        traffic(sys.argv[2], sys.argv[3], sys.argv[4])
+        traffic(sys.argv[2], sys.argv[3], sys.argv[4], *(int(v) for v in sys.argv[5:7]))
     else:
         shares(sys.argv[1])
