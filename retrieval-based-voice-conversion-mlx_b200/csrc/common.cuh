@@ -69,6 +69,11 @@ struct Epilogue {
   // flipped kernel), which gives it the coalesced "output row == accumulator row" epilogue.
   int act_zs;   // 0 / 1 = dense
   int Lp_act;   // padded rows of out_act when act_zs > 1
+  // 1 = phase-major polyphase upsample (tensor-core back-end only): the GEMM columns are ordered
+  // (channel group of 16, half of the phases, slice of the group, phase within the half, channel), see
+  // conv_mma.cu "phase-major"; requires an even `up` and cout % 16 == 0.  A fused noise conv must then have
+  // stride 4, 8 taps, padding 2.
+  int pm;
 };
 
 // One convolution as an implicit GEMM:  D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]

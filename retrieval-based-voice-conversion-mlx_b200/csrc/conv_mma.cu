@@ -28,9 +28,17 @@
 namespace rvcdec {
 
 // ------------------------------ kernel -------------------------------------
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0>
 struct MmaCfg {
   static constexpr int MT = MB * 128;
+  // PM = 1: phase-major polyphase upsample tile (see the PM epilogue below): N_TILE = PH phases x 2 slices x 8
+  // channels; every epilogue warp owns a staging area of 32 x (2*PH*32 + 16) bytes for the warp-level transpose
+  static constexpr int PH = N_TILE / 16;
+  static constexpr int STG_LANE = PH * 32 + 16;
+  static constexpr int STG_WARP = PM ? 32 * STG_LANE : 0;
+  static constexpr int STG_BYTES = 16 * STG_WARP;
+  static constexpr int CONST_BYTES = PM ? (256 + 8 * 128) * 4 : 0;  // per-channel bias (<= 256) + noise-conv taps [8][<= 128]
+  static constexpr int THREADS = PM ? 64 + 16 * 32 : 64 + 8 * 32;  // producer warp + MMA warp + epilogue warps
   static constexpr int ACC_STAGES = (2 * MB * N_TILE <= 512) ? 2 : 1;
   static constexpr int ACC_COLS = ACC_STAGES * MB * N_TILE;
   static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128 : ACC_COLS <= 256 ? 256 : 512;
@@ -40,21 +48,23 @@ struct MmaCfg {
   static constexpr int B_SLICE_BYTES = N_TILE * 16;
   static constexpr int B_STAGE_BYTES = (KC / 8) * B_SLICE_BYTES;
   static constexpr int NUM_BARS = 2 * A_STAGES + 2 * B_STAGES + 2 * ACC_STAGES;
-  static constexpr int SMEM_BYTES = 128 /*align slack*/ + A_STAGES * A_BUF_BYTES + B_STAGES * B_STAGE_BYTES + NUM_BARS * 8 + 16;
+  static constexpr int SMEM_BYTES = 128 /*align slack*/ + A_STAGES * A_BUF_BYTES + B_STAGES * B_STAGE_BYTES + STG_BYTES + CONST_BYTES + NUM_BARS * 8 + 16;
   static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 };
 
 constexpr int MMA_THREADS = 320;  // producer warp + MMA warp + 2 epilogue warpgroups
 
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES>
-__global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES>;
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES, int PM>
+__global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 127u) & ~127u;
   const uint32_t a_smem = smem_base;
   const uint32_t b_smem = a_smem + A_STAGES * Cfg::A_BUF_BYTES;
-  const uint32_t bars = b_smem + B_STAGES * Cfg::B_STAGE_BYTES;
+  const uint32_t stg_smem = b_smem + B_STAGES * Cfg::B_STAGE_BYTES;
+  const uint32_t const_smem = stg_smem + Cfg::STG_BYTES;
+  const uint32_t bars = const_smem + Cfg::CONST_BYTES;
   const uint32_t a_full = bars, a_empty = bars + 8 * A_STAGES, b_full = bars + 16 * A_STAGES, b_empty = b_full + 8 * B_STAGES,
                  acc_full = b_empty + 8 * B_STAGES, acc_empty = acc_full + 8 * Cfg::ACC_STAGES;
   const uint32_t tmem_slot = acc_empty + 8 * Cfg::ACC_STAGES;
@@ -68,7 +78,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
   if (threadIdx.x == 0) {
     for (int i = 0; i < A_STAGES; ++i) { mbar_init(a_full + 8 * i, 1); mbar_init(a_empty + 8 * i, 1); }
     for (int i = 0; i < B_STAGES; ++i) { mbar_init(b_full + 8 * i, 1); mbar_init(b_empty + 8 * i, 1); }
-    for (int i = 0; i < Cfg::ACC_STAGES; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, MMA_THREADS - 64); }
+    for (int i = 0; i < Cfg::ACC_STAGES; ++i) { mbar_init(acc_full + 8 * i, 1); mbar_init(acc_empty + 8 * i, Cfg::THREADS - 64); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -77,6 +87,20 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
                  "r"((uint32_t)Cfg::TMEM_COLS)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if constexpr (PM != 0) {
+    // per-channel bias (+ noise-conv bias) and the noise-conv taps live in shared memory: the strided har reads of
+    // the epilogue sweep the small L1 (most of it is carved out as shared memory), so uniform global loads of these
+    // constants kept missing it (profiles/r1bc: the first use of each was a long-scoreboard stall)
+    float* cst = reinterpret_cast<float*>(smem_gen + (const_smem - smem_base));
+    const Epilogue& e = p.epi;
+    const int PHc = Cfg::PH;
+    for (int c = threadIdx.x; c < e.cout; c += Cfg::THREADS) {
+      const int n_new = (c >> 4) * 2 * N_TILE + (((c >> 3) & 1) * PHc) * 8 + (c & 7);
+      cst[c] = __ldg(e.bias + n_new) + (e.nz_har ? __ldg(e.nz_bias + c) : 0.f);
+    }
+    if (e.nz_har)
+      for (int i = threadIdx.x; i < 8 * e.cout; i += Cfg::THREADS) cst[256 + i] = __ldg(e.nz_w + i);
   }
   tc_fence_before();
   __syncthreads();
@@ -199,6 +223,138 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
       mbar_wait(acc_full + 8 * as, (acc_it / Cfg::ACC_STAGES) & 1u);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (MB * N_TILE);
+      if constexpr (PM != 0) {
+        // ---- phase-major polyphase upsample (ConvTranspose1d, hifigan_nsf.py:198) [+ noise_convs[i](har), :199] ----
+        // N tile n_tile = (channel group cg of 16) * 2 + half; its columns are ordered (slice sl of the group, phase rr
+        // of this half, channel c): column (sl*PH + rr)*8 + c is output row t_in*up + half*PH + rr of slice 2*cg + sl.
+        // A thread (= input row) therefore owns PH consecutive output rows of a slice (PH*32 B in fp32), and a warp
+        // owns 32 such runs.  The warp transposes them through its shared-memory staging area so that every global
+        // store instruction writes consecutive 16 B (fp32) / 8 B (16-bit) pieces: the former one-phase-per-tile
+        // scatter wrote 32 B pieces 32*up bytes apart and ran at 1.3 TB/s (profiles/r1at id 20).
+        // 16 epilogue warps: (TMEM lane quarter q) x (row block mb) x (slice sl); the epilogue is a long chain of
+        // dependent loads and FMAs per warp, so the warps are what hides its latency (profiles/r1bb: 8 warps with
+        // both slices each ran at ~10 clk per instruction).
+        constexpr int PH = Cfg::PH;
+        constexpr int NC = PH * 8;       // columns (= floats per thread) of one slice
+        constexpr int NZS = 4, NZK = 8;  // the fused noise conv: stride 4, 8 taps, pad 2 (checked by the host)
+        constexpr int NH = NZS * PH + NZK - NZS;
+        const int cg = n_tile >> 1, half = n_tile & 1;
+        const int sl = (warp - 2) >> 3;
+        float* stg = reinterpret_cast<float*>(smem_gen + (stg_smem - smem_base) + (size_t)(warp - 2) * Cfg::STG_WARP);
+#pragma unroll 1
+        for (int mb = wg & 1; mb < MB; mb += 2) {
+          const int tb = t0 + mb * 128 + q * 32;
+          const int t_in = tb + lane;
+          const bool valid = t_in < p.L_in;
+          const int co0 = cg * 16 + sl * 8;
+          float hv[NH];
+          if (e.nz_har) {
+            // the warp's har window (32 lanes x up*4 samples, contiguous) -> staging with coalesced 8 B loads, lane
+            // rows padded by 2 words (stride 42 / 50 words: conflict-free 8 B reads), then each lane takes its NH samples
+            const int lane_words = e.up * NZS;                 // 40 / 48
+            const int pairs_per_lane = lane_words >> 1;        // 20 / 24
+            const float* hb = e.nz_har + (size_t)b * e.nz_src;
+            const int s_w = (tb * e.up + half * PH) * NZS - (NZK - NZS) / 2;  // even
+            const int n_pairs = (31 * lane_words + NH + 1) >> 1;
+            for (int m = lane; m < n_pairs; m += 32) {
+              const int sidx = s_w + 2 * m;
+              float2 h2 = make_float2(0.f, 0.f);
+              if (sidx >= 0 && sidx < e.nz_src) h2 = __ldg(reinterpret_cast<const float2*>(hb + sidx));
+              *reinterpret_cast<float2*>(stg + 2 * m + 2 * (m / pairs_per_lane)) = h2;
+            }
+            __syncwarp();
+            const float2* mine = reinterpret_cast<const float2*>(stg + lane * (lane_words + 2));
+#pragma unroll
+            for (int j = 0; j < NH / 2; ++j) {
+              const float2 h2 = mine[j];
+              hv[2 * j] = h2.x; hv[2 * j + 1] = h2.y;
+            }
+            __syncwarp();
+          }
+          const float* cst = reinterpret_cast<const float*>(smem_gen + (const_smem - smem_base));
+          const float4 b0 = *reinterpret_cast<const float4*>(cst + co0), b1 = *reinterpret_cast<const float4*>(cst + co0 + 4);
+          float a[NC];
+          {
+            const uint32_t t_col = t_acc + mb * N_TILE + sl * NC;
+            uint32_t r[32];
+            tc_ld32(t_col, r);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) a[i] = __uint_as_float(r[i]);
+            if constexpr (NC - 32 == 8) {
+              uint32_t r8[8];
+              tc_ld8(t_col + 32, r8);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) a[32 + i] = __uint_as_float(r8[i]);
+            } else {
+              uint32_t r16[16];
+              tc_ld16(t_col + 32, r16);
+#pragma unroll
+              for (int i = 0; i < 16; ++i) a[32 + i] = __uint_as_float(r16[i]);
+            }
+            static_assert(NC == 40 || NC == 48, "phase-major tiles: 5 or 6 phases per half");
+          }
+#pragma unroll
+          for (int rr = 0; rr < PH; ++rr) {
+            float* v = &a[rr * 8];
+            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+          }
+          if (e.nz_har) {
+#pragma unroll
+            for (int j = 0; j < NZK; ++j) {
+              const float4* wp4 = reinterpret_cast<const float4*>(cst + 256 + j * e.cout + co0);
+              const float4 w0 = wp4[0], w1 = wp4[1];
+#pragma unroll
+              for (int rr = 0; rr < PH; ++rr) {
+                float* v = &a[rr * 8];
+                const float hh = hv[NZS * rr + j];
+                v[0] = fmaf(hh, w0.x, v[0]); v[1] = fmaf(hh, w0.y, v[1]); v[2] = fmaf(hh, w0.z, v[2]); v[3] = fmaf(hh, w0.w, v[3]);
+                v[4] = fmaf(hh, w1.x, v[4]); v[5] = fmaf(hh, w1.y, v[5]); v[6] = fmaf(hh, w1.z, v[6]); v[7] = fmaf(hh, w1.w, v[7]);
+              }
+            }
+          }
+          // registers -> staging (lane stride STG_LANE = 11 / 13 x 16 B: conflict-free quarter-warp stores)
+          {
+            float4* mine = reinterpret_cast<float4*>(stg + lane * (Cfg::STG_LANE / 4));
+#pragma unroll
+            for (int i = 0; i < NC / 4; ++i) mine[i] = make_float4(a[4 * i], a[4 * i + 1], a[4 * i + 2], a[4 * i + 3]);
+          }
+          __syncwarp();
+          // staging -> global, consecutive lanes = consecutive 16 B pieces of the warp's 32 runs
+          const size_t row0 = ((size_t)b * (e.cout >> 3) + cg * 2 + sl) * e.Lp_out + PADL + (size_t)half * PH;
+          float4 f[2 * PH];
+#pragma unroll
+          for (int it = 0; it < 2 * PH; ++it) {
+            const int P = it * 32 + lane;
+            const int ln = P / (2 * PH), pp = P - ln * (2 * PH);
+            f[it] = *reinterpret_cast<const float4*>(stg + ln * (Cfg::STG_LANE / 4) + pp * 4);
+          }
+#pragma unroll
+          for (int it = 0; it < 2 * PH; ++it) {
+            const int P = it * 32 + lane;
+            const int ln = P / (2 * PH), pp = P - ln * (2 * PH);
+            if (tb + ln < p.L_in) {
+              const size_t el = (row0 + (size_t)(tb + ln) * e.up) * 8 + pp * 4;
+              const float4 ff = f[it];
+              if (e.out_f32) *reinterpret_cast<float4*>(e.out_f32 + el) = ff;
+              if (e.out_act) {
+                uint2 pk;
+                if (e.act_fmt == ACT_F16) {
+                  __half2 h0 = __floats2half2_rn(fmaxf(ff.x, ff.x * e.slope), fmaxf(ff.y, ff.y * e.slope));
+                  __half2 h1 = __floats2half2_rn(fmaxf(ff.z, ff.z * e.slope), fmaxf(ff.w, ff.w * e.slope));
+                  pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
+                } else {
+                  __nv_bfloat162 h0 = __floats2bfloat162_rn(fmaxf(ff.x, ff.x * e.slope), fmaxf(ff.y, ff.y * e.slope));
+                  __nv_bfloat162 h1 = __floats2bfloat162_rn(fmaxf(ff.z, ff.z * e.slope), fmaxf(ff.w, ff.w * e.slope));
+                  pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
+                }
+                *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(e.out_act) + el) = pk;
+              }
+            }
+          }
+          __syncwarp();
+        }
+      } else {
 #pragma unroll 1
       for (int item = wg; item < ITEMS; item += 2) {
         const int mb = item / CH;
@@ -323,6 +479,7 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
           }
         }
       }
+      }
       tc_fence_before();
       mbar_arrive(acc_empty + 8 * as);
       ++acc_it;
@@ -339,10 +496,11 @@ __global__ void __launch_bounds__(MMA_THREADS, 1) conv_mma_kernel(const __grid_c
   }
 }
 
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0>
 static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s) {
-  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES>;
-  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES>;
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
+  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
+  if ((PM != 0) != (p.epi.pm != 0)) return cudaErrorInvalidValue;
   {  // per-device attribute; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) return e;
@@ -355,16 +513,19 @@ static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s)
   const long long total = (long long)q.B * q.m_tiles * q.n_tiles;
   if (total <= 0 || total > 0x7fffffffLL) return cudaErrorInvalidValue;
   const int grid = (int)(total < num_sms ? total : num_sms);
-  kern<<<grid, MMA_THREADS, Cfg::SMEM_BYTES, s>>>(q);
+  kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, s>>>(q);
   return cudaGetLastError();
 }
 
 bool conv_mma_supported(int n_tile, int kc) {
   return (n_tile == 256 && kc == 64) || (n_tile == 128 && kc == 64) || (n_tile == 64 && kc == 64) ||
-         (n_tile == 32 && kc == 32);
+         (n_tile == 32 && kc == 32) || (n_tile == 80 && kc == 64) || (n_tile == 96 && kc == 64);
 }
 
 cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms, cudaStream_t s) {
+  // phase-major upsample tiles (rate 10 / 12): 5 / 6 phases x 16 channels, accumulators double-buffered
+  if (n_tile == 80 && kc == 64) return launch_inst<80, 2, 64, 5, 2, 1>(p, num_sms, s);
+  if (n_tile == 96 && kc == 64) return launch_inst<96, 2, 64, 3, 2, 1>(p, num_sms, s);
   if (n_tile == 256 && kc == 64) return launch_inst<256, 2, 64, 4>(p, num_sms, s);
   // 128-wide tiles: option a_stages = 3 adds a third 40 KB activation stage.  Measured (profiles/r1af_*): the
   // 128-channel stage gets 7 % SLOWER with it (229 vs 214 ms), so two stages stay the default.

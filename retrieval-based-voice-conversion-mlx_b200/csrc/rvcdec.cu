@@ -80,6 +80,7 @@ struct rvcdec_handle {
   ConvLayer conv_pre;
   std::vector<ConvLayer> ups;
   std::vector<ConvLayer> ups_zs;  // stride-2 upsamples as ordinary convs over a zero-stuffed input (n_tile == 0: unused)
+  std::vector<ConvLayer> ups_pm;  // rate-10 / 12 upsamples with phase-major GEMM columns (coalesced epilogue; n_tile == 0: unused)
   std::vector<ConvLayer> rbconv;  // index ((i*nk + j)*nd + m)*2 + which
   std::vector<NoiseLayer> noise;
   std::vector<float> post_w;  // [k][C]
@@ -96,6 +97,7 @@ struct rvcdec_handle {
   long long* d_timing = nullptr;
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
+  int ups_pm_on = 1;   // 1 = upsamples that have a phase-major image use it (and carry the stage's 8-tap noise conv + 16-bit copy)
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
   int max_ntile = 128;  // (r1ab: N = 128 tiles keep the accumulators double-buffered in TMEM; 256-wide tiles serialise MMA and epilogue) largest GEMM N tile the weight images are built for (takes effect at the next rvcdec_load_weights)
   int a_stages = 2;  // activation ring depth of the 128-wide conv_mma tiling (r1af: a third stage costs 7 % on the 128-channel stage)
@@ -229,11 +231,16 @@ uint16_t to16(float v, int fmt) {
   __nv_bfloat16 h = __float2bfloat16_rn(v); uint16_t u; memcpy(&u, &h, 2); return u;
 }
 
-void finish_layer(ConvLayer& L, bool want_mma, int max_ntile = 256) {
+void finish_layer(ConvLayer& L, bool want_mma, int max_ntile = 256, int force_ntile = 0) {
   L.mask_f32.clear();
   for (int c0 = 0; c0 < L.N_total; c0 += 64) L.mask_f32.push_back(tap_mask(L, c0, 64));
   L.n_tile = 0; L.kc = 0;
   if (!want_mma) return;
+  if (force_ntile) {
+    if (L.N_total % force_ntile == 0 && L.Cin % 64 == 0 && L.N_total / force_ntile <= MAX_NTILES && conv_mma_supported(force_ntile, 64)) {
+      L.n_tile = force_ntile; L.kc = 64;
+    }
+  } else
   for (int nt : {256, 128, 64, 32}) {
     if (nt > max_ntile || L.N_total % nt) continue;
     const int kc = (nt == 32) ? 32 : 64;
@@ -304,6 +311,27 @@ bool use_pair_mrf(const rvcdec_handle* h, int mode, int i);
 bool zs_out_stage(const rvcdec_handle* h, int mode, int i) {
   if (mode == 0 || !h->zero_stuff || i + 1 >= h->nups) return false;
   return h->cfg.upsample_rates[i + 1] == 2 && h->ups_zs[i + 1].n_tile != 0 && use_fused_mrf(h, mode, i + 1);
+}
+
+// Stage i's upsample runs the phase-major tensor-core image (fast modes, dense input).
+bool use_ups_pm(const rvcdec_handle* h, int mode, int i) {
+  if (mode == 0 || !h->ups_pm_on || i < 0 || i >= h->nups || !h->ups_pm[i].n_tile) return false;
+  if (i > 0 && zs_out_stage(h, mode, i - 1)) return false;
+  return true;
+}
+// ... and also carries the stage's noise conv (8 taps, stride 4) in its epilogue.
+bool pm_noise(const rvcdec_handle* h, int mode, int i) {
+  if (!use_ups_pm(h, mode, i)) return false;
+  const NoiseLayer& nl = h->noise[i];
+  return nl.k == 8 && nl.stride == 4 && nl.pad == 2;
+}
+// ... and, when the stage runs the per-conv MRF path, writes the activated 16-bit operand copy (a0) as well, which
+// replaces the noise_add pass.  The upsample then must not read its input out of a0: the previous stage (per-conv
+// path, all items in one group, dense output) leaves its output in a2 instead.
+bool pm_act(const rvcdec_handle* h, int mode, int i) {
+  if (!pm_noise(h, mode, i) || use_fused_mrf(h, mode, i) || use_pair_mrf(h, mode, i)) return false;
+  if (i == 0) return true;
+  return !use_fused_mrf(h, mode, i - 1) && !use_pair_mrf(h, mode, i - 1) && h->mrf_items == 0 && !zs_out_stage(h, mode, i - 1);
 }
 
 struct Workspace {
@@ -649,8 +677,12 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     const NoiseLayer& nl = h->noise[i];
     // Short noise convs ride in the upsample epilogue when the stage runs the fused MRF kernel (which
     // reads the fp32 stage input only, so no activated 16-bit copy is needed).
-    const bool fuse_noise = nl.k <= 8 && (use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i)));
+    const bool fuse_other = nl.k <= 8 && (use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i)));
+    const bool pm = use_ups_pm(h, mode, i) && (!fuse_other || pm_noise(h, mode, i)), pma = pm_act(h, mode, i);
+    const bool pmn = pm_noise(h, mode, i) && (pma || use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i)));
+    const bool fuse_noise = pmn || (nl.k <= 8 && (use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i))));
     const bool zs_out = zs_out_stage(h, mode, i);
+    const bool next_in_a2 = (i + 1 < h->nups) && i + 1 >= 1 && pm_act(h, mode, i + 1);  // see pm_act
     if (zs_in) {
       // x = ups[i](...) as an ordinary convolution over the zero-stuffed tensor the previous stage wrote
       CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fmt_in), B, h->ch[i - 1], Lo, Lpo, s)); ++h->launches;
@@ -665,18 +697,24 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
       if (rc) return rc;
     } else
     {  // x = ups[i](leaky_relu(x, 0.1))  (hifigan_nsf.py:185,198); the activation was applied by the producer
+      const ConvLayer& UL = pm ? h->ups_pm[i] : h->ups[i];
       Epilogue e{};
-      e.bias = h->ups[i].d_bias; e.scale = 1.f; e.slope = 0.1f;
+      e.bias = UL.d_bias; e.scale = 1.f; e.slope = 0.1f; e.pm = pm ? 1 : 0;
       e.out_f32 = w.xs0; e.up = u; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
       if (fuse_noise) {  // ... + noise_convs[i](har_source)  (:199)
         e.nz_har = w.har; e.nz_w = nl.d_w; e.nz_bias = nl.d_bias;
         e.nz_k = nl.k; e.nz_stride = nl.stride; e.nz_pad = nl.pad; e.nz_src = T * h->upp;
       }
-      int rc = run_conv(h, g_ups.c_str(), h->ups[i], mode, fmt_in, stage_in, B, L, e, s);
+      if (pma) {  // leaky_relu(x, 0.1) as the ResBlocks' first operand (what noise_add wrote)
+        if (stage_in == w.a0) return fail(RVCDEC_ERR_STATE, "phase-major upsample %d would overwrite its own input", i);
+        e.out_act = w.a0; e.act_fmt = fs;
+      }
+      int rc = run_conv(h, g_ups.c_str(), UL, mode, fmt_in, stage_in, B, L, e, s);
       if (rc) return rc;
     }
     // (after the upsample has read the previous stage's tensor out of a0: new geometry, new pad rows)
-    if ((fuse_noise || (zs_in && nl.k <= 8)) && !zs_out) { CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
+    if (pma) { CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
+    else if ((fuse_noise || (zs_in && nl.k <= 8)) && !zs_out) { CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
     if (!fuse_noise && !(zs_in && nl.k <= 8)) {
       MARK(g_noise.c_str(), 2.0 * B * Lo * C * nl.k, (double)B * Lo * C * (8 + act_bytes(fs)));
       CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches;
@@ -740,7 +778,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
                     e.act_zs = 2; e.Lp_act = Lp_zs;
                     e.out_act = (uint8_t*)w.a0 + (size_t)b0 * C * Lp_zs * ab;
                   } else {
-                    e.out_act = A(w.a0);
+                    e.out_act = next_in_a2 ? A(w.a2) : A(w.a0);  // a2's last reader (this pair's conv1) is done
                   }
                 }
               }
@@ -752,7 +790,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
       }
     }
     if (stop == 20 + i) { MARK(nullptr, 0, 0); return 0; }
-    stage_in = w.a0;
+    stage_in = next_in_a2 ? w.a2 : w.a0;
     fmt_in = fs;
     L = Lo;
     zs_in = zs_out;
@@ -859,6 +897,7 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   }
   h->ups.assign(h->nups, ConvLayer());
   h->ups_zs.assign(h->nups, ConvLayer());
+  h->ups_pm.assign(h->nups, ConvLayer());
   h->noise.assign(h->nups, NoiseLayer());
   h->rbconv.assign((size_t)h->nups * h->nk * h->nd * 2, ConvLayer());
   for (int i = 0; i < h->nups; ++i) {
@@ -888,6 +927,28 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
     }
     h->ups[i].bias.resize((size_t)u * C);
     for (int r = 0; r < u; ++r) memcpy(&h->ups[i].bias[(size_t)r * C], v.data(), sizeof(float) * C);
+    if (u % 2 == 0 && C % 16 == 0 && conv_mma_supported(u / 2 * 16, 64) && u / 2 * 16 != 64 && Cin % 64 == 0) {
+      // Phase-major column order: tile (co/16, half) holds the phases r = half*PH + rr of 16 channels as
+      // column ((co/8 % 2)*PH + rr)*8 + co%8.  Each half of the phases reads two of the three input shifts, so the
+      // per-tile tap masks keep skipping the all-zero weight blocks.
+      const ConvLayer& S = h->ups[i];
+      ConvLayer& P = h->ups_pm[i];
+      const int PH = u / 2, NT = PH * 16;
+      P.name = un + "(phase-major)";
+      P.Cin = S.Cin; P.N_total = S.N_total; P.cout = C; P.up = u; P.ntaps = S.ntaps; P.halo = S.halo;
+      P.macs_per_row = S.macs_per_row;
+      for (int t = 0; t < S.ntaps; ++t) P.shift[t] = S.shift[t];
+      P.wf.assign(S.wf.size(), 0.f);
+      P.bias.resize((size_t)u * C);
+      for (int r = 0; r < u; ++r)
+        for (int co = 0; co < C; ++co) {
+          const int n_new = ((co / 16) * 2 + r / PH) * NT + (((co / 8) % 2) * PH + r % PH) * 8 + co % 8;
+          P.bias[n_new] = v[co];
+          for (int t = 0; t < S.ntaps; ++t)
+            for (int ci = 0; ci < Cin; ++ci)
+              P.wf[((size_t)t * Cin + ci) * P.N_total + n_new] = S.wf[((size_t)t * Cin + ci) * S.N_total + r * C + co];
+        }
+    }
     // noise_convs (:142-154): kernel 2s, stride s, pad s/2 (1/1/0 when s == 1)
     int stride = 1;
     for (int q = i + 1; q < h->nups; ++q) stride *= c.upsample_rates[q];
@@ -939,6 +1000,7 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   fin(h->conv_pre);
   for (auto& L : h->ups) fin(L);
   for (auto& L : h->ups_zs) if (L.ntaps) finish_layer(L, true);
+  for (auto& L : h->ups_pm) if (L.ntaps) { finish_layer(L, true, 256, L.up / 2 * 16); L.wf.clear(); L.wf.shrink_to_fit(); }
   for (auto& L : h->rbconv) fin(L);
   return 0;
 }
@@ -959,6 +1021,7 @@ int rvcdec_load_weights(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t 
   if ((rc = upload_layer(h, h->conv_pre))) return rc;
   for (auto& L : h->ups) if ((rc = upload_layer(h, L))) return rc;
   for (auto& L : h->ups_zs) if (L.ntaps && (rc = upload_layer(h, L))) return rc;
+  for (auto& L : h->ups_pm) if (L.n_tile && (rc = upload_layer(h, L))) return rc;
   for (auto& L : h->rbconv) if ((rc = upload_layer(h, L))) return rc;
   for (auto& nl : h->noise) {
     if ((rc = upload(h, nl.w, &nl.d_w))) return rc;
@@ -1140,6 +1203,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     h->timing_launches = 0;
     return 0;
   }
+  if (k == "ups_pm") {
+    if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "ups_pm must be 0 or 1");
+    h->ups_pm_on = (int)value;
+    return 0;
+  }
   if (k == "zero_stuff") {
     if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "zero_stuff must be 0 or 1");
     h->zero_stuff = (int)value;
@@ -1220,7 +1288,7 @@ int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_
       if (need(n)) return RVCDEC_ERR_ARG;
       if (i == h->nups - 1) CK(launch_unpack(w.sum, ACT_F32, dst, B, h->ch[i], L, padded_rows(L), s));  // pre-activation
       else if (zs_out_stage(h, mode, i)) CK(launch_unpack(w.a0, fmt_stage(mode, i), dst, B, h->ch[i], L, padded_rows(2 * L), s, 2));  // zero-stuffed rows
-      else CK(launch_unpack(w.a0, fmt_stage(mode, i), dst, B, h->ch[i], L, padded_rows(L), s));          // leaky_relu(.,0.1)
+      else CK(launch_unpack((i + 1 < h->nups && pm_act(h, mode, i + 1)) ? w.a2 : w.a0, fmt_stage(mode, i), dst, B, h->ch[i], L, padded_rows(L), s));  // leaky_relu(.,0.1)
       return n;
     }
   }
@@ -1251,6 +1319,7 @@ int64_t rvcdec_debug_packed(const rvcdec_handle* h, const char* layer, int32_t k
   const std::string nm = layer;
   if (nm == h->conv_pre.name) L = &h->conv_pre;
   for (auto& u : h->ups) if (u.name == nm) L = &u;
+  for (auto& u : h->ups_pm) if (u.ntaps && u.name == nm) L = &u;
   for (auto& r : h->rbconv) if (r.name == nm) L = &r;
   if (!L) return fail(RVCDEC_ERR_ARG, "unknown layer '%s'", layer);
   const void* src = nullptr;

@@ -182,6 +182,40 @@ def test_fused_mrf_variants_agree(dev, fused, zs, cfg_name, B, T, seed):
     assert float((y - y0).abs().max()) <= 2e-3, float((y - y0).abs().max())
 
 
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 31), ("40k", 2, 97, 32), ("48k", 1, 3, 33), ("48k", 3, 43, 34), ("32k", 1, 61, 35)])
+def test_phase_major_upsample_matches_phase_scatter(dev, cfg_name, B, T, seed):
+    """rvcdec_set_option("ups_pm"): the rate-10 / 12 upsamples with phase-major GEMM columns (warp-transposed, coalesced
+    epilogue that also carries stage 1's 8-tap noise conv and writes the activated 16-bit operand) against the
+    one-phase-per-tile scatter epilogue + noise_add pass.  Same operand rounding and tap order, so the stage inputs agree
+    to fp32 rounding; ragged lengths (T*12 not a multiple of 32 or 128) exercise the partial last tiles."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K, "32k": O.CONFIG_32K}[cfg_name]
+    m = build_module(cfg, 3000 + seed)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        m(xd, fd, gd, noise=nd_, mode="fast")
+        m._handle.set_option("ups_pm", 0)
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        t0 = layer_taps(m, cfg, xd, fd, gd, nd_, "fast")
+        m._handle.set_option("ups_pm", 1)
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+        t1 = layer_taps(m, cfg, xd, fd, gd, nd_, "fast")
+    if cfg_name != "32k":
+        assert n1 < n0, (n0, n1)  # stage 1 lost its noise_add launch
+    for k in ("stage0.in", "stage0.out", "stage1.in", "stage1.out"):
+        scale = float(t0[k].abs().max())
+        assert float((t1[k] - t0[k]).abs().max()) <= 2e-5 * max(scale, 1.0) + (2e-2 * scale if k.endswith(".out") else 0), k
+    assert float((t1["stage1.in"] - t0["stage1.in"]).abs().max()) <= 1e-5
+    corr = O.multires_logmel_corr(y1, y_ref, cfg.sr)
+    assert corr["min"] >= FAST_BAR, corr
+    assert float((y1 - y0).abs().max()) <= 2e-3, float((y1 - y0).abs().max())
+
+
 @pytest.mark.parametrize("fused", [1])
 @pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 21), ("40k", 1, 97, 22), ("48k", 1, 3, 23), ("32k", 3, 61, 24)])
 def test_fused_conv_post_matches_separate_kernel(dev, fused, cfg_name, B, T, seed):

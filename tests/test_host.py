@@ -154,6 +154,38 @@ def test_v2_48k_tilings(built_lib):
     h.close()
 
 
+def test_phase_major_upsample_images(built_lib):
+    """The rate-10 / 12 upsamples also get a phase-major tensor-core image: tile (co/16, half of the phases), columns
+    (slice, phase, channel); it is the standard polyphase image with permuted columns, and every tile still skips one of
+    the three input shifts."""
+    from rvc_b200 import _lib
+
+    d, cfg = load_golden("v2_48k_B2_T24")
+    sd = golden_state(d, cfg)
+    h = _lib.Handle(_lib.make_config(*cfg.ctor_args(), cfg.gin_channels, cfg.sr), 0)
+    h.pack_host(sd)
+    for i, (u, C) in enumerate([(12, 256), (10, 128)]):
+        base, pm = f"ups.{i}", f"ups.{i}(phase-major)"
+        Cin, N, cout, up, ntaps, halo, n_tile, kc = (int(v) for v in h.packed(pm, 5))
+        PH = u // 2
+        assert (N, cout, up, n_tile, kc) == (u * C, C, u, PH * 16, 64)
+        wf = torch.from_numpy(h.packed(base, 0).reshape(ntaps, Cin, N))
+        r = torch.arange(u).repeat_interleave(C)
+        co = torch.arange(C).repeat(u)
+        n_new = ((co // 16) * 2 + r // PH) * n_tile + (((co // 8) % 2) * PH + r % PH) * 8 + co % 8
+        assert sorted(n_new.tolist()) == list(range(N))
+        img = _decode16(h.packed(pm, 4), "bf16").reshape(N // n_tile, ntaps, Cin // kc, kc // 8, n_tile, 8)
+        back = img.permute(1, 2, 3, 5, 0, 4).reshape(ntaps, Cin, N)
+        assert torch.equal(back[:, :, n_new], wf.bfloat16().float())
+        bias = torch.from_numpy(h.packed(pm, 6))
+        assert torch.equal(bias[n_new], torch.from_numpy(h.packed(base, 6)))
+        masks = h.packed(pm, 3)
+        assert len(masks) == N // n_tile and all(bin(int(v)).count("1") == 2 for v in masks)
+    with pytest.raises(Exception):
+        h.packed("ups.2(phase-major)", 5)
+    h.close()
+
+
 def test_chunk_plan_matches_reference_geometry():
     from rvc_b200 import chunking as ch
 

@@ -8,7 +8,7 @@ for o in "$@"; do
   echo "[$o] rc=$?"; python - <<PY
 import json
 d=json.load(open("gpurun_out/${tag}_ab$i.json"))
-print(round(d["value"],1), round(d["ms_per_step"],2), d["clocks"]["sm_mhz"], {k: round(v["ms_per_step"],2) for k,v in d["layers"].items() if k.startswith("mrf")})
+print(round(d["value"],1), round(d["ms_per_step"],2), d["clocks"]["sm_mhz"], {k: round(v["ms_per_step"],2) for k,v in d["layers"].items() if k.startswith("mrf")}, {k: round(v["ms_per_step"],2) for k,v in d["layers"].items() if not k.startswith("mrf")})
 PY
   i=$((i+1))
 done
