@@ -27,6 +27,24 @@
 
 namespace rvcdec {
 
+// packed fp32x2 arithmetic (sm_100 FADD2 / FFMA2): halves the phase-major epilogue's FP instruction count
+__device__ __forceinline__ uint64_t f2_pack_u(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_splat(float v) { return f2_pack_u(__float_as_uint(v), __float_as_uint(v)); }
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
 // ------------------------------ kernel -------------------------------------
 template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0>
 struct MmaCfg {
@@ -42,7 +60,8 @@ struct MmaCfg {
   static constexpr int ACC_STAGES = (2 * MB * N_TILE <= 512) ? 2 : 1;
   static constexpr int ACC_COLS = ACC_STAGES * MB * N_TILE;
   static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128 : ACC_COLS <= 256 ? 256 : 512;
-  static constexpr int A_ROWS = MT + 2 * PADL;
+  static constexpr int A_HALO = PM ? 8 : PADL;  // rows of halo an activation stage has room for (upsamples shift by +-1)
+  static constexpr int A_ROWS = MT + 2 * A_HALO;
   static constexpr int A_SLICE_BYTES = A_ROWS * 16;
   static constexpr int A_BUF_BYTES = (KC / 8) * A_SLICE_BYTES;
   static constexpr int B_SLICE_BYTES = N_TILE * 16;
@@ -220,6 +239,36 @@ __global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(con
       const int n_tile = rem - m_tile * p.n_tiles;
       const int t0 = m_tile * Cfg::MT;
       const uint32_t as = acc_it % Cfg::ACC_STAGES;
+      // phase-major upsample: this row's har samples are requested before the accumulator wait (the epilogue has few
+      // warps, so every exposed global-load latency counts).  A/B (profiles/r1be-r1bh): plain per-lane 8 B loads (lane
+      // stride up*16 B) beat staging the warp's contiguous window through shared memory - the L1 data pipe, which
+      // also carries the transpose, is the unit that saturates (80 %).
+      [[maybe_unused]] float hv[PM ? 4 * (N_TILE / 16) + 4 : 1];
+      if constexpr (PM != 0) {
+        static_assert(MB == 2, "phase-major epilogue: one item per warp and tile");
+        constexpr int PH = Cfg::PH, U = 2 * PH, NZS = 4, NZK = 8, NH = NZS * PH + NZK - NZS;
+        if (e.nz_har) {
+          const int t_in = t0 + (wg & 1) * 128 + q * 32 + lane;
+          const float* hb = e.nz_har + (size_t)b * e.nz_src;
+          const int s0 = (t_in * U + (n_tile & 1) * PH) * NZS - (NZK - NZS) / 2;  // even
+          if (t_in < p.L_in && s0 >= 0 && s0 + NH <= e.nz_src) {
+            const float2* h2p = reinterpret_cast<const float2*>(hb + s0);
+#pragma unroll
+            for (int j = 0; j < NH / 2; ++j) {
+              const float2 h2 = __ldg(h2p + j);
+              hv[2 * j] = h2.x; hv[2 * j + 1] = h2.y;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < NH / 2; ++j) {
+              const int sidx = s0 + 2 * j;
+              float2 h2 = make_float2(0.f, 0.f);
+              if (t_in < p.L_in && sidx >= 0 && sidx < e.nz_src) h2 = __ldg(reinterpret_cast<const float2*>(hb + sidx));
+              hv[2 * j] = h2.x; hv[2 * j + 1] = h2.y;
+            }
+          }
+        }
+      }
       mbar_wait(acc_full + 8 * as, (acc_it / Cfg::ACC_STAGES) & 1u);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (MB * N_TILE);
@@ -238,119 +287,98 @@ __global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(con
         constexpr int NC = PH * 8;       // columns (= floats per thread) of one slice
         constexpr int NZS = 4, NZK = 8;  // the fused noise conv: stride 4, 8 taps, pad 2 (checked by the host)
         constexpr int NH = NZS * PH + NZK - NZS;
+        constexpr int U = 2 * PH;        // upsample rate == 16 B pieces per staged run
+        constexpr int RUNS = 32 / U;     // runs one store instruction covers (lanes >= RUNS*U idle)
+        constexpr int ITER = (32 + RUNS - 1) / RUNS;
+        constexpr int SL4 = Cfg::STG_LANE / 4;
         const int cg = n_tile >> 1, half = n_tile & 1;
         const int sl = (warp - 2) >> 3;
+        const int sub = lane / U, pp = lane - sub * U;  // this lane's run / piece in the store loop
         float* stg = reinterpret_cast<float*>(smem_gen + (stg_smem - smem_base) + (size_t)(warp - 2) * Cfg::STG_WARP);
-#pragma unroll 1
-        for (int mb = wg & 1; mb < MB; mb += 2) {
+        const float* cst = reinterpret_cast<const float*>(smem_gen + (const_smem - smem_base));
+        const int co0 = cg * 16 + sl * 8;
+        {
+          const int mb = wg & 1;
           const int tb = t0 + mb * 128 + q * 32;
           const int t_in = tb + lane;
           const bool valid = t_in < p.L_in;
-          const int co0 = cg * 16 + sl * 8;
-          float hv[NH];
-          if (e.nz_har) {
-            // the warp's har window (32 lanes x up*4 samples, contiguous) -> staging with coalesced 8 B loads, lane
-            // rows padded by 2 words (stride 42 / 50 words: conflict-free 8 B reads), then each lane takes its NH samples
-            const int lane_words = e.up * NZS;                 // 40 / 48
-            const int pairs_per_lane = lane_words >> 1;        // 20 / 24
-            const float* hb = e.nz_har + (size_t)b * e.nz_src;
-            const int s_w = (tb * e.up + half * PH) * NZS - (NZK - NZS) / 2;  // even
-            const int n_pairs = (31 * lane_words + NH + 1) >> 1;
-            for (int m = lane; m < n_pairs; m += 32) {
-              const int sidx = s_w + 2 * m;
-              float2 h2 = make_float2(0.f, 0.f);
-              if (sidx >= 0 && sidx < e.nz_src) h2 = __ldg(reinterpret_cast<const float2*>(hb + sidx));
-              *reinterpret_cast<float2*>(stg + 2 * m + 2 * (m / pairs_per_lane)) = h2;
-            }
-            __syncwarp();
-            const float2* mine = reinterpret_cast<const float2*>(stg + lane * (lane_words + 2));
-#pragma unroll
-            for (int j = 0; j < NH / 2; ++j) {
-              const float2 h2 = mine[j];
-              hv[2 * j] = h2.x; hv[2 * j + 1] = h2.y;
-            }
-            __syncwarp();
-          }
-          const float* cst = reinterpret_cast<const float*>(smem_gen + (const_smem - smem_base));
-          const float4 b0 = *reinterpret_cast<const float4*>(cst + co0), b1 = *reinterpret_cast<const float4*>(cst + co0 + 4);
-          float a[NC];
+          uint64_t a2[NC / 2];  // packed fp32 pairs (FADD2 / FFMA2)
           {
             const uint32_t t_col = t_acc + mb * N_TILE + sl * NC;
             uint32_t r[32];
             tc_ld32(t_col, r);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) a[i] = __uint_as_float(r[i]);
+            for (int i = 0; i < 16; ++i) a2[i] = f2_pack_u(r[2 * i], r[2 * i + 1]);
             if constexpr (NC - 32 == 8) {
               uint32_t r8[8];
               tc_ld8(t_col + 32, r8);
 #pragma unroll
-              for (int i = 0; i < 8; ++i) a[32 + i] = __uint_as_float(r8[i]);
+              for (int i = 0; i < 4; ++i) a2[16 + i] = f2_pack_u(r8[2 * i], r8[2 * i + 1]);
             } else {
               uint32_t r16[16];
               tc_ld16(t_col + 32, r16);
 #pragma unroll
-              for (int i = 0; i < 16; ++i) a[32 + i] = __uint_as_float(r16[i]);
+              for (int i = 0; i < 8; ++i) a2[16 + i] = f2_pack_u(r16[2 * i], r16[2 * i + 1]);
             }
             static_assert(NC == 40 || NC == 48, "phase-major tiles: 5 or 6 phases per half");
           }
+          {  // per-channel bias (upsample + noise conv), the same for every phase
+            const ulonglong2 bq0 = *reinterpret_cast<const ulonglong2*>(cst + co0), bq1 = *reinterpret_cast<const ulonglong2*>(cst + co0 + 4);
 #pragma unroll
-          for (int rr = 0; rr < PH; ++rr) {
-            float* v = &a[rr * 8];
-            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+            for (int rr = 0; rr < PH; ++rr) {
+              a2[rr * 4 + 0] = f2_add(a2[rr * 4 + 0], bq0.x); a2[rr * 4 + 1] = f2_add(a2[rr * 4 + 1], bq0.y);
+              a2[rr * 4 + 2] = f2_add(a2[rr * 4 + 2], bq1.x); a2[rr * 4 + 3] = f2_add(a2[rr * 4 + 3], bq1.y);
+            }
           }
           if (e.nz_har) {
 #pragma unroll
             for (int j = 0; j < NZK; ++j) {
-              const float4* wp4 = reinterpret_cast<const float4*>(cst + 256 + j * e.cout + co0);
-              const float4 w0 = wp4[0], w1 = wp4[1];
+              const float* wj = cst + 256 + j * e.cout + co0;
+              const ulonglong2 wq0 = *reinterpret_cast<const ulonglong2*>(wj), wq1 = *reinterpret_cast<const ulonglong2*>(wj + 4);
 #pragma unroll
               for (int rr = 0; rr < PH; ++rr) {
-                float* v = &a[rr * 8];
-                const float hh = hv[NZS * rr + j];
-                v[0] = fmaf(hh, w0.x, v[0]); v[1] = fmaf(hh, w0.y, v[1]); v[2] = fmaf(hh, w0.z, v[2]); v[3] = fmaf(hh, w0.w, v[3]);
-                v[4] = fmaf(hh, w1.x, v[4]); v[5] = fmaf(hh, w1.y, v[5]); v[6] = fmaf(hh, w1.z, v[6]); v[7] = fmaf(hh, w1.w, v[7]);
+                const uint64_t hh = f2_splat(hv[NZS * rr + j]);
+                a2[rr * 4 + 0] = f2_fma(hh, wq0.x, a2[rr * 4 + 0]); a2[rr * 4 + 1] = f2_fma(hh, wq0.y, a2[rr * 4 + 1]);
+                a2[rr * 4 + 2] = f2_fma(hh, wq1.x, a2[rr * 4 + 2]); a2[rr * 4 + 3] = f2_fma(hh, wq1.y, a2[rr * 4 + 3]);
               }
             }
           }
           // registers -> staging (lane stride STG_LANE = 11 / 13 x 16 B: conflict-free quarter-warp stores)
           {
-            float4* mine = reinterpret_cast<float4*>(stg + lane * (Cfg::STG_LANE / 4));
+            ulonglong2* mine = reinterpret_cast<ulonglong2*>(stg + lane * SL4);
 #pragma unroll
-            for (int i = 0; i < NC / 4; ++i) mine[i] = make_float4(a[4 * i], a[4 * i + 1], a[4 * i + 2], a[4 * i + 3]);
+            for (int i = 0; i < NC / 4; ++i) mine[i] = make_ulonglong2(a2[2 * i], a2[2 * i + 1]);
           }
           __syncwarp();
-          // staging -> global, consecutive lanes = consecutive 16 B pieces of the warp's 32 runs
+          // staging -> global: lane (sub, pp) takes 16 B piece pp of run it*RUNS + sub, so one store instruction writes
+          // RUNS whole runs (PH*32 B each, 2*PH*32 B apart: the other half of the phases belongs to the neighbouring
+          // N tile) and every address is the previous one plus a compile-time constant
           const size_t row0 = ((size_t)b * (e.cout >> 3) + cg * 2 + sl) * e.Lp_out + PADL + (size_t)half * PH;
-          float4 f[2 * PH];
+          const size_t el0 = (row0 + (size_t)(tb + sub) * U) * 8 + pp * 4;
+          const int lim = (sub < RUNS) ? min(32, p.L_in - tb) - sub : 0;  // run it*RUNS + sub exists iff it*RUNS < lim
+          const float* src = stg + sub * SL4 + pp * 4;
+          float4 f[ITER];
 #pragma unroll
-          for (int it = 0; it < 2 * PH; ++it) {
-            const int P = it * 32 + lane;
-            const int ln = P / (2 * PH), pp = P - ln * (2 * PH);
-            f[it] = *reinterpret_cast<const float4*>(stg + ln * (Cfg::STG_LANE / 4) + pp * 4);
-          }
+          for (int it = 0; it < ITER; ++it) f[it] = *reinterpret_cast<const float4*>(src + it * RUNS * SL4);
+          float* of = e.out_f32 ? e.out_f32 + el0 : nullptr;
+          uint16_t* oa = e.out_act ? reinterpret_cast<uint16_t*>(e.out_act) + el0 : nullptr;
+          const bool f16 = e.act_fmt == ACT_F16;
 #pragma unroll
-          for (int it = 0; it < 2 * PH; ++it) {
-            const int P = it * 32 + lane;
-            const int ln = P / (2 * PH), pp = P - ln * (2 * PH);
-            if (tb + ln < p.L_in) {
-              const size_t el = (row0 + (size_t)(tb + ln) * e.up) * 8 + pp * 4;
-              const float4 ff = f[it];
-              if (e.out_f32) *reinterpret_cast<float4*>(e.out_f32 + el) = ff;
-              if (e.out_act) {
-                uint2 pk;
-                if (e.act_fmt == ACT_F16) {
-                  __half2 h0 = __floats2half2_rn(fmaxf(ff.x, ff.x * e.slope), fmaxf(ff.y, ff.y * e.slope));
-                  __half2 h1 = __floats2half2_rn(fmaxf(ff.z, ff.z * e.slope), fmaxf(ff.w, ff.w * e.slope));
-                  pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
-                } else {
-                  __nv_bfloat162 h0 = __floats2bfloat162_rn(fmaxf(ff.x, ff.x * e.slope), fmaxf(ff.y, ff.y * e.slope));
-                  __nv_bfloat162 h1 = __floats2bfloat162_rn(fmaxf(ff.z, ff.z * e.slope), fmaxf(ff.w, ff.w * e.slope));
-                  pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
-                }
-                *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(e.out_act) + el) = pk;
-              }
+          for (int it = 0; it < ITER; ++it) {
+            const bool ok = it * RUNS < lim;
+            const float4 ff = f[it];
+            if (of && ok) *reinterpret_cast<float4*>(of + it * RUNS * U * 8) = ff;
+            uint2 pk;
+            const float m0 = fmaxf(ff.x, ff.x * e.slope), m1 = fmaxf(ff.y, ff.y * e.slope);
+            const float m2 = fmaxf(ff.z, ff.z * e.slope), m3 = fmaxf(ff.w, ff.w * e.slope);
+            if (f16) {
+              __half2 h0 = __floats2half2_rn(m0, m1), h1 = __floats2half2_rn(m2, m3);
+              pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
+            } else {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(m0, m1), h1 = __floats2bfloat162_rn(m2, m3);
+              pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
             }
+            if (oa && ok) *reinterpret_cast<uint2*>(oa + it * RUNS * U * 8) = pk;
           }
           __syncwarp();
         }
@@ -500,7 +528,7 @@ template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0
 static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s) {
   using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
   auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
-  if ((PM != 0) != (p.epi.pm != 0)) return cudaErrorInvalidValue;
+  if ((PM != 0) != (p.epi.pm != 0) || p.halo > Cfg::A_HALO) return cudaErrorInvalidValue;
   {  // per-device attribute; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) return e;
@@ -524,8 +552,10 @@ bool conv_mma_supported(int n_tile, int kc) {
 
 cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms, cudaStream_t s) {
   // phase-major upsample tiles (rate 10 / 12): 5 / 6 phases x 16 channels, accumulators double-buffered
-  if (n_tile == 80 && kc == 64) return launch_inst<80, 2, 64, 5, 2, 1>(p, num_sms, s);
-  if (n_tile == 96 && kc == 64) return launch_inst<96, 2, 64, 3, 2, 1>(p, num_sms, s);
+  // (three activation stages for the rate-10 tile: an upsample has only 2 taps of MMAs per 64-channel chunk, so with
+  // two stages the MMA warp spent more than half of its time waiting for activation tiles, profiles/r1bg)
+  if (n_tile == 80 && kc == 64) return p.a_stages == 2 ? launch_inst<80, 2, 64, 5, 2, 1>(p, num_sms, s) : launch_inst<80, 2, 64, 3, 3, 1>(p, num_sms, s);
+  if (n_tile == 96 && kc == 64) return launch_inst<96, 2, 64, 4, 2, 1>(p, num_sms, s);
   if (n_tile == 256 && kc == 64) return launch_inst<256, 2, 64, 4>(p, num_sms, s);
   // 128-wide tiles: option a_stages = 3 adds a third 40 KB activation stage.  Measured (profiles/r1af_*): the
   // 128-channel stage gets 7 % SLOWER with it (229 vs 214 ms), so two stages stay the default.

@@ -260,7 +260,9 @@ def test_fused_pair_kernel_matches_per_conv_path(dev, cfg_name, B, T, seed):
         m._handle.set_option("pair_mrf", 1)
         y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
         n1 = m.last_launch_count
-    assert n1 <= n0 - 9, (n0, n1)  # 18 conv launches -> 9 pair launches (and no separate noise_add)
+    # 18 conv launches -> 9 pair launches; the per-conv baseline already has its noise conv inside the phase-major
+    # upsample where that applies (48k / 40k), the pair path keeps a noise_add launch unless "pair_noise" is set
+    assert n1 <= n0 - 8, (n0, n1)
     assert float((y1 - y0).abs().max()) <= 2e-3, float((y1 - y0).abs().max())
     if T >= 50:
         assert O.multires_logmel_corr(y1, y_ref, cfg.sr)["min"] >= FAST_BAR
@@ -278,14 +280,21 @@ def test_item_grouped_launches_are_bit_identical(dev, cfg_name, B, T, seed):
     with torch.no_grad():
         h = m._ensure_handle(dev)
         h.set_option("mrf_items", 0)
+        ypm = m(xd, fd, gd, noise=nd_, mode="fast").cpu()  # default: stage 1's noise conv + operand copy ride in the upsample
+        # grouped launches keep the separate noise_add pass (the stage hand-off buffers differ), so bit identity is
+        # checked between the two launch shapes of that same arithmetic
+        h.set_option("ups_pm", 0)
         y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
         n0 = m.last_launch_count
         h.set_option("mrf_items", 1)  # 1 MiB budget: groups of 1-2 items at these sizes
         y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
         n1 = m.last_launch_count
+        h.set_option("ups_pm", 1)
+        y2 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()  # grouped launches + phase-major upsamples
         h.set_option("mrf_items", 0)
     assert n1 > n0, (n0, n1)
     assert torch.equal(y0, y1)
+    assert float((y2 - ypm).abs().max()) <= 2e-3 and float((y2 - y0).abs().max()) <= 2e-3
 
 
 @pytest.mark.parametrize("split_k", [7, 11])
