@@ -123,6 +123,12 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *   "zero_stuff" 1 = (default) a stride-2 upsample that feeds a fused-MRF stage runs as an ordinary convolution
  *                    over a zero-stuffed copy of its input (written by the previous stage's last kernel);
  *                0 = polyphase form everywhere.
+ *   "ups_pm"     1 = (default) the rate-10 / 12 upsamples (hifigan_nsf.py:198) use their phase-major weight image: GEMM
+ *                    columns ordered (16-channel group, half of the phases, slice, phase, channel), warp-transposed
+ *                    coalesced epilogue; on a per-conv MRF stage whose noise conv has 8 taps (stage 1) the epilogue
+ *                    also adds noise_convs[i](har) (:199) and writes the ResBlocks' activated 16-bit operand, which
+ *                    replaces the noise_add pass.  0 = one phase per N tile with the scatter epilogue.
+ *   "pm_a_stages" 2 (default) or 3 activation stages of the rate-10 phase-major tile (no measurable difference).
  *   "fused_post" 1 = (default) conv_post + tanh (hifigan_nsf.py:209-210) are computed in the epilogue of the last
  *                    stage's final fused-MRF launch (32-channel last stage, 7 taps, "fused_mrf" 1); 0 = own kernel.
  *   "fused_epi_warps" 8 (default) or 16 epilogue warps in the fused ResBlock kernel.
