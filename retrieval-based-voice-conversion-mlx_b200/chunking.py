@@ -101,3 +101,53 @@ def stitch(decoded: Sequence[np.ndarray], trims: Sequence[int], crossfade: int =
         out[-n:] = out[-n:] * fade_out + seg[:n] * fade_in
         out = np.concatenate([out, seg[n:]])
     return out
+
+
+def decode_chunks(model, x, f0, g, chunks: Sequence[Chunk], *, mode=None, noise=None, device=None,
+                  rank: int = 0, world: int = 1):
+    """Decode this rank's share of ``chunks`` of one padded utterance in ONE batched call and return
+    ``{chunk.index: 1-D float32 waveform of chunk.frames * upp samples}`` (untrimmed).
+
+    The reference walks ``opt_ts`` sequentially and calls ``net_g.infer`` once per chunk
+    (pipeline.py:478-544); chunks share no state, so here they are dealt to ``world`` ranks
+    (``shard_units``: longest first) and each rank submits its chunks as one batch.  Chunks shorter than
+    the rank's longest are zero-padded at the end: the decoder's receptive field (about 12 frames) is far
+    below the ``t_pad`` context (100 frames) that ``stitch`` trims, so the kept samples do not see the padding.
+
+    x (1, C, n) / f0 (1, n): CPU tensors of the padded utterance; g (1, gin, 1) or None.
+    noise: None = in-kernel Philox draws through the host-buffer entry point (``decode_host``); or a CPU tensor
+    (1, n * upp) of standard-normal draws, cut per chunk and injected through the device-pointer entry
+    point (``forward``) - what the parity tests use."""
+    import torch
+
+    mine = [chunks[i] for i in shard_units([c.frames for c in chunks], world)[rank]]
+    if not mine:
+        return {}
+    upp = model.upp
+    B, Tmax = len(mine), max(c.frames for c in mine)
+    xb = torch.zeros(B, x.shape[1], Tmax, dtype=torch.float32).pin_memory()
+    fb = torch.zeros(B, Tmax, dtype=torch.float32).pin_memory()
+    for k, c in enumerate(mine):
+        xb[k, :, :c.frames] = x[0, :, c.start:c.stop]
+        fb[k, :c.frames] = f0[0, c.start:c.stop]
+    gb = None if g is None else g.reshape(1, -1, 1).expand(B, -1, 1).contiguous()
+    if noise is None:
+        y = model.decode_host(xb, fb, gb, mode=mode, device=device)
+    else:
+        nb = torch.zeros(B, Tmax * upp, dtype=torch.float32)
+        for k, c in enumerate(mine):
+            nb[k, :c.frames * upp] = noise[0, c.start * upp:c.stop * upp]
+        dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        with torch.no_grad():
+            y = model(xb.to(dev), fb.to(dev), None if gb is None else gb.to(dev), noise=nb.to(dev), mode=mode).cpu()
+    return {c.index: y[k, 0, :c.frames * upp].numpy() for k, c in enumerate(mine)}
+
+
+def decode_long(model, x, f0, g, *, mode=None, crossfade: int = 0, noise=None, device=None, split_points=None,
+                x_pad: int = 1, x_query: int = 6, x_center: int = 38, x_max: int = 41) -> np.ndarray:
+    """Single-process long-form decode: plan the reference's ``t_pad``-overlap chunks for a PADDED utterance
+    (x: (1, C, n_frames + 2 * pad)), decode them as one batch, trim and join (``stitch``)."""
+    pad = x_pad * FRAMES_PER_SECOND
+    chunks = plan_chunks(x.shape[2] - 2 * pad, x_pad, x_query, x_center, x_max, split_points)
+    dec = decode_chunks(model, x, f0, g, chunks, mode=mode, noise=noise, device=device)
+    return stitch([dec[c.index] for c in chunks], [c.trim * model.upp for c in chunks], crossfade)

@@ -451,3 +451,35 @@ def test_long_form_chunked_decode_matches_reference_stitching(dev):
     y, y_ref = ch.stitch(outs, trims), ch.stitch(refs, trims)
     assert y.shape == (n_frames * cfg.upp,)
     assert float(np.abs(y - y_ref).max()) <= FP32_BAR
+
+
+def test_batched_long_form_driver_matches_per_chunk_decode(dev):
+    """chunking.decode_long: all t_pad-overlap chunks of an utterance submitted as ONE zero-padded batch, trimmed and
+    concatenated, against the oracle run chunk by chunk on the same injected noise (fp32 mode), and the two-rank
+    sharding of the same plan (decode_chunks with rank / world) against the single-rank result."""
+    from rvc_b200 import chunking as ch
+
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 22)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    n_frames, pad = 300, 100
+    total = n_frames + 2 * pad
+    x, f0, g, _ = O.synth_inputs(cfg, 1, total, seed=9)
+    noise = torch.randn(1, total * cfg.upp, generator=torch.Generator().manual_seed(3))
+    splits = [70, 190]  # ragged chunk lengths: 270, 320, 310 frames
+    y = ch.decode_long(m, x, f0, g, mode="fp32", noise=noise, split_points=splits)
+    chunks = ch.plan_chunks(n_frames, split_points=splits)
+    refs = [O.decoder_forward(w, cfg, x[:, :, c.start:c.stop], f0[:, c.start:c.stop], g,
+                              noise[:, c.start * cfg.upp:c.stop * cfg.upp])[0, 0].numpy() for c in chunks]
+    y_ref = ch.stitch(refs, [c.trim * cfg.upp for c in chunks])
+    assert y.shape == y_ref.shape == (n_frames * cfg.upp,)
+    assert float(np.abs(y - y_ref).max()) <= FP32_BAR
+    parts = {}
+    for r in range(2):
+        parts.update(ch.decode_chunks(m, x, f0, g, chunks, mode="fp32", noise=noise, rank=r, world=2))
+    y2 = ch.stitch([parts[c.index] for c in chunks], [c.trim * cfg.upp for c in chunks])
+    assert float(np.abs(y2 - y).max()) <= 1e-5
+    # host-buffer path (in-kernel noise): shape / range only
+    yh = ch.decode_long(m, x, f0, g, mode="fast", split_points=splits, crossfade=240)
+    assert yh.shape == (n_frames * cfg.upp,) and np.isfinite(yh).all() and float(np.abs(yh).max()) <= 1.0
