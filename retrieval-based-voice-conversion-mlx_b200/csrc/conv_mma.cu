@@ -46,7 +46,7 @@ __device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
 }
 
 // ------------------------------ kernel -------------------------------------
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0, int EW = 8>
 struct MmaCfg {
   static constexpr int MT = MB * 128;
   // PM = 1: phase-major polyphase upsample tile (see the PM epilogue below): N_TILE = PH phases x 2 slices x 8
@@ -56,7 +56,10 @@ struct MmaCfg {
   static constexpr int STG_WARP = PM ? 32 * STG_LANE : 0;
   static constexpr int STG_BYTES = 16 * STG_WARP;
   static constexpr int CONST_BYTES = PM ? (256 + 8 * 128) * 4 : 0;  // per-channel bias (<= 256) + noise-conv taps [8][<= 128]
-  static constexpr int THREADS = PM ? 64 + 16 * 32 : 64 + 8 * 32;  // producer warp + MMA warp + epilogue warps
+  static constexpr int EPI_WARPS = PM ? 16 : EW;        // 8, or 16 (items of 16 columns: twice the warps to hide the epilogue's latencies)
+  static constexpr int CW = EPI_WARPS == 16 ? 16 : 32;  // accumulator columns per epilogue work item (non-PM paths)
+  static constexpr int THREADS = 64 + EPI_WARPS * 32;   // producer warp + MMA warp + epilogue warps
+  static_assert(EW == 8 || EW == 16, "8 or 16 epilogue warps");
   static constexpr int ACC_STAGES = (2 * MB * N_TILE <= 512) ? 2 : 1;
   static constexpr int ACC_COLS = ACC_STAGES * MB * N_TILE;
   static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128 : ACC_COLS <= 256 ? 256 : 512;
@@ -74,9 +77,9 @@ struct MmaCfg {
 
 constexpr int MMA_THREADS = 320;  // producer warp + MMA warp + 2 epilogue warpgroups
 
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES, int PM>
-__global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
-  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES, int PM, int EW>
+__global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 127u) & ~127u;
   const uint32_t a_smem = smem_base;
@@ -225,8 +228,10 @@ __global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(con
   } else {
     // ===================== epilogue warps (2 warpgroups) =====================
     const int q = warp & 3;          // TMEM lane quarter this warp may access
-    const int wg = (warp - 2) >> 2;  // work items (mb, 32-column chunk) alternate between the warpgroups
-    constexpr int CH = N_TILE / 32;
+    const int wg = (warp - 2) >> 2;  // work items (mb, CW-column chunk) are dealt to the warpgroups in turn
+    constexpr int CW = Cfg::CW;
+    constexpr int WGS = Cfg::EPI_WARPS / 4;
+    constexpr int CH = N_TILE / CW;
     constexpr int ITEMS = MB * CH;
     const Epilogue& e = p.epi;
     const bool fast = (e.up == 1);
@@ -384,27 +389,27 @@ __global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(con
         }
       } else {
 #pragma unroll 1
-      for (int item = wg; item < ITEMS; item += 2) {
+      for (int item = wg; item < ITEMS; item += WGS) {
         const int mb = item / CH;
-        const int c0 = (item - mb * CH) * 32;
+        const int c0 = (item - mb * CH) * CW;
         const int t_in = t0 + mb * 128 + q * 32 + lane;
         const bool valid = t_in < p.L_in;
         if (fast) {
-          uint32_t r[32];
+          uint32_t r[CW];
           // ---- lean path (every ordinary conv): up == 1, output row == input row ----
           const int n0 = n_tile * N_TILE + c0;
           const size_t off = (((size_t)b * (e.cout >> 3) + (n0 >> 3)) * e.Lp_out + PADL + t_in) * 8;
-          float4 rr[8], sm[8];
+          float4 rr[CW / 4], sm[CW / 4];
           if (e.res && valid) {  // issue the residual loads before waiting on TMEM
 #pragma unroll
-            for (int s8 = 0; s8 < 4; ++s8) {
+            for (int s8 = 0; s8 < CW / 8; ++s8) {
               rr[2 * s8] = *reinterpret_cast<const float4*>(e.res + off + s8 * slice_stride);
               rr[2 * s8 + 1] = *reinterpret_cast<const float4*>(e.res + off + s8 * slice_stride + 4);
             }
           }
           if (e.sum_in && valid) {
 #pragma unroll
-            for (int s8 = 0; s8 < 4; ++s8) {
+            for (int s8 = 0; s8 < CW / 8; ++s8) {
               sm[2 * s8] = *reinterpret_cast<const float4*>(e.sum_in + off + s8 * slice_stride);
               sm[2 * s8 + 1] = *reinterpret_cast<const float4*>(e.sum_in + off + s8 * slice_stride + 4);
             }
@@ -419,13 +424,20 @@ __global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(con
               hv[j] = (valid && j < e.nz_k && sidx >= 0 && sidx < e.nz_src) ? __ldg(hb + sidx) : 0.f;
             }
           }
-          tc_ld32(t_acc + mb * N_TILE + c0, r);
-          if (valid) {
+          // bias of the 32 columns, requested before the TMEM wait as well (the volatile TMEM load pins everything
+          // after it: profiles/r1bl, the first FADD of every 8-column group sat on its own bias load)
+          float4 bb[CW / 4];
+          {
             const float4* bp = reinterpret_cast<const float4*>(e.bias + (size_t)b * e.bias_bstride + n0);
 #pragma unroll
-            for (int s8 = 0; s8 < 4; ++s8) {
+            for (int i = 0; i < CW / 4; ++i) bb[i] = __ldg(bp + i);
+          }
+          if constexpr (CW == 32) tc_ld32(t_acc + mb * N_TILE + c0, r); else tc_ld16(t_acc + mb * N_TILE + c0, r);
+          if (valid) {
+#pragma unroll
+            for (int s8 = 0; s8 < CW / 8; ++s8) {
               float v[8];
-              const float4 b0 = __ldg(bp + 2 * s8), b1 = __ldg(bp + 2 * s8 + 1);
+              const float4 b0 = bb[2 * s8], b1 = bb[2 * s8 + 1];
               v[0] = __uint_as_float(r[s8 * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[s8 * 8 + 1]) + b0.y;
               v[2] = __uint_as_float(r[s8 * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[s8 * 8 + 3]) + b0.w;
               v[4] = __uint_as_float(r[s8 * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[s8 * 8 + 5]) + b1.y;
@@ -495,7 +507,7 @@ __global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(con
           // 8 columns per TMEM load so the accumulator registers are indexed statically (a 32-wide
           // array indexed by the s8 loop variable lived in local memory: STL/LDL in the r1c capture).
 #pragma unroll 1
-          for (int s8 = 0; s8 < 4; ++s8) {
+          for (int s8 = 0; s8 < CW / 8; ++s8) {
             uint32_t r8[8];
             tc_ld8(t_acc + mb * N_TILE + c0 + s8 * 8, r8);
             if (valid) {
@@ -524,10 +536,10 @@ __global__ void __launch_bounds__(PM ? 576 : MMA_THREADS, 1) conv_mma_kernel(con
   }
 }
 
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0, int EW = 8>
 static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s) {
-  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
-  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES, PM>;
+  using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
+  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
   if ((PM != 0) != (p.epi.pm != 0) || p.halo > Cfg::A_HALO) return cudaErrorInvalidValue;
   {  // per-device attribute; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -559,7 +571,10 @@ cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms
   if (n_tile == 256 && kc == 64) return launch_inst<256, 2, 64, 4>(p, num_sms, s);
   // 128-wide tiles: option a_stages = 3 adds a third 40 KB activation stage.  Measured (profiles/r1af_*): the
   // 128-channel stage gets 7 % SLOWER with it (229 vs 214 ms), so two stages stay the default.
-  if (n_tile == 128 && kc == 64) return p.a_stages == 3 ? launch_inst<128, 2, 64, 6, 3>(p, num_sms, s) : launch_inst<128, 2, 64, 6, 2>(p, num_sms, s);
+  if (n_tile == 128 && kc == 64) {
+    if (p.a_stages == 3) return launch_inst<128, 2, 64, 6, 3>(p, num_sms, s);
+    return p.epi_warps == 16 ? launch_inst<128, 2, 64, 6, 2, 0, 16>(p, num_sms, s) : launch_inst<128, 2, 64, 6, 2>(p, num_sms, s);
+  }
   if (n_tile == 64 && kc == 64) return launch_inst<64, 4, 64, 4>(p, num_sms, s);
   if (n_tile == 32 && kc == 32) return launch_inst<32, 4, 32, 4>(p, num_sms, s);
   return cudaErrorInvalidValue;

@@ -97,6 +97,7 @@ struct rvcdec_handle {
   long long* d_timing = nullptr;
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
+  int conv_epi_warps = 8;  // epilogue warps of the 128-wide conv_mma tiling (8 over 32-column items, 16 over 16-column items)
   int pm_a_stages = 2; // activation ring depth of the rate-10 phase-major upsample tile (2 or 3)
   int ups_pm_on = 1;   // 1 = upsamples that have a phase-major image use it (and carry the stage's 8-tap noise conv + 16-bit copy)
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
@@ -408,6 +409,7 @@ int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, 
   for (int t = 0; t < L.ntaps; ++t) p.shift[t] = L.shift[t];
   p.epi = epi;
   p.a_stages = epi.pm ? h->pm_a_stages : h->a_stages;
+  p.epi_warps = h->conv_epi_warps;
   if (mode == 0) {
     p.w = L.d_wf;
     for (size_t i = 0; i < L.mask_f32.size() && i < (size_t)MAX_NTILES; ++i) p.tapmask[i] = L.mask_f32[i];
@@ -1202,6 +1204,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     if (!value && h->d_timing) { cudaFree(h->d_timing); h->d_timing = nullptr; }
     if (h->d_timing) CK(cudaMemset(h->d_timing, 0, sizeof(long long) * rvcdec_handle::kTimingMaxLaunches * h->num_sms * 16));
     h->timing_launches = 0;
+    return 0;
+  }
+  if (k == "conv_epi_warps") {
+    if (value != 8 && value != 16) return fail(RVCDEC_ERR_ARG, "conv_epi_warps must be 8 or 16");
+    h->conv_epi_warps = (int)value;
     return 0;
   }
   if (k == "pm_a_stages") {
