@@ -89,6 +89,7 @@ struct ConvParams {
   uint32_t tapmask[MAX_NTILES];  // per N tile: bit j set = tap j has non-zero weights
   int m_tiles, n_tiles;    // tiles per batch item along time, tiles along N
   int a_stages;            // activation ring depth of the 128-wide tensor-core tiling (3; anything else = 2)
+  int epi_warps_small;     // same for the 64- / 32-wide tilings (zero-stuffed stride-2 upsamples, per-conv stages 2-3)
   int epi_warps;           // 16 = the 128-wide tiling runs 16 epilogue warps over 16-column items; anything else = 8 / 32
   Epilogue epi;
 };

@@ -575,8 +575,8 @@ cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms
     if (p.a_stages == 3) return launch_inst<128, 2, 64, 6, 3>(p, num_sms, s);
     return p.epi_warps == 16 ? launch_inst<128, 2, 64, 6, 2, 0, 16>(p, num_sms, s) : launch_inst<128, 2, 64, 6, 2>(p, num_sms, s);
   }
-  if (n_tile == 64 && kc == 64) return launch_inst<64, 4, 64, 4>(p, num_sms, s);
-  if (n_tile == 32 && kc == 32) return launch_inst<32, 4, 32, 4>(p, num_sms, s);
+  if (n_tile == 64 && kc == 64) return p.epi_warps_small == 16 ? launch_inst<64, 4, 64, 4, 2, 0, 16>(p, num_sms, s) : launch_inst<64, 4, 64, 4>(p, num_sms, s);
+  if (n_tile == 32 && kc == 32) return p.epi_warps_small == 16 ? launch_inst<32, 4, 32, 4, 2, 0, 16>(p, num_sms, s) : launch_inst<32, 4, 32, 4>(p, num_sms, s);
   return cudaErrorInvalidValue;
 }
 

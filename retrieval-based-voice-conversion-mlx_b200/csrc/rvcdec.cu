@@ -97,7 +97,8 @@ struct rvcdec_handle {
   long long* d_timing = nullptr;
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
-  int conv_epi_warps = 8;  // epilogue warps of the 128-wide conv_mma tiling (8 over 32-column items, 16 over 16-column items)
+  int conv_epi_warps = 16;  // (profiles/r1bq: 16 warps 214 ms vs 8 warps 221 ms on the 128-channel stage) epilogue warps of the 128-wide conv_mma tiling (8 over 32-column items, 16 over 16-column items)
+  int conv_epi_warps_small = 16;  // same for the 64- / 32-wide tilings (profiles/r1br: ups2 21.8 -> 17.6 ms, ups3 13.9 -> 12.3 ms)
   int pm_a_stages = 2; // activation ring depth of the rate-10 phase-major upsample tile (2 or 3)
   int ups_pm_on = 1;   // 1 = upsamples that have a phase-major image use it (and carry the stage's 8-tap noise conv + 16-bit copy)
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
@@ -410,6 +411,7 @@ int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, 
   p.epi = epi;
   p.a_stages = epi.pm ? h->pm_a_stages : h->a_stages;
   p.epi_warps = h->conv_epi_warps;
+  p.epi_warps_small = h->conv_epi_warps_small;
   if (mode == 0) {
     p.w = L.d_wf;
     for (size_t i = 0; i < L.mask_f32.size() && i < (size_t)MAX_NTILES; ++i) p.tapmask[i] = L.mask_f32[i];
@@ -1209,6 +1211,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
   if (k == "conv_epi_warps") {
     if (value != 8 && value != 16) return fail(RVCDEC_ERR_ARG, "conv_epi_warps must be 8 or 16");
     h->conv_epi_warps = (int)value;
+    return 0;
+  }
+  if (k == "conv_epi_warps_small") {
+    if (value != 8 && value != 16) return fail(RVCDEC_ERR_ARG, "conv_epi_warps_small must be 8 or 16");
+    h->conv_epi_warps_small = (int)value;
     return 0;
   }
   if (k == "pm_a_stages") {
