@@ -78,6 +78,36 @@ def make_case(name, cfg, B, T, init_seed, in_seed, noise_seed, store_weights):
     np.savez_compressed(os.path.join(OUT, name + ".npz"), **data)
 
 
+def make_nof0_case(name, cfg, B, T, init_seed, in_seed):
+    """The sibling decoder of the no-f0 models: HiFiGANGenerator.forward (hifigan.py:72-97), deterministic (no noise)."""
+    from rvc.lib.algorithm.generators.hifigan import HiFiGANGenerator
+
+    torch.manual_seed(init_seed)
+    m = HiFiGANGenerator(cfg.initial_channel, list(cfg.resblock_kernel_sizes), [list(d) for d in cfg.resblock_dilation_sizes],
+                         list(cfg.upsample_rates), cfg.upsample_initial_channel, list(cfg.upsample_kernel_sizes),
+                         gin_channels=cfg.gin_channels).eval()
+    x, _, g, _ = O.synth_inputs(cfg, B, T, seed=in_seed)
+    with torch.no_grad():
+        y = m(x, g=g)
+    y_or = O.generator_forward_nof0(O.folded_weights(m.state_dict()), cfg, x, g)
+    err = float((y - y_or).abs().max())
+    print(f"{name}: out {tuple(y.shape)} rms {float(y.pow(2).mean().sqrt()):.4f} oracle-vs-reference max-abs {err:.3e}")
+    assert err < 5e-6, err
+    data = dict(
+        x=x.numpy(), g=g.numpy(), y=y.numpy(), init_seed=np.int64(init_seed),
+        cfg_initial_channel=np.int64(cfg.initial_channel),
+        cfg_resblock_kernel_sizes=np.array(cfg.resblock_kernel_sizes),
+        cfg_resblock_dilation_sizes=np.array(cfg.resblock_dilation_sizes),
+        cfg_upsample_rates=np.array(cfg.upsample_rates),
+        cfg_upsample_initial_channel=np.int64(cfg.upsample_initial_channel),
+        cfg_upsample_kernel_sizes=np.array(cfg.upsample_kernel_sizes),
+        cfg_gin_channels=np.int64(cfg.gin_channels), cfg_sr=np.int64(cfg.sr),
+    )
+    for k, v in checksums(m.state_dict()).items():
+        data["ck::" + k] = v
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **data)
+
+
 def make_sine_case():
     """SineGenerator alone (hifigan.py:197-228), including a long contour and the real
     RMVPE contour shipped with the reference (ios_test_data/rmvpe_f0.npy)."""
@@ -127,3 +157,4 @@ if __name__ == "__main__":
     make_case("v2_40k_B1_T32", O.CONFIG_40K, 1, 32, init_seed=1234, in_seed=31, noise_seed=32, store_weights=False)
     make_case("v2_32k_B1_T16", O.CONFIG_32K, 1, 16, init_seed=1234, in_seed=41, noise_seed=42, store_weights=False)
     make_sine_case()
+    make_nof0_case("nof0_40k_B2_T20", O.CONFIG_40K, 2, 20, init_seed=77, in_seed=78)

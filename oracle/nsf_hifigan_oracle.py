@@ -218,6 +218,27 @@ def decoder_forward(
     return x.float()
 
 
+def generator_forward_nof0(w: Dict[str, torch.Tensor], cfg: DecoderConfig, x: torch.Tensor, g: Optional[torch.Tensor],
+                           dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """HiFiGANGenerator.forward (rvc/lib/algorithm/generators/hifigan.py:72-97): the sibling decoder of the no-f0
+    models (selected at synthesizers.py:127-135) - the same conv stack without the harmonic source and noise convs."""
+    W = {k: v.to(dtype) for k, v in w.items()}
+    nk = len(cfg.resblock_kernel_sizes)
+    x = F.conv1d(x.to(dtype), W["conv_pre.weight"], W["conv_pre.bias"], padding=3)  # :74
+    if g is not None:
+        x = x + F.conv1d(g.to(dtype), W["cond.weight"], W["cond.bias"])  # :76-77
+    for i, (u, k) in enumerate(zip(cfg.upsample_rates, cfg.upsample_kernel_sizes)):
+        x = F.leaky_relu(x, LRELU_SLOPE)  # :80
+        x = F.conv_transpose1d(x, W[f"ups.{i}.weight"], W[f"ups.{i}.bias"], stride=u, padding=(k - u) // 2)  # :81, :56
+        xs = None
+        for j in range(nk):  # :82-87
+            y = resblock_forward(W, f"resblocks.{i * nk + j}", x, cfg.resblock_kernel_sizes[j], cfg.resblock_dilation_sizes[j])
+            xs = y if xs is None else xs + y
+        x = xs / nk  # :88
+    x = F.leaky_relu(x)  # :90 default slope 0.01
+    return torch.tanh(F.conv1d(x, W["conv_post.weight"], None, padding=3)).float()  # :91-93
+
+
 def resblock_forward(W, prefix: str, x: torch.Tensor, k: int, dilations: Sequence[int]) -> torch.Tensor:
     """ResBlock.forward (residuals.py:71-80) with x_mask=None."""
     for m, d in enumerate(dilations):

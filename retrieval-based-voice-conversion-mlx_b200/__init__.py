@@ -4,8 +4,8 @@ Only the decoder hot path lives here; see DESIGN.md for scope.  Importing this p
 load the CUDA library; the first ``forward`` (or ``_lib.lib()``) does, and fails loudly if it is
 missing.
 """
-from .decoder import HiFiGANNSFGenerator, ResBlock, SourceModuleHnNSF  # noqa: F401
+from .decoder import HiFiGANGenerator, HiFiGANNSFGenerator, ResBlock, SourceModuleHnNSF  # noqa: F401
 from . import _lib  # noqa: F401
 from . import chunking  # noqa: F401
 
-__all__ = ["HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking"]
+__all__ = ["HiFiGANGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking"]

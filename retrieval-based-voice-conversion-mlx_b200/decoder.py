@@ -154,6 +154,10 @@ class HiFiGANNSFGenerator(torch.nn.Module):
         return self
 
     # -- packed weights ----------------------------------------------------
+    def _decoder_state(self):
+        """The tensors rvcdec_load_weights receives (reference state_dict names)."""
+        return self.state_dict()
+
     def _weights_key(self):
         return tuple((p.data_ptr(), p._version, p.device.index) for p in self.parameters())
 
@@ -175,7 +179,7 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             self._applied_fused = self.fused_mrf
         key = self._weights_key()
         if key != self._packed_key:
-            self._handle.load_weights(self.state_dict())
+            self._handle.load_weights(self._decoder_state())
             self._packed_key = key
         return self._handle
 
@@ -259,3 +263,76 @@ class HiFiGANNSFGenerator(torch.nn.Module):
         h.forward_host(x.data_ptr(), f0.data_ptr(), gp, None, seed, out.data_ptr(), B, T, m, max_device_bytes)
         self.last_launch_count = h.launch_count()
         return out
+
+
+class HiFiGANGenerator(HiFiGANNSFGenerator):
+    """B200-native sibling decoder of the no-f0 models: ``HiFiGANGenerator``
+    (rvc/lib/algorithm/generators/hifigan.py:11-112, constructed at synthesizers.py:127-135) with the
+    reference's constructor, parameter names and ``forward(x, g) -> waveform``.
+
+    It is the NSF decoder without the harmonic source and the noise convs, and runs on the same kernels
+    through the same C ABI: the library is handed zero ``noise_convs`` / ``m_source`` tensors, so every
+    ``x + noise_convs[i](har)`` adds exactly 0 and the result equals the plain stack (hifigan.py:72-97).
+    (The source kernel and the stage-0 noise pass still run - about 2 % of a step; a config flag that skips
+    them is the obvious next step.)  Sub-modules are created in the reference's order, so a seeded default
+    init is bit-identical to the reference's."""
+
+    def __init__(self, initial_channel: int, resblock_kernel_sizes: list, resblock_dilation_sizes: list,
+                 upsample_rates: list, upsample_initial_channel: int, upsample_kernel_sizes: list, gin_channels: int = 0):
+        torch.nn.Module.__init__(self)
+        self.num_kernels = len(resblock_kernel_sizes)
+        self.num_upsamples = len(upsample_rates)
+        self.conv_pre = torch.nn.Conv1d(initial_channel, upsample_initial_channel, 7, 1, padding=3)
+        self.ups = torch.nn.ModuleList()
+        self.resblocks = torch.nn.ModuleList()
+        ch = upsample_initial_channel
+        for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
+            if u % 2 != 0:
+                raise ValueError("odd upsample rates are not supported by the B200 decoder (32k/40k/48k are all even)")
+            ch = upsample_initial_channel // (2 ** (i + 1))
+            self.ups.append(weight_norm(torch.nn.ConvTranspose1d(upsample_initial_channel // (2 ** i), ch, k, u, padding=(k - u) // 2)))
+            for kk, d in zip(resblock_kernel_sizes, resblock_dilation_sizes):
+                self.resblocks.append(ResBlock(ch, kk, d))
+        self.conv_post = torch.nn.Conv1d(ch, 1, 7, 1, padding=3, bias=False)
+        self.ups.apply(_burn_init_weights)
+        if gin_channels != 0:
+            self.cond = torch.nn.Conv1d(gin_channels, upsample_initial_channel, 1)
+        self.upp = math.prod(upsample_rates)
+        self.lrelu_slope = LRELU_SLOPE
+        self.checkpointing = False
+        self.mode = os.environ.get("RVC_B200_MODE", "fast")
+        self.noise_source = "philox"  # never used: the source output is multiplied by zero weights
+        self.max_workspace_bytes = int(os.environ.get("RVC_B200_MAX_WORKSPACE", "0"))
+        # the library's config carries a sample rate for the (unused) source; any valid value does
+        self._cfg_args = (initial_channel, list(resblock_kernel_sizes), [list(d) for d in resblock_dilation_sizes],
+                          list(upsample_rates), upsample_initial_channel, list(upsample_kernel_sizes), gin_channels, 48000)
+        self._gin = gin_channels
+        self._cin = initial_channel
+        self._rates = list(upsample_rates)
+        self._chs = [upsample_initial_channel // (2 ** (i + 1)) for i in range(len(upsample_rates))]
+        self.fused_mrf = int(os.environ["RVC_B200_FUSED_MRF"]) if "RVC_B200_FUSED_MRF" in os.environ else None
+        self._applied_fused = None
+        self._handle = None
+        self._packed_key = None
+        self._workspace = None
+        self.last_launch_count = 0
+
+    def _decoder_state(self):
+        sd = dict(self.state_dict())
+        sd["m_source.l_linear.weight"] = torch.zeros(1, 1)
+        sd["m_source.l_linear.bias"] = torch.zeros(1)
+        for i, C in enumerate(self._chs):
+            stride = math.prod(self._rates[i + 1:]) if i + 1 < len(self._rates) else 1
+            kernel = 1 if stride == 1 else stride * 2 - stride % 2
+            sd[f"noise_convs.{i}.weight"] = torch.zeros(C, 1, kernel)
+            sd[f"noise_convs.{i}.bias"] = torch.zeros(C)
+        return sd
+
+    def forward(self, x: torch.Tensor, g: Optional[torch.Tensor] = None, *, mode: Optional[str] = None):
+        f0 = torch.zeros(x.shape[0], x.shape[2], device=x.device, dtype=torch.float32)
+        return HiFiGANNSFGenerator.forward(self, x, f0, g, noise="philox", mode=mode)
+
+    def decode_host(self, x: torch.Tensor, g: Optional[torch.Tensor] = None, *, mode: Optional[str] = None,
+                    out: Optional[torch.Tensor] = None, device: Optional[int] = None, max_device_bytes: int = 0) -> torch.Tensor:
+        f0 = torch.zeros(x.shape[0], x.shape[2], dtype=torch.float32)
+        return HiFiGANNSFGenerator.decode_host(self, x, f0, g, mode=mode, out=out, device=device, max_device_bytes=max_device_bytes)

@@ -483,3 +483,28 @@ def test_batched_long_form_driver_matches_per_chunk_decode(dev):
     # host-buffer path (in-kernel noise): shape / range only
     yh = ch.decode_long(m, x, f0, g, mode="fast", split_points=splits, crossfade=240)
     assert yh.shape == (n_frames * cfg.upp,) and np.isfinite(yh).all() and float(np.abs(yh).max()) <= 1.0
+
+
+def test_nof0_sibling_decoder_matches_reference_golden(dev):
+    """rvc_b200.HiFiGANGenerator (the no-f0 models' decoder, hifigan.py:72-97) on the NSF kernels with zeroed
+    source / noise-conv layers, against the reference-generated golden output: fp32 mode to the fp32 bar, fast mode by
+    waveform correlation and relative max-abs error (the signal is quiet: no harmonic source feeds it)."""
+    from rvc_b200 import HiFiGANGenerator
+
+    d, cfg = load_golden("nof0_40k_B2_T20")
+    torch.manual_seed(int(d["init_seed"]))
+    m = HiFiGANGenerator(cfg.initial_channel, list(cfg.resblock_kernel_sizes), [list(r) for r in cfg.resblock_dilation_sizes],
+                         list(cfg.upsample_rates), cfg.upsample_initial_channel, list(cfg.upsample_kernel_sizes),
+                         gin_channels=cfg.gin_channels).eval().to(dev)
+    x, g, y_ref = torch.from_numpy(d["x"]), torch.from_numpy(d["g"]), torch.from_numpy(d["y"])
+    with torch.no_grad():
+        y32 = m(x.to(dev), g.to(dev), mode="fp32").cpu()
+        yf = m(x.to(dev), g.to(dev), mode="fast").cpu()
+        yh = m.decode_host(x, g, mode="fp32")
+    assert y32.shape == y_ref.shape
+    assert float((y32 - y_ref).abs().max()) <= 1e-5
+    assert torch.equal(yh, y32)
+    scale = float(y_ref.abs().max())
+    cc = float(torch.corrcoef(torch.stack([yf.flatten(), y_ref.flatten()]))[0, 1])
+    assert cc >= FAST_BAR, cc
+    assert float((yf - y_ref).abs().max()) <= 0.05 * scale, (float((yf - y_ref).abs().max()), scale)

@@ -88,3 +88,32 @@ def test_oracle_matches_live_reference():
     noise = O.draw_reference_noise(5, 1, 20 * cfg.upp)
     got = O.decoder_forward(O.folded_weights(ref.state_dict()), cfg, x, f0, g, noise)
     assert float((got - y).abs().max()) <= 2e-6
+
+
+def test_nof0_sibling_oracle_and_module_init_match_reference_golden():
+    """HiFiGANGenerator (hifigan.py:11-112, the decoder of the no-f0 models): the oracle restatement reproduces the
+    reference's output on the golden inputs, and rvc_b200.HiFiGANGenerator default-initialised under the same seed has
+    the reference's state_dict (names, shapes, per-tensor checksums)."""
+    import numpy as np
+    from helpers import load_golden
+    from rvc_b200 import HiFiGANGenerator
+
+    d, cfg = load_golden("nof0_40k_B2_T20")
+    torch.manual_seed(int(d["init_seed"]))
+    m = HiFiGANGenerator(cfg.initial_channel, list(cfg.resblock_kernel_sizes), [list(r) for r in cfg.resblock_dilation_sizes],
+                         list(cfg.upsample_rates), cfg.upsample_initial_channel, list(cfg.upsample_kernel_sizes),
+                         gin_channels=cfg.gin_channels).eval()
+    sd = m.state_dict()
+    assert sorted(sd.keys()) == sorted(k[4:] for k in d.files if k.startswith("ck::"))
+    for k in d.files:
+        if k.startswith("ck::"):
+            v = sd[k[4:]].double()
+            np.testing.assert_allclose(np.array([float(v.sum()), float(v.abs().sum())]), d[k], rtol=1e-12, atol=1e-12, err_msg=k)
+    y = O.generator_forward_nof0(O.folded_weights(sd), cfg, torch.from_numpy(d["x"]), torch.from_numpy(d["g"]))
+    assert float((y - torch.from_numpy(d["y"])).abs().max()) <= 5e-6
+    # the tensors handed to the C ABI add all-zero source / noise-conv layers under the NSF names
+    st = m._decoder_state()
+    assert st["noise_convs.0.weight"].shape == (256, 1, 80) and st["noise_convs.3.weight"].shape == (32, 1, 1)
+    assert all(float(st[k].abs().sum()) == 0.0 for k in st if k.startswith(("noise_convs.", "m_source.")))
+    with pytest.raises(RuntimeError):
+        m(torch.from_numpy(d["x"]), torch.from_numpy(d["g"]))  # CPU tensors: no fallback
