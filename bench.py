@@ -222,6 +222,9 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # stdout carries exactly one JSON line: NCCL writes its "NCCL version ..." banner (NCCL_DEBUG=VERSION and above)
         # and any warning to stdout by default, so its log is pointed at stderr
+        # (at level VERSION the banner is a bare printf to stdout; from WARN up it goes through NCCL's log file)
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     B, T = args.chunks, args.frames
