@@ -256,13 +256,18 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
           const int t_in = t0 + (wg & 1) * 128 + q * 32 + lane;
           const float* hb = e.nz_har + (size_t)b * e.nz_src;
           const int s0 = (t_in * U + (n_tile & 1) * PH) * NZS - (NZK - NZS) / 2;  // even
-          if (t_in < p.L_in && s0 >= 0 && s0 + NH <= e.nz_src) {
-            const float2* h2p = reinterpret_cast<const float2*>(hb + s0);
+          constexpr int NR4 = (NH + 2 + 3) / 4;
+          if (t_in < p.L_in && s0 >= 2 && s0 - 2 + NR4 * 4 <= e.nz_src) {
+            // s0 - 2 is a multiple of 4 samples: 16 B loads (7 instead of 12 requests per lane on the L1 data pipe)
+            const float4* h4p = reinterpret_cast<const float4*>(hb + s0 - 2);
+            float raw[NR4 * 4];
 #pragma unroll
-            for (int j = 0; j < NH / 2; ++j) {
-              const float2 h2 = __ldg(h2p + j);
-              hv[2 * j] = h2.x; hv[2 * j + 1] = h2.y;
+            for (int j = 0; j < NR4; ++j) {
+              const float4 h4 = __ldg(h4p + j);
+              raw[4 * j] = h4.x; raw[4 * j + 1] = h4.y; raw[4 * j + 2] = h4.z; raw[4 * j + 3] = h4.w;
             }
+#pragma unroll
+            for (int j = 0; j < NH; ++j) hv[j] = raw[j + 2];
           } else {
 #pragma unroll
             for (int j = 0; j < NH / 2; ++j) {
