@@ -128,6 +128,9 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *                    coalesced epilogue; on a per-conv MRF stage whose noise conv has 8 taps (stage 1) the epilogue
  *                    also adds noise_convs[i](har) (:199) and writes the ResBlocks' activated 16-bit operand, which
  *                    replaces the noise_add pass.  0 = one phase per N tile with the scatter epilogue.
+ *   "no_source"  1 = the decoder has no harmonic source and no noise convs - the reference's sibling HiFiGANGenerator
+ *                    (rvc/lib/algorithm/generators/hifigan.py:72-97, the no-f0 models): the source kernel and every
+ *                    x + noise_convs[i](har) are skipped (f0 / noise arguments are ignored); 0 = (default) NSF decoder.
  *   "conv_epi_warps" / "conv_epi_warps_small"  16 (default) or 8 epilogue warps in the 128-wide / the 64- and 32-wide
  *                    conv_mma tilings; 16 warps work on 16-column items, 8 warps on 32-column items (profiles/r1bq, r1br).
  *   "pm_a_stages" 2 (default) or 3 activation stages of the rate-10 phase-major tile (no measurable difference).

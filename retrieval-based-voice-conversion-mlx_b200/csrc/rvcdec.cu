@@ -97,6 +97,8 @@ struct rvcdec_handle {
   long long* d_timing = nullptr;
   int timing_launches = 0;
   static constexpr int kTimingMaxLaunches = 32;
+  int no_source = 0;   // 1 = no harmonic source / noise convs (the no-f0 sibling HiFiGANGenerator, hifigan.py:72-97): the source
+                       // kernel is skipped and no stage adds noise_convs[i](har)
   int conv_epi_warps = 16;  // (profiles/r1bq: 16 warps 214 ms vs 8 warps 221 ms on the 128-channel stage) epilogue warps of the 128-wide conv_mma tiling (8 over 32-column items, 16 over 16-column items)
   int conv_epi_warps_small = 16;  // same for the 64- / 32-wide tilings (profiles/r1br: ups2 21.8 -> 17.6 ms, ups3 13.9 -> 12.3 ms)
   int pm_a_stages = 2; // activation ring depth of the rate-10 phase-major upsample tile (2 or 3)
@@ -325,6 +327,7 @@ bool use_ups_pm(const rvcdec_handle* h, int mode, int i) {
 // ... and also carries the stage's noise conv (8 taps, stride 4) in its epilogue.
 bool pm_noise(const rvcdec_handle* h, int mode, int i) {
   if (!use_ups_pm(h, mode, i)) return false;
+  if (h->no_source) return true;  // nothing to add: any phase-major upsample qualifies
   const NoiseLayer& nl = h->noise[i];
   return nl.k == 8 && nl.stride == 4 && nl.pad == 2;
 }
@@ -647,8 +650,13 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   SourceParams sp{};
   sp.f0 = f0; sp.noise = noise; sp.har = w.har; sp.seed = seed + 0x9E3779B97F4A7C15ull * item0;
   sp.B = B; sp.T = T; sp.upp = h->upp; sp.sr = (float)c.sr; sp.lin_w = h->lin_w; sp.lin_b = h->lin_b;
-  MARK("source", 0, (double)B * T * h->upp * (noise ? 8 : 4));
-  CK(launch_source(sp, s)); ++h->launches;
+  if (h->no_source) {
+    // stages that still run the noise_add pass (for its activated operand copy) multiply har by zero weights
+    CK(cudaMemsetAsync(w.har, 0, (size_t)B * T * h->upp * sizeof(float), s));
+  } else {
+    MARK("source", 0, (double)B * T * h->upp * (noise ? 8 : 4));
+    CK(launch_source(sp, s)); ++h->launches;
+  }
   if (stop == 1) { MARK(nullptr, 0, 0); return 0; }
 
   MARK("prep", 0, (double)B * c.initial_channel * T * (4 + act_bytes(fpre)));
@@ -682,7 +690,8 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     const NoiseLayer& nl = h->noise[i];
     // Short noise convs ride in the upsample epilogue when the stage runs the fused MRF kernel (which
     // reads the fp32 stage input only, so no activated 16-bit copy is needed).
-    const bool fuse_other = nl.k <= 8 && (use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i)));
+    const bool nz_epi = nl.k <= 8 || h->no_source;  // the noise conv can ride in (or is absent from) an upsample epilogue
+    const bool fuse_other = nz_epi && (use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i)));
     const bool pm = use_ups_pm(h, mode, i) && (!fuse_other || pm_noise(h, mode, i)), pma = pm_act(h, mode, i);
     const bool pmn = pm_noise(h, mode, i) && (pma || use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i)));
     const bool fuse_noise = pmn || (nl.k <= 8 && (use_fused_mrf(h, mode, i) || (h->pair_noise && use_pair_mrf(h, mode, i))));
@@ -694,7 +703,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
       Epilogue e{};
       e.bias = h->ups_zs[i].d_bias; e.scale = 1.f; e.slope = 0.1f;
       e.out_f32 = w.xs0; e.up = 1; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
-      if (nl.k <= 8) {  // the coalesced epilogue carries noise convs of up to 8 taps
+      if (nl.k <= 8 && !h->no_source) {  // the coalesced epilogue carries noise convs of up to 8 taps
         e.nz_har = w.har; e.nz_w = nl.d_w; e.nz_bias = nl.d_bias;
         e.nz_k = nl.k; e.nz_stride = nl.stride; e.nz_pad = nl.pad; e.nz_src = T * h->upp;
       }
@@ -706,7 +715,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
       Epilogue e{};
       e.bias = UL.d_bias; e.scale = 1.f; e.slope = 0.1f; e.pm = pm ? 1 : 0;
       e.out_f32 = w.xs0; e.up = u; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
-      if (fuse_noise) {  // ... + noise_convs[i](har_source)  (:199)
+      if (fuse_noise && !h->no_source) {  // ... + noise_convs[i](har_source)  (:199)
         e.nz_har = w.har; e.nz_w = nl.d_w; e.nz_bias = nl.d_bias;
         e.nz_k = nl.k; e.nz_stride = nl.stride; e.nz_pad = nl.pad; e.nz_src = T * h->upp;
       }
@@ -719,8 +728,8 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
     }
     // (after the upsample has read the previous stage's tensor out of a0: new geometry, new pad rows)
     if (pma) { CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
-    else if ((fuse_noise || (zs_in && nl.k <= 8)) && !zs_out) { CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
-    if (!fuse_noise && !(zs_in && nl.k <= 8)) {
+    else if ((fuse_noise || (zs_in && nz_epi)) && !zs_out) { CK(launch_zero_pads(w.a0, nullptr, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches; }
+    if (!fuse_noise && !(zs_in && nz_epi)) {
       MARK(g_noise.c_str(), 2.0 * B * Lo * C * nl.k, (double)B * Lo * C * (8 + act_bytes(fs)));
       CK(launch_zero_pads(w.a0, w.a1, w.a2, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches;
       // x = x + noise_convs[i](har_source)  (:199)
@@ -1206,6 +1215,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     if (!value && h->d_timing) { cudaFree(h->d_timing); h->d_timing = nullptr; }
     if (h->d_timing) CK(cudaMemset(h->d_timing, 0, sizeof(long long) * rvcdec_handle::kTimingMaxLaunches * h->num_sms * 16));
     h->timing_launches = 0;
+    return 0;
+  }
+  if (k == "no_source") {
+    if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "no_source must be 0 or 1");
+    h->no_source = (int)value;
     return 0;
   }
   if (k == "conv_epi_warps") {

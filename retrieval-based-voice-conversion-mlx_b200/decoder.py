@@ -272,9 +272,8 @@ class HiFiGANGenerator(HiFiGANNSFGenerator):
 
     It is the NSF decoder without the harmonic source and the noise convs, and runs on the same kernels
     through the same C ABI: the library is handed zero ``noise_convs`` / ``m_source`` tensors, so every
-    ``x + noise_convs[i](har)`` adds exactly 0 and the result equals the plain stack (hifigan.py:72-97).
-    (The source kernel and the stage-0 noise pass still run - about 2 % of a step; a config flag that skips
-    them is the obvious next step.)  Sub-modules are created in the reference's order, so a seeded default
+    ``x + noise_convs[i](har)`` would add exactly 0, and the handle option ``no_source`` makes it skip the
+    source kernel and those additions altogether (hifigan.py:72-97).  Sub-modules are created in the reference's order, so a seeded default
     init is bit-identical to the reference's."""
 
     def __init__(self, initial_channel: int, resblock_kernel_sizes: list, resblock_dilation_sizes: list,
@@ -327,6 +326,13 @@ class HiFiGANGenerator(HiFiGANNSFGenerator):
             sd[f"noise_convs.{i}.weight"] = torch.zeros(C, 1, kernel)
             sd[f"noise_convs.{i}.bias"] = torch.zeros(C)
         return sd
+
+    def _ensure_handle(self, device: torch.device) -> _lib.Handle:
+        fresh = self._handle is None or self._handle.device != (device.index if device.index is not None else torch.cuda.current_device())
+        h = HiFiGANNSFGenerator._ensure_handle(self, device)
+        if fresh:
+            h.set_option("no_source", 1)  # skip the source kernel and the noise adds (they would add exactly 0)
+        return h
 
     def forward(self, x: torch.Tensor, g: Optional[torch.Tensor] = None, *, mode: Optional[str] = None):
         f0 = torch.zeros(x.shape[0], x.shape[2], device=x.device, dtype=torch.float32)

@@ -501,6 +501,16 @@ def test_nof0_sibling_decoder_matches_reference_golden(dev):
         y32 = m(x.to(dev), g.to(dev), mode="fp32").cpu()
         yf = m(x.to(dev), g.to(dev), mode="fast").cpu()
         yh = m.decode_host(x, g, mode="fp32")
+        m(x.to(dev), g.to(dev), mode="fast")
+        n_skip = m.last_launch_count
+        # option "no_source" = 0: source kernel + noise adds run and add exactly 0 (all-zero layers)
+        m._handle.set_option("no_source", 0)
+        y32_z = m(x.to(dev), g.to(dev), mode="fp32").cpu()
+        yf_z = m(x.to(dev), g.to(dev), mode="fast").cpu()
+        n_full = m.last_launch_count
+        m._handle.set_option("no_source", 1)
+    assert n_skip < n_full, (n_skip, n_full)
+    assert torch.equal(y32_z, y32) and torch.equal(yf_z, yf)
     assert y32.shape == y_ref.shape
     assert float((y32 - y_ref).abs().max()) <= 1e-5
     assert torch.equal(yh, y32)
