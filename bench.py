@@ -168,6 +168,13 @@ def measured_traffic(B, T, steps, spans):
         return None, f"no capture: {e}"
 
 
+def workload_config(B, T, mode):
+    """The `config` object of both arms (the reference arm times a bounded sample of the same workload)."""
+    return {"workload": f"RVCv2 48kHz HiFiGAN-NSF decoder, {B} x {T / 100:.0f} s padded chunks per GPU (BASELINE configs[3]: 1024 x 30 s over 8 GPUs), "
+                        f"mode={mode}, random-init weights seed 1234, in-kernel Philox source noise",
+            "chunks_per_gpu": B, "frames_per_chunk": T, "l2": "inputs (295 MB/step) and activations (GBs/layer) exceed the 126 MB L2; no flush needed"}
+
+
 # ------------------------------------------------------------------ arms
 def cpu_reference_throughput(T: int, reps: int, warm: int):
     """The reference's CPU implementation of the path = the oracle port (torch CPU fp32), all host threads."""
@@ -199,10 +206,10 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": thr, "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "RVCv2 48kHz HiFiGAN-NSF decoder, 30 s padded chunks (BASELINE configs[3]); CPU arm timed on a bounded "
-                               "sample: one 10 s chunk (T=1000) per step"},
+        "config": workload_config(args.chunks, args.frames, args.mode),
         "cpu_baseline": {"value": thr, "unit": "audio-s/s", "cores": cores, "kind": "port",
-                         "sample": "oracle port (torch CPU fp32 restatement of hifigan_nsf.py:173-212), B=1, T=1000 frames per step"},
+                         "sample": "oracle port (torch CPU fp32 restatement of hifigan_nsf.py:173-212) timed on a bounded sample of "
+                                   "the workload: one 10 s chunk (B=1, T=1000 frames, same per-frame work) per step"},
         "e2e": {"value": thr, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -316,9 +323,7 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.mode == "fp32" else "bf16/f16 operands, f32 accumulate", "data": "synthetic",
-        "config": {"workload": f"RVCv2 48kHz HiFiGAN-NSF decoder, {B} x {T / 100:.0f} s padded chunks per GPU (BASELINE configs[3]: 1024 x 30 s over 8 GPUs), "
-                               f"mode={args.mode}, random-init weights seed 1234, in-kernel Philox source noise",
-                   "chunks_per_gpu": B, "frames_per_chunk": T, "l2": "inputs (295 MB/step) and activations (GBs/layer) exceed the 126 MB L2; no flush needed"},
+        "config": workload_config(B, T, args.mode),
         "clocks": clocks, "gpu_launches": launches,
         "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "roofline": roof, "peaks": {"source": pk_kind, "hbm_gbs": pk["hbm_gbs"], "bf16_tflops_sustained": pk["bf16_tflops_sustained"],

@@ -518,3 +518,26 @@ def test_nof0_sibling_decoder_matches_reference_golden(dev):
     cc = float(torch.corrcoef(torch.stack([yf.flatten(), y_ref.flatten()]))[0, 1])
     assert cc >= FAST_BAR, cc
     assert float((yf - y_ref).abs().max()) <= 0.05 * scale, (float((yf - y_ref).abs().max()), scale)
+
+
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 75, 71), ("40k", 1, 33, 72)])
+def test_conv_epilogue_shape_options_are_bit_identical(dev, cfg_name, B, T, seed):
+    """rvcdec_set_option("conv_epi_warps" / "conv_epi_warps_small" / "pm_a_stages"): 8 epilogue warps over 32-column
+    items or 16 over 16-column items, two or three activation stages - launch shapes of the same arithmetic, so the
+    waveforms must be bit-identical (per-conv MRF path everywhere so that every tiling is exercised)."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K}[cfg_name]
+    m = build_module(cfg, 8000 + seed).to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    outs = []
+    with torch.no_grad():
+        m.fused_mrf = 0
+        h = m._ensure_handle(dev)
+        for ew, ews, pas in ((16, 16, 2), (8, 8, 2), (16, 8, 3), (8, 16, 3)):
+            h.set_option("conv_epi_warps", ew)
+            h.set_option("conv_epi_warps_small", ews)
+            h.set_option("pm_a_stages", pas)
+            outs.append(m(xd, fd, gd, noise=nd_, mode="fast").cpu())
+        h.set_option("conv_epi_warps", 16); h.set_option("conv_epi_warps_small", 16); h.set_option("pm_a_stages", 2)
+    for y in outs[1:]:
+        assert torch.equal(y, outs[0])
