@@ -296,7 +296,6 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
         constexpr int PH = Cfg::PH;
         constexpr int NC = PH * 8;       // columns (= floats per thread) of one slice
         constexpr int NZS = 4, NZK = 8;  // the fused noise conv: stride 4, 8 taps, pad 2 (checked by the host)
-        constexpr int NH = NZS * PH + NZK - NZS;
         constexpr int U = 2 * PH;        // upsample rate == 16 B pieces per staged run
         constexpr int RUNS = 32 / U;     // runs one store instruction covers (lanes >= RUNS*U idle)
         constexpr int ITER = (32 + RUNS - 1) / RUNS;
@@ -310,8 +309,6 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
         {
           const int mb = wg & 1;
           const int tb = t0 + mb * 128 + q * 32;
-          const int t_in = tb + lane;
-          const bool valid = t_in < p.L_in;
           uint64_t a2[NC / 2];  // packed fp32 pairs (FADD2 / FFMA2)
           {
             const uint32_t t_col = t_acc + mb * N_TILE + sl * NC;

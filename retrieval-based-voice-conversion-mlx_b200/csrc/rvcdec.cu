@@ -321,6 +321,7 @@ bool zs_out_stage(const rvcdec_handle* h, int mode, int i) {
 // Stage i's upsample runs the phase-major tensor-core image (fast modes, dense input).
 bool use_ups_pm(const rvcdec_handle* h, int mode, int i) {
   if (mode == 0 || !h->ups_pm_on || i < 0 || i >= h->nups || !h->ups_pm[i].n_tile) return false;
+  if (h->ch[i] > 256) return false;  // the kernel keeps the per-channel bias of at most 256 channels in shared memory
   if (i > 0 && zs_out_stage(h, mode, i - 1)) return false;
   return true;
 }
@@ -329,7 +330,7 @@ bool pm_noise(const rvcdec_handle* h, int mode, int i) {
   if (!use_ups_pm(h, mode, i)) return false;
   if (h->no_source) return true;  // nothing to add: any phase-major upsample qualifies
   const NoiseLayer& nl = h->noise[i];
-  return nl.k == 8 && nl.stride == 4 && nl.pad == 2;
+  return nl.k == 8 && nl.stride == 4 && nl.pad == 2 && h->ch[i] <= 128;  // (8 taps x 128 channels of shared memory)
 }
 // ... and, when the stage runs the per-conv MRF path, writes the activated 16-bit operand copy (a0) as well, which
 // replaces the noise_add pass.  The upsample then must not read its input out of a0: the previous stage (per-conv
