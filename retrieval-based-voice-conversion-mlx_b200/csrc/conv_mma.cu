@@ -2,13 +2,16 @@
 //
 //   D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]      (fp32 accumulate in TMEM)
 //
-// CTA = 10 warps, warp-specialised, persistent over (item, time-tile, N-tile):
+// CTA = 18 warps (10 with EW = 8), warp-specialised, persistent over (item, time-tile, N-tile):
 //   warp 0   TMA producer   1-D bulk copies (cp.async.bulk, UBLKCP) of activation slices and
 //                           weight blocks into shared memory, completion on mbarriers
 //   warp 1   MMA issuer     one thread issues tcgen05.mma (kind::f16, M=128, N=N_TILE, K=16),
 //                           tcgen05.commit releases smem stages / publishes the accumulator
-//   warps 2-9 epilogue      tcgen05.ld accumulator -> registers -> fused epilogue (bias, residual,
-//                           MRF average, leaky_relu, 16-bit convert) -> coalesced global stores
+//   warps 2-17 epilogue     tcgen05.ld accumulator -> registers -> fused epilogue (bias, residual,
+//                           MRF average, leaky_relu, 16-bit convert) -> coalesced global stores;
+//                           16 warps over 16-column items (EW = 16, default) or 8 over 32-column items;
+//                           every global load of an item is issued before the (volatile) TMEM load
+//   PM = 1                  phase-major polyphase upsample tiles with a warp-transposed epilogue (see below)
 //
 // Shared-memory operand layout: NO swizzle, K-major "interleaved" core matrices.  The blocked-8
 // HBM layout ([slice][row][8 ch]) copied verbatim IS that layout: 8 rows x 16 B core matrices,
