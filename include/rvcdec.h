@@ -45,7 +45,12 @@ typedef enum {
  *   FP32: CUDA-core FFMA kernels, fp32 everywhere (parity mode, <= 2e-3 max-abs).
  *   FAST: tcgen05 tensor-core implicit GEMMs, 16-bit operands, fp32 accumulate,
  *         fp32 residual stream (>= 0.999 multi-resolution log-mel correlation). */
-typedef enum { RVCDEC_MODE_FP32 = 0, RVCDEC_MODE_FAST = 1 } rvcdec_mode;
+typedef enum {
+  RVCDEC_MODE_FP32 = 0,
+  RVCDEC_MODE_FAST = 1,       /* bf16 operands up to and including stage 1, fp16 after (the default fast plan) */
+  RVCDEC_MODE_FAST_F16 = 2,   /* fp16 operands everywhere (experiments; range-unsafe for arbitrary checkpoints) */
+  RVCDEC_MODE_FAST_BF16 = 3   /* bf16 operands everywhere (experiments; misses the fast-mode bar, SURVEY 8d probe) */
+} rvcdec_mode;
 
 /* The constructor values of the reference class, hifigan_nsf.py:75-86
  * (checkpointing is training-only and has no counterpart here). */

@@ -100,13 +100,15 @@ __global__ void __launch_bounds__(SRC_THREADS) source_kernel(SourceParams p) {
   const int nframes = min(SRC_FPB, p.T - l0);
   const int nsamp = nframes * p.upp;
   const size_t base = (size_t)b * p.T * p.upp + (size_t)l0 * p.upp;
+  // Philox counter of sample 0 of this span: indexed by the GLOBAL item (item0 + b), not by the position in the launch
+  const uint64_t pbase = (p.item0 + (uint64_t)b) * (uint64_t)p.T * (uint64_t)p.upp + (uint64_t)l0 * (uint64_t)p.upp;
   for (int i = threadIdx.x; i < nsamp; i += SRC_THREADS) {
     const int fr = i / p.upp;
     const int k = i - fr * p.upp;
     const double ph = s_finc[fr] * (double)(k + 1) + s_C[fr];
     const float frac = (float)(ph - floor(ph));
     const float sine = 0.1f * sinpif(2.0f * frac);
-    const float z = p.noise ? __ldg(p.noise + base + i) : philox_normal(p.seed, base + i);
+    const float z = p.noise ? __ldg(p.noise + base + i) : philox_normal(p.seed, pbase + (uint64_t)i);
     const float v = (s_f0[fr] > 0.f) ? (sine + 0.003f * z) : ((0.1f / 3.0f) * z);
     p.har[base + i] = tanhf(p.lin_w * v + p.lin_b);
   }
@@ -429,7 +431,7 @@ __global__ void __launch_bounds__(256) post7_kernel(const float* __restrict__ x,
       }
     }
     float* o = out + (size_t)b * L + t0;
-    if (t0 + 3 < L && ((((size_t)b * L + t0) & 3) == 0)) {
+    if (t0 + 3 < L && ((reinterpret_cast<uintptr_t>(o) & 15u) == 0)) {
       *reinterpret_cast<float4*>(o) = make_float4(tanhf(acc[0]), tanhf(acc[1]), tanhf(acc[2]), tanhf(acc[3]));
     } else {
 #pragma unroll

@@ -263,7 +263,9 @@ struct SourceParams {
   const float* f0;      // (B, T)
   const float* noise;   // (B, T*upp) or null
   float* har;           // (B, T*upp)
-  uint64_t seed;
+  uint64_t seed;     // Philox key of the whole call
+  uint64_t item0;    // global index of item 0 of this launch: draw (item, sample) is a function of (seed, item0 + b, sample)
+                     // only, so the waveform does not depend on how a batch is cut into passes
   int B, T, upp;
   float sr, lin_w, lin_b;
 };

@@ -65,6 +65,18 @@ struct NoiseLayer {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// Every entry point runs on the handle's device and leaves the caller's current device as it found it
+// (one process may drive several GPUs, one handle each).
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) err = cudaSetDevice(dev); else prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 }  // namespace
 
 struct rvcdec_handle {
@@ -418,7 +430,9 @@ int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, 
   p.epi_warps_small = h->conv_epi_warps_small;
   if (mode == 0) {
     p.w = L.d_wf;
-    for (size_t i = 0; i < L.mask_f32.size() && i < (size_t)MAX_NTILES; ++i) p.tapmask[i] = L.mask_f32[i];
+    if (L.mask_f32.size() > (size_t)MAX_NTILES)
+      return fail(RVCDEC_ERR_ARG, "layer %s: %d GEMM columns exceed the fp32 back-end's %d tap masks of 64 columns", L.name.c_str(), L.N_total, MAX_NTILES);
+    for (size_t i = 0; i < L.mask_f32.size(); ++i) p.tapmask[i] = L.mask_f32[i];
     CK(launch_conv_f32(p, s));
   } else {
     if (!L.n_tile) return fail(RVCDEC_ERR_ARG, "layer %s has no tensor-core tiling (N=%d, Cin=%d)", L.name.c_str(), L.N_total, L.Cin);
@@ -649,7 +663,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   const int fpre = fmt_pre(mode);
 
   SourceParams sp{};
-  sp.f0 = f0; sp.noise = noise; sp.har = w.har; sp.seed = seed + 0x9E3779B97F4A7C15ull * item0;
+  sp.f0 = f0; sp.noise = noise; sp.har = w.har; sp.seed = seed; sp.item0 = item0;
   sp.B = B; sp.T = T; sp.upp = h->upp; sp.sr = (float)c.sr; sp.lin_w = h->lin_w; sp.lin_b = h->lin_b;
   if (h->no_source) {
     // stages that still run the noise_add pass (for its activated operand copy) multiply har by zero weights
@@ -867,7 +881,7 @@ void rvcdec_destroy(rvcdec_handle* h) {
   if (!h) return;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) == cudaSuccess && h->device < ndev) {
-    cudaSetDevice(h->device);
+    DeviceGuard dguard(h->device);
     free_device(h);
     if (h->d_timing) cudaFree(h->d_timing);
     if (h->hbuf) cudaFree(h->hbuf);
@@ -1031,7 +1045,8 @@ int rvcdec_load_weights(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t 
     h->loaded = false;
     return fail(RVCDEC_ERR_CUDA, "no CUDA device: %s", cudaGetErrorString(e));
   }
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dguard(h->device);
+  CK(dguard.err);
   free_device(h);
   if ((rc = upload_layer(h, h->conv_pre))) return rc;
   for (auto& L : h->ups) if ((rc = upload_layer(h, L))) return rc;
@@ -1072,7 +1087,8 @@ int rvcdec_forward(rvcdec_handle* h, const float* x, const float* f0, const floa
   int rc = check_forward_args(h, x, f0, g, out, B, T, mode);
   if (rc) return rc;
   if (!workspace) return fail(RVCDEC_ERR_ARG, "null workspace");
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dguard(h->device);
+  CK(dguard.err);
   const size_t per1 = carve(h, nullptr, 1, T, mode).bytes;
   if (workspace_bytes < per1) return fail(RVCDEC_ERR_WORKSPACE, "workspace of %zu bytes cannot hold one item (%zu needed)", workspace_bytes, per1);
   int Bm = B;
@@ -1094,7 +1110,8 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
                         uint64_t seed, float* out, int32_t B, int32_t T, int32_t mode, size_t max_device_bytes) {
   int rc = check_forward_args(h, x, f0, g, out, B, T, mode);
   if (rc) return rc;
-  CK(cudaSetDevice(h->device));
+  DeviceGuard dguard(h->device);
+  CK(dguard.err);
   if (!h->stream) CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   if (!h->h2d_stream) {
     CK(cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
@@ -1141,6 +1158,9 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
   }
   void* ws = p;
   h->launches = 0;
+  // The pass loop queues copies on three streams; whatever way it ends, nothing may still be in flight into the
+  // caller's buffers when this function returns (the caller is free to release `out` / `x` right away).
+  auto run_passes = [&]() -> int {
   int pass = 0;
   for (int b0 = 0; b0 < B; b0 += Bm, ++pass) {
     const int nb = std::min(Bm, B - b0);
@@ -1163,8 +1183,13 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
     CK(cudaMemcpyAsync(out + b0 * n, dout[s2], nb * n * 4, cudaMemcpyDeviceToHost, h->d2h_stream));
     CK(cudaEventRecord(h->ev_out[s2], h->d2h_stream));
   }
-  CK(cudaStreamSynchronize(h->d2h_stream));
-  CK(cudaStreamSynchronize(h->stream));
+  return 0;
+  };
+  rc = run_passes();
+  const cudaError_t e1 = cudaStreamSynchronize(h->h2d_stream), e2 = cudaStreamSynchronize(h->stream),
+                    e3 = cudaStreamSynchronize(h->d2h_stream);
+  if (rc) return rc;  // (message of the first failure is kept)
+  CK(e1); CK(e2); CK(e3);
   return 0;
 }
 
@@ -1209,8 +1234,9 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
   if (!h || !key) return fail(RVCDEC_ERR_ARG, "null argument");
   const std::string k = key;
   if (k == "fused_timing") {  // allocate / reset the timing buffer of the instrumented fused kernel
+    DeviceGuard dguard(h->device);
+    CK(dguard.err);
     if (value && !h->d_timing) {
-      CK(cudaSetDevice(h->device));
       CK(cudaMalloc(&h->d_timing, sizeof(long long) * rvcdec_handle::kTimingMaxLaunches * h->num_sms * 16));
     }
     if (!value && h->d_timing) { cudaFree(h->d_timing); h->d_timing = nullptr; }
@@ -1293,6 +1319,8 @@ int rvcdec_debug_set_stop(rvcdec_handle* h, int32_t stop_after) {
 int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_t dst_numel, void* workspace,
                           int32_t B, int32_t T, int32_t mode, void* stream) {
   if (!h || !name || !dst || !workspace) return fail(RVCDEC_ERR_ARG, "null argument");
+  DeviceGuard dguard(h->device);
+  CK(dguard.err);
   Workspace w = carve(h, workspace, B, T, mode);
   const std::string nm = name;
   cudaStream_t s = (cudaStream_t)stream;
@@ -1337,6 +1365,8 @@ int64_t rvcdec_debug_fused_timing(rvcdec_handle* h, int64_t* dst, int64_t dst_nu
   if (!h->d_timing) return 0;
   const int64_t n = (int64_t)h->timing_launches * h->num_sms * 16;
   if (dst_numel < n) return fail(RVCDEC_ERR_ARG, "destination too small");
+  DeviceGuard dguard(h->device);
+  CK(dguard.err);
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpy(dst, h->d_timing, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost));
   return h->timing_launches;

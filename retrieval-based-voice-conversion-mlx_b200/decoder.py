@@ -138,6 +138,8 @@ class HiFiGANNSFGenerator(torch.nn.Module):
         self._handle: Optional[_lib.Handle] = None
         self._packed_key = None
         self._workspace: Optional[torch.Tensor] = None
+        self._ws_event = None
+        self._ws_stream = None
         self.last_launch_count = 0
 
     # -- reference protocol ------------------------------------------------
@@ -192,6 +194,10 @@ class HiFiGANNSFGenerator(torch.nn.Module):
         return ws
 
     # -- forward -----------------------------------------------------------
+    def _draw_seed(self) -> int:
+        """One 63-bit Philox key per call from the torch CPU generator (so ``torch.manual_seed`` reproduces a decode)."""
+        return int(torch.randint(0, 2 ** 62, (1,)).item())
+
     def forward(self, x: torch.Tensor, f0: torch.Tensor, g: Optional[torch.Tensor] = None, *,
                 noise: Optional[torch.Tensor] = None, mode: Optional[str] = None):
         from . import ops  # registers the custom op
@@ -217,7 +223,7 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             elif noise == "philox":
                 # in-kernel draws: one 63-bit key from the torch CPU generator per call
                 noise = None
-                seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+                seed = self._draw_seed()
             else:
                 raise ValueError("noise must be a tensor, 'torch' or 'philox'")
         if noise is not None:
@@ -233,7 +239,16 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             have = self._workspace.numel() if (self._workspace is not None and self._workspace.device == x.device) else 0
             cap = need if have >= need else int(0.7 * (torch.cuda.mem_get_info(x.device)[0] + have))
         ws = self._get_workspace(min(need, max(cap, h.workspace_bytes(1, T, m))), x.device)
+        # the cached scratch is shared by every forward of this module: a call on another stream must wait for the
+        # previous call's kernels before it overwrites it
+        cur = torch.cuda.current_stream(x.device)
+        if self._ws_event is not None and self._ws_stream != cur.cuda_stream:
+            cur.wait_event(self._ws_event)
         out = ops.nsf_hifigan_decode(x.contiguous().float(), f0.contiguous().float(), g, noise, ws, h.ptr.value, m, self.upp, seed)
+        if self._ws_event is None:
+            self._ws_event = torch.cuda.Event()
+        self._ws_event.record(cur)
+        self._ws_stream = cur.cuda_stream
         self.last_launch_count = h.launch_count()
         return out.unsqueeze(1)
 
@@ -257,9 +272,15 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             g = g.reshape(B, self._gin).contiguous().float()
             gp = g.data_ptr()
         n = T * self.upp
+        if Cx != self._cin or tuple(f0.shape) != (B, T):
+            raise ValueError(f"expected x (B,{self._cin},T) and f0 (B,T); got {tuple(x.shape)} and {tuple(f0.shape)}")
         if out is None:
             out = torch.empty(B, 1, n, dtype=torch.float32, pin_memory=True)
-        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        elif out.is_cuda or out.dtype != torch.float32 or not out.is_contiguous() or out.numel() != B * n:
+            # the library DMAs B*T*upp floats into this buffer: anything else would be overrun
+            raise ValueError(f"out must be a contiguous CPU float32 tensor of {B * n} elements (B*T*upp); got "
+                             f"{tuple(out.shape)} {out.dtype} on {out.device}")
+        seed = self._draw_seed()
         h.forward_host(x.data_ptr(), f0.data_ptr(), gp, None, seed, out.data_ptr(), B, T, m, max_device_bytes)
         self.last_launch_count = h.launch_count()
         return out
@@ -314,7 +335,13 @@ class HiFiGANGenerator(HiFiGANNSFGenerator):
         self._handle = None
         self._packed_key = None
         self._workspace = None
+        self._ws_event = None
+        self._ws_stream = None
         self.last_launch_count = 0
+
+    def _draw_seed(self) -> int:
+        # the reference's no-f0 decoder draws nothing (hifigan.py:72-97): leave the caller's RNG stream alone
+        return 0
 
     def _decoder_state(self):
         sd = dict(self.state_dict())

@@ -21,3 +21,22 @@ def built_lib():
     if not os.path.exists(_lib.LIB_PATH):
         ge.build()
     return _lib.lib()
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """GPU runs leave the measured parity margins (helpers.record_parity) where gpurun brings them back."""
+    import json
+
+    try:
+        import helpers
+    except Exception:
+        return
+    if not helpers._PARITY:
+        return
+    out = os.environ.get("RVC_PARITY_RECORD", os.path.join(ROOT, "gpurun_out", "parity_r2.json"))
+    try:
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        with open(out, "w") as f:
+            json.dump({"bars": {"fp32_max_abs": 2e-3, "fast_min_logmel_corr": 0.999}, "records": helpers._PARITY}, f, indent=1)
+    except OSError:
+        pass

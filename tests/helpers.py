@@ -55,3 +55,41 @@ def tensors(d):
     noise = torch.from_numpy(d["noise"])
     y = torch.from_numpy(d["y"])
     return x, f0, g, noise, y
+
+
+# ---- round-2 helpers -----------------------------------------------------------------------------------------------
+def load_real_case():
+    """tests/golden/real_48k_T1350.npz (oracle/make_golden_r2.py): inputs re-created from seeds and verified against the
+    fixture's checksums, the reference's real RMVPE contour, and the stored pieces of the reference's waveform."""
+    d = np.load(os.path.join(GOLDEN, "real_48k_T1350.npz"))
+    cfg = O.CONFIG_48K
+    T = d["f0"].shape[1]
+    x, _, g, _ = O.synth_inputs(cfg, 1, T, seed=int(d["in_seed"]))
+    noise = O.draw_reference_noise(int(d["noise_seed"]), 1, T * cfg.upp)
+    for name, t in (("x", x), ("g", g), ("noise", noise)):
+        got = np.array([float(t.double().sum()), float(t.double().abs().sum())])
+        np.testing.assert_allclose(got, d[name + "_ck"], rtol=1e-12, atol=1e-9, err_msg=f"re-created {name} differs from the fixture's")
+    return d, cfg, x, torch.from_numpy(d["f0"]), g, noise
+
+
+def check_against_real_fixture(d, y, tol):
+    """y (648000,) float32 numpy against the stored segments and per-frame block sums of the reference's waveform."""
+    upp = 480
+    worst = 0.0
+    for off, seg in zip(d["seg_off"], d["seg"]):
+        worst = max(worst, float(np.abs(y[off:off + seg.shape[0]] - seg).max()))
+    yb = y.astype(np.float64).reshape(-1, upp)
+    blk = np.stack([yb.sum(1), np.abs(yb).sum(1)], 1)
+    blk_err = float(np.abs(blk - d["blocks"]).max()) / upp  # mean error per sample of the worst 10 ms block
+    assert worst <= tol, worst
+    assert blk_err <= tol, blk_err
+    return worst, blk_err
+
+
+_PARITY = []
+
+
+def record_parity(entry: dict) -> None:
+    """Fast-mode / fp32 margins measured by the GPU tests; tests/conftest.py writes them to
+    gpurun_out/parity_r2.json at session end (copied to profiles/ by hand)."""
+    _PARITY.append(entry)

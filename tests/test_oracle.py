@@ -117,3 +117,35 @@ def test_nof0_sibling_oracle_and_module_init_match_reference_golden():
     assert all(float(st[k].abs().sum()) == 0.0 for k in st if k.startswith(("noise_convs.", "m_source.")))
     with pytest.raises(RuntimeError):
         m(torch.from_numpy(d["x"]), torch.from_numpy(d["g"]))  # CPU tensors: no fallback
+
+
+def test_philox_oracle_known_answers_and_moments():
+    """The in-kernel noise generator's oracle (oracle/philox_oracle.py) reproduces the Random123 known-answer vectors
+    of Philox4x32-10, and its Box-Muller normals have the moments of N(0,1)."""
+    from oracle import philox_oracle as P
+
+    for ctr, key, out in P.KAT:
+        got = P.philox4x32_10(*ctr, *key)
+        assert tuple(int(v) for v in got) == out
+    z = P.source_noise(0x1234567890ABCDEF, 3, 2, 500_000)
+    assert z.shape == (2, 500_000)
+    f = z.ravel()
+    assert abs(f.mean()) < 4e-3 and abs(f.var() - 1) < 6e-3
+    assert abs(((f - f.mean()) ** 4).mean() / f.var() ** 2 - 3) < 0.03
+    assert abs(np.corrcoef(f[:-1], f[1:])[0, 1]) < 4e-3
+    assert abs(np.corrcoef(z[0], z[1])[0, 1]) < 6e-3
+    # draws are a function of (seed, global item, sample): item 4 of a call == item 1 of a call that starts at item 3
+    assert np.array_equal(P.source_noise(9, 0, 5, 1000)[4], P.source_noise(9, 3, 2, 1000)[1])
+
+
+def test_oracle_on_the_reference_real_contour_fixture():
+    """BASELINE configs[2] input: the reference's real RMVPE contour, 13.5 s.  The oracle reproduces the stored pieces
+    of the reference's own waveform (segments + per-frame block sums)."""
+    from helpers import check_against_real_fixture, load_real_case
+
+    d, cfg, x, f0, g, noise = load_real_case()
+    assert f0.shape == (1, 1350) and float(f0.max()) > 160 and 0.4 < float((f0 > 0).float().mean()) < 0.6
+    m_sd = golden_state(d, cfg)
+    y = O.decoder_forward(O.folded_weights(m_sd), cfg, x, f0, g, noise)
+    worst, blk = check_against_real_fixture(d, y[0, 0].numpy(), 5e-6)
+    assert abs(float(y.pow(2).mean().sqrt()) - float(d["y_rms"])) < 1e-6
