@@ -7,5 +7,9 @@ missing.
 from .decoder import HiFiGANGenerator, HiFiGANNSFGenerator, ResBlock, SourceModuleHnNSF  # noqa: F401
 from . import _lib  # noqa: F401
 from . import chunking  # noqa: F401
+from . import configs  # noqa: F401
+from . import loader  # noqa: F401
+from .loader import load_checkpoint  # noqa: F401
 
-__all__ = ["HiFiGANGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking"]
+__all__ = ["HiFiGANGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking", "configs", "loader",
+           "load_checkpoint"]

@@ -163,11 +163,32 @@ class HiFiGANNSFGenerator(torch.nn.Module):
     def _weights_key(self):
         return tuple((p.data_ptr(), p._version, p.device.index) for p in self.parameters())
 
+    def set_content_key(self, key: Optional[str]) -> None:
+        """Content hash of the current weights (loader.content_hash): handles that hold the packed images of these
+        weights are shared through ``loader.PACKED``.  The key is dropped as soon as a parameter is modified in place."""
+        self.content_key = key
+        self._content_versions = tuple(p._version for p in self.parameters())
+
+    def _cache_key(self, idx: int):
+        ck = getattr(self, "content_key", None)
+        if ck is None or getattr(self, "_content_versions", None) != tuple(p._version for p in self.parameters()):
+            return None
+        return (ck, idx)
+
     def _ensure_handle(self, device: torch.device) -> _lib.Handle:
         idx = device.index if device.index is not None else torch.cuda.current_device()
         if self._handle is not None and self._handle.device != idx:
-            self._handle.close()
-            self._handle = None
+            self._handle = None  # (closed by its last reference: the packed-weight cache may share it)
+        if self._handle is None:
+            ckey = self._cache_key(idx)
+            if ckey is not None:
+                from . import loader
+
+                cached = loader.PACKED.get(ckey)
+                if cached is not None:  # folded + repacked + uploaded once already for these very weights
+                    self._handle = cached
+                    self._packed_key = self._weights_key()
+                    self._applied_fused = None
         if self._handle is None:
             self._handle = _lib.Handle(_lib.make_config(*self._cfg_args), idx)
             self._packed_key = None
@@ -181,8 +202,21 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             self._applied_fused = self.fused_mrf
         key = self._weights_key()
         if key != self._packed_key:
+            ckey = self._cache_key(idx)
+            if ckey is None and getattr(self, "content_key", None) is not None:
+                # weights changed after load_checkpoint: this module needs its own handle from now on
+                from . import loader
+
+                if any(v is self._handle for v in loader.PACKED._d.values()):
+                    self._handle = _lib.Handle(_lib.make_config(*self._cfg_args), idx)
+                    self._applied_fused = None
+                self.content_key = None
             self._handle.load_weights(self._decoder_state())
             self._packed_key = key
+            if ckey is not None:
+                from . import loader
+
+                loader.PACKED.put(ckey, self._handle)
         return self._handle
 
     def _get_workspace(self, nbytes: int, device: torch.device) -> torch.Tensor:
