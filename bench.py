@@ -301,6 +301,36 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def longform_leg(model, cfg, n_dev, reps=3):
+    """BASELINE configs[4]: 5 min of 48 kHz audio (30 000 frames + 2 x 100 frames of t_pad context) split with the
+    reference's chunk geometry (x_center = 38 s -> 8 chunks of <= 4000 frames), decoded by the single-process runner
+    (one worker thread + library handle + stream set per device, waveforms gathered by the D2H copies into one pinned
+    buffer), trimmed and joined on the host.  End to end from host latents to the stitched host waveform: slicing into
+    pinned staging, H2D, decode, D2H, stitch.  Reported for trim + concat (reference semantics) and with the sin^2
+    crossfade; wall clock (it spans several devices and the host)."""
+    from rvc_b200 import MultiGpuDecoder
+
+    n_frames, pad = 30000, 100
+    x, f0, g = synth_batch(cfg, 1, n_frames + 2 * pad, seed=4321, pin=False)
+    dec = MultiGpuDecoder(model, devices=list(range(n_dev)), mode="fast")
+    out = {}
+    try:
+        for name, cf in (("trim_concat", 0), ("crossfade_sin2_10ms", 480)):
+            dec.decode_long(x, f0, g, crossfade=cf)  # warm-up: handles, staging buffers, scratch
+            ts = []
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                y = dec.decode_long(x, f0, g, crossfade=cf)
+                ts.append(time.perf_counter() - t0)
+            assert y.shape == (n_frames * cfg.upp,) and bool((abs(y) <= 1.0).all())
+            out[name] = {"seconds": min(ts), "audio_s_per_s": n_frames / 100.0 / min(ts)}
+        st = dec.stats()
+    finally:
+        dec.close()
+    return {"workload": "5 min utterance, 8 t_pad-overlap chunks (reference geometry x_pad=1, x_center=38, x_max=41), single-process runner",
+            "n_devices": n_dev, "chunks": 8, "units_per_device": [s["units"] // (2 * (reps + 1)) for s in st], "best_of": reps, **out}
+
+
 def parity_check(model, cfg, dev):
     """One untimed 30 s chunk (the bench's chunk shape) with injected noise against the oracle: the numbers the
     north_star bars are stated on, measured in the same process as the throughput."""
@@ -386,6 +416,18 @@ def run_ours(args):
     h2d = x_h.numel() * 4 + f0_h.numel() * 4 + g_h.numel() * 4
     d2h = out_h.numel() * 4
 
+    # ---- BASELINE configs[4]: long-form across all GPUs of the job, single-process runner on rank 0 -----------------
+    longform = None
+    if not args.no_longform:
+        torch.cuda.empty_cache()
+        if rank == 0 and torch.cuda.device_count() >= world:
+            try:
+                model._workspace = None
+                torch.cuda.empty_cache()
+                longform = longform_leg(model, cfg, world)
+            except Exception as e:  # noqa: BLE001
+                longform = {"error": str(e)}
+        barrier()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -440,6 +482,8 @@ def run_ours(args):
         line["cpu_baseline"] = cpu
     if parity:
         line["parity"] = parity
+    if longform:
+        line["longform"] = longform
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -455,6 +499,7 @@ def main():
     ap.add_argument("--chunks", type=int, default=CHUNKS_PER_GPU)
     ap.add_argument("--frames", type=int, default=T_FRAMES)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-longform", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -128,6 +128,10 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *   "zero_stuff" 1 = (default) a stride-2 upsample that feeds a fused-MRF stage runs as an ordinary convolution
  *                    over a zero-stuffed copy of its input (written by the previous stage's last kernel);
  *                0 = polyphase form everywhere.
+ *   "poly2"      1 = a stride-2 upsample that feeds a fused-MRF stage runs in true polyphase form: dense 16-bit input, GEMM
+ *                    columns ordered (slice, phase, channel) so that an accumulator row holds output rows 2t and 2t+1 of a slice,
+ *                    warp-transposed coalesced fp32 epilogue with the noise conv fused; no zeros are read or multiplied.
+ *                    0 = (default) the zero-stuffed form below - the two measure the same end to end (profiles/r2e_*).
  *   "ups_pm"     1 = (default) the rate-10 / 12 upsamples (hifigan_nsf.py:198) use their phase-major weight image: GEMM
  *                    columns ordered (16-channel group, half of the phases, slice, phase, channel), warp-transposed
  *                    coalesced epilogue; on a per-conv MRF stage whose noise conv has 8 taps (stage 1) the epilogue
@@ -145,6 +149,9 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *   "pair_mrf"   1 = the 128-channel stage runs one launch per (conv1, conv2) pair (mrf_pair.cu: fp32 residual in
  *                    TMEM, operand tile in smem, half the HBM traffic); 0 = (default) one launch per conv - the two
  *                    measure the same on B200 (profiles/r1z_*), see DESIGN.md section 3.
+ *   "pair_max_k" N > 0 = on the 128-channel stage, ResBlocks whose kernel size is <= N run one fused launch per (conv1,
+ *                    conv2) pair (mrf_pair.cu) while the others keep one launch per conv; 0 = none (see DESIGN.md 3 for the
+ *                    measured default).
  *   "pair_noise" 1 = with "pair_mrf", the stage's short noise conv rides in its upsample's epilogue; 0 = (default).
  *   "fused_split_k" fused ResBlock chains as two launches (dilations 1,3 -> fp32 -> dilation 5), which halves the rows
  *                    recomputed at tile edges: N > 0 = chains with kernel size >= N; 0 = (default) chains whose recompute
@@ -152,6 +159,10 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
  *   "max_ntile"  128 (default) or 256: widest GEMM N tile of the tensor-core weight images; takes effect at the next
  *                    rvcdec_load_weights.  128 keeps the accumulators double-buffered in TMEM (profiles/r1ab_*).
  *   "a_stages"   2 (default) or 3 activation stages in the 128-wide tiling (3 measured slower, profiles/r1af_*).
+ *   "graphs"     1 = (default) the launch sequence of a pass is captured into a CUDA graph the first time a (buffers,
+ *                    B, T, mode) combination is seen and replayed afterwards (the Philox key is read from device memory,
+ *                    so one graph serves every seed); calls that need per-launch host side effects (profiling, debug
+ *                    stops) launch directly.  0 = always launch directly.  Results are bit-identical either way.
  *   "mrf_items"  0 (default) = every launch of a per-conv MRF stage covers all items; N > 0 = launches run over groups
  *                    of items whose 16-bit hand-off tensor stays under N MiB (bit-identical results; measured slower on
  *                    30 s chunks, profiles/r1ag_*). */
@@ -185,6 +196,9 @@ int32_t rvcdec_profile_read(rvcdec_handle* h, rvcdec_profile_entry* out, int32_t
  * output, 0.1) for i < last, the raw stage output for the last stage.
  * Returns the number of floats written, or <0. */
 int rvcdec_debug_set_stop(rvcdec_handle* h, int32_t stop_after);
+/* Counters / host-side timings of the handle: "graph_hits", "graph_captures", "graphs_cached" (CUDA-graph cache), and
+ * for the last rvcdec_forward_host call "host_setup_s", "host_enqueue_s", "host_wait_s".  -1 for an unknown name. */
+double rvcdec_debug_stat(const rvcdec_handle* h, const char* name);
 int64_t rvcdec_debug_read(rvcdec_handle* h, const char* name, float* dst, int64_t dst_numel,
                           void* workspace, int32_t B, int32_t T, int32_t mode, void* stream);
 /* Instrumented twin of the fused ResBlock kernel: after rvcdec_set_option(h, "fused_timing", 1) every

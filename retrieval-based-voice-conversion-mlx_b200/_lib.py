@@ -51,7 +51,7 @@ class ProfileEntry(C.Structure):
 EXPORTS = [
     "rvcdec_create", "rvcdec_load_weights", "rvcdec_workspace_bytes", "rvcdec_forward", "rvcdec_forward_host",
     "rvcdec_set_option", "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
-    "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
+    "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_debug_stat", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
 ]
 
 _lib = None
@@ -95,6 +95,8 @@ def lib() -> C.CDLL:
     L.rvcdec_debug_packed.restype = i64
     L.rvcdec_debug_fused_timing.argtypes = [vp, vp, i64]
     L.rvcdec_debug_fused_timing.restype = i64
+    L.rvcdec_debug_stat.argtypes = [vp, C.c_char_p]
+    L.rvcdec_debug_stat.restype = C.c_double
     L.rvcdec_destroy.argtypes = [vp]
     L.rvcdec_destroy.restype = None
     L.rvcdec_last_error.argtypes = []
@@ -206,6 +208,9 @@ class Handle:
         n = lib().rvcdec_debug_fused_timing(self._h, buf.ctypes.data, buf.size)
         check(n, "rvcdec_debug_fused_timing")
         return buf[: n * num_sms * 16].reshape(n, num_sms, 16)
+
+    def stat(self, name: str) -> float:
+        return float(lib().rvcdec_debug_stat(self._h, name.encode()))
 
     def launch_count(self) -> int:
         return int(lib().rvcdec_last_launch_count(self._h))

@@ -103,6 +103,14 @@ def stitch(decoded: Sequence[np.ndarray], trims: Sequence[int], crossfade: int =
     return out
 
 
+def pinned(t):
+    """Page-locked copy of a host tensor when a CUDA driver is present (staging buffers of the host-buffer calls);
+    the tensor itself otherwise (CPU-only tests of the host logic)."""
+    import torch
+
+    return t.pin_memory() if torch.cuda.is_available() else t
+
+
 def decode_chunks(model, x, f0, g, chunks: Sequence[Chunk], *, mode=None, noise=None, device=None,
                   rank: int = 0, world: int = 1):
     """Decode this rank's share of ``chunks`` of one padded utterance in ONE batched call and return
@@ -125,8 +133,8 @@ def decode_chunks(model, x, f0, g, chunks: Sequence[Chunk], *, mode=None, noise=
         return {}
     upp = model.upp
     B, Tmax = len(mine), max(c.frames for c in mine)
-    xb = torch.zeros(B, x.shape[1], Tmax, dtype=torch.float32).pin_memory()
-    fb = torch.zeros(B, Tmax, dtype=torch.float32).pin_memory()
+    xb = pinned(torch.zeros(B, x.shape[1], Tmax, dtype=torch.float32))
+    fb = pinned(torch.zeros(B, Tmax, dtype=torch.float32))
     for k, c in enumerate(mine):
         xb[k, :, :c.frames] = x[0, :, c.start:c.stop]
         fb[k, :c.frames] = f0[0, c.start:c.stop]
@@ -151,3 +159,27 @@ def decode_long(model, x, f0, g, *, mode=None, crossfade: int = 0, noise=None, d
     chunks = plan_chunks(x.shape[2] - 2 * pad, x_pad, x_query, x_center, x_max, split_points)
     dec = decode_chunks(model, x, f0, g, chunks, mode=mode, noise=noise, device=device)
     return stitch([dec[c.index] for c in chunks], [c.trim * model.upp for c in chunks], crossfade)
+
+
+def gather_chunks(local: dict, chunks: Sequence[Chunk], upp: int, crossfade: int = 0, dst: int = 0):
+    """``torchrun`` deployments (one process per GPU): every rank passes the ``{chunk.index: waveform}`` dict its
+    ``decode_chunks(rank=, world=)`` call returned; rank ``dst`` receives all of them (``gather_object`` - the only
+    cross-rank step of the path, a result gather), stitches and returns the utterance, other ranks get None.
+    Works on any initialised backend (nccl on the GPU box, gloo in the CPU tests); without a process group it just
+    stitches ``local``."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        parts = [None] * dist.get_world_size() if dist.get_rank() == dst else None
+        dist.gather_object(local, parts, dst=dst)
+        if dist.get_rank() != dst:
+            return None
+        merged = {}
+        for p in parts:
+            merged.update(p)
+    else:
+        merged = dict(local)
+    missing = [c.index for c in chunks if c.index not in merged]
+    if missing:
+        raise RuntimeError(f"chunks {missing} were decoded by no rank")
+    return stitch([merged[c.index] for c in chunks], [c.trim * upp for c in chunks], crossfade)

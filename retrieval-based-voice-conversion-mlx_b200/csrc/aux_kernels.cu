@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(SRC_THREADS) source_kernel(SourceParams p) {
   __shared__ float s_f0[SRC_FPB];
   const int b = blockIdx.y;
   const int l0 = blockIdx.x * SRC_FPB;
+  const uint64_t seed = p.seed_dev ? __ldg(p.seed_dev) : p.seed;
   const float* f0 = p.f0 + (size_t)b * p.T;
   const double inv_sr = 1.0 / (double)p.sr;
   const double dupp = (double)p.upp;
@@ -108,10 +109,16 @@ __global__ void __launch_bounds__(SRC_THREADS) source_kernel(SourceParams p) {
     const double ph = s_finc[fr] * (double)(k + 1) + s_C[fr];
     const float frac = (float)(ph - floor(ph));
     const float sine = 0.1f * sinpif(2.0f * frac);
-    const float z = p.noise ? __ldg(p.noise + base + i) : philox_normal(p.seed, pbase + (uint64_t)i);
+    const float z = p.noise ? __ldg(p.noise + base + i) : philox_normal(seed, pbase + (uint64_t)i);
     const float v = (s_f0[fr] > 0.f) ? (sine + 0.003f * z) : ((0.1f / 3.0f) * z);
     p.har[base + i] = tanhf(p.lin_w * v + p.lin_b);
   }
+}
+
+__global__ void set_u64_kernel(uint64_t* dst, uint64_t v) { *dst = v; }
+cudaError_t launch_set_u64(uint64_t* dst, uint64_t v, cudaStream_t s) {
+  set_u64_kernel<<<1, 1, 0, s>>>(dst, v);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_source(const SourceParams& p, cudaStream_t s) {
@@ -331,8 +338,16 @@ static cudaError_t launch_noise_add_big(const NoiseAddParams& p, cudaStream_t s)
   const int span = (rows_per_tile - 1) * p.stride + p.k;
   const size_t smem = ((size_t)p.k * p.C + span) * sizeof(float);
   auto kern = noise_add_big_kernel<T>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  // (the size depends on the layer, so the attribute is raised to the largest request seen per device)
+  static int granted[64] = {0};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
+  if (dev >= 64 || granted[dev] < (int)smem) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    if (dev < 64) granted[dev] = (int)smem;
+  }
   const int tiles_per_item = (p.L + rows_per_tile - 1) / rows_per_tile;
   const long long total = (long long)p.B * tiles_per_item;
   const int blocks = (int)std::min<long long>(total, 148 * 2);

@@ -179,6 +179,19 @@ __device__ __forceinline__ void epilogue_store(const Epilogue& e, int b, int t_i
   }
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per (function, device): set it once, not on every launch
+// (59 launches per single-utterance decode each paid a driver call for it).  `done` is a per-call-site bit mask
+// by device ordinal; a lost race only repeats the idempotent call.
+inline cudaError_t set_smem_once(const void* func, int bytes, unsigned long long& done) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 64 && ((done >> dev) & 1ull)) return cudaSuccess;
+  e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess && dev < 64) done |= 1ull << dev;
+  return e;
+}
+
 // ---- launchers implemented in the .cu files --------------------------------
 cudaError_t launch_conv_f32(const ConvParams& p, cudaStream_t s);
 // returns cudaErrorInvalidValue when no instantiation fits (N tile / K chunk)
@@ -263,6 +276,7 @@ struct SourceParams {
   const float* f0;      // (B, T)
   const float* noise;   // (B, T*upp) or null
   float* har;           // (B, T*upp)
+  const uint64_t* seed_dev;  // non-null: the key is read from device memory (launch sequences replayed as CUDA graphs)
   uint64_t seed;     // Philox key of the whole call
   uint64_t item0;    // global index of item 0 of this launch: draw (item, sample) is a function of (seed, item0 + b, sample)
                      // only, so the waveform does not depend on how a batch is cut into passes
@@ -270,6 +284,7 @@ struct SourceParams {
   float sr, lin_w, lin_b;
 };
 cudaError_t launch_source(const SourceParams& p, cudaStream_t s);
+cudaError_t launch_set_u64(uint64_t* dst, uint64_t v, cudaStream_t s);
 
 // biasB[b][n] = bias_pre[n] + (g ? bias_cond[n] + sum_c Wc[n][c] g[b][c] : 0)
 cudaError_t launch_cond(const float* g, const float* Wc, const float* bias_cond, const float* bias_pre,

@@ -54,13 +54,15 @@ struct MmaCfg {
   static constexpr int MT = MB * 128;
   // PM = 1: phase-major polyphase upsample tile (see the PM epilogue below): N_TILE = PH phases x 2 slices x 8
   // channels; every epilogue warp owns a staging area of 32 x (2*PH*32 + 16) bytes for the warp-level transpose
+  // PM = 2: stride-2 polyphase upsample tile, columns (slice, phase, channel): every epilogue warp transposes its 32 rows x
+  // 64 B through a staging area of 32 x 80 B (16 B of padding per lane keeps the quarter-warp stores conflict-free)
   static constexpr int PH = N_TILE / 16;
-  static constexpr int STG_LANE = PH * 32 + 16;
+  static constexpr int STG_LANE = PM == 2 ? 80 : PH * 32 + 16;
   static constexpr int STG_WARP = PM ? 32 * STG_LANE : 0;
   static constexpr int STG_BYTES = 16 * STG_WARP;
-  static constexpr int CONST_BYTES = PM ? (256 + 8 * 128) * 4 : 0;  // per-channel bias (<= 256) + noise-conv taps [8][<= 128]
+  static constexpr int CONST_BYTES = PM == 1 ? (256 + 8 * 128) * 4 : 0;  // per-channel bias (<= 256) + noise-conv taps [8][<= 128]
   static constexpr int EPI_WARPS = PM ? 16 : EW;        // 8, or 16 (items of 16 columns: twice the warps to hide the epilogue's latencies)
-  static constexpr int CW = EPI_WARPS == 16 ? 16 : 32;  // accumulator columns per epilogue work item (non-PM paths)
+  static constexpr int CW = EPI_WARPS == 16 ? 16 : 32;  // accumulator columns per epilogue work item (PM != 1 paths)
   static constexpr int THREADS = 64 + EPI_WARPS * 32;   // producer warp + MMA warp + epilogue warps
   static_assert(EW == 8 || EW == 16, "8 or 16 epilogue warps");
   static constexpr int ACC_STAGES = (2 * MB * N_TILE <= 512) ? 2 : 1;
@@ -113,7 +115,7 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if constexpr (PM != 0) {
+  if constexpr (PM == 1) {
     // per-channel bias (+ noise-conv bias) and the noise-conv taps live in shared memory: the strided har reads of
     // the epilogue sweep the small L1 (most of it is carved out as shared memory), so uniform global loads of these
     // constants kept missing it (profiles/r1bc: the first use of each was a long-scoreboard stall)
@@ -251,8 +253,8 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
       // warps, so every exposed global-load latency counts).  A/B (profiles/r1be-r1bh): plain per-lane 8 B loads (lane
       // stride up*16 B) beat staging the warp's contiguous window through shared memory - the L1 data pipe, which
       // also carries the transpose, is the unit that saturates (80 %).
-      [[maybe_unused]] float hv[PM ? 4 * (N_TILE / 16) + 4 : 1];
-      if constexpr (PM != 0) {
+      [[maybe_unused]] float hv[PM == 1 ? 4 * (N_TILE / 16) + 4 : 1];
+      if constexpr (PM == 1) {
         static_assert(MB == 2, "phase-major epilogue: one item per warp and tile");
         constexpr int PH = Cfg::PH, U = 2 * PH, NZS = 4, NZK = 8, NH = NZS * PH + NZK - NZS;
         if (e.nz_har) {
@@ -285,7 +287,94 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
       mbar_wait(acc_full + 8 * as, (acc_it / Cfg::ACC_STAGES) & 1u);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + ((uint32_t)(q * 32) << 16) + as * (MB * N_TILE);
-      if constexpr (PM != 0) {
+      if constexpr (PM == 2) {
+        // ---- stride-2 polyphase upsample (ConvTranspose1d k = 4, stride 2; hifigan_nsf.py:198 [+ :199]) ----
+        // GEMM columns are ordered (slice, phase, channel): the 16 columns of a work item are output rows 2t and 2t+1
+        // of one slice for this thread's input row t, i.e. 64 contiguous bytes of fp32, and a warp owns a 2 KB run.
+        // No zeros are read or multiplied (the zero-stuffed form did both) and the previous stage writes a dense 16-bit
+        // tensor.  Stored straight from the registers, the 64 B lane stride makes every STG.128 touch 16 cache lines
+        // (measured r2d: 26 ms against 17 ms for the zero-stuffed form), so the warp transposes the run through its
+        // staging area and every store instruction writes 512 contiguous bytes.  fp32 output only: the fused MRF stage
+        // that follows reads nothing else.
+        static_assert(Cfg::CW == 16, "stride-2 polyphase epilogue works on 16-column items");
+        constexpr int CH2 = N_TILE / 16;
+        constexpr int ITEMS2 = MB * CH2;
+        constexpr int WGS2 = Cfg::EPI_WARPS / 4;
+        const uint32_t my_stg = stg_smem + (uint32_t)(warp - 2) * Cfg::STG_WARP;
+#pragma unroll 1
+        for (int item = wg; item < ITEMS2; item += WGS2) {
+          const int mb = item / CH2;
+          const int c0 = (item - mb * CH2) * 16;
+          const int tb = t0 + mb * 128 + q * 32;
+          const int t_in = tb + lane;
+          const bool valid = t_in < p.L_in;
+          const int n0 = n_tile * N_TILE + c0;
+          const int co = (n0 >> 4) * 8;
+          // har samples under the two output rows' noise convs (<= 8 taps), requested before the accumulator wait
+          float hp[2][8];
+          if (e.nz_har) {
+            const float* hb = e.nz_har + (size_t)b * e.nz_src;
+#pragma unroll
+            for (int ph = 0; ph < 2; ++ph) {
+              const int s0 = (2 * t_in + ph) * e.nz_stride - e.nz_pad;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const int sidx = s0 + j;
+                hp[ph][j] = (valid && j < e.nz_k && sidx >= 0 && sidx < e.nz_src) ? __ldg(hb + sidx) : 0.f;
+              }
+            }
+          }
+          float4 bb[4];
+          {
+            const float4* bp = reinterpret_cast<const float4*>(e.bias + n0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) bb[i] = __ldg(bp + i);
+          }
+          uint32_t r[16];
+          tc_ld16(t_acc + mb * N_TILE + c0, r);
+#pragma unroll
+          for (int ph = 0; ph < 2; ++ph) {
+            float v[8];
+            const float4 b0 = bb[2 * ph], b1 = bb[2 * ph + 1];
+            v[0] = __uint_as_float(r[ph * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[ph * 8 + 1]) + b0.y;
+            v[2] = __uint_as_float(r[ph * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[ph * 8 + 3]) + b0.w;
+            v[4] = __uint_as_float(r[ph * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[ph * 8 + 5]) + b1.y;
+            v[6] = __uint_as_float(r[ph * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[ph * 8 + 7]) + b1.w;
+            if (e.nz_har) {
+              const float4 nb0 = __ldg(reinterpret_cast<const float4*>(e.nz_bias + co));
+              const float4 nb1 = __ldg(reinterpret_cast<const float4*>(e.nz_bias + co + 4));
+              v[0] += nb0.x; v[1] += nb0.y; v[2] += nb0.z; v[3] += nb0.w;
+              v[4] += nb1.x; v[5] += nb1.y; v[6] += nb1.z; v[7] += nb1.w;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                if (j < e.nz_k) {
+                  const float hj = hp[ph][j];
+                  const float4 w0 = __ldg(reinterpret_cast<const float4*>(e.nz_w + (size_t)j * e.cout + co));
+                  const float4 w1 = __ldg(reinterpret_cast<const float4*>(e.nz_w + (size_t)j * e.cout + co + 4));
+                  v[0] = fmaf(hj, w0.x, v[0]); v[1] = fmaf(hj, w0.y, v[1]); v[2] = fmaf(hj, w0.z, v[2]); v[3] = fmaf(hj, w0.w, v[3]);
+                  v[4] = fmaf(hj, w1.x, v[4]); v[5] = fmaf(hj, w1.y, v[5]); v[6] = fmaf(hj, w1.z, v[6]); v[7] = fmaf(hj, w1.w, v[7]);
+                }
+              }
+            }
+            const uint32_t dst = my_stg + (uint32_t)(lane * Cfg::STG_LANE + ph * 32);
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+          }
+          __syncwarp();
+          // staging -> global: piece pp = 32 k + lane of the warp's 128 16-byte pieces belongs to thread pp / 4
+          float* run0 = e.out_f32 + (((size_t)b * (e.cout >> 3) + (n0 >> 4)) * e.Lp_out + PADL + 2 * (size_t)tb) * 8;
+          const int rows_ok = min(32, p.L_in - tb);  // threads [0, rows_ok) hold real rows
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int pp = 32 * k + lane;
+            float4 f;
+            const uint32_t src = my_stg + (uint32_t)((pp >> 2) * Cfg::STG_LANE + (pp & 3) * 16);
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f.x), "=f"(f.y), "=f"(f.z), "=f"(f.w) : "r"(src) : "memory");
+            if ((pp >> 2) < rows_ok) *reinterpret_cast<float4*>(run0 + pp * 4) = f;
+          }
+          __syncwarp();
+        }
+      } else if constexpr (PM == 1) {
         // ---- phase-major polyphase upsample (ConvTranspose1d, hifigan_nsf.py:198) [+ noise_convs[i](har), :199] ----
         // N tile n_tile = (channel group cg of 16) * 2 + half; its columns are ordered (slice sl of the group, phase rr
         // of this half, channel c): column (sl*PH + rr)*8 + c is output row t_in*up + half*PH + rr of slice 2*cg + sl.
@@ -545,9 +634,13 @@ template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0
 static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s) {
   using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
   auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
-  if ((PM != 0) != (p.epi.pm != 0) || p.halo > Cfg::A_HALO) return cudaErrorInvalidValue;
-  {  // per-device attribute; cheap enough to set on every launch
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+  if (PM != p.epi.pm || p.halo > Cfg::A_HALO) return cudaErrorInvalidValue;
+  if (PM == 2 && (p.epi.up != 2 || p.epi.act_zs > 1 || p.epi.res || p.epi.sum_in || p.epi.out_act || !p.epi.out_f32 || p.epi.bias_bstride ||
+                  (p.epi.nz_har && p.epi.nz_k > 8)))
+    return cudaErrorInvalidValue;
+  {
+    static unsigned long long done = 0;  // one per instantiation
+    cudaError_t e = set_smem_once(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES, done);
     if (e != cudaSuccess) return e;
   }
   if (p.Cin % KC != 0 || p.N_total % N_TILE != 0 || p.halo > PADL || p.ntaps > MAX_TAPS) return cudaErrorInvalidValue;
@@ -573,6 +666,12 @@ cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms
   // two stages the MMA warp spent more than half of its time waiting for activation tiles, profiles/r1bg)
   if (n_tile == 80 && kc == 64) return p.a_stages == 2 ? launch_inst<80, 2, 64, 5, 2, 1>(p, num_sms, s) : launch_inst<80, 2, 64, 3, 3, 1>(p, num_sms, s);
   if (n_tile == 96 && kc == 64) return launch_inst<96, 2, 64, 4, 2, 1>(p, num_sms, s);
+  // stride-2 polyphase upsamples (columns (slice, phase, channel), warp-transposed coalesced epilogue)
+  if (p.epi.pm == 2) {
+    if (n_tile == 128 && kc == 64) return launch_inst<128, 2, 64, 6, 2, 2, 16>(p, num_sms, s);
+    if (n_tile == 64 && kc == 64) return launch_inst<64, 4, 64, 4, 2, 2, 16>(p, num_sms, s);
+    return cudaErrorInvalidValue;
+  }
   if (n_tile == 256 && kc == 64) return launch_inst<256, 2, 64, 4>(p, num_sms, s);
   // 128-wide tiles: option a_stages = 3 adds a third 40 KB activation stage.  Measured (profiles/r1af_*): the
   // 128-channel stage gets 7 % SLOWER with it (229 vs 214 ms), so two stages stay the default.

@@ -631,7 +631,8 @@ static cudaError_t launch_fused_inst(const FusedParams& p, int num_sms, cudaStre
   using Cfg = FusedCfg<C, MB, S>;
   auto kern = p.timing ? (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, EW, true, true> : mrf_fused_kernel<C, MB, S, EW, false, true>)
                        : (p.fmt == ACT_BF16 ? mrf_fused_kernel<C, MB, S, EW, true, false> : mrf_fused_kernel<C, MB, S, EW, false, false>);
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+  static unsigned long long done[4] = {0, 0, 0, 0};  // one per (format, timing) twin of this instantiation
+  cudaError_t e = set_smem_once(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES, done[(p.timing ? 2 : 0) + (p.fmt == ACT_BF16 ? 1 : 0)]);
   if (e != cudaSuccess) return e;
   FusedParams q = p;
   const int valid = Cfg::MT - 2 * p.margin;

@@ -11,7 +11,13 @@
 //          acc1[2][128 x 128]      fp32   conv1 accumulators                                  (= all 512 columns)
 //   smem   A        (256 + 2*32 pad rows) x 128 ch, blocked-8 K-major 16-bit (no-swizzle UMMA layout); ONE tile
 //                   serves both convs (see below)
-//          W ring   8 x 16 KB: one (tap, 64-channel chunk) block of the conv_mma weight image per stage
+//          W ring   4 x 16 KB: one (tap, 64-channel chunk) block of the conv_mma weight image per stage
+//          out      16 x 4 KB: per-epilogue-warp staging of the fp32 output rows, drained by bulk async stores
+//                   (cp.async.bulk shared -> global).  Round 1 stored the output with STG from registers: every CTA
+//                   reaches its store phase at the same time, the 128 KB-per-SM bursts run at the HBM rate and the
+//                   epilogue warps sat in them for ~8k clk per tile (timing twin r1x: fin:stg) while the tensor pipe
+//                   waited for the NEXT tile's conv1 epilogue from the same warps.  The TMA engine now drains the
+//                   staging in the background; a warp only waits for its previous drain when it needs the staging again.
 //
 // A 128 x 128 tap block is 32 KB, so (unlike mrf_fused.cu) a conv's taps cannot stay resident: the loop is
 // tap-outer / row-block-inner, each weight block feeds 8 MMAs (2 row blocks x 4 K steps) and both
@@ -42,10 +48,12 @@ constexpr int A_BUF = NSL * A_SLICE;
 constexpr int KC = 64;
 constexpr int B_SLICE = C * 16;
 constexpr int W_STAGE = (KC / 8) * B_SLICE;
-constexpr int S = 8;
+constexpr int S = 4;
 constexpr int ACC1_COL0 = MB * C;
 constexpr int NUM_BARS = 2 * S + 3 * MB + 2;
-constexpr int SMEM_BYTES = 128 + A_BUF + S * W_STAGE + NUM_BARS * 8 + 16;
+constexpr int STG_WARP = 4 * 32 * 32;  // 4 slices x 32 rows x 8 fp32: the output rows of one epilogue warp and row block
+constexpr int STG_BYTES = EW * STG_WARP;
+constexpr int SMEM_BYTES = 128 + A_BUF + S * W_STAGE + STG_BYTES + NUM_BARS * 8 + 16;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 static_assert(ACC1_COL0 + MB * C <= 512, "TMEM budget");
 constexpr int NC = C / (EW / 4);  // 32 accumulator columns per epilogue warp
@@ -63,6 +71,14 @@ __device__ __forceinline__ uint32_t ppack2(float a, float b, bool bf16) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 __device__ __forceinline__ float plrelu(float v, float slope) { return fmaxf(v, v * slope); }
+// shared -> global bulk async copy (TMA engine), tracked by the issuing thread's bulk async-group
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// the staging may be overwritten once every committed group has READ its source
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 }  // namespace
 
 // TIMING = true: instrumented twin (tools/pair_timing.py); the MMA warp and epilogue warp 2 accumulate clock64
@@ -89,7 +105,8 @@ __global__ void __launch_bounds__(pair::THREADS, 1) mrf_pair_kernel(const __grid
   const uint32_t a0_smem = smem_base;
   const uint32_t a1_smem = a0_smem;  // conv2's operand overwrites conv1's in place (tap-outer order, see the header)
   const uint32_t w_smem = a0_smem + A_BUF;
-  const uint32_t bars = w_smem + S * W_STAGE;
+  const uint32_t stg_smem = w_smem + S * W_STAGE;
+  const uint32_t bars = stg_smem + STG_BYTES;
   const uint32_t w_full = bars, w_empty = w_full + 8 * S, a0_ready = w_empty + 8 * S, a1_ready = a0_ready + 8 * MB,
                  x_ready = a1_ready + 8 * MB, acc1_full = x_ready + 8 * MB, x_full = acc1_full + 8;
   const uint32_t tmem_slot = x_full + 8;
@@ -373,6 +390,14 @@ __global__ void __launch_bounds__(pair::THREADS, 1) mrf_pair_kernel(const __grid
         const long long t_st = TIMING ? clock64() : 0;
         {
           const int tq = t - lane;  // time of lane 0's row (the warp's 32 rows are consecutive)
+          // rows of this warp that are stored: every condition is an interval in the row index, so they are contiguous
+          const uint32_t smask = __ballot_sync(0xffffffffu, store_out);
+          const int lo = smask ? (__ffs((int)smask) - 1) : 0, cnt = __popc(smask);
+          const uint32_t my_stg = stg_smem + (uint32_t)(warp - 2) * STG_WARP;
+          if (p.out_f32) {  // the previous drain of this staging area must have read it
+            if (lane == 0) bulk_wait_read();
+            __syncwarp();
+          }
 #pragma unroll
           for (int s8 = 0; s8 < NS8; ++s8) {
             const size_t off = ((u.item_base + (size_t)(sl0 + s8) * p.Lp) + PADL + t) * 8;
@@ -394,10 +419,10 @@ __global__ void __launch_bounds__(pair::THREADS, 1) mrf_pair_kernel(const __grid
 #pragma unroll
               for (int i = 0; i < 8; ++i) o[i] = 0.f;
             }
-            if (p.out_f32) {
-              // (pointer arithmetic only; rows of lanes with !store_out are never dereferenced)
-              float* row0 = p.out_f32 + ((ptrdiff_t)((u.item_base + (size_t)(sl0 + s8) * p.Lp) + PADL) + tq) * 8;
-              warp_store_rows_f32(row0, make_float4(o[0], o[1], o[2], o[3]), make_float4(o[4], o[5], o[6], o[7]), store_out);
+            if (p.out_f32) {  // rows in the global layout: [row][8 fp32] per slice
+              const uint32_t dst = my_stg + (uint32_t)(s8 * 1024 + lane * 32);
+              asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "f"(o[0]), "f"(o[1]), "f"(o[2]), "f"(o[3]) : "memory");
+              asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + 16), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7]) : "memory");
             }
             if (p.out_act && store_out) {
               uint32_t pk[4];
@@ -414,6 +439,19 @@ __global__ void __launch_bounds__(pair::THREADS, 1) mrf_pair_kernel(const __grid
               }
             }
           }
+          if (p.out_f32) {
+            fence_proxy_async();  // generic-proxy writes of the staging -> visible to the bulk copy engine
+            __syncwarp();
+            if (lane == 0 && cnt > 0) {
+#pragma unroll
+              for (int s8 = 0; s8 < NS8; ++s8) {
+                // (pointer arithmetic in ptrdiff_t: tq may be negative at a sequence start, lo moves it to a valid row)
+                float* g_dst = p.out_f32 + ((ptrdiff_t)((u.item_base + (size_t)(sl0 + s8) * p.Lp) + PADL) + tq + lo) * 8;
+                bulk_s2g(g_dst, my_stg + (uint32_t)(s8 * 1024 + lo * 32), (uint32_t)cnt * 32u);
+              }
+              bulk_commit();
+            }
+          }
         }
         if (TIMING) tacc[7] += clock64() - t_st;
       }
@@ -421,6 +459,7 @@ __global__ void __launch_bounds__(pair::THREADS, 1) mrf_pair_kernel(const __grid
       u = nx;
       ++seq;
     }
+    if (lane == 0) bulk_wait_all();  // the staging must outlive its drains
   }
   if (TIMING && p.timing && (threadIdx.x == 32 || threadIdx.x == 64)) {
     // MMA warp: [0] wait operand (conv1), [1] wait operand (conv2), [2] wait weights, [3] tap loops incl. [2], [5] total
@@ -448,7 +487,8 @@ cudaError_t launch_mrf_pair(const PairParams& p, int num_sms, cudaStream_t s) {
   using namespace pair;
   auto kern = p.timing ? (p.fmt == ACT_BF16 ? mrf_pair_kernel<true, true> : mrf_pair_kernel<false, true>)
                        : (p.fmt == ACT_BF16 ? mrf_pair_kernel<true, false> : mrf_pair_kernel<false, false>);
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+  static unsigned long long done[4] = {0, 0, 0, 0};
+  cudaError_t e = set_smem_once(reinterpret_cast<const void*>(kern), SMEM_BYTES, done[(p.timing ? 2 : 0) + (p.fmt == ACT_BF16 ? 1 : 0)]);
   if (e != cudaSuccess) return e;
   const int valid = MT - 2 * p.margin;
   if (valid < 128 || p.k1 < 1 || p.k2 < 1 || (p.k1 - 1) / 2 * p.d1 > PAD || (p.k2 - 1) / 2 * p.d2 > PAD ||

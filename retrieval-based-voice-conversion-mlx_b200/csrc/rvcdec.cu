@@ -1,6 +1,7 @@
 // librvcdec.so - C ABI (include/rvcdec.h) over the sm_100a decoder kernels.
 // Host side: weight-norm folding and repacking at load time, workspace carving, and the
 // launch sequence of HiFiGANNSFGenerator.forward (reference hifigan_nsf.py:173-212).
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -92,6 +93,8 @@ struct rvcdec_handle {
   ConvLayer conv_pre;
   std::vector<ConvLayer> ups;
   std::vector<ConvLayer> ups_zs;  // stride-2 upsamples as ordinary convs over a zero-stuffed input (n_tile == 0: unused)
+  std::vector<ConvLayer> ups_p2;  // stride-2 upsamples in true polyphase form, GEMM columns ordered (slice, phase, channel): a thread's
+                                  // 16 columns are output rows 2t, 2t+1 of one slice = 64 contiguous bytes (n_tile == 0: unused)
   std::vector<ConvLayer> ups_pm;  // rate-10 / 12 upsamples with phase-major GEMM columns (coalesced epilogue; n_tile == 0: unused)
   std::vector<ConvLayer> rbconv;  // index ((i*nk + j)*nd + m)*2 + which
   std::vector<NoiseLayer> noise;
@@ -115,6 +118,9 @@ struct rvcdec_handle {
   int conv_epi_warps_small = 16;  // same for the 64- / 32-wide tilings (profiles/r1br: ups2 21.8 -> 17.6 ms, ups3 13.9 -> 12.3 ms)
   int pm_a_stages = 2; // activation ring depth of the rate-10 phase-major upsample tile (2 or 3)
   int ups_pm_on = 1;   // 1 = upsamples that have a phase-major image use it (and carry the stage's 8-tap noise conv + 16-bit copy)
+  int poly2 = 0;       // 1 = stride-2 upsamples of fused-MRF stages run their polyphase image (no zeros read or multiplied; takes
+                       // precedence over zero_stuff).  Measured on par with the zero-stuffed form (profiles/r2e_*: ups2 19 vs 17.4 ms,
+                       // the two MRF stages in front 3-8 ms faster for their dense output), so it stays an option
   int zero_stuff = 1;  // 1 = stride-2 upsamples of fused-MRF stages read a zero-stuffed input (coalesced epilogue)
   int max_ntile = 128;  // (r1ab: N = 128 tiles keep the accumulators double-buffered in TMEM; 256-wide tiles serialise MMA and epilogue) largest GEMM N tile the weight images are built for (takes effect at the next rvcdec_load_weights)
   int a_stages = 2;  // activation ring depth of the 128-wide conv_mma tiling (r1af: a third stage costs 7 % on the 128-channel stage)
@@ -123,6 +129,8 @@ struct rvcdec_handle {
   int fused_split_k = 0;  // fused ResBlock chains as two launches (less tile-edge recompute): > 0 = those with kernel size >= this,
                           // 0 = automatic (chains whose recompute exceeds a quarter of the tile), -1 = never
   int pair_noise = 0;  // 1 = the pair stage's short noise conv rides in its upsample's epilogue (no noise_add launch)
+  int pair_max_k = 0;  // > 0: on a per-conv 128-channel stage, ResBlocks with kernel size <= this run one fused launch per
+                       // (conv1, conv2) pair (mrf_pair.cu) instead of two conv launches; the others stay per-conv
   int pair_mrf = 0;  // 1 = fused conv1+conv2 pair kernel (mrf_pair.cu) on the 128-channel stage (r1z: on par with the per-conv path, so off)
   int fused_epi_warps = 8;   // epilogue warps of the fused ResBlock kernel (8 or 16)
   int fused_post = 1; // 1 = conv_post + tanh fused into the last stage's final fused-MRF launch (C = 32, 7 taps)
@@ -136,6 +144,25 @@ struct rvcdec_handle {
   std::vector<std::string> prof_names;
   std::vector<double> prof_ms, prof_flops, prof_bytes;
   std::vector<int64_t> prof_launches;
+  // CUDA graphs: the launch sequence of one pass is captured once per (buffers, shape, mode) and replayed; the Philox
+  // key is the only value that changes between replays and lives in device memory (d_seed)
+  int use_graphs = 1;
+  uint64_t epoch = 0;  // bumped by everything that changes the launch sequence (options, weights): drops the cache
+  struct GraphEntry {
+    const void *x, *f0, *g, *noise, *out, *ws;
+    int B, T, mode;
+    uint64_t item0, epoch;
+    cudaGraphExec_t exec;
+    int64_t launches;
+    uint64_t last_use;
+  };
+  std::vector<GraphEntry> graphs;
+  uint64_t graph_clock = 0, graph_hits = 0, graph_captures = 0;
+  uint64_t* d_seed = nullptr;
+  cudaStream_t cap_stream = nullptr;
+  // host-side time of the last rvcdec_forward_host call, seconds: [0] set-up (memory query, buffers), [1] enqueueing
+  // the passes, [2] waiting for the streams
+  double host_t[3] = {0, 0, 0};
   // forward_host state
   cudaStream_t stream = nullptr;
   // host-buffer entry point: copies of pass i+1 / i-1 overlap the kernels of pass i
@@ -324,9 +351,16 @@ int fmt_stage(int mode, int i) {
 
 bool use_fused_mrf(const rvcdec_handle* h, int mode, int i);
 bool use_pair_mrf(const rvcdec_handle* h, int mode, int i);
+// Stage i's stride-2 upsample runs in polyphase form with the (slice, phase, channel) column order ("poly2").
+bool use_p2(const rvcdec_handle* h, int mode, int i) {
+  if (mode == 0 || !h->poly2 || i < 1 || i >= h->nups || h->cfg.upsample_rates[i] != 2 || !h->ups_p2[i].n_tile) return false;
+  if (!use_fused_mrf(h, mode, i)) return false;  // (the epilogue writes the fp32 stage input only)
+  const NoiseLayer& nl = h->noise[i];
+  return h->no_source || (nl.k <= 8 && nl.stride <= 4);
+}
 // Stage i writes its 16-bit output zero-stuffed when stage i+1 is a stride-2 upsample feeding a fused MRF stage.
 bool zs_out_stage(const rvcdec_handle* h, int mode, int i) {
-  if (mode == 0 || !h->zero_stuff || i + 1 >= h->nups) return false;
+  if (mode == 0 || !h->zero_stuff || i + 1 >= h->nups || use_p2(h, mode, i + 1)) return false;
   return h->cfg.upsample_rates[i + 1] == 2 && h->ups_zs[i + 1].n_tile != 0 && use_fused_mrf(h, mode, i + 1);
 }
 
@@ -486,6 +520,59 @@ bool use_pair_mrf(const rvcdec_handle* h, int mode, int i) {
       if (!mrf_pair_supported(h->ch[i], c1.halo, c2.halo)) return false;
     }
   return true;
+}
+
+// Mixed mode ("pair_max_k"): ResBlock j of per-conv stage i runs the fused-pair kernel.
+bool pair_rb(const rvcdec_handle* h, int mode, int i, int j) {
+  if (mode == 0 || h->pair_max_k <= 0 || h->ch[i] != 128 || h->mrf_items != 0) return false;
+  if (h->cfg.resblock_kernel_sizes[j] > h->pair_max_k) return false;
+  for (int m = 0; m < h->nd; ++m) {
+    const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
+    const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
+    if (c1.n_tile != 128 || c1.kc != 64 || c2.n_tile != 128 || c2.kc != 64) return false;
+    if (!mrf_pair_supported(h->ch[i], c1.halo, c2.halo)) return false;
+  }
+  return true;
+}
+
+// One ResBlock j of stage i as nd fused-pair launches.  The fp32 residual stream ping-pongs between xr and the
+// a1|a2 region (whose 16-bit pad rows are clobbered: the caller re-zeroes them before the next per-conv ResBlock).
+int run_pair_rb(rvcdec_handle* h, const char* group, int i, int j, const Workspace& w, int B, int Lo, int Lpo, int fs,
+                bool last, bool zs_out, void* stage_out_act, cudaStream_t s) {
+  const int C = h->ch[i];
+  float* buf[2] = {w.xr, (float*)w.a1};
+  const double el = (double)B * Lo * C;
+  for (int m = 0; m < h->nd; ++m) {
+    const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
+    const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
+    PairParams p{};
+    p.x_in = (m == 0) ? w.xs0 : buf[(m - 1) & 1];
+    p.w1 = c1.d_wp[fs == ACT_BF16 ? 1 : 0]; p.w2 = c2.d_wp[fs == ACT_BF16 ? 1 : 0];
+    p.b1 = c1.d_bias; p.b2 = c2.d_bias;
+    p.k1 = c1.ntaps; p.d1 = c1.ntaps > 1 ? c1.shift[1] - c1.shift[0] : 1;
+    p.k2 = c2.ntaps; p.d2 = c2.ntaps > 1 ? c2.shift[1] - c2.shift[0] : 1;
+    p.fmt = fs; p.slope = 0.1f; p.B = B; p.L = Lo; p.Lp = Lpo; p.margin = c1.halo + c2.halo;
+    p.scale = 1.f; p.out_slope = 0.1f; p.out_fmt = fs; p.out_zs = 1; p.Lp_out_act = Lpo;
+    double bytes = el * 8;
+    if (m < h->nd - 1) {
+      p.out_f32 = buf[m & 1];
+    } else {
+      p.scale = 1.f / (float)h->nk;
+      p.sum_in = (j == 0) ? nullptr : w.sum;
+      if (j > 0) bytes += el * 4;
+      if (j < h->nk - 1 || last) p.out_f32 = w.sum; else bytes -= el * 4;
+      if (j == h->nk - 1 && !last) {
+        p.out_act = stage_out_act;
+        if (zs_out) { p.out_zs = 2; p.Lp_out_act = padded_rows(2 * Lo); }
+        bytes += el * act_bytes(fs);
+      }
+    }
+    MARK(group, 2.0 * B * Lo * (c1.macs_per_row + c2.macs_per_row), bytes);
+    if (h->d_timing && h->timing_launches < rvcdec_handle::kTimingMaxLaunches)
+      p.timing = h->d_timing + (size_t)(h->timing_launches++) * h->num_sms * 16;
+    CK(launch_mrf_pair(p, h->num_sms, s)); ++h->launches;
+  }
+  return 0;
 }
 
 // xs = sum_j ResBlock_j(x) / nk with one launch per (conv1, conv2) pair.  The fp32 residual stream ping-pongs
@@ -653,7 +740,8 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
 
 // One pass over B items (B small enough for the workspace).
 int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float* g, const float* noise, uint64_t seed,
-                 uint64_t item0, float* out, void* wsbase, int B, int T, int mode, cudaStream_t s) {
+                 uint64_t item0, float* out, void* wsbase, int B, int T, int mode, cudaStream_t s,
+                 const uint64_t* seed_dev = nullptr) {
   const rvcdec_config& c = h->cfg;
   Workspace w = carve(h, wsbase, B, T, mode);
   const int stop = h->debug_stop;
@@ -663,7 +751,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   const int fpre = fmt_pre(mode);
 
   SourceParams sp{};
-  sp.f0 = f0; sp.noise = noise; sp.har = w.har; sp.seed = seed; sp.item0 = item0;
+  sp.f0 = f0; sp.noise = noise; sp.har = w.har; sp.seed = seed; sp.item0 = item0; sp.seed_dev = seed_dev;
   sp.B = B; sp.T = T; sp.upp = h->upp; sp.sr = (float)c.sr; sp.lin_w = h->lin_w; sp.lin_b = h->lin_b;
   if (h->no_source) {
     // stages that still run the noise_add pass (for its activated operand copy) multiply har by zero weights
@@ -726,9 +814,10 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
       if (rc) return rc;
     } else
     {  // x = ups[i](leaky_relu(x, 0.1))  (hifigan_nsf.py:185,198); the activation was applied by the producer
-      const ConvLayer& UL = pm ? h->ups_pm[i] : h->ups[i];
+      const bool p2 = use_p2(h, mode, i);
+      const ConvLayer& UL = p2 ? h->ups_p2[i] : (pm ? h->ups_pm[i] : h->ups[i]);
       Epilogue e{};
-      e.bias = UL.d_bias; e.scale = 1.f; e.slope = 0.1f; e.pm = pm ? 1 : 0;
+      e.bias = UL.d_bias; e.scale = 1.f; e.slope = 0.1f; e.pm = p2 ? 2 : (pm ? 1 : 0);
       e.out_f32 = w.xs0; e.up = u; e.cout = C; e.L_out = Lo; e.Lp_out = Lpo;
       if (fuse_noise && !h->no_source) {  // ... + noise_convs[i](har_source)  (:199)
         e.nz_har = w.har; e.nz_w = nl.d_w; e.nz_bias = nl.d_bias;
@@ -779,7 +868,19 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
         const int nb = std::min(G, B - b0);
         auto A = [&](void* p_) { return (void*)((uint8_t*)p_ + (size_t)b0 * item_el * ab); };
         auto F = [&](float* p_) { return p_ + (size_t)b0 * item_el; };
+        bool pads_dirty = false;  // a fused-pair ResBlock used the a1|a2 region as an fp32 buffer
         for (int j = 0; j < h->nk; ++j) {
+          if (G == B && pair_rb(h, mode, i, j) && !(j == h->nk - 1 && next_in_a2)) {
+            void* oa = zs_out ? w.a0 : (next_in_a2 ? w.a2 : w.a0);
+            int rc = run_pair_rb(h, g_mrf.c_str(), i, j, w, B, Lo, Lpo, fs, last, zs_out, oa, s);
+            if (rc) return rc;
+            pads_dirty = true;
+            continue;
+          }
+          if (pads_dirty) {
+            CK(launch_zero_pads(w.a1, w.a2, nullptr, act_bytes(fs), B, C, Lo, Lpo, s)); ++h->launches;
+            pads_dirty = false;
+          }
           for (int m = 0; m < h->nd; ++m) {
             const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
             const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
@@ -833,6 +934,66 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   return 0;
 }
 
+void drop_graphs(rvcdec_handle* h) {
+  for (auto& e : h->graphs) cudaGraphExecDestroy(e.exec);
+  h->graphs.clear();
+}
+
+// One pass, replayed from a CUDA graph when the same buffers / shape / mode were seen before (the reference's call
+// pattern is one B = 1 chunk after another through the same staging buffers: ~60 dependent launches each).  Anything
+// that needs host-visible side effects per launch (profiling events, debug stops, the timing twin) runs directly.
+int run_pass(rvcdec_handle* h, const float* x, const float* f0, const float* g, const float* noise, uint64_t seed,
+             uint64_t item0, float* out, void* ws, int B, int T, int mode, cudaStream_t s) {
+  const bool can = h->use_graphs && !h->prof_on && h->debug_stop == 0 && !h->d_timing;
+  if (!can) return forward_pass(h, x, f0, g, noise, seed, item0, out, ws, B, T, mode, s);
+  if (!h->d_seed) {
+    CK(cudaMalloc((void**)&h->d_seed, sizeof(uint64_t)));
+    CK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+  }
+  CK(launch_set_u64(h->d_seed, seed, s));
+  rvcdec_handle::GraphEntry* hit = nullptr;
+  for (auto& e : h->graphs)
+    if (e.x == x && e.f0 == f0 && e.g == g && e.noise == noise && e.out == out && e.ws == ws && e.B == B && e.T == T &&
+        e.mode == mode && e.item0 == item0 && e.epoch == h->epoch) { hit = &e; break; }
+  if (!hit) {
+    const int64_t before = h->launches;
+    cudaGraph_t graph = nullptr;
+    cudaError_t ce = cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed);
+    int rc = 0;
+    if (ce == cudaSuccess) {
+      rc = forward_pass(h, x, f0, g, noise, seed, item0, out, ws, B, T, mode, h->cap_stream, h->d_seed);
+      ce = cudaStreamEndCapture(h->cap_stream, &graph);
+    }
+    cudaGraphExec_t exec = nullptr;
+    if (rc == 0 && ce == cudaSuccess && graph) ce = cudaGraphInstantiate(&exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (rc != 0 || ce != cudaSuccess || !exec) {
+      // capture is an optimisation: fall back to direct launches for the rest of this handle's life
+      (void)cudaGetLastError();
+      h->use_graphs = 0;
+      h->launches = before;
+      if (rc) return rc;
+      return forward_pass(h, x, f0, g, noise, seed, item0, out, ws, B, T, mode, s);
+    }
+    if (h->graphs.size() >= 32) {  // LRU
+      size_t victim = 0;
+      for (size_t i = 1; i < h->graphs.size(); ++i) if (h->graphs[i].last_use < h->graphs[victim].last_use) victim = i;
+      cudaGraphExecDestroy(h->graphs[victim].exec);
+      h->graphs.erase(h->graphs.begin() + victim);
+    }
+    h->graphs.push_back({x, f0, g, noise, out, ws, B, T, mode, item0, h->epoch, exec, h->launches - before, 0});
+    h->launches = before;
+    hit = &h->graphs.back();
+    ++h->graph_captures;
+  } else {
+    ++h->graph_hits;
+  }
+  hit->last_use = ++h->graph_clock;
+  CK(cudaGraphLaunch(hit->exec, s));
+  h->launches += hit->launches + 1;
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -882,7 +1043,10 @@ void rvcdec_destroy(rvcdec_handle* h) {
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) == cudaSuccess && h->device < ndev) {
     DeviceGuard dguard(h->device);
+    drop_graphs(h);
     free_device(h);
+    if (h->d_seed) cudaFree(h->d_seed);
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->d_timing) cudaFree(h->d_timing);
     if (h->hbuf) cudaFree(h->hbuf);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -927,6 +1091,7 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   h->ups.assign(h->nups, ConvLayer());
   h->ups_zs.assign(h->nups, ConvLayer());
   h->ups_pm.assign(h->nups, ConvLayer());
+  h->ups_p2.assign(h->nups, ConvLayer());
   h->noise.assign(h->nups, NoiseLayer());
   h->rbconv.assign((size_t)h->nups * h->nk * h->nd * 2, ConvLayer());
   for (int i = 0; i < h->nups; ++i) {
@@ -956,6 +1121,26 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
     }
     h->ups[i].bias.resize((size_t)u * C);
     for (int r = 0; r < u; ++r) memcpy(&h->ups[i].bias[(size_t)r * C], v.data(), sizeof(float) * C);
+    if (u == 2 && C % 8 == 0) {
+      // Polyphase image of a stride-2 upsample with the columns of a slice's two phases side by side:
+      // n_new = ((co/8)*2 + r)*8 + co%8, so input row t's 16 columns of slice co/8 are output rows 2t and 2t+1.
+      const ConvLayer& S = h->ups[i];
+      ConvLayer& P = h->ups_p2[i];
+      P.name = un + "(polyphase-2)";
+      P.Cin = S.Cin; P.N_total = S.N_total; P.cout = C; P.up = u; P.ntaps = S.ntaps; P.halo = S.halo;
+      P.macs_per_row = S.macs_per_row;
+      for (int t = 0; t < S.ntaps; ++t) P.shift[t] = S.shift[t];
+      P.wf.assign(S.wf.size(), 0.f);
+      P.bias.resize((size_t)u * C);
+      for (int r = 0; r < u; ++r)
+        for (int co = 0; co < C; ++co) {
+          const int n_new = ((co / 8) * 2 + r) * 8 + co % 8;
+          P.bias[n_new] = v[co];
+          for (int t = 0; t < S.ntaps; ++t)
+            for (int ci = 0; ci < Cin; ++ci)
+              P.wf[((size_t)t * Cin + ci) * P.N_total + n_new] = S.wf[((size_t)t * Cin + ci) * S.N_total + r * C + co];
+        }
+    }
     if (u % 2 == 0 && C % 16 == 0 && conv_mma_supported(u / 2 * 16, 64) && u / 2 * 16 != 64 && Cin % 64 == 0) {
       // Phase-major column order: tile (co/16, half) holds the phases r = half*PH + rr of 16 channels as
       // column ((co/8 % 2)*PH + rr)*8 + co%8.  Each half of the phases reads two of the three input shifts, so the
@@ -1030,6 +1215,7 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   for (auto& L : h->ups) fin(L);
   for (auto& L : h->ups_zs) if (L.ntaps) finish_layer(L, true);
   for (auto& L : h->ups_pm) if (L.ntaps) { finish_layer(L, true, 256, L.up / 2 * 16); L.wf.clear(); L.wf.shrink_to_fit(); }
+  for (auto& L : h->ups_p2) if (L.ntaps) finish_layer(L, true, 128);
   for (auto& L : h->rbconv) fin(L);
   return 0;
 }
@@ -1047,11 +1233,15 @@ int rvcdec_load_weights(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t 
   }
   DeviceGuard dguard(h->device);
   CK(dguard.err);
+  CK(cudaDeviceSynchronize());  // replayed graphs may still read the old images
+  drop_graphs(h);
+  ++h->epoch;
   free_device(h);
   if ((rc = upload_layer(h, h->conv_pre))) return rc;
   for (auto& L : h->ups) if ((rc = upload_layer(h, L))) return rc;
   for (auto& L : h->ups_zs) if (L.ntaps && (rc = upload_layer(h, L))) return rc;
   for (auto& L : h->ups_pm) if (L.n_tile && (rc = upload_layer(h, L))) return rc;
+  for (auto& L : h->ups_p2) if (L.n_tile && (rc = upload_layer(h, L))) return rc;
   for (auto& L : h->rbconv) if ((rc = upload_layer(h, L))) return rc;
   for (auto& nl : h->noise) {
     if ((rc = upload(h, nl.w, &nl.d_w))) return rc;
@@ -1098,9 +1288,9 @@ int rvcdec_forward(rvcdec_handle* h, const float* x, const float* f0, const floa
   const size_t n = (size_t)T * h->upp;
   for (int b0 = 0; b0 < B; b0 += Bm) {
     const int nb = std::min(Bm, B - b0);
-    rc = forward_pass(h, x + (size_t)b0 * h->cfg.initial_channel * T, f0 + (size_t)b0 * T,
-                      g ? g + (size_t)b0 * h->cfg.gin_channels : nullptr, noise ? noise + b0 * n : nullptr, seed,
-                      (uint64_t)b0, out + b0 * n, workspace, nb, T, mode, (cudaStream_t)stream);
+    rc = run_pass(h, x + (size_t)b0 * h->cfg.initial_channel * T, f0 + (size_t)b0 * T,
+                  g ? g + (size_t)b0 * h->cfg.gin_channels : nullptr, noise ? noise + b0 * n : nullptr, seed,
+                  (uint64_t)b0, out + b0 * n, workspace, nb, T, mode, (cudaStream_t)stream);
     if (rc) return rc;
   }
   return 0;
@@ -1110,6 +1300,7 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
                         uint64_t seed, float* out, int32_t B, int32_t T, int32_t mode, size_t max_device_bytes) {
   int rc = check_forward_args(h, x, f0, g, out, B, T, mode);
   if (rc) return rc;
+  const auto t_begin = std::chrono::steady_clock::now();
   DeviceGuard dguard(h->device);
   CK(dguard.err);
   if (!h->stream) CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -1123,11 +1314,6 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
     }
   }
   const bool auto_cap = (max_device_bytes == 0);
-  if (auto_cap) {  // 60 % of what is free now (plus what this handle already holds)
-    size_t free_b = 0, total_b = 0;
-    CK(cudaMemGetInfo(&free_b, &total_b));
-    max_device_bytes = (size_t)(0.6 * (double)(free_b + h->hbuf_bytes));
-  }
   const size_t n = (size_t)T * h->upp;
   const int Cx = h->cfg.initial_channel, G = h->cfg.gin_channels;
   // two sets of input / output staging buffers (double buffering across passes) + one workspace
@@ -1138,12 +1324,24 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
   int Bm = B;
   // at least three passes on a large batch, so that most of the host<->device traffic hides behind kernels
   if (auto_cap && B >= 6) Bm = (B + 2) / 3;
+  if (auto_cap) {
+    // 60 % of what is free now (plus what this handle already holds) - but the memory query takes a device-wide lock
+    // and was seen to cost milliseconds (tools/latency_bench.py), so it is skipped when the scratch this handle
+    // already owns covers the preferred split (the steady state of a per-chunk caller)
+    if (2 * io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes <= h->hbuf_bytes) {
+      max_device_bytes = h->hbuf_bytes;
+    } else {
+      size_t free_b = 0, total_b = 0;
+      CK(cudaMemGetInfo(&free_b, &total_b));
+      max_device_bytes = (size_t)(0.6 * (double)(free_b + h->hbuf_bytes));
+    }
+  }
   while (Bm > 1 && 2 * io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes > max_device_bytes) Bm = (Bm + 1) / 2;
   while (Bm < B && !(auto_cap && B >= 6 && Bm >= (B + 2) / 3) &&
          2 * io_bytes(Bm + 1) + carve(h, nullptr, Bm + 1, T, mode).bytes <= max_device_bytes) ++Bm;
   const size_t need = 2 * io_bytes(Bm) + carve(h, nullptr, Bm, T, mode).bytes;
   if (need > h->hbuf_bytes) {
-    if (h->hbuf) { CK(cudaDeviceSynchronize()); CK(cudaFree(h->hbuf)); h->hbuf = nullptr; h->hbuf_bytes = 0; }
+    if (h->hbuf) { CK(cudaDeviceSynchronize()); drop_graphs(h); CK(cudaFree(h->hbuf)); h->hbuf = nullptr; h->hbuf_bytes = 0; }
     CK(cudaMalloc(&h->hbuf, need));
     h->hbuf_bytes = need;
   }
@@ -1175,7 +1373,7 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
     // kernels: need the inputs, and the output staging buffer drained by the copy of two passes ago
     CK(cudaStreamWaitEvent(h->stream, h->ev_in[s2], 0));
     if (pass >= 2) CK(cudaStreamWaitEvent(h->stream, h->ev_out[s2], 0));
-    rc = forward_pass(h, dx[s2], df0[s2], (g && G) ? dg[s2] : nullptr, dnz[s2], seed, (uint64_t)b0, dout[s2], ws, nb, T, mode, h->stream);
+    rc = run_pass(h, dx[s2], df0[s2], (g && G) ? dg[s2] : nullptr, dnz[s2], seed, (uint64_t)b0, dout[s2], ws, nb, T, mode, h->stream);
     if (rc) return rc;
     CK(cudaEventRecord(h->ev_comp[s2], h->stream));
     // waveform of this pass back to the host while the next pass computes
@@ -1185,9 +1383,15 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
   }
   return 0;
   };
+  const auto t_setup = std::chrono::steady_clock::now();
   rc = run_passes();
+  const auto t_enq = std::chrono::steady_clock::now();
   const cudaError_t e1 = cudaStreamSynchronize(h->h2d_stream), e2 = cudaStreamSynchronize(h->stream),
                     e3 = cudaStreamSynchronize(h->d2h_stream);
+  const auto t_end = std::chrono::steady_clock::now();
+  h->host_t[0] = std::chrono::duration<double>(t_setup - t_begin).count();
+  h->host_t[1] = std::chrono::duration<double>(t_enq - t_setup).count();
+  h->host_t[2] = std::chrono::duration<double>(t_end - t_enq).count();
   if (rc) return rc;  // (message of the first failure is kept)
   CK(e1); CK(e2); CK(e3);
   return 0;
@@ -1233,6 +1437,18 @@ int32_t rvcdec_profile_read(rvcdec_handle* h, rvcdec_profile_entry* out, int32_t
 int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
   if (!h || !key) return fail(RVCDEC_ERR_ARG, "null argument");
   const std::string k = key;
+  ++h->epoch;  // any knob may change the launch sequence: captured graphs of older epochs are never replayed
+  if (!h->graphs.empty()) {
+    DeviceGuard dguard(h->device);
+    CK(dguard.err);
+    CK(cudaDeviceSynchronize());
+    drop_graphs(h);
+  }
+  if (k == "graphs") {
+    if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "graphs must be 0 or 1");
+    h->use_graphs = (int)value;
+    return 0;
+  }
   if (k == "fused_timing") {  // allocate / reset the timing buffer of the instrumented fused kernel
     DeviceGuard dguard(h->device);
     CK(dguard.err);
@@ -1269,6 +1485,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     h->ups_pm_on = (int)value;
     return 0;
   }
+  if (k == "poly2") {
+    if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "poly2 must be 0 or 1");
+    h->poly2 = (int)value;
+    return 0;
+  }
   if (k == "zero_stuff") {
     if (value < 0 || value > 1) return fail(RVCDEC_ERR_ARG, "zero_stuff must be 0 or 1");
     h->zero_stuff = (int)value;
@@ -1296,6 +1517,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
   }
   if (k == "pair_noise") { h->pair_noise = value ? 1 : 0; return RVCDEC_OK; }
   if (k == "pair_mrf") { h->pair_mrf = value ? 1 : 0; return RVCDEC_OK; }
+  if (k == "pair_max_k") {
+    if (value < 0 || value > 64) return fail(RVCDEC_ERR_ARG, "pair_max_k out of range");
+    h->pair_max_k = (int)value;
+    return RVCDEC_OK;
+  }
   if (k == "fused_epi_warps") {
     if (value != 8 && value != 16) return fail(RVCDEC_ERR_ARG, "fused_epi_warps must be 8 or 16");
     h->fused_epi_warps = (int)value;
@@ -1308,6 +1534,18 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     return 0;
   }
   return fail(RVCDEC_ERR_ARG, "unknown option '%s'", key);
+}
+
+double rvcdec_debug_stat(const rvcdec_handle* h, const char* name) {
+  if (!h || !name) return -1.0;
+  const std::string k = name;
+  if (k == "graph_hits") return (double)h->graph_hits;
+  if (k == "graph_captures") return (double)h->graph_captures;
+  if (k == "graphs_cached") return (double)h->graphs.size();
+  if (k == "host_setup_s") return h->host_t[0];
+  if (k == "host_enqueue_s") return h->host_t[1];
+  if (k == "host_wait_s") return h->host_t[2];
+  return -1.0;
 }
 
 int rvcdec_debug_set_stop(rvcdec_handle* h, int32_t stop_after) {
@@ -1385,6 +1623,7 @@ int64_t rvcdec_debug_packed(const rvcdec_handle* h, const char* layer, int32_t k
   if (nm == h->conv_pre.name) L = &h->conv_pre;
   for (auto& u : h->ups) if (u.name == nm) L = &u;
   for (auto& u : h->ups_pm) if (u.ntaps && u.name == nm) L = &u;
+  for (auto& u : h->ups_p2) if (u.ntaps && u.name == nm) L = &u;
   for (auto& r : h->rbconv) if (r.name == nm) L = &r;
   if (!L) return fail(RVCDEC_ERR_ARG, "unknown layer '%s'", layer);
   const void* src = nullptr;

@@ -247,3 +247,147 @@ def test_nof0_sibling_logmel_margins(dev):
     e32, ef, corr = _margins("nof0_40k_B2_T300", y32, yf, y_ref, cfg.sr)
     assert e32 <= 1e-4, e32
     assert corr["min"] >= FAST_BAR, corr
+
+
+def test_multi_gpu_runner_long_form_matches_oracle_and_survives_a_failed_worker(dev):
+    """runner.MultiGpuDecoder (BASELINE configs[4]): t_pad-overlap chunks dealt to one worker per device, waveforms
+    gathered by the D2H copies into one pinned buffer, host trim + concat.  fp32 mode with injected noise against the
+    oracle run chunk by chunk; then two workers (both on cuda:0 - the box has one GPU here) of which one fails its
+    batch: its units are re-dealt and the result is unchanged."""
+    from rvc_b200 import chunking as ch
+    from rvc_b200 import MultiGpuDecoder
+
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 23)
+    w = O.folded_weights(m.state_dict())
+    n_frames, pad = 500, 100
+    total = n_frames + 2 * pad
+    x, f0, g, _ = O.synth_inputs(cfg, 1, total, seed=10)
+    noise = torch.randn(1, total * cfg.upp, generator=torch.Generator().manual_seed(4))
+    splits = [120, 260, 390]
+    chunks = ch.plan_chunks(n_frames, split_points=splits)
+    refs = [O.decoder_forward(w, cfg, x[:, :, c.start:c.stop], f0[:, c.start:c.stop], g,
+                              noise[:, c.start * cfg.upp:c.stop * cfg.upp])[0, 0].numpy() for c in chunks]
+    y_ref = ch.stitch(refs, [c.trim * cfg.upp for c in chunks])
+    ndev = torch.cuda.device_count()
+    dec = MultiGpuDecoder(m, devices=list(range(ndev)), mode="fp32")
+    y = dec.decode_long(x, f0, g, split_points=splits, noise=noise)
+    assert y.shape == y_ref.shape == (n_frames * cfg.upp,)
+    assert float(np.abs(y - y_ref).max()) <= FP32_BAR
+    assert sum(s["units"] for s in dec.stats()) == len(chunks)
+    dec.close()
+    # one of two workers fails: re-queue
+    dec2 = MultiGpuDecoder(m, devices=[0, ndev - 1] if ndev > 1 else [0, 0], mode="fp32")
+    calls = {"n": 0}
+
+    def hook(device, share):
+        calls["n"] += 1
+        return calls["n"] == 2  # the second batch submitted (whichever worker) fails once
+    dec2.fail_hook = hook
+    y2 = dec2.decode_long(x, f0, g, split_points=splits, noise=noise)
+    st = dec2.stats()
+    assert dec2.requeued >= 1 and sum(1 for s in st if not s["healthy"]) == 1, st
+    assert float(np.abs(y2 - y).max()) <= 1e-5
+    # fast mode with in-kernel noise + sin^2 crossfade: shape / range, and the current device is left alone
+    cur = torch.cuda.current_device()
+    dec3 = MultiGpuDecoder(m, mode="fast")
+    y3 = dec3.decode_long(x, f0, g, split_points=splits, crossfade=240, seed=7)
+    assert torch.cuda.current_device() == cur
+    assert y3.shape == (n_frames * cfg.upp,) and np.isfinite(y3).all() and float(np.abs(y3).max()) <= 1.0
+    dec2.close(); dec3.close()
+
+
+def test_graph_replay_is_bit_identical_to_direct_launches(dev):
+    """rvcdec_set_option("graphs"): the launch sequence of a pass replayed from a CUDA graph (captured once per buffers /
+    shape / mode; the Philox key comes from device memory) against direct launches - same kernels, same arguments,
+    bit-identical waveforms, for injected noise, for in-kernel noise under two seeds, and through the host-buffer call."""
+    cfg = O.CONFIG_48K
+    m = build_module(cfg, 31).to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, 2, 60, seed=15)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    outs = {}
+    with torch.no_grad():
+        h = m._ensure_handle(dev)
+        for graphs in (0, 1):
+            h.set_option("graphs", graphs)
+            ys = []
+            for rep in range(3):  # rep 0 captures (graphs = 1), reps 1-2 replay when the allocator hands back the same buffers
+                ys.append(m(xd, fd, gd, noise=nd_, mode="fast").clone())
+            assert torch.equal(ys[0], ys[1]) and torch.equal(ys[0], ys[2])
+            torch.manual_seed(1); p1 = m(xd, fd, gd, noise="philox", mode="fast").clone()
+            torch.manual_seed(2); p2 = m(xd, fd, gd, noise="philox", mode="fast").clone()
+            torch.manual_seed(1); p1b = m(xd, fd, gd, noise="philox", mode="fast").clone()
+            assert torch.equal(p1, p1b) and not torch.equal(p1, p2)
+            torch.manual_seed(1); hh = [m.decode_host(x, f0, g, mode="fast").clone() for _ in range(2)]
+            torch.manual_seed(1); hh.append(m.decode_host(x, f0, g, mode="fast").clone())
+            assert torch.equal(hh[0], hh[2]) and not torch.equal(hh[0], hh[1])
+            outs[graphs] = (ys[0].cpu(), p1.cpu(), p2.cpu(), hh[0], m(xd, fd, gd, noise=nd_, mode="fp32").cpu())
+        h.set_option("graphs", 1)
+    for a, b in zip(outs[0], outs[1]):
+        assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("max_k", [3, 7, 11])
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 81), ("40k", 1, 97, 82), ("48k", 3, 2, 83)])
+def test_mixed_pair_and_per_conv_resblocks_agree(dev, max_k, cfg_name, B, T, seed):
+    """rvcdec_set_option("pair_max_k"): on the 128-channel stage the ResBlocks with kernel size <= max_k run the
+    fused-pair kernel (fp32 residual in TMEM, output rows drained by bulk async stores from per-warp staging), the
+    others one launch per conv.  Same operands and fp32 accumulation: the waveforms agree to rounding order, and each
+    meets the fast bar.  Covers items shorter than a tile, several tiles per item and ragged tile ends."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K}[cfg_name]
+    m = build_module(cfg, 9000 + seed)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        h = m._ensure_handle(dev)
+        h.set_option("pair_max_k", 0)
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        h.set_option("pair_max_k", max_k)
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        y1b = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+        h.set_option("pair_max_k", 0)
+    n_pair_rb = sum(1 for k in cfg.resblock_kernel_sizes if k <= max_k)
+    assert n1 <= n0 - 3 * n_pair_rb + 1, (n0, n1)  # 6 conv launches -> 3 pair launches per ResBlock (+ one pad re-zero)
+    assert torch.equal(y1, y1b)
+    assert float((y1 - y0).abs().max()) <= 2e-3, float((y1 - y0).abs().max())
+    if T >= 50:
+        assert O.multires_logmel_corr(y1, y_ref, cfg.sr)["min"] >= FAST_BAR
+
+
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 91), ("40k", 1, 97, 92), ("48k", 3, 2, 93), ("32k", 2, 61, 94)])
+def test_stride2_polyphase_upsample_matches_zero_stuffed_form(dev, cfg_name, B, T, seed):
+    """rvcdec_set_option("poly2"): the stride-2 upsamples in true polyphase form (dense 16-bit input, GEMM columns ordered
+    (slice, phase, channel), two output rows per accumulator row, noise conv fused) against the zero-stuffed ordinary
+    convolution they replace: same operand values and the same products, so the stage inputs agree to fp32 summation
+    order.  Ragged lengths exercise partial tiles; T = 2 an item shorter than a tile."""
+    import sys
+    sys.path.insert(0, __file__.rsplit("/", 1)[0])
+    from test_gpu import layer_taps
+
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K, "32k": O.CONFIG_32K}[cfg_name]
+    m = build_module(cfg, 9100 + seed)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        h = m._ensure_handle(dev)
+        h.set_option("poly2", 0)
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        t0 = layer_taps(m, cfg, xd, fd, gd, nd_, "fast")
+        h.set_option("poly2", 1)
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        t1 = layer_taps(m, cfg, xd, fd, gd, nd_, "fast")
+    for k in ("stage1.out", "stage2.in", "stage2.out", "stage3.in"):
+        scale = max(1.0, float(t0[k].abs().max()))
+        tol = 2e-5 * scale + (2e-2 * scale if k == "stage2.out" else 0)  # stage 2's output went through 16-bit chains
+        assert float((t1[k] - t0[k]).abs().max()) <= tol, (k, float((t1[k] - t0[k]).abs().max()))
+    assert float((y1 - y0).abs().max()) <= 2e-3
+    if T >= 50:
+        assert O.multires_logmel_corr(y1, y_ref, cfg.sr)["min"] >= FAST_BAR

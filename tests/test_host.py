@@ -240,3 +240,121 @@ def test_gloo_world2_sharding(tmp_path):
                         "--master-port", "29533", str(script)], capture_output=True, text=True, env=env, timeout=300)
     assert p.returncode == 0, p.stdout + p.stderr
     assert p.stdout.count("ok") == 2
+
+
+def test_gloo_world2_long_form_decode_chunks_and_gather(tmp_path):
+    """The torchrun form of BASELINE configs[4] on CPU with gloo, world size 2: chunking.decode_chunks(rank, world)
+    deals the t_pad-overlap chunks longest-first, each rank decodes its share as one zero-padded batch through the
+    host-buffer call (a stand-in model with the decoder's interface: sample s of a chunk depends only on the frames
+    within +-3 of it, like a conv stack with a short receptive field), chunking.gather_chunks collects the results on
+    rank 0 and the stitched utterance equals the single-rank run."""
+    script = tmp_path / "lf.py"
+    script.write_text(
+        "import os, sys, numpy as np, torch, torch.distributed as dist\n"
+        f"sys.path.insert(0, {ROOT!r})\n"
+        "from rvc_b200 import chunking as ch\n"
+        "class Fake:\n"
+        "    upp = 4\n"
+        "    def decode_host(self, x, f0, g, mode=None, device=None, out=None):\n"
+        "        B, C, T = x.shape\n"
+        "        k = torch.ones(1, C, 7) / (7 * C)\n"
+        "        y = torch.nn.functional.conv1d(x, k, padding=3)          # (B, 1, T): receptive field +-3 frames\n"
+        "        y = y.repeat_interleave(self.upp, dim=2) + 1e-3 * f0.repeat_interleave(self.upp, dim=1)[:, None]\n"
+        "        return y + (0 if g is None else g.sum(dim=(1, 2))[:, None, None])\n"
+        "dist.init_process_group('gloo')\n"
+        "r, w = dist.get_rank(), dist.get_world_size()\n"
+        "gen = torch.Generator().manual_seed(3)\n"
+        "n_frames, pad = 900, 100\n"
+        "x = torch.randn(1, 8, n_frames + 2 * pad, generator=gen); f0 = torch.rand(1, n_frames + 2 * pad, generator=gen) * 200\n"
+        "g = torch.randn(1, 4, 1, generator=gen)\n"
+        "chunks = ch.plan_chunks(n_frames, split_points=[250, 430, 700])\n"
+        "mine = ch.decode_chunks(Fake(), x, f0, g, chunks, rank=r, world=w)\n"
+        "assert set(mine) == set(ch.shard_units([c.frames for c in chunks], w)[r]), mine.keys()\n"
+        "y = ch.gather_chunks(mine, chunks, Fake.upp)\n"
+        "if r == 0:\n"
+        "    single = ch.decode_chunks(Fake(), x, f0, g, chunks)\n"
+        "    y1 = ch.stitch([single[c.index] for c in chunks], [c.trim * Fake.upp for c in chunks])\n"
+        "    whole = Fake().decode_host(x, f0, g)[0, 0].numpy()[pad * 4: -pad * 4]\n"
+        "    assert y.shape == (n_frames * 4,) and np.allclose(y, y1, atol=1e-6) and np.allclose(y, whole, atol=1e-6)\n"
+        "else:\n"
+        "    assert y is None\n"
+        "print('ok', r, sorted(mine))\n"
+    )
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29534", str(script)], capture_output=True, text=True, env=env, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert p.stdout.count("ok") == 2
+
+
+def test_runner_deals_requeues_and_gathers_without_a_gpu():
+    """runner.MultiGpuDecoder's host logic (LPT dealing, one pinned output buffer, re-queue of a failed worker's units)
+    with stand-in handles: worker 1 fails its first batch, its units are re-dealt to worker 0 and every unit still
+    arrives at its offset."""
+    import numpy as np
+    import torch
+    from rvc_b200 import runner as R
+
+    class FakeHandle:
+        def __init__(self, dev):
+            self.dev, self.calls = dev, 0
+
+        def forward_host(self, x, f0, g, noise, seed, out, B, T, mode, cap):
+            import ctypes as C
+            self.calls += 1
+            xs = np.ctypeslib.as_array(C.cast(x, C.POINTER(C.c_float)), shape=(B, 8, T))
+            ys = np.ctypeslib.as_array(C.cast(out, C.POINTER(C.c_float)), shape=(B, T * 4))
+            ys[:] = np.repeat(xs.sum(1), 4, axis=1)
+
+        def close(self):
+            pass
+
+    dec = R.MultiGpuDecoder.__new__(R.MultiGpuDecoder)
+    dec.mode, dec.upp, dec.cin, dec.gin, dec.requeued = 1, 4, 8, 0, 0
+    dec.workers = [R._Worker(0, FakeHandle(0)), R._Worker(1, FakeHandle(1))]
+    dec.fail_hook = lambda dev, share: dev == 1
+    x = torch.randn(1, 8, 1000)
+    f0 = torch.zeros(1, 1000)
+    units = [R.Unit(0, 0, 300), R.Unit(1, 250, 200), R.Unit(2, 400, 300), R.Unit(3, 650, 350)]
+    out, offs = dec.decode_units(x, f0, None, units)
+    for u in units:
+        want = np.repeat(x[0, :, u.start:u.start + u.frames].sum(0).numpy(), 4)
+        got = out[offs[u.index]: offs[u.index] + u.frames * 4].numpy()
+        assert np.allclose(got, want, atol=1e-6), u
+    st = dec.stats()
+    assert st[1]["healthy"] is False and "injected" in st[1]["error"] and st[0]["units"] == 4 and dec.requeued == 2
+
+
+def test_stride2_polyphase_images(built_lib):
+    """The stride-2 upsamples also get a true polyphase image with the columns of a slice's two phases side by side
+    (n = ((co/8)*2 + r)*8 + co%8): evaluated as the kernel does (input row t -> output rows 2t, 2t+1) it reproduces
+    ConvTranspose1d(k=4, stride 2, padding 1) of hifigan_nsf.py:111-130."""
+    from rvc_b200 import _lib
+
+    d, cfg = load_golden("v2_48k_B2_T24")
+    sd = golden_state(d, cfg)
+    w = O.folded_weights(sd)
+    h = _lib.Handle(_lib.make_config(*cfg.ctor_args(), cfg.gin_channels, cfg.sr), 0)
+    h.pack_host(sd)
+    gen = torch.Generator().manual_seed(1)
+    for i, (Cin, C, nt) in ((2, (128, 64, 128)), (3, (64, 32, 64))):
+        name = f"ups.{i}(polyphase-2)"
+        meta = [int(v) for v in h.packed(name, 5)]
+        assert meta[:5] == [Cin, 2 * C, C, 2, 3] and meta[6:] == [nt, 64], meta
+        wf = h.packed(name, 0).reshape(3, Cin, 2 * C)
+        shifts = [int(v) for v in h.packed(name, 2)]
+        assert shifts == [-1, 0, 1]
+        bias = torch.from_numpy(h.packed(name, 6)).double()
+        x = torch.randn(2, Cin, 29, generator=gen)
+        xp = F.pad(x, (1, 1)).double()
+        D = torch.zeros(2, 29, 2 * C, dtype=torch.float64)
+        for tap, s in enumerate(shifts):
+            D += xp[:, :, 1 + s: 1 + s + 29].transpose(1, 2) @ torch.from_numpy(wf[tap]).double()
+        D = D + bias
+        got = D.reshape(2, 29, C // 8, 2, 8).permute(0, 2, 4, 1, 3).reshape(2, C, 58)  # (b, slice, c, t, r) -> (b, co, 2t + r)
+        exp = F.conv_transpose1d(x.double(), w[f"ups.{i}.weight"].double(), w[f"ups.{i}.bias"].double(), stride=2, padding=1)
+        assert float((got - exp).abs().max()) < 2e-6, name
+        # every phase uses two of the three shifts: the shift -1 block is zero in the r = 1 columns and vice versa
+        cols = np.arange(2 * C).reshape(C // 8, 2, 8)
+        assert not np.any(wf[0][:, cols[:, 1].ravel()]) and not np.any(wf[2][:, cols[:, 0].ravel()])
+    h.close()
