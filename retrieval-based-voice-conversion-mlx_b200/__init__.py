@@ -10,8 +10,9 @@ from . import chunking  # noqa: F401
 from . import configs  # noqa: F401
 from . import loader  # noqa: F401
 from .loader import load_checkpoint  # noqa: F401
+from .synthesizer import Synthesizer  # noqa: F401
 from . import runner  # noqa: F401
 from .runner import MultiGpuDecoder  # noqa: F401
 
 __all__ = ["HiFiGANGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking", "configs", "loader",
-           "load_checkpoint", "runner", "MultiGpuDecoder"]
+           "load_checkpoint", "runner", "MultiGpuDecoder", "Synthesizer"]

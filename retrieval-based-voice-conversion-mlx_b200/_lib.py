@@ -40,6 +40,13 @@ class Config(C.Structure):
     ]
 
 
+class SynConfig(C.Structure):
+    """rvcsyn_config (include/rvcsyn.h)."""
+    _fields_ = [(n, C.c_int32) for n in ("inter_channels", "hidden_channels", "filter_channels", "n_heads", "n_layers", "kernel_size",
+                                         "text_dim", "spk_embed_dim", "gin_channels", "use_f0", "window_size", "flow_kernel",
+                                         "flow_layers", "n_flows")] + [("dec", Config)]
+
+
 class Tensor(C.Structure):
     _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64)]
 
@@ -52,6 +59,9 @@ EXPORTS = [
     "rvcdec_create", "rvcdec_load_weights", "rvcdec_workspace_bytes", "rvcdec_forward", "rvcdec_forward_host",
     "rvcdec_set_option", "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
     "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_debug_stat", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
+    # include/rvcsyn.h
+    "rvcsyn_create", "rvcsyn_load_weights", "rvcsyn_workspace_bytes", "rvcsyn_infer", "rvcsyn_decoder", "rvcsyn_last_launch_count",
+    "rvcsyn_destroy", "rvcsyn_last_error", "rvcsyn_debug_set_stop", "rvcsyn_debug_read",
 ]
 
 _lib = None
@@ -103,6 +113,26 @@ def lib() -> C.CDLL:
     L.rvcdec_last_error.restype = C.c_char_p
     L.rvcdec_version.argtypes = []
     L.rvcdec_version.restype = C.c_char_p
+    L.rvcsyn_create.argtypes = [C.POINTER(SynConfig), C.c_int, C.POINTER(vp)]
+    L.rvcsyn_create.restype = C.c_int
+    L.rvcsyn_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]
+    L.rvcsyn_load_weights.restype = C.c_int
+    L.rvcsyn_workspace_bytes.argtypes = [vp, i32, i32, i32]
+    L.rvcsyn_workspace_bytes.restype = sz
+    L.rvcsyn_infer.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, u64, vp, vp, vp, sz, i32, i32, i32, vp]
+    L.rvcsyn_infer.restype = C.c_int
+    L.rvcsyn_debug_set_stop.argtypes = [vp, i32]
+    L.rvcsyn_debug_set_stop.restype = C.c_int
+    L.rvcsyn_debug_read.argtypes = [vp, C.c_char_p, vp, i64, vp, i32, i32, vp]
+    L.rvcsyn_debug_read.restype = i64
+    L.rvcsyn_decoder.argtypes = [vp]
+    L.rvcsyn_decoder.restype = vp
+    L.rvcsyn_last_launch_count.argtypes = [vp]
+    L.rvcsyn_last_launch_count.restype = i64
+    L.rvcsyn_destroy.argtypes = [vp]
+    L.rvcsyn_destroy.restype = None
+    L.rvcsyn_last_error.argtypes = []
+    L.rvcsyn_last_error.restype = C.c_char_p
     _lib = L
     return L
 
@@ -140,6 +170,54 @@ def make_config(initial_channel: int, resblock_kernel_sizes: Sequence[int], resb
         for m, d in enumerate(resblock_dilation_sizes[j]):
             c.resblock_dilation_sizes[j][m] = d
     return c
+
+
+class SynHandle:
+    """Owns one rvcsyn_handle (the whole Synthesizer.infer; include/rvcsyn.h)."""
+
+    def __init__(self, cfg: SynConfig, device: int):
+        self._h = C.c_void_p()
+        rc = lib().rvcsyn_create(C.byref(cfg), int(device), C.byref(self._h))
+        if rc < 0:
+            raise RuntimeError(f"rvcsyn_create failed ({rc}): {(lib().rvcsyn_last_error() or b'').decode()}")
+        self.device = int(device)
+
+    def _check(self, rc: int, what: str) -> None:
+        if rc < 0:
+            raise RuntimeError(f"{what} failed ({rc}): {(lib().rvcsyn_last_error() or b'').decode()}")
+
+    def load_weights(self, state: Dict[str, "object"]) -> None:
+        arr, keep = Handle._tensor_array(None, state)
+        self._check(lib().rvcsyn_load_weights(self._h, arr, len(state)), "rvcsyn_load_weights")
+
+    def workspace_bytes(self, B: int, T: int, mode: int) -> int:
+        return int(lib().rvcsyn_workspace_bytes(self._h, B, T, mode))
+
+    def infer(self, phone, lengths, pitch, nsff0, sid, noise_zp, noise_src, seed, out, z_out, workspace, B, T, mode, stream) -> None:
+        self._check(lib().rvcsyn_infer(self._h, phone, lengths, pitch, nsff0, sid, noise_zp, noise_src, C.c_uint64(seed & (2**64 - 1)), out,
+                                       z_out, workspace.data_ptr(), workspace.numel(), B, T, mode, stream), "rvcsyn_infer")
+
+    def set_stop(self, stop: int) -> None:
+        self._check(lib().rvcsyn_debug_set_stop(self._h, int(stop)), "rvcsyn_debug_set_stop")
+
+    def debug_read(self, name: str, dst, workspace, B: int, T: int, stream) -> int:
+        n = lib().rvcsyn_debug_read(self._h, name.encode(), dst.data_ptr(), dst.numel(), workspace.data_ptr(), B, T, stream)
+        self._check(n, "rvcsyn_debug_read")
+        return int(n)
+
+    def launch_count(self) -> int:
+        return int(lib().rvcsyn_last_launch_count(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            lib().rvcsyn_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class Handle:

@@ -74,6 +74,9 @@ struct Epilogue {
   // conv_mma.cu "phase-major"; requires an even `up` and cout % 16 == 0.  A fused noise conv must then have
   // stride 4, 8 taps, padding 2.
   int pm;
+  // optional per-item valid length (rows >= lengths[b] are written as zeros: the x * x_mask of the reference's masked
+  // sequence models, encoders.py:139; honoured by the fp32 back-end and the generic tensor-core epilogue)
+  const int* lengths;
 };
 
 // One convolution as an implicit GEMM:  D[t, n] = sum_tap sum_ci A[t + shift[tap], ci] * W[tap][ci][n]
@@ -91,6 +94,8 @@ struct ConvParams {
   int a_stages;            // activation ring depth of the 128-wide tensor-core tiling (3; anything else = 2)
   int epi_warps_small;     // same for the 64- / 32-wide tilings (zero-stuffed stride-2 upsamples, per-conv stages 2-3)
   int epi_warps;           // 16 = the 128-wide tiling runs 16 epilogue warps over 16-column items; anything else = 8 / 32
+  int in_slices_phys;      // fp32 back-end: 8-channel slices per item of the tensor act_in points into (0 = Cin / 8); lets a
+                           // convolution read a channel sub-range of a wider tensor (coupling layers, residuals.py:239)
   Epilogue epi;
 };
 
@@ -144,6 +149,10 @@ __device__ __forceinline__ void epilogue_store(const Epilogue& e, int b, int t_i
       const float4 q = *reinterpret_cast<const float4*>(e.sum_in + off + i);
       v[i] += q.x; v[i + 1] += q.y; v[i + 2] += q.z; v[i + 3] += q.w;
     }
+  }
+  if (e.lengths && row >= __ldg(e.lengths + b)) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = 0.f;
   }
   if (e.out_f32) {
 #pragma unroll

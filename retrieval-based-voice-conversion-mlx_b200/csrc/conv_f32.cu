@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(256) conv_f32_kernel(const __grid_constant__ C
   const int n0 = n_tile * F32_TN;
   const uint32_t mask = p.tapmask[n_tile];
   const int nsl = p.Cin >> 3;
+  const int nsl_phys = p.in_slices_phys ? p.in_slices_phys : nsl;
   const int rows = F32_TM + 2 * p.halo;
   const float* act = reinterpret_cast<const float*>(p.act_in);
   const float* W = reinterpret_cast<const float*>(p.w);
@@ -43,7 +44,7 @@ __global__ void __launch_bounds__(256) conv_f32_kernel(const __grid_constant__ C
 
   for (int cs = 0; cs < nsl; ++cs) {
     // stage activations: rows t0-halo .. t0+TM+halo of slice cs, transposed
-    const float* src = act + (((size_t)b * nsl + cs) * p.Lp_in + PADL + t0 - p.halo) * 8;
+    const float* src = act + (((size_t)b * nsl_phys + cs) * p.Lp_in + PADL + t0 - p.halo) * 8;
     for (int i = tid; i < rows * 2; i += 256) {
       const int r = i >> 1, h = i & 1;
       const float4 q = *reinterpret_cast<const float4*>(src + (size_t)r * 8 + h * 4);

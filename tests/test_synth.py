@@ -1,0 +1,164 @@
+"""the rest of Synthesizer.infer (emb_g, TextEncoder, z_p sampling, reverse flow) in front of the decoder.
+CPU tests pin the oracle restatement (oracle/synth_oracle.py) and the module's seeded initialisation against the golden
+generated from the unmodified reference (oracle/make_golden_r2.py --synth); GPU tests run rvc_b200.Synthesizer.infer
+(module -> ctypes -> rvcsyn_infer) against that golden and against the oracle at a larger, ragged shape."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nsf_hifigan_oracle as O
+from oracle import synth_oracle as SO
+from helpers import GOLDEN, record_parity
+
+SYN_48K = [1025, 32, 192, 192, 768, 2, 6, 3, 0, "1", [3, 7, 11], [[1, 3, 5], [1, 3, 5], [1, 3, 5]], [12, 10, 2, 2], 512,
+           [24, 20, 4, 4], 109, 256, 48000]
+CFGD = dict(inter_channels=192, hidden_channels=192, n_heads=2, n_layers=6, kernel_size=3)
+
+
+def _golden():
+    return np.load(os.path.join(GOLDEN, "synth_48k_B2_T40.npz"))
+
+
+def _module(d):
+    """rvc_b200.Synthesizer initialised under the fixture's seed, with the fixture's non-zero flow.post tensors."""
+    import rvc_b200
+
+    torch.manual_seed(int(d["init_seed"]))
+    m = rvc_b200.Synthesizer(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").eval()
+    with torch.no_grad():
+        for k in d.files:
+            if k.startswith("sd::"):
+                dict(m.named_parameters())[k[4:]].copy_(torch.from_numpy(d[k]))
+    return m
+
+
+def _inputs(d):
+    return (torch.from_numpy(d["phone"].astype(np.float32)), torch.from_numpy(d["lengths"]), torch.from_numpy(d["pitch"]),
+            torch.from_numpy(d["nsff0"]), torch.from_numpy(d["sid"]), torch.from_numpy(d["noise_zp"]),
+            torch.from_numpy(d["noise_src"].astype(np.float32)))
+
+
+def test_module_init_and_oracle_match_the_reference_golden():
+    d = _golden()
+    m = _module(d)
+    sd = m.state_dict()
+    cks = [k for k in d.files if k.startswith("ck::")]
+    # every tensor infer.py:484-485 keeps (the fixture was written after `del net_g.enc_q`)
+    assert sorted(k[4:] for k in cks) == sorted(k for k in sd.keys() if not k.startswith("enc_q."))
+    for k in cks:
+        v = sd[k[4:]].double()
+        np.testing.assert_allclose(np.array([float(v.sum()), float(v.abs().sum())]), d[k], rtol=1e-12, atol=1e-12, err_msg=k)
+    phone, lens, pitch, nsff0, sid, nzp, nsrc = _inputs(d)
+    W = SO.folded({k: v for k, v in sd.items() if not k.startswith("enc_q.")})
+    zm, g, mask, z_p, m_p, logs_p = SO.synthesizer_front(W, CFGD, phone, lens, pitch, sid, nzp)
+    assert float((z_p - torch.from_numpy(d["z_p"])).abs().max()) <= 2e-5
+    assert float((m_p - torch.from_numpy(d["m_p"])).abs().max()) <= 2e-5
+    assert float((zm - torch.from_numpy(d["z"])).abs().max()) <= 2e-5
+    assert float(zm[1, :, 29:].abs().max()) == 0.0  # item 1 is 29 frames long: masked frames are exactly zero
+    Wd = O.folded_weights({k[4:]: v for k, v in sd.items() if k.startswith("dec.")})
+    y = O.decoder_forward(Wd, O.CONFIG_48K, zm, nsff0, g, nsrc)
+    assert float((y - torch.from_numpy(d["o"])).abs().max()) <= 2e-5
+    with pytest.raises(RuntimeError):
+        m.infer(phone, lens, pitch, nsff0, sid)  # CPU tensors: no fallback
+
+
+@pytest.mark.skipif(__import__("oracle.stage_ref", fromlist=["ref_path"]).ref_path() is None, reason="reference not importable")
+def test_seeded_init_equals_the_live_reference_including_enc_q():
+    import sys
+    from oracle.stage_ref import ref_path
+    import rvc_b200
+
+    if ref_path() not in sys.path:
+        sys.path.insert(0, ref_path())
+    from rvc.lib.algorithm.synthesizers import Synthesizer as Ref
+
+    torch.manual_seed(11)
+    a = Ref(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").state_dict()
+    torch.manual_seed(11)
+    b = rvc_b200.Synthesizer(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").state_dict()
+    assert list(a.keys()) == list(b.keys()) and len(a) == 560
+    assert all(torch.equal(a[k], b[k]) for k in a)
+    torch.manual_seed(12)
+    a = Ref(*SYN_48K, use_f0=0, text_enc_hidden_dim=768, vocoder="HiFi-GAN").state_dict()
+    torch.manual_seed(12)
+    b = rvc_b200.Synthesizer(*SYN_48K, use_f0=0, text_enc_hidden_dim=768, vocoder="HiFi-GAN").state_dict()
+    assert list(a.keys()) == list(b.keys()) and all(torch.equal(a[k], b[k]) for k in a)
+
+
+def test_flip_folding_is_a_channel_reversal():
+    """The library folds the flow's Flip layers into the neighbouring 1x1 convolutions (rvcsyn.cu): a coupling layer that
+    sees flip(x) reads the upper channel half in reverse order and updates the lower half in reverse order."""
+    torch.manual_seed(0)
+    x = torch.randn(1, 8, 5)
+    pre, post = torch.randn(6, 4, 1), torch.randn(4, 6, 1)
+    xf = torch.flip(x, [1])
+    x0, x1 = xf[:, :4], xf[:, 4:]
+    m = torch.nn.functional.conv1d(torch.tanh(torch.nn.functional.conv1d(x0, pre)), post)
+    ref = torch.flip(torch.cat([x0, x1 - m], 1), [1])                       # back in the storage frame
+    pre_f, post_f = torch.flip(pre, [1]), torch.flip(post, [0])             # reversed input / output channels
+    m2 = torch.nn.functional.conv1d(torch.tanh(torch.nn.functional.conv1d(x[:, 4:], pre_f)), post_f)
+    got = torch.cat([x[:, :4] - m2, x[:, 4:]], 1)
+    assert float((got - ref).abs().max()) <= 1e-6
+
+
+@pytest.mark.gpu
+def test_synthesizer_infer_matches_the_reference_golden():
+    d = _golden()
+    dev = torch.device("cuda", 0)
+    m = _module(d).to(dev)
+    phone, lens, pitch, nsff0, sid, nzp, nsrc = _inputs(d)
+    o, x_mask, (z, _, _, _) = m.infer(phone.to(dev), lens.to(dev), pitch.to(dev), nsff0.to(dev), sid.to(dev),
+                                      noise_zp=nzp.to(dev), noise_src=nsrc.to(dev), mode="fp32")
+    o_ref, z_ref = torch.from_numpy(d["o"]), torch.from_numpy(d["z"])
+    assert o.shape == o_ref.shape == (2, 1, 40 * 480) and x_mask.shape == (2, 1, 40)
+    ez, eo = float((z.cpu() - z_ref).abs().max()), float((o.cpu() - o_ref).abs().max())
+    assert float(z[1, :, 29:].abs().max()) == 0.0
+    assert ez <= 1e-4, ez
+    assert eo <= 2e-3, eo
+    of, _, _ = m.infer(phone.to(dev), lens.to(dev), pitch.to(dev), nsff0.to(dev), sid.to(dev),
+                       noise_zp=nzp.to(dev), noise_src=nsrc.to(dev), mode="fast")
+    corr = O.multires_logmel_corr(of.cpu(), o_ref, 48000)
+    record_parity({"test": "synthesizer_infer_golden_B2_T40", "z_max_abs": ez, "fp32_max_abs": eo, "fast_logmel": corr,
+                   "launches": m.last_launch_count})
+    assert corr["min"] >= 0.999, corr
+
+
+@pytest.mark.gpu
+def test_synthesizer_infer_against_the_oracle_at_a_ragged_batch():
+    """B = 3, T = 333 (several attention tiles, a partial last tile), lengths 333 / 200 / 64; default noise = device
+    generator draws in the reference's order."""
+    import rvc_b200
+
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(77)
+    m = rvc_b200.Synthesizer(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").eval()
+    with torch.no_grad():
+        for i in range(4):
+            m.flow.flows[2 * i].post.weight.normal_(0, 0.05)
+            m.flow.flows[2 * i].post.bias.normal_(0, 0.05)
+    sd = m.state_dict()
+    B, T = 3, 333
+    gen = torch.Generator().manual_seed(5)
+    phone = torch.randn(B, T, 768, generator=gen)
+    pitch = torch.randint(1, 256, (B, T), generator=gen)
+    nsff0 = O.synth_f0(B, T, gen)
+    sid = torch.tensor([0, 57, 108])
+    lens = torch.tensor([333, 200, 64])
+    m = m.to(dev)
+    torch.manual_seed(9)
+    o, x_mask, (z, _, _, _) = m.infer(phone.to(dev), lens.to(dev), pitch.to(dev), nsff0.to(dev), sid.to(dev), mode="fp32")
+    torch.manual_seed(9)
+    nzp = torch.randn(B, 192, T, device=dev).cpu()
+    torch.rand(1, 1, 1, device=dev)
+    nsrc = torch.randn(B, T * 480, 1, device=dev).cpu().reshape(B, -1)
+    W = SO.folded({k: v for k, v in sd.items() if not k.startswith("enc_q.")})
+    zm, g, mask, *_ = SO.synthesizer_front(W, CFGD, phone, lens, pitch, sid, nzp)
+    Wd = O.folded_weights({k[4:]: v for k, v in sd.items() if k.startswith("dec.")})
+    y = O.decoder_forward(Wd, O.CONFIG_48K, zm, nsff0, g, nsrc)
+    ez, eo = float((z.cpu() - zm).abs().max()), float((o.cpu() - y).abs().max())
+    record_parity({"test": "synthesizer_infer_oracle_B3_T333_ragged", "z_max_abs": ez, "fp32_max_abs": eo})
+    assert torch.equal(x_mask.cpu(), mask)
+    assert ez <= 2e-4, ez
+    assert eo <= 2e-3, eo
