@@ -66,6 +66,10 @@ typedef struct {
   int32_t resblock_kernel_sizes[RVCDEC_MAX_KERNELS];   /* 3,7,11 (odd) */
   int32_t num_dilations;                   /* 3 */
   int32_t resblock_dilation_sizes[RVCDEC_MAX_KERNELS][RVCDEC_MAX_DILATIONS]; /* 1,3,5 */
+  int32_t harmonic_num;                    /* overtones of the harmonic source: 0 = HiFiGANNSFGenerator (hifigan_nsf.py:93);
+                                              8 = the sibling HiFiGANMRFGenerator (hifigan_mrf.py:223-374 as built at
+                                              synthesizers.py:86-97): 9 sines with random initial phases, Linear(9, 1) merge,
+                                              and a conv_post with a bias */
 } rvcdec_config;
 
 /* One fp32 tensor of the decoder's state_dict, in HOST memory, named exactly as
@@ -107,6 +111,12 @@ int rvcdec_forward(rvcdec_handle* h, const float* x, const float* f0, const floa
                    const float* noise, uint64_t seed, float* out,
                    void* workspace, size_t workspace_bytes,
                    int32_t B, int32_t T, int32_t mode, void* stream);
+
+/* Sources with overtones (harmonic_num > 0): `noise` of rvcdec_forward is then (B, T*upp, harmonic_num+1) and the random
+ * initial phases the reference draws with torch.rand(B, harmonic_num+1) (hifigan_mrf.py:129-134; column 0 is forced to 0)
+ * are taken from `phases` (DEVICE, (B, harmonic_num+1), cycles in [0,1)) by every following rvcdec_forward on this handle;
+ * NULL (the default) = drawn in-kernel from the Philox key. */
+int rvcdec_set_initial_phases(rvcdec_handle* h, const float* phases);
 
 /* Same call with HOST buffers (pinned memory recommended): copies inputs to the
  * device, decodes, copies the waveform back, and returns after the copy has

@@ -332,3 +332,73 @@ def multires_logmel_corr(y: torch.Tensor, y_ref: torch.Tensor, sr: int) -> Dict[
     res["min"] = min(vals)
     res["mean"] = sum(vals) / len(vals)
     return res
+
+
+# --------------------------------------------------------------------------
+# Sibling decoder HiFiGANMRFGenerator (rvc/lib/algorithm/generators/hifigan_mrf.py:223-374)
+# --------------------------------------------------------------------------
+def mrf_sine_source(f0: torch.Tensor, upp: int, sr: int, rand_ini: torch.Tensor, noise: torch.Tensor, dtype: torch.dtype = torch.float64,
+                    sine_amp: float = 0.1, noise_std: float = 0.003) -> torch.Tensor:
+    """SineGenerator.forward of the MRF variant (hifigan_mrf.py:86-176) in closed form.
+
+    The reference upsamples f0 to the sample rate (nearest, :338), forms rad = (f0 * (k+1) / sr) % 1 per harmonic k, adds a
+    random initial phase to sample 0 of every overtone (:129-134) and takes a per-sample cumsum with an explicit wrap
+    correction (:137-142); sin(2 pi x) only sees the cumsum modulo 1.  Because f0 is constant inside a frame the cumsum is
+    closed-form there:  phase_k[l*upp + j] = ini_k + (k+1) * (sum_{l'<l} upp * f0[l']/sr + (j+1) * f0[l]/sr)  (mod 1),
+    so only a FRAME-level prefix is needed.  dtype float64 is the accumulation the CUDA kernel uses; the reference's fp32
+    per-sample cumsum differs from it by its own rounding (grows with the number of samples).
+    f0 (B, T); rand_ini (B, H) uniform [0,1) with column 0 = 0; noise (B, T*upp, H).  Returns (B, T*upp, H)."""
+    B, T = f0.shape
+    H = rand_ini.shape[1]
+    f = f0.to(dtype) / sr
+    prefix = torch.cumsum(f * upp, dim=1) - f * upp                       # (B, T): advance before frame l
+    j = torch.arange(1, upp + 1, dtype=dtype)
+    base = (prefix.unsqueeze(-1) + f.unsqueeze(-1) * j).reshape(B, T * upp)  # fundamental phase (cycles)
+    k = torch.arange(1, H + 1, dtype=dtype)
+    phase = base.unsqueeze(-1) * k + rand_ini.to(dtype).unsqueeze(1)
+    sines = torch.sin(2 * math.pi * (phase - torch.floor(phase))) * sine_amp
+    uv = (f0 > 0).to(dtype).repeat_interleave(upp, dim=1).unsqueeze(-1)
+    amp = uv * noise_std + (1 - uv) * sine_amp / 3
+    return (sines * uv + amp * noise.to(dtype)).to(torch.float32)
+
+
+def mrf_state_to_nsf_names(state: Dict[str, torch.Tensor], nk: int) -> Dict[str, torch.Tensor]:
+    """HiFiGANMRFGenerator state dict -> the NSF decoder's names (same layers under other names):
+    upsamples.i -> ups.i, mrfs.i.j.layers.m.conv1/conv2 -> resblocks.(i*nk+j).convs1/convs2.m."""
+    out = {}
+    for k, v in state.items():
+        if k.startswith("upsamples."):
+            k = "ups." + k[len("upsamples."):]
+        elif k.startswith("mrfs."):
+            p = k.split(".")
+            i, j, m, which = int(p[1]), int(p[2]), int(p[4]), p[5]
+            k = f"resblocks.{i * nk + j}.convs{1 if which == 'conv1' else 2}.{m}." + ".".join(p[6:])
+        out[k] = v
+    return out
+
+
+def decoder_forward_mrf(w: Dict[str, torch.Tensor], cfg: DecoderConfig, x, f0, g, rand_ini, noise, dtype=torch.float32,
+                        source_dtype=torch.float64) -> torch.Tensor:
+    """HiFiGANMRFGenerator.forward (hifigan_mrf.py:335-367).  ``w`` = folded weights under the NSF names
+    (mrf_state_to_nsf_names + folded_weights); conv_post has a bias here (:327-329), l_linear is (1, H)."""
+    W = {k: v.to(dtype) for k, v in w.items()}
+    nk = len(cfg.resblock_kernel_sizes)
+    s = mrf_sine_source(f0, cfg.upp, cfg.sr, rand_ini, noise, dtype=source_dtype).to(dtype)   # (B, n, H)
+    har = torch.tanh(F.linear(s, W["m_source.l_linear.weight"], W["m_source.l_linear.bias"])).transpose(1, 2)  # (B, 1, n)
+    x = F.conv1d(x.to(dtype), W["conv_pre.weight"], W["conv_pre.bias"], padding=3)
+    if g is not None:
+        x = x + F.conv1d(g.to(dtype), W["cond.weight"], W["cond.bias"])
+    for i, (u, k) in enumerate(zip(cfg.upsample_rates, cfg.upsample_kernel_sizes)):
+        x = F.leaky_relu(x, LRELU_SLOPE)
+        x = F.conv_transpose1d(x, W[f"ups.{i}.weight"], W[f"ups.{i}.bias"], stride=u, padding=(k - u) // 2)
+        stride = math.prod(cfg.upsample_rates[i + 1:]) if i + 1 < len(cfg.upsample_rates) else 1
+        nkern = 1 if stride == 1 else stride * 2 - stride % 2
+        npad = 0 if stride == 1 else (nkern - stride) // 2
+        x = x + F.conv1d(har, W[f"noise_convs.{i}.weight"], W[f"noise_convs.{i}.bias"], stride=stride, padding=npad)
+        xs = None
+        for j in range(nk):
+            y = resblock_forward(W, f"resblocks.{i * nk + j}", x, cfg.resblock_kernel_sizes[j], cfg.resblock_dilation_sizes[j])
+            xs = y if xs is None else xs + y
+        x = xs / nk
+    x = F.leaky_relu(x)
+    return torch.tanh(F.conv1d(x, W["conv_post.weight"], W["conv_post.bias"], padding=3)).float()

@@ -4,7 +4,7 @@ Only the decoder hot path lives here; see DESIGN.md for scope.  Importing this p
 load the CUDA library; the first ``forward`` (or ``_lib.lib()``) does, and fails loudly if it is
 missing.
 """
-from .decoder import HiFiGANGenerator, HiFiGANNSFGenerator, ResBlock, SourceModuleHnNSF  # noqa: F401
+from .decoder import HiFiGANGenerator, HiFiGANMRFGenerator, HiFiGANNSFGenerator, ResBlock, SourceModuleHnNSF  # noqa: F401
 from . import _lib  # noqa: F401
 from . import chunking  # noqa: F401
 from . import configs  # noqa: F401
@@ -14,5 +14,5 @@ from .synthesizer import Synthesizer  # noqa: F401
 from . import runner  # noqa: F401
 from .runner import MultiGpuDecoder  # noqa: F401
 
-__all__ = ["HiFiGANGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking", "configs", "loader",
+__all__ = ["HiFiGANGenerator", "HiFiGANMRFGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking", "configs", "loader",
            "load_checkpoint", "runner", "MultiGpuDecoder", "Synthesizer"]

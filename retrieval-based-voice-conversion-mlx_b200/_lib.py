@@ -37,6 +37,7 @@ class Config(C.Structure):
         ("resblock_kernel_sizes", C.c_int32 * MAX_KERNELS),
         ("num_dilations", C.c_int32),
         ("resblock_dilation_sizes", (C.c_int32 * MAX_DIL) * MAX_KERNELS),
+        ("harmonic_num", C.c_int32),
     ]
 
 
@@ -57,7 +58,7 @@ class ProfileEntry(C.Structure):
 
 EXPORTS = [
     "rvcdec_create", "rvcdec_load_weights", "rvcdec_workspace_bytes", "rvcdec_forward", "rvcdec_forward_host",
-    "rvcdec_set_option", "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
+    "rvcdec_set_option", "rvcdec_set_initial_phases", "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
     "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_debug_stat", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
     # include/rvcsyn.h
     "rvcsyn_create", "rvcsyn_load_weights", "rvcsyn_workspace_bytes", "rvcsyn_infer", "rvcsyn_decoder", "rvcsyn_last_launch_count",
@@ -89,6 +90,8 @@ def lib() -> C.CDLL:
     L.rvcdec_forward_host.restype = C.c_int
     L.rvcdec_set_option.argtypes = [vp, C.c_char_p, i64]
     L.rvcdec_set_option.restype = C.c_int
+    L.rvcdec_set_initial_phases.argtypes = [vp, vp]
+    L.rvcdec_set_initial_phases.restype = C.c_int
     L.rvcdec_last_launch_count.argtypes = [vp]
     L.rvcdec_last_launch_count.restype = i64
     L.rvcdec_profile_enable.argtypes = [vp, i32]
@@ -148,7 +151,7 @@ def check(rc: int, what: str) -> None:
 
 def make_config(initial_channel: int, resblock_kernel_sizes: Sequence[int], resblock_dilation_sizes,
                 upsample_rates: Sequence[int], upsample_initial_channel: int, upsample_kernel_sizes: Sequence[int],
-                gin_channels: int, sr: int) -> Config:
+                gin_channels: int, sr: int, harmonic_num: int = 0) -> Config:
     if len(upsample_rates) > MAX_UPS or len(resblock_kernel_sizes) > MAX_KERNELS:
         raise ValueError("too many upsample / resblock stages")
     nd = {len(d) for d in resblock_dilation_sizes}
@@ -159,6 +162,7 @@ def make_config(initial_channel: int, resblock_kernel_sizes: Sequence[int], resb
     c.upsample_initial_channel = upsample_initial_channel
     c.gin_channels = gin_channels
     c.sr = sr
+    c.harmonic_num = harmonic_num
     c.num_upsamples = len(upsample_rates)
     for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
         c.upsample_rates[i] = u
@@ -275,6 +279,9 @@ class Handle:
     def forward_host(self, x, f0, g, noise, seed, out, B, T, mode, max_device_bytes=0) -> None:
         check(lib().rvcdec_forward_host(self._h, x, f0, g, noise, C.c_uint64(seed & (2**64 - 1)), out, B, T, mode,
                                         max_device_bytes), "rvcdec_forward_host")
+
+    def set_initial_phases(self, ptr) -> None:
+        check(lib().rvcdec_set_initial_phases(self._h, ptr), "rvcdec_set_initial_phases")
 
     def set_option(self, key: str, value: int) -> None:
         check(lib().rvcdec_set_option(self._h, key.encode(), int(value)), "rvcdec_set_option")

@@ -74,12 +74,37 @@ __global__ void __launch_bounds__(SRC_THREADS) source_kernel(SourceParams p) {
   for (int i = threadIdx.x; i < nsamp; i += SRC_THREADS) {
     const int fr = i / p.upp;
     const int k = i - fr * p.upp;
-    const double ph = s_finc[fr] * (double)(k + 1) + s_C[fr];
-    const float frac = (float)(ph - floor(ph));
-    const float sine = 0.1f * sinpif(2.0f * frac);
-    const float z = p.noise ? __ldg(p.noise + base + i) : philox_normal(seed, pbase + (uint64_t)i);
-    const float v = (s_f0[fr] > 0.f) ? (sine + 0.003f * z) : ((0.1f / 3.0f) * z);
-    p.har[base + i] = tanhf(p.lin_w * v + p.lin_b);
+    const double ph = s_finc[fr] * (double)(k + 1) + s_C[fr];  // fundamental phase in cycles (closed form inside a frame)
+    const bool voiced = s_f0[fr] > 0.f;
+    if (p.H <= 1) {
+      const float frac = (float)(ph - floor(ph));
+      const float sine = 0.1f * sinpif(2.0f * frac);
+      const float z = p.noise ? __ldg(p.noise + base + i) : philox_normal(seed, pbase + (uint64_t)i);
+      const float v = voiced ? (sine + 0.003f * z) : ((0.1f / 3.0f) * z);
+      p.har[base + i] = tanhf(p.lin_w * v + p.lin_b);
+    } else {
+      // overtone k2 runs at (k2 + 1) times the fundamental's phase plus its own initial phase (hifigan_mrf.py:124-142:
+      // per-sample cumsum of (f0 (k2+1) / sr) % 1 with rand_ini added to sample 0)
+      float acc = p.lin_b;
+      for (int k2 = 0; k2 < p.H; ++k2) {
+        float ini = 0.f;
+        if (k2 > 0) {
+          if (p.rand_ini) ini = __ldg(p.rand_ini + (size_t)b * p.H + k2);
+          else {
+            const uint64_t ci = (1ull << 62) + (p.item0 + (uint64_t)b) * (uint64_t)p.H + (uint64_t)k2;
+            ini = (float)philox4x32_10((uint32_t)ci, (uint32_t)(ci >> 32), (uint32_t)seed, (uint32_t)(seed >> 32)).x * 2.3283064365386963e-10f;
+          }
+        }
+        const double phk = ph * (double)(k2 + 1) + (double)ini;
+        const float frac = (float)(phk - floor(phk));
+        const float sine = 0.1f * sinpif(2.0f * frac);
+        const uint64_t ni = (uint64_t)(base + i) * (uint64_t)p.H + (uint64_t)k2;
+        const float z = p.noise ? __ldg(p.noise + ni) : philox_normal(seed, (pbase + (uint64_t)i) * (uint64_t)p.H + (uint64_t)k2);
+        const float v = voiced ? (sine + 0.003f * z) : ((0.1f / 3.0f) * z);
+        acc = fmaf(p.lin_wv[k2], v, acc);
+      }
+      p.har[base + i] = tanhf(acc);
+    }
   }
 }
 
@@ -346,7 +371,7 @@ cudaError_t launch_noise_add(const NoiseAddParams& p, cudaStream_t s) {
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) post_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                    float* __restrict__ out, int B, int C, int L, int Lp, int k,
-                                                   float slope) {
+                                                   float slope, float bias) {
   extern __shared__ float sw[];  // [k][C]
   for (int i = threadIdx.x; i < k * C; i += blockDim.x) sw[i] = w[i];
   __syncthreads();
@@ -371,14 +396,14 @@ __global__ void __launch_bounds__(256) post_kernel(const float* __restrict__ x, 
         acc = fmaf(lrelu(q1.z, slope), wj[6], acc); acc = fmaf(lrelu(q1.w, slope), wj[7], acc);
       }
     }
-    out[i] = tanhf(acc);
+    out[i] = tanhf(acc + bias);
   }
 }
 
 // k = 7 specialisation: every thread produces 4 consecutive samples from a 10-row window, so each
 // input row is fetched 2.5x instead of 7x per output (the generic kernel above is L1-bandwidth bound).
 __global__ void __launch_bounds__(256) post7_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                                    float* __restrict__ out, int B, int C, int L, int Lp, float slope) {
+                                                    float* __restrict__ out, int B, int C, int L, int Lp, float slope, float bias) {
   extern __shared__ float sw[];  // [7][C]
   for (int i = threadIdx.x; i < 7 * C; i += blockDim.x) sw[i] = w[i];
   __syncthreads();
@@ -415,26 +440,26 @@ __global__ void __launch_bounds__(256) post7_kernel(const float* __restrict__ x,
     }
     float* o = out + (size_t)b * L + t0;
     if (t0 + 3 < L && ((reinterpret_cast<uintptr_t>(o) & 15u) == 0)) {
-      *reinterpret_cast<float4*>(o) = make_float4(tanhf(acc[0]), tanhf(acc[1]), tanhf(acc[2]), tanhf(acc[3]));
+      *reinterpret_cast<float4*>(o) = make_float4(tanhf(acc[0] + bias), tanhf(acc[1] + bias), tanhf(acc[2] + bias), tanhf(acc[3] + bias));
     } else {
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        if (t0 + q < L) o[q] = tanhf(acc[q]);
+        if (t0 + q < L) o[q] = tanhf(acc[q] + bias);
     }
   }
 }
 
 cudaError_t launch_post(const float* x, const float* w, float* out, int B, int C, int L, int Lp, int k, float slope,
-                        cudaStream_t s) {
+                        cudaStream_t s, float bias) {
   if (k == 7) {
     const size_t total = (size_t)B * ((L + 3) / 4);
     const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
-    post7_kernel<<<blocks, 256, (size_t)7 * C * sizeof(float), s>>>(x, w, out, B, C, L, Lp, slope);
+    post7_kernel<<<blocks, 256, (size_t)7 * C * sizeof(float), s>>>(x, w, out, B, C, L, Lp, slope, bias);
     return cudaGetLastError();
   }
   const size_t total = (size_t)B * L;
   const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 32));
-  post_kernel<<<blocks, 256, (size_t)k * C * sizeof(float), s>>>(x, w, out, B, C, L, Lp, k, slope);
+  post_kernel<<<blocks, 256, (size_t)k * C * sizeof(float), s>>>(x, w, out, B, C, L, Lp, k, slope, bias);
   return cudaGetLastError();
 }
 

@@ -249,6 +249,7 @@ struct FusedParams {
                          // them as constant operands instead of taking shared-memory bandwidth from the MMAs
   float* post_out;      // (B, L)
   float post_slope;
+  float post_bias;      // conv_post bias (0 for the NSF decoder, hifigan_nsf.py:164; the MRF sibling has one, hifigan_mrf.py:327)
   FusedRB rb[FUSED_MAX_RB];
 };
 bool mrf_fused_supported(int C, int max_taps, int max_halo);
@@ -291,6 +292,12 @@ struct SourceParams {
                      // only, so the waveform does not depend on how a batch is cut into passes
   int B, T, upp;
   float sr, lin_w, lin_b;
+  // sources with overtones (HiFiGANMRFGenerator, hifigan_mrf.py:86-176): H = harmonic_num + 1 sines, harmonic k at (k+1) f0
+  // with initial phase rand_ini[b][k] (cycles; null = in-kernel uniform draws, 0 for k = 0), noise (B, T*upp, H), merged by
+  // Linear(H, 1) = lin_wv . v + lin_b.  H = 1 is the NSF source (lin_wv[0] = lin_w).
+  int H;
+  float lin_wv[16];
+  const float* rand_ini;
 };
 cudaError_t launch_source(const SourceParams& p, cudaStream_t s);
 cudaError_t launch_set_u64(uint64_t* dst, uint64_t v, cudaStream_t s);
@@ -316,7 +323,7 @@ struct NoiseAddParams {
 cudaError_t launch_noise_add(const NoiseAddParams& p, cudaStream_t s);
 // out[b][t] = tanh(sum_j sum_c w[j][c] * lrelu(x[b][c][t+j-pad], slope))
 cudaError_t launch_post(const float* x, const float* w, float* out, int B, int C, int L, int Lp, int k, float slope,
-                        cudaStream_t s);
+                        cudaStream_t s, float bias = 0.f);
 // blocked-8 (fp32 or 16-bit) -> plain (B, C, L) fp32, for tests
 cudaError_t launch_unpack(const void* src, int fmt, float* dst, int B, int C, int L, int Lp, cudaStream_t s, int row_stride = 1);
 

@@ -590,7 +590,7 @@ __global__ void __launch_bounds__(fused_threads(EW), 1) mrf_fused_kernel(const _
 #pragma unroll
                     for (int c = 0; c < CG; ++c) acc += q[c * cg_stride];
                   }
-                  p.post_out[(size_t)u.item * p.L + to] = tanhf(acc);
+                  p.post_out[(size_t)u.item * p.L + to] = tanhf(acc + p.post_bias);
                 }
               }
             }

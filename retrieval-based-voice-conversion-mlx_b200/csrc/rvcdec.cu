@@ -101,6 +101,10 @@ struct rvcdec_handle {
   std::vector<float> post_w;  // [k][C]
   std::vector<float> cond_w, cond_b;
   float lin_w = 1.f, lin_b = 0.f;
+  int H = 1;                 // sines of the harmonic source (cfg.harmonic_num + 1)
+  float lin_wv[16] = {0};    // m_source.l_linear weights (H of them)
+  float post_bias = 0.f;     // conv_post bias (optional tensor; the MRF sibling has one)
+  const float* rand_ini = nullptr;  // rvcdec_set_initial_phases
   float* d_post_w = nullptr;
   float* d_cond_w = nullptr;
   float* d_cond_b = nullptr;
@@ -149,7 +153,7 @@ struct rvcdec_handle {
   int use_graphs = 1;
   uint64_t epoch = 0;  // bumped by everything that changes the launch sequence (options, weights): drops the cache
   struct GraphEntry {
-    const void *x, *f0, *g, *noise, *out, *ws;
+    const void *x, *f0, *g, *noise, *out, *ws, *ini;
     int B, T, mode;
     uint64_t item0, epoch;
     cudaGraphExec_t exec;
@@ -665,7 +669,7 @@ int run_fused_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w
   };
   const double post_fl = post_out ? 2.0 * B * Lo * C * 7 : 0.0;
   auto arm_post = [&]() {  // the launch that completes the MRF average also produces the waveform
-    p.post_w = h->d_post_w; p.post_out = post_out; p.post_slope = 0.01f; p.out_f32 = nullptr; p.margin += 3;
+    p.post_w = h->d_post_w; p.post_out = post_out; p.post_slope = 0.01f; p.post_bias = h->post_bias; p.out_f32 = nullptr; p.margin += 3;
     for (size_t q = 0; q < h->post_w.size() && q < sizeof(p.post_wc) / sizeof(float); ++q) p.post_wc[q] = h->post_w[q];
   };
   if (h->fused_mrf == 2) {
@@ -753,11 +757,13 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   SourceParams sp{};
   sp.f0 = f0; sp.noise = noise; sp.har = w.har; sp.seed = seed; sp.item0 = item0; sp.seed_dev = seed_dev;
   sp.B = B; sp.T = T; sp.upp = h->upp; sp.sr = (float)c.sr; sp.lin_w = h->lin_w; sp.lin_b = h->lin_b;
+  sp.H = h->H; sp.rand_ini = h->rand_ini ? h->rand_ini + (size_t)item0 * h->H : nullptr;
+  for (int k = 0; k < 16; ++k) sp.lin_wv[k] = h->lin_wv[k];
   if (h->no_source) {
     // stages that still run the noise_add pass (for its activated operand copy) multiply har by zero weights
     CK(cudaMemsetAsync(w.har, 0, (size_t)B * T * h->upp * sizeof(float), s));
   } else {
-    MARK("source", 0, (double)B * T * h->upp * (noise ? 8 : 4));
+    MARK("source", 0, (double)B * T * h->upp * (noise ? 4 + 4 * h->H : 4));
     CK(launch_source(sp, s)); ++h->launches;
   }
   if (stop == 1) { MARK(nullptr, 0, 0); return 0; }
@@ -928,7 +934,7 @@ int forward_pass(rvcdec_handle* h, const float* x, const float* f0, const float*
   // x = tanh(conv_post(leaky_relu(x)))  (:209-210), default slope 0.01
   if (!post_fused) {
     MARK("conv_post", 2.0 * B * L * h->ch[h->nups - 1] * 7, (double)B * L * (h->ch[h->nups - 1] * 4 + 4));
-    CK(launch_post(w.sum, h->d_post_w, out, B, h->ch[h->nups - 1], L, padded_rows(L), 7, 0.01f, s)); ++h->launches;
+    CK(launch_post(w.sum, h->d_post_w, out, B, h->ch[h->nups - 1], L, padded_rows(L), 7, 0.01f, s, h->post_bias)); ++h->launches;
   }
   MARK(nullptr, 0, 0);
   return 0;
@@ -953,7 +959,7 @@ int run_pass(rvcdec_handle* h, const float* x, const float* f0, const float* g, 
   CK(launch_set_u64(h->d_seed, seed, s));
   rvcdec_handle::GraphEntry* hit = nullptr;
   for (auto& e : h->graphs)
-    if (e.x == x && e.f0 == f0 && e.g == g && e.noise == noise && e.out == out && e.ws == ws && e.B == B && e.T == T &&
+    if (e.x == x && e.f0 == f0 && e.g == g && e.noise == noise && e.out == out && e.ws == ws && e.ini == h->rand_ini && e.B == B && e.T == T &&
         e.mode == mode && e.item0 == item0 && e.epoch == h->epoch) { hit = &e; break; }
   if (!hit) {
     const int64_t before = h->launches;
@@ -981,7 +987,7 @@ int run_pass(rvcdec_handle* h, const float* x, const float* f0, const float* g, 
       cudaGraphExecDestroy(h->graphs[victim].exec);
       h->graphs.erase(h->graphs.begin() + victim);
     }
-    h->graphs.push_back({x, f0, g, noise, out, ws, B, T, mode, item0, h->epoch, exec, h->launches - before, 0});
+    h->graphs.push_back({x, f0, g, noise, out, ws, h->rand_ini, B, T, mode, item0, h->epoch, exec, h->launches - before, 0});
     h->launches = before;
     hit = &h->graphs.back();
     ++h->graph_captures;
@@ -1010,8 +1016,10 @@ int rvcdec_create(const rvcdec_config* cfg, int device, rvcdec_handle** out) {
     return fail(RVCDEC_ERR_ARG, "bad layer counts");
   if (c.initial_channel % 8 || c.initial_channel <= 0) return fail(RVCDEC_ERR_ARG, "initial_channel must be a positive multiple of 8");
   if (c.sr <= 0 || c.gin_channels < 0) return fail(RVCDEC_ERR_ARG, "bad sr / gin_channels");
+  if (c.harmonic_num < 0 || c.harmonic_num > 15) return fail(RVCDEC_ERR_ARG, "harmonic_num must be in [0, 15]");
   auto h = new rvcdec_handle();
   h->cfg = c; h->device = device; h->nups = c.num_upsamples; h->nk = c.num_kernels; h->nd = c.num_dilations;
+  h->H = c.harmonic_num + 1;
   h->upp = 1;
   for (int i = 0; i < h->nups; ++i) {
     const int u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
@@ -1072,8 +1080,9 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   std::vector<float> W, v;
   const int C0 = c.upsample_initial_channel;
   // m_source.l_linear (hifigan_nsf.py:45)
-  if ((rc = get_vec(tm, "m_source.l_linear.weight", 1, v))) return rc;
+  if ((rc = get_vec(tm, "m_source.l_linear.weight", h->H, v))) return rc;
   h->lin_w = v[0];
+  for (int k = 0; k < 16; ++k) h->lin_wv[k] = k < h->H ? v[k] : 0.f;
   if ((rc = get_vec(tm, "m_source.l_linear.bias", 1, v))) return rc;
   h->lin_b = v[0];
   // conv_pre (:95-97)
@@ -1201,6 +1210,11 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   // conv_post (:164): (1, C, 7) no bias -> [j][c]
   const int Cl = h->ch[h->nups - 1];
   if ((rc = get_weight(tm, "conv_post", 1, (int64_t)Cl * 7, W))) return rc;
+  h->post_bias = 0.f;
+  if (const rvcdec_tensor* pb = tm.find("conv_post.bias")) {  // hifigan_mrf.py:327-329 (the NSF decoder's conv_post has none)
+    if (pb->numel != 1) return fail(RVCDEC_ERR_WEIGHTS, "conv_post.bias: expected 1 element");
+    h->post_bias = pb->data[0];
+  }
   h->post_w.resize((size_t)7 * Cl);
   for (int cc = 0; cc < Cl; ++cc)
     for (int j = 0; j < 7; ++j) h->post_w[(size_t)j * Cl + cc] = W[(size_t)cc * 7 + j];
@@ -1289,7 +1303,7 @@ int rvcdec_forward(rvcdec_handle* h, const float* x, const float* f0, const floa
   for (int b0 = 0; b0 < B; b0 += Bm) {
     const int nb = std::min(Bm, B - b0);
     rc = run_pass(h, x + (size_t)b0 * h->cfg.initial_channel * T, f0 + (size_t)b0 * T,
-                  g ? g + (size_t)b0 * h->cfg.gin_channels : nullptr, noise ? noise + b0 * n : nullptr, seed,
+                  g ? g + (size_t)b0 * h->cfg.gin_channels : nullptr, noise ? noise + b0 * n * h->H : nullptr, seed,
                   (uint64_t)b0, out + b0 * n, workspace, nb, T, mode, (cudaStream_t)stream);
     if (rc) return rc;
   }
@@ -1319,7 +1333,7 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
   // two sets of input / output staging buffers (double buffering across passes) + one workspace
   auto io_bytes = [&](int b) {
     return align_up((size_t)b * Cx * T * 4, 256) + align_up((size_t)b * T * 4, 256) + align_up((size_t)b * std::max(G, 1) * 4, 256) +
-           (noise ? align_up((size_t)b * n * 4, 256) : 0) + align_up((size_t)b * n * 4, 256);
+           (noise ? align_up((size_t)b * n * h->H * 4, 256) : 0) + align_up((size_t)b * n * 4, 256);
   };
   int Bm = B;
   // at least three passes on a large batch, so that most of the host<->device traffic hides behind kernels
@@ -1351,7 +1365,7 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
     dx[s2] = (float*)p; p += align_up((size_t)Bm * Cx * T * 4, 256);
     df0[s2] = (float*)p; p += align_up((size_t)Bm * T * 4, 256);
     dg[s2] = (float*)p; p += align_up((size_t)Bm * std::max(G, 1) * 4, 256);
-    if (noise) { dnz[s2] = (float*)p; p += align_up((size_t)Bm * n * 4, 256); }
+    if (noise) { dnz[s2] = (float*)p; p += align_up((size_t)Bm * n * h->H * 4, 256); }
     dout[s2] = (float*)p; p += align_up((size_t)Bm * n * 4, 256);
   }
   void* ws = p;
@@ -1368,7 +1382,7 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
     CK(cudaMemcpyAsync(dx[s2], x + (size_t)b0 * Cx * T, (size_t)nb * Cx * T * 4, cudaMemcpyHostToDevice, h->h2d_stream));
     CK(cudaMemcpyAsync(df0[s2], f0 + (size_t)b0 * T, (size_t)nb * T * 4, cudaMemcpyHostToDevice, h->h2d_stream));
     if (g && G) CK(cudaMemcpyAsync(dg[s2], g + (size_t)b0 * G, (size_t)nb * G * 4, cudaMemcpyHostToDevice, h->h2d_stream));
-    if (noise) CK(cudaMemcpyAsync(dnz[s2], noise + b0 * n, nb * n * 4, cudaMemcpyHostToDevice, h->h2d_stream));
+    if (noise) CK(cudaMemcpyAsync(dnz[s2], noise + b0 * n * h->H, nb * n * h->H * 4, cudaMemcpyHostToDevice, h->h2d_stream));
     CK(cudaEventRecord(h->ev_in[s2], h->h2d_stream));
     // kernels: need the inputs, and the output staging buffer drained by the copy of two passes ago
     CK(cudaStreamWaitEvent(h->stream, h->ev_in[s2], 0));
@@ -1394,6 +1408,12 @@ int rvcdec_forward_host(rvcdec_handle* h, const float* x, const float* f0, const
   h->host_t[2] = std::chrono::duration<double>(t_end - t_enq).count();
   if (rc) return rc;  // (message of the first failure is kept)
   CK(e1); CK(e2); CK(e3);
+  return 0;
+}
+
+int rvcdec_set_initial_phases(rvcdec_handle* h, const float* phases) {
+  if (!h) return fail(RVCDEC_ERR_ARG, "null handle");
+  h->rand_ini = phases;
   return 0;
 }
 

@@ -261,7 +261,7 @@ class HiFiGANNSFGenerator(torch.nn.Module):
             else:
                 raise ValueError("noise must be a tensor, 'torch' or 'philox'")
         if noise is not None:
-            noise = noise.reshape(B, n).contiguous().float()
+            noise = noise.reshape(B, -1).contiguous().float()  # (B, n), or (B, n * harmonics) for the MRF sibling
         if g is not None:
             if self._gin == 0:
                 g = None
@@ -403,3 +403,143 @@ class HiFiGANGenerator(HiFiGANNSFGenerator):
                     out: Optional[torch.Tensor] = None, device: Optional[int] = None, max_device_bytes: int = 0) -> torch.Tensor:
         f0 = torch.zeros(x.shape[0], x.shape[2], dtype=torch.float32)
         return HiFiGANNSFGenerator.decode_host(self, x, f0, g, mode=mode, out=out, device=device, max_device_bytes=max_device_bytes)
+
+
+class _MRFLayer(torch.nn.Module):  # hifigan_mrf.py:13-57
+    def __init__(self, channels, kernel_size, dilation):
+        super().__init__()
+        self.conv1 = weight_norm(torch.nn.Conv1d(channels, channels, kernel_size, padding=(kernel_size * dilation - dilation) // 2,
+                                                 dilation=dilation))
+        self.conv2 = weight_norm(torch.nn.Conv1d(channels, channels, kernel_size, padding=kernel_size // 2, dilation=1))
+
+
+class _MRFBlock(torch.nn.Module):  # hifigan_mrf.py:60-85
+    def __init__(self, channels, kernel_size, dilations):
+        super().__init__()
+        self.layers = torch.nn.ModuleList([_MRFLayer(channels, kernel_size, d) for d in dilations])
+
+
+class _MRFSource(torch.nn.Module):  # hifigan_mrf.py:179-220 (l_sin_gen has no parameters)
+    def __init__(self, sampling_rate: int, harmonic_num: int = 0):
+        super().__init__()
+        self.sampling_rate, self.harmonic_num = sampling_rate, harmonic_num
+        self.l_linear = torch.nn.Linear(harmonic_num + 1, 1)
+        self.l_tanh = torch.nn.Tanh()
+
+
+class HiFiGANMRFGenerator(HiFiGANNSFGenerator):
+    """B200-native sibling decoder ``HiFiGANMRFGenerator`` (rvc/lib/algorithm/generators/hifigan_mrf.py:223-374, the
+    "MRF HiFi-GAN" vocoder selected at synthesizers.py:85-97) with the reference's keyword constructor, parameter names
+    (``upsamples``, ``mrfs.i.j.layers.m.conv1``, weight-normed ``conv_pre`` / ``conv_post`` with bias) and
+    ``forward(x, f0, g)``.  It is the NSF conv stack with a 9-sine harmonic source (overtones with random initial phases
+    merged by Linear(9, 1)), so it runs on the same kernels behind the same C ABI: ``rvcdec_config.harmonic_num`` selects
+    the source, the state dict is handed to the library under the NSF names.
+
+    The reference integrates the phase with a per-SAMPLE fp32 cumsum (hifigan_mrf.py:137-142); f0 is constant inside a
+    frame, so the source kernel keeps the closed form it already used - a frame-level fp64 prefix plus (j+1) f0/sr inside
+    the frame, times (k+1) per overtone - which equals the reference's sum in exact arithmetic.
+
+    Extra keyword-only arguments of ``forward``: ``noise`` (B, T*upp, H) standard-normal draws and ``rand_ini`` (B, H)
+    initial phases in [0, 1) (column 0 ignored: the fundamental starts at 0); default = drawn with the torch generator
+    of x's device in the reference's order (``rand(B, H)`` then ``randn(B, T*upp, H)``); "philox" = in-kernel draws."""
+
+    def __init__(self, in_channel: int, upsample_initial_channel: int, upsample_rates: list, upsample_kernel_sizes: list,
+                 resblock_kernel_sizes: list, resblock_dilations: list, gin_channels: int, sample_rate: int, harmonic_num: int,
+                 checkpointing: bool = False):
+        torch.nn.Module.__init__(self)
+        self.num_kernels = len(resblock_kernel_sizes)
+        self.num_upsamples = len(upsample_rates)
+        self.checkpointing = checkpointing
+        self.f0_upsample = torch.nn.Upsample(scale_factor=math.prod(upsample_rates))
+        self.m_source = _MRFSource(sample_rate, harmonic_num)
+        self.conv_pre = weight_norm(torch.nn.Conv1d(in_channel, upsample_initial_channel, kernel_size=7, stride=1, padding=3))
+        self.upsamples = torch.nn.ModuleList()
+        self.noise_convs = torch.nn.ModuleList()
+        stride_f0s = [math.prod(upsample_rates[i + 1:]) if i + 1 < len(upsample_rates) else 1 for i in range(len(upsample_rates))]
+        for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
+            if u % 2 != 0:
+                raise ValueError("odd upsample rates are not supported by the B200 decoder (32k/40k/48k are all even)")
+            self.upsamples.append(weight_norm(torch.nn.ConvTranspose1d(upsample_initial_channel // (2 ** i),
+                                                                       upsample_initial_channel // (2 ** (i + 1)), kernel_size=k,
+                                                                       stride=u, padding=(k - u) // 2, output_padding=0)))
+            stride = stride_f0s[i]
+            kernel = 1 if stride == 1 else stride * 2 - stride % 2
+            padding = 0 if stride == 1 else (kernel - stride) // 2
+            self.noise_convs.append(torch.nn.Conv1d(1, upsample_initial_channel // (2 ** (i + 1)), kernel_size=kernel, stride=stride,
+                                                    padding=padding))
+        self.mrfs = torch.nn.ModuleList()
+        channel = upsample_initial_channel
+        for i in range(len(self.upsamples)):
+            channel = upsample_initial_channel // (2 ** (i + 1))
+            self.mrfs.append(torch.nn.ModuleList([_MRFBlock(channel, kernel_size=k, dilations=d)
+                                                  for k, d in zip(resblock_kernel_sizes, resblock_dilations)]))
+        self.conv_post = weight_norm(torch.nn.Conv1d(channel, 1, kernel_size=7, stride=1, padding=3))
+        if gin_channels != 0:
+            self.cond = torch.nn.Conv1d(gin_channels, upsample_initial_channel, 1)
+        self.upp = math.prod(upsample_rates)
+        self.lrelu_slope = LRELU_SLOPE
+        self.harmonics = harmonic_num + 1
+        self.mode = os.environ.get("RVC_B200_MODE", "fast")
+        self.noise_source = os.environ.get("RVC_B200_NOISE", "torch")
+        self.max_workspace_bytes = int(os.environ.get("RVC_B200_MAX_WORKSPACE", "0"))
+        self._cfg_args = (in_channel, list(resblock_kernel_sizes), [list(d) for d in resblock_dilations], list(upsample_rates),
+                          upsample_initial_channel, list(upsample_kernel_sizes), gin_channels, sample_rate, harmonic_num)
+        self._gin = gin_channels
+        self._cin = in_channel
+        self.fused_mrf = int(os.environ["RVC_B200_FUSED_MRF"]) if "RVC_B200_FUSED_MRF" in os.environ else None
+        self._applied_fused = None
+        self._handle = None
+        self._packed_key = None
+        self._workspace = None
+        self._ws_event = None
+        self._ws_stream = None
+        self.last_launch_count = 0
+
+    def remove_weight_norm(self):
+        for l in [self.conv_pre, self.conv_post] + list(self.upsamples):
+            _strip(l)
+        for stage in self.mrfs:
+            for blk in stage:
+                for lay in blk.layers:
+                    _strip(lay.conv1)
+                    _strip(lay.conv2)
+
+    def _decoder_state(self):
+        """The library's (NSF) names: upsamples.i -> ups.i, mrfs.i.j.layers.m.conv1/2 -> resblocks.(i*nk+j).convs1/2.m."""
+        out = {}
+        nk = self.num_kernels
+        for k, v in self.state_dict().items():
+            if k.startswith("upsamples."):
+                k = "ups." + k[len("upsamples."):]
+            elif k.startswith("mrfs."):
+                p = k.split(".")
+                i, j, m, which = int(p[1]), int(p[2]), int(p[4]), p[5]
+                k = f"resblocks.{i * nk + j}.convs{1 if which == 'conv1' else 2}.{m}." + ".".join(p[6:])
+            out[k] = v
+        return out
+
+    def forward(self, x: torch.Tensor, f0: torch.Tensor, g: Optional[torch.Tensor] = None, *,
+                noise=None, rand_ini: Optional[torch.Tensor] = None, mode: Optional[str] = None):
+        if not x.is_cuda:
+            raise RuntimeError("rvc_b200.HiFiGANMRFGenerator runs only on a CUDA (sm_100a) device; there is no CPU fallback")
+        B, _, T = x.shape
+        n, H = T * self.upp, self.harmonics
+        if noise is None:
+            noise = self.noise_source
+        if isinstance(noise, str) and noise == "torch":
+            # reference draw order on this device's generator: hifigan_mrf.py:129 then :172
+            rand_ini = torch.rand(B, H, device=x.device)
+            noise = torch.randn(B, n, H, device=x.device, dtype=torch.float32)
+        h = self._ensure_handle(x.device)
+        keep = None
+        if isinstance(noise, torch.Tensor):
+            if rand_ini is None:
+                raise ValueError("injected noise needs rand_ini (B, harmonics) as well")
+            keep = rand_ini.reshape(B, H).contiguous().float().clone()
+            keep[:, 0] = 0
+            h.set_initial_phases(keep.data_ptr())
+            noise = noise.reshape(B, n * H)
+        try:
+            return HiFiGANNSFGenerator.forward(self, x, f0, g, noise=noise, mode=mode)
+        finally:
+            h.set_initial_phases(None)

@@ -27,7 +27,7 @@ from typing import Dict, Optional, Tuple
 import torch
 
 from . import _lib
-from .decoder import HiFiGANGenerator, HiFiGANNSFGenerator
+from .decoder import HiFiGANGenerator, HiFiGANMRFGenerator, HiFiGANNSFGenerator
 
 CONFIG_FIELDS = ("spec_channels", "segment_size", "inter_channels", "hidden_channels", "filter_channels", "n_heads",
                  "n_layers", "kernel_size", "p_dropout", "resblock", "resblock_kernel_sizes", "resblock_dilation_sizes",
@@ -113,16 +113,24 @@ PACKED = PackedCache()
 def load_checkpoint(cpt: dict, device: Optional[torch.device] = None, strict: bool = True):
     """Build the decoder of an extracted model and fill it from ``cpt["weight"]``.
 
-    Returns an ``HiFiGANNSFGenerator`` (f0 models, vocoder "HiFi-GAN") or ``HiFiGANGenerator`` (no-f0 models) in eval
+    Returns an ``HiFiGANNSFGenerator`` (f0 models, vocoder "HiFi-GAN"), ``HiFiGANMRFGenerator`` (f0 models, vocoder
+    "MRF HiFi-GAN") or ``HiFiGANGenerator`` (no-f0 models) in eval
     mode, moved to ``device`` when given.  ``module.content_key`` carries the packed-weight cache key; the first
     forward on a device looks the handle up in ``loader.PACKED`` before folding anything."""
     c = checkpoint_config(cpt)
     voc = c["vocoder"]
-    if voc != "HiFi-GAN":
-        raise NotImplementedError(f'vocoder "{voc}" (synthesizers.py:85-106) has no B200 decoder; "HiFi-GAN" with or without f0 is supported')
+    if voc not in ("HiFi-GAN", "MRF HiFi-GAN") or (voc == "MRF HiFi-GAN" and not c["use_f0"]):
+        raise NotImplementedError(f'vocoder "{voc}" (synthesizers.py:85-106) has no B200 decoder; "HiFi-GAN" (with or without f0) and '
+                                  '"MRF HiFi-GAN" (f0 models) are supported')
     args = (c["inter_channels"], list(c["resblock_kernel_sizes"]), [list(d) for d in c["resblock_dilation_sizes"]],
             list(c["upsample_rates"]), c["upsample_initial_channel"], list(c["upsample_kernel_sizes"]))
-    if c["use_f0"]:
+    if voc == "MRF HiFi-GAN":  # synthesizers.py:86-97
+        m = HiFiGANMRFGenerator(in_channel=c["inter_channels"], upsample_initial_channel=c["upsample_initial_channel"],
+                                upsample_rates=list(c["upsample_rates"]), upsample_kernel_sizes=list(c["upsample_kernel_sizes"]),
+                                resblock_kernel_sizes=list(c["resblock_kernel_sizes"]),
+                                resblock_dilations=[list(d) for d in c["resblock_dilation_sizes"]], gin_channels=c["gin_channels"],
+                                sample_rate=c["sr"], harmonic_num=8)
+    elif c["use_f0"]:
         m = HiFiGANNSFGenerator(*args, gin_channels=c["gin_channels"], sr=c["sr"])
     else:
         m = HiFiGANGenerator(*args, gin_channels=c["gin_channels"])

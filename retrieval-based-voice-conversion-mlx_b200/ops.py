@@ -22,8 +22,8 @@ def nsf_hifigan_decode(x: torch.Tensor, f0: torch.Tensor, g: Optional[torch.Tens
     B, _, T = x.shape
     L = _lib.lib()
     n = T * upp
-    if noise is not None and tuple(noise.shape) != (B, n):
-        raise RuntimeError(f"noise must be (B, T*upp) = ({B}, {n})")
+    if noise is not None and (noise.shape[0] != B or noise.numel() % (B * n) != 0):
+        raise RuntimeError(f"noise must be (B, T*upp[, harmonics]) with B = {B}, T*upp = {n}")
     out = torch.empty(B, n, dtype=torch.float32, device=x.device)
     stream = torch.cuda.current_stream(x.device).cuda_stream
     with torch.cuda.device(x.device):

@@ -15,7 +15,7 @@ import torch
 from torch.nn.utils.parametrizations import weight_norm
 
 from . import _lib
-from .decoder import HiFiGANGenerator, HiFiGANNSFGenerator
+from .decoder import HiFiGANGenerator, HiFiGANMRFGenerator, HiFiGANNSFGenerator
 
 
 class _LayerNorm(torch.nn.Module):  # normalization.py:4-26
@@ -147,12 +147,17 @@ class Synthesizer(torch.nn.Module):
                  spk_embed_dim: int, gin_channels: int, sr: int, use_f0: bool, text_enc_hidden_dim: int = 768,
                  vocoder: str = "HiFi-GAN", randomized: bool = True, checkpointing: bool = False, **kwargs):
         super().__init__()
-        if vocoder != "HiFi-GAN":
+        if vocoder not in ("HiFi-GAN", "MRF HiFi-GAN") or (vocoder == "MRF HiFi-GAN" and not use_f0):
             raise NotImplementedError(f'vocoder "{vocoder}" (synthesizers.py:85-106) has no B200 implementation')
         self.segment_size, self.use_f0, self.randomized = segment_size, use_f0, randomized
         self.enc_p = _TextEncoder(inter_channels, hidden_channels, filter_channels, n_heads, n_layers, kernel_size, p_dropout,
                                   text_enc_hidden_dim, f0=use_f0)
-        if use_f0:
+        if use_f0 and vocoder == "MRF HiFi-GAN":  # synthesizers.py:86-97
+            self.dec = HiFiGANMRFGenerator(in_channel=inter_channels, upsample_initial_channel=upsample_initial_channel,
+                                           upsample_rates=upsample_rates, upsample_kernel_sizes=upsample_kernel_sizes,
+                                           resblock_kernel_sizes=resblock_kernel_sizes, resblock_dilations=resblock_dilation_sizes,
+                                           gin_channels=gin_channels, sample_rate=sr, harmonic_num=8, checkpointing=checkpointing)
+        elif use_f0:
             self.dec = HiFiGANNSFGenerator(inter_channels, resblock_kernel_sizes, resblock_dilation_sizes, upsample_rates,
                                            upsample_initial_channel, upsample_kernel_sizes, gin_channels=gin_channels, sr=sr,
                                            checkpointing=checkpointing)
@@ -187,6 +192,10 @@ class Synthesizer(torch.nn.Module):
     # -- packed weights ----------------------------------------------------
     def _state_for_library(self):
         sd = {k: v for k, v in self.state_dict().items() if not k.startswith("enc_q.")}
+        if isinstance(self.dec, HiFiGANMRFGenerator):  # the library knows the decoder's layers under the NSF names
+            sd = {k: v for k, v in sd.items() if not k.startswith("dec.")}
+            for k, v in self.dec._decoder_state().items():
+                sd["dec." + k] = v
         if not self.use_f0:  # the library receives all-zero source / noise-conv layers for the no-f0 decoder (decoder.py)
             for k, v in self.dec._decoder_state().items():
                 sd["dec." + k] = v
@@ -219,7 +228,8 @@ class Synthesizer(torch.nn.Module):
     @torch.no_grad()
     def infer(self, phone: torch.Tensor, phone_lengths: torch.Tensor, pitch: Optional[torch.Tensor] = None,
               nsff0: Optional[torch.Tensor] = None, sid: torch.Tensor = None, rate: Optional[torch.Tensor] = None, *,
-              noise_zp: Optional[torch.Tensor] = None, noise_src: Optional[torch.Tensor] = None, mode: Optional[str] = None):
+              noise_zp: Optional[torch.Tensor] = None, noise_src: Optional[torch.Tensor] = None,
+              rand_ini: Optional[torch.Tensor] = None, mode: Optional[str] = None):
         if not phone.is_cuda:
             raise RuntimeError("rvc_b200.Synthesizer.infer runs only on a CUDA (sm_100a) device; there is no CPU fallback")
         if rate is not None:
@@ -232,16 +242,27 @@ class Synthesizer(torch.nn.Module):
         inter = self._syn_args["inter_channels"]
         if noise_zp is None:  # reference draw order on this device's generator: synthesizers.py:228, then hifigan.py:189,223
             noise_zp = torch.randn(B, inter, T, device=dev, dtype=torch.float32)
+        H = getattr(self.dec, "harmonics", 1)
         if noise_src is None and self.use_f0:
-            torch.rand(1, 1, 1, device=dev)
-            noise_src = torch.randn(B, T * upp, 1, device=dev, dtype=torch.float32)
+            if H > 1:  # hifigan_mrf.py:129,172
+                rand_ini = torch.rand(B, H, device=dev)
+                noise_src = torch.randn(B, T * upp, H, device=dev, dtype=torch.float32)
+            else:
+                torch.rand(1, 1, 1, device=dev)
+                noise_src = torch.randn(B, T * upp, 1, device=dev, dtype=torch.float32)
+        ini = None
+        if H > 1:
+            if rand_ini is None:
+                raise ValueError("injected source noise needs rand_ini (B, harmonics) for the MRF decoder")
+            ini = rand_ini.reshape(B, H).to(dev).contiguous().float().clone()
+            ini[:, 0] = 0
         lengths = phone_lengths.to(device=dev, dtype=torch.int32).contiguous()
         phone = phone.contiguous().float()
         pitch_p = pitch.to(device=dev, dtype=torch.int64).contiguous() if (self.use_f0 and pitch is not None) else None
         f0 = nsff0.contiguous().float() if (self.use_f0 and nsff0 is not None) else torch.zeros(B, T, device=dev)
         sid = sid.to(device=dev, dtype=torch.int64).contiguous()
         nz = noise_zp.reshape(B, inter, T).contiguous().float()
-        ns = noise_src.reshape(B, T * upp).contiguous().float() if noise_src is not None else None
+        ns = noise_src.reshape(B, T * upp * H).contiguous().float() if noise_src is not None else None
         need = h.workspace_bytes(B, T, m)
         if self._workspace is None or self._workspace.device != dev or self._workspace.numel() < need:
             self._workspace = None
@@ -249,6 +270,8 @@ class Synthesizer(torch.nn.Module):
         out = torch.empty(B, T * upp, dtype=torch.float32, device=dev)
         z = torch.empty(B, inter, T, dtype=torch.float32, device=dev)
         stream = torch.cuda.current_stream(dev).cuda_stream
+        dec_ptr = _lib.C.c_void_p(_lib.lib().rvcsyn_decoder(h._h))
+        _lib.check(_lib.lib().rvcdec_set_initial_phases(dec_ptr, ini.data_ptr() if ini is not None else None), "rvcdec_set_initial_phases")
         h.infer(phone.data_ptr(), lengths.data_ptr(), pitch_p.data_ptr() if pitch_p is not None else None, f0.data_ptr(),
                 sid.data_ptr(), nz.data_ptr(), ns.data_ptr() if ns is not None else None, 0, out.data_ptr(), z.data_ptr(),
                 self._workspace, B, T, m, stream)
