@@ -60,7 +60,7 @@ typedef struct {
   int32_t gin_channels;                    /* 256, 0 = no conditioning conv */
   int32_t sr;                              /* 48000 */
   int32_t num_upsamples;                   /* 4 */
-  int32_t upsample_rates[RVCDEC_MAX_UPS];          /* 12,10,2,2 (even rates only) */
+  int32_t upsample_rates[RVCDEC_MAX_UPS];          /* 12,10,2,2 (odd rates need kernel = 2 x rate) */
   int32_t upsample_kernel_sizes[RVCDEC_MAX_UPS];   /* 24,20,4,4 */
   int32_t num_kernels;                     /* 3 */
   int32_t resblock_kernel_sizes[RVCDEC_MAX_KERNELS];   /* 3,7,11 (odd) */

@@ -81,6 +81,11 @@ CONFIG_TINY = DecoderConfig(
 )
 
 
+# Odd upsample rates (hifigan_nsf.py:113-117 padding u//2 + 1 / output_padding 1, noise convs with odd strides :142-143).
+CONFIG_ODD = DecoderConfig(initial_channel=32, upsample_rates=(5, 3, 2, 2), upsample_initial_channel=128,
+                           upsample_kernel_sizes=(10, 6, 4, 4), gin_channels=16, sr=24000)
+
+
 def get_padding(kernel_size: int, dilation: int = 1) -> int:
     """commons.py:19-27."""
     return int((kernel_size * dilation - dilation) / 2)
@@ -390,7 +395,8 @@ def decoder_forward_mrf(w: Dict[str, torch.Tensor], cfg: DecoderConfig, x, f0, g
         x = x + F.conv1d(g.to(dtype), W["cond.weight"], W["cond.bias"])
     for i, (u, k) in enumerate(zip(cfg.upsample_rates, cfg.upsample_kernel_sizes)):
         x = F.leaky_relu(x, LRELU_SLOPE)
-        x = F.conv_transpose1d(x, W[f"ups.{i}.weight"], W[f"ups.{i}.bias"], stride=u, padding=(k - u) // 2)
+        pad, opad = ((k - u) // 2, 0) if u % 2 == 0 else (u // 2 + u % 2, u % 2)  # hifigan_mrf.py:279-296
+        x = F.conv_transpose1d(x, W[f"ups.{i}.weight"], W[f"ups.{i}.bias"], stride=u, padding=pad, output_padding=opad)
         stride = math.prod(cfg.upsample_rates[i + 1:]) if i + 1 < len(cfg.upsample_rates) else 1
         nkern = 1 if stride == 1 else stride * 2 - stride % 2
         npad = 0 if stride == 1 else (nkern - stride) // 2

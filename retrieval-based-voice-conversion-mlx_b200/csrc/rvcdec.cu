@@ -87,6 +87,7 @@ struct rvcdec_handle {
   int upp = 1;
   int nups = 0, nk = 0, nd = 0;
   std::vector<int> ch;  // channels after each upsample
+  std::vector<int> ups_pad;  // ConvTranspose1d padding of each upsample (hifigan_nsf.py:113-117)
   bool loaded = false;
   bool fast_ok = false;
   std::string fast_why;
@@ -1023,7 +1024,14 @@ int rvcdec_create(const rvcdec_config* cfg, int device, rvcdec_handle** out) {
   h->upp = 1;
   for (int i = 0; i < h->nups; ++i) {
     const int u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
-    if (u < 1 || u % 2 || k < u || (k - u) % 2) { delete h; return fail(RVCDEC_ERR_ARG, "upsample %d: rate %d / kernel %d unsupported (even rates with k-u even only)", i, u, k); }
+    // hifigan_nsf.py:113-127: even rates pad (k-u)/2, odd rates pad u/2 + 1 with output_padding 1; the output must be
+    // exactly u times the input (x + noise_convs[i](har), :199, needs equal lengths in the reference as well)
+    const int pad = (u % 2 == 0) ? (k - u) / 2 : u / 2 + 1, opad = u % 2;
+    if (u < 1 || k < u || k + opad - 2 * pad != u) {
+      delete h;
+      return fail(RVCDEC_ERR_ARG, "upsample %d: rate %d / kernel %d gives an output that is not %d x the input (even rates need k - u even, odd rates k = 2u)", i, u, k, u);
+    }
+    h->ups_pad.push_back(pad);
     const int C = c.upsample_initial_channel >> (i + 1);
     if (C < 8 || C % 8 || (C << (i + 1)) != c.upsample_initial_channel) { delete h; return fail(RVCDEC_ERR_ARG, "channel count %d at stage %d must be a multiple of 8", C, i); }
     h->ch.push_back(C);
@@ -1108,14 +1116,14 @@ static int pack_all(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n) {
     const std::string un = "ups." + std::to_string(i);
     if ((rc = get_weight(tm, un, Cin, (int64_t)C * k, W))) return rc;  // weight-norm dim 0 = C_in
     h->ups[i].name = un;
-    if ((rc = pack_ups(h->ups[i], W, Cin, C, k, u, (k - u) / 2))) return rc;
+    if ((rc = pack_ups(h->ups[i], W, Cin, C, k, u, h->ups_pad[i]))) return rc;
     if ((rc = get_vec(tm, un + ".bias", C, v))) return rc;
     h->ups_zs[i] = ConvLayer();
     if (u == 2 && k <= MAX_TAPS) {
       // ConvTranspose1d(k, stride u, padding p) == Conv1d over the zero-stuffed input z[i*u] = x[i] with the
       // flipped kernel: y[o] = b + sum_j z[o - (k-1-p) + j] * w[:, :, k-1-j]
       ConvLayer& Z = h->ups_zs[i];
-      const int p0 = (k - u) / 2;
+      const int p0 = h->ups_pad[i];
       Z.name = un + "(zero-stuffed)";
       Z.Cin = Cin; Z.N_total = C; Z.cout = C; Z.up = 1; Z.ntaps = k; Z.halo = 0;
       Z.macs_per_row = (double)Cin * C * k / u;  // algorithmic MACs per OUTPUT row

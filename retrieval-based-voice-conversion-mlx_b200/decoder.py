@@ -103,10 +103,9 @@ class HiFiGANNSFGenerator(torch.nn.Module):
         stride_f0s = [math.prod(upsample_rates[i + 1:]) if i + 1 < len(upsample_rates) else 1
                       for i in range(len(upsample_rates))]
         for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
-            if u % 2 != 0:
-                raise ValueError("odd upsample rates are not supported by the B200 decoder (32k/40k/48k are all even)")
+            padding = (k - u) // 2 if u % 2 == 0 else u // 2 + u % 2  # hifigan_nsf.py:113-117
             self.ups.append(weight_norm(torch.nn.ConvTranspose1d(upsample_initial_channel // (2 ** i), channels[i], k, u,
-                                                                 padding=(k - u) // 2, output_padding=0)))
+                                                                 padding=padding, output_padding=u % 2)))
             stride = stride_f0s[i]
             kernel = 1 if stride == 1 else stride * 2 - stride % 2
             padding = 0 if stride == 1 else (kernel - stride) // 2
@@ -342,7 +341,9 @@ class HiFiGANGenerator(HiFiGANNSFGenerator):
         ch = upsample_initial_channel
         for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
             if u % 2 != 0:
-                raise ValueError("odd upsample rates are not supported by the B200 decoder (32k/40k/48k are all even)")
+                # hifigan.py:56 pads (k-u)//2 whatever the rate: an odd rate makes every stage one sample longer than u x its
+                # input, which no released configuration uses
+                raise ValueError("odd upsample rates are not supported by the no-f0 decoder")
             ch = upsample_initial_channel // (2 ** (i + 1))
             self.ups.append(weight_norm(torch.nn.ConvTranspose1d(upsample_initial_channel // (2 ** i), ch, k, u, padding=(k - u) // 2)))
             for kk, d in zip(resblock_kernel_sizes, resblock_dilation_sizes):
@@ -457,11 +458,10 @@ class HiFiGANMRFGenerator(HiFiGANNSFGenerator):
         self.noise_convs = torch.nn.ModuleList()
         stride_f0s = [math.prod(upsample_rates[i + 1:]) if i + 1 < len(upsample_rates) else 1 for i in range(len(upsample_rates))]
         for i, (u, k) in enumerate(zip(upsample_rates, upsample_kernel_sizes)):
-            if u % 2 != 0:
-                raise ValueError("odd upsample rates are not supported by the B200 decoder (32k/40k/48k are all even)")
+            padding = (k - u) // 2 if u % 2 == 0 else u // 2 + u % 2  # hifigan_mrf.py:279-284
             self.upsamples.append(weight_norm(torch.nn.ConvTranspose1d(upsample_initial_channel // (2 ** i),
                                                                        upsample_initial_channel // (2 ** (i + 1)), kernel_size=k,
-                                                                       stride=u, padding=(k - u) // 2, output_padding=0)))
+                                                                       stride=u, padding=padding, output_padding=u % 2)))
             stride = stride_f0s[i]
             kernel = 1 if stride == 1 else stride * 2 - stride % 2
             padding = 0 if stride == 1 else (kernel - stride) // 2

@@ -106,7 +106,7 @@ def test_source_kernel_matches_oracle(dev):
     assert float((got - exp32).abs().max()) <= 1e-4
 
 
-@pytest.mark.parametrize("name", ["tiny_24k_B2_T40", "v2_48k_B2_T24", "v2_40k_B1_T32", "v2_32k_B1_T16"])
+@pytest.mark.parametrize("name", ["tiny_24k_B2_T40", "v2_48k_B2_T24", "v2_40k_B1_T32", "v2_32k_B1_T16", "odd_rates_24k_B2_T30"])
 def test_fp32_mode_matches_reference_golden(dev, name):
     d, cfg, m, w = _module_for(name, dev)
     x, f0, g, noise, y = tensors(d)

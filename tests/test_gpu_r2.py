@@ -391,3 +391,28 @@ def test_stride2_polyphase_upsample_matches_zero_stuffed_form(dev, cfg_name, B, 
     assert float((y1 - y0).abs().max()) <= 2e-3
     if T >= 50:
         assert O.multires_logmel_corr(y1, y_ref, cfg.sr)["min"] >= FAST_BAR
+
+
+def test_odd_upsample_rates_fast_mode(dev):
+    """Odd upsample rates (hifigan_nsf.py:113-117: padding u//2 + 1, output_padding 1; noise convs with odd strides and
+    kernels 2s - 1, :142-143): rates (5, 3, 2, 2) with kernels (10, 6, 4, 4).  fp32 mode is checked against the
+    reference-generated golden in test_gpu.py; here the fast mode against the oracle at a longer length."""
+    # (full-width channels: the narrow golden configuration has an 8-channel last stage, which has no tensor-core tiling
+    #  and is refused loudly in fast mode)
+    cfg = O.DecoderConfig(upsample_rates=(5, 3, 2, 2), upsample_kernel_sizes=(10, 6, 4, 4), sr=24000)
+    narrow = build_module(O.CONFIG_ODD, 99).to(dev)
+    xs, fs, gs, ns = O.synth_inputs(O.CONFIG_ODD, 1, 20, seed=1)
+    with pytest.raises(RuntimeError, match="fast mode unsupported"):
+        narrow(xs.to(dev), fs.to(dev), gs.to(dev), noise=ns.to(dev), mode="fast")
+    m = build_module(cfg, 99)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, 2, 400, seed=63)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    with torch.no_grad():
+        y32 = m(x.to(dev), f0.to(dev), g.to(dev), noise=noise.to(dev), mode="fp32").cpu()
+        yf = m(x.to(dev), f0.to(dev), g.to(dev), noise=noise.to(dev), mode="fast").cpu()
+    e32, ef, corr = _margins("odd_rates_5_3_2_2_B2_T400", y32, yf, y_ref, cfg.sr)
+    assert y32.shape == (2, 1, 400 * 60)
+    assert e32 <= FP32_BAR, e32
+    assert corr["min"] >= FAST_BAR, corr

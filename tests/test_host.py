@@ -19,10 +19,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def test_abi_exports_every_declared_symbol(built_lib):
     from rvc_b200 import _lib
 
-    hdr = open(os.path.join(ROOT, "include", "rvcdec.h")).read()
-    declared = set(re.findall(r"\b(rvcdec_[a-z_0-9]+)\s*\(", hdr))
-    assert declared, "no declarations parsed"
-    assert declared == set(_lib.EXPORTS)
+    declared = set()
+    for header, prefix in (("rvcdec.h", "rvcdec"), ("rvcsyn.h", "rvcsyn")):
+        hdr = open(os.path.join(ROOT, "include", header)).read()
+        found = set(re.findall(r"\b(%s_[a-z_0-9]+)\s*\(" % prefix, hdr))
+        assert found, f"no declarations parsed in {header}"
+        declared |= found
+    assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
     for sym in declared:
         assert getattr(built_lib, sym) is not None
     assert b"sm_100a" in built_lib.rvcdec_version()

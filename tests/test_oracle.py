@@ -10,7 +10,7 @@ import torch
 from oracle import nsf_hifigan_oracle as O
 from helpers import golden_state, load_golden, tensors
 
-CASES = ["tiny_24k_B2_T40", "v2_48k_B2_T24", "v2_40k_B1_T32", "v2_32k_B1_T16"]
+CASES = ["tiny_24k_B2_T40", "v2_48k_B2_T24", "v2_40k_B1_T32", "v2_32k_B1_T16", "odd_rates_24k_B2_T30"]
 
 
 @pytest.mark.parametrize("name", CASES)
