@@ -11,8 +11,9 @@ from . import configs  # noqa: F401
 from . import loader  # noqa: F401
 from .loader import load_checkpoint  # noqa: F401
 from .synthesizer import Synthesizer  # noqa: F401
+from .refinegan import RefineGANGenerator  # noqa: F401
 from . import runner  # noqa: F401
 from .runner import MultiGpuDecoder  # noqa: F401
 
 __all__ = ["HiFiGANGenerator", "HiFiGANMRFGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking", "configs", "loader",
-           "load_checkpoint", "runner", "MultiGpuDecoder", "Synthesizer"]
+           "load_checkpoint", "runner", "MultiGpuDecoder", "Synthesizer", "RefineGANGenerator"]

@@ -48,6 +48,12 @@ class SynConfig(C.Structure):
                                          "flow_layers", "n_flows")] + [("dec", Config)]
 
 
+class RefineConfig(C.Structure):
+    """rvcrefine_config (include/rvcrefine.h)."""
+    _fields_ = [("sample_rate", C.c_int32), ("num_upsamples", C.c_int32), ("upsample_rates", C.c_int32 * MAX_UPS), ("num_mels", C.c_int32),
+                ("start_channels", C.c_int32), ("upsample_initial_channel", C.c_int32), ("gin_channels", C.c_int32)]
+
+
 class Tensor(C.Structure):
     _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64)]
 
@@ -63,6 +69,9 @@ EXPORTS = [
     # include/rvcsyn.h
     "rvcsyn_create", "rvcsyn_load_weights", "rvcsyn_workspace_bytes", "rvcsyn_infer", "rvcsyn_decoder", "rvcsyn_last_launch_count",
     "rvcsyn_destroy", "rvcsyn_last_error", "rvcsyn_debug_set_stop", "rvcsyn_debug_read",
+    # include/rvcrefine.h
+    "rvcrefine_create", "rvcrefine_load_weights", "rvcrefine_workspace_bytes", "rvcrefine_forward", "rvcrefine_noise_floats",
+    "rvcrefine_last_launch_count", "rvcrefine_destroy", "rvcrefine_last_error",
 ]
 
 _lib = None
@@ -116,6 +125,22 @@ def lib() -> C.CDLL:
     L.rvcdec_last_error.restype = C.c_char_p
     L.rvcdec_version.argtypes = []
     L.rvcdec_version.restype = C.c_char_p
+    L.rvcrefine_create.argtypes = [C.POINTER(RefineConfig), C.c_int, C.POINTER(vp)]
+    L.rvcrefine_create.restype = C.c_int
+    L.rvcrefine_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]
+    L.rvcrefine_load_weights.restype = C.c_int
+    L.rvcrefine_workspace_bytes.argtypes = [vp, i32, i32]
+    L.rvcrefine_workspace_bytes.restype = sz
+    L.rvcrefine_forward.argtypes = [vp, vp, vp, vp, vp, u64, vp, vp, sz, i32, i32, vp]
+    L.rvcrefine_forward.restype = C.c_int
+    L.rvcrefine_noise_floats.argtypes = [vp, i32, i32]
+    L.rvcrefine_noise_floats.restype = i64
+    L.rvcrefine_last_launch_count.argtypes = [vp]
+    L.rvcrefine_last_launch_count.restype = i64
+    L.rvcrefine_destroy.argtypes = [vp]
+    L.rvcrefine_destroy.restype = None
+    L.rvcrefine_last_error.argtypes = []
+    L.rvcrefine_last_error.restype = C.c_char_p
     L.rvcsyn_create.argtypes = [C.POINTER(SynConfig), C.c_int, C.POINTER(vp)]
     L.rvcsyn_create.restype = C.c_int
     L.rvcsyn_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]
@@ -174,6 +199,48 @@ def make_config(initial_channel: int, resblock_kernel_sizes: Sequence[int], resb
         for m, d in enumerate(resblock_dilation_sizes[j]):
             c.resblock_dilation_sizes[j][m] = d
     return c
+
+
+class RefineHandle:
+    """Owns one rvcrefine_handle (the RefineGAN sibling decoder; include/rvcrefine.h)."""
+
+    def __init__(self, cfg: RefineConfig, device: int):
+        self._h = C.c_void_p()
+        self._check(lib().rvcrefine_create(C.byref(cfg), int(device), C.byref(self._h)), "rvcrefine_create")
+        self.device = int(device)
+
+    @staticmethod
+    def _check(rc: int, what: str) -> None:
+        if rc < 0:
+            raise RuntimeError(f"{what} failed ({rc}): {(lib().rvcrefine_last_error() or b'').decode()}")
+
+    def load_weights(self, state: Dict[str, "object"]) -> None:
+        arr, keep = Handle._tensor_array(None, state)
+        self._check(lib().rvcrefine_load_weights(self._h, arr, len(state)), "rvcrefine_load_weights")
+
+    def workspace_bytes(self, B: int, T: int) -> int:
+        return int(lib().rvcrefine_workspace_bytes(self._h, B, T))
+
+    def noise_floats(self, B: int, T: int) -> int:
+        return int(lib().rvcrefine_noise_floats(self._h, B, T))
+
+    def forward(self, mel, f0, g, noise, seed, out, workspace, B, T, stream) -> None:
+        self._check(lib().rvcrefine_forward(self._h, mel, f0, g, noise, C.c_uint64(seed & (2**64 - 1)), out, workspace.data_ptr(),
+                                            workspace.numel(), B, T, stream), "rvcrefine_forward")
+
+    def launch_count(self) -> int:
+        return int(lib().rvcrefine_last_launch_count(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            lib().rvcrefine_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class SynHandle:

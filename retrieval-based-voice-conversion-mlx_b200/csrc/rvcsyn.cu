@@ -254,11 +254,14 @@ int rvcsyn_create(const rvcsyn_config* cfg, int device, rvcsyn_handle** out) {
   if (c.kernel_size < 1 || c.kernel_size % 2 == 0 || c.kernel_size > MAX_TAPS || c.flow_kernel % 2 == 0 || c.flow_kernel > MAX_TAPS ||
       c.n_layers < 1 || c.flow_layers < 1 || c.n_flows < 1 || c.n_flows % 2)
     return sfail(RVCDEC_ERR_ARG, "unsupported kernel sizes / layer counts (odd kernels <= %d, an even number of flows)", MAX_TAPS);
-  if (c.dec.initial_channel != c.inter_channels || c.dec.gin_channels != c.gin_channels)
-    return sfail(RVCDEC_ERR_ARG, "decoder configuration does not match inter_channels / gin_channels");
+  // dec.num_upsamples == 0: front end only (the caller runs another decoder on z * x_mask, e.g. the RefineGAN sibling)
   rvcdec_handle* dec = nullptr;
-  int rc = rvcdec_create(&c.dec, device, &dec);
-  if (rc) return sfail(rc, "decoder: %s", rvcdec_last_error());
+  if (c.dec.num_upsamples != 0) {
+    if (c.dec.initial_channel != c.inter_channels || c.dec.gin_channels != c.gin_channels)
+      return sfail(RVCDEC_ERR_ARG, "decoder configuration does not match inter_channels / gin_channels");
+    int rc = rvcdec_create(&c.dec, device, &dec);
+    if (rc) return sfail(rc, "decoder: %s", rvcdec_last_error());
+  }
   auto h = new rvcsyn_handle();
   h->cfg = c; h->device = device; h->dec = dec;
   *out = h;
@@ -272,7 +275,7 @@ void rvcsyn_destroy(rvcsyn_handle* h) {
     DevGuard dg(h->device);
     for (void* p : h->allocs) cudaFree(p);
   }
-  rvcdec_destroy(h->dec);
+  if (h->dec) rvcdec_destroy(h->dec);
   delete h;
 }
 
@@ -359,8 +362,10 @@ int rvcsyn_load_weights(rvcsyn_handle* h, const rvcdec_tensor* tensors, int32_t 
     }
   }
   // decoder
-  rc = rvcdec_load_weights(h->dec, dec_t.data(), (int32_t)dec_t.size());
-  if (rc) return sfail(rc, "decoder: %s", rvcdec_last_error());
+  if (h->dec) {
+    rc = rvcdec_load_weights(h->dec, dec_t.data(), (int32_t)dec_t.size());
+    if (rc) return sfail(rc, "decoder: %s", rvcdec_last_error());
+  }
   DevGuard dg(h->device);
   SCK(dg.err);
   for (void* p : h->allocs) cudaFree(p);
@@ -388,7 +393,7 @@ int rvcsyn_load_weights(rvcsyn_handle* h, const rvcdec_tensor* tensors, int32_t 
 
 size_t rvcsyn_workspace_bytes(const rvcsyn_handle* h, int32_t B, int32_t T, int32_t mode) {
   if (!h || B < 1 || T < 1) return 0;
-  return align_up(carve_syn(h, nullptr, B, T).bytes, 256) + rvcdec_workspace_bytes(h->dec, B, T, mode);
+  return align_up(carve_syn(h, nullptr, B, T).bytes, 256) + (h->dec ? rvcdec_workspace_bytes(h->dec, B, T, mode) : 0);
 }
 
 int rvcsyn_debug_set_stop(rvcsyn_handle* h, int32_t stop) {
@@ -422,16 +427,17 @@ int64_t rvcsyn_debug_read(rvcsyn_handle* h, const char* name, float* dst, int64_
   return n;
 }
 
-int64_t rvcsyn_last_launch_count(const rvcsyn_handle* h) { return h ? h->launches + rvcdec_last_launch_count(h->dec) : 0; }
+int64_t rvcsyn_last_launch_count(const rvcsyn_handle* h) { return h ? h->launches + (h->dec ? rvcdec_last_launch_count(h->dec) : 0) : 0; }
 
 int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, const int64_t* pitch, const float* nsff0,
                  const int64_t* sid, const float* noise_zp, const float* noise_src, uint64_t seed, float* out, float* z_out,
                  void* workspace, size_t workspace_bytes, int32_t B, int32_t T, int32_t mode, void* stream) {
-  if (!h || !phone || !lengths || !sid || !out || !workspace) return sfail(RVCDEC_ERR_ARG, "null argument");
+  if (!h || !phone || !lengths || !sid || !workspace) return sfail(RVCDEC_ERR_ARG, "null argument");
+  if (h->dec ? !out : !z_out) return sfail(RVCDEC_ERR_ARG, h->dec ? "null output" : "a front-end-only handle needs z_out");
   if (!h->loaded) return sfail(RVCDEC_ERR_STATE, "rvcsyn_load_weights has not succeeded on this handle");
   if (B < 1 || T < 1) return sfail(RVCDEC_ERR_ARG, "B and T must be >= 1");
   const rvcsyn_config& c = h->cfg;
-  if (c.use_f0 && (!pitch || !nsff0)) return sfail(RVCDEC_ERR_ARG, "an f0 model needs pitch and nsff0");
+  if (c.use_f0 && (!pitch || (h->dec && !nsff0))) return sfail(RVCDEC_ERR_ARG, "an f0 model needs pitch and nsff0");
   const size_t need = rvcsyn_workspace_bytes(h, B, T, mode);
   if (workspace_bytes < need) return sfail(RVCDEC_ERR_WORKSPACE, "workspace of %zu bytes is smaller than the %zu needed for B=%d, T=%d", workspace_bytes, need, B, T);
   DevGuard dg(h->device);
@@ -541,6 +547,7 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
   // z * mask -> (B, inter, T) fp32 for the decoder (and the caller, if asked for)
   SCK(launch_unpack(w.xf, ACT_F32, w.z_nct, B, I, T, Lp, s)); ++h->launches;
   if (z_out) SCK(cudaMemcpyAsync(z_out, w.z_nct, (size_t)B * I * T * 4, cudaMemcpyDeviceToDevice, s));
+  if (!h->dec) return 0;
   rc = rvcdec_forward(h->dec, w.z_nct, nsff0, c.gin_channels ? w.g : nullptr, noise_src, seed, out, dec_ws,
                       workspace_bytes - align_up(w.bytes, 256), B, T, mode, stream);
   if (rc) return sfail(rc, "decoder: %s", rvcdec_last_error());

@@ -28,6 +28,7 @@ import torch
 
 from . import _lib
 from .decoder import HiFiGANGenerator, HiFiGANMRFGenerator, HiFiGANNSFGenerator
+from .refinegan import RefineGANGenerator
 
 CONFIG_FIELDS = ("spec_channels", "segment_size", "inter_channels", "hidden_channels", "filter_channels", "n_heads",
                  "n_layers", "kernel_size", "p_dropout", "resblock", "resblock_kernel_sizes", "resblock_dilation_sizes",
@@ -119,9 +120,17 @@ def load_checkpoint(cpt: dict, device: Optional[torch.device] = None, strict: bo
     forward on a device looks the handle up in ``loader.PACKED`` before folding anything."""
     c = checkpoint_config(cpt)
     voc = c["vocoder"]
-    if voc not in ("HiFi-GAN", "MRF HiFi-GAN") or (voc == "MRF HiFi-GAN" and not c["use_f0"]):
-        raise NotImplementedError(f'vocoder "{voc}" (synthesizers.py:85-106) has no B200 decoder; "HiFi-GAN" (with or without f0) and '
-                                  '"MRF HiFi-GAN" (f0 models) are supported')
+    if voc not in ("HiFi-GAN", "MRF HiFi-GAN", "RefineGAN") or (voc != "HiFi-GAN" and not c["use_f0"]):
+        raise NotImplementedError(f'vocoder "{voc}" with f0={c["use_f0"]} has no decoder (synthesizers.py:85-135): "HiFi-GAN" (with or '
+                                  'without f0), "MRF HiFi-GAN" and "RefineGAN" (f0 models) are supported')
+    if voc == "RefineGAN":  # synthesizers.py:98-106
+        m = RefineGANGenerator(sample_rate=c["sr"], downsample_rates=list(c["upsample_rates"])[::-1], upsample_rates=list(c["upsample_rates"]),
+                               start_channels=16, num_mels=c["inter_channels"])
+        missing, unexpected = m.load_state_dict(decoder_state(cpt["weight"]), strict=False)
+        if strict and (missing or unexpected):
+            raise KeyError(f"decoder state mismatch: missing {list(missing)[:4]}..., unexpected {list(unexpected)[:4]}...")
+        m.eval()
+        return m.to(device) if device is not None else m
     args = (c["inter_channels"], list(c["resblock_kernel_sizes"]), [list(d) for d in c["resblock_dilation_sizes"]],
             list(c["upsample_rates"]), c["upsample_initial_channel"], list(c["upsample_kernel_sizes"]))
     if voc == "MRF HiFi-GAN":  # synthesizers.py:86-97

@@ -16,6 +16,7 @@ from torch.nn.utils.parametrizations import weight_norm
 
 from . import _lib
 from .decoder import HiFiGANGenerator, HiFiGANMRFGenerator, HiFiGANNSFGenerator
+from .refinegan import RefineGANGenerator
 
 
 class _LayerNorm(torch.nn.Module):  # normalization.py:4-26
@@ -147,8 +148,9 @@ class Synthesizer(torch.nn.Module):
                  spk_embed_dim: int, gin_channels: int, sr: int, use_f0: bool, text_enc_hidden_dim: int = 768,
                  vocoder: str = "HiFi-GAN", randomized: bool = True, checkpointing: bool = False, **kwargs):
         super().__init__()
-        if vocoder not in ("HiFi-GAN", "MRF HiFi-GAN") or (vocoder == "MRF HiFi-GAN" and not use_f0):
-            raise NotImplementedError(f'vocoder "{vocoder}" (synthesizers.py:85-106) has no B200 implementation')
+        if vocoder not in ("HiFi-GAN", "MRF HiFi-GAN", "RefineGAN") or (vocoder != "HiFi-GAN" and not use_f0):
+            raise NotImplementedError(f'vocoder "{vocoder}" without pitch guidance has no decoder in the reference either (synthesizers.py:120-126)'
+                                      if vocoder in ("MRF HiFi-GAN", "RefineGAN") else f'unknown vocoder "{vocoder}"')
         self.segment_size, self.use_f0, self.randomized = segment_size, use_f0, randomized
         self.enc_p = _TextEncoder(inter_channels, hidden_channels, filter_channels, n_heads, n_layers, kernel_size, p_dropout,
                                   text_enc_hidden_dim, f0=use_f0)
@@ -157,6 +159,9 @@ class Synthesizer(torch.nn.Module):
                                            upsample_rates=upsample_rates, upsample_kernel_sizes=upsample_kernel_sizes,
                                            resblock_kernel_sizes=resblock_kernel_sizes, resblock_dilations=resblock_dilation_sizes,
                                            gin_channels=gin_channels, sample_rate=sr, harmonic_num=8, checkpointing=checkpointing)
+        elif use_f0 and vocoder == "RefineGAN":  # synthesizers.py:98-106
+            self.dec = RefineGANGenerator(sample_rate=sr, downsample_rates=upsample_rates[::-1], upsample_rates=upsample_rates,
+                                          start_channels=16, num_mels=inter_channels, checkpointing=checkpointing)
         elif use_f0:
             self.dec = HiFiGANNSFGenerator(inter_channels, resblock_kernel_sizes, resblock_dilation_sizes, upsample_rates,
                                            upsample_initial_channel, upsample_kernel_sizes, gin_channels=gin_channels, sr=sr,
@@ -171,7 +176,7 @@ class Synthesizer(torch.nn.Module):
                               n_heads=n_heads, n_layers=n_layers, kernel_size=kernel_size, text_dim=text_enc_hidden_dim,
                               spk_embed_dim=spk_embed_dim, gin_channels=gin_channels, use_f0=1 if use_f0 else 0, window_size=10,
                               flow_kernel=5, flow_layers=3, n_flows=4)
-        self.mode = self.dec.mode
+        self.mode = getattr(self.dec, "mode", "fp32")
         self._handle: Optional[_lib.SynHandle] = None
         self._packed_key = None
         self._workspace: Optional[torch.Tensor] = None
@@ -192,6 +197,8 @@ class Synthesizer(torch.nn.Module):
     # -- packed weights ----------------------------------------------------
     def _state_for_library(self):
         sd = {k: v for k, v in self.state_dict().items() if not k.startswith("enc_q.")}
+        if isinstance(self.dec, RefineGANGenerator):  # front end only: the decoder has its own handle (include/rvcrefine.h)
+            return {k: v for k, v in sd.items() if not k.startswith("dec.")}
         if isinstance(self.dec, HiFiGANMRFGenerator):  # the library knows the decoder's layers under the NSF names
             sd = {k: v for k, v in sd.items() if not k.startswith("dec.")}
             for k, v in self.dec._decoder_state().items():
@@ -212,7 +219,8 @@ class Synthesizer(torch.nn.Module):
             c = _lib.SynConfig()
             for k, v in self._syn_args.items():
                 setattr(c, k, int(v))
-            c.dec = _lib.make_config(*self.dec._cfg_args)
+            if not isinstance(self.dec, RefineGANGenerator):
+                c.dec = _lib.make_config(*self.dec._cfg_args)  # (left zeroed = front end only for the RefineGAN decoder)
             self._handle = _lib.SynHandle(c, idx)
             self._packed_key = None
             if not self.use_f0:  # the handle's own decoder skips the source kernel and the noise adds (decoder.py)
@@ -236,6 +244,8 @@ class Synthesizer(torch.nn.Module):
             raise NotImplementedError("rate (head trimming, synthesizers.py:230-234) is not supported: trim the inputs instead")
         dev = phone.device
         B, T, D = phone.shape
+        if isinstance(self.dec, RefineGANGenerator):
+            return self._infer_refinegan(phone, phone_lengths, pitch, nsff0, sid, noise_zp, noise_src)
         m = _lib.MODES[mode or self.mode]
         h = self._ensure_handle(dev)
         upp = self.dec.upp
@@ -278,3 +288,31 @@ class Synthesizer(torch.nn.Module):
         self.last_launch_count = h.launch_count()
         x_mask = (torch.arange(T, device=dev)[None, :] < phone_lengths.to(dev)[:, None]).unsqueeze(1).to(phone.dtype)
         return out.unsqueeze(1), x_mask, (z, None, None, None)
+
+    def _infer_refinegan(self, phone, phone_lengths, pitch, nsff0, sid, noise_zp, noise_dec):
+        """vocoder "RefineGAN": the library's front end (rvcsyn_infer on a front-end-only handle) hands z * x_mask to the
+        RefineGAN decoder's own call (rvcrefine_forward).  ``noise_src`` of ``infer`` carries the decoder's flat draw
+        buffer here (``dec.noise_numel``)."""
+        dev = phone.device
+        B, T, _ = phone.shape
+        h = self._ensure_handle(dev)
+        inter = self._syn_args["inter_channels"]
+        if noise_zp is None:
+            noise_zp = torch.randn(B, inter, T, device=dev, dtype=torch.float32)
+        lengths = phone_lengths.to(device=dev, dtype=torch.int32).contiguous()
+        phone = phone.contiguous().float()
+        pitch_p = pitch.to(device=dev, dtype=torch.int64).contiguous()
+        sid = sid.to(device=dev, dtype=torch.int64).contiguous()
+        nz = noise_zp.reshape(B, inter, T).contiguous().float()
+        need = h.workspace_bytes(B, T, 0)
+        if self._workspace is None or self._workspace.device != dev or self._workspace.numel() < need:
+            self._workspace = None
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+        z = torch.empty(B, inter, T, dtype=torch.float32, device=dev)
+        h.infer(phone.data_ptr(), lengths.data_ptr(), pitch_p.data_ptr(), None, sid.data_ptr(), nz.data_ptr(), None, 0, None, z.data_ptr(),
+                self._workspace, B, T, 0, torch.cuda.current_stream(dev).cuda_stream)
+        g = self.emb_g.weight.detach()[sid].unsqueeze(-1)  # row gather of the speaker table (synthesizers.py:226)
+        o = self.dec(z, nsff0.to(dev).float(), g, noise=noise_dec)
+        self.last_launch_count = h.launch_count() + self.dec.last_launch_count
+        x_mask = (torch.arange(T, device=dev)[None, :] < phone_lengths.to(dev)[:, None]).unsqueeze(1).to(phone.dtype)
+        return o, x_mask, (z, None, None, None)

@@ -110,7 +110,9 @@ def test_checkpoint_loader_builds_the_same_decoder_and_caches_by_content(checkpo
     nf = dict(cpt, f0=0, weight={k: v for k, v in cpt["weight"].items() if "m_source" not in k and "noise_convs" not in k})
     assert isinstance(rvc_b200.load_checkpoint(nf), rvc_b200.HiFiGANGenerator)
     with pytest.raises(NotImplementedError):
-        rvc_b200.load_checkpoint(dict(cpt, vocoder="RefineGAN"))
+        rvc_b200.load_checkpoint(dict(cpt, vocoder="RefineGAN", f0=0))  # no decoder in the reference either (synthesizers.py:123-126)
+    with pytest.raises((KeyError, RuntimeError)):
+        rvc_b200.load_checkpoint(dict(cpt, vocoder="RefineGAN"))         # NSF weights do not fit the RefineGAN decoder
     with pytest.raises(KeyError):
         rvc_b200.load_checkpoint(dict(cpt, weight={k: v for k, v in cpt["weight"].items() if k != "dec.conv_pre.bias"}))
 
