@@ -331,6 +331,43 @@ def longform_leg(model, cfg, n_dev, reps=3):
             "n_devices": n_dev, "chunks": 8, "units_per_device": [s["units"] // (2 * (reps + 1)) for s in st], "best_of": reps, **out}
 
 
+def synthesizer_leg(dev, B=16, T=3000, reps=3):
+    """the whole net_g.infer (speaker embedding, TextEncoder, z_p sampling, reverse flow, decoder) through
+    rvc_b200.Synthesizer -> rvcsyn_infer, device-resident inputs, CUDA events; the front end runs in fp32 (parity first)."""
+    import rvc_b200
+
+    SYN_48K = [1025, 32, 192, 192, 768, 2, 6, 3, 0, "1", [3, 7, 11], [[1, 3, 5]] * 3, [12, 10, 2, 2], 512, [24, 20, 4, 4], 109, 256, 48000]
+    torch.manual_seed(1234)
+    m = rvc_b200.Synthesizer(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").eval().to(dev)
+    gen = torch.Generator().manual_seed(1)
+    phone = torch.randn(B, T, 768, generator=gen).to(dev)
+    pitch = torch.randint(1, 256, (B, T), generator=gen).to(dev)
+    f0 = (100 + 100 * torch.rand(B, T, generator=gen)).to(dev)
+    sid = torch.zeros(B, dtype=torch.long, device=dev)
+    lens = torch.full((B,), T, dtype=torch.long, device=dev)
+    nzp = torch.randn(B, 192, T, device=dev)
+    nsrc = torch.randn(B, T * 480, device=dev)
+
+    def timed(stop):
+        m._handle.set_stop(stop)
+        m.infer(phone, lens, pitch, f0, sid, noise_zp=nzp, noise_src=nsrc, mode="fast")
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            m.infer(phone, lens, pitch, f0, sid, noise_zp=nzp, noise_src=nsrc, mode="fast")
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    m.infer(phone, lens, pitch, f0, sid, noise_zp=nzp, noise_src=nsrc, mode="fast")
+    ms_all, ms_front = timed(0), timed(9)
+    m._handle.set_stop(0)
+    return {"workload": f"net_g.infer, {B} x {T / 100:.0f} s, fast decoder + fp32 front end, injected noise, device-resident inputs",
+            "infer_ms": ms_all, "front_end_ms": ms_front, "front_end_share": ms_front / ms_all,
+            "audio_s_per_s": B * T / 100.0 / ms_all * 1e3, "launches": m.last_launch_count}
+
+
 def parity_check(model, cfg, dev):
     """One untimed 30 s chunk (the bench's chunk shape) with injected noise against the oracle: the numbers the
     north_star bars are stated on, measured in the same process as the throughput."""
@@ -460,11 +497,17 @@ def run_ours(args):
         roof["traffic_source"] = "scaled from the committed ncu --set full capture (not measured in this run)"
         roof["algorithmic_bytes_per_launch"] = dom["bytes"] / spans
     total_tflops = 2 * MMAC_PER_FRAME * T * B * args.steps / (ms * 1e-3) / 1e12
-    cpu = parity = None
+    cpu = parity = synth = None
     if world == 1 and not args.no_cpu:
         r = cpu_reference_runs(1, 1, full=False)
         cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         parity = parity_check(model, cfg, dev)
+        try:
+            model._workspace = None
+            torch.cuda.empty_cache()
+            synth = synthesizer_leg(dev)
+        except Exception as e:  # noqa: BLE001
+            synth = {"error": str(e)}
     line = {
         "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -484,6 +527,8 @@ def run_ours(args):
         line["parity"] = parity
     if longform:
         line["longform"] = longform
+    if synth:
+        line["synthesizer"] = synth
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

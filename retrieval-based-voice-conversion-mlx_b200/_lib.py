@@ -11,7 +11,8 @@ import os
 from typing import Dict, Sequence
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librvcdec.so")
+# (RVC_B200_LIB: A/B runs against another build of the library, e.g. an older one that lacks the newer entry points)
+LIB_PATH = os.environ.get("RVC_B200_LIB") or os.path.join(HERE, "librvcdec.so")
 
 MAX_UPS = 8
 MAX_KERNELS = 8
@@ -86,6 +87,23 @@ def lib() -> C.CDLL:
             f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(there is no CPU or PyTorch fallback for the decoder)")
     L = C.CDLL(LIB_PATH)
+    if os.environ.get("RVC_B200_LIB"):
+        have = L
+
+        class _Tolerant:  # an older build: entry points it lacks get a stub that raises when called
+            def __getattr__(self, name):
+                try:
+                    return getattr(have, name)
+                except AttributeError:
+                    class _Missing:
+                        argtypes = restype = None
+
+                        def __call__(self, *a, **k):
+                            raise RuntimeError(f"{name} is not exported by {LIB_PATH}")
+                    m = _Missing()
+                    setattr(self, name, m)
+                    return m
+        L = _Tolerant()
     vp, i32, i64, u64, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_size_t
     L.rvcdec_create.argtypes = [C.POINTER(Config), C.c_int, C.POINTER(vp)]
     L.rvcdec_create.restype = C.c_int

@@ -75,7 +75,7 @@ struct Epilogue {
   // stride 4, 8 taps, padding 2.
   int pm;
   // optional per-item valid length (rows >= lengths[b] are written as zeros: the x * x_mask of the reference's masked
-  // sequence models, encoders.py:139; honoured by the fp32 back-end and the generic tensor-core epilogue)
+  // sequence models, encoders.py:139; honoured by the fp32 back-end only)
   const int* lengths;
 };
 
@@ -102,7 +102,9 @@ struct ConvParams {
 __device__ __forceinline__ float lrelu(float v, float slope) { return v > 0.f ? v : v * slope; }
 
 // Apply the epilogue to NV (4 or 8) consecutive GEMM columns n0.. of input row t_in of item b.
-template <int NV>
+// MASK = true also honours Epilogue::lengths (fp32 back-end only: the tensor-core kernels are compiled without it, the
+// extra live pointer cost the 128-wide tiling 16 B of spills and 2 % of its time, A/B profiles/r2n_*)
+template <int NV, bool MASK = false>
 __device__ __forceinline__ void epilogue_store(const Epilogue& e, int b, int t_in, int n0, float (&v)[NV]) {
   const int r = n0 / e.cout;
   const int co = n0 - r * e.cout;
@@ -150,9 +152,11 @@ __device__ __forceinline__ void epilogue_store(const Epilogue& e, int b, int t_i
       v[i] += q.x; v[i + 1] += q.y; v[i + 2] += q.z; v[i + 3] += q.w;
     }
   }
-  if (e.lengths && row >= __ldg(e.lengths + b)) {
+  if constexpr (MASK) {
+    if (e.lengths && row >= __ldg(e.lengths + b)) {
 #pragma unroll
-    for (int i = 0; i < NV; ++i) v[i] = 0.f;
+      for (int i = 0; i < NV; ++i) v[i] = 0.f;
+    }
   }
   if (e.out_f32) {
 #pragma unroll

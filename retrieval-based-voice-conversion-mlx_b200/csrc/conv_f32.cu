@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(256) conv_f32_kernel(const __grid_constant__ C
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
     const int t = t0 + ty * 8 + r;
-    if (t < p.L_in) epilogue_store<4>(p.epi, b, t, n, acc[r]);
+    if (t < p.L_in) epilogue_store<4, true>(p.epi, b, t, n, acc[r]);
   }
 }
 
