@@ -82,7 +82,10 @@ struct MmaCfg {
 
 constexpr int MMA_THREADS = 320;  // producer warp + MMA warp + 2 epilogue warpgroups
 
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES, int PM, int EW>
+// LEAN = 1: ordinary convolutions only (up == 1, no fused noise conv, dense 16-bit output) - the 36 ResBlock launches of
+// the 256- / 128-channel stages.  The epilogue warps run at the 96-register cap of an 18-warp CTA, and the registers the
+// noise-conv / zero-stuffing / phase-scatter code keeps alive cost the general kernel 24 B of spills per thread.
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES, int PM, int EW, int LEAN>
 __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_mma_kernel(const __grid_constant__ ConvParams p) {
   using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
   extern __shared__ uint8_t smem_raw[];
@@ -239,7 +242,7 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
     constexpr int CH = N_TILE / CW;
     constexpr int ITEMS = MB * CH;
     const Epilogue& e = p.epi;
-    const bool fast = (e.up == 1);
+    const bool fast = LEAN ? true : (e.up == 1);
     const size_t slice_stride = (size_t)e.Lp_out * 8;
     uint32_t acc_it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -508,14 +511,16 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
               sm[2 * s8 + 1] = *reinterpret_cast<const float4*>(e.sum_in + off + s8 * slice_stride + 4);
             }
           }
-          float hv[8];  // har samples under this row's (<= 8-tap) noise conv, loaded before the TMEM wait
-          if (e.nz_har) {
-            const float* hb = e.nz_har + (size_t)b * e.nz_src;
-            const int s0 = t_in * e.nz_stride - e.nz_pad;
+          [[maybe_unused]] float hv[LEAN ? 1 : 8];  // har samples under this row's (<= 8-tap) noise conv, loaded before the TMEM wait
+          if constexpr (!LEAN) {
+            if (e.nz_har) {
+              const float* hb = e.nz_har + (size_t)b * e.nz_src;
+              const int s0 = t_in * e.nz_stride - e.nz_pad;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int sidx = s0 + j;
-              hv[j] = (valid && j < e.nz_k && sidx >= 0 && sidx < e.nz_src) ? __ldg(hb + sidx) : 0.f;
+              for (int j = 0; j < 8; ++j) {
+                const int sidx = s0 + j;
+                hv[j] = (valid && j < e.nz_k && sidx >= 0 && sidx < e.nz_src) ? __ldg(hb + sidx) : 0.f;
+              }
             }
           }
           // bias of the 32 columns, requested before the TMEM wait as well (the volatile TMEM load pins everything
@@ -540,7 +545,7 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
                 v[0] += rr[2 * s8].x; v[1] += rr[2 * s8].y; v[2] += rr[2 * s8].z; v[3] += rr[2 * s8].w;
                 v[4] += rr[2 * s8 + 1].x; v[5] += rr[2 * s8 + 1].y; v[6] += rr[2 * s8 + 1].z; v[7] += rr[2 * s8 + 1].w;
               }
-              if (e.nz_har) {  // fused noise_convs[i](har_source), hifigan_nsf.py:199 (har values hoisted above)
+              if constexpr (!LEAN) { if (e.nz_har) {  // fused noise_convs[i](har_source), hifigan_nsf.py:199 (har values hoisted above)
                 const int co = n0 + s8 * 8;
                 const float4 nb0 = __ldg(reinterpret_cast<const float4*>(e.nz_bias + co));
                 const float4 nb1 = __ldg(reinterpret_cast<const float4*>(e.nz_bias + co + 4));
@@ -555,7 +560,7 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
                     v[4] = fmaf(hv[j], w1.x, v[4]); v[5] = fmaf(hv[j], w1.y, v[5]); v[6] = fmaf(hv[j], w1.z, v[6]); v[7] = fmaf(hv[j], w1.w, v[7]);
                   }
                 }
-              }
+              } }
               if (e.scale != 1.f) {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) v[i] *= e.scale;
@@ -585,7 +590,7 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
                     pk[i] = *reinterpret_cast<uint32_t*>(&hh);
                   }
                 }
-                if (e.act_zs > 1) {  // zero-stuffed rows for the next stage's stride-act_zs transposed conv
+                if (!LEAN && e.act_zs > 1) {  // zero-stuffed rows for the next stage's stride-act_zs transposed conv
                   uint16_t* oa = reinterpret_cast<uint16_t*>(e.out_act) +
                                  ((((size_t)b * (e.cout >> 3) + (n0 >> 3) + s8) * e.Lp_act + PADL) + (size_t)t_in * e.act_zs) * 8;
                   *reinterpret_cast<uint4*>(oa) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -596,7 +601,7 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
               }
             }
           }
-        } else {
+        } else if constexpr (!LEAN) {
           // ---- generic path (polyphase upsample: phase scatter) ----
           // 8 columns per TMEM load so the accumulator registers are indexed statically (a 32-wide
           // array indexed by the s8 loop variable lived in local memory: STL/LDL in the r1c capture).
@@ -630,10 +635,11 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
   }
 }
 
-template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0, int EW = 8>
+template <int N_TILE, int MB, int KC, int B_STAGES, int A_STAGES = 2, int PM = 0, int EW = 8, int LEAN = 0>
 static cudaError_t launch_inst(const ConvParams& p, int num_sms, cudaStream_t s) {
   using Cfg = MmaCfg<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
-  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW>;
+  auto kern = conv_mma_kernel<N_TILE, MB, KC, B_STAGES, A_STAGES, PM, EW, LEAN>;
+  if (LEAN && (p.epi.up != 1 || p.epi.nz_har || p.epi.act_zs > 1)) return cudaErrorInvalidValue;
   if (PM != p.epi.pm || p.halo > Cfg::A_HALO) return cudaErrorInvalidValue;
   if (PM == 2 && (p.epi.up != 2 || p.epi.act_zs > 1 || p.epi.res || p.epi.sum_in || p.epi.out_act || !p.epi.out_f32 || p.epi.bias_bstride ||
                   (p.epi.nz_har && p.epi.nz_k > 8)))
@@ -677,6 +683,7 @@ cudaError_t launch_conv_mma(const ConvParams& p, int n_tile, int kc, int num_sms
   // 128-channel stage gets 7 % SLOWER with it (229 vs 214 ms), so two stages stay the default.
   if (n_tile == 128 && kc == 64) {
     if (p.a_stages == 3) return launch_inst<128, 2, 64, 6, 3>(p, num_sms, s);
+    if (p.epi_warps == 16 && p.lean && p.epi.up == 1 && !p.epi.nz_har && p.epi.act_zs <= 1) return launch_inst<128, 2, 64, 6, 2, 0, 16, 1>(p, num_sms, s);
     return p.epi_warps == 16 ? launch_inst<128, 2, 64, 6, 2, 0, 16>(p, num_sms, s) : launch_inst<128, 2, 64, 6, 2>(p, num_sms, s);
   }
   if (n_tile == 64 && kc == 64) return p.epi_warps_small == 16 ? launch_inst<64, 4, 64, 4, 2, 0, 16>(p, num_sms, s) : launch_inst<64, 4, 64, 4>(p, num_sms, s);

@@ -121,6 +121,8 @@ struct rvcdec_handle {
                        // kernel is skipped and no stage adds noise_convs[i](har)
   int conv_epi_warps = 16;  // (profiles/r1bq: 16 warps 214 ms vs 8 warps 221 ms on the 128-channel stage) epilogue warps of the 128-wide conv_mma tiling (8 over 32-column items, 16 over 16-column items)
   int conv_epi_warps_small = 16;  // same for the 64- / 32-wide tilings (profiles/r1br: ups2 21.8 -> 17.6 ms, ups3 13.9 -> 12.3 ms)
+  int conv_lean = 1;   // 1 = ordinary convolutions (up == 1, no fused noise conv, dense output) of the 128-wide tiling run the
+                       // instantiation compiled without the noise-conv / zero-stuffing / phase-scatter epilogue code
   int pm_a_stages = 2; // activation ring depth of the rate-10 phase-major upsample tile (2 or 3)
   int ups_pm_on = 1;   // 1 = upsamples that have a phase-major image use it (and carry the stage's 8-tap noise conv + 16-bit copy)
   int poly2 = 0;       // 1 = stride-2 upsamples of fused-MRF stages run their polyphase image (no zeros read or multiplied; takes
@@ -467,6 +469,7 @@ int run_conv(rvcdec_handle* h, const char* group, const ConvLayer& L, int mode, 
   p.a_stages = epi.pm ? h->pm_a_stages : h->a_stages;
   p.epi_warps = h->conv_epi_warps;
   p.epi_warps_small = h->conv_epi_warps_small;
+  p.lean = h->conv_lean;
   if (mode == 0) {
     p.w = L.d_wf;
     if (L.mask_f32.size() > (size_t)MAX_NTILES)
@@ -1503,6 +1506,7 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     h->conv_epi_warps_small = (int)value;
     return 0;
   }
+  if (k == "conv_lean") { h->conv_lean = value ? 1 : 0; return RVCDEC_OK; }
   if (k == "pm_a_stages") {
     if (value != 2 && value != 3) return fail(RVCDEC_ERR_ARG, "pm_a_stages must be 2 or 3");
     h->pm_a_stages = (int)value;
