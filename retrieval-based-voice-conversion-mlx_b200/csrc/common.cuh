@@ -268,6 +268,8 @@ struct PairParams {
   const float* x_in;          // fp32 blocked-8 (B, 128, L); must not alias out_f32 (tiles read their neighbours' rows)
   const void* w1;             // conv_mma weight images, N tile 128 / K chunk 64: [tap][chunk][slice 8][n 128][8] 16-bit
   const void* w2;
+  const void* w1h;            // the same weights split by output-channel half: [tap][half 2][slice 16][n 64][8] (mrf_pair2.cu)
+  const void* w2h;
   const float* b1;
   const float* b2;
   int k1, d1, k2, d2;         // taps / dilation of conv1, conv2
@@ -286,6 +288,9 @@ struct PairParams {
 };
 bool mrf_pair_supported(int C, int halo1, int halo2);
 cudaError_t launch_mrf_pair(const PairParams& p, int num_sms, cudaStream_t s);
+// the same pair on CTA pairs (cta_group::2, two tiles in flight; mrf_pair2.cu)
+bool mrf_pair2_supported(int C, int halo1, int halo2);
+cudaError_t launch_mrf_pair2(const PairParams& p, int num_sms, cudaStream_t s);
 
 struct SourceParams {
   const float* f0;      // (B, T)

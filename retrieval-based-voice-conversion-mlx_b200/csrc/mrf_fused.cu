@@ -506,7 +506,8 @@ __global__ void __launch_bounds__(fused_threads(EW), 1) mrf_fused_kernel(const _
             tmem_load_cols<NC>(t_lane + mb * C + hh * NC, rr);
             // The next unit's operand rows are published BEFORE this block's global stores are issued: the proxy
             // fence in publish() waits for the thread's outstanding global stores (timing twin of mrf_pair.cu, r1q/r1s).
-            if (nx.valid) store_unit_x(xn, mb);
+            if (nx.valid) TWAIT(6, store_unit_x(xn, mb));
+            const long long t_out = TIMING ? clock64() : 0;
             float pj[Cfg::POST_TAPS];  // conv_post partial dot products of this row over this warp's channels
 #pragma unroll
             for (int j = 0; j < Cfg::POST_TAPS; ++j) pj[j] = 0.f;
@@ -563,6 +564,7 @@ __global__ void __launch_bounds__(fused_threads(EW), 1) mrf_fused_kernel(const _
                 }
               }
             }
+            if (TIMING) tacc[7] += clock64() - t_out;
             if (do_post) {
               // stage the partial sums of this block, then (column-half 0 warps) finish the samples whose 7-row
               // windows are complete: tile rows [mb*128 - 3, mb*128 + 125).  The ring keeps 3 blocks, so the one
@@ -607,13 +609,14 @@ __global__ void __launch_bounds__(fused_threads(EW), 1) mrf_fused_kernel(const _
     // wait acc1_full, wait x_full, stage-input load, total
     long long* o = p.timing + (size_t)blockIdx.x * 16 + (threadIdx.x == 32 ? 0 : 8);
     if (threadIdx.x == 32) {
-      o[0] = tacc[0]; o[1] = 0; o[2] = 0;
+      o[0] = tacc[0]; o[2] = 0;  // o[1] is written by the epilogue warp (final epilogue: output section)
       o[3] = clock64() - t_begin;
       // operand-row waits by position: conv1 block 0, conv1 blocks >= 1, conv2 block 0, conv2 blocks >= 1
       o[4] = 0; o[5] = 0; o[6] = t_taps; o[7] = 0;
     } else {
       o[0] = tacc[0]; o[1] = tacc[1]; o[2] = tacc[2]; o[3] = clock64() - t_begin;
-      o[4] = tacc[3]; o[5] = tacc[4]; o[6] = tacc[5];
+      o[4] = tacc[3]; o[5] = tacc[4]; o[6] = tacc[5]; o[7] = tacc[6];
+      (p.timing + (size_t)blockIdx.x * 16)[1] = tacc[7];
     }
   }
   tc_fence_before();

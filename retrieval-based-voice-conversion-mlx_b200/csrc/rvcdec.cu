@@ -48,6 +48,10 @@ struct ConvLayer {
   int n_tile = 0, kc = 0;
   std::vector<uint32_t> mask_mma;
   std::vector<uint16_t> wp[2];  // [fmt] f16 / bf16
+  // 128 -> 128 channel layers only: the image split by output-channel half for CTA pairs (mrf_pair2.cu):
+  // [tap][half 2][slice 16][n 64][8], one contiguous 16 KB block per (tap, CTA)
+  std::vector<uint16_t> wp2[2];
+  uint16_t* d_wp2[2] = {nullptr, nullptr};
   // device copies
   float* d_wf = nullptr;
   float* d_bias = nullptr;
@@ -138,6 +142,7 @@ struct rvcdec_handle {
   int pair_noise = 0;  // 1 = the pair stage's short noise conv rides in its upsample's epilogue (no noise_add launch)
   int pair_max_k = 0;  // > 0: on a per-conv 128-channel stage, ResBlocks with kernel size <= this run one fused launch per
                        // (conv1, conv2) pair (mrf_pair.cu) instead of two conv launches; the others stay per-conv
+  int pair_kernel = 1;  // 1 = mrf_pair.cu (one CTA per 256-row tile), 2 = mrf_pair2.cu (CTA pairs, cta_group::2, two tiles in flight)
   int pair_mrf = 0;  // 1 = fused conv1+conv2 pair kernel (mrf_pair.cu) on the 128-channel stage (r1z: on par with the per-conv path, so off)
   int fused_epi_warps = 8;   // epilogue warps of the fused ResBlock kernel (8 or 16)
   int fused_post = 1; // 1 = conv_post + tanh fused into the last stage's final fused-MRF launch (C = 32, 7 taps)
@@ -316,6 +321,16 @@ void finish_layer(ConvLayer& L, bool want_mma, int max_ntile = 256, int force_nt
             for (int n = 0; n < nt; ++n)
               for (int e = 0; e < 8; ++e)
                 wp[o++] = to16(L.wf[((size_t)t * L.Cin + c * kc + sl * 8 + e) * L.N_total + tile * nt + n], fmt);
+    if (L.Cin == 128 && L.N_total == 128 && L.up == 1) {
+      std::vector<uint16_t>& w2 = L.wp2[fmt];
+      w2.assign((size_t)L.ntaps * 128 * 128, 0);
+      size_t o2 = 0;
+      for (int t = 0; t < L.ntaps; ++t)
+        for (int half = 0; half < 2; ++half)
+          for (int sl = 0; sl < 16; ++sl)
+            for (int n = 0; n < 64; ++n)
+              for (int e = 0; e < 8; ++e) w2[o2++] = to16(L.wf[((size_t)t * L.Cin + sl * 8 + e) * L.N_total + half * 64 + n], fmt);
+    }
   }
 }
 
@@ -336,6 +351,8 @@ int upload_layer(rvcdec_handle* h, ConvLayer& L) {
   if ((rc = upload(h, L.bias, &L.d_bias))) return rc;
   for (int f = 0; f < 2; ++f)
     if ((rc = upload(h, L.wp[f], &L.d_wp[f]))) return rc;
+  for (int f = 0; f < 2; ++f)
+    if ((rc = upload(h, L.wp2[f], &L.d_wp2[f]))) return rc;
   if ((rc = upload(h, L.cbias, &L.d_cbias))) return rc;
   return 0;
 }
@@ -525,7 +542,7 @@ bool use_pair_mrf(const rvcdec_handle* h, int mode, int i) {
       const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
       const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
       if (c1.n_tile != 128 || c1.kc != 64 || c2.n_tile != 128 || c2.kc != 64) return false;  // weight image it streams
-      if (!mrf_pair_supported(h->ch[i], c1.halo, c2.halo)) return false;
+      if (!(h->pair_kernel == 2 ? mrf_pair2_supported(h->ch[i], c1.halo, c2.halo) : mrf_pair_supported(h->ch[i], c1.halo, c2.halo))) return false;
     }
   return true;
 }
@@ -538,7 +555,7 @@ bool pair_rb(const rvcdec_handle* h, int mode, int i, int j) {
     const ConvLayer& c1 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 0];
     const ConvLayer& c2 = h->rbconv[(((size_t)i * h->nk + j) * h->nd + m) * 2 + 1];
     if (c1.n_tile != 128 || c1.kc != 64 || c2.n_tile != 128 || c2.kc != 64) return false;
-    if (!mrf_pair_supported(h->ch[i], c1.halo, c2.halo)) return false;
+    if (!(h->pair_kernel == 2 ? mrf_pair2_supported(h->ch[i], c1.halo, c2.halo) : mrf_pair_supported(h->ch[i], c1.halo, c2.halo))) return false;
   }
   return true;
 }
@@ -556,6 +573,7 @@ int run_pair_rb(rvcdec_handle* h, const char* group, int i, int j, const Workspa
     PairParams p{};
     p.x_in = (m == 0) ? w.xs0 : buf[(m - 1) & 1];
     p.w1 = c1.d_wp[fs == ACT_BF16 ? 1 : 0]; p.w2 = c2.d_wp[fs == ACT_BF16 ? 1 : 0];
+    p.w1h = c1.d_wp2[fs == ACT_BF16 ? 1 : 0]; p.w2h = c2.d_wp2[fs == ACT_BF16 ? 1 : 0];
     p.b1 = c1.d_bias; p.b2 = c2.d_bias;
     p.k1 = c1.ntaps; p.d1 = c1.ntaps > 1 ? c1.shift[1] - c1.shift[0] : 1;
     p.k2 = c2.ntaps; p.d2 = c2.ntaps > 1 ? c2.shift[1] - c2.shift[0] : 1;
@@ -578,7 +596,7 @@ int run_pair_rb(rvcdec_handle* h, const char* group, int i, int j, const Workspa
     MARK(group, 2.0 * B * Lo * (c1.macs_per_row + c2.macs_per_row), bytes);
     if (h->d_timing && h->timing_launches < rvcdec_handle::kTimingMaxLaunches)
       p.timing = h->d_timing + (size_t)(h->timing_launches++) * h->num_sms * 16;
-    CK(launch_mrf_pair(p, h->num_sms, s)); ++h->launches;
+    CK(h->pair_kernel == 2 ? launch_mrf_pair2(p, h->num_sms, s) : launch_mrf_pair(p, h->num_sms, s)); ++h->launches;
   }
   return 0;
 }
@@ -597,6 +615,7 @@ int run_pair_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w,
       PairParams p{};
       p.x_in = (m == 0) ? w.xs0 : buf[(m - 1) & 1];
       p.w1 = c1.d_wp[fs == ACT_BF16 ? 1 : 0]; p.w2 = c2.d_wp[fs == ACT_BF16 ? 1 : 0];
+    p.w1h = c1.d_wp2[fs == ACT_BF16 ? 1 : 0]; p.w2h = c2.d_wp2[fs == ACT_BF16 ? 1 : 0];
       p.b1 = c1.d_bias; p.b2 = c2.d_bias;
       p.k1 = c1.ntaps; p.d1 = c1.ntaps > 1 ? c1.shift[1] - c1.shift[0] : 1;
       p.k2 = c2.ntaps; p.d2 = c2.ntaps > 1 ? c2.shift[1] - c2.shift[0] : 1;
@@ -619,7 +638,7 @@ int run_pair_mrf(rvcdec_handle* h, const char* group, int i, const Workspace& w,
       MARK(group, 2.0 * B * Lo * (c1.macs_per_row + c2.macs_per_row), bytes);
       if (h->d_timing && h->timing_launches < rvcdec_handle::kTimingMaxLaunches)
         p.timing = h->d_timing + (size_t)(h->timing_launches++) * h->num_sms * 16;
-      CK(launch_mrf_pair(p, h->num_sms, s)); ++h->launches;
+      CK(h->pair_kernel == 2 ? launch_mrf_pair2(p, h->num_sms, s) : launch_mrf_pair(p, h->num_sms, s)); ++h->launches;
     }
   return 0;
 }
@@ -1548,7 +1567,11 @@ int rvcdec_set_option(rvcdec_handle* h, const char* key, int64_t value) {
     return RVCDEC_OK;
   }
   if (k == "pair_noise") { h->pair_noise = value ? 1 : 0; return RVCDEC_OK; }
-  if (k == "pair_mrf") { h->pair_mrf = value ? 1 : 0; return RVCDEC_OK; }
+  if (k == "pair_mrf") { h->pair_mrf = value ? 1 : 0; drop_graphs(h); return RVCDEC_OK; }
+  if (k == "pair_kernel") {
+    if (value != 1 && value != 2) return fail(RVCDEC_ERR_ARG, "pair_kernel must be 1 or 2");
+    h->pair_kernel = (int)value; drop_graphs(h); return RVCDEC_OK;
+  }
   if (k == "pair_max_k") {
     if (value < 0 || value > 64) return fail(RVCDEC_ERR_ARG, "pair_max_k out of range");
     h->pair_max_k = (int)value;

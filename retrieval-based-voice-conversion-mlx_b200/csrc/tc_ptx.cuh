@@ -159,6 +159,83 @@ __device__ __forceinline__ void tc_st8(uint32_t taddr, const uint32_t (&r)[8]) {
                : "memory");
 }
 
+// ---- CTA pairs (cta_group::2): one tcgen05.mma covers M = 256 rows, 128 per CTA; every CTA supplies its own A rows and
+// HALF of B (N/2 rows); the accumulator of CTA r holds rows [128 r, 128 r + 128) x N.  tools/umma_bench3.cu checks exactly
+// this operand split and the handshake below (profiles/r2r_umma_cta_group2_issue_rate.txt). ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of the same shared-memory offset in CTA `rank` of the cluster (shared::cluster window)
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+// arrive on a barrier given by its shared::cluster address (own or peer CTA), releasing this thread's prior writes
+// (own and remote shared memory, TMEM reads ordered by tcgen05.fence::before_thread_sync) at cluster scope
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// the same with the default (CTA-scope release) semantics, as CUTLASS's ClusterBarrier::arrive(cta_id): enough when what the
+// arrival publishes lives in THIS CTA's shared memory / TMEM (the cluster-scope form costs a MEMBAR.ALL.GPU per arrive)
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// bounded wait with cluster-scope acquire (the arrivals may come from the peer CTA)
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  long long t_start = 0;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return;
+    if ((spin & 1023u) == 1023u) {
+      const long long now = clock64();
+      if (t_start == 0) t_start = now;
+      else if (now - t_start > 4000000000LL) {
+        printf("rvcdec: cluster mbarrier timeout (block %d thread %d bar 0x%x parity %u)\n", (int)blockIdx.x,
+               (int)threadIdx.x, bar, parity);
+        __trap();
+      }
+    }
+  }
+}
+// generic-proxy writes (own AND peer shared memory) -> visible to the async proxy (tcgen05.mma operand reads)
+__device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void st_cluster_v4(uint32_t cluster_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void tc2_mma_f16_pred_lh(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                                    uint32_t idesc, uint32_t accumulate, uint32_t leader) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "setp.ne.b32 q, %7, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(leader)
+      : "memory");
+}
+// completion of this thread's prior MMAs -> the barrier at this shared-memory offset in BOTH CTAs of the pair
+__device__ __forceinline__ void tc2_commit_pred(uint32_t bar, uint32_t leader) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %2;\n\t}" ::"r"(bar),
+      "r"(leader), "h"((uint16_t)3)
+      : "memory");
+}
+
 // ---- coalesced fp32 row stores ------------------------------------------------------------------
 // In the blocked-8 fp32 layout one row of a channel slice is 32 B, and an epilogue thread owns one row (TMEM
 // lane = row).  Storing it as two float4 per lane makes every STG.128 touch 32 half sectors at a 32 B stride;
@@ -192,9 +269,10 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr, uint32_t lbo_b
 }
 // Instruction descriptor for kind::f16: D fp32 (bit 4), A/B format (0 = f16, 1 = bf16) at bits 7 / 10,
 // both operands K-major (bits 15, 16 = 0), N >> 3 at bits [17,23), M >> 4 at bits [24,29).
-__host__ __device__ inline uint32_t make_idesc(int fmt, int n) {
+__host__ __device__ inline uint32_t make_idesc_m(int fmt, int n, int m) {
   const uint32_t f = (fmt == ACT_BF16) ? 1u : 0u;
-  return (1u << 4) | (f << 7) | (f << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  return (1u << 4) | (f << 7) | (f << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
+__host__ __device__ inline uint32_t make_idesc(int fmt, int n) { return make_idesc_m(fmt, n, 128); }
 
 }  // namespace rvcdec

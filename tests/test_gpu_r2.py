@@ -416,3 +416,42 @@ def test_odd_upsample_rates_fast_mode(dev):
     assert y32.shape == (2, 1, 400 * 60)
     assert e32 <= FP32_BAR, e32
     assert corr["min"] >= FAST_BAR, corr
+
+
+@pytest.mark.parametrize("cfg_name,B,T,seed", [("48k", 2, 150, 101), ("40k", 1, 97, 102), ("48k", 3, 2, 103), ("32k", 2, 61, 104),
+                                               ("48k", 5, 333, 105)])
+def test_cta_pair_kernel_matches_per_conv_path(dev, cfg_name, B, T, seed):
+    """rvcdec_set_option("pair_kernel", 2): the 128-channel stage's (conv1, conv2) pairs on CTA pairs (mrf_pair2.cu:
+    tcgen05.mma.cta_group::2 over a 256-row cluster tile, each CTA streaming half of every weight block, two tiles in
+    flight, the inner tile boundary exchanged through distributed shared memory) against one launch per conv.  Same operand
+    rounding and fp32 accumulation; only the order in which bias / residual enter the sums differs.  Covers items
+    shorter than a tile, several tiles per item, ragged tile ends, an odd number of tiles per cluster and repeat calls."""
+    cfg = {"48k": O.CONFIG_48K, "40k": O.CONFIG_40K, "32k": O.CONFIG_32K}[cfg_name]
+    m = build_module(cfg, 11000 + seed)
+    w = O.folded_weights(m.state_dict())
+    m = m.to(dev)
+    x, f0, g, noise = O.synth_inputs(cfg, B, T, seed=seed)
+    y_ref = O.decoder_forward(w, cfg, x, f0, g, noise)
+    xd, fd, gd, nd_ = x.to(dev), f0.to(dev), g.to(dev), noise.to(dev)
+    with torch.no_grad():
+        h = m._ensure_handle(dev)
+        h.set_option("pair_mrf", 0)
+        y0 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n0 = m.last_launch_count
+        h.set_option("pair_kernel", 2)
+        h.set_option("pair_mrf", 1)
+        y1 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        y1b = m(xd, fd, gd, noise=nd_, mode="fast").cpu()
+        n1 = m.last_launch_count
+        h.set_option("pair_kernel", 1)
+        y2 = m(xd, fd, gd, noise=nd_, mode="fast").cpu()  # the one-CTA pair kernel: same sums in the same order
+        h.set_option("pair_mrf", 0)
+    assert n1 <= n0 - 8, (n0, n1)
+    assert torch.equal(y1, y1b)
+    d = float((y1 - y0).abs().max())
+    record_parity({"test": "cta_pair_kernel_vs_per_conv", "cfg": cfg_name, "B": B, "T": T, "max_abs": d,
+                   "max_abs_vs_one_cta_pair": float((y1 - y2).abs().max())})
+    assert d <= 2e-3, d
+    assert float((y1 - y2).abs().max()) <= 1e-5
+    if T >= 50:
+        assert O.multires_logmel_corr(y1, y_ref, cfg.sr)["min"] >= FAST_BAR

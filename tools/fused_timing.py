@@ -21,8 +21,8 @@ with torch.no_grad():
     m._handle.set_option("fused_timing", 1)
     m(x, f0, g, mode="fast")
     t = m._handle.fused_timing()
-names = ["mma:wait_rows", "mma:wait_acc1", "mma:wait_w", "mma:total", "rows:c1b0", "rows:c1b1+", "mma:tap_loops", "rows:c2",
-         "epi:wait_acc1", "epi:wait_x", "epi:xload", "epi:total", "epi1:tmem_ld", "epi1:math+sts", "epi1:fence+arrive", ""]
+names = ["mma:wait_rows", "fin:out(sum+math+stg)", "mma:wait_w", "mma:total", "rows:c1b0", "rows:c1b1+", "mma:tap_loops", "rows:c2",
+         "epi:wait_acc1", "epi:wait_x", "epi:xload", "epi:total", "epi1:tmem_ld", "epi1:math+sts", "epi1:fence+arrive", "fin:next_x(ldg wait+sttm+sts+publish)"]
 for i in range(t.shape[0]):
     a = t[i].astype(float).mean(axis=0)
     print(f"launch {i}: " + "  ".join(f"{n}={a[j]/1e3:.0f}k" for j, n in enumerate(names) if n))

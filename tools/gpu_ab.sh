@@ -4,7 +4,7 @@ tag=$1; shift
 mkdir -p gpurun_out
 i=0
 for o in "$@"; do
-  RVC_B200_OPTS="$o" python bench.py --chunks ${CHUNKS:-64} --steps 3 --warmup 2 --no-cpu > gpurun_out/${tag}_ab$i.json 2> gpurun_out/${tag}_ab$i.err
+  RVC_B200_OPTS="$o" python bench.py --chunks ${CHUNKS:-64} --steps 3 --warmup 2 --no-cpu --no-longform > gpurun_out/${tag}_ab$i.json 2> gpurun_out/${tag}_ab$i.err
   echo "[$o] rc=$?"; python - <<PY
 import json
 d=json.load(open("gpurun_out/${tag}_ab$i.json"))
