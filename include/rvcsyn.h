@@ -64,6 +64,12 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
                  const int64_t* sid, const float* noise_zp, const float* noise_src, uint64_t seed, float* out, float* z_out,
                  void* workspace, size_t workspace_bytes, int32_t B, int32_t T, int32_t mode, void* stream);
 
+/* Tuning knobs.  "front_fp32" (0 / 1, default 0): in the fast modes (mode != 0) everything before the decoder - q|k|v, o,
+ * FFN, proj, the coupling layers' pre / WaveNet / post convolutions - runs on the tensor-core back-end from 16-bit operand
+ * copies (fp16; bf16 in mode 3) with fp32 accumulation; 1 keeps that part on the fp32 back-end whatever the mode.  mode 0 is
+ * fp32 throughout. */
+int rvcsyn_set_option(rvcsyn_handle* h, const char* key, int64_t value);
+
 /* ---- test hooks ---- stop after: 1 embedding, 2 / 3 / 4 / 5 q|k|v / attention / first LayerNorm / end of encoder layer 0,
  * 6 encoder (stats), 7 z_p, 8 first coupling layer, 9 flow; 0 = run everything.  rvcsyn_debug_read copies a named
  * intermediate of the last call ("x", "qkv", "att", "stats", "xf", "hh") as plain (B, C, T) fp32 into a device buffer. */

@@ -69,7 +69,7 @@ EXPORTS = [
     "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_debug_stat", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
     # include/rvcsyn.h
     "rvcsyn_create", "rvcsyn_load_weights", "rvcsyn_workspace_bytes", "rvcsyn_infer", "rvcsyn_decoder", "rvcsyn_last_launch_count",
-    "rvcsyn_destroy", "rvcsyn_last_error", "rvcsyn_debug_set_stop", "rvcsyn_debug_read",
+    "rvcsyn_destroy", "rvcsyn_last_error", "rvcsyn_debug_set_stop", "rvcsyn_debug_read", "rvcsyn_set_option",
     # include/rvcrefine.h
     "rvcrefine_create", "rvcrefine_load_weights", "rvcrefine_workspace_bytes", "rvcrefine_forward", "rvcrefine_noise_floats",
     "rvcrefine_last_launch_count", "rvcrefine_destroy", "rvcrefine_last_error",
@@ -167,6 +167,8 @@ def lib() -> C.CDLL:
     L.rvcsyn_workspace_bytes.restype = sz
     L.rvcsyn_infer.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, u64, vp, vp, vp, sz, i32, i32, i32, vp]
     L.rvcsyn_infer.restype = C.c_int
+    L.rvcsyn_set_option.argtypes = [vp, C.c_char_p, i64]
+    L.rvcsyn_set_option.restype = C.c_int
     L.rvcsyn_debug_set_stop.argtypes = [vp, i32]
     L.rvcsyn_debug_set_stop.restype = C.c_int
     L.rvcsyn_debug_read.argtypes = [vp, C.c_char_p, vp, i64, vp, i32, i32, vp]
@@ -288,6 +290,9 @@ class SynHandle:
 
     def set_stop(self, stop: int) -> None:
         self._check(lib().rvcsyn_debug_set_stop(self._h, int(stop)), "rvcsyn_debug_set_stop")
+
+    def set_option(self, key: str, value: int):
+        self._check(lib().rvcsyn_set_option(self._h, key.encode(), int(value)), "rvcsyn_set_option")
 
     def debug_read(self, name: str, dst, workspace, B: int, T: int, stream) -> int:
         n = lib().rvcsyn_debug_read(self._h, name.encode(), dst.data_ptr(), dst.numel(), workspace.data_ptr(), B, T, stream)

@@ -95,7 +95,7 @@ struct ConvParams {
   int epi_warps_small;     // same for the 64- / 32-wide tilings (zero-stuffed stride-2 upsamples, per-conv stages 2-3)
   int epi_warps;           // 16 = the 128-wide tiling runs 16 epilogue warps over 16-column items; anything else = 8 / 32
   int lean;                // 1 = ordinary convolutions of the 128-wide tiling may run the LEAN instantiation (option "conv_lean")
-  int in_slices_phys;      // fp32 back-end: 8-channel slices per item of the tensor act_in points into (0 = Cin / 8); lets a
+  int in_slices_phys;      // 8-channel slices per item of the tensor act_in points into (0 = Cin / 8); lets a
                            // convolution read a channel sub-range of a wider tensor (coupling layers, residuals.py:239)
   Epilogue epi;
 };

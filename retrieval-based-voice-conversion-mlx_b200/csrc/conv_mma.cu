@@ -157,7 +157,7 @@ __global__ void __launch_bounds__((PM || EW == 16) ? 576 : MMA_THREADS, 1) conv_
       const int n_tile = rem - m_tile * n_tiles;
       const int t0 = m_tile * Cfg::MT;
       const uint32_t mask = p.tapmask[n_tile];
-      const uint8_t* a_src = act + (((size_t)b * nsl) * p.Lp_in + PADL + t0 - p.halo) * 16;
+      const uint8_t* a_src = act + (((size_t)b * (p.in_slices_phys ? p.in_slices_phys : nsl)) * p.Lp_in + PADL + t0 - p.halo) * 16;
       const uint8_t* w_src = wgt + (size_t)n_tile * ntaps * nkc * Cfg::B_STAGE_BYTES;
       for (int kc = 0; kc < nkc; ++kc) {
         mbar_wait(a_empty + 8 * a_stage, a_phase ^ 1u);

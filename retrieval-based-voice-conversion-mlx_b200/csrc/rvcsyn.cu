@@ -19,13 +19,15 @@ namespace rvcdec {
 // kernels of synth_front.cu
 cudaError_t launch_pack_btc(const float* x, float* out, int B, int T, int C, int Lp, cudaStream_t s);
 cudaError_t launch_embed_post(float* x, const long long* pitch, const float* emb_pitch, const int* lengths, int B, int T, int H,
-                              int Lp, float scale, cudaStream_t s);
+                              int Lp, float scale, void* x16, int fmt, cudaStream_t s);
 cudaError_t launch_gather_rows(const float* table, const long long* idx, float* out, int B, int D, int rows, cudaStream_t s);
 cudaError_t launch_layernorm(const float* x, float* y, const float* gamma, const float* beta, const int* lengths, int B, int T, int C,
-                             int Lp, float eps, cudaStream_t s);
-cudaError_t launch_gate(const float* a, float* acts, int B, int T, int H, int Lp, cudaStream_t s);
+                             int Lp, float eps, void* y16, int fmt, cudaStream_t s);
+cudaError_t launch_gate(const float* a, float* acts, int B, int T, int H, int Lp, void* acts16, int fmt, cudaStream_t s);
 cudaError_t launch_zp(const float* stats, const float* noise, float* zp, const int* lengths, uint64_t seed, uint64_t item0, int B,
-                      int T, int C, int Lp, cudaStream_t s);
+                      int T, int C, int Lp, void* zp16, int fmt, cudaStream_t s);
+cudaError_t launch_cast16(const float* x, void* y16, int fmt, int B, int T, int C, int Lp, cudaStream_t s);
+cudaError_t launch_mask_rows(float* x32, int phys32, void* x16, int phys16, const int* lengths, int B, int T, int C, int Lp, cudaStream_t s);
 cudaError_t launch_attention(const float* qkv, float* out, const float* emb_rel_k, const float* emb_rel_v, const int* lengths, int B,
                              int T, int heads, int kc, int window, int Lp, cudaStream_t s);
 }  // namespace rvcdec
@@ -70,7 +72,39 @@ struct FConv {
   std::vector<float> wf, bias;
   float* d_wf = nullptr;
   float* d_bias = nullptr;
+  // tensor-core image (conv_mma.cu; mode != 0): [N tile][tap][K chunk][slice kc/8][n n_tile][8], fp16 and bf16
+  int n_tile = 0, kc = 0;
+  std::vector<uint16_t> wp[2];
+  uint16_t* d_wp[2] = {nullptr, nullptr};
 };
+
+uint16_t f_to16(float v, int fmt) {
+  if (fmt == 1) { __nv_bfloat16 b = __float2bfloat16_rn(v); return *reinterpret_cast<uint16_t*>(&b); }
+  __half hv = __float2half_rn(v);
+  return *reinterpret_cast<uint16_t*>(&hv);
+}
+
+// Tiling of the tensor-core back-end for this layer (widest N tile that divides N; 32-wide tiles with 32-channel chunks
+// for the coupling layers' 96-channel halves), and the packed images.
+void pack_mma(FConv& L) {
+  L.n_tile = 0;
+  if (L.Cin % 64 == 0 && L.N % 128 == 0) { L.n_tile = 128; L.kc = 64; }
+  else if (L.Cin % 64 == 0 && L.N % 64 == 0) { L.n_tile = 64; L.kc = 64; }
+  else if (L.Cin % 32 == 0 && L.N % 32 == 0) { L.n_tile = 32; L.kc = 32; }
+  if (!L.n_tile || L.N / L.n_tile > MAX_NTILES || !conv_mma_supported(L.n_tile, L.kc)) { L.n_tile = 0; return; }
+  const int nt = L.n_tile, kc = L.kc, nkc = L.Cin / kc, ntiles = L.N / nt;
+  for (int fmt = 0; fmt < 2; ++fmt) {
+    std::vector<uint16_t>& wp = L.wp[fmt];
+    wp.assign((size_t)L.ntaps * L.Cin * L.N, 0);
+    size_t o = 0;
+    for (int tile = 0; tile < ntiles; ++tile)
+      for (int t = 0; t < L.ntaps; ++t)
+        for (int c = 0; c < nkc; ++c)
+          for (int sl = 0; sl < kc / 8; ++sl)
+            for (int n = 0; n < nt; ++n)
+              for (int e = 0; e < 8; ++e) wp[o++] = f_to16(L.wf[((size_t)t * L.Cin + c * kc + sl * 8 + e) * L.N + tile * nt + n], fmt);
+  }
+}
 
 struct TMap {
   std::map<std::string, const rvcdec_tensor*> m;
@@ -158,6 +192,8 @@ struct rvcsyn_handle {
   std::vector<FlowLayer> flow;
   std::vector<void*> allocs;
   int64_t launches = 0;
+  int num_sms = 148;
+  int front_fp32 = 0;  // option "front_fp32": 1 = the front end stays on the fp32 back-end in every mode
   int debug_stop = 0;  // tests: 1 embed, 2 qkv of layer 0, 3 attention of layer 0, 4 first LayerNorm, 5 layer 0 done,
                        // 6 encoder done (stats), 7 z_p, 8 first coupling layer done, 9 flow done
 };
@@ -178,11 +214,16 @@ int up(rvcsyn_handle* h, const std::vector<T>& v, T** d) {
 int up_conv(rvcsyn_handle* h, FConv& L) {
   int rc;
   if ((rc = up(h, L.wf, &L.d_wf))) return rc;
+  pack_mma(L);
+  for (int f = 0; f < 2; ++f)
+    if ((rc = up(h, L.wp[f], &L.d_wp[f]))) return rc;
   return up(h, L.bias, &L.d_bias);
 }
 
 struct SynWs {
   float *phone, *x, *qkv, *att, *tmp, *h1, *stats, *xf, *hh, *a, *acts, *outacc, *g, *condB, *z_nct;
+  // 16-bit operand copies for the tensor-core front end (mode != 0), same blocked-8 layout
+  uint16_t *x16, *att16, *h116, *xf16, *hh16, *acts16, *out16;
   size_t bytes;
 };
 
@@ -208,6 +249,13 @@ SynWs carve_syn(const rvcsyn_handle* h, void* base, int B, int T) {
   w.g = take((size_t)B * std::max(c.gin_channels, 1) * 4);
   w.condB = take((size_t)B * 2 * H * c.flow_layers * 4);
   w.z_nct = take((size_t)B * I * T * 4);
+  w.x16 = (uint16_t*)take((size_t)B * H * Lp * 2);
+  w.att16 = (uint16_t*)take((size_t)B * H * Lp * 2);
+  w.h116 = (uint16_t*)take((size_t)B * c.filter_channels * Lp * 2);
+  w.xf16 = (uint16_t*)take((size_t)B * I * Lp * 2);
+  w.hh16 = (uint16_t*)take((size_t)B * H * Lp * 2);
+  w.acts16 = (uint16_t*)take((size_t)B * H * Lp * 2);
+  w.out16 = (uint16_t*)take((size_t)B * H * Lp * 2);
   w.bytes = off;
   return w;
 }
@@ -225,6 +273,25 @@ int fconv(rvcsyn_handle* h, const FConv& L, const float* in, int in_phys_slices,
   p.in_slices_phys = in_phys_slices;
   p.epi = e;
   SCK(launch_conv_f32(p, s));
+  ++h->launches;
+  return 0;
+}
+
+// the same through the tensor-core back-end: 16-bit blocked-8 input in format fmt (the epilogue knows nothing of lengths:
+// the caller masks the rows beyond an item's length with launch_mask_rows where the reference multiplies by x_mask)
+int mconv(rvcsyn_handle* h, const FConv& L, const void* in16, int fmt, int in_phys_slices, int B, int T, const Epilogue& e, cudaStream_t s) {
+  if (!L.n_tile) return sfail(RVCDEC_ERR_ARG, "front-end convolution %d -> %d has no tensor-core tiling", L.Cin, L.N);
+  ConvParams p{};
+  p.act_in = in16; p.act_fmt_in = fmt; p.w = L.d_wp[fmt == ACT_BF16 ? 1 : 0];
+  p.B = B; p.Cin = L.Cin; p.L_in = T; p.Lp_in = padded_rows(T);
+  p.N_total = L.N; p.ntaps = L.ntaps; p.halo = L.halo;
+  for (int t = 0; t < L.ntaps; ++t) p.shift[t] = L.shift[t];
+  for (int i = 0; i < L.N / L.n_tile; ++i) p.tapmask[i] = (1u << L.ntaps) - 1u;
+  p.in_slices_phys = in_phys_slices;
+  p.a_stages = 2; p.epi_warps = 16; p.epi_warps_small = 8; p.lean = 1;
+  p.epi = e;
+  p.epi.lengths = nullptr;
+  SCK(launch_conv_mma(p, L.n_tile, L.kc, h->num_sms, s));
   ++h->launches;
   return 0;
 }
@@ -264,6 +331,8 @@ int rvcsyn_create(const rvcsyn_config* cfg, int device, rvcsyn_handle** out) {
   }
   auto h = new rvcsyn_handle();
   h->cfg = c; h->device = device; h->dec = dec;
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0) h->num_sms = sms;
   *out = h;
   return 0;
 }
@@ -396,6 +465,13 @@ size_t rvcsyn_workspace_bytes(const rvcsyn_handle* h, int32_t B, int32_t T, int3
   return align_up(carve_syn(h, nullptr, B, T).bytes, 256) + (h->dec ? rvcdec_workspace_bytes(h->dec, B, T, mode) : 0);
 }
 
+int rvcsyn_set_option(rvcsyn_handle* h, const char* key, int64_t value) {
+  if (!h || !key) return sfail(RVCDEC_ERR_ARG, "null argument");
+  const std::string k = key;
+  if (k == "front_fp32") { h->front_fp32 = value ? 1 : 0; return RVCDEC_OK; }
+  return sfail(RVCDEC_ERR_ARG, "unknown option '%s'", key);
+}
+
 int rvcsyn_debug_set_stop(rvcsyn_handle* h, int32_t stop) {
   if (!h) return sfail(RVCDEC_ERR_ARG, "null handle");
   h->debug_stop = stop;
@@ -449,9 +525,27 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
   const int NL = c.flow_layers;
   h->launches = 0;
   int rc;
+  // mode != 0: every convolution but the phone embedding runs on the tensor-core back-end from 16-bit operand copies
+  // (fp16; bf16 in mode 3) with fp32 accumulation, bias, residual and LayerNorm; attention, gate and z_p stay fp32
+  const bool fast = mode != 0 && !h->front_fp32;
+  const int ff = (mode == 3) ? ACT_BF16 : ACT_F16;
+  // y = conv(x): fp32 back-end from `in32`, or tensor cores from `in16`
+  auto conv = [&](const FConv& L, const float* in32, const void* in16, int phys, const Epilogue& e) -> int {
+    return fast ? mconv(h, L, in16, ff, phys, B, T, e, s) : fconv(h, L, in32, phys, B, T, e, s);
+  };
+  // x * x_mask behind a tensor-core convolution
+  auto mask = [&](float* x32, int phys32, void* x16, int phys16, int C) -> int {
+    if (!fast) return 0;
+    SCK(launch_mask_rows(x32, phys32, x16, phys16, lengths, B, T, C, Lp, s)); ++h->launches;
+    return 0;
+  };
   // zero padding rows of every tensor a convolution with taps reads (FFN k = 3, WaveNet k = 5)
   SCK(launch_zero_pads(w.x, w.hh, nullptr, 4, B, H, T, Lp, s)); ++h->launches;
   SCK(launch_zero_pads(w.h1, nullptr, nullptr, 4, B, F, T, Lp, s)); ++h->launches;
+  if (fast) {
+    SCK(launch_zero_pads(w.x16, w.hh16, nullptr, 2, B, H, T, Lp, s)); ++h->launches;
+    SCK(launch_zero_pads(w.h116, nullptr, nullptr, 2, B, F, T, Lp, s)); ++h->launches;
+  }
   // g = emb_g(sid)  (synthesizers.py:226)
   SCK(launch_gather_rows(h->d_emb_g, (const long long*)sid, w.g, B, c.gin_channels, c.spk_embed_dim, s)); ++h->launches;
   // ---- TextEncoder (encoders.py:127-144) ----
@@ -461,7 +555,8 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
     e.out_f32 = w.x;
     if ((rc = fconv(h, h->emb_phone, w.phone, 0, B, T, e, s))) return rc;
   }
-  SCK(launch_embed_post(w.x, c.use_f0 ? (const long long*)pitch : nullptr, h->d_emb_pitch, lengths, B, T, H, Lp, sqrtf((float)H), s)); ++h->launches;
+  SCK(launch_embed_post(w.x, c.use_f0 ? (const long long*)pitch : nullptr, h->d_emb_pitch, lengths, B, T, H, Lp, sqrtf((float)H),
+                        fast ? w.x16 : nullptr, ff, s)); ++h->launches;
   const int stop = h->debug_stop;
   if (stop == 1) return 0;
   for (int l = 0; l < c.n_layers; ++l) {
@@ -469,51 +564,55 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
     {  // q | k | v
       Epilogue e = epi_basic(A.qkv.d_bias, 3 * H, T, nullptr);
       e.out_f32 = w.qkv;
-      if ((rc = fconv(h, A.qkv, w.x, 0, B, T, e, s))) return rc;
+      if ((rc = conv(A.qkv, w.x, w.x16, 0, e))) return rc;
     }
     if (stop == 2 && l == 0) return 0;
     SCK(launch_attention(w.qkv, w.att, A.d_ek, A.d_ev, lengths, B, T, c.n_heads, H / c.n_heads, c.window_size, Lp, s)); ++h->launches;
+    if (fast) { SCK(launch_cast16(w.att, w.att16, ff, B, T, H, Lp, s)); ++h->launches; }
     if (stop == 3 && l == 0) return 0;
     {  // x + conv_o(att)  -> LayerNorm  (encoders.py:77-79)
       Epilogue e = epi_basic(A.o.d_bias, H, T, nullptr);
       e.res = w.x; e.out_f32 = w.tmp;
-      if ((rc = fconv(h, A.o, w.att, 0, B, T, e, s))) return rc;
+      if ((rc = conv(A.o, w.att, w.att16, 0, e))) return rc;
     }
-    SCK(launch_layernorm(w.tmp, w.x, A.d_g1, A.d_b1, lengths, B, T, H, Lp, 1e-5f, s)); ++h->launches;
+    SCK(launch_layernorm(w.tmp, w.x, A.d_g1, A.d_b1, lengths, B, T, H, Lp, 1e-5f, fast ? w.x16 : nullptr, ff, s)); ++h->launches;
     if (stop == 4 && l == 0) return 0;
     {  // FFN: conv_1 -> relu -> mask  (attentions.py:221-224); x is masked already
       Epilogue e = epi_basic(A.ffn1.d_bias, F, T, lengths);
-      e.out_act = w.h1; e.slope = 0.f;
-      if ((rc = fconv(h, A.ffn1, w.x, 0, B, T, e, s))) return rc;
+      e.slope = 0.f;
+      if (fast) { e.out_act = w.h116; e.act_fmt = ff; } else e.out_act = w.h1;
+      if ((rc = conv(A.ffn1, w.x, w.x16, 0, e)) || (rc = mask(nullptr, 0, w.h116, 0, F))) return rc;
     }
     {  // x + conv_2(...) * mask -> LayerNorm  (:225-226, encoders.py:81-83)
       Epilogue e = epi_basic(A.ffn2.d_bias, H, T, nullptr);
       e.res = w.x; e.out_f32 = w.tmp;
       // (rows beyond the length: conv_2 * mask = 0 and x = 0 there, and the LayerNorm below zeroes them anyway)
-      if ((rc = fconv(h, A.ffn2, w.h1, 0, B, T, e, s))) return rc;
+      if ((rc = conv(A.ffn2, w.h1, w.h116, 0, e))) return rc;
     }
-    SCK(launch_layernorm(w.tmp, w.x, A.d_g2, A.d_b2, lengths, B, T, H, Lp, 1e-5f, s)); ++h->launches;
+    SCK(launch_layernorm(w.tmp, w.x, A.d_g2, A.d_b2, lengths, B, T, H, Lp, 1e-5f, fast ? w.x16 : nullptr, ff, s)); ++h->launches;
     if (stop == 5 && l == 0) return 0;
   }
   {  // stats = proj(x) * mask  (encoders.py:141)
     Epilogue e = epi_basic(h->proj.d_bias, 2 * I, T, lengths);
     e.out_f32 = w.stats;
-    if ((rc = fconv(h, h->proj, w.x, 0, B, T, e, s))) return rc;
+    if ((rc = conv(h->proj, w.x, w.x16, 0, e)) || (rc = mask(w.stats, 0, nullptr, 0, 2 * I))) return rc;
   }
   if (stop == 6) return 0;
   // z_p = (m_p + exp(logs_p) * randn * 0.66666) * mask  (synthesizers.py:228)
-  SCK(launch_zp(w.stats, noise_zp, w.xf, lengths, seed, 0, B, T, I, Lp, s)); ++h->launches;
+  SCK(launch_zp(w.stats, noise_zp, w.xf, lengths, seed, 0, B, T, I, Lp, fast ? w.xf16 : nullptr, ff, s)); ++h->launches;
   if (stop == 7) return 0;
   // ---- flow(reverse=True) (residuals.py:162-165) ----
   const size_t half_off = (size_t)(half / 8) * Lp * 8;  // element offset of the upper channel half inside an item
   for (int i = c.n_flows - 1; i >= 0; --i) {
     const FlowLayer& Fl = h->flow[i];
-    const float* x0 = Fl.flipped ? w.xf + half_off : w.xf;   // the half the layer conditions on
-    float* x1 = Fl.flipped ? w.xf : w.xf + half_off;          // the half it updates
+    const size_t o0 = Fl.flipped ? half_off : 0, o1 = Fl.flipped ? 0 : half_off;
+    const float* x0 = w.xf + o0;   // the half the layer conditions on
+    float* x1 = w.xf + o1;         // the half it updates
     {  // h = pre(x0) * mask
       Epilogue e = epi_basic(Fl.pre.d_bias, H, T, lengths);
       e.out_f32 = w.hh;
-      if ((rc = fconv(h, Fl.pre, x0, I / 8, B, T, e, s))) return rc;
+      if (fast) { e.out_act = w.hh16; e.act_fmt = ff; e.slope = 1.f; }
+      if ((rc = conv(Fl.pre, x0, w.xf16 + o0, I / 8, e)) || (rc = mask(w.hh, 0, w.hh16, 0, H))) return rc;
     }
     // WaveNet (modules.py:84-117): per-item bias = in_layer bias + cond_layer(g) slice
     SCK(launch_cond(c.gin_channels ? w.g : nullptr, Fl.d_cond_w, Fl.d_cond_b, Fl.d_in_bias_all, w.condB, B, c.gin_channels, 2 * H * NL, s)); ++h->launches;
@@ -522,24 +621,27 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
         Epilogue e = epi_basic(w.condB + (size_t)l * 2 * H, 2 * H, T, nullptr);
         e.bias_bstride = 2 * H * NL;
         e.out_f32 = w.a;
-        if ((rc = fconv(h, Fl.in[l], w.hh, 0, B, T, e, s))) return rc;
+        if ((rc = conv(Fl.in[l], w.hh, w.hh16, 0, e))) return rc;
       }
-      SCK(launch_gate(w.a, w.acts, B, T, H, Lp, s)); ++h->launches;
+      SCK(launch_gate(w.a, w.acts, B, T, H, Lp, fast ? w.acts16 : nullptr, ff, s)); ++h->launches;
       {  // output += skip part
         Epilogue e = epi_basic(Fl.skip[l].d_bias, H, T, nullptr);
         e.res = (l == 0) ? nullptr : w.outacc; e.out_f32 = w.outacc;
-        if ((rc = fconv(h, Fl.skip[l], w.acts, 0, B, T, e, s))) return rc;
+        if (fast && l == NL - 1) { e.out_act = w.out16; e.act_fmt = ff; e.slope = 1.f; }
+        if ((rc = conv(Fl.skip[l], w.acts, w.acts16, 0, e))) return rc;
       }
       if (l < NL - 1) {  // x = (x + res part) * mask
         Epilogue e = epi_basic(Fl.res[l].d_bias, H, T, lengths);
         e.res = w.hh; e.out_f32 = w.hh;
-        if ((rc = fconv(h, Fl.res[l], w.acts, 0, B, T, e, s))) return rc;
+        if (fast) { e.out_act = w.hh16; e.act_fmt = ff; e.slope = 1.f; }
+        if ((rc = conv(Fl.res[l], w.acts, w.acts16, 0, e)) || (rc = mask(w.hh, 0, w.hh16, 0, H))) return rc;
       }
     }
     {  // x1 = (x1 - post(output * mask)) * mask   (mean-only coupling, reverse; residuals.py:239-255)
       Epilogue e = epi_basic(Fl.post.d_bias, I, T, lengths);
       e.scale = -1.f; e.sum_in = x1; e.out_f32 = x1;
-      if ((rc = fconv(h, Fl.post, w.outacc, 0, B, T, e, s))) return rc;
+      if (fast) { e.out_act = w.xf16 + o1; e.act_fmt = ff; e.slope = 1.f; }
+      if ((rc = conv(Fl.post, w.outacc, w.out16, 0, e)) || (rc = mask(x1, I / 8, w.xf16 + o1, I / 8, half))) return rc;
     }
     if (stop == 8 && i == c.n_flows - 1) return 0;
   }

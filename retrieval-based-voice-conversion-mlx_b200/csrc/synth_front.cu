@@ -15,6 +15,23 @@ __device__ __forceinline__ size_t blk_off(int b, int nsl, int sl, int Lp, int t)
 }
 
 // (B, T, C) row-major fp32 (phone features, encoders.py:130) -> blocked-8
+// 8 fp32 values -> one 16-byte row of the 16-bit operand copy (same element offset as the fp32 tensor): the
+// tensor-core front end (mode != 0) feeds every convolution from such copies
+__device__ __forceinline__ void store16(void* base16, size_t elem_off, const float (&v)[8], int fmt) {
+  uint32_t pk[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (fmt == ACT_BF16) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      pk[i] = *reinterpret_cast<uint32_t*>(&h);
+    } else {
+      __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+      pk[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+  }
+  *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(base16) + elem_off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+}
+
 __global__ void pack_btc_kernel(const float* __restrict__ x, float* __restrict__ out, int B, int T, int C, int Lp) {
   const int nsl = C >> 3;
   const size_t total = (size_t)B * nsl * T;
@@ -38,7 +55,7 @@ cudaError_t launch_pack_btc(const float* x, float* out, int B, int T, int C, int
 
 // x = leaky_relu((x + emb_pitch[pitch]) * sqrt(H), 0.1) * mask      (encoders.py:130-139; x holds emb_phone(phone))
 __global__ void embed_post_kernel(float* __restrict__ x, const long long* __restrict__ pitch, const float* __restrict__ emb_pitch,
-                                  const int* __restrict__ lengths, int B, int T, int H, int Lp, float scale) {
+                                  const int* __restrict__ lengths, int B, int T, int H, int Lp, float scale, void* x16, int fmt) {
   const int nsl = H >> 3;
   const size_t total = (size_t)B * nsl * T;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -64,13 +81,14 @@ __global__ void embed_post_kernel(float* __restrict__ x, const long long* __rest
     }
     *reinterpret_cast<float4*>(px) = *reinterpret_cast<float4*>(v);
     *reinterpret_cast<float4*>(px + 4) = *reinterpret_cast<float4*>(v + 4);
+    if (x16) store16(x16, blk_off(b, nsl, sl, Lp, t), v, fmt);
   }
 }
 cudaError_t launch_embed_post(float* x, const long long* pitch, const float* emb_pitch, const int* lengths, int B, int T, int H,
-                              int Lp, float scale, cudaStream_t s) {
+                              int Lp, float scale, void* x16, int fmt, cudaStream_t s) {
   const size_t total = (size_t)B * (H / 8) * T;
   const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 16));
-  embed_post_kernel<<<blocks, 256, 0, s>>>(x, pitch, emb_pitch, lengths, B, T, H, Lp, scale);
+  embed_post_kernel<<<blocks, 256, 0, s>>>(x, pitch, emb_pitch, lengths, B, T, H, Lp, scale, x16, fmt);
   return cudaGetLastError();
 }
 
@@ -92,7 +110,8 @@ cudaError_t launch_gather_rows(const float* table, const long long* idx, float* 
 // One warp per time step would waste lanes at C = 192; a thread per (b, t) reads its row's slices at a stride and the
 // warp's 32 consecutive time steps make every access a contiguous 1 KB run.
 __global__ void layernorm_kernel(const float* __restrict__ x, float* __restrict__ y, const float* __restrict__ gamma,
-                                 const float* __restrict__ beta, const int* __restrict__ lengths, int B, int T, int C, int Lp, float eps) {
+                                 const float* __restrict__ beta, const int* __restrict__ lengths, int B, int T, int C, int Lp, float eps,
+                                 void* y16, int fmt) {
   const int nsl = C >> 3;
   const size_t total = (size_t)B * T;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -124,19 +143,20 @@ __global__ void layernorm_kernel(const float* __restrict__ x, float* __restrict_
       for (int c = 0; c < 8; ++c) v[c] = ok ? (v[c] - mean) * rstd * __ldg(gamma + sl * 8 + c) + __ldg(beta + sl * 8 + c) : 0.f;
       *reinterpret_cast<float4*>(y + o) = *reinterpret_cast<float4*>(v);
       *reinterpret_cast<float4*>(y + o + 4) = *reinterpret_cast<float4*>(v + 4);
+      if (y16) store16(y16, o, v, fmt);
     }
   }
 }
 cudaError_t launch_layernorm(const float* x, float* y, const float* gamma, const float* beta, const int* lengths, int B, int T, int C,
-                             int Lp, float eps, cudaStream_t s) {
+                             int Lp, float eps, void* y16, int fmt, cudaStream_t s) {
   const size_t total = (size_t)B * T;
   const int blocks = (int)std::min<size_t>((total + 127) / 128, (size_t)(148 * 16));
-  layernorm_kernel<<<blocks, 128, 0, s>>>(x, y, gamma, beta, lengths, B, T, C, Lp, eps);
+  layernorm_kernel<<<blocks, 128, 0, s>>>(x, y, gamma, beta, lengths, B, T, C, Lp, eps, y16, fmt);
   return cudaGetLastError();
 }
 
 // acts = tanh(a[:, :H]) * sigmoid(a[:, H:])     (commons.py:88-103; the conditioning g_l is part of a's per-item bias)
-__global__ void gate_kernel(const float* __restrict__ a, float* __restrict__ acts, int B, int T, int H, int Lp) {
+__global__ void gate_kernel(const float* __restrict__ a, float* __restrict__ acts, int B, int T, int H, int Lp, void* acts16, int fmt) {
   const int nsl = H >> 3;
   const size_t total = (size_t)B * nsl * T;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -156,19 +176,20 @@ __global__ void gate_kernel(const float* __restrict__ a, float* __restrict__ act
     float* po = acts + blk_off(b, nsl, sl, Lp, t);
     *reinterpret_cast<float4*>(po) = *reinterpret_cast<float4*>(tv);
     *reinterpret_cast<float4*>(po + 4) = *reinterpret_cast<float4*>(tv + 4);
+    if (acts16) store16(acts16, blk_off(b, nsl, sl, Lp, t), tv, fmt);
   }
 }
-cudaError_t launch_gate(const float* a, float* acts, int B, int T, int H, int Lp, cudaStream_t s) {
+cudaError_t launch_gate(const float* a, float* acts, int B, int T, int H, int Lp, void* acts16, int fmt, cudaStream_t s) {
   const size_t total = (size_t)B * (H / 8) * T;
   const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 16));
-  gate_kernel<<<blocks, 256, 0, s>>>(a, acts, B, T, H, Lp);
+  gate_kernel<<<blocks, 256, 0, s>>>(a, acts, B, T, H, Lp, acts16, fmt);
   return cudaGetLastError();
 }
 
 // z_p = (m + exp(logs) * noise * 0.66666) * mask       (synthesizers.py:228); stats = [m | logs] (2C channels, masked)
 // noise: (B, C, T) fp32 draws to inject, or null -> in-kernel Philox keyed by (seed, global item, channel, frame)
 __global__ void zp_kernel(const float* __restrict__ stats, const float* __restrict__ noise, float* __restrict__ zp,
-                          const int* __restrict__ lengths, uint64_t seed, uint64_t item0, int B, int T, int C, int Lp) {
+                          const int* __restrict__ lengths, uint64_t seed, uint64_t item0, int B, int T, int C, int Lp, void* zp16, int fmt) {
   const int nsl = C >> 3;
   const size_t total = (size_t)B * nsl * T;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -194,13 +215,14 @@ __global__ void zp_kernel(const float* __restrict__ stats, const float* __restri
     float* po = zp + blk_off(b, nsl, sl, Lp, t);
     *reinterpret_cast<float4*>(po) = *reinterpret_cast<float4*>(m);
     *reinterpret_cast<float4*>(po + 4) = *reinterpret_cast<float4*>(m + 4);
+    if (zp16) store16(zp16, blk_off(b, nsl, sl, Lp, t), m, fmt);
   }
 }
 cudaError_t launch_zp(const float* stats, const float* noise, float* zp, const int* lengths, uint64_t seed, uint64_t item0, int B,
-                      int T, int C, int Lp, cudaStream_t s) {
+                      int T, int C, int Lp, void* zp16, int fmt, cudaStream_t s) {
   const size_t total = (size_t)B * (C / 8) * T;
   const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 16));
-  zp_kernel<<<blocks, 256, 0, s>>>(stats, noise, zp, lengths, seed, item0, B, T, C, Lp);
+  zp_kernel<<<blocks, 256, 0, s>>>(stats, noise, zp, lengths, seed, item0, B, T, C, Lp, zp16, fmt);
   return cudaGetLastError();
 }
 
@@ -388,6 +410,49 @@ cudaError_t launch_attention(const float* qkv, float* out, const float* emb_rel_
   if (e != cudaSuccess) return e;
   dim3 grid((T + ATT_BQ - 1) / ATT_BQ, heads, B);
   attention_kernel<<<grid, 256, smem, s>>>(qkv, out, emb_rel_k, emb_rel_v, lengths, B, T, heads, Lp, 1.f / sqrtf((float)kc));
+  return cudaGetLastError();
+}
+
+// fp32 blocked-8 tensor -> 16-bit operand copy (attention output, which the o-projection reads)
+__global__ void cast16_kernel(const float* __restrict__ x, void* __restrict__ y16, int fmt, int B, int T, int C, int Lp) {
+  const int nsl = C >> 3;
+  const size_t total = (size_t)B * nsl * T;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int t = (int)(i % T);
+    const size_t bs = i / T;
+    const size_t o = blk_off((int)(bs / nsl), nsl, (int)(bs % nsl), Lp, t);
+    float v[8];
+    *reinterpret_cast<float4*>(v) = *reinterpret_cast<const float4*>(x + o);
+    *reinterpret_cast<float4*>(v + 4) = *reinterpret_cast<const float4*>(x + o + 4);
+    store16(y16, o, v, fmt);
+  }
+}
+cudaError_t launch_cast16(const float* x, void* y16, int fmt, int B, int T, int C, int Lp, cudaStream_t s) {
+  const size_t total = (size_t)B * (C / 8) * T;
+  const int blocks = (int)std::min<size_t>((total + 255) / 256, (size_t)(148 * 16));
+  cast16_kernel<<<blocks, 256, 0, s>>>(x, y16, fmt, B, T, C, Lp);
+  return cudaGetLastError();
+}
+
+// x * x_mask after a tensor-core convolution (whose epilogue knows nothing of lengths): rows t >= lengths[b] of the fp32
+// tensor and / or its 16-bit copy (each with its own slices-per-item count: a coupling layer updates one channel half of z)
+// are zeroed.  One CTA per (item, slice); a full-length item costs one comparison.
+__global__ void mask_rows_kernel(float* __restrict__ x32, int phys32, void* __restrict__ x16, int phys16, const int* __restrict__ lengths,
+                                 int T, int C, int Lp) {
+  const int nsl = C >> 3;
+  const int b = blockIdx.x / nsl, sl = blockIdx.x % nsl;
+  const int len = lengths[b];
+  for (int t = len + (int)threadIdx.x; t < T; t += blockDim.x) {
+    if (x32) {
+      float* p = x32 + blk_off(b, phys32, sl, Lp, t);
+      *reinterpret_cast<float4*>(p) = make_float4(0.f, 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(p + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (x16) *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(x16) + blk_off(b, phys16, sl, Lp, t)) = make_uint4(0, 0, 0, 0);
+  }
+}
+cudaError_t launch_mask_rows(float* x32, int phys32, void* x16, int phys16, const int* lengths, int B, int T, int C, int Lp, cudaStream_t s) {
+  mask_rows_kernel<<<B * (C / 8), 128, 0, s>>>(x32, phys32 ? phys32 : C / 8, x16, phys16 ? phys16 : C / 8, lengths, T, C, Lp);
   return cudaGetLastError();
 }
 

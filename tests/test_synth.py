@@ -162,3 +162,50 @@ def test_synthesizer_infer_against_the_oracle_at_a_ragged_batch():
     assert torch.equal(x_mask.cpu(), mask)
     assert ez <= 2e-4, ez
     assert eo <= 2e-3, eo
+
+
+@pytest.mark.gpu
+def test_tensor_core_front_end_against_the_fp32_front_end():
+    """mode="fast": q|k|v, o, FFN, proj and the coupling layers' convolutions on the tensor-core back-end from fp16 operand
+    copies (fp32 accumulate, bias, residual, LayerNorm, attention, gate).  Ragged batch (lengths 333 / 200 / 64): z of
+    the fast front end against the fp32 front end (option front_fp32) with the same injected noise - rows beyond an
+    item's length exactly zero, everything else within the operand rounding - and the waveform at the fast bar."""
+    import rvc_b200
+
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(78)
+    m = rvc_b200.Synthesizer(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").eval()
+    with torch.no_grad():
+        for i in range(4):
+            m.flow.flows[2 * i].post.weight.normal_(0, 0.05)
+            m.flow.flows[2 * i].post.bias.normal_(0, 0.05)
+    B, T = 3, 333
+    gen = torch.Generator().manual_seed(6)
+    phone = torch.randn(B, T, 768, generator=gen).to(dev)
+    pitch = torch.randint(1, 256, (B, T), generator=gen).to(dev)
+    nsff0 = O.synth_f0(B, T, gen).to(dev)
+    sid = torch.tensor([0, 57, 108]).to(dev)
+    lens = torch.tensor([333, 200, 64]).to(dev)
+    nzp = torch.randn(B, 192, T, generator=gen).to(dev)
+    nsrc = torch.randn(B, T * 480, generator=gen).to(dev)
+    m = m.to(dev)
+    kw = dict(noise_zp=nzp, noise_src=nsrc)
+    o32, _, (z32, _, _, _) = m.infer(phone, lens, pitch, nsff0, sid, mode="fp32", **kw)
+    n32 = m.last_launch_count
+    h = m._ensure_handle(dev)
+    h.set_option("front_fp32", 1)
+    o_a, _, (z_a, _, _, _) = m.infer(phone, lens, pitch, nsff0, sid, mode="fast", **kw)
+    h.set_option("front_fp32", 0)
+    o_b, _, (z_b, _, _, _) = m.infer(phone, lens, pitch, nsff0, sid, mode="fast", **kw)
+    o_b2, _, (z_b2, _, _, _) = m.infer(phone, lens, pitch, nsff0, sid, mode="fast", **kw)
+    assert torch.equal(z_a, z32)                      # fp32 front end whatever the decoder's mode
+    assert torch.equal(z_b, z_b2) and torch.equal(o_b, o_b2)
+    assert float(z_b[1, :, 200:].abs().max()) == 0.0 and float(z_b[2, :, 64:].abs().max()) == 0.0
+    ez = float((z_b - z32).abs().max())
+    rel = float((z_b - z32).norm() / z32.norm())
+    corr = O.multires_logmel_corr(o_b.cpu()[:1], o32.cpu()[:1], 48000)
+    record_parity({"test": "tensor_core_front_end_B3_T333_ragged", "z_max_abs_vs_fp32_front": ez, "z_rel_l2": rel, "fast_logmel_vs_fp32": corr,
+                   "launches_fast": m.last_launch_count, "launches_fp32": n32})
+    assert rel <= 5e-3, (rel, ez)
+    assert ez <= 0.1, ez
+    assert corr["min"] >= 0.999, corr
