@@ -225,6 +225,22 @@ int64_t rvcdec_debug_fused_timing(rvcdec_handle* h, int64_t* dst, int64_t dst_nu
 int rvcdec_debug_pack_host(rvcdec_handle* h, const rvcdec_tensor* tensors, int32_t n);
 int64_t rvcdec_debug_packed(const rvcdec_handle* h, const char* layer, int32_t kind, void* dst, int64_t dst_bytes);
 
+/* ---- allocation-free harmonic source -------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * har[b][s] = tanh(lin_w * SineGenerator(f0)[b][s] + lin_b), the quantity the "har" tap of rvcdec_forward exposes (one
+ * sine, no overtones), computed with the frame-level fp64 phase prefix in a STATIC 512 KB device array inside the library
+ * instead of a workspace: the call allocates nothing (no cudaMalloc / cudaFree, no handle, no graph) and only enqueues
+ * two kernels on `stream`.  Limit: B * (T + 1) <= 65536; larger requests return RVCDEC_ERR_ARG with a message.
+ * All pointers DEVICE, on the CURRENT device: f0 (B, T) Hz; noise (B, T*upp) standard-normal draws or NULL (in-kernel
+ * Philox keyed by seed and the sample index); har (B, T*upp) out.  sr / upp / lin_w / lin_b: sampling rate, samples per
+ * frame, and m_source.l_linear's weight and bias.
+ * Every GPU that loads the library holds the array until exit; every call shares it and it keeps the last call's
+ * contents (a call writes each entry before it reads it).  Calls that overlap on the GPU race on it: serialise them. */
+int rvcdec_source_noalloc(const float* f0, const float* noise, uint64_t seed, float* har, int32_t B, int32_t T, int32_t upp,
+                          float sr, float lin_w, float lin_b, void* stream);
+
 void rvcdec_destroy(rvcdec_handle* h);
 const char* rvcdec_last_error(void);
 const char* rvcdec_version(void);

@@ -66,7 +66,7 @@ class ProfileEntry(C.Structure):
 EXPORTS = [
     "rvcdec_create", "rvcdec_load_weights", "rvcdec_workspace_bytes", "rvcdec_forward", "rvcdec_forward_host",
     "rvcdec_set_option", "rvcdec_set_initial_phases", "rvcdec_last_launch_count", "rvcdec_profile_enable", "rvcdec_profile_read", "rvcdec_debug_set_stop", "rvcdec_debug_read", "rvcdec_debug_pack_host",
-    "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_debug_stat", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
+    "rvcdec_debug_packed", "rvcdec_debug_fused_timing", "rvcdec_debug_stat", "rvcdec_source_noalloc", "rvcdec_destroy", "rvcdec_last_error", "rvcdec_version",
     # include/rvcsyn.h
     "rvcsyn_create", "rvcsyn_load_weights", "rvcsyn_workspace_bytes", "rvcsyn_infer", "rvcsyn_decoder", "rvcsyn_last_launch_count",
     "rvcsyn_destroy", "rvcsyn_last_error", "rvcsyn_debug_set_stop", "rvcsyn_debug_read", "rvcsyn_set_option",
@@ -125,6 +125,8 @@ def lib() -> C.CDLL:
     L.rvcdec_profile_enable.restype = C.c_int
     L.rvcdec_profile_read.argtypes = [vp, C.POINTER(ProfileEntry), i32]
     L.rvcdec_profile_read.restype = i32
+    L.rvcdec_source_noalloc.argtypes = [vp, vp, u64, vp, i32, i32, i32, C.c_float, C.c_float, C.c_float, vp]
+    L.rvcdec_source_noalloc.restype = C.c_int
     L.rvcdec_debug_set_stop.argtypes = [vp, i32]
     L.rvcdec_debug_set_stop.restype = C.c_int
     L.rvcdec_debug_read.argtypes = [vp, C.c_char_p, vp, i64, vp, i32, i32, i32, vp]

@@ -1,6 +1,7 @@
 // librvcdec.so - C ABI (include/rvcdec.h) over the sm_100a decoder kernels.
 // Host side: weight-norm folding and repacking at load time, workspace carving, and the
 // launch sequence of HiFiGANNSFGenerator.forward (reference hifigan_nsf.py:173-212).
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -1704,3 +1705,105 @@ int64_t rvcdec_debug_packed(const rvcdec_handle* h, const char* layer, int32_t k
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free harmonic source (no counterpart in the reference: added for
+// callers that cannot call cudaMalloc - code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// Same arithmetic as source_kernel (aux_kernels.cu; hifigan.py:197-228 + hifigan_nsf.py:48-52, one sine), but with the
+// frame-level fp64 phase prefix as a real device-wide scan kept in SCRATCH - here a file-scope device array, so the entry
+// point allocates nothing: no cudaMalloc / cudaFree, no workspace argument, no graph, no handle.  Every GPU that loads
+// the library holds the array (512 KB) until exit.  All calls share it and it keeps the last call's contents: every
+// element a call reads is written by that call first (entry 0 of every item is stored as 0 each time), and calls that
+// overlap on the GPU (different streams, several host threads) RACE on it - serialise them.
+// ---------------------------------------------------------------------------------------------------------------------
+#include "philox.cuh"
+
+constexpr int kNoAllocMaxPrefix = 1 << 16;  // B * (T + 1) <= 65536 phase-prefix entries
+static __device__ __align__(256) double g_noalloc_prefix[kNoAllocMaxPrefix];
+
+namespace {
+
+constexpr int NA_THREADS = 256;
+
+// prefix[b][l] = sum over frames j < l of the wrapped per-frame phase advance (cycles, modulo 1); one CTA per item
+__global__ void __launch_bounds__(NA_THREADS) noalloc_prefix_kernel(const float* __restrict__ f0, double* __restrict__ prefix, int T,
+                                                                    int upp, double inv_sr) {
+  __shared__ double chunk_sum[NA_THREADS];
+  const int b = blockIdx.x;
+  const float* f = f0 + (size_t)b * T;
+  double* o = prefix + (size_t)b * (T + 1);
+  const int per = (T + NA_THREADS - 1) / NA_THREADS;
+  const int j0 = min(threadIdx.x * per, T), j1 = min(j0 + per, T);
+  const double dupp = (double)upp;
+  double s = 0.0;
+  for (int j = j0; j < j1; ++j) {
+    const double adv = (double)f[j] * inv_sr * dupp + 0.5;
+    s += (adv - floor(adv)) - 0.5;
+  }
+  chunk_sum[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {  // exclusive scan over the 256 chunk sums
+    double acc = 0.0;
+    for (int i = 0; i < NA_THREADS; ++i) { const double v = chunk_sum[i]; chunk_sum[i] = acc; acc += v; }
+    o[0] = 0.0;  // must start at zero whatever the last call left here
+  }
+  __syncthreads();
+  double c = chunk_sum[threadIdx.x];
+  for (int j = j0; j < j1; ++j) {
+    const double adv = (double)f[j] * inv_sr * dupp + 0.5;
+    c += (adv - floor(adv)) - 0.5;
+    o[j + 1] = c - floor(c);
+  }
+}
+
+__global__ void __launch_bounds__(NA_THREADS) noalloc_source_kernel(const float* __restrict__ f0, const double* __restrict__ prefix,
+                                                                    const float* __restrict__ noise, float* __restrict__ har,
+                                                                    uint64_t seed, int B, int T, int upp, double inv_sr, float lin_w,
+                                                                    float lin_b) {
+  const size_t n = (size_t)T * upp, total = (size_t)B * n;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i / n);
+    const size_t s = i - (size_t)b * n;
+    const int fr = (int)(s / upp), k = (int)(s - (size_t)fr * upp);
+    const float fv = f0[(size_t)b * T + fr];
+    const double pc = prefix[(size_t)b * (T + 1) + fr];
+    const double ph = (double)fv * inv_sr * (double)(k + 1) + (pc - floor(pc));
+    const float frac = (float)(ph - floor(ph));
+    const float sine = 0.1f * sinpif(2.0f * frac);
+    const float z = noise ? __ldg(noise + i) : philox_normal(seed, (uint64_t)i);
+    const float v = fv > 0.f ? (sine + 0.003f * z) : ((0.1f / 3.0f) * z);
+    har[i] = tanhf(lin_w * v + lin_b);
+  }
+}
+
+}  // namespace
+
+extern "C" int rvcdec_source_noalloc(const float* f0, const float* noise, uint64_t seed, float* har, int32_t B, int32_t T, int32_t upp,
+                                     float sr, float lin_w, float lin_b, void* stream) {
+  if (!f0 || !har) return fail(RVCDEC_ERR_ARG, "null argument");
+  if (B < 1 || T < 1 || upp < 1 || !(sr > 0.f)) return fail(RVCDEC_ERR_ARG, "B, T, upp must be >= 1 and sr > 0");
+  if ((int64_t)B * ((int64_t)T + 1) > (int64_t)kNoAllocMaxPrefix)
+    return fail(RVCDEC_ERR_ARG, "rvcdec_source_noalloc: B * (T + 1) = %lld exceeds the static scratch of %d phase-prefix entries; split the batch "
+                "or use rvcdec_forward with a caller workspace", (long long)B * ((long long)T + 1), kNoAllocMaxPrefix);
+  // The array's name is a host-side stand-in in host code: its device address is looked up once per device, with that
+  // device current (the caller's current device is the one f0 / har live on).
+  static double* dev_ptr[64] = {nullptr};
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(RVCDEC_ERR_ARG, "device index %d out of range", dev);
+  double* prefix = dev_ptr[dev];
+  if (!prefix) {
+    CK(cudaGetSymbolAddress((void**)&prefix, g_noalloc_prefix));
+    dev_ptr[dev] = prefix;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const double inv_sr = 1.0 / (double)sr;
+  noalloc_prefix_kernel<<<B, NA_THREADS, 0, s>>>(f0, prefix, T, upp, inv_sr);
+  CK(cudaGetLastError());
+  const size_t total = (size_t)B * T * upp;
+  const int blocks = (int)std::min<size_t>((total + NA_THREADS - 1) / NA_THREADS, (size_t)(148 * 16));
+  noalloc_source_kernel<<<blocks, NA_THREADS, 0, s>>>(f0, prefix, noise, har, seed, B, T, upp, inv_sr, lin_w, lin_b);
+  CK(cudaGetLastError());
+  return RVCDEC_OK;
+}
