@@ -363,7 +363,7 @@ def synthesizer_leg(dev, B=16, T=3000, reps=3):
     m.infer(phone, lens, pitch, f0, sid, noise_zp=nzp, noise_src=nsrc, mode="fast")
     ms_all, ms_front = timed(0), timed(9)
     m._handle.set_stop(0)
-    return {"workload": f"net_g.infer, {B} x {T / 100:.0f} s, fast decoder + fp32 front end, injected noise, device-resident inputs",
+    return {"workload": f"net_g.infer, {B} x {T / 100:.0f} s, fast mode (decoder, front-end convolutions and attention on the tensor cores; softmax, LayerNorm, gate, z_p fp32), injected noise, device-resident inputs",
             "infer_ms": ms_all, "front_end_ms": ms_front, "front_end_share": ms_front / ms_all,
             "audio_s_per_s": B * T / 100.0 / ms_all * 1e3, "launches": m.last_launch_count}
 

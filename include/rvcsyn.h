@@ -67,7 +67,8 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
 /* Tuning knobs.  "front_fp32" (0 / 1, default 0): in the fast modes (mode != 0) everything before the decoder - q|k|v, o,
  * FFN, proj, the coupling layers' pre / WaveNet / post convolutions - runs on the tensor-core back-end from 16-bit operand
  * copies (fp16; bf16 in mode 3) with fp32 accumulation; 1 keeps that part on the fp32 back-end whatever the mode.  mode 0 is
- * fp32 throughout. */
+ * fp32 throughout.  "att_mma" (0 / 1, default 1): in the fast modes the windowed relative-position attention runs on the tensor
+ * cores too (scores and P V as tcgen05 GEMMs, online softmax in fp32); 0 = the fp32 attention kernel. */
 int rvcsyn_set_option(rvcsyn_handle* h, const char* key, int64_t value);
 
 /* ---- test hooks ---- stop after: 1 embedding, 2 / 3 / 4 / 5 q|k|v / attention / first LayerNorm / end of encoder layer 0,

@@ -26,6 +26,10 @@ cudaError_t launch_layernorm(const float* x, float* y, const float* gamma, const
 cudaError_t launch_gate(const float* a, float* acts, int B, int T, int H, int Lp, void* acts16, int fmt, cudaStream_t s);
 cudaError_t launch_zp(const float* stats, const float* noise, float* zp, const int* lengths, uint64_t seed, uint64_t item0, int B,
                       int T, int C, int Lp, void* zp16, int fmt, cudaStream_t s);
+cudaError_t launch_att_pack_rel(const float* ek, const float* ev, void* ek_img, void* ev_img, int fmt, cudaStream_t s);
+int att_mma_rel_bytes();
+cudaError_t launch_attention_mma(const void* qkv16, float* out, void* out16, const void* ek_img, const void* ev_img, const int* lengths,
+                                 int B, int T, int heads, int kc, int window, int Lp, int fmt, cudaStream_t s);
 cudaError_t launch_cast16(const float* x, void* y16, int fmt, int B, int T, int C, int Lp, cudaStream_t s);
 cudaError_t launch_mask_rows(float* x32, int phys32, void* x16, int phys16, const int* lengths, int B, int T, int C, int Lp, cudaStream_t s);
 cudaError_t launch_attention(const float* qkv, float* out, const float* emb_rel_k, const float* emb_rel_v, const int* lengths, int B,
@@ -167,6 +171,7 @@ void pack_fconv(FConv& L, const std::vector<float>& W, const std::vector<float>&
 struct AttnLayer {
   FConv qkv, o, ffn1, ffn2;
   std::vector<float> ek, ev, g1, b1, g2, b2;
+  uint8_t* d_rel16[2] = {nullptr, nullptr};  // [fmt] Ek | Ev as 16-bit B operand images of att_mma.cu
   float *d_ek = nullptr, *d_ev = nullptr, *d_g1 = nullptr, *d_b1 = nullptr, *d_g2 = nullptr, *d_b2 = nullptr;
 };
 
@@ -193,6 +198,7 @@ struct rvcsyn_handle {
   std::vector<void*> allocs;
   int64_t launches = 0;
   int num_sms = 148;
+  int att_mma = 1;     // option "att_mma": 1 = fast modes run the attention on the tensor cores (att_mma.cu), 0 = fp32 kernel
   int front_fp32 = 0;  // option "front_fp32": 1 = the front end stays on the fp32 back-end in every mode
   int debug_stop = 0;  // tests: 1 embed, 2 qkv of layer 0, 3 attention of layer 0, 4 first LayerNorm, 5 layer 0 done,
                        // 6 encoder done (stats), 7 z_p, 8 first coupling layer done, 9 flow done
@@ -223,7 +229,7 @@ int up_conv(rvcsyn_handle* h, FConv& L) {
 struct SynWs {
   float *phone, *x, *qkv, *att, *tmp, *h1, *stats, *xf, *hh, *a, *acts, *outacc, *g, *condB, *z_nct;
   // 16-bit operand copies for the tensor-core front end (mode != 0), same blocked-8 layout
-  uint16_t *x16, *att16, *h116, *xf16, *hh16, *acts16, *out16;
+  uint16_t *x16, *att16, *h116, *xf16, *hh16, *acts16, *out16, *qkv16;
   size_t bytes;
 };
 
@@ -256,6 +262,7 @@ SynWs carve_syn(const rvcsyn_handle* h, void* base, int B, int T) {
   w.hh16 = (uint16_t*)take((size_t)B * H * Lp * 2);
   w.acts16 = (uint16_t*)take((size_t)B * H * Lp * 2);
   w.out16 = (uint16_t*)take((size_t)B * H * Lp * 2);
+  w.qkv16 = (uint16_t*)take((size_t)B * 3 * H * Lp * 2);
   w.bytes = off;
   return w;
 }
@@ -448,6 +455,15 @@ int rvcsyn_load_weights(rvcsyn_handle* h, const rvcdec_tensor* tensors, int32_t 
         (rc = up(h, A.g2, &A.d_g2)) || (rc = up(h, A.b2, &A.d_b2)))
       return rc;
   }
+  for (auto& A : h->attn)
+    for (int f = 0; f < 2; ++f) {  // Ek | Ev as 16-bit B operand images (att_mma.cu)
+      void* img = nullptr;
+      SCK(cudaMalloc(&img, 2 * (size_t)att_mma_rel_bytes()));
+      h->allocs.push_back(img);
+      A.d_rel16[f] = (uint8_t*)img;
+      SCK(launch_att_pack_rel(A.d_ek, A.d_ev, img, (uint8_t*)img + att_mma_rel_bytes(), f == 1 ? ACT_BF16 : ACT_F16, 0));
+    }
+  SCK(cudaDeviceSynchronize());
   for (auto& Fl : h->flow) {
     if ((rc = up_conv(h, Fl.pre)) || (rc = up_conv(h, Fl.post)) || (rc = up(h, Fl.cond_w, &Fl.d_cond_w)) ||
         (rc = up(h, Fl.cond_b, &Fl.d_cond_b)) || (rc = up(h, Fl.in_bias_all, &Fl.d_in_bias_all)))
@@ -469,6 +485,7 @@ int rvcsyn_set_option(rvcsyn_handle* h, const char* key, int64_t value) {
   if (!h || !key) return sfail(RVCDEC_ERR_ARG, "null argument");
   const std::string k = key;
   if (k == "front_fp32") { h->front_fp32 = value ? 1 : 0; return RVCDEC_OK; }
+  if (k == "att_mma") { h->att_mma = value ? 1 : 0; return RVCDEC_OK; }
   return sfail(RVCDEC_ERR_ARG, "unknown option '%s'", key);
 }
 
@@ -542,6 +559,8 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
   // zero padding rows of every tensor a convolution with taps reads (FFN k = 3, WaveNet k = 5)
   SCK(launch_zero_pads(w.x, w.hh, nullptr, 4, B, H, T, Lp, s)); ++h->launches;
   SCK(launch_zero_pads(w.h1, nullptr, nullptr, 4, B, F, T, Lp, s)); ++h->launches;
+  const bool att_tc = fast && h->att_mma;
+  if (att_tc) { SCK(launch_zero_pads(w.qkv16, nullptr, nullptr, 2, B, 3 * H, T, Lp, s)); ++h->launches; }  // key / value tiles run past T
   if (fast) {
     SCK(launch_zero_pads(w.x16, w.hh16, nullptr, 2, B, H, T, Lp, s)); ++h->launches;
     SCK(launch_zero_pads(w.h116, nullptr, nullptr, 2, B, F, T, Lp, s)); ++h->launches;
@@ -564,11 +583,21 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
     {  // q | k | v
       Epilogue e = epi_basic(A.qkv.d_bias, 3 * H, T, nullptr);
       e.out_f32 = w.qkv;
+      if (att_tc) {  // the tensor-core attention reads q | k | v as 16-bit operand tiles
+        e.out_act = w.qkv16; e.act_fmt = ff; e.slope = 1.f;
+        if (stop != 2) e.out_f32 = nullptr;
+      }
       if ((rc = conv(A.qkv, w.x, w.x16, 0, e))) return rc;
     }
     if (stop == 2 && l == 0) return 0;
-    SCK(launch_attention(w.qkv, w.att, A.d_ek, A.d_ev, lengths, B, T, c.n_heads, H / c.n_heads, c.window_size, Lp, s)); ++h->launches;
-    if (fast) { SCK(launch_cast16(w.att, w.att16, ff, B, T, H, Lp, s)); ++h->launches; }
+    if (att_tc) {
+      const uint8_t* rel = A.d_rel16[ff == ACT_BF16 ? 1 : 0];
+      SCK(launch_attention_mma(w.qkv16, w.att, w.att16, rel, rel + att_mma_rel_bytes(), lengths, B, T, c.n_heads, H / c.n_heads, c.window_size,
+                               Lp, ff, s)); ++h->launches;
+    } else {
+      SCK(launch_attention(w.qkv, w.att, A.d_ek, A.d_ev, lengths, B, T, c.n_heads, H / c.n_heads, c.window_size, Lp, s)); ++h->launches;
+      if (fast) { SCK(launch_cast16(w.att, w.att16, ff, B, T, H, Lp, s)); ++h->launches; }
+    }
     if (stop == 3 && l == 0) return 0;
     {  // x + conv_o(att)  -> LayerNorm  (encoders.py:77-79)
       Epilogue e = epi_basic(A.o.d_bias, H, T, nullptr);

@@ -209,3 +209,104 @@ def test_tensor_core_front_end_against_the_fp32_front_end():
     assert rel <= 5e-3, (rel, ez)
     assert ez <= 0.1, ez
     assert corr["min"] >= 0.999, corr
+
+
+def _ref_attention(qkv, ek, ev, lens, heads=2, W=10, round16=False):
+    """fp64 restatement of attentions.py:89-125 on a (B, 3H, T) q | k | v tensor (optionally rounded to fp16 first, as the
+    tensor-core kernel reads it)."""
+    import math
+
+    B, C3, T = qkv.shape
+    H = C3 // 3
+    kc = H // heads
+    f = (lambda x: x.half().double()) if round16 else (lambda x: x.double())
+    q, k, v = [f(qkv[:, i * H:(i + 1) * H].reshape(B, heads, kc, T).transpose(2, 3)) for i in range(3)]
+    ek, ev = f(ek), f(ev)
+    idx = torch.arange(T)
+    d = idx[None, :] - idx[:, None]
+    rel = q @ ek.t()  # (B, heads, T, 2W+1)
+    s = q @ k.transpose(2, 3) + torch.where(d.abs() <= W, rel.gather(3, (d.clamp(-W, W) + W).expand(B, heads, T, T)),
+                                            torch.zeros((), dtype=torch.float64))
+    s = s / math.sqrt(kc)
+    for b, n in enumerate(lens):
+        dead = torch.ones(T, T, dtype=torch.bool)
+        dead[:n, :n] = False
+        s[b, :, dead] = -1e4
+    p = torch.softmax(s, -1)
+    pb = torch.zeros(B, heads, T, 2 * W + 1, dtype=torch.float64)
+    for j in range(2 * W + 1):
+        t = torch.arange(max(0, W - j), min(T, T - (j - W)))
+        pb[:, :, t, j] = p[:, :, t, t + (j - W)]
+    return (p @ v + pb @ ev).transpose(2, 3).reshape(B, H, T)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,T,lens", [(3, 333, [333, 200, 64]), (2, 128, [128, 1]), (1, 1000, [777])])
+def test_tensor_core_attention_against_the_fp32_kernel(B, T, lens):
+    """att_mma.cu (scores and P V as tcgen05 GEMMs over 128 x 128 tiles, online softmax, relative keys through a 21-column
+    side GEMM, relative values as one more K = 32 MMA into the same accumulator) against the fp32 attention kernel on the
+    SAME fp16-rounded q | k | v: output of layer 0's attention ("att" tap), ragged lengths, partial last tiles, a one-frame
+    item.  The kernel is held to an fp64 restatement on the fp16-rounded q | k | v it reads (5e-4 of the output scale); the
+    distance to the fp32 kernel is the rounding of q | k | v itself (seeded random weights make the logits large: 1-3 %),
+    bounded here and, end to end, by z of the whole front end with either kernel."""
+    import rvc_b200
+
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(79)
+    m = rvc_b200.Synthesizer(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").eval()
+    with torch.no_grad():  # relative embeddings large enough to matter
+        for l in range(6):
+            m.enc_p.encoder.attn_layers[l].emb_rel_k.normal_(0, 0.3)
+            m.enc_p.encoder.attn_layers[l].emb_rel_v.normal_(0, 0.3)
+    ek = m.enc_p.encoder.attn_layers[0].emb_rel_k.detach()[0].clone()
+    ev = m.enc_p.encoder.attn_layers[0].emb_rel_v.detach()[0].clone()
+    gen = torch.Generator().manual_seed(7)
+    phone = torch.randn(B, T, 768, generator=gen).to(dev)
+    pitch = torch.randint(1, 256, (B, T), generator=gen).to(dev)
+    nsff0 = O.synth_f0(B, T, gen).to(dev)
+    sid = torch.zeros(B, dtype=torch.long, device=dev)
+    lens_t = torch.tensor(lens).to(dev)
+    nzp = torch.randn(B, 192, T, generator=gen).to(dev)
+    nsrc = torch.randn(B, T * 480, generator=gen).to(dev)
+    m = m.to(dev)
+    kw = dict(noise_zp=nzp, noise_src=nsrc, mode="fast")
+    m.infer(phone, lens_t, pitch, nsff0, sid, **kw)
+    h = m._ensure_handle(dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    att, z = {}, {}
+
+    def tap(name, C, stop):
+        h.set_stop(stop)
+        m.infer(phone, lens_t, pitch, nsff0, sid, **kw)
+        dst = torch.empty(B, C, T, dtype=torch.float32, device=dev)
+        assert h.debug_read(name, dst, m._workspace, B, T, stream) == dst.numel()
+        torch.cuda.synchronize()
+        h.set_stop(0)
+        return dst.cpu()
+
+    try:
+        h.set_option("att_mma", 0)
+        qkv = tap("qkv", 576, 2)
+        for on in (0, 1):
+            h.set_option("att_mma", on)
+            att[on] = tap("att", 192, 3)
+            _, _, (zz, _, _, _) = m.infer(phone, lens_t, pitch, nsff0, sid, **kw)
+            z[on] = zz.cpu()
+    finally:
+        h.set_stop(0)
+        h.set_option("att_mma", 1)
+    assert bool(torch.isfinite(att[1]).all())
+    r_exact, r_16 = _ref_attention(qkv, ek, ev, lens), _ref_attention(qkv, ek, ev, lens, round16=True)
+    e_kernel, e_round, e_fp32 = [], [], []
+    for b, n in enumerate(lens):  # rows beyond an item's length are zeroed downstream (LayerNorm mask): compare the live rows
+        sc = float(r_exact[b, :, :n].abs().max()) + 1e-9
+        e_kernel.append(float((att[1][b, :, :n].double() - r_16[b, :, :n]).abs().max()) / sc)
+        e_round.append(float((att[1][b, :, :n] - att[0][b, :, :n]).abs().max()) / sc)
+        e_fp32.append(float((att[0][b, :, :n].double() - r_exact[b, :, :n]).abs().max()) / sc)
+    rel_z = float((z[1] - z[0]).norm() / z[0].norm())
+    record_parity({"test": "tensor_core_attention", "B": B, "T": T, "lens": lens, "vs_fp64_on_fp16_inputs": e_kernel,
+                   "vs_fp32_kernel": e_round, "fp32_kernel_vs_fp64": e_fp32, "z_rel_l2_vs_fp32_attention": rel_z})
+    assert max(e_fp32) <= 2e-4, e_fp32
+    assert max(e_kernel) <= 5e-4, e_kernel
+    assert max(e_round) <= 8e-2, e_round
+    assert rel_z <= 1e-2, rel_z

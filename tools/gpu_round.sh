@@ -17,3 +17,6 @@ sz=$(stat -c %s /tmp/${tag}_full.ncu-rep 2>/dev/null || echo 0); echo "rep bytes
 if [ "$sz" -gt 0 ] && [ "$sz" -lt 40000000 ]; then cp /tmp/${tag}_full.ncu-rep gpurun_out/; fi
 fi
 du -sh gpurun_out
+if [[ $what == *s* ]]; then
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/${tag}_synth_launches.csv \
+  python tools/synth_bench.py 4 3000 > gpurun_out/${tag}_ncu_synth.log 2>&1; echo "synth launchlist rc=$?"; fi
