@@ -333,7 +333,7 @@ def longform_leg(model, cfg, n_dev, reps=3):
 
 def synthesizer_leg(dev, B=16, T=3000, reps=3):
     """the whole net_g.infer (speaker embedding, TextEncoder, z_p sampling, reverse flow, decoder) through
-    rvc_b200.Synthesizer -> rvcsyn_infer, device-resident inputs, CUDA events; the front end runs in fp32 (parity first)."""
+    rvc_b200.Synthesizer -> rvcsyn_infer, device-resident inputs, CUDA events; fast mode (front-end convolutions and attention on the tensor cores)."""
     import rvc_b200
 
     SYN_48K = [1025, 32, 192, 192, 768, 2, 6, 3, 0, "1", [3, 7, 11], [[1, 3, 5]] * 3, [12, 10, 2, 2], 512, [24, 20, 4, 4], 109, 256, 48000]

@@ -89,17 +89,25 @@ def stitch(decoded: Sequence[np.ndarray], trims: Sequence[int], crossfade: int =
         raise ValueError("crossfade longer than the available context")
     fade_in = np.sin(0.5 * np.pi * np.linspace(0.0, 1.0, 2 * crossfade, dtype=np.float32)) ** 2
     fade_out = 1.0 - fade_in
-    out = None
+    # one pass into a preallocated buffer (growing the output by concatenation copied it once per chunk)
+    n = 2 * crossfade
+    spans = []
     for k, (d, t) in enumerate(zip(decoded, trims)):
         lo = t - (crossfade if k > 0 else 0)
         hi = len(d) - t + (crossfade if k < len(decoded) - 1 else 0)
-        seg = np.array(d[lo:hi], dtype=np.float32, copy=True)
-        if out is None:
-            out = seg
+        spans.append((lo, hi))
+    total = sum(hi - lo for lo, hi in spans) - n * (len(decoded) - 1)
+    out = np.empty(total, dtype=np.float32)
+    pos = 0
+    for k, (d, (lo, hi)) in enumerate(zip(decoded, spans)):
+        seg = np.asarray(d[lo:hi], dtype=np.float32)
+        if k == 0:
+            out[: len(seg)] = seg
+            pos = len(seg)
             continue
-        n = 2 * crossfade
-        out[-n:] = out[-n:] * fade_out + seg[:n] * fade_in
-        out = np.concatenate([out, seg[n:]])
+        out[pos - n: pos] = out[pos - n: pos] * fade_out + seg[:n] * fade_in
+        out[pos: pos + len(seg) - n] = seg[n:]
+        pos += len(seg) - n
     return out
 
 

@@ -47,6 +47,8 @@ class _Worker:
     x_stage: Optional[torch.Tensor] = None
     f_stage: Optional[torch.Tensor] = None
     g_stage: Optional[torch.Tensor] = None
+    tmp: Optional[torch.Tensor] = None      # pinned scratch of ragged shares (grow-only: a pinned allocation costs ~20 ms per 50 MB)
+    nz_stage: Optional[torch.Tensor] = None
 
 
 class MultiGpuDecoder:
@@ -89,6 +91,7 @@ class MultiGpuDecoder:
         if not any(w.healthy for w in self.workers):
             raise RuntimeError("no device could be set up: " + "; ".join(f"cuda:{w.device}: {w.error}" for w in self.workers))
         self.requeued = 0
+        self._out_flat: Optional[torch.Tensor] = None
 
     # ------------------------------------------------------------------
     def _run_share(self, w: _Worker, share: List[Unit], x, f0, g, out_flat: torch.Tensor, offsets: Dict[int, int], seed: int, noise=None):
@@ -112,7 +115,10 @@ class MultiGpuDecoder:
             gb[:] = g.reshape(1, -1)
         nz_ptr = None
         if noise is not None:  # injected source noise (parity tests): (1, n_total * upp) standard-normal draws
-            nb = chunking.pinned(torch.zeros(B, n, dtype=torch.float32))
+            if w.nz_stage is None or w.nz_stage.numel() < B * n:
+                w.nz_stage = chunking.pinned(torch.zeros(B * n, dtype=torch.float32))
+            nb = w.nz_stage[: B * n].view(B, n)
+            nb.zero_()
             for k, u in enumerate(share):
                 nb[k, :u.frames * self.upp] = noise[0, u.start * self.upp:(u.start + u.frames) * self.upp]
             nz_ptr = nb.data_ptr()
@@ -124,7 +130,9 @@ class MultiGpuDecoder:
             w.handle.forward_host(xb.data_ptr(), fb.data_ptr(), gb.data_ptr() if (g is not None and self.gin) else None, nz_ptr,
                                   seed + share[0].index, dst.data_ptr(), B, Tmax, self.mode, 0)
         else:  # ragged share: decode into a pinned scratch, then copy each unit's valid samples
-            tmp = chunking.pinned(torch.empty(B, n, dtype=torch.float32))
+            if w.tmp is None or w.tmp.numel() < B * n:
+                w.tmp = chunking.pinned(torch.empty(B * n, dtype=torch.float32))
+            tmp = w.tmp[: B * n].view(B, n)
             w.handle.forward_host(xb.data_ptr(), fb.data_ptr(), gb.data_ptr() if (g is not None and self.gin) else None, nz_ptr,
                                   seed + share[0].index, tmp.data_ptr(), B, Tmax, self.mode, 0)
             for k, u in enumerate(share):
@@ -136,14 +144,18 @@ class MultiGpuDecoder:
     def decode_units(self, x: torch.Tensor, f0: torch.Tensor, g: Optional[torch.Tensor], units: Sequence[Unit],
                      out_flat: Optional[torch.Tensor] = None, seed: int = 0, noise: Optional[torch.Tensor] = None):
         """Decode every unit; returns ``(out_flat, offsets)`` with unit ``u``'s ``u.frames * upp`` samples at
-        ``out_flat[offsets[u.index]:]``.  ``out_flat`` (pinned) is allocated when not given."""
+        ``out_flat[offsets[u.index]:]``.  When ``out_flat`` is not given the decoder's own pinned buffer is used (grow-only,
+        OVERWRITTEN by the next call: copy what must outlive it, as ``decode_long`` does)."""
         units = list(units)
         offsets, total = {}, 0
         for u in units:
             offsets[u.index] = total
             total += u.frames * self.upp
         if out_flat is None or out_flat.numel() < total:
-            out_flat = chunking.pinned(torch.empty(total, dtype=torch.float32))
+            cached = getattr(self, "_out_flat", None)
+            if cached is None or cached.numel() < total:
+                cached = self._out_flat = chunking.pinned(torch.empty(total, dtype=torch.float32))
+            out_flat = cached
         pending = units
         while pending:
             healthy = [w for w in self.workers if w.healthy]
