@@ -68,7 +68,9 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
  * FFN, proj, the coupling layers' pre / WaveNet / post convolutions - runs on the tensor-core back-end from 16-bit operand
  * copies (fp16; bf16 in mode 3) with fp32 accumulation; 1 keeps that part on the fp32 back-end whatever the mode.  mode 0 is
  * fp32 throughout.  "att_mma" (0 / 1, default 1): in the fast modes the windowed relative-position attention runs on the tensor
- * cores too (scores and P V as tcgen05 GEMMs, online softmax in fp32); 0 = the fp32 attention kernel. */
+ * cores too (scores and P V as tcgen05 GEMMs, online softmax in fp32); 0 = the fp32 attention kernel.  "graphs" (0 / 1, default
+ * 1) with "graph_max_frames" (default 16384): calls with injected z_p noise and B * T up to that many frames copy their inputs to
+ * fixed places in the workspace and replay the front end's ~130 launches as one CUDA graph per (workspace, B, T, mode). */
 int rvcsyn_set_option(rvcsyn_handle* h, const char* key, int64_t value);
 
 /* ---- test hooks ---- stop after: 1 embedding, 2 / 3 / 4 / 5 q|k|v / attention / first LayerNorm / end of encoder layer 0,

@@ -198,6 +198,21 @@ struct rvcsyn_handle {
   std::vector<void*> allocs;
   int64_t launches = 0;
   int num_sms = 148;
+  // CUDA-graph replay of the front end's launch sequence (small batches)
+  struct GraphEntry {
+    const void* ws;
+    int B, T, mode;
+    bool has_pitch;
+    uint64_t epoch;
+    cudaGraphExec_t exec;
+    int64_t launches;
+    uint64_t last_use;
+  };
+  std::vector<GraphEntry> graphs;
+  uint64_t epoch = 0, graph_clock = 0, graph_hits = 0, graph_captures = 0;
+  cudaStream_t cap_stream = nullptr;
+  int use_graphs = 1;                // option "graphs"
+  int64_t graph_max_frames = 16384;  // option "graph_max_frames": B * T up to which the sequence is graphed
   int att_mma = 1;     // option "att_mma": 1 = fast modes run the attention on the tensor cores (att_mma.cu), 0 = fp32 kernel
   int front_fp32 = 0;  // option "front_fp32": 1 = the front end stays on the fp32 back-end in every mode
   int debug_stop = 0;  // tests: 1 embed, 2 qkv of layer 0, 3 attention of layer 0, 4 first LayerNorm, 5 layer 0 done,
@@ -230,6 +245,10 @@ struct SynWs {
   float *phone, *x, *qkv, *att, *tmp, *h1, *stats, *xf, *hh, *a, *acts, *outacc, *g, *condB, *z_nct;
   // 16-bit operand copies for the tensor-core front end (mode != 0), same blocked-8 layout
   uint16_t *x16, *att16, *h116, *xf16, *hh16, *acts16, *out16, *qkv16;
+  // fixed places for the inputs of the graphed front end
+  float *in_phone, *in_nzp;
+  int32_t* in_len;
+  int64_t *in_pitch, *in_sid;
   size_t bytes;
 };
 
@@ -263,6 +282,11 @@ SynWs carve_syn(const rvcsyn_handle* h, void* base, int B, int T) {
   w.acts16 = (uint16_t*)take((size_t)B * H * Lp * 2);
   w.out16 = (uint16_t*)take((size_t)B * H * Lp * 2);
   w.qkv16 = (uint16_t*)take((size_t)B * 3 * H * Lp * 2);
+  w.in_phone = take((size_t)B * T * c.text_dim * 4);
+  w.in_nzp = take((size_t)B * I * T * 4);
+  w.in_len = (int32_t*)take((size_t)B * 4);
+  w.in_pitch = (int64_t*)take((size_t)B * T * 8);
+  w.in_sid = (int64_t*)take((size_t)B * 8);
   w.bytes = off;
   return w;
 }
@@ -349,6 +373,8 @@ void rvcsyn_destroy(rvcsyn_handle* h) {
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) == cudaSuccess && h->device < ndev) {
     DevGuard dg(h->device);
+    for (auto& e : h->graphs) cudaGraphExecDestroy(e.exec);
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     for (void* p : h->allocs) cudaFree(p);
   }
   if (h->dec) rvcdec_destroy(h->dec);
@@ -444,6 +470,9 @@ int rvcsyn_load_weights(rvcsyn_handle* h, const rvcdec_tensor* tensors, int32_t 
   }
   DevGuard dg(h->device);
   SCK(dg.err);
+  for (auto& e : h->graphs) cudaGraphExecDestroy(e.exec);  // they hold the old weight pointers
+  h->graphs.clear();
+  ++h->epoch;
   for (void* p : h->allocs) cudaFree(p);
   h->allocs.clear();
   if ((rc = up_conv(h, h->emb_phone)) || (rc = up_conv(h, h->proj)) || (rc = up(h, h->emb_pitch, &h->d_emb_pitch)) ||
@@ -484,8 +513,11 @@ size_t rvcsyn_workspace_bytes(const rvcsyn_handle* h, int32_t B, int32_t T, int3
 int rvcsyn_set_option(rvcsyn_handle* h, const char* key, int64_t value) {
   if (!h || !key) return sfail(RVCDEC_ERR_ARG, "null argument");
   const std::string k = key;
+  ++h->epoch;  // a cached graph was captured under the old options
   if (k == "front_fp32") { h->front_fp32 = value ? 1 : 0; return RVCDEC_OK; }
   if (k == "att_mma") { h->att_mma = value ? 1 : 0; return RVCDEC_OK; }
+  if (k == "graphs") { h->use_graphs = value ? 1 : 0; return RVCDEC_OK; }
+  if (k == "graph_max_frames") { h->graph_max_frames = value; return RVCDEC_OK; }
   return sfail(RVCDEC_ERR_ARG, "unknown option '%s'", key);
 }
 
@@ -542,141 +574,203 @@ int rvcsyn_infer(rvcsyn_handle* h, const float* phone, const int32_t* lengths, c
   const int NL = c.flow_layers;
   h->launches = 0;
   int rc;
-  // mode != 0: every convolution but the phone embedding runs on the tensor-core back-end from 16-bit operand copies
-  // (fp16; bf16 in mode 3) with fp32 accumulation, bias, residual and LayerNorm; attention, gate and z_p stay fp32
-  const bool fast = mode != 0 && !h->front_fp32;
-  const int ff = (mode == 3) ? ACT_BF16 : ACT_F16;
-  // y = conv(x): fp32 back-end from `in32`, or tensor cores from `in16`
-  auto conv = [&](const FConv& L, const float* in32, const void* in16, int phys, const Epilogue& e) -> int {
-    return fast ? mconv(h, L, in16, ff, phys, B, T, e, s) : fconv(h, L, in32, phys, B, T, e, s);
-  };
-  // x * x_mask behind a tensor-core convolution
-  auto mask = [&](float* x32, int phys32, void* x16, int phys16, int C) -> int {
-    if (!fast) return 0;
-    SCK(launch_mask_rows(x32, phys32, x16, phys16, lengths, B, T, C, Lp, s)); ++h->launches;
+  const int stop0 = h->debug_stop;
+  // Everything in front of the decoder as one launch sequence on stream `s`, reading the inputs through the pointers given
+  // (the caller's, or the workspace copies the CUDA-graph path replays on).
+  auto front = [&](const float* phone, const int32_t* lengths, const int64_t* pitch, const int64_t* sid, const float* noise_zp,
+                   cudaStream_t s) -> int {
+    // mode != 0: every convolution but the phone embedding runs on the tensor-core back-end from 16-bit operand copies
+    // (fp16; bf16 in mode 3) with fp32 accumulation, bias, residual and LayerNorm; attention, gate and z_p stay fp32
+    const bool fast = mode != 0 && !h->front_fp32;
+    const int ff = (mode == 3) ? ACT_BF16 : ACT_F16;
+    // y = conv(x): fp32 back-end from `in32`, or tensor cores from `in16`
+    auto conv = [&](const FConv& L, const float* in32, const void* in16, int phys, const Epilogue& e) -> int {
+      return fast ? mconv(h, L, in16, ff, phys, B, T, e, s) : fconv(h, L, in32, phys, B, T, e, s);
+    };
+    // x * x_mask behind a tensor-core convolution
+    auto mask = [&](float* x32, int phys32, void* x16, int phys16, int C) -> int {
+      if (!fast) return 0;
+      SCK(launch_mask_rows(x32, phys32, x16, phys16, lengths, B, T, C, Lp, s)); ++h->launches;
+      return 0;
+    };
+    // zero padding rows of every tensor a convolution with taps reads (FFN k = 3, WaveNet k = 5)
+    SCK(launch_zero_pads(w.x, w.hh, nullptr, 4, B, H, T, Lp, s)); ++h->launches;
+    SCK(launch_zero_pads(w.h1, nullptr, nullptr, 4, B, F, T, Lp, s)); ++h->launches;
+    const bool att_tc = fast && h->att_mma;
+    if (att_tc) { SCK(launch_zero_pads(w.qkv16, nullptr, nullptr, 2, B, 3 * H, T, Lp, s)); ++h->launches; }  // key / value tiles run past T
+    if (fast) {
+      SCK(launch_zero_pads(w.x16, w.hh16, nullptr, 2, B, H, T, Lp, s)); ++h->launches;
+      SCK(launch_zero_pads(w.h116, nullptr, nullptr, 2, B, F, T, Lp, s)); ++h->launches;
+    }
+    // g = emb_g(sid)  (synthesizers.py:226)
+    SCK(launch_gather_rows(h->d_emb_g, (const long long*)sid, w.g, B, c.gin_channels, c.spk_embed_dim, s)); ++h->launches;
+    // ---- TextEncoder (encoders.py:127-144) ----
+    SCK(launch_pack_btc(phone, w.phone, B, T, c.text_dim, Lp, s)); ++h->launches;
+    {
+      Epilogue e = epi_basic(h->emb_phone.d_bias, H, T, nullptr);
+      e.out_f32 = w.x;
+      if ((rc = fconv(h, h->emb_phone, w.phone, 0, B, T, e, s))) return rc;
+    }
+    SCK(launch_embed_post(w.x, c.use_f0 ? (const long long*)pitch : nullptr, h->d_emb_pitch, lengths, B, T, H, Lp, sqrtf((float)H),
+                          fast ? w.x16 : nullptr, ff, s)); ++h->launches;
+    const int stop = h->debug_stop;
+    if (stop == 1) return 0;
+    for (int l = 0; l < c.n_layers; ++l) {
+      const AttnLayer& A = h->attn[l];
+      {  // q | k | v
+        Epilogue e = epi_basic(A.qkv.d_bias, 3 * H, T, nullptr);
+        e.out_f32 = w.qkv;
+        if (att_tc) {  // the tensor-core attention reads q | k | v as 16-bit operand tiles
+          e.out_act = w.qkv16; e.act_fmt = ff; e.slope = 1.f;
+          if (stop != 2) e.out_f32 = nullptr;
+        }
+        if ((rc = conv(A.qkv, w.x, w.x16, 0, e))) return rc;
+      }
+      if (stop == 2 && l == 0) return 0;
+      if (att_tc) {
+        const uint8_t* rel = A.d_rel16[ff == ACT_BF16 ? 1 : 0];
+        SCK(launch_attention_mma(w.qkv16, w.att, w.att16, rel, rel + att_mma_rel_bytes(), lengths, B, T, c.n_heads, H / c.n_heads, c.window_size,
+                                 Lp, ff, s)); ++h->launches;
+      } else {
+        SCK(launch_attention(w.qkv, w.att, A.d_ek, A.d_ev, lengths, B, T, c.n_heads, H / c.n_heads, c.window_size, Lp, s)); ++h->launches;
+        if (fast) { SCK(launch_cast16(w.att, w.att16, ff, B, T, H, Lp, s)); ++h->launches; }
+      }
+      if (stop == 3 && l == 0) return 0;
+      {  // x + conv_o(att)  -> LayerNorm  (encoders.py:77-79)
+        Epilogue e = epi_basic(A.o.d_bias, H, T, nullptr);
+        e.res = w.x; e.out_f32 = w.tmp;
+        if ((rc = conv(A.o, w.att, w.att16, 0, e))) return rc;
+      }
+      SCK(launch_layernorm(w.tmp, w.x, A.d_g1, A.d_b1, lengths, B, T, H, Lp, 1e-5f, fast ? w.x16 : nullptr, ff, s)); ++h->launches;
+      if (stop == 4 && l == 0) return 0;
+      {  // FFN: conv_1 -> relu -> mask  (attentions.py:221-224); x is masked already
+        Epilogue e = epi_basic(A.ffn1.d_bias, F, T, lengths);
+        e.slope = 0.f;
+        if (fast) { e.out_act = w.h116; e.act_fmt = ff; } else e.out_act = w.h1;
+        if ((rc = conv(A.ffn1, w.x, w.x16, 0, e)) || (rc = mask(nullptr, 0, w.h116, 0, F))) return rc;
+      }
+      {  // x + conv_2(...) * mask -> LayerNorm  (:225-226, encoders.py:81-83)
+        Epilogue e = epi_basic(A.ffn2.d_bias, H, T, nullptr);
+        e.res = w.x; e.out_f32 = w.tmp;
+        // (rows beyond the length: conv_2 * mask = 0 and x = 0 there, and the LayerNorm below zeroes them anyway)
+        if ((rc = conv(A.ffn2, w.h1, w.h116, 0, e))) return rc;
+      }
+      SCK(launch_layernorm(w.tmp, w.x, A.d_g2, A.d_b2, lengths, B, T, H, Lp, 1e-5f, fast ? w.x16 : nullptr, ff, s)); ++h->launches;
+      if (stop == 5 && l == 0) return 0;
+    }
+    {  // stats = proj(x) * mask  (encoders.py:141)
+      Epilogue e = epi_basic(h->proj.d_bias, 2 * I, T, lengths);
+      e.out_f32 = w.stats;
+      if ((rc = conv(h->proj, w.x, w.x16, 0, e)) || (rc = mask(w.stats, 0, nullptr, 0, 2 * I))) return rc;
+    }
+    if (stop == 6) return 0;
+    // z_p = (m_p + exp(logs_p) * randn * 0.66666) * mask  (synthesizers.py:228)
+    SCK(launch_zp(w.stats, noise_zp, w.xf, lengths, seed, 0, B, T, I, Lp, fast ? w.xf16 : nullptr, ff, s)); ++h->launches;
+    if (stop == 7) return 0;
+    // ---- flow(reverse=True) (residuals.py:162-165) ----
+    const size_t half_off = (size_t)(half / 8) * Lp * 8;  // element offset of the upper channel half inside an item
+    for (int i = c.n_flows - 1; i >= 0; --i) {
+      const FlowLayer& Fl = h->flow[i];
+      const size_t o0 = Fl.flipped ? half_off : 0, o1 = Fl.flipped ? 0 : half_off;
+      const float* x0 = w.xf + o0;   // the half the layer conditions on
+      float* x1 = w.xf + o1;         // the half it updates
+      {  // h = pre(x0) * mask
+        Epilogue e = epi_basic(Fl.pre.d_bias, H, T, lengths);
+        e.out_f32 = w.hh;
+        if (fast) { e.out_act = w.hh16; e.act_fmt = ff; e.slope = 1.f; }
+        if ((rc = conv(Fl.pre, x0, w.xf16 + o0, I / 8, e)) || (rc = mask(w.hh, 0, w.hh16, 0, H))) return rc;
+      }
+      // WaveNet (modules.py:84-117): per-item bias = in_layer bias + cond_layer(g) slice
+      SCK(launch_cond(c.gin_channels ? w.g : nullptr, Fl.d_cond_w, Fl.d_cond_b, Fl.d_in_bias_all, w.condB, B, c.gin_channels, 2 * H * NL, s)); ++h->launches;
+      for (int l = 0; l < NL; ++l) {
+        {
+          Epilogue e = epi_basic(w.condB + (size_t)l * 2 * H, 2 * H, T, nullptr);
+          e.bias_bstride = 2 * H * NL;
+          e.out_f32 = w.a;
+          if ((rc = conv(Fl.in[l], w.hh, w.hh16, 0, e))) return rc;
+        }
+        SCK(launch_gate(w.a, w.acts, B, T, H, Lp, fast ? w.acts16 : nullptr, ff, s)); ++h->launches;
+        {  // output += skip part
+          Epilogue e = epi_basic(Fl.skip[l].d_bias, H, T, nullptr);
+          e.res = (l == 0) ? nullptr : w.outacc; e.out_f32 = w.outacc;
+          if (fast && l == NL - 1) { e.out_act = w.out16; e.act_fmt = ff; e.slope = 1.f; }
+          if ((rc = conv(Fl.skip[l], w.acts, w.acts16, 0, e))) return rc;
+        }
+        if (l < NL - 1) {  // x = (x + res part) * mask
+          Epilogue e = epi_basic(Fl.res[l].d_bias, H, T, lengths);
+          e.res = w.hh; e.out_f32 = w.hh;
+          if (fast) { e.out_act = w.hh16; e.act_fmt = ff; e.slope = 1.f; }
+          if ((rc = conv(Fl.res[l], w.acts, w.acts16, 0, e)) || (rc = mask(w.hh, 0, w.hh16, 0, H))) return rc;
+        }
+      }
+      {  // x1 = (x1 - post(output * mask)) * mask   (mean-only coupling, reverse; residuals.py:239-255)
+        Epilogue e = epi_basic(Fl.post.d_bias, I, T, lengths);
+        e.scale = -1.f; e.sum_in = x1; e.out_f32 = x1;
+        if (fast) { e.out_act = w.xf16 + o1; e.act_fmt = ff; e.slope = 1.f; }
+        if ((rc = conv(Fl.post, w.outacc, w.out16, 0, e)) || (rc = mask(x1, I / 8, w.xf16 + o1, I / 8, half))) return rc;
+      }
+      if (stop == 8 && i == c.n_flows - 1) return 0;
+    }
+    if (stop == 9) return 0;
+    // z * mask -> (B, inter, T) fp32 for the decoder (and the caller, if asked for)
+    SCK(launch_unpack(w.xf, ACT_F32, w.z_nct, B, I, T, Lp, s)); ++h->launches;
     return 0;
   };
-  // zero padding rows of every tensor a convolution with taps reads (FFN k = 3, WaveNet k = 5)
-  SCK(launch_zero_pads(w.x, w.hh, nullptr, 4, B, H, T, Lp, s)); ++h->launches;
-  SCK(launch_zero_pads(w.h1, nullptr, nullptr, 4, B, F, T, Lp, s)); ++h->launches;
-  const bool att_tc = fast && h->att_mma;
-  if (att_tc) { SCK(launch_zero_pads(w.qkv16, nullptr, nullptr, 2, B, 3 * H, T, Lp, s)); ++h->launches; }  // key / value tiles run past T
-  if (fast) {
-    SCK(launch_zero_pads(w.x16, w.hh16, nullptr, 2, B, H, T, Lp, s)); ++h->launches;
-    SCK(launch_zero_pads(w.h116, nullptr, nullptr, 2, B, F, T, Lp, s)); ++h->launches;
-  }
-  // g = emb_g(sid)  (synthesizers.py:226)
-  SCK(launch_gather_rows(h->d_emb_g, (const long long*)sid, w.g, B, c.gin_channels, c.spk_embed_dim, s)); ++h->launches;
-  // ---- TextEncoder (encoders.py:127-144) ----
-  SCK(launch_pack_btc(phone, w.phone, B, T, c.text_dim, Lp, s)); ++h->launches;
-  {
-    Epilogue e = epi_basic(h->emb_phone.d_bias, H, T, nullptr);
-    e.out_f32 = w.x;
-    if ((rc = fconv(h, h->emb_phone, w.phone, 0, B, T, e, s))) return rc;
-  }
-  SCK(launch_embed_post(w.x, c.use_f0 ? (const long long*)pitch : nullptr, h->d_emb_pitch, lengths, B, T, H, Lp, sqrtf((float)H),
-                        fast ? w.x16 : nullptr, ff, s)); ++h->launches;
-  const int stop = h->debug_stop;
-  if (stop == 1) return 0;
-  for (int l = 0; l < c.n_layers; ++l) {
-    const AttnLayer& A = h->attn[l];
-    {  // q | k | v
-      Epilogue e = epi_basic(A.qkv.d_bias, 3 * H, T, nullptr);
-      e.out_f32 = w.qkv;
-      if (att_tc) {  // the tensor-core attention reads q | k | v as 16-bit operand tiles
-        e.out_act = w.qkv16; e.act_fmt = ff; e.slope = 1.f;
-        if (stop != 2) e.out_f32 = nullptr;
+  // Small batches are launch-bound here (~130 launches of a few microseconds of work each: 2.2 ms at B = 1 whatever T), so
+  // their sequence is captured once per (workspace, B, T, mode) and replayed as a CUDA graph; the inputs are first copied
+  // to fixed places in the workspace so that one graph serves every call.  Large batches, debug stops and in-kernel z_p
+  // draws (the seed is a kernel argument) launch directly.
+  const bool graphable = h->use_graphs && stop0 == 0 && noise_zp != nullptr && (int64_t)B * T <= h->graph_max_frames;
+  if (!graphable) {
+    if ((rc = front(phone, lengths, pitch, sid, noise_zp, s))) return rc;
+    if (stop0) return 0;
+  } else {
+    SCK(cudaMemcpyAsync(w.in_phone, phone, (size_t)B * T * c.text_dim * 4, cudaMemcpyDeviceToDevice, s));
+    SCK(cudaMemcpyAsync(w.in_len, lengths, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
+    if (pitch) SCK(cudaMemcpyAsync(w.in_pitch, pitch, (size_t)B * T * 8, cudaMemcpyDeviceToDevice, s));
+    SCK(cudaMemcpyAsync(w.in_sid, sid, (size_t)B * 8, cudaMemcpyDeviceToDevice, s));
+    SCK(cudaMemcpyAsync(w.in_nzp, noise_zp, (size_t)B * I * T * 4, cudaMemcpyDeviceToDevice, s));
+    rvcsyn_handle::GraphEntry* hit = nullptr;
+    for (auto& e : h->graphs)
+      if (e.ws == workspace && e.B == B && e.T == T && e.mode == mode && e.has_pitch == (pitch != nullptr) && e.epoch == h->epoch) { hit = &e; break; }
+    if (!hit) {
+      if (!h->cap_stream) SCK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+      cudaGraph_t graph = nullptr;
+      cudaError_t ce = cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeRelaxed);
+      int frc = 0;
+      if (ce == cudaSuccess) {
+        frc = front(w.in_phone, w.in_len, pitch ? w.in_pitch : nullptr, w.in_sid, w.in_nzp, h->cap_stream);
+        ce = cudaStreamEndCapture(h->cap_stream, &graph);
       }
-      if ((rc = conv(A.qkv, w.x, w.x16, 0, e))) return rc;
-    }
-    if (stop == 2 && l == 0) return 0;
-    if (att_tc) {
-      const uint8_t* rel = A.d_rel16[ff == ACT_BF16 ? 1 : 0];
-      SCK(launch_attention_mma(w.qkv16, w.att, w.att16, rel, rel + att_mma_rel_bytes(), lengths, B, T, c.n_heads, H / c.n_heads, c.window_size,
-                               Lp, ff, s)); ++h->launches;
+      cudaGraphExec_t exec = nullptr;
+      if (frc == 0 && ce == cudaSuccess && graph) ce = cudaGraphInstantiate(&exec, graph, 0);
+      if (graph) cudaGraphDestroy(graph);
+      if (frc != 0 || ce != cudaSuccess || !exec) {  // capture is an optimisation: direct launches from now on
+        (void)cudaGetLastError();
+        h->use_graphs = 0;
+        h->launches = 0;
+        if (frc) return frc;
+        if ((rc = front(phone, lengths, pitch, sid, noise_zp, s))) return rc;
+      } else {
+        if (h->graphs.size() >= 8) {  // LRU
+          size_t victim = 0;
+          for (size_t i = 1; i < h->graphs.size(); ++i) if (h->graphs[i].last_use < h->graphs[victim].last_use) victim = i;
+          cudaGraphExecDestroy(h->graphs[victim].exec);
+          h->graphs.erase(h->graphs.begin() + victim);
+        }
+        h->graphs.push_back({workspace, B, T, mode, pitch != nullptr, h->epoch, exec, h->launches, 0});
+        hit = &h->graphs.back();
+        ++h->graph_captures;
+      }
     } else {
-      SCK(launch_attention(w.qkv, w.att, A.d_ek, A.d_ev, lengths, B, T, c.n_heads, H / c.n_heads, c.window_size, Lp, s)); ++h->launches;
-      if (fast) { SCK(launch_cast16(w.att, w.att16, ff, B, T, H, Lp, s)); ++h->launches; }
+      ++h->graph_hits;
     }
-    if (stop == 3 && l == 0) return 0;
-    {  // x + conv_o(att)  -> LayerNorm  (encoders.py:77-79)
-      Epilogue e = epi_basic(A.o.d_bias, H, T, nullptr);
-      e.res = w.x; e.out_f32 = w.tmp;
-      if ((rc = conv(A.o, w.att, w.att16, 0, e))) return rc;
+    if (hit) {
+      hit->last_use = ++h->graph_clock;
+      SCK(cudaGraphLaunch(hit->exec, s));
+      h->launches = hit->launches + 1;
     }
-    SCK(launch_layernorm(w.tmp, w.x, A.d_g1, A.d_b1, lengths, B, T, H, Lp, 1e-5f, fast ? w.x16 : nullptr, ff, s)); ++h->launches;
-    if (stop == 4 && l == 0) return 0;
-    {  // FFN: conv_1 -> relu -> mask  (attentions.py:221-224); x is masked already
-      Epilogue e = epi_basic(A.ffn1.d_bias, F, T, lengths);
-      e.slope = 0.f;
-      if (fast) { e.out_act = w.h116; e.act_fmt = ff; } else e.out_act = w.h1;
-      if ((rc = conv(A.ffn1, w.x, w.x16, 0, e)) || (rc = mask(nullptr, 0, w.h116, 0, F))) return rc;
-    }
-    {  // x + conv_2(...) * mask -> LayerNorm  (:225-226, encoders.py:81-83)
-      Epilogue e = epi_basic(A.ffn2.d_bias, H, T, nullptr);
-      e.res = w.x; e.out_f32 = w.tmp;
-      // (rows beyond the length: conv_2 * mask = 0 and x = 0 there, and the LayerNorm below zeroes them anyway)
-      if ((rc = conv(A.ffn2, w.h1, w.h116, 0, e))) return rc;
-    }
-    SCK(launch_layernorm(w.tmp, w.x, A.d_g2, A.d_b2, lengths, B, T, H, Lp, 1e-5f, fast ? w.x16 : nullptr, ff, s)); ++h->launches;
-    if (stop == 5 && l == 0) return 0;
   }
-  {  // stats = proj(x) * mask  (encoders.py:141)
-    Epilogue e = epi_basic(h->proj.d_bias, 2 * I, T, lengths);
-    e.out_f32 = w.stats;
-    if ((rc = conv(h->proj, w.x, w.x16, 0, e)) || (rc = mask(w.stats, 0, nullptr, 0, 2 * I))) return rc;
-  }
-  if (stop == 6) return 0;
-  // z_p = (m_p + exp(logs_p) * randn * 0.66666) * mask  (synthesizers.py:228)
-  SCK(launch_zp(w.stats, noise_zp, w.xf, lengths, seed, 0, B, T, I, Lp, fast ? w.xf16 : nullptr, ff, s)); ++h->launches;
-  if (stop == 7) return 0;
-  // ---- flow(reverse=True) (residuals.py:162-165) ----
-  const size_t half_off = (size_t)(half / 8) * Lp * 8;  // element offset of the upper channel half inside an item
-  for (int i = c.n_flows - 1; i >= 0; --i) {
-    const FlowLayer& Fl = h->flow[i];
-    const size_t o0 = Fl.flipped ? half_off : 0, o1 = Fl.flipped ? 0 : half_off;
-    const float* x0 = w.xf + o0;   // the half the layer conditions on
-    float* x1 = w.xf + o1;         // the half it updates
-    {  // h = pre(x0) * mask
-      Epilogue e = epi_basic(Fl.pre.d_bias, H, T, lengths);
-      e.out_f32 = w.hh;
-      if (fast) { e.out_act = w.hh16; e.act_fmt = ff; e.slope = 1.f; }
-      if ((rc = conv(Fl.pre, x0, w.xf16 + o0, I / 8, e)) || (rc = mask(w.hh, 0, w.hh16, 0, H))) return rc;
-    }
-    // WaveNet (modules.py:84-117): per-item bias = in_layer bias + cond_layer(g) slice
-    SCK(launch_cond(c.gin_channels ? w.g : nullptr, Fl.d_cond_w, Fl.d_cond_b, Fl.d_in_bias_all, w.condB, B, c.gin_channels, 2 * H * NL, s)); ++h->launches;
-    for (int l = 0; l < NL; ++l) {
-      {
-        Epilogue e = epi_basic(w.condB + (size_t)l * 2 * H, 2 * H, T, nullptr);
-        e.bias_bstride = 2 * H * NL;
-        e.out_f32 = w.a;
-        if ((rc = conv(Fl.in[l], w.hh, w.hh16, 0, e))) return rc;
-      }
-      SCK(launch_gate(w.a, w.acts, B, T, H, Lp, fast ? w.acts16 : nullptr, ff, s)); ++h->launches;
-      {  // output += skip part
-        Epilogue e = epi_basic(Fl.skip[l].d_bias, H, T, nullptr);
-        e.res = (l == 0) ? nullptr : w.outacc; e.out_f32 = w.outacc;
-        if (fast && l == NL - 1) { e.out_act = w.out16; e.act_fmt = ff; e.slope = 1.f; }
-        if ((rc = conv(Fl.skip[l], w.acts, w.acts16, 0, e))) return rc;
-      }
-      if (l < NL - 1) {  // x = (x + res part) * mask
-        Epilogue e = epi_basic(Fl.res[l].d_bias, H, T, lengths);
-        e.res = w.hh; e.out_f32 = w.hh;
-        if (fast) { e.out_act = w.hh16; e.act_fmt = ff; e.slope = 1.f; }
-        if ((rc = conv(Fl.res[l], w.acts, w.acts16, 0, e)) || (rc = mask(w.hh, 0, w.hh16, 0, H))) return rc;
-      }
-    }
-    {  // x1 = (x1 - post(output * mask)) * mask   (mean-only coupling, reverse; residuals.py:239-255)
-      Epilogue e = epi_basic(Fl.post.d_bias, I, T, lengths);
-      e.scale = -1.f; e.sum_in = x1; e.out_f32 = x1;
-      if (fast) { e.out_act = w.xf16 + o1; e.act_fmt = ff; e.slope = 1.f; }
-      if ((rc = conv(Fl.post, w.outacc, w.out16, 0, e)) || (rc = mask(x1, I / 8, w.xf16 + o1, I / 8, half))) return rc;
-    }
-    if (stop == 8 && i == c.n_flows - 1) return 0;
-  }
-  if (stop == 9) return 0;
-  // z * mask -> (B, inter, T) fp32 for the decoder (and the caller, if asked for)
-  SCK(launch_unpack(w.xf, ACT_F32, w.z_nct, B, I, T, Lp, s)); ++h->launches;
   if (z_out) SCK(cudaMemcpyAsync(z_out, w.z_nct, (size_t)B * I * T * 4, cudaMemcpyDeviceToDevice, s));
   if (!h->dec) return 0;
   rc = rvcdec_forward(h->dec, w.z_nct, nsff0, c.gin_channels ? w.g : nullptr, noise_src, seed, out, dec_ws,

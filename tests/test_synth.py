@@ -310,3 +310,51 @@ def test_tensor_core_attention_against_the_fp32_kernel(B, T, lens):
     assert max(e_kernel) <= 5e-4, e_kernel
     assert max(e_round) <= 8e-2, e_round
     assert rel_z <= 1e-2, rel_z
+
+
+@pytest.mark.gpu
+def test_front_end_graph_replay_is_bit_identical_to_direct_launches():
+    """rvcsyn_set_option("graphs"): small batches copy their inputs to fixed workspace places and replay the front end's launch
+    sequence as a CUDA graph.  Capture call, replay call with OTHER inputs in other tensors, and direct launches agree bit
+    for bit, in fp32 and fast mode; a changed option invalidates the graph."""
+    import rvc_b200
+
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(80)
+    m = rvc_b200.Synthesizer(*SYN_48K, use_f0=1, text_enc_hidden_dim=768, vocoder="HiFi-GAN").eval().to(dev)
+    B, T = 2, 150
+    h = m._ensure_handle(dev)
+
+    def inputs(seed):
+        gen = torch.Generator().manual_seed(seed)
+        return dict(phone=torch.randn(B, T, 768, generator=gen).to(dev), lens=torch.tensor([150, 77]).to(dev),
+                    pitch=torch.randint(1, 256, (B, T), generator=gen).to(dev), f0=O.synth_f0(B, T, gen).to(dev),
+                    sid=torch.tensor([3, 100]).to(dev), nzp=torch.randn(B, 192, T, generator=gen).to(dev),
+                    nsrc=torch.randn(B, T * 480, generator=gen).to(dev))
+
+    def run(i, mode):
+        o, _, (z, _, _, _) = m.infer(i["phone"], i["lens"], i["pitch"], i["f0"], i["sid"], noise_zp=i["nzp"], noise_src=i["nsrc"], mode=mode)
+        return o.clone(), z.clone()
+
+    a, b = inputs(1), inputs(2)
+    for mode in ("fp32", "fast"):
+        h.set_option("graphs", 1)
+        oa1, za1 = run(a, mode)   # capture
+        ob1, zb1 = run(b, mode)   # replay on other inputs
+        oa2, za2 = run(a, mode)
+        n_graph = m.last_launch_count
+        h.set_option("graphs", 0)
+        oa0, za0 = run(a, mode)
+        ob0, zb0 = run(b, mode)
+        n_direct = m.last_launch_count
+        assert torch.equal(za1, za0) and torch.equal(za2, za0) and torch.equal(zb1, zb0)
+        assert torch.equal(oa1, oa0) and torch.equal(ob1, ob0)
+        assert not torch.equal(za0, zb0)
+        assert n_graph == n_direct + 1, (n_graph, n_direct)
+    h.set_option("graphs", 1)
+    _, z1 = run(a, "fast")
+    h.set_option("att_mma", 0)  # another kernel sequence: the cached graph must not be replayed
+    _, z2 = run(a, "fast")
+    h.set_option("att_mma", 1)
+    _, z3 = run(a, "fast")
+    assert torch.equal(z1, z3) and not torch.equal(z1, z2)
