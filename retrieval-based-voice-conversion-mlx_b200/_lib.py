@@ -73,6 +73,8 @@ EXPORTS = [
     # include/rvcrefine.h
     "rvcrefine_create", "rvcrefine_load_weights", "rvcrefine_workspace_bytes", "rvcrefine_forward", "rvcrefine_noise_floats",
     "rvcrefine_last_launch_count", "rvcrefine_destroy", "rvcrefine_last_error",
+    "rvcrmvpe_create", "rvcrmvpe_load_weights", "rvcrmvpe_mel_workspace_bytes", "rvcrmvpe_mel", "rvcrmvpe_workspace_bytes", "rvcrmvpe_forward",
+    "rvcrmvpe_decode", "rvcrmvpe_debug_read", "rvcrmvpe_last_launch_count", "rvcrmvpe_destroy", "rvcrmvpe_last_error",
 ]
 
 _lib = None
@@ -161,6 +163,28 @@ def lib() -> C.CDLL:
     L.rvcrefine_destroy.restype = None
     L.rvcrefine_last_error.argtypes = []
     L.rvcrefine_last_error.restype = C.c_char_p
+    L.rvcrmvpe_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.rvcrmvpe_create.restype = C.c_int
+    L.rvcrmvpe_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]
+    L.rvcrmvpe_load_weights.restype = C.c_int
+    L.rvcrmvpe_mel_workspace_bytes.argtypes = [vp, i32, i32]
+    L.rvcrmvpe_mel_workspace_bytes.restype = sz
+    L.rvcrmvpe_mel.argtypes = [vp, vp, vp, vp, sz, i32, i32, vp]
+    L.rvcrmvpe_mel.restype = C.c_int
+    L.rvcrmvpe_workspace_bytes.argtypes = [vp, i32, i32]
+    L.rvcrmvpe_workspace_bytes.restype = sz
+    L.rvcrmvpe_forward.argtypes = [vp, vp, vp, vp, sz, i32, i32, vp]
+    L.rvcrmvpe_forward.restype = C.c_int
+    L.rvcrmvpe_decode.argtypes = [vp, vp, C.c_float, vp, i32, vp]
+    L.rvcrmvpe_decode.restype = C.c_int
+    L.rvcrmvpe_debug_read.argtypes = [vp, C.c_char_p, vp, i64, vp, i32, i32, vp]
+    L.rvcrmvpe_debug_read.restype = i64
+    L.rvcrmvpe_last_launch_count.argtypes = [vp]
+    L.rvcrmvpe_last_launch_count.restype = i64
+    L.rvcrmvpe_destroy.argtypes = [vp]
+    L.rvcrmvpe_destroy.restype = None
+    L.rvcrmvpe_last_error.argtypes = []
+    L.rvcrmvpe_last_error.restype = C.c_char_p
     L.rvcsyn_create.argtypes = [C.POINTER(SynConfig), C.c_int, C.POINTER(vp)]
     L.rvcsyn_create.restype = C.c_int
     L.rvcsyn_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]
@@ -413,6 +437,58 @@ class Handle:
     def close(self) -> None:
         if self._h:
             lib().rvcdec_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class RmvpeHandle:
+    """Owns one rvcrmvpe_handle (the RMVPE f0 predictor; include/rvcrmvpe.h)."""
+
+    def __init__(self, device: int):
+        self._h = C.c_void_p()
+        self._check(lib().rvcrmvpe_create(int(device), C.byref(self._h)), "rvcrmvpe_create")
+        self.device = int(device)
+
+    @staticmethod
+    def _check(rc: int, what: str) -> None:
+        if rc < 0:
+            raise RuntimeError(f"{what} failed ({rc}): {(lib().rvcrmvpe_last_error() or b'').decode()}")
+
+    def load_weights(self, state: Dict[str, "object"]) -> None:
+        arr, keep = Handle._tensor_array(None, state)
+        self._check(lib().rvcrmvpe_load_weights(self._h, arr, len(state)), "rvcrmvpe_load_weights")
+
+    def workspace_bytes(self, B: int, T: int) -> int:
+        return int(lib().rvcrmvpe_workspace_bytes(self._h, B, T))
+
+    def mel_workspace_bytes(self, B: int, n: int) -> int:
+        return int(lib().rvcrmvpe_mel_workspace_bytes(self._h, B, n))
+
+    def forward(self, mel, hidden, workspace, B, T, stream) -> None:
+        self._check(lib().rvcrmvpe_forward(self._h, mel, hidden, workspace.data_ptr(), workspace.numel(), B, T, stream), "rvcrmvpe_forward")
+
+    def mel(self, audio, mel, workspace, B, n, stream) -> None:
+        self._check(lib().rvcrmvpe_mel(self._h, audio, mel, workspace.data_ptr(), workspace.numel(), B, n, stream), "rvcrmvpe_mel")
+
+    def decode(self, hidden, thred, f0, T, stream) -> None:
+        self._check(lib().rvcrmvpe_decode(self._h, hidden, C.c_float(thred), f0, T, stream), "rvcrmvpe_decode")
+
+    def debug_read(self, name: str, dst, workspace, B: int, T: int, stream) -> int:
+        n = lib().rvcrmvpe_debug_read(self._h, name.encode(), dst.data_ptr(), dst.numel(), workspace.data_ptr(), B, T, stream)
+        self._check(n, "rvcrmvpe_debug_read")
+        return int(n)
+
+    def launch_count(self) -> int:
+        return int(lib().rvcrmvpe_last_launch_count(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            lib().rvcrmvpe_destroy(self._h)
             self._h = C.c_void_p()
 
     def __del__(self):
