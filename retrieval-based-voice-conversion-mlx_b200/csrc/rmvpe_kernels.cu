@@ -40,24 +40,61 @@ __global__ void __launch_bounds__(256) conv2d_kernel(Conv2dParams p) {
   float acc[CO];
 #pragma unroll
   for (int o = 0; o < CO; ++o) acc[o] = 0.f;
+  // What a thread stages per 8-channel step does not depend on the step: (channel within the step, pixel offset) of its
+  // tile elements and the offsets of its weights are computed once (the divisions by the run-time tile shape cost more
+  // than the loads), and the NEXT step's values are fetched into registers while the current one is computed.
+  constexpr int NT = (CI * 66 * 6 + 255) / 256, NW = (CI * KS * KS * CO + 255) / 256;
+  const int n_tile = CI * sh * sw;
+  int tpix[NT];   // pixel offset inside a channel plane, -1 = zero padding / outside, -2 = no element
+  int tch[NT];
+#pragma unroll
+  for (int j = 0; j < NT; ++j) {
+    const int i = threadIdx.x + 256 * j;
+    tpix[j] = -2; tch[j] = 0;
+    if (i < n_tile) {
+      const int c = i / (sh * sw), r = i - c * sh * sw;
+      const int yy = y0 + r / sw - PADK, xx = x0 + r % sw - PADK;
+      tch[j] = c;
+      tpix[j] = (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) ? yy * p.W + xx : -1;
+    }
+  }
+  int woff[NW], wch[NW];
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const int i = threadIdx.x + 256 * j;
+    woff[j] = -1; wch[j] = 0;
+    if (i < CI * KS * KS * CO) {
+      const int o = i % CO, t = (i / CO) % (KS * KS), c = i / (CO * KS * KS);
+      wch[j] = c;
+      if (co0 + o < p.Cout) woff[j] = ((co0 + o) * p.Cin + c) * KS * KS + t;
+    }
+  }
+  const size_t plane = (size_t)p.H * p.W;
+  const float* base0 = p.in0 + (size_t)b * p.C0 * plane;
+  const float* base1 = p.in1 ? p.in1 + (size_t)b * (p.Cin - p.C0) * plane : nullptr;
+  float tv[NT], wv_[NW];
+  auto fetch = [&](int c0) {
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      const int ci = c0 + tch[j];
+      tv[j] = 0.f;
+      if (tpix[j] >= 0 && ci < p.Cin) tv[j] = __ldg((ci < p.C0 ? base0 + (size_t)ci * plane : base1 + (size_t)(ci - p.C0) * plane) + tpix[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      wv_[j] = 0.f;
+      if (woff[j] >= 0 && c0 + wch[j] < p.Cin) wv_[j] = __ldg(p.w + woff[j] + (size_t)c0 * KS * KS);
+    }
+  };
+  fetch(0);
   for (int c0 = 0; c0 < p.Cin; c0 += CI) {
     __syncthreads();
-    for (int i = threadIdx.x; i < CI * sh * sw; i += 256) {
-      const int c = i / (sh * sw), r = i - c * sh * sw;
-      const int yy = y0 + r / sw - PADK, xx = x0 + r % sw - PADK, ci = c0 + c;
-      float v = 0.f;
-      if (ci < p.Cin && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
-        const float* src = ci < p.C0 ? p.in0 + ((size_t)b * p.C0 + ci) * p.H * p.W : p.in1 + ((size_t)b * (p.Cin - p.C0) + (ci - p.C0)) * p.H * p.W;
-        v = __ldg(src + (size_t)yy * p.W + xx);
-      }
-      tile[i] = v;
-    }
-    for (int i = threadIdx.x; i < CI * KS * KS * CO; i += 256) {
-      const int o = i % CO, t = (i / CO) % (KS * KS), c = i / (CO * KS * KS);
-      const int co = co0 + o, ci = c0 + c;
-      wsm[i] = (co < p.Cout && ci < p.Cin) ? __ldg(p.w + ((size_t)co * p.Cin + ci) * KS * KS + t) : 0.f;
-    }
+#pragma unroll
+    for (int j = 0; j < NT; ++j) if (tpix[j] != -2) tile[threadIdx.x + 256 * j] = tv[j];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) if (threadIdx.x + 256 * j < CI * KS * KS * CO) wsm[threadIdx.x + 256 * j] = wv_[j];
     __syncthreads();
+    if (c0 + CI < p.Cin) fetch(c0 + CI);
 #pragma unroll 1
     for (int c = 0; c < CI; ++c) {
 #pragma unroll
@@ -283,8 +320,97 @@ __global__ void __launch_bounds__(3 * GRU_H) gru_kernel(const float* __restrict_
     __syncthreads();
   }
 }
-cudaError_t launch_gru(const float* gi, const float* whhT, const float* bhh, float* out, int B, int T, cudaStream_t s) {
+cudaError_t launch_gru_simple(const float* gi, const float* whhT, const float* bhh, float* out, int B, int T, cudaStream_t s) {
   gru_kernel<<<dim3(2, B), 3 * GRU_H, 0, s>>>(gi, whhT, bhh, out, B, T);
+  return cudaGetLastError();
+}
+
+// The same recurrence on a CLUSTER of 4 CTAs per (direction, item) with the recurrent weights resident in shared memory:
+// CTA r owns hidden units [64 r, 64 r + 64), i.e. 192 of the 768 gate rows = 192 KB of fp32 weights, kept as w[k][local row]
+// (conflict-free: a warp reads 32 consecutive rows of one k, h[k] is a broadcast).  Per step every CTA forms its 192 dot
+// products (two threads per row, halves of k), its first 64 threads apply the gates and write the new h values into the
+// h buffers of all four CTAs through distributed shared memory; one cluster barrier per step (h is double-buffered).
+// 7.5 us per step for the L2-streamed kernel above -> ~1.7 us (profiles/r2am_*).
+constexpr int GRU_CL = 4, GRU_UNITS = GRU_H / GRU_CL, GRU_ROWS = 3 * GRU_UNITS, GRU_CT = 2 * GRU_ROWS;
+constexpr int GRU_SMEM = (GRU_H * GRU_ROWS + 2 * GRU_ROWS + 2 * GRU_H) * 4;
+__global__ void __cluster_dims__(GRU_CL, 1, 1) __launch_bounds__(GRU_CT, 1)
+gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT, const float* __restrict__ bhh, float* __restrict__ out, int B, int T) {
+  extern __shared__ __align__(16) float gsm[];
+  float* wsm = gsm;                          // [k 256][row 192]
+  float* part = wsm + GRU_H * GRU_ROWS;      // [half 2][row 192]
+  float* hbuf = part + 2 * GRU_ROWS;         // [2][256]
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int dir = blockIdx.y, b = blockIdx.z, t_ = threadIdx.x;
+  const int row = t_ % GRU_ROWS, half = t_ / GRU_ROWS;
+  // local row lr = gate * 64 + u  <->  global row gate * 256 + 64 * rank + u
+  const float* wg = whhT + (size_t)dir * GRU_H * 3 * GRU_H;
+  for (int i = t_; i < GRU_H * GRU_ROWS; i += GRU_CT) {
+    const int k = i / GRU_ROWS, lr = i - k * GRU_ROWS;
+    wsm[i] = __ldg(wg + (size_t)k * 3 * GRU_H + (lr / GRU_UNITS) * GRU_H + GRU_UNITS * rank + lr % GRU_UNITS);
+  }
+  for (int i = t_; i < 2 * GRU_H; i += GRU_CT) hbuf[i] = 0.f;
+  const int u = t_, ug = GRU_UNITS * (int)rank + t_;  // gate threads: t_ < 64
+  float br = 0.f, bz = 0.f, bn = 0.f;
+  if (t_ < GRU_UNITS) {
+    const float* bb = bhh + dir * 3 * GRU_H;
+    br = bb[ug]; bz = bb[GRU_H + ug]; bn = bb[2 * GRU_H + ug];
+  }
+  // addresses of this thread's slot in the four CTAs' h buffers
+  uint32_t hdst[GRU_CL];
+  {
+    const uint32_t local = (uint32_t)__cvta_generic_to_shared(hbuf);
+#pragma unroll
+    for (int c = 0; c < GRU_CL; ++c) asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(hdst[c]) : "r"(local), "r"(c));
+  }
+  __syncthreads();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  float g_r = 0.f, g_z = 0.f, g_n = 0.f;
+  auto load_gi = [&](int step) {
+    const int t = dir ? T - 1 - step : step;
+    const float* g = gi + ((size_t)b * T + t) * 6 * GRU_H + dir * 3 * GRU_H;
+    g_r = __ldg(g + ug); g_z = __ldg(g + GRU_H + ug); g_n = __ldg(g + 2 * GRU_H + ug);
+  };
+  if (t_ < GRU_UNITS && T > 0) load_gi(0);
+  for (int step = 0; step < T; ++step) {
+    const float* h = hbuf + (step & 1) * GRU_H;
+    const float* wp = wsm + (size_t)(half * (GRU_H / 2)) * GRU_ROWS + row;
+    const float* hp = h + half * (GRU_H / 2);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll 8
+    for (int k = 0; k < GRU_H / 2; k += 4) {
+      a0 = fmaf(wp[(k + 0) * GRU_ROWS], hp[k + 0], a0);
+      a1 = fmaf(wp[(k + 1) * GRU_ROWS], hp[k + 1], a1);
+      a2 = fmaf(wp[(k + 2) * GRU_ROWS], hp[k + 2], a2);
+      a3 = fmaf(wp[(k + 3) * GRU_ROWS], hp[k + 3], a3);
+    }
+    part[half * GRU_ROWS + row] = (a0 + a1) + (a2 + a3);
+    __syncthreads();
+    if (t_ < GRU_UNITS) {
+      const float cr = g_r, cz = g_z, cn = g_n;
+      if (step + 1 < T) load_gi(step + 1);  // in flight across the barrier
+      const float hr = part[u] + part[GRU_ROWS + u] + br;
+      const float hz = part[GRU_UNITS + u] + part[GRU_ROWS + GRU_UNITS + u] + bz;
+      const float hn = part[2 * GRU_UNITS + u] + part[GRU_ROWS + 2 * GRU_UNITS + u] + bn;
+      const float r = 1.f / (1.f + expf(-(cr + hr)));
+      const float z = 1.f / (1.f + expf(-(cz + hz)));
+      const float n = tanhf(cn + r * hn);
+      const float hnew = (1.f - z) * n + z * h[ug];
+      const int t = dir ? T - 1 - step : step;
+      out[((size_t)b * T + t) * 2 * GRU_H + dir * GRU_H + ug] = hnew;
+      const uint32_t off = (uint32_t)((((step + 1) & 1) * GRU_H + ug) * 4);
+#pragma unroll
+      for (int c = 0; c < GRU_CL; ++c) asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(hdst[c] + off), "f"(hnew) : "memory");
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  }
+}
+
+cudaError_t launch_gru(const float* gi, const float* whhT, const float* bhh, float* out, int B, int T, cudaStream_t s) {
+  static unsigned long long done = 0;
+  cudaError_t e = set_smem_once(reinterpret_cast<const void*>(gru_cluster_kernel), GRU_SMEM, done);
+  if (e != cudaSuccess) return e;
+  gru_cluster_kernel<<<dim3(GRU_CL, 2, B), GRU_CT, GRU_SMEM, s>>>(gi, whhT, bhh, out, B, T);
   return cudaGetLastError();
 }
 
