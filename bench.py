@@ -331,6 +331,28 @@ def longform_leg(model, cfg, n_dev, reps=3):
             "n_devices": n_dev, "chunks": 8, "units_per_device": [s["units"] // (2 * (reps + 1)) for s in st], "best_of": reps, **out}
 
 
+def rmvpe_leg(dev, secs=60, reps=3):
+    """the RMVPE f0 predictor (rvc_b200.RMVPE0Predictor, random weights, fp32) end to end from a host numpy
+    array of 16 kHz audio to the host f0 array: H2D, mel spectrogram, U-Net + BiGRU, decode, D2H.  Wall clock."""
+    import numpy as np
+    import rvc_b200
+
+    torch.manual_seed(1)
+    p = rvc_b200.RMVPE0Predictor(None, dev)
+    p.model.to(dev)
+    n = secs * 16000
+    audio = (0.3 * np.sin(2 * np.pi * 200 * np.arange(n) / 16000) + 0.01 * np.random.default_rng(0).standard_normal(n)).astype(np.float32)
+    f0 = p.infer_from_audio(audio)
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        f0 = p.infer_from_audio(audio)
+        ts.append(time.perf_counter() - t0)
+    assert f0.shape == (1 + n // 160,) and bool(np.isfinite(f0).all())
+    return {"workload": f"RMVPE0Predictor.infer_from_audio, {secs} s of 16 kHz audio, host array -> host f0, fp32, random weights",
+            "seconds": min(ts), "audio_s_per_s": secs / min(ts), "frames": int(f0.shape[0]), "launches_model": p.model.last_launch_count}
+
+
 def synthesizer_leg(dev, B=16, T=3000, reps=3):
     """the whole net_g.infer (speaker embedding, TextEncoder, z_p sampling, reverse flow, decoder) through
     rvc_b200.Synthesizer -> rvcsyn_infer, device-resident inputs, CUDA events; fast mode (front-end convolutions and attention on the tensor cores)."""
@@ -497,7 +519,7 @@ def run_ours(args):
         roof["traffic_source"] = "scaled from the committed ncu --set full capture (not measured in this run)"
         roof["algorithmic_bytes_per_launch"] = dom["bytes"] / spans
     total_tflops = 2 * MMAC_PER_FRAME * T * B * args.steps / (ms * 1e-3) / 1e12
-    cpu = parity = synth = None
+    cpu = parity = synth = rmv = None
     if world == 1 and not args.no_cpu:
         r = cpu_reference_runs(1, 1, full=False)
         cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -508,6 +530,10 @@ def run_ours(args):
             synth = synthesizer_leg(dev)
         except Exception as e:  # noqa: BLE001
             synth = {"error": str(e)}
+        try:
+            rmv = rmvpe_leg(dev)
+        except Exception as e:  # noqa: BLE001
+            rmv = {"error": str(e)}
     line = {
         "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -529,6 +555,8 @@ def run_ours(args):
         line["longform"] = longform
     if synth:
         line["synthesizer"] = synth
+    if rmv:
+        line["rmvpe"] = rmv
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
