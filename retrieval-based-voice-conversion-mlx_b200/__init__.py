@@ -14,8 +14,10 @@ from .synthesizer import Synthesizer  # noqa: F401
 from .refinegan import RefineGANGenerator  # noqa: F401
 from .rmvpe import RMVPE0Predictor  # noqa: F401
 from . import rmvpe  # noqa: F401
+from .hubert import HubertModelWithFinalProj  # noqa: F401
+from . import hubert  # noqa: F401
 from . import runner  # noqa: F401
 from .runner import MultiGpuDecoder  # noqa: F401
 
 __all__ = ["HiFiGANGenerator", "HiFiGANMRFGenerator", "HiFiGANNSFGenerator", "ResBlock", "SourceModuleHnNSF", "chunking", "configs", "loader",
-           "load_checkpoint", "runner", "MultiGpuDecoder", "Synthesizer", "RefineGANGenerator", "RMVPE0Predictor", "rmvpe"]
+           "load_checkpoint", "runner", "MultiGpuDecoder", "Synthesizer", "RefineGANGenerator", "RMVPE0Predictor", "rmvpe", "HubertModelWithFinalProj", "hubert"]

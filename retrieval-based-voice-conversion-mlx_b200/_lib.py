@@ -59,6 +59,59 @@ class Tensor(C.Structure):
     _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64)]
 
 
+class HubertHandle:
+    """Owns one rvchubert_handle (the HuBERT / ContentVec content embedder; include/rvchubert.h)."""
+
+    def __init__(self, device: int):
+        self._h = C.c_void_p()
+        self._check(lib().rvchubert_create(int(device), C.byref(self._h)), "rvchubert_create")
+        self.device = int(device)
+
+    @staticmethod
+    def _check(rc: int, what: str) -> None:
+        if rc < 0:
+            raise RuntimeError(f"{what} failed ({rc}): {(lib().rvchubert_last_error() or b'').decode()}")
+
+    def load_weights(self, state: Dict[str, "object"]) -> None:
+        arr, keep = Handle._tensor_array(None, state)
+        self._check(lib().rvchubert_load_weights(self._h, arr, len(state)), "rvchubert_load_weights")
+
+    @staticmethod
+    def frames(n: int) -> int:
+        return int(lib().rvchubert_frames(int(n)))
+
+    def workspace_bytes(self, B: int, n: int) -> int:
+        return int(lib().rvchubert_workspace_bytes(self._h, B, n))
+
+    def forward(self, audio, hidden, workspace, B, n, stream) -> None:
+        self._check(lib().rvchubert_forward(self._h, audio, hidden, workspace.data_ptr(), workspace.numel(), B, n, stream), "rvchubert_forward")
+
+    def final_proj(self, x, out, rows, stream) -> None:
+        self._check(lib().rvchubert_final_proj(self._h, x, out, rows, stream), "rvchubert_final_proj")
+
+    def set_option(self, key: str, value: int) -> None:
+        self._check(lib().rvchubert_set_option(self._h, key.encode(), int(value)), "rvchubert_set_option")
+
+    def debug_read(self, name: str, dst, workspace, B: int, n: int, stream) -> int:
+        k = lib().rvchubert_debug_read(self._h, name.encode(), dst.data_ptr(), dst.numel(), workspace.data_ptr(), B, n, stream)
+        self._check(k, "rvchubert_debug_read")
+        return int(k)
+
+    def launch_count(self) -> int:
+        return int(lib().rvchubert_last_launch_count(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            lib().rvchubert_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class ProfileEntry(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("ms", C.c_double), ("flops", C.c_double), ("bytes", C.c_double), ("spans", C.c_int64)]
 
@@ -75,6 +128,9 @@ EXPORTS = [
     "rvcrefine_last_launch_count", "rvcrefine_destroy", "rvcrefine_last_error",
     "rvcrmvpe_create", "rvcrmvpe_load_weights", "rvcrmvpe_mel_workspace_bytes", "rvcrmvpe_mel", "rvcrmvpe_workspace_bytes", "rvcrmvpe_forward",
     "rvcrmvpe_decode", "rvcrmvpe_debug_read", "rvcrmvpe_last_launch_count", "rvcrmvpe_destroy", "rvcrmvpe_last_error",
+    # include/rvchubert.h
+    "rvchubert_create", "rvchubert_load_weights", "rvchubert_frames", "rvchubert_workspace_bytes", "rvchubert_forward", "rvchubert_final_proj",
+    "rvchubert_debug_read", "rvchubert_set_option", "rvchubert_last_launch_count", "rvchubert_destroy", "rvchubert_last_error",
 ]
 
 _lib = None
@@ -185,6 +241,28 @@ def lib() -> C.CDLL:
     L.rvcrmvpe_destroy.restype = None
     L.rvcrmvpe_last_error.argtypes = []
     L.rvcrmvpe_last_error.restype = C.c_char_p
+    L.rvchubert_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.rvchubert_create.restype = C.c_int
+    L.rvchubert_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]
+    L.rvchubert_load_weights.restype = C.c_int
+    L.rvchubert_frames.argtypes = [i32]
+    L.rvchubert_frames.restype = i32
+    L.rvchubert_workspace_bytes.argtypes = [vp, i32, i32]
+    L.rvchubert_workspace_bytes.restype = sz
+    L.rvchubert_forward.argtypes = [vp, vp, vp, vp, sz, i32, i32, vp]
+    L.rvchubert_forward.restype = C.c_int
+    L.rvchubert_final_proj.argtypes = [vp, vp, vp, i64, vp]
+    L.rvchubert_final_proj.restype = C.c_int
+    L.rvchubert_debug_read.argtypes = [vp, C.c_char_p, vp, i64, vp, i32, i32, vp]
+    L.rvchubert_debug_read.restype = i64
+    L.rvchubert_set_option.argtypes = [vp, C.c_char_p, i64]
+    L.rvchubert_set_option.restype = C.c_int
+    L.rvchubert_last_launch_count.argtypes = [vp]
+    L.rvchubert_last_launch_count.restype = i64
+    L.rvchubert_destroy.argtypes = [vp]
+    L.rvchubert_destroy.restype = None
+    L.rvchubert_last_error.argtypes = []
+    L.rvchubert_last_error.restype = C.c_char_p
     L.rvcsyn_create.argtypes = [C.POINTER(SynConfig), C.c_int, C.POINTER(vp)]
     L.rvcsyn_create.restype = C.c_int
     L.rvcsyn_load_weights.argtypes = [vp, C.POINTER(Tensor), i32]

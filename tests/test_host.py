@@ -20,7 +20,7 @@ def test_abi_exports_every_declared_symbol(built_lib):
     from rvc_b200 import _lib
 
     declared = set()
-    for header, prefix in (("rvcdec.h", "rvcdec"), ("rvcsyn.h", "rvcsyn"), ("rvcrefine.h", "rvcrefine"), ("rvcrmvpe.h", "rvcrmvpe")):
+    for header, prefix in (("rvcdec.h", "rvcdec"), ("rvcsyn.h", "rvcsyn"), ("rvcrefine.h", "rvcrefine"), ("rvcrmvpe.h", "rvcrmvpe"), ("rvchubert.h", "rvchubert")):
         hdr = open(os.path.join(ROOT, "include", header)).read()
         found = set(re.findall(r"\b(%s_[a-z_0-9]+)\s*\(" % prefix, hdr))
         assert found, f"no declarations parsed in {header}"

@@ -1,0 +1,19 @@
+"""One 30 s forward of the HuBERT embedder (for an ncu launch list): python tools/hubert_one.py [seconds]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+import rvc_b200  # noqa: E402
+
+secs = float(sys.argv[1]) if len(sys.argv) > 1 else 30.0
+torch.manual_seed(1)
+m = rvc_b200.HubertModelWithFinalProj().eval()
+a = (0.3 * torch.randn(1, int(secs * 16000))).cuda()
+m(a)
+torch.cuda.synchronize()
+y = m(a)["last_hidden_state"]
+torch.cuda.synchronize()
+print(tuple(y.shape), float(y.abs().mean()))
