@@ -4,6 +4,8 @@
 // k-tap Conv1d reads k * C contiguous floats per output row with a row pitch of s * C), so the whole model is
 //   gemm128 (bias / GELU / residual epilogues), layer norm, the grouped positional convolution, attention,
 // plus the first conv layer (one input channel) with its GroupNorm statistics from a 10 x 10 autocorrelation of the audio.
+#include <cuda_fp16.h>
+
 #include <cstdint>
 
 #include "common.cuh"
@@ -118,7 +120,8 @@ cudaError_t launch_gemm128(const float* A, size_t lda, size_t strideA, const flo
 // ---------------------------------------------------------------------------------------------------------------------
 template <int C>
 __global__ void __launch_bounds__(256) hubert_ln_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ gamma,
-                                                        const float* __restrict__ beta, float* __restrict__ out, size_t rows, float eps) {
+                                                        const float* __restrict__ beta, float* __restrict__ out, __half* __restrict__ out16,
+                                                        size_t rows, float eps) {
   constexpr int PER = C / 32;
   const size_t r = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -143,14 +146,16 @@ __global__ void __launch_bounds__(256) hubert_ln_kernel(const float* __restrict_
 #pragma unroll
   for (int i = 0; i < PER; ++i) {
     const int c = lane + 32 * i;
-    out[r * C + c] = (v[i] - mean) * inv * __ldg(gamma + c) + __ldg(beta + c);
+    const float y = (v[i] - mean) * inv * __ldg(gamma + c) + __ldg(beta + c);
+    if (out) out[r * C + c] = y;
+    if (out16) out16[r * C + c] = __float2half_rn(y);
   }
 }
-cudaError_t launch_hubert_ln(const float* a, const float* b, const float* gamma, const float* beta, float* out, size_t rows, int C, float eps,
-                             cudaStream_t s) {
+cudaError_t launch_hubert_ln(const float* a, const float* b, const float* gamma, const float* beta, float* out, __half* out16, size_t rows, int C,
+                             float eps, cudaStream_t s) {
   const unsigned grid = (unsigned)((rows + 7) / 8);
-  if (C == 768) hubert_ln_kernel<768><<<grid, 256, 0, s>>>(a, b, gamma, beta, out, rows, eps);
-  else if (C == 512) hubert_ln_kernel<512><<<grid, 256, 0, s>>>(a, b, gamma, beta, out, rows, eps);
+  if (C == 768) hubert_ln_kernel<768><<<grid, 256, 0, s>>>(a, b, gamma, beta, out, out16, rows, eps);
+  else if (C == 512) hubert_ln_kernel<512><<<grid, 256, 0, s>>>(a, b, gamma, beta, out, out16, rows, eps);
   else return cudaErrorInvalidValue;
   return cudaGetLastError();
 }
@@ -226,7 +231,7 @@ __global__ void hubert_feat0_affine_kernel(const double* __restrict__ stats, con
 // out[b][t][c] = gelu(scale[b][c] * sum_j w[c][j] a[b][5 t + j] + shift[b][c]);  32 frames x 512 channels per CTA
 __global__ void __launch_bounds__(256) hubert_feat0_kernel(const float* __restrict__ audio, size_t n, const float* __restrict__ w,
                                                            const float* __restrict__ scale, const float* __restrict__ shift, float* __restrict__ out,
-                                                           int L0, int Cout) {
+                                                           __half* __restrict__ out16, int L0, int Cout) {
   constexpr int TT = 32;
   __shared__ float as[TT * F0S + F0K];
   const int b = blockIdx.y, t0 = blockIdx.x * TT;
@@ -245,18 +250,21 @@ __global__ void __launch_bounds__(256) hubert_feat0_kernel(const float* __restri
       float y = 0.f;
 #pragma unroll
       for (int j = 0; j < F0K; ++j) y = fmaf(wv[j], as[tt * F0S + j], y);
-      out[((size_t)b * L0 + t0 + tt) * Cout + c] = gelu_erf(fmaf(y, sc, sh));
+      const float g = gelu_erf(fmaf(y, sc, sh));
+      const size_t o = ((size_t)b * L0 + t0 + tt) * Cout + c;
+      if (out) out[o] = g;
+      if (out16) out16[o] = __float2half_rn(g);
     }
   }
 }
 
 cudaError_t launch_hubert_feat0(const float* audio, size_t n, const float* w, const float* gamma, const float* beta, double* stats, float* scale,
-                                float* shift, float* out, int B, int L0, int Cout, float eps, cudaStream_t s) {
+                                float* shift, float* out, __half* out16, int B, int L0, int Cout, float eps, cudaStream_t s) {
   cudaError_t e = cudaMemsetAsync(stats, 0, (size_t)B * F0NS * sizeof(double), s);
   if (e != cudaSuccess) return e;
   hubert_feat0_stats_kernel<<<dim3((L0 + 4095) / 4096, B), 256, 0, s>>>(audio, n, L0, stats);
   hubert_feat0_affine_kernel<<<dim3((Cout + 127) / 128, B), 128, 0, s>>>(stats, w, gamma, beta, scale, shift, L0, Cout, eps);
-  hubert_feat0_kernel<<<dim3((L0 + 31) / 32, B), 256, 0, s>>>(audio, n, w, scale, shift, out, L0, Cout);
+  hubert_feat0_kernel<<<dim3((L0 + 31) / 32, B), 256, 0, s>>>(audio, n, w, scale, shift, out, out16, L0, Cout);
   return cudaGetLastError();
 }
 
@@ -322,7 +330,8 @@ cudaError_t launch_hubert_posconv(const float* x, const float* wp, const float* 
 constexpr int AT = 64, AD = 64, AP = AT + 4;
 constexpr size_t HUBERT_ATT_SMEM = (size_t)4 * AD * AP * sizeof(float);
 
-__global__ void __launch_bounds__(256) hubert_attention_kernel(const float* __restrict__ qkv, float* __restrict__ ctx, int T, int heads, float scale) {
+__global__ void __launch_bounds__(256) hubert_attention_kernel(const float* __restrict__ qkv, float* __restrict__ ctx, __half* __restrict__ ctx16, int T, int heads,
+                                                               float scale) {
   extern __shared__ __align__(16) float sm[];
   float(*Qs)[AP] = (float(*)[AP])sm;                    // [d][q], pre-scaled
   float(*Ks)[AP] = (float(*)[AP])(sm + AD * AP);        // [d][k]
@@ -415,10 +424,15 @@ __global__ void __launch_bounds__(256) hubert_attention_kernel(const float* __re
     const int t = q0 + ty * 4 + i;
     if (t >= T) continue;
     const float inv = 1.f / lrow[i];
-    *(float4*)(ctx + ((size_t)b * T + t) * C + h * AD + tx * 4) = make_float4(o[i][0] * inv, o[i][1] * inv, o[i][2] * inv, o[i][3] * inv);
+    const size_t oo = ((size_t)b * T + t) * C + h * AD + tx * 4;
+    if (ctx) *(float4*)(ctx + oo) = make_float4(o[i][0] * inv, o[i][1] * inv, o[i][2] * inv, o[i][3] * inv);
+    if (ctx16) {
+      __half2 h0 = __floats2half2_rn(o[i][0] * inv, o[i][1] * inv), h1 = __floats2half2_rn(o[i][2] * inv, o[i][3] * inv);
+      *(uint2*)(ctx16 + oo) = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+    }
   }
 }
-cudaError_t launch_hubert_attention(const float* qkv, float* ctx, int B, int T, int heads, cudaStream_t s) {
+cudaError_t launch_hubert_attention(const float* qkv, float* ctx, __half* ctx16, int B, int T, int heads, cudaStream_t s) {
   static bool attr_set[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -428,7 +442,7 @@ cudaError_t launch_hubert_attention(const float* qkv, float* ctx, int B, int T, 
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
-  hubert_attention_kernel<<<dim3((T + AT - 1) / AT, heads, B), 256, HUBERT_ATT_SMEM, s>>>(qkv, ctx, T, heads, 0.125f);
+  hubert_attention_kernel<<<dim3((T + AT - 1) / AT, heads, B), 256, HUBERT_ATT_SMEM, s>>>(qkv, ctx, ctx16, T, heads, 0.125f);
   return cudaGetLastError();
 }
 

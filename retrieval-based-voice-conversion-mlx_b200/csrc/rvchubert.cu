@@ -2,6 +2,8 @@
 // positional conv's weight norm, q | k | v fused) and the layer schedule of transformers' HubertModel for the base
 // configuration (modeling_hubert.py:178-477, :889-966; the reference subclasses it in rvc/lib/utils.py:31-34) over the
 // kernels of hubert_kernels.cu.
+#include <cuda_fp16.h>
+
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -18,12 +20,14 @@ using namespace rvcdec;
 namespace rvcdec {
 cudaError_t launch_gemm128(const float* A, size_t lda, size_t strideA, const float* W, const float* bias, const float* R, float* C, size_t ldc,
                            size_t strideC, int batch, int M, int N, int K, int act, cudaStream_t s);
-cudaError_t launch_hubert_ln(const float* a, const float* b, const float* gamma, const float* beta, float* out, size_t rows, int C, float eps,
-                             cudaStream_t s);
+cudaError_t launch_hubert_ln(const float* a, const float* b, const float* gamma, const float* beta, float* out, __half* out16, size_t rows, int C,
+                             float eps, cudaStream_t s);
 cudaError_t launch_hubert_feat0(const float* audio, size_t n, const float* w, const float* gamma, const float* beta, double* stats, float* scale,
-                                float* shift, float* out, int B, int L0, int Cout, float eps, cudaStream_t s);
+                                float* shift, float* out, __half* out16, int B, int L0, int Cout, float eps, cudaStream_t s);
 cudaError_t launch_hubert_posconv(const float* x, const float* wp, const float* bias, float* out, int B, int T, int C, cudaStream_t s);
-cudaError_t launch_hubert_attention(const float* qkv, float* ctx, int B, int T, int heads, cudaStream_t s);
+cudaError_t launch_hubert_attention(const float* qkv, float* ctx, __half* ctx16, int B, int T, int heads, cudaStream_t s);
+cudaError_t launch_gemm_tc(const __half* A, size_t lda, size_t strideA, const __half* W, const float* bias, const float* R, float* C32, __half* C16,
+                           size_t ldc, size_t strideC, int batch, int M, int N, int K, int act, cudaStream_t s);
 }  // namespace rvcdec
 
 namespace {
@@ -76,7 +80,9 @@ void conv_lengths(int n, int L[NCONV]) {
 struct rvchubert_handle {
   int device = 0;
   bool loaded = false, has_proj = false, keep_layer0 = false;
+  bool tc = true;            // GEMMs on the tensor cores with fp16 operands (gemm_tc.cu); 0: fp32 CUDA-core GEMMs
   float* dev = nullptr;
+  __half* dev16 = nullptr;   // the GEMM weights once more in fp16, same offsets as in `dev`
   size_t conv_w[NCONV] = {}, gn_g = 0, gn_b = 0, fp_lng = 0, fp_lnb = 0, fp_w = 0, fp_b = 0, pos_w = 0, pos_b = 0, enc_lng = 0, enc_lnb = 0,
          proj_w = 0, proj_b = 0;
   LayerW layer[NLAYER] = {};
@@ -117,6 +123,7 @@ int push_named(std::vector<float>& host, const TMh& tm, const std::string& name,
 struct HWs {
   double* stats;
   float *scale, *shift, *bufA, *bufB, *featln, *xp, *pos, *emb, *x, *x1, *qkv, *ffn, *keep0;
+  __half *a16, *b16, *featln16, *in16, *ctx16, *x1_16, *ffn16;  // fp16 operands of the tensor-core mode
   size_t bytes;
 };
 
@@ -141,6 +148,13 @@ HWs carve_h(void* base, int B, int n) {
   w.qkv = (float*)take(rows * 3 * HID * 4);
   w.ffn = (float*)take(rows * FFN * 4);
   w.keep0 = (float*)take(rows * HID * 4);
+  w.a16 = (__half*)take((size_t)B * L[0] * CONV_DIM * 2);
+  w.b16 = (__half*)take((size_t)B * L[1] * CONV_DIM * 2);
+  w.featln16 = (__half*)take(rows * CONV_DIM * 2);
+  w.in16 = (__half*)take(rows * HID * 2);
+  w.ctx16 = (__half*)take(rows * HID * 2);
+  w.x1_16 = (__half*)take(rows * HID * 2);
+  w.ffn16 = (__half*)take(rows * FFN * 2);
   w.bytes = off;
   return w;
 }
@@ -165,9 +179,10 @@ int rvchubert_create(int device, rvchubert_handle** out) {
 
 void rvchubert_destroy(rvchubert_handle* h) {
   if (!h) return;
-  if (h->dev) {
+  if (h->dev || h->dev16) {
     HGuard g(h->device);
     cudaFree(h->dev);
+    cudaFree(h->dev16);
   }
   delete h;
 }
@@ -183,6 +198,7 @@ int32_t rvchubert_frames(int32_t n_samples) {
 int rvchubert_set_option(rvchubert_handle* h, const char* key, int64_t value) {
   if (!h || !key) return hfail(RVCDEC_ERR_ARG, "null argument");
   if (!strcmp(key, "keep_layer0")) { h->keep_layer0 = value != 0; return 0; }
+  if (!strcmp(key, "tc")) { h->tc = value != 0; return 0; }
   return hfail(RVCDEC_ERR_ARG, "unknown option %s", key);
 }
 
@@ -287,6 +303,13 @@ int rvchubert_load_weights(rvchubert_handle* h, const rvcdec_tensor* tensors, in
   if (h->dev) { HCK(cudaFree(h->dev)); h->dev = nullptr; }
   HCK(cudaMalloc((void**)&h->dev, host.size() * sizeof(float)));
   HCK(cudaMemcpy(h->dev, host.data(), host.size() * sizeof(float), cudaMemcpyHostToDevice));
+  {  // fp16 image of the same array (only the GEMM weights are read from it)
+    std::vector<__half> h16(host.size());
+    for (size_t i = 0; i < host.size(); ++i) h16[i] = __float2half_rn(host[i]);
+    if (h->dev16) { HCK(cudaFree(h->dev16)); h->dev16 = nullptr; }
+    HCK(cudaMalloc((void**)&h->dev16, h16.size() * sizeof(__half)));
+    HCK(cudaMemcpy(h->dev16, h16.data(), h16.size() * sizeof(__half), cudaMemcpyHostToDevice));
+  }
   h->loaded = true;
   return 0;
 }
@@ -314,41 +337,51 @@ int rvchubert_forward(rvchubert_handle* h, const float* audio, float* hidden, vo
   cudaStream_t s = (cudaStream_t)stream;
   const float* P = h->dev;
   h->launches = 0;
-  // conv feature extractor: layer 0 with its GroupNorm, then six strided convs as GEMMs over k * 512-float rows
-  HCK(launch_hubert_feat0(audio, (size_t)n_samples, P + h->conv_w[0], P + h->gn_g, P + h->gn_b, w.stats, w.scale, w.shift, w.bufA, B, L[0], CONV_DIM,
-                          LN_EPS, s));
-  h->launches += 3;
-  float* src = w.bufA;
-  float* dst = w.bufB;
-  for (int i = 1; i < NCONV; ++i) {
-    HCK(launch_gemm128(src, (size_t)CONV_S[i] * CONV_DIM, (size_t)L[i - 1] * CONV_DIM, P + h->conv_w[i], nullptr, nullptr, dst, CONV_DIM,
-                       (size_t)L[i] * CONV_DIM, B, L[i], CONV_DIM, CONV_K[i] * CONV_DIM, 1, s));
+  const size_t rows = (size_t)B * T;
+  if (rows > 0x7fffffff) return hfail(RVCDEC_ERR_ARG, "B * T too large");
+  const int M = (int)rows;
+  const bool tc = h->tc;
+  const __half* P16 = h->dev16;
+  // one linear layer over rows: fp32 CUDA-core GEMM, or fp16 operands on the tensor cores (fp32 accumulation either way)
+  auto linear = [&](const float* a32, const __half* a16, size_t lda, size_t strideA, size_t w, const float* bias, const float* res, float* c32,
+                    __half* c16, size_t ldc, size_t strideC, int batch, int m, int n, int k, int act) -> cudaError_t {
     ++h->launches;
+    if (tc) return launch_gemm_tc(a16, lda, strideA, P16 + w, bias, res, c32, c16, ldc, strideC, batch, m, n, k, act, s);
+    return launch_gemm128(a32, lda, strideA, P + w, bias, res, c32, ldc, strideC, batch, m, n, k, act, s);
+  };
+  // conv feature extractor: layer 0 with its GroupNorm, then six strided convs as GEMMs over k * 512-element rows
+  HCK(launch_hubert_feat0(audio, (size_t)n_samples, P + h->conv_w[0], P + h->gn_g, P + h->gn_b, w.stats, w.scale, w.shift, tc ? nullptr : w.bufA,
+                          tc ? w.a16 : nullptr, B, L[0], CONV_DIM, LN_EPS, s));
+  h->launches += 3;
+  float *src = w.bufA, *dst = w.bufB;
+  __half *src16 = w.a16, *dst16 = w.b16;
+  for (int i = 1; i < NCONV; ++i) {
+    const bool last = i == NCONV - 1;  // the last layer's output is kept in fp32 (layer norm input, "features" hook)
+    HCK(linear(src, src16, (size_t)CONV_S[i] * CONV_DIM, (size_t)L[i - 1] * CONV_DIM, h->conv_w[i], nullptr, nullptr, (tc && !last) ? nullptr : dst,
+               (tc && !last) ? dst16 : nullptr, CONV_DIM, (size_t)L[i] * CONV_DIM, B, L[i], CONV_DIM, CONV_K[i] * CONV_DIM, 1));
     float* t = src; src = dst; dst = t;
+    __half* t16 = src16; src16 = dst16; dst16 = t16;
   }
   const float* feat = src;  // (B, T, 512): six swaps leave the result in bufA
-  const size_t rows = (size_t)B * T;
-  const int M = (int)rows;
-  if (rows > 0x7fffffff) return hfail(RVCDEC_ERR_ARG, "B * T too large");
   // feature projection (modeling_hubert.py:216-232)
-  HCK(launch_hubert_ln(feat, nullptr, P + h->fp_lng, P + h->fp_lnb, w.featln, rows, CONV_DIM, LN_EPS, s));
-  HCK(launch_gemm128(w.featln, CONV_DIM, 0, P + h->fp_w, P + h->fp_b, nullptr, w.xp, HID, 0, 1, M, HID, CONV_DIM, 0, s));
+  HCK(launch_hubert_ln(feat, nullptr, P + h->fp_lng, P + h->fp_lnb, tc ? nullptr : w.featln, tc ? w.featln16 : nullptr, rows, CONV_DIM, LN_EPS, s));
+  HCK(linear(w.featln, w.featln16, CONV_DIM, 0, h->fp_w, P + h->fp_b, nullptr, w.xp, nullptr, HID, 0, 1, M, HID, CONV_DIM, 0));
   // encoder front (modeling_hubert.py:437-440): x + gelu(pos_conv(x)), LayerNorm
   HCK(launch_hubert_posconv(w.xp, P + h->pos_w, P + h->pos_b, w.pos, B, T, HID, s));
-  HCK(launch_hubert_ln(w.xp, w.pos, P + h->enc_lng, P + h->enc_lnb, w.emb, rows, HID, LN_EPS, s));
-  h->launches += 4;
+  HCK(launch_hubert_ln(w.xp, w.pos, P + h->enc_lng, P + h->enc_lnb, w.emb, tc ? w.in16 : nullptr, rows, HID, LN_EPS, s));
+  h->launches += 3;
   const float* in = w.emb;
   for (int i = 0; i < NLAYER; ++i) {  // HubertEncoderLayer.forward (modeling_hubert.py:388-405)
     const LayerW& Lw = h->layer[i];
-    HCK(launch_gemm128(in, HID, 0, P + Lw.wqkv, P + Lw.bqkv, nullptr, w.qkv, 3 * HID, 0, 1, M, 3 * HID, HID, 0, s));
-    HCK(launch_hubert_attention(w.qkv, w.pos, B, T, HEADS, s));
-    HCK(launch_gemm128(w.pos, HID, 0, P + Lw.wo, P + Lw.bo, in, w.x1, HID, 0, 1, M, HID, HID, 0, s));
-    HCK(launch_hubert_ln(w.x1, nullptr, P + Lw.ln1g, P + Lw.ln1b, w.x1, rows, HID, LN_EPS, s));
-    HCK(launch_gemm128(w.x1, HID, 0, P + Lw.w1, P + Lw.b1, nullptr, w.ffn, FFN, 0, 1, M, FFN, HID, 1, s));
-    HCK(launch_gemm128(w.ffn, FFN, 0, P + Lw.w2, P + Lw.b2, w.x1, w.x, HID, 0, 1, M, HID, FFN, 0, s));
+    HCK(linear(in, w.in16, HID, 0, Lw.wqkv, P + Lw.bqkv, nullptr, w.qkv, nullptr, 3 * HID, 0, 1, M, 3 * HID, HID, 0));
+    HCK(launch_hubert_attention(w.qkv, tc ? nullptr : w.pos, tc ? w.ctx16 : nullptr, B, T, HEADS, s));
+    HCK(linear(w.pos, w.ctx16, HID, 0, Lw.wo, P + Lw.bo, in, w.x1, nullptr, HID, 0, 1, M, HID, HID, 0));
+    HCK(launch_hubert_ln(w.x1, nullptr, P + Lw.ln1g, P + Lw.ln1b, w.x1, tc ? w.x1_16 : nullptr, rows, HID, LN_EPS, s));
+    HCK(linear(w.x1, w.x1_16, HID, 0, Lw.w1, P + Lw.b1, nullptr, tc ? nullptr : w.ffn, tc ? w.ffn16 : nullptr, FFN, 0, 1, M, FFN, HID, 1));
+    HCK(linear(w.ffn, w.ffn16, FFN, 0, Lw.w2, P + Lw.b2, w.x1, w.x, nullptr, HID, 0, 1, M, HID, FFN, 0));
     float* out = i == NLAYER - 1 ? hidden : w.x;
-    HCK(launch_hubert_ln(w.x, nullptr, P + Lw.ln2g, P + Lw.ln2b, out, rows, HID, LN_EPS, s));
-    h->launches += 7;
+    HCK(launch_hubert_ln(w.x, nullptr, P + Lw.ln2g, P + Lw.ln2b, out, (tc && i != NLAYER - 1) ? w.in16 : nullptr, rows, HID, LN_EPS, s));
+    h->launches += 3;
     if (i == 0 && h->keep_layer0) HCK(cudaMemcpyAsync(w.keep0, out, rows * HID * sizeof(float), cudaMemcpyDeviceToDevice, s));
     in = w.x;
   }

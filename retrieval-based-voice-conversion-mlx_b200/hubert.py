@@ -113,7 +113,15 @@ class HubertModelWithFinalProj(nn.Module):
         self._handle: Optional[_lib.HubertHandle] = None
         self._sig = None
         self._workspace: Optional[torch.Tensor] = None
+        self._options: Dict[str, int] = {}
         self.last_launch_count = 0
+
+    def set_option(self, key: str, value: int) -> None:
+        """``rvchubert_set_option``: "tc" (1, default: GEMMs on the tensor cores with fp16 operands and fp32 accumulation;
+        0: fp32 CUDA-core GEMMs), "keep_layer0" (test hook)."""
+        self._options[key] = int(value)
+        if self._handle is not None:
+            self._handle.set_option(key, int(value))
 
     @staticmethod
     def _map_old_names(state_dict, prefix, *args):
@@ -145,6 +153,8 @@ class HubertModelWithFinalProj(nn.Module):
         if self._handle is None or self._sig != sig:
             if self._handle is None or self._handle.device != (dev.index or 0):
                 self._handle = _lib.HubertHandle(dev.index or 0)
+                for k, v in self._options.items():
+                    self._handle.set_option(k, v)
             state = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in sd.items() if v.dtype.is_floating_point}
             self._handle.load_weights(state)
             self._sig = sig

@@ -50,10 +50,13 @@ def main():
         n = int(secs * 16000)
         host = (0.3 * torch.randn(B, n)).pin_memory()
         audio = host.to(dev)
+        m.set_option("tc", 0)
+        ms32 = ev(lambda: m(audio))
+        m.set_option("tc", 1)
         ms = ev(lambda: m(audio))
         fl, T = flops(B, n)
         rec = {"B": B, "seconds": secs, "frames": T, "model_ms": ms, "audio_s_per_s": B * secs / (ms * 1e-3), "tflops": fl / (ms * 1e-3) / 1e12,
-               "launches": m.last_launch_count}
+               "model_ms_fp32_mode": ms32, "launches": m.last_launch_count}
         if B == 1:
             ts = []
             for _ in range(3):
