@@ -9,7 +9,7 @@
  *                          GELU), LayerNorm + Linear 512 -> 768, weight-normed grouped positional conv + GELU, LayerNorm,
  *                          12 post-LN transformer layers (12 heads, FFN 3072, erf-GELU)
  *   rvchubert_final_proj   model.final_proj (Linear 768 -> 256; v1 voice models, pipeline.py:332-334)
- * fp32 throughout.  Same conventions as rvcdec.h: plain C types, device pointers of the handle's device, 0 on success /
+ * fp32 parameters and outputs; the GEMM operands are fp16 in the default tensor-core mode (rvchubert_set_option).  Same conventions as rvcdec.h: plain C types, device pointers of the handle's device, 0 on success /
  * negative rvcdec_status, rvchubert_last_error() for the text.
  */
 #ifndef RVCHUBERT_H_
@@ -54,7 +54,10 @@ int rvchubert_final_proj(rvchubert_handle* h, const float* x, float* out, int64_
 int64_t rvchubert_debug_read(rvchubert_handle* h, const char* name, float* dst, int64_t dst_numel, void* workspace, int32_t B,
                              int32_t n_samples, void* stream);
 
-/* options: "keep_layer0" (0 / 1, default 0: copy the first transformer layer's output aside for rvchubert_debug_read). */
+/* options: "tc" (default 1: the linear layers and strided convolutions as fp16-operand, fp32-accumulating tensor-core GEMMs,
+ * ~6e-3 max error on the O(1) features; 0: fp32 CUDA-core GEMMs, 1e-5), "att_tc" (default 1; with tc: attention on the tensor
+ * cores from the fp16 q | k | v rows; 0: the fp32 attention kernel), "keep_layer0" (0 / 1, default 0: copy the first
+ * transformer layer's output aside for rvchubert_debug_read). */
 int rvchubert_set_option(rvchubert_handle* h, const char* key, int64_t value);
 
 int64_t rvchubert_last_launch_count(const rvchubert_handle* h);

@@ -1,0 +1,239 @@
+// Self-attention of the HuBERT encoder layers on the tensor cores (tensor-core mode of include/rvchubert.h): the twin of
+// hubert_attention_kernel (hubert_kernels.cu) and a sibling of att_mma.cu without relative positions or length masks.
+//   qkv16 (B * T, 3 * 768) fp16 rows [q | k | v] (gemm_tc.cu's output), 12 heads of 64;
+//   ctx16[b, t, h 64 + d] = softmax_s(q_t . k_s / 8) v_s   as fp16 rows (the A operand of the out_proj GEMM).
+// One CTA per (128-query tile, head, item), flash-attention style over 128-key tiles:
+//   TMEM  S[2] 128 x 128 fp32 (double-buffered scores), O 128 x 64 fp32 (running output)
+//   smem  Q, K[2], V[2] tiles gathered with 16-byte cp.async from the row-major tensor into [8-channel chunk][row][8]
+//         (Q and K: K-major operands; V: the MN-major B operand of P V), P[2] probabilities as the fp16 A operand
+// Warps: 0 = producer, 1 = MMA issuer, 2-5 = softmax (one query row per thread = its TMEM lane); exp2 domain; the running
+// output is rescaled in TMEM only when a row maximum of the warp moves.
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace rvcdec {
+
+namespace hatt {
+constexpr int BQ = 128, BK = 128, KC = 64;
+constexpr int NCH = KC / 8;                // 8-channel chunks per head
+constexpr int T_SLICE = 128 * 16;          // bytes per chunk of a 128-row fp16 tile
+constexpr int QKV_TILE = NCH * T_SLICE;    // 16 KB
+constexpr int P_TILE = (BK / 8) * T_SLICE; // 32 KB: [key block 16][query row 128][8 keys]
+constexpr int OFF_Q = 0, OFF_K = OFF_Q + QKV_TILE, OFF_V = OFF_K + 2 * QKV_TILE, OFF_P = OFF_V + 2 * QKV_TILE, OFF_BAR = OFF_P + 2 * P_TILE;
+constexpr int NUM_BARS = 11;
+constexpr int SMEM_BYTES = 128 + OFF_BAR + NUM_BARS * 8 + 16;
+constexpr int THREADS = 192;
+constexpr int TM_S = 0, TM_O = 256;  // TMEM columns
+}  // namespace hatt
+
+namespace {
+__device__ __forceinline__ uint32_t hidesc_bmn(int n) { return make_idesc(ACT_F16, n) | (1u << 16); }
+__device__ __forceinline__ float hex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t hpack2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ void hcp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void hcp_async_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+}  // namespace
+
+__global__ void __launch_bounds__(hatt::THREADS, 1) hubert_att_tc_kernel(const __half* __restrict__ qkv16, __half* __restrict__ ctx16, int T,
+                                                                         int heads) {
+  using namespace hatt;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t sb = (smem_u32(smem_raw) + 127u) & ~127u;
+  uint8_t* sg = smem_raw + (sb - smem_u32(smem_raw));
+  const uint32_t bars = sb + OFF_BAR;
+  const uint32_t q_full = bars, k_full = bars + 8, v_full = bars + 24, s_full = bars + 40, o_done = bars + 56, p_ready = bars + 72;
+  const uint32_t tmem_slot = bars + NUM_BARS * 8;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sg + OFF_BAR + NUM_BARS * 8);
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * BQ, h = blockIdx.y, b = blockIdx.z;
+  const int C = heads * KC, C3 = 3 * C;
+  const int n_kt = (T + BK - 1) / BK;
+
+  if (threadIdx.x == 0) {
+    mbar_init(q_full, 32);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(k_full + 8 * i, 32); mbar_init(v_full + 8 * i, 32); mbar_init(s_full + 8 * i, 1); mbar_init(o_done + 8 * i, 1);
+      mbar_init(p_ready + 8 * i, 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== producer: Q once; K / V tiles double-buffered =====================
+    // one warp instruction covers 8 rows x 4 chunks (gemm_tc.cu); rows at or beyond T are zero-filled (their scores are
+    // masked; zero V rows keep 0 x V finite)
+    const int r8 = lane & 7, cq = lane >> 3;
+    const __half* base = qkv16 + (size_t)b * T * C3 + h * KC;
+    auto gather = [&](uint32_t dst, int which, int row0, uint32_t bar) {
+#pragma unroll 4
+      for (int it = 0; it < 32; ++it) {
+        const int row = (it >> 1) * 8 + r8, chunk = (it & 1) * 4 + cq, t = row0 + row;
+        const bool ok = t < T;
+        hcp_async16(dst + (uint32_t)(chunk * T_SLICE + row * 16), base + (size_t)(ok ? t : 0) * C3 + which * C + chunk * 8, ok ? 16u : 0u);
+      }
+      hcp_async_arrive_noinc(bar);
+    };
+    gather(sb + OFF_Q, 0, q0, q_full);
+    for (int j = 0; j < n_kt; ++j) {
+      const int st = j & 1;
+      if (j >= 2) mbar_wait(s_full + 8 * st, ((j - 2) >> 1) & 1);  // K stage free: S(j-2) has completed
+      gather(sb + OFF_K + st * QKV_TILE, 1, j * BK, k_full + 8 * st);
+      if (j >= 2) mbar_wait(o_done + 8 * st, ((j - 2) >> 1) & 1);  // V stage free: P V(j-2) has completed
+      gather(sb + OFF_V + st * QKV_TILE, 2, j * BK, v_full + 8 * st);
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one elected lane) =====================
+    if (elect_one()) {
+      const uint32_t idS = make_idesc(ACT_F16, BK), idO = hidesc_bmn(KC);
+      mbar_wait(q_full, 0);
+      for (int j = 0; j <= n_kt; ++j) {
+        if (j < n_kt) {  // S(j) = Q K(j)^T; its buffer was read out by softmax(j - 2), which P V(j - 2) waited for
+          const int st = j & 1;
+          mbar_wait(k_full + 8 * st, (j >> 1) & 1);
+          fence_proxy_async();  // cp.async wrote the tiles through the generic proxy
+          tc_fence_after();
+          for (int ks = 0; ks < KC / 16; ++ks)
+            tc_mma_f16(tm + TM_S + st * BK, make_smem_desc(sb + OFF_Q + 2 * ks * T_SLICE, T_SLICE, 128),
+                       make_smem_desc(sb + OFF_K + st * QKV_TILE + 2 * ks * T_SLICE, T_SLICE, 128), idS, ks ? 1u : 0u);
+          tc_commit(s_full + 8 * st);
+        }
+        if (j >= 1) {  // O += P(j-1) V(j-1)
+          const int i = j - 1, st = i & 1;
+          mbar_wait(p_ready + 8 * st, (i >> 1) & 1);
+          mbar_wait(v_full + 8 * st, (i >> 1) & 1);
+          fence_proxy_async();
+          tc_fence_after();
+          for (int ks = 0; ks < BK / 16; ++ks)
+            tc_mma_f16(tm + TM_O, make_smem_desc(sb + OFF_P + st * P_TILE + 2 * ks * T_SLICE, T_SLICE, 128),
+                       make_smem_desc(sb + OFF_V + st * QKV_TILE + ks * 256, 128, T_SLICE), idO, (i | ks) ? 1u : 0u);
+          tc_commit(o_done + 8 * st);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================== softmax warps: thread = query row = TMEM lane =====================
+    const int qd = warp & 3, r = qd * 32 + lane, t = q0 + r;
+    const uint32_t tl = tm + ((uint32_t)(qd * 32) << 16);
+    const float c2 = 1.4426950408889634f * 0.125f;  // scores / sqrt(64) in the log2 domain
+    float m_run = -3.0e38f, l_run = 0.f;
+    for (int j = 0; j < n_kt; ++j) {
+      const int st = j & 1, s0 = j * BK;
+      mbar_wait(s_full + 8 * st, (j >> 1) & 1);
+      tc_fence_after();
+      float mx = -3.0e38f;
+#pragma unroll 1
+      for (int c = 0; c < BK / 32; ++c) {
+        uint32_t sc[32];
+        tc_ld32(tl + TM_S + st * BK + c * 32, sc);
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (s0 + c * 32 + i < T) mx = fmaxf(mx, __uint_as_float(sc[i]) * c2);
+      }
+      const float m_new = fmaxf(m_run, mx);
+      const float corr = hex2(m_run - m_new);
+      if (j >= 2) mbar_wait(o_done + 8 * st, ((j - 2) >> 1) & 1);  // the P buffer of this stage was last read by P V(j - 2)
+      uint8_t* Pt = sg + OFF_P + st * P_TILE + r * 16;
+      float ps = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < BK / 32; ++c) {
+        uint32_t sc[32];
+        tc_ld32(tl + TM_S + st * BK + c * 32, sc);
+        float pv[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float e = (s0 + c * 32 + i < T) ? hex2(fmaf(__uint_as_float(sc[i]), c2, -m_new)) : 0.f;
+          pv[i] = e;
+          ps += e;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          *reinterpret_cast<uint4*>(Pt + (c * 4 + k) * T_SLICE) = make_uint4(hpack2(pv[8 * k], pv[8 * k + 1]), hpack2(pv[8 * k + 2], pv[8 * k + 3]),
+                                                                             hpack2(pv[8 * k + 4], pv[8 * k + 5]), hpack2(pv[8 * k + 6], pv[8 * k + 7]));
+      }
+      l_run = l_run * corr + ps;
+      m_run = m_new;
+      // rescale the running output only if a maximum of this warp's rows moved (P V(j - 1) must have landed first)
+      if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+        mbar_wait(o_done + 8 * ((j - 1) & 1), ((j - 1) >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < KC / 8; ++c) {
+          uint32_t o8[8];
+          tc_ld8(tl + TM_O + c * 8, o8);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o8[i] = __float_as_uint(__uint_as_float(o8[i]) * corr);
+          tc_st8(tl + TM_O + c * 8, o8);
+        }
+        tc_wait_st();
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_ready + 8 * st);
+    }
+    {  // normalise and store channels h * 64 .. of row t
+      const int last = n_kt - 1;
+      mbar_wait(o_done + 8 * (last & 1), (last >> 1) & 1);
+      tc_fence_after();
+      const float inv = 1.f / l_run;
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        uint32_t o8[8];
+        tc_ld8(tl + TM_O + c * 8, o8);
+        if (t < T) {
+          float v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(o8[i]) * inv;
+          *reinterpret_cast<uint4*>(ctx16 + ((size_t)b * T + t) * C + h * KC + c * 8) =
+              make_uint4(hpack2(v[0], v[1]), hpack2(v[2], v[3]), hpack2(v[4], v[5]), hpack2(v[6], v[7]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(512u) : "memory");
+  }
+}
+
+cudaError_t launch_hubert_att_tc(const __half* qkv16, __half* ctx16, int B, int T, int heads, cudaStream_t s) {
+  using namespace hatt;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 64 && !attr_set[dev]) {
+    e = cudaFuncSetAttribute(hubert_att_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set[dev] = true;
+  }
+  hubert_att_tc_kernel<<<dim3((T + BQ - 1) / BQ, heads, B), THREADS, SMEM_BYTES, s>>>(qkv16, ctx16, T, heads);
+  return cudaGetLastError();
+}
+
+}  // namespace rvcdec

@@ -26,6 +26,7 @@ cudaError_t launch_hubert_feat0(const float* audio, size_t n, const float* w, co
                                 float* shift, float* out, __half* out16, int B, int L0, int Cout, float eps, cudaStream_t s);
 cudaError_t launch_hubert_posconv(const float* x, const float* wp, const float* bias, float* out, int B, int T, int C, cudaStream_t s);
 cudaError_t launch_hubert_attention(const float* qkv, float* ctx, __half* ctx16, int B, int T, int heads, cudaStream_t s);
+cudaError_t launch_hubert_att_tc(const __half* qkv16, __half* ctx16, int B, int T, int heads, cudaStream_t s);
 cudaError_t launch_gemm_tc(const __half* A, size_t lda, size_t strideA, const __half* W, const float* bias, const float* R, float* C32, __half* C16,
                            size_t ldc, size_t strideC, int batch, int M, int N, int K, int act, cudaStream_t s);
 }  // namespace rvcdec
@@ -80,6 +81,7 @@ void conv_lengths(int n, int L[NCONV]) {
 struct rvchubert_handle {
   int device = 0;
   bool loaded = false, has_proj = false, keep_layer0 = false;
+  bool att_tc = true;        // with tc: attention on the tensor cores too (hubert_att_tc.cu)
   bool tc = true;            // GEMMs on the tensor cores with fp16 operands (gemm_tc.cu); 0: fp32 CUDA-core GEMMs
   float* dev = nullptr;
   __half* dev16 = nullptr;   // the GEMM weights once more in fp16, same offsets as in `dev`
@@ -123,7 +125,7 @@ int push_named(std::vector<float>& host, const TMh& tm, const std::string& name,
 struct HWs {
   double* stats;
   float *scale, *shift, *bufA, *bufB, *featln, *xp, *pos, *emb, *x, *x1, *qkv, *ffn, *keep0;
-  __half *a16, *b16, *featln16, *in16, *ctx16, *x1_16, *ffn16;  // fp16 operands of the tensor-core mode
+  __half *a16, *b16, *featln16, *in16, *ctx16, *x1_16, *ffn16, *qkv16;  // fp16 operands of the tensor-core mode
   size_t bytes;
 };
 
@@ -155,6 +157,7 @@ HWs carve_h(void* base, int B, int n) {
   w.ctx16 = (__half*)take(rows * HID * 2);
   w.x1_16 = (__half*)take(rows * HID * 2);
   w.ffn16 = (__half*)take(rows * FFN * 2);
+  w.qkv16 = (__half*)take(rows * 3 * HID * 2);
   w.bytes = off;
   return w;
 }
@@ -199,6 +202,7 @@ int rvchubert_set_option(rvchubert_handle* h, const char* key, int64_t value) {
   if (!h || !key) return hfail(RVCDEC_ERR_ARG, "null argument");
   if (!strcmp(key, "keep_layer0")) { h->keep_layer0 = value != 0; return 0; }
   if (!strcmp(key, "tc")) { h->tc = value != 0; return 0; }
+  if (!strcmp(key, "att_tc")) { h->att_tc = value != 0; return 0; }
   return hfail(RVCDEC_ERR_ARG, "unknown option %s", key);
 }
 
@@ -373,8 +377,10 @@ int rvchubert_forward(rvchubert_handle* h, const float* audio, float* hidden, vo
   const float* in = w.emb;
   for (int i = 0; i < NLAYER; ++i) {  // HubertEncoderLayer.forward (modeling_hubert.py:388-405)
     const LayerW& Lw = h->layer[i];
-    HCK(linear(in, w.in16, HID, 0, Lw.wqkv, P + Lw.bqkv, nullptr, w.qkv, nullptr, 3 * HID, 0, 1, M, 3 * HID, HID, 0));
-    HCK(launch_hubert_attention(w.qkv, tc ? nullptr : w.pos, tc ? w.ctx16 : nullptr, B, T, HEADS, s));
+    const bool atc = tc && h->att_tc;
+    HCK(linear(in, w.in16, HID, 0, Lw.wqkv, P + Lw.bqkv, nullptr, atc ? nullptr : w.qkv, atc ? w.qkv16 : nullptr, 3 * HID, 0, 1, M, 3 * HID, HID, 0));
+    if (atc) HCK(launch_hubert_att_tc(w.qkv16, w.ctx16, B, T, HEADS, s));
+    else HCK(launch_hubert_attention(w.qkv, tc ? nullptr : w.pos, tc ? w.ctx16 : nullptr, B, T, HEADS, s));
     HCK(linear(w.pos, w.ctx16, HID, 0, Lw.wo, P + Lw.bo, in, w.x1, nullptr, HID, 0, 1, M, HID, HID, 0));
     HCK(launch_hubert_ln(w.x1, nullptr, P + Lw.ln1g, P + Lw.ln1b, w.x1, tc ? w.x1_16 : nullptr, rows, HID, LN_EPS, s));
     HCK(linear(w.x1, w.x1_16, HID, 0, Lw.w1, P + Lw.b1, nullptr, tc ? nullptr : w.ffn, tc ? w.ffn16 : nullptr, FFN, 0, 1, M, FFN, HID, 1));
