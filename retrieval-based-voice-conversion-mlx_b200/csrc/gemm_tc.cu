@@ -2,8 +2,9 @@
 //   C[m, n] = epi(sum_k A[m * lda + k] * W[n * K + k] + bias[n]) (+ R[m * ldc + n]),  A, W fp16, accumulation fp32 in TMEM.
 // A is row-major with an arbitrary row pitch (the feature extractor's strided convolutions read k * 512 halves per frame at
 // a pitch of s * 512, hubert_kernels.cu), which rules out one bulk copy per tile: four producer warps gather the 128 x 64
-// tiles with 16-byte cp.async into the no-swizzle K-major core-matrix layout ([k chunk of 8][row][8 halves]: descriptor
-// LBO = rows * 16 B, SBO = 128 B, the layout of conv_mma.cu's operands), signalling an mbarrier per stage
+// tiles with 16-byte cp.async into the no-swizzle K-major core-matrix layout ([k chunk of 8][row][8 halves], the layout of
+// conv_mma.cu's operands; descriptor SBO = 128 B, LBO = the chunk stride, padded by 16 B so that the eight lanes that copy
+// one row's 128 contiguous bytes land in eight different bank groups), signalling an mbarrier per stage
 // (cp.async.mbarrier.arrive.noinc); a fifth warp issues tcgen05.mma (M 128 x N 128 x K 16, four per stage) and frees each
 // stage with tcgen05.commit; the producer warps then read the accumulator (tcgen05.ld, one row per thread) and apply
 // bias / erf-GELU / residual, writing fp32 and / or fp16.  Three 32 KB stages, so two CTAs share an SM and one's epilogue
@@ -19,8 +20,8 @@ namespace rvcdec {
 
 namespace {
 constexpr int TG_M = 128, TG_N = 128, TG_K = 64, TG_STAGES = 3;
-constexpr int TG_TILE = TG_M * TG_K * 2;          // 16 KB per operand per stage
-constexpr int TG_CHUNK_STRIDE = TG_M * 16;        // bytes between consecutive 8-element K chunks of a tile
+constexpr int TG_CHUNK_STRIDE = TG_M * 16 + 16;   // bytes between consecutive 8-element K chunks of a tile (padded, see above)
+constexpr int TG_TILE = 16640;                    // per operand per stage: 8 chunks x 2064 B, rounded up to 128 B
 constexpr int TG_THREADS = 160;
 constexpr int TG_SMEM = 128 + TG_STAGES * 2 * TG_TILE + 64 + 16;
 
@@ -69,33 +70,30 @@ __global__ void __launch_bounds__(TG_THREADS, 2) gemm_tc_kernel(const GemmTcPara
 
   if (warp < 4) {
     // ===================== producers: gather the A and W tiles of every K step =====================
-    // one warp instruction covers 8 rows x 4 chunks (lanes l and l + 8 read neighbouring 16 B of a row; the 8 lanes of a
-    // quarter hit 8 different shared-memory bank groups); this thread: rows (4 warp + j) * 8 + l % 8, chunks h * 4 + l / 8
-    const int r8 = lane & 7, cq = lane >> 3;
-    const __half* arow[4];
-    const __half* wrow[4];
-    uint32_t asz[4], doff[4];
+    // one warp instruction covers 4 rows x 8 chunks: a quarter warp (the unit a 16-byte-per-lane access is processed in)
+    // reads one row's 128 contiguous bytes.  (With 8 rows x 4 chunks per instruction every quarter touched 8 half-used
+    // sectors and the L1 tag stage, not the tensor pipe, set the pace: profiles/r2ar_*.)  This thread: chunk l % 8 of
+    // rows warp * 32 + j * 4 + l / 8, j < 8.
+    const int ch = lane & 7, rs = lane >> 3;
+    const int row0 = warp * 32 + rs;
+    const __half* ap = A + (size_t)(m0 + row0) * p.lda + ch * 8;
+    const __half* wp = p.W + (size_t)(n0 + row0) * p.K + ch * 8;
+    const size_t a4 = 4 * p.lda, w4 = (size_t)4 * p.K;
+    const uint32_t d0 = (uint32_t)(ch * TG_CHUNK_STRIDE + row0 * 16);
+    uint32_t amask = 0;  // bit j: row j of this thread exists
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int row = (warp * 4 + j) * 8 + r8;
-      const bool ok = m0 + row < p.M;
-      arow[j] = A + (size_t)(ok ? m0 + row : 0) * p.lda + cq * 8;
-      asz[j] = ok ? 16u : 0u;
-      wrow[j] = p.W + (size_t)(n0 + row) * p.K + cq * 8;
-      doff[j] = (uint32_t)(cq * TG_CHUNK_STRIDE + row * 16);
-    }
+    for (int j = 0; j < 8; ++j) amask |= (m0 + row0 + j * 4 < p.M) ? (1u << j) : 0u;
     for (int kt = 0; kt < nk; ++kt) {
       const int s = kt % TG_STAGES;
       if (kt >= TG_STAGES) mbar_wait(empty0 + 8 * s, ((kt / TG_STAGES) - 1) & 1);
-      const uint32_t sa = sb + s * 2 * TG_TILE, sw = sa + TG_TILE;
+      const uint32_t sa = sb + s * 2 * TG_TILE + d0, sw = sa + TG_TILE;
       const int ko = kt * TG_K;
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          cp_async16(sa + doff[j] + h * 4 * TG_CHUNK_STRIDE, arow[j] + ko + h * 32, asz[j]);
-          cp_async16(sw + doff[j] + h * 4 * TG_CHUNK_STRIDE, wrow[j] + ko + h * 32, 16u);
-        }
+      for (int j = 0; j < 8; ++j) {
+        const bool ok = (amask >> j) & 1u;
+        cp_async16(sa + j * 64, ok ? ap + j * a4 + ko : A, ok ? 16u : 0u);
+        cp_async16(sw + j * 64, wp + j * w4 + ko, 16u);
+      }
       cp_async_arrive_noinc(full0 + 8 * s);
     }
     // ===================== epilogue: one accumulator row per thread =====================

@@ -18,8 +18,9 @@ namespace rvcdec {
 namespace hatt {
 constexpr int BQ = 128, BK = 128, KC = 64;
 constexpr int NCH = KC / 8;                // 8-channel chunks per head
-constexpr int T_SLICE = 128 * 16;          // bytes per chunk of a 128-row fp16 tile
-constexpr int QKV_TILE = NCH * T_SLICE;    // 16 KB
+constexpr int T_SLICE = 128 * 16;          // bytes per key block of the P tile (128 query rows x 8 keys)
+constexpr int G_SLICE = T_SLICE + 16;      // chunk stride of the gathered Q / K / V tiles (padded: gemm_tc.cu)
+constexpr int QKV_TILE = 16640;            // 8 chunks x 2064 B, rounded up to 128 B
 constexpr int P_TILE = (BK / 8) * T_SLICE; // 32 KB: [key block 16][query row 128][8 keys]
 constexpr int OFF_Q = 0, OFF_K = OFF_Q + QKV_TILE, OFF_V = OFF_K + 2 * QKV_TILE, OFF_P = OFF_V + 2 * QKV_TILE, OFF_BAR = OFF_P + 2 * P_TILE;
 constexpr int NUM_BARS = 11;
@@ -82,16 +83,16 @@ __global__ void __launch_bounds__(hatt::THREADS, 1) hubert_att_tc_kernel(const _
 
   if (warp == 0) {
     // ===================== producer: Q once; K / V tiles double-buffered =====================
-    // one warp instruction covers 8 rows x 4 chunks (gemm_tc.cu); rows at or beyond T are zero-filled (their scores are
-    // masked; zero V rows keep 0 x V finite)
-    const int r8 = lane & 7, cq = lane >> 3;
+    // one warp instruction covers 4 rows x 8 chunks (a quarter warp reads one row's 128 contiguous bytes, gemm_tc.cu); rows
+    // at or beyond T are zero-filled (their scores are masked; zero V rows keep 0 x V finite)
+    const int ch = lane & 7, rs = lane >> 3;
     const __half* base = qkv16 + (size_t)b * T * C3 + h * KC;
     auto gather = [&](uint32_t dst, int which, int row0, uint32_t bar) {
 #pragma unroll 4
       for (int it = 0; it < 32; ++it) {
-        const int row = (it >> 1) * 8 + r8, chunk = (it & 1) * 4 + cq, t = row0 + row;
+        const int row = it * 4 + rs, t = row0 + row;
         const bool ok = t < T;
-        hcp_async16(dst + (uint32_t)(chunk * T_SLICE + row * 16), base + (size_t)(ok ? t : 0) * C3 + which * C + chunk * 8, ok ? 16u : 0u);
+        hcp_async16(dst + (uint32_t)(ch * G_SLICE + row * 16), base + (size_t)(ok ? t : 0) * C3 + which * C + ch * 8, ok ? 16u : 0u);
       }
       hcp_async_arrive_noinc(bar);
     };
@@ -115,8 +116,8 @@ __global__ void __launch_bounds__(hatt::THREADS, 1) hubert_att_tc_kernel(const _
           fence_proxy_async();  // cp.async wrote the tiles through the generic proxy
           tc_fence_after();
           for (int ks = 0; ks < KC / 16; ++ks)
-            tc_mma_f16(tm + TM_S + st * BK, make_smem_desc(sb + OFF_Q + 2 * ks * T_SLICE, T_SLICE, 128),
-                       make_smem_desc(sb + OFF_K + st * QKV_TILE + 2 * ks * T_SLICE, T_SLICE, 128), idS, ks ? 1u : 0u);
+            tc_mma_f16(tm + TM_S + st * BK, make_smem_desc(sb + OFF_Q + 2 * ks * G_SLICE, G_SLICE, 128),
+                       make_smem_desc(sb + OFF_K + st * QKV_TILE + 2 * ks * G_SLICE, G_SLICE, 128), idS, ks ? 1u : 0u);
           tc_commit(s_full + 8 * st);
         }
         if (j >= 1) {  // O += P(j-1) V(j-1)
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(hatt::THREADS, 1) hubert_att_tc_kernel(const _
           tc_fence_after();
           for (int ks = 0; ks < BK / 16; ++ks)
             tc_mma_f16(tm + TM_O, make_smem_desc(sb + OFF_P + st * P_TILE + 2 * ks * T_SLICE, T_SLICE, 128),
-                       make_smem_desc(sb + OFF_V + st * QKV_TILE + ks * 256, 128, T_SLICE), idO, (i | ks) ? 1u : 0u);
+                       make_smem_desc(sb + OFF_V + st * QKV_TILE + ks * 256, 128, G_SLICE), idO, (i | ks) ? 1u : 0u);
           tc_commit(o_done + 8 * st);
         }
       }

@@ -147,10 +147,22 @@ class HubertModelWithFinalProj(nn.Module):
         return model.eval()
 
     # ------------------------------------------------------------------
+    def _apply(self, fn, *args, **kwargs):
+        self._sig_tensors = None  # .to() / .cuda() may replace tensor objects
+        return super()._apply(fn, *args, **kwargs)
+
+    def _tensor_sig(self):
+        """(version, address) of every parameter / buffer: the handle re-uploads when one changed.  The tensor list is cached
+        (walking 100+ submodules costs ~1 ms per call, more than a short clip's GPU time)."""
+        ts = getattr(self, "_sig_tensors", None)
+        if ts is None:
+            ts = self._sig_tensors = list(self.parameters()) + list(self.buffers())
+        return tuple((v._version, v.data_ptr()) for v in ts)
+
     def _ensure_handle(self, dev: torch.device) -> "_lib.HubertHandle":
-        sd = self.state_dict()
-        sig = (dev.index or 0, tuple((k, v._version, v.data_ptr()) for k, v in sd.items()))
+        sig = (dev.index or 0, self._tensor_sig())
         if self._handle is None or self._sig != sig:
+            sd = self.state_dict()
             if self._handle is None or self._handle.device != (dev.index or 0):
                 self._handle = _lib.HubertHandle(dev.index or 0)
                 for k, v in self._options.items():

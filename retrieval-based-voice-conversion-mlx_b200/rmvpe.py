@@ -87,8 +87,20 @@ class E2E(nn.Module):
         self._mel_basis = np.ascontiguousarray(np.asarray(basis, dtype=np.float32))
         self._sig = None
 
+    def _apply(self, fn, *args, **kwargs):
+        self._sig_tensors = None  # .to() / .cuda() replace the buffer objects
+        return super()._apply(fn, *args, **kwargs)
+
+    def _tensor_sig(self):
+        """(version, address) of every parameter / buffer; the tensor list is cached (walking the 741-entry state dict costs
+        5 ms per call, as much as the GPU needs for a short clip)."""
+        ts = getattr(self, "_sig_tensors", None)
+        if ts is None:
+            ts = self._sig_tensors = list(self.parameters()) + list(self.buffers())
+        return tuple((v._version, v.data_ptr()) for v in ts)
+
     def _ensure_handle(self, dev: torch.device) -> "_lib.RmvpeHandle":
-        sig = (dev.index or 0, tuple((k, v._version, v.data_ptr()) for k, v in self.state_dict().items()))
+        sig = (dev.index or 0, self._tensor_sig())
         if self._handle is None or self._sig != sig:
             if self._handle is None or self._handle.device != (dev.index or 0):
                 self._handle = _lib.RmvpeHandle(dev.index or 0)
