@@ -8,7 +8,8 @@
  *                      4 ConvBlockRes; BatchNorm folded at load), Conv2d 16 -> 3, BiGRU(384, 256), Linear(512, 360), sigmoid
  *   rvcrmvpe_decode    RMVPE0Predictor.decode / to_local_average_cents (RMVPE.py:484-541)
  * mel2hidden's reflect padding of the frame axis to a multiple of 32 (RMVPE.py:445-482) is host-side (rvc_b200.rmvpe).
- * fp32 throughout (parity first; this part is ~10 % of the decoder's FLOPs per frame).  Same conventions as rvcdec.h: plain C
+ * fp32 parameters and activations; the deep levels' 3 x 3 convolutions take fp16 operands on the tensor cores by default
+ * (rvcrmvpe_set_option "tc").  Same conventions as rvcdec.h: plain C
  * types, device pointers of the handle's device, 0 on success / negative rvcdec_status, rvcrmvpe_last_error() for the text.
  */
 #ifndef RVCRMVPE_H_
@@ -46,9 +47,14 @@ int rvcrmvpe_forward(rvcrmvpe_handle* h, const float* mel, float* hidden, void* 
 int rvcrmvpe_decode(rvcrmvpe_handle* h, const float* hidden, float thred, float* f0, int32_t T, void* stream);
 
 /* test hook: copies a named intermediate of the last rvcrmvpe_forward ("skip4" = last encoder level before pooling (B, 256, T/16, 8), "cnn" =
- * (B, T, 384), "gru" = (B, T, 512)) into a device buffer; returns the number of floats or < 0. */
+ * (B, T, 384), "gru" = (B, T, 512), "inter" = output of the intermediate blocks (B, 512, T/32, 4), kept only with the option keep_inter) into a device buffer; returns the number of floats or < 0. */
 int64_t rvcrmvpe_debug_read(rvcrmvpe_handle* h, const char* name, float* dst, int64_t dst_numel, void* workspace, int32_t B, int32_t T,
                             void* stream);
+
+/* options: "tc" (default 1: the 3 x 3 convolutions with Cin % 64 == 0 and Cout % 128 == 0 - encoder levels 3-4, the intermediate
+ * blocks, decoder levels 0-1 - as fp16-operand, fp32-accumulating implicit GEMMs on the tensor cores; 0: every layer in fp32),
+ * "keep_inter" (0 / 1, default 0: test hook, see rvcrmvpe_debug_read). */
+int rvcrmvpe_set_option(rvcrmvpe_handle* h, const char* key, int64_t value);
 
 int64_t rvcrmvpe_last_launch_count(const rvcrmvpe_handle* h);
 void rvcrmvpe_destroy(rvcrmvpe_handle* h);

@@ -127,7 +127,7 @@ EXPORTS = [
     "rvcrefine_create", "rvcrefine_load_weights", "rvcrefine_workspace_bytes", "rvcrefine_forward", "rvcrefine_noise_floats",
     "rvcrefine_last_launch_count", "rvcrefine_destroy", "rvcrefine_last_error",
     "rvcrmvpe_create", "rvcrmvpe_load_weights", "rvcrmvpe_mel_workspace_bytes", "rvcrmvpe_mel", "rvcrmvpe_workspace_bytes", "rvcrmvpe_forward",
-    "rvcrmvpe_decode", "rvcrmvpe_debug_read", "rvcrmvpe_last_launch_count", "rvcrmvpe_destroy", "rvcrmvpe_last_error",
+    "rvcrmvpe_decode", "rvcrmvpe_debug_read", "rvcrmvpe_set_option", "rvcrmvpe_last_launch_count", "rvcrmvpe_destroy", "rvcrmvpe_last_error",
     # include/rvchubert.h
     "rvchubert_create", "rvchubert_load_weights", "rvchubert_frames", "rvchubert_workspace_bytes", "rvchubert_forward", "rvchubert_final_proj",
     "rvchubert_debug_read", "rvchubert_set_option", "rvchubert_last_launch_count", "rvchubert_destroy", "rvchubert_last_error",
@@ -235,6 +235,8 @@ def lib() -> C.CDLL:
     L.rvcrmvpe_decode.restype = C.c_int
     L.rvcrmvpe_debug_read.argtypes = [vp, C.c_char_p, vp, i64, vp, i32, i32, vp]
     L.rvcrmvpe_debug_read.restype = i64
+    L.rvcrmvpe_set_option.argtypes = [vp, C.c_char_p, i64]
+    L.rvcrmvpe_set_option.restype = C.c_int
     L.rvcrmvpe_last_launch_count.argtypes = [vp]
     L.rvcrmvpe_last_launch_count.restype = i64
     L.rvcrmvpe_destroy.argtypes = [vp]
@@ -560,6 +562,9 @@ class RmvpeHandle:
         n = lib().rvcrmvpe_debug_read(self._h, name.encode(), dst.data_ptr(), dst.numel(), workspace.data_ptr(), B, T, stream)
         self._check(n, "rvcrmvpe_debug_read")
         return int(n)
+
+    def set_option(self, key: str, value: int) -> None:
+        self._check(lib().rvcrmvpe_set_option(self._h, key.encode(), int(value)), "rvcrmvpe_set_option")
 
     def launch_count(self) -> int:
         return int(lib().rvcrmvpe_last_launch_count(self._h))

@@ -325,41 +325,42 @@ cudaError_t launch_gru_simple(const float* gi, const float* whhT, const float* b
   return cudaGetLastError();
 }
 
-// The same recurrence on a CLUSTER of 4 CTAs per (direction, item) with the recurrent weights resident in shared memory:
-// CTA r owns hidden units [64 r, 64 r + 64), i.e. 192 of the 768 gate rows = 192 KB of fp32 weights, kept as w[k][local row]
-// (conflict-free: a warp reads 32 consecutive rows of one k, h[k] is a broadcast).  Per step every CTA forms its 192 dot
-// products (two threads per row, halves of k), its first 64 threads apply the gates and write the new h values into the
-// h buffers of all four CTAs through distributed shared memory; one cluster barrier per step (h is double-buffered).
-// 7.5 us per step for the L2-streamed kernel above -> ~1.7 us (profiles/r2am_*).
-constexpr int GRU_CL = 4, GRU_UNITS = GRU_H / GRU_CL, GRU_ROWS = 3 * GRU_UNITS, GRU_CT = 2 * GRU_ROWS;
-constexpr int GRU_SMEM = (GRU_H * GRU_ROWS + 2 * GRU_ROWS + 2 * GRU_H) * 4;
+// The same recurrence on a CLUSTER of 8 CTAs per (direction, item) with the recurrent weights resident in REGISTERS:
+// CTA c owns hidden units [32 c, 32 c + 32), i.e. 96 of the 768 gate rows; its 384 threads hold 64 weights each (thread =
+// one row x one quarter of k; a warp = 32 rows of one gate and one quarter, so the hidden vector is read with broadcast
+// 16-byte loads: 16 per thread and step).  A first version kept the weights in shared memory (4 CTAs x 192 KB) and was
+// bound by streaming them through the LSU every step (3072 wavefronts, 2.3 us per step, profiles/r2av_*).  Per step:
+// 64 FMAs per thread, the four quarter sums meet in shared memory, the CTA's first warp applies the gates and writes the 32
+// new h values into the h buffers of all eight CTAs through distributed shared memory; one cluster barrier per step
+// (h is double-buffered).
+constexpr int GRU_CL = 8, GRU_UNITS = GRU_H / GRU_CL, GRU_ROWS = 3 * GRU_UNITS, GRU_Q = 4, GRU_KQ = GRU_H / GRU_Q, GRU_CT = GRU_Q * GRU_ROWS;
+static_assert(GRU_UNITS == 32 && GRU_CT == 384, "one warp per (gate, quarter)");
 __global__ void __cluster_dims__(GRU_CL, 1, 1) __launch_bounds__(GRU_CT, 1)
 gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT, const float* __restrict__ bhh, float* __restrict__ out, int B, int T) {
-  extern __shared__ __align__(16) float gsm[];
-  float* wsm = gsm;                          // [k 256][row 192]
-  float* part = wsm + GRU_H * GRU_ROWS;      // [half 2][row 192]
-  float* hbuf = part + 2 * GRU_ROWS;         // [2][256]
+  __shared__ __align__(16) float hbuf[2][GRU_H];
+  __shared__ float part[GRU_Q][GRU_ROWS];
   uint32_t rank;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
   const int dir = blockIdx.y, b = blockIdx.z, t_ = threadIdx.x;
-  const int row = t_ % GRU_ROWS, half = t_ / GRU_ROWS;
-  // local row lr = gate * 64 + u  <->  global row gate * 256 + 64 * rank + u
-  const float* wg = whhT + (size_t)dir * GRU_H * 3 * GRU_H;
-  for (int i = t_; i < GRU_H * GRU_ROWS; i += GRU_CT) {
-    const int k = i / GRU_ROWS, lr = i - k * GRU_ROWS;
-    wsm[i] = __ldg(wg + (size_t)k * 3 * GRU_H + (lr / GRU_UNITS) * GRU_H + GRU_UNITS * rank + lr % GRU_UNITS);
+  const int warp = t_ >> 5, lane = t_ & 31;
+  const int gate = warp % 3, q = warp / 3, row = gate * GRU_UNITS + lane;      // local row
+  const int grow = gate * GRU_H + GRU_UNITS * (int)rank + lane;                 // row of W_hh
+  float wreg[GRU_KQ];
+  {
+    const float* wg = whhT + ((size_t)dir * GRU_H + q * GRU_KQ) * 3 * GRU_H + grow;
+#pragma unroll
+    for (int j = 0; j < GRU_KQ; ++j) wreg[j] = __ldg(wg + (size_t)j * 3 * GRU_H);
   }
-  for (int i = t_; i < 2 * GRU_H; i += GRU_CT) hbuf[i] = 0.f;
-  const int u = t_, ug = GRU_UNITS * (int)rank + t_;  // gate threads: t_ < 64
+  for (int i = t_; i < 2 * GRU_H; i += GRU_CT) (&hbuf[0][0])[i] = 0.f;
+  const int ug = GRU_UNITS * (int)rank + lane;  // gate threads: warp 0
   float br = 0.f, bz = 0.f, bn = 0.f;
-  if (t_ < GRU_UNITS) {
+  if (warp == 0) {
     const float* bb = bhh + dir * 3 * GRU_H;
     br = bb[ug]; bz = bb[GRU_H + ug]; bn = bb[2 * GRU_H + ug];
   }
-  // addresses of this thread's slot in the four CTAs' h buffers
-  uint32_t hdst[GRU_CL];
+  uint32_t hdst[GRU_CL];  // this CTA's h buffer as seen in each CTA of the cluster
   {
-    const uint32_t local = (uint32_t)__cvta_generic_to_shared(hbuf);
+    const uint32_t local = (uint32_t)__cvta_generic_to_shared(&hbuf[0][0]);
 #pragma unroll
     for (int c = 0; c < GRU_CL; ++c) asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(hdst[c]) : "r"(local), "r"(c));
   }
@@ -371,27 +372,28 @@ gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT,
     const float* g = gi + ((size_t)b * T + t) * 6 * GRU_H + dir * 3 * GRU_H;
     g_r = __ldg(g + ug); g_z = __ldg(g + GRU_H + ug); g_n = __ldg(g + 2 * GRU_H + ug);
   };
-  if (t_ < GRU_UNITS && T > 0) load_gi(0);
+  if (warp == 0 && T > 0) load_gi(0);
   for (int step = 0; step < T; ++step) {
-    const float* h = hbuf + (step & 1) * GRU_H;
-    const float* wp = wsm + (size_t)(half * (GRU_H / 2)) * GRU_ROWS + row;
-    const float* hp = h + half * (GRU_H / 2);
+    const float* h = hbuf[step & 1];
+    const float4* hp = reinterpret_cast<const float4*>(h + q * GRU_KQ);
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll 8
-    for (int k = 0; k < GRU_H / 2; k += 4) {
-      a0 = fmaf(wp[(k + 0) * GRU_ROWS], hp[k + 0], a0);
-      a1 = fmaf(wp[(k + 1) * GRU_ROWS], hp[k + 1], a1);
-      a2 = fmaf(wp[(k + 2) * GRU_ROWS], hp[k + 2], a2);
-      a3 = fmaf(wp[(k + 3) * GRU_ROWS], hp[k + 3], a3);
+#pragma unroll
+    for (int k = 0; k < GRU_KQ / 4; ++k) {
+      const float4 hv = hp[k];
+      a0 = fmaf(wreg[4 * k + 0], hv.x, a0);
+      a1 = fmaf(wreg[4 * k + 1], hv.y, a1);
+      a2 = fmaf(wreg[4 * k + 2], hv.z, a2);
+      a3 = fmaf(wreg[4 * k + 3], hv.w, a3);
     }
-    part[half * GRU_ROWS + row] = (a0 + a1) + (a2 + a3);
+    part[q][row] = (a0 + a1) + (a2 + a3);
     __syncthreads();
-    if (t_ < GRU_UNITS) {
+    if (warp == 0) {
       const float cr = g_r, cz = g_z, cn = g_n;
       if (step + 1 < T) load_gi(step + 1);  // in flight across the barrier
-      const float hr = part[u] + part[GRU_ROWS + u] + br;
-      const float hz = part[GRU_UNITS + u] + part[GRU_ROWS + GRU_UNITS + u] + bz;
-      const float hn = part[2 * GRU_UNITS + u] + part[GRU_ROWS + 2 * GRU_UNITS + u] + bn;
+      const float hr = ((part[0][lane] + part[1][lane]) + (part[2][lane] + part[3][lane])) + br;
+      const float hz = ((part[0][GRU_UNITS + lane] + part[1][GRU_UNITS + lane]) + (part[2][GRU_UNITS + lane] + part[3][GRU_UNITS + lane])) + bz;
+      const float hn = ((part[0][2 * GRU_UNITS + lane] + part[1][2 * GRU_UNITS + lane]) +
+                        (part[2][2 * GRU_UNITS + lane] + part[3][2 * GRU_UNITS + lane])) + bn;
       const float r = 1.f / (1.f + expf(-(cr + hr)));
       const float z = 1.f / (1.f + expf(-(cz + hz)));
       const float n = tanhf(cn + r * hn);
@@ -407,10 +409,7 @@ gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT,
 }
 
 cudaError_t launch_gru(const float* gi, const float* whhT, const float* bhh, float* out, int B, int T, cudaStream_t s) {
-  static unsigned long long done = 0;
-  cudaError_t e = set_smem_once(reinterpret_cast<const void*>(gru_cluster_kernel), GRU_SMEM, done);
-  if (e != cudaSuccess) return e;
-  gru_cluster_kernel<<<dim3(GRU_CL, 2, B), GRU_CT, GRU_SMEM, s>>>(gi, whhT, bhh, out, B, T);
+  gru_cluster_kernel<<<dim3(GRU_CL, 2, B), GRU_CT, 0, s>>>(gi, whhT, bhh, out, B, T);
   return cudaGetLastError();
 }
 

@@ -1,5 +1,7 @@
 // C ABI of the RMVPE f0 predictor (include/rvcrmvpe.h): weight folding (BatchNorm -> per-channel scale / shift), the layer
 // schedule of E2E(4, 1, (2, 2)) (rvc/lib/predictors/RMVPE.py:246-339) over the kernels of rmvpe_kernels.cu, mel front end and decode.
+#include <cuda_fp16.h>
+
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -21,6 +23,17 @@ struct Conv2dParams {
   int B, Cout, H, W, relu, out_btcw, tw;
 };
 cudaError_t launch_conv2d(const Conv2dParams& p, int ks, cudaStream_t s);
+struct ConvTcParams {
+  const float* in0; const float* in1; int C0, Cin;
+  const __half* wimg;
+  const float* scale; const float* shift; const float* res;
+  float* out;
+  int B, Cout, H, W, relu;
+};
+bool conv3x3_tc_supported(int Cin, int C0, int Cout);
+size_t conv3x3_tc_image_elems(int Cin, int Cout);
+void conv3x3_tc_pack_host(const float* w, int Cin, int Cout, __half* img);
+cudaError_t launch_conv3x3_tc(const ConvTcParams& p, cudaStream_t s);
 cudaError_t launch_convt2x(const float* in, const float* w, const float* scale, const float* shift, float* out, int B, int Cin, int Cout,
                            int H, int W, cudaStream_t s);
 cudaError_t launch_avgpool2(const float* in, float* out, size_t planes, int H, int W, cudaStream_t s);
@@ -66,7 +79,7 @@ constexpr int LEVELS = 5, INTERS = 4, BLOCKS = 4, C_BASE = 16, GRU_HID = 256, GR
 constexpr float BN_EPS = 1e-5f;
 
 // one convolution with its folded BatchNorm (or bias): offsets into the flat parameter array
-struct ConvW { size_t w = 0, scale = 0, shift = 0; int cin = 0, cout = 0; bool has_scale = false, has_shift = false; };
+struct ConvW { size_t w = 0, scale = 0, shift = 0, img = 0; int cin = 0, cout = 0; bool has_scale = false, has_shift = false, has_img = false; };
 // ConvBlockRes (RMVPE.py:13-57)
 struct Block { ConvW c1, c2, sc; bool shortcut = false; };
 
@@ -78,7 +91,11 @@ struct rvcrmvpe_handle {
   int device = 0;
   bool loaded = false;
   std::vector<float> host;   // every parameter, folded, in one array
+  std::vector<__half> host16;  // fp16 tile images of the 3 x 3 convolutions the tensor-core kernel takes (rmvpe_conv_tc.cu)
   float* dev = nullptr;
+  __half* dev16 = nullptr;
+  bool keep_inter = false;
+  bool tc = true;            // those convolutions on the tensor cores (fp16 operands, fp32 accumulation); 0: all fp32
   float in_a = 1.f, in_c = 0.f;                 // encoder input BatchNorm (one channel)
   std::vector<Block> enc[LEVELS], inter[INTERS], dec[LEVELS];
   ConvW up[LEVELS];                              // decoder ConvTranspose2d + BN
@@ -110,12 +127,19 @@ size_t push(std::vector<float>& v, const float* src, size_t n) {
 }
 
 // conv weight + BatchNorm `bn` folded into scale / shift (eval mode: y = (x - mean) / sqrt(var + eps) * w + b)
-int load_conv_bn(rvcrmvpe_handle* h, const TM& tm, const std::string& conv, const std::string& bn, int cin, int cout, int ks, ConvW& c) {
+int load_conv_bn(rvcrmvpe_handle* h, const TM& tm, const std::string& conv, const std::string& bn, int cin, int cout, int ks, ConvW& c,
+                 bool pack_tc = false) {
   int rc = 0;
   const rvcdec_tensor* w = tm.get(conv + ".weight", (int64_t)cin * cout * ks * ks, &rc);
   if (!w) return rc;
   c.cin = cin; c.cout = cout;
   c.w = push(h->host, w->data, (size_t)w->numel);
+  if (pack_tc && ks == 3 && conv3x3_tc_supported(cin, cin, cout)) {  // (a concatenated input splits at cin / 2, a multiple of 64 too)
+    c.img = (h->host16.size() + 127) / 128 * 128;
+    h->host16.resize(c.img + conv3x3_tc_image_elems(cin, cout));
+    conv3x3_tc_pack_host(w->data, cin, cout, h->host16.data() + c.img);
+    c.has_img = true;
+  }
   const rvcdec_tensor *g = tm.get(bn + ".weight", cout, &rc), *b = tm.get(bn + ".bias", cout, &rc), *mu = tm.get(bn + ".running_mean", cout, &rc),
                       *var = tm.get(bn + ".running_var", cout, &rc);
   if (!g || !b || !mu || !var) return rc;
@@ -132,8 +156,8 @@ int load_conv_bn(rvcrmvpe_handle* h, const TM& tm, const std::string& conv, cons
 
 int load_block(rvcrmvpe_handle* h, const TM& tm, const std::string& p, int cin, int cout, Block& blk) {
   int rc;
-  if ((rc = load_conv_bn(h, tm, p + ".conv.0", p + ".conv.1", cin, cout, 3, blk.c1))) return rc;
-  if ((rc = load_conv_bn(h, tm, p + ".conv.3", p + ".conv.4", cout, cout, 3, blk.c2))) return rc;
+  if ((rc = load_conv_bn(h, tm, p + ".conv.0", p + ".conv.1", cin, cout, 3, blk.c1, true))) return rc;
+  if ((rc = load_conv_bn(h, tm, p + ".conv.3", p + ".conv.4", cout, cout, 3, blk.c2, true))) return rc;
   blk.shortcut = cin != cout;  // RMVPE.py:47-51
   if (blk.shortcut) {
     const rvcdec_tensor *w = tm.get(p + ".shortcut.weight", (int64_t)cin * cout, &rc), *b = tm.get(p + ".shortcut.bias", cout, &rc);
@@ -175,20 +199,29 @@ int rvcrmvpe_create(int device, rvcrmvpe_handle** out) {
 
 void rvcrmvpe_destroy(rvcrmvpe_handle* h) {
   if (!h) return;
-  if (h->dev) {
+  if (h->dev || h->dev16) {
     MGuard g(h->device);
     cudaFree(h->dev);
+    cudaFree(h->dev16);
   }
   delete h;
 }
 
 int64_t rvcrmvpe_last_launch_count(const rvcrmvpe_handle* h) { return h ? h->launches : 0; }
 
+int rvcrmvpe_set_option(rvcrmvpe_handle* h, const char* key, int64_t value) {
+  if (!h || !key) return mfail(RVCDEC_ERR_ARG, "null argument");
+  if (!strcmp(key, "tc")) { h->tc = value != 0; return 0; }
+  if (!strcmp(key, "keep_inter")) { h->keep_inter = value != 0; return 0; }
+  return mfail(RVCDEC_ERR_ARG, "unknown option %s", key);
+}
+
 int rvcrmvpe_load_weights(rvcrmvpe_handle* h, const rvcdec_tensor* tensors, int32_t n) {
   if (!h || !tensors) return mfail(RVCDEC_ERR_ARG, "null argument");
   TM tm;
   for (int i = 0; i < n; ++i) tm.m[tensors[i].name ? tensors[i].name : ""] = &tensors[i];
   h->host.clear();
+  h->host16.clear();
   h->loaded = false;
   int rc = 0;
   {  // encoder input BatchNorm, one channel (RMVPE.py:119, :138)
@@ -263,6 +296,12 @@ int rvcrmvpe_load_weights(rvcrmvpe_handle* h, const rvcdec_tensor* tensors, int3
   if (h->dev) { MCK(cudaFree(h->dev)); h->dev = nullptr; }
   MCK(cudaMalloc((void**)&h->dev, h->host.size() * sizeof(float)));
   MCK(cudaMemcpy(h->dev, h->host.data(), h->host.size() * sizeof(float), cudaMemcpyHostToDevice));
+  if (h->dev16) { MCK(cudaFree(h->dev16)); h->dev16 = nullptr; }
+  if (!h->host16.empty()) {
+    MCK(cudaMalloc((void**)&h->dev16, h->host16.size() * sizeof(__half)));
+    MCK(cudaMemcpy(h->dev16, h->host16.data(), h->host16.size() * sizeof(__half), cudaMemcpyHostToDevice));
+  }
+  std::vector<__half>().swap(h->host16);
   h->loaded = true;
   return 0;
 }
@@ -274,7 +313,7 @@ namespace {
 struct MWs {
   float* buf[4];          // rotating activations, each B x 16 x T x 128 floats (the largest tensor of the U-Net)
   float* skip[LEVELS];    // encoder outputs kept for the decoder's concatenation
-  float *feat, *gi, *gout;
+  float *feat, *gi, *gout, *inter;
   size_t bytes;
 };
 
@@ -288,6 +327,7 @@ MWs carve_m(void* base, int B, int T) {
   w.feat = take((size_t)B * T * GRU_IN);
   w.gi = take((size_t)B * T * 6 * GRU_HID);
   w.gout = take((size_t)B * T * 2 * GRU_HID);
+  w.inter = take((size_t)B * 512 * (T / 32) * 4);   // copy of the intermediate blocks' output (test hook, option keep_inter)
   w.bytes = off;
   return w;
 }
@@ -299,7 +339,15 @@ int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float*
   Conv2dParams p{};
   p.in0 = in0; p.in1 = in1; p.C0 = C0; p.Cin = k.c1.cin; p.w = P + k.c1.w; p.scale = P + k.c1.scale; p.shift = P + k.c1.shift;
   p.out = t1; p.B = B; p.Cout = k.c1.cout; p.H = H; p.W = W; p.relu = 1;
-  MCK(launch_conv2d(p, 3, s)); ++h->launches;
+  auto conv3 = [&](const Conv2dParams& q, const ConvW& cw) -> cudaError_t {
+    ++h->launches;
+    if (h->tc && cw.has_img && conv3x3_tc_supported(q.Cin, q.C0, q.Cout)) {
+      ConvTcParams t{q.in0, q.in1, q.C0, q.Cin, h->dev16 + cw.img, q.scale, q.shift, q.res, q.out, q.B, q.Cout, q.H, q.W, q.relu};
+      return launch_conv3x3_tc(t, s);
+    }
+    return launch_conv2d(q, 3, s);
+  };
+  MCK(conv3(p, k.c1));
   const float* res = in0;  // identity shortcut: only when the input is one tensor of Cout channels
   if (k.shortcut) {
     Conv2dParams q{};
@@ -311,7 +359,7 @@ int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float*
   Conv2dParams r{};
   r.in0 = t1; r.C0 = k.c2.cin; r.Cin = k.c2.cin; r.w = P + k.c2.w; r.scale = P + k.c2.scale; r.shift = P + k.c2.shift; r.res = res;
   r.out = dst; r.B = B; r.Cout = k.c2.cout; r.H = H; r.W = W; r.relu = 1;
-  MCK(launch_conv2d(r, 3, s)); ++h->launches;
+  MCK(conv3(r, k.c2));
   return 0;
 }
 
@@ -384,6 +432,7 @@ int rvcrmvpe_forward(rvcrmvpe_handle* h, const float* mel, float* hidden, void* 
     }
     cur = const_cast<float*>(x);
   }
+  if (h->keep_inter) MCK(cudaMemcpyAsync(w.inter, cur, (size_t)B * C * H * W * sizeof(float), cudaMemcpyDeviceToDevice, s));
   // ---- decoder (RMVPE.py:209-214, :240-243): ConvTranspose2d + BN + ReLU, cat with the skip, 4 blocks ----
   for (int i = 0; i < LEVELS; ++i) {
     float* fr[3]; int k = 0;
@@ -461,6 +510,10 @@ int64_t rvcrmvpe_debug_read(rvcrmvpe_handle* h, const char* name, float* dst, in
   if (nm == "cnn") { src = w.feat; n = (int64_t)B * T * GRU_IN; }
   else if (nm == "gru") { src = w.gout; n = (int64_t)B * T * 2 * GRU_HID; }
   else if (nm == "skip4") { src = w.skip[4]; n = (int64_t)B * 256 * (T / 16) * 8; }
+  else if (nm == "inter") {
+    if (!h->keep_inter) return mfail(RVCDEC_ERR_ARG, "inter is kept only with the keep_inter option");
+    src = w.inter; n = (int64_t)B * 512 * (T / 32) * 4;
+  }
   else return mfail(RVCDEC_ERR_ARG, "unknown intermediate '%s'", name);
   if (dst_numel < n) return mfail(RVCDEC_ERR_ARG, "destination too small");
   MCK(cudaMemcpyAsync(dst, src, (size_t)n * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));

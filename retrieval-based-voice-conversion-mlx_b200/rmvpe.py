@@ -79,7 +79,15 @@ class E2E(nn.Module):
         self._sig = None
         self._workspace: Optional[torch.Tensor] = None
         self._mel_basis: Optional[np.ndarray] = None
+        self._options = {}
         self.last_launch_count = 0
+
+    def set_option(self, key: str, value: int) -> None:
+        """``rvcrmvpe_set_option``: "tc" (1, default: the deep levels' 3 x 3 convolutions on the tensor cores with fp16
+        operands; 0: every layer in fp32)."""
+        self._options[key] = int(value)
+        if self._handle is not None:
+            self._handle.set_option(key, int(value))
 
     # ------------------------------------------------------------------
     def set_mel_basis(self, basis) -> None:
@@ -104,6 +112,8 @@ class E2E(nn.Module):
         if self._handle is None or self._sig != sig:
             if self._handle is None or self._handle.device != (dev.index or 0):
                 self._handle = _lib.RmvpeHandle(dev.index or 0)
+                for k, v in self._options.items():
+                    self._handle.set_option(k, v)
             state = {k: v.detach().to("cpu", torch.float32).contiguous() for k, v in self.state_dict().items()
                      if v.dtype.is_floating_point}
             basis = self._mel_basis if self._mel_basis is not None else mel_filterbank()
