@@ -331,14 +331,17 @@ cudaError_t launch_gru_simple(const float* gi, const float* whhT, const float* b
 // 16-byte loads: 16 per thread and step).  A first version kept the weights in shared memory (4 CTAs x 192 KB) and was
 // bound by streaming them through the LSU every step (3072 wavefronts, 2.3 us per step, profiles/r2av_*).  Per step:
 // 64 FMAs per thread, the four quarter sums meet in shared memory, the CTA's first warp applies the gates and writes the 32
-// new h values into the h buffers of all eight CTAs through distributed shared memory; one cluster barrier per step
-// (h is double-buffered).
+// new h values into the h buffers of all eight CTAs with st.async: the store carries its own completion (complete_tx on an
+// mbarrier of the receiving CTA, which expects 256 x 4 bytes per step), so a step needs no cluster barrier - every thread
+// waits on its CTA's local mbarrier for the next h (h is double-buffered; a CTA sends h(s+1) only after it received all
+// of h(s), i.e. after every CTA finished reading the buffer that h(s+1) overwrites).
 constexpr int GRU_CL = 8, GRU_UNITS = GRU_H / GRU_CL, GRU_ROWS = 3 * GRU_UNITS, GRU_Q = 4, GRU_KQ = GRU_H / GRU_Q, GRU_CT = GRU_Q * GRU_ROWS;
 static_assert(GRU_UNITS == 32 && GRU_CT == 384, "one warp per (gate, quarter)");
 __global__ void __cluster_dims__(GRU_CL, 1, 1) __launch_bounds__(GRU_CT, 1)
 gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT, const float* __restrict__ bhh, float* __restrict__ out, int B, int T) {
   __shared__ __align__(16) float hbuf[2][GRU_H];
   __shared__ float part[GRU_Q][GRU_ROWS];
+  __shared__ __align__(8) unsigned long long hbar[2];
   uint32_t rank;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
   const int dir = blockIdx.y, b = blockIdx.z, t_ = threadIdx.x;
@@ -352,17 +355,26 @@ gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT,
     for (int j = 0; j < GRU_KQ; ++j) wreg[j] = __ldg(wg + (size_t)j * 3 * GRU_H);
   }
   for (int i = t_; i < 2 * GRU_H; i += GRU_CT) (&hbuf[0][0])[i] = 0.f;
+  const uint32_t bar_local = (uint32_t)__cvta_generic_to_shared(&hbar[0]);
+  if (t_ == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_local) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_local + 8) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   const int ug = GRU_UNITS * (int)rank + lane;  // gate threads: warp 0
   float br = 0.f, bz = 0.f, bn = 0.f;
   if (warp == 0) {
     const float* bb = bhh + dir * 3 * GRU_H;
     br = bb[ug]; bz = bb[GRU_H + ug]; bn = bb[2 * GRU_H + ug];
   }
-  uint32_t hdst[GRU_CL];  // this CTA's h buffer as seen in each CTA of the cluster
+  uint32_t hdst[GRU_CL], bdst[GRU_CL];  // this CTA's h buffer / mbarriers as seen in each CTA of the cluster
   {
     const uint32_t local = (uint32_t)__cvta_generic_to_shared(&hbuf[0][0]);
 #pragma unroll
-    for (int c = 0; c < GRU_CL; ++c) asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(hdst[c]) : "r"(local), "r"(c));
+    for (int c = 0; c < GRU_CL; ++c) {
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(hdst[c]) : "r"(local), "r"(c));
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(bdst[c]) : "r"(bar_local), "r"(c));
+    }
   }
   __syncthreads();
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -374,7 +386,12 @@ gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT,
   };
   if (warp == 0 && T > 0) load_gi(0);
   for (int step = 0; step < T; ++step) {
-    const float* h = hbuf[step & 1];
+    const int cur = step & 1, nxt = cur ^ 1;
+    const bool more = step + 1 < T;
+    // arm the barrier that collects h(step + 1): one local arrival + 256 floats from the eight CTAs' gate warps
+    if (t_ == 0 && more)
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_local + 8 * nxt), "r"(GRU_H * 4) : "memory");
+    const float* h = hbuf[cur];
     const float4* hp = reinterpret_cast<const float4*>(h + q * GRU_KQ);
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
@@ -389,7 +406,7 @@ gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT,
     __syncthreads();
     if (warp == 0) {
       const float cr = g_r, cz = g_z, cn = g_n;
-      if (step + 1 < T) load_gi(step + 1);  // in flight across the barrier
+      if (more) load_gi(step + 1);  // in flight while the others' h values arrive
       const float hr = ((part[0][lane] + part[1][lane]) + (part[2][lane] + part[3][lane])) + br;
       const float hz = ((part[0][GRU_UNITS + lane] + part[1][GRU_UNITS + lane]) + (part[2][GRU_UNITS + lane] + part[3][GRU_UNITS + lane])) + bz;
       const float hn = ((part[0][2 * GRU_UNITS + lane] + part[1][2 * GRU_UNITS + lane]) +
@@ -400,12 +417,32 @@ gru_cluster_kernel(const float* __restrict__ gi, const float* __restrict__ whhT,
       const float hnew = (1.f - z) * n + z * h[ug];
       const int t = dir ? T - 1 - step : step;
       out[((size_t)b * T + t) * 2 * GRU_H + dir * GRU_H + ug] = hnew;
-      const uint32_t off = (uint32_t)((((step + 1) & 1) * GRU_H + ug) * 4);
+      if (more) {
+        const uint32_t off = (uint32_t)((nxt * GRU_H + ug) * 4);
 #pragma unroll
-      for (int c = 0; c < GRU_CL; ++c) asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(hdst[c] + off), "f"(hnew) : "memory");
+        for (int c = 0; c < GRU_CL; ++c)
+          asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(hdst[c] + off),
+                       "r"(__float_as_uint(hnew)), "r"(bdst[c] + 8 * nxt)
+                       : "memory");
+      }
     }
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (more) {  // h(step + 1) complete in this CTA's buffer: the (step / 2)-th use of barrier nxt
+      const uint32_t parity = (uint32_t)((step >> 1) & 1);
+      uint32_t done = 0;
+      for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar_local + 8 * nxt), "r"(parity)
+            : "memory");
+        if (spin > (1u << 26)) __trap();  // a protocol bug must not hang the GPU
+      }
+    }
   }
+  // no CTA may exit while others still send into its shared memory
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 cudaError_t launch_gru(const float* gi, const float* whhT, const float* bhh, float* out, int B, int T, cudaStream_t s) {
