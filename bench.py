@@ -332,8 +332,9 @@ def longform_leg(model, cfg, n_dev, reps=3):
 
 
 def rmvpe_leg(dev, secs=60, reps=3):
-    """the RMVPE f0 predictor (rvc_b200.RMVPE0Predictor, random weights, fp32) end to end from a host numpy
-    array of 16 kHz audio to the host f0 array: H2D, mel spectrogram, U-Net + BiGRU, decode, D2H.  Wall clock."""
+    """the RMVPE f0 predictor (rvc_b200.RMVPE0Predictor, random weights, default mode: the 3 x 3 convolutions
+    from level 1 down on the tensor cores with fp16 operands) end to end from a host numpy array of 16 kHz audio to the host f0
+    array: H2D, mel spectrogram, U-Net + BiGRU, decode, D2H.  Wall clock."""
     import numpy as np
     import rvc_b200
 
@@ -349,8 +350,29 @@ def rmvpe_leg(dev, secs=60, reps=3):
         f0 = p.infer_from_audio(audio)
         ts.append(time.perf_counter() - t0)
     assert f0.shape == (1 + n // 160,) and bool(np.isfinite(f0).all())
-    return {"workload": f"RMVPE0Predictor.infer_from_audio, {secs} s of 16 kHz audio, host array -> host f0, fp32, random weights",
+    return {"workload": f"RMVPE0Predictor.infer_from_audio, {secs} s of 16 kHz audio, host array -> host f0, random weights",
             "seconds": min(ts), "audio_s_per_s": secs / min(ts), "frames": int(f0.shape[0]), "launches_model": p.model.last_launch_count}
+
+
+def hubert_leg(dev, secs=30, reps=3):
+    """SURVEY 8f row 4, second half: the HuBERT / ContentVec embedder (rvc_b200.HubertModelWithFinalProj, random weights,
+    default mode: GEMMs and attention on the tensor cores) from a pinned host waveform to the host features: H2D, conv feature
+    extractor, 12 transformer layers, D2H.  Wall clock."""
+    import rvc_b200
+
+    torch.manual_seed(1)
+    m = rvc_b200.HubertModelWithFinalProj().eval()
+    n = secs * 16000
+    host = (0.3 * torch.randn(1, n)).pin_memory()
+    y = m(host.to(dev, non_blocking=True))["last_hidden_state"].cpu()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        y = m(host.to(dev, non_blocking=True))["last_hidden_state"].cpu()
+        ts.append(time.perf_counter() - t0)
+    assert y.shape[0] == 1 and y.shape[2] == 768 and bool(torch.isfinite(y).all())
+    return {"workload": f"HubertModelWithFinalProj(audio)['last_hidden_state'], {secs} s of 16 kHz audio, host waveform -> host features, random weights",
+            "seconds": min(ts), "audio_s_per_s": secs / min(ts), "frames": int(y.shape[1]), "launches": m.last_launch_count}
 
 
 def synthesizer_leg(dev, B=16, T=3000, reps=3):
@@ -519,7 +541,7 @@ def run_ours(args):
         roof["traffic_source"] = "scaled from the committed ncu --set full capture (not measured in this run)"
         roof["algorithmic_bytes_per_launch"] = dom["bytes"] / spans
     total_tflops = 2 * MMAC_PER_FRAME * T * B * args.steps / (ms * 1e-3) / 1e12
-    cpu = parity = synth = rmv = None
+    cpu = parity = synth = rmv = hub = None
     if world == 1 and not args.no_cpu:
         r = cpu_reference_runs(1, 1, full=False)
         cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -534,6 +556,10 @@ def run_ours(args):
             rmv = rmvpe_leg(dev)
         except Exception as e:  # noqa: BLE001
             rmv = {"error": str(e)}
+        try:
+            hub = hubert_leg(dev)
+        except Exception as e:  # noqa: BLE001
+            hub = {"error": str(e)}
     line = {
         "metric": METRIC, "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -557,6 +583,8 @@ def run_ours(args):
         line["synthesizer"] = synth
     if rmv:
         line["rmvpe"] = rmv
+    if hub:
+        line["hubert"] = hub
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
