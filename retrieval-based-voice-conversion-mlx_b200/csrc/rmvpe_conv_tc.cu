@@ -44,6 +44,8 @@ struct ConvTcParams {
   const float* scale; const float* shift; const float* res;
   float* out;
   int B, Cout, H, W, relu;
+  float* part;   // split-K: raw partial sums [split][B][Cout][H W] (conv3x3_tc_finish_kernel reduces them), else null
+  int ksplit;    // number of K splits (1 = none)
 };
 
 template <int BN>
@@ -60,9 +62,11 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
   const uint32_t full0 = sb + OFF_BAR, empty0 = full0 + 8 * STAGES, acc_full = empty0 + 8 * STAGES, tmem_slot = acc_full + 8;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sg + OFF_BAR + 8 * (2 * STAGES + 1));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tile = blockIdx.x, m0 = blockIdx.y * BM * MT, b = blockIdx.z;
+  static_assert(MT == 1, "one pixel tile per CTA");
+  const int n_tile = blockIdx.x, m0 = blockIdx.y * BM, b = blockIdx.z / p.ksplit, sp = blockIdx.z - b * p.ksplit;
   const int HW = p.H * p.W, K9 = 9 * p.Cin, nk = (K9 + BKK - 1) / BKK;
-  const int ntile = min(MT, (HW - m0 + BM - 1) / BM), nq = ntile * nk;  // flat sequence of (pixel tile, K step) pairs
+  const int kbeg = (int)((long long)nk * sp / p.ksplit), nq = (int)((long long)nk * (sp + 1) / p.ksplit) - kbeg;  // this CTA's K steps
+  constexpr int ntile = 1;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full0 + 8 * s, 129); mbar_init(empty0 + 8 * s, 1); }
@@ -83,7 +87,7 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
     const int grp = warp >> 2, r = (warp & 3) * 32 + lane;
     const int C1 = p.Cin - p.C0;
     for (int q = grp; q < nq; q += 2) {
-      const int tile = q / nk, kt = q - tile * nk, s = q % STAGES;
+      const int tile = 0, kt = kbeg + q, s = q % STAGES;
       const int m = m0 + tile * BM + r;
       const bool valid = m < HW;
       const int y = valid ? m / p.W : 0, x = valid ? m - y * p.W : 0;
@@ -126,6 +130,10 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
         const int m = m0 + tile * BM + r;
         const bool valid = m < HW;
         auto finish = [&](int co, uint32_t a) {
+          if (p.part) {  // split-K: the raw partial sum; scale / shift / ReLU / residual wait for the reduction
+            p.part[(((size_t)sp * p.B + b) * p.Cout + co) * HW + m] = __uint_as_float(a);
+            return;
+          }
           float o = __uint_as_float(a) * (p.scale ? __ldg(p.scale + co) : 1.f) + (p.shift ? __ldg(p.shift + co) : 0.f);
           if (p.relu) o = fmaxf(o, 0.f);
           const size_t oi = ((size_t)b * p.Cout + co) * HW + m;
@@ -157,7 +165,7 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
     if (lane == 0) {
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.wimg) + (size_t)n_tile * nk * W_TILE;
       for (int q = 0; q < nq; ++q) {
-        const int s = q % STAGES, kt = q % nk;
+        const int s = q % STAGES, kt = kbeg + q;
         if (q >= STAGES) mbar_wait(empty0 + 8 * s, ((q / STAGES) - 1) & 1);
         mbar_expect_tx(full0 + 8 * s, W_TILE);
         bulk_g2s(sb + s * STAGE + A_TILE, wsrc + (size_t)kt * W_TILE, W_TILE, full0 + 8 * s);
@@ -168,7 +176,7 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
     // ===================== MMA issuer =====================
     const uint32_t idesc = make_idesc(ACT_F16, BN);
     for (int q = 0; q < nq; ++q) {
-      const int s = q % STAGES, tile = q / nk, kt = q - tile * nk;
+      const int s = q % STAGES, tile = 0;
       mbar_wait(full0 + 8 * s, (q / STAGES) & 1);
       tc_fence_after();
       if (lane == 0) {
@@ -176,7 +184,7 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
 #pragma unroll
         for (int ks = 0; ks < BKK / 16; ++ks)
           tc_mma_f16(tm + tile * BN, make_smem_desc(sa + 2 * ks * CH, CH, 128), make_smem_desc(sw + 2 * ks * WCH, WCH, 128), idesc,
-                     (kt | ks) ? 1u : 0u);
+                     (q | ks) ? 1u : 0u);
         tc_commit(empty0 + 8 * s);
         if (q == nq - 1) tc_commit(acc_full);
       }
@@ -218,6 +226,32 @@ void conv3x3_tc_pack_host(const float* w, int Cin, int Cout, __half* img) {
           }
 }
 
+// split-K reduction in a fixed order (bit-reproducible), then the epilogue of the unsplit kernel
+__global__ void conv3x3_tc_finish_kernel(const float* __restrict__ part, int ksplit, const float* __restrict__ scale, const float* __restrict__ shift,
+                                         const float* __restrict__ res, float* __restrict__ out, size_t n, int Cout, int HW, int relu) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float a = 0.f;
+  for (int s = 0; s < ksplit; ++s) a += part[(size_t)s * n + i];
+  const int co = (int)((i / HW) % Cout);
+  float o = a * (scale ? __ldg(scale + co) : 1.f) + (shift ? __ldg(shift + co) : 0.f);
+  if (relu) o = fmaxf(o, 0.f);
+  if (res) o += res[i];
+  out[i] = o;
+}
+
+// number of K splits for a layer: only where the grid would leave most SMs idle (the deep levels: 4-24 CTAs of 36-144 steps)
+int conv3x3_tc_splits(int Cin, int Cout, int HW, int B) {
+  using namespace ctc;
+  const int BN = tile_n(Cout), nk = (9 * Cin + BKK - 1) / BKK;
+  const long long ctas = (long long)(Cout / BN) * ((HW + BM - 1) / BM) * B;
+  if (BN != 128 || ctas >= 74 || nk < 8) return 1;
+  int sp = (int)((148 + ctas - 1) / ctas);
+  if (sp > nk / 4) sp = nk / 4;
+  if (sp > 16) sp = 16;
+  return sp < 2 ? 1 : sp;
+}
+
 template <int BN>
 static cudaError_t launch_conv3x3_tc_n(const ConvTcParams& p, cudaStream_t s) {
   using namespace ctc;
@@ -230,12 +264,16 @@ static cudaError_t launch_conv3x3_tc_n(const ConvTcParams& p, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
-  conv3x3_tc_kernel<BN><<<dim3(p.Cout / BN, (p.H * p.W + BM * Geo<BN>::MT - 1) / (BM * Geo<BN>::MT), p.B), THREADS, Geo<BN>::SMEM, s>>>(p);
+  conv3x3_tc_kernel<BN><<<dim3(p.Cout / BN, (p.H * p.W + BM - 1) / BM, p.B * p.ksplit), THREADS, Geo<BN>::SMEM, s>>>(p);
+  if (p.part) {
+    const size_t n = (size_t)p.B * p.Cout * p.H * p.W;
+    conv3x3_tc_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p.part, p.ksplit, p.scale, p.shift, p.res, p.out, n, p.Cout, p.H * p.W, p.relu);
+  }
   return cudaGetLastError();
 }
 
 cudaError_t launch_conv3x3_tc(const ConvTcParams& p, cudaStream_t s) {
-  if (!conv3x3_tc_supported(p.Cin, p.C0, p.Cout)) return cudaErrorInvalidValue;
+  if (!conv3x3_tc_supported(p.Cin, p.C0, p.Cout) || p.ksplit < 1 || (p.ksplit > 1 && !p.part)) return cudaErrorInvalidValue;
   switch (ctc::tile_n(p.Cout)) {
     case 128: return launch_conv3x3_tc_n<128>(p, s);
     case 64: return launch_conv3x3_tc_n<64>(p, s);

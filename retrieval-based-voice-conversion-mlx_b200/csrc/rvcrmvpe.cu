@@ -29,7 +29,10 @@ struct ConvTcParams {
   const float* scale; const float* shift; const float* res;
   float* out;
   int B, Cout, H, W, relu;
+  float* part;
+  int ksplit;
 };
+int conv3x3_tc_splits(int Cin, int Cout, int HW, int B);
 bool conv3x3_tc_supported(int Cin, int C0, int Cout);
 size_t conv3x3_tc_image_elems(int Cin, int Cout);
 void conv3x3_tc_pack_host(const float* w, int Cin, int Cout, __half* img);
@@ -95,6 +98,8 @@ struct rvcrmvpe_handle {
   float* dev = nullptr;
   __half* dev16 = nullptr;
   bool keep_inter = false;
+  float* part = nullptr;     // split-K scratch of the current forward (in the caller's workspace)
+  size_t part_floats = 0;
   bool tc = true;            // those convolutions on the tensor cores (fp16 operands, fp32 accumulation); 0: all fp32
   float in_a = 1.f, in_c = 0.f;                 // encoder input BatchNorm (one channel)
   std::vector<Block> enc[LEVELS], inter[INTERS], dec[LEVELS];
@@ -313,7 +318,7 @@ namespace {
 struct MWs {
   float* buf[4];          // rotating activations, each B x 16 x T x 128 floats (the largest tensor of the U-Net)
   float* skip[LEVELS];    // encoder outputs kept for the decoder's concatenation
-  float *feat, *gi, *gout, *inter;
+  float *feat, *gi, *gout, *inter, *part;
   size_t bytes;
 };
 
@@ -327,7 +332,8 @@ MWs carve_m(void* base, int B, int T) {
   w.feat = take((size_t)B * T * GRU_IN);
   w.gi = take((size_t)B * T * 6 * GRU_HID);
   w.gout = take((size_t)B * T * 2 * GRU_HID);
-  w.inter = take((size_t)B * 512 * (T / 32) * 4);   // copy of the intermediate blocks' output (test hook, option keep_inter)
+  w.inter = take((size_t)B * 512 * (T / 32) * 4);
+  w.part = take((size_t)16 * B * 256 * T);  // split-K partial sums: at most 16 splits of the largest layer that may split (128 ch x T/8 x 16)   // copy of the intermediate blocks' output (test hook, option keep_inter)
   w.bytes = off;
   return w;
 }
@@ -342,7 +348,12 @@ int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float*
   auto conv3 = [&](const Conv2dParams& q, const ConvW& cw) -> cudaError_t {
     ++h->launches;
     if (h->tc && cw.has_img && conv3x3_tc_supported(q.Cin, q.C0, q.Cout)) {
-      ConvTcParams t{q.in0, q.in1, q.C0, q.Cin, h->dev16 + cw.img, q.scale, q.shift, q.res, q.out, q.B, q.Cout, q.H, q.W, q.relu};
+      ConvTcParams t{q.in0, q.in1, q.C0, q.Cin, h->dev16 + cw.img, q.scale, q.shift, q.res, q.out, q.B, q.Cout, q.H, q.W, q.relu, nullptr, 1};
+      const int sp = conv3x3_tc_splits(q.Cin, q.Cout, q.H * q.W, q.B);
+      if (sp > 1 && h->part && (size_t)sp * q.B * q.Cout * q.H * q.W <= h->part_floats) {
+        t.part = h->part; t.ksplit = sp;
+        ++h->launches;
+      }
       return launch_conv3x3_tc(t, s);
     }
     return launch_conv2d(q, 3, s);
@@ -399,6 +410,8 @@ int rvcrmvpe_forward(rvcrmvpe_handle* h, const float* mel, float* hidden, void* 
   MWs w = carve_m(workspace, B, T);
   const float* P = h->dev;
   h->launches = 0;
+  h->part = w.part;
+  h->part_floats = (size_t)16 * B * 256 * T;
   int rc;
   // mel (B, 128, T) -> (B, 1, T, 128), encoder input BatchNorm
   MCK(launch_mel_in(mel, w.buf[0], B, T, h->in_a, h->in_c, s)); ++h->launches;
