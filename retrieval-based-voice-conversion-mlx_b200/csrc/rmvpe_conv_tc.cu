@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
   constexpr int ntile = 1;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(full0 + 8 * s, 129); mbar_init(empty0 + 8 * s, 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full0 + 8 * s, 5); /* four producer warps + the weight loader's expect_tx */ mbar_init(empty0 + 8 * s, 1); }
     mbar_init(acc_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -118,7 +118,8 @@ __global__ void __launch_bounds__(ctc::THREADS, ctc::Geo<BN>::MIN_CTAS) conv3x3_
         }
       }
       fence_proxy_async();  // generic-proxy stores, read by the MMA through the async proxy
-      mbar_arrive(full0 + 8 * s);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(full0 + 8 * s);  // one arrival per warp
     }
     if (warp < 4) {
       // ===================== epilogue: thread = pixel = TMEM lane =====================
