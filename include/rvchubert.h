@@ -55,7 +55,8 @@ int64_t rvchubert_debug_read(rvchubert_handle* h, const char* name, float* dst, 
                              int32_t n_samples, void* stream);
 
 /* options: "tc" (default 1: the linear layers and strided convolutions as fp16-operand, fp32-accumulating tensor-core GEMMs,
- * ~6e-3 max error on the O(1) features; 0: fp32 CUDA-core GEMMs, 1e-5), "att_tc" (default 1; with tc: attention on the tensor
+ * ~6e-3 max error on the O(1) features; 0: fp32 CUDA-core GEMMs, 1e-5), "tma" (default 1; with tc: GEMM operands through
+ * 2-D tensor maps, 0: gathered with cp.async - same arithmetic), "att_tc" (default 1; with tc: attention on the tensor
  * cores from the fp16 q | k | v rows; 0: the fp32 attention kernel), "keep_layer0" (0 / 1, default 0: copy the first
  * transformer layer's output aside for rvchubert_debug_read). */
 int rvchubert_set_option(rvchubert_handle* h, const char* key, int64_t value);

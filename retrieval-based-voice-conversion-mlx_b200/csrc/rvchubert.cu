@@ -27,6 +27,8 @@ cudaError_t launch_hubert_feat0(const float* audio, size_t n, const float* w, co
 cudaError_t launch_hubert_posconv(const float* x, const float* wp, const float* bias, float* out, int B, int T, int C, cudaStream_t s);
 cudaError_t launch_hubert_attention(const float* qkv, float* ctx, __half* ctx16, int B, int T, int heads, cudaStream_t s);
 cudaError_t launch_hubert_att_tc(const __half* qkv16, __half* ctx16, int B, int T, int heads, cudaStream_t s);
+cudaError_t launch_gemm_tma(const __half* A, size_t lda, size_t strideA, const __half* W, const float* bias, const float* R, float* C32, __half* C16,
+                            size_t ldc, size_t strideC, int batch, int M, int N, int K, int act, cudaStream_t s);
 cudaError_t launch_gemm_tc(const __half* A, size_t lda, size_t strideA, const __half* W, const float* bias, const float* R, float* C32, __half* C16,
                            size_t ldc, size_t strideC, int batch, int M, int N, int K, int act, cudaStream_t s);
 }  // namespace rvcdec
@@ -81,6 +83,7 @@ void conv_lengths(int n, int L[NCONV]) {
 struct rvchubert_handle {
   int device = 0;
   bool loaded = false, has_proj = false, keep_layer0 = false;
+  bool tma = true;           // with tc: operands through tensor maps (gemm_tma.cu) instead of cp.async gathers (gemm_tc.cu)
   bool att_tc = true;        // with tc: attention on the tensor cores too (hubert_att_tc.cu)
   bool tc = true;            // GEMMs on the tensor cores with fp16 operands (gemm_tc.cu); 0: fp32 CUDA-core GEMMs
   float* dev = nullptr;
@@ -203,6 +206,7 @@ int rvchubert_set_option(rvchubert_handle* h, const char* key, int64_t value) {
   if (!strcmp(key, "keep_layer0")) { h->keep_layer0 = value != 0; return 0; }
   if (!strcmp(key, "tc")) { h->tc = value != 0; return 0; }
   if (!strcmp(key, "att_tc")) { h->att_tc = value != 0; return 0; }
+  if (!strcmp(key, "tma")) { h->tma = value != 0; return 0; }
   return hfail(RVCDEC_ERR_ARG, "unknown option %s", key);
 }
 
@@ -350,6 +354,7 @@ int rvchubert_forward(rvchubert_handle* h, const float* audio, float* hidden, vo
   auto linear = [&](const float* a32, const __half* a16, size_t lda, size_t strideA, size_t w, const float* bias, const float* res, float* c32,
                     __half* c16, size_t ldc, size_t strideC, int batch, int m, int n, int k, int act) -> cudaError_t {
     ++h->launches;
+    if (tc && h->tma) return launch_gemm_tma(a16, lda, strideA, P16 + w, bias, res, c32, c16, ldc, strideC, batch, m, n, k, act, s);
     if (tc) return launch_gemm_tc(a16, lda, strideA, P16 + w, bias, res, c32, c16, ldc, strideC, batch, m, n, k, act, s);
     return launch_gemm128(a32, lda, strideA, P + w, bias, res, c32, ldc, strideC, batch, m, n, k, act, s);
   };
