@@ -231,7 +231,7 @@ __global__ void hubert_feat0_affine_kernel(const double* __restrict__ stats, con
 // out[b][t][c] = gelu(scale[b][c] * sum_j w[c][j] a[b][5 t + j] + shift[b][c]);  32 frames x 512 channels per CTA
 __global__ void __launch_bounds__(256) hubert_feat0_kernel(const float* __restrict__ audio, size_t n, const float* __restrict__ w,
                                                            const float* __restrict__ scale, const float* __restrict__ shift, float* __restrict__ out,
-                                                           __half* __restrict__ out16, int L0, int Cout) {
+                                                           __half* __restrict__ out16, int L0, int Lstride, int Cout) {
   constexpr int TT = 32;
   __shared__ float as[TT * F0S + F0K];
   const int b = blockIdx.y, t0 = blockIdx.x * TT;
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(256) hubert_feat0_kernel(const float* __restri
 #pragma unroll
       for (int j = 0; j < F0K; ++j) y = fmaf(wv[j], as[tt * F0S + j], y);
       const float g = gelu_erf(fmaf(y, sc, sh));
-      const size_t o = ((size_t)b * L0 + t0 + tt) * Cout + c;
+      const size_t o = ((size_t)b * Lstride + t0 + tt) * Cout + c;
       if (out) out[o] = g;
       if (out16) out16[o] = __float2half_rn(g);
     }
@@ -259,12 +259,12 @@ __global__ void __launch_bounds__(256) hubert_feat0_kernel(const float* __restri
 }
 
 cudaError_t launch_hubert_feat0(const float* audio, size_t n, const float* w, const float* gamma, const float* beta, double* stats, float* scale,
-                                float* shift, float* out, __half* out16, int B, int L0, int Cout, float eps, cudaStream_t s) {
+                                float* shift, float* out, __half* out16, int B, int L0, int Lstride, int Cout, float eps, cudaStream_t s) {
   cudaError_t e = cudaMemsetAsync(stats, 0, (size_t)B * F0NS * sizeof(double), s);
   if (e != cudaSuccess) return e;
   hubert_feat0_stats_kernel<<<dim3((L0 + 4095) / 4096, B), 256, 0, s>>>(audio, n, L0, stats);
   hubert_feat0_affine_kernel<<<dim3((Cout + 127) / 128, B), 128, 0, s>>>(stats, w, gamma, beta, scale, shift, L0, Cout, eps);
-  hubert_feat0_kernel<<<dim3((L0 + 31) / 32, B), 256, 0, s>>>(audio, n, w, scale, shift, out, out16, L0, Cout);
+  hubert_feat0_kernel<<<dim3((L0 + 31) / 32, B), 256, 0, s>>>(audio, n, w, scale, shift, out, out16, L0, Lstride, Cout);
   return cudaGetLastError();
 }
 

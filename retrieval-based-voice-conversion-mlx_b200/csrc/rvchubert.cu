@@ -23,10 +23,11 @@ cudaError_t launch_gemm128(const float* A, size_t lda, size_t strideA, const flo
 cudaError_t launch_hubert_ln(const float* a, const float* b, const float* gamma, const float* beta, float* out, __half* out16, size_t rows, int C,
                              float eps, cudaStream_t s);
 cudaError_t launch_hubert_feat0(const float* audio, size_t n, const float* w, const float* gamma, const float* beta, double* stats, float* scale,
-                                float* shift, float* out, __half* out16, int B, int L0, int Cout, float eps, cudaStream_t s);
+                                float* shift, float* out, __half* out16, int B, int L0, int Lstride, int Cout, float eps, cudaStream_t s);
 cudaError_t launch_hubert_posconv(const float* x, const float* wp, const float* bias, float* out, int B, int T, int C, cudaStream_t s);
 cudaError_t launch_hubert_attention(const float* qkv, float* ctx, __half* ctx16, int B, int T, int heads, cudaStream_t s);
 cudaError_t launch_hubert_att_tc(const __half* qkv16, __half* ctx16, int B, int T, int heads, cudaStream_t s);
+cudaError_t launch_posconv_tma(const __half* x16, const __half* wimg, const float* bias, float* out, int B, int T, int C, cudaStream_t s);
 cudaError_t launch_gemm_tma(const __half* A, size_t lda, size_t strideA, const __half* W, const float* bias, const float* R, float* C32, __half* C16,
                             size_t ldc, size_t strideC, int batch, int M, int N, int K, int act, cudaStream_t s);
 cudaError_t launch_gemm_tc(const __half* A, size_t lda, size_t strideA, const __half* W, const float* bias, const float* R, float* C32, __half* C16,
@@ -88,6 +89,7 @@ struct rvchubert_handle {
   bool tc = true;            // GEMMs on the tensor cores with fp16 operands (gemm_tc.cu); 0: fp32 CUDA-core GEMMs
   float* dev = nullptr;
   __half* dev16 = nullptr;   // the GEMM weights once more in fp16, same offsets as in `dev`
+  __half* pc16 = nullptr;    // positional conv weights for the tensor-core kernel: [16 groups][128 taps][48 co][64 ci] (ci >= 48 zero)
   size_t conv_w[NCONV] = {}, gn_g = 0, gn_b = 0, fp_lng = 0, fp_lnb = 0, fp_w = 0, fp_b = 0, pos_w = 0, pos_b = 0, enc_lng = 0, enc_lnb = 0,
          proj_w = 0, proj_b = 0;
   LayerW layer[NLAYER] = {};
@@ -128,7 +130,7 @@ int push_named(std::vector<float>& host, const TMh& tm, const std::string& name,
 struct HWs {
   double* stats;
   float *scale, *shift, *bufA, *bufB, *featln, *xp, *pos, *emb, *x, *x1, *qkv, *ffn, *keep0;
-  __half *a16, *b16, *featln16, *in16, *ctx16, *x1_16, *ffn16, *qkv16;  // fp16 operands of the tensor-core mode
+  __half *a16, *b16, *featln16, *in16, *ctx16, *x1_16, *ffn16, *qkv16, *xp16;  // fp16 operands of the tensor-core mode
   size_t bytes;
 };
 
@@ -142,8 +144,9 @@ HWs carve_h(void* base, int B, int n) {
   w.stats = (double*)take((size_t)B * N_STATS * sizeof(double));
   w.scale = (float*)take((size_t)B * CONV_DIM * 4);
   w.shift = (float*)take((size_t)B * CONV_DIM * 4);
-  w.bufA = (float*)take((size_t)B * L[0] * CONV_DIM * 4);
-  w.bufB = (float*)take((size_t)B * L[1] * CONV_DIM * 4);
+  // items are L + (L & 1) frames apart: a stride-2 layer then reads the batch as one matrix of rows 2 * 512 apart (gemm_tma.cu)
+  w.bufA = (float*)take((size_t)B * (L[0] + 1) * CONV_DIM * 4);
+  w.bufB = (float*)take((size_t)B * (L[1] + 1) * CONV_DIM * 4);
   w.featln = (float*)take(rows * CONV_DIM * 4);
   w.xp = (float*)take(rows * HID * 4);
   w.pos = (float*)take(rows * HID * 4);   // positional conv output, then the attention context
@@ -153,14 +156,15 @@ HWs carve_h(void* base, int B, int n) {
   w.qkv = (float*)take(rows * 3 * HID * 4);
   w.ffn = (float*)take(rows * FFN * 4);
   w.keep0 = (float*)take(rows * HID * 4);
-  w.a16 = (__half*)take((size_t)B * L[0] * CONV_DIM * 2);
-  w.b16 = (__half*)take((size_t)B * L[1] * CONV_DIM * 2);
+  w.a16 = (__half*)take((size_t)B * (L[0] + 1) * CONV_DIM * 2);
+  w.b16 = (__half*)take((size_t)B * (L[1] + 1) * CONV_DIM * 2);
   w.featln16 = (__half*)take(rows * CONV_DIM * 2);
   w.in16 = (__half*)take(rows * HID * 2);
   w.ctx16 = (__half*)take(rows * HID * 2);
   w.x1_16 = (__half*)take(rows * HID * 2);
   w.ffn16 = (__half*)take(rows * FFN * 2);
   w.qkv16 = (__half*)take(rows * 3 * HID * 2);
+  w.xp16 = (__half*)take(rows * HID * 2);
   w.bytes = off;
   return w;
 }
@@ -185,10 +189,11 @@ int rvchubert_create(int device, rvchubert_handle** out) {
 
 void rvchubert_destroy(rvchubert_handle* h) {
   if (!h) return;
-  if (h->dev || h->dev16) {
+  if (h->dev || h->dev16 || h->pc16) {
     HGuard g(h->device);
     cudaFree(h->dev);
     cudaFree(h->dev16);
+    cudaFree(h->pc16);
   }
   delete h;
 }
@@ -215,6 +220,7 @@ int rvchubert_load_weights(rvchubert_handle* h, const rvcdec_tensor* tensors, in
   TMh tm;
   for (int i = 0; i < n; ++i) tm.m[tensors[i].name ? tensors[i].name : ""] = &tensors[i];
   std::vector<float> host;
+  std::vector<__half> pc_img;
   h->loaded = false;
   int rc = 0;
   // feature extractor (HubertFeatureEncoder, modeling_hubert.py:178-213; conv_bias = False)
@@ -271,6 +277,13 @@ int rvchubert_load_weights(rvchubert_handle* h, const rvcdec_tensor* tensors, in
           for (int co = 0; co < cg; ++co)
             dst[(((size_t)grp * cg + ci) * POS_K + j) * cg + co] = (float)(v->data[((size_t)(grp * cg + co) * cg + ci) * POS_K + j] * norm[j]);
     if ((rc = push_named(host, tm, p + "bias", HID, h->pos_b))) return rc;
+    pc_img.assign((size_t)POS_G * POS_K * cg * 64, __float2half_rn(0.f));
+    for (int grp = 0; grp < POS_G; ++grp)
+      for (int j = 0; j < POS_K; ++j)
+        for (int co = 0; co < cg; ++co)
+          for (int ci = 0; ci < cg; ++ci)
+            pc_img[(((size_t)grp * POS_K + j) * cg + co) * 64 + ci] =
+                __float2half_rn((float)(v->data[((size_t)(grp * cg + co) * cg + ci) * POS_K + j] * norm[j]));
   }
   if ((rc = push_named(host, tm, "encoder.layer_norm.weight", HID, h->enc_lng))) return rc;
   if ((rc = push_named(host, tm, "encoder.layer_norm.bias", HID, h->enc_lnb))) return rc;
@@ -317,6 +330,9 @@ int rvchubert_load_weights(rvchubert_handle* h, const rvcdec_tensor* tensors, in
     if (h->dev16) { HCK(cudaFree(h->dev16)); h->dev16 = nullptr; }
     HCK(cudaMalloc((void**)&h->dev16, h16.size() * sizeof(__half)));
     HCK(cudaMemcpy(h->dev16, h16.data(), h16.size() * sizeof(__half), cudaMemcpyHostToDevice));
+    if (h->pc16) { HCK(cudaFree(h->pc16)); h->pc16 = nullptr; }
+    HCK(cudaMalloc((void**)&h->pc16, pc_img.size() * sizeof(__half)));
+    HCK(cudaMemcpy(h->pc16, pc_img.data(), pc_img.size() * sizeof(__half), cudaMemcpyHostToDevice));
   }
   h->loaded = true;
   return 0;
@@ -360,23 +376,28 @@ int rvchubert_forward(rvchubert_handle* h, const float* audio, float* hidden, vo
   };
   // conv feature extractor: layer 0 with its GroupNorm, then six strided convs as GEMMs over k * 512-element rows
   HCK(launch_hubert_feat0(audio, (size_t)n_samples, P + h->conv_w[0], P + h->gn_g, P + h->gn_b, w.stats, w.scale, w.shift, tc ? nullptr : w.bufA,
-                          tc ? w.a16 : nullptr, B, L[0], CONV_DIM, LN_EPS, s));
+                          tc ? w.a16 : nullptr, B, L[0], L[0] + (L[0] & 1), CONV_DIM, LN_EPS, s));
   h->launches += 3;
   float *src = w.bufA, *dst = w.bufB;
   __half *src16 = w.a16, *dst16 = w.b16;
   for (int i = 1; i < NCONV; ++i) {
     const bool last = i == NCONV - 1;  // the last layer's output is kept in fp32 (layer norm input, "features" hook)
-    HCK(linear(src, src16, (size_t)CONV_S[i] * CONV_DIM, (size_t)L[i - 1] * CONV_DIM, h->conv_w[i], nullptr, nullptr, (tc && !last) ? nullptr : dst,
-               (tc && !last) ? dst16 : nullptr, CONV_DIM, (size_t)L[i] * CONV_DIM, B, L[i], CONV_DIM, CONV_K[i] * CONV_DIM, 1));
+    const size_t in_stride = (size_t)(L[i - 1] + (L[i - 1] & 1)) * CONV_DIM;
+    const size_t out_stride = last ? (size_t)L[i] * CONV_DIM : (size_t)(L[i] + (L[i] & 1)) * CONV_DIM;  // the features stay (B, T, 512)
+    HCK(linear(src, src16, (size_t)CONV_S[i] * CONV_DIM, in_stride, h->conv_w[i], nullptr, nullptr, (tc && !last) ? nullptr : dst,
+               (tc && !last) ? dst16 : nullptr, CONV_DIM, out_stride, B, L[i], CONV_DIM, CONV_K[i] * CONV_DIM, 1));
     float* t = src; src = dst; dst = t;
     __half* t16 = src16; src16 = dst16; dst16 = t16;
   }
   const float* feat = src;  // (B, T, 512): six swaps leave the result in bufA
   // feature projection (modeling_hubert.py:216-232)
   HCK(launch_hubert_ln(feat, nullptr, P + h->fp_lng, P + h->fp_lnb, tc ? nullptr : w.featln, tc ? w.featln16 : nullptr, rows, CONV_DIM, LN_EPS, s));
-  HCK(linear(w.featln, w.featln16, CONV_DIM, 0, h->fp_w, P + h->fp_b, nullptr, w.xp, nullptr, HID, 0, 1, M, HID, CONV_DIM, 0));
+  const bool pc_tc = tc && h->tma;
+  HCK(linear(w.featln, w.featln16, CONV_DIM, 0, h->fp_w, P + h->fp_b, nullptr, w.xp, pc_tc ? w.xp16 : nullptr, HID, 0, 1, M, HID, CONV_DIM, 0));
   // encoder front (modeling_hubert.py:437-440): x + gelu(pos_conv(x)), LayerNorm
-  HCK(launch_hubert_posconv(w.xp, P + h->pos_w, P + h->pos_b, w.pos, B, T, HID, s));
+  cudaError_t pe = pc_tc ? launch_posconv_tma(w.xp16, h->pc16, P + h->pos_b, w.pos, B, T, HID, s) : cudaErrorNotSupported;
+  if (pe == cudaErrorNotSupported) pe = launch_hubert_posconv(w.xp, P + h->pos_w, P + h->pos_b, w.pos, B, T, HID, s);
+  HCK(pe);
   HCK(launch_hubert_ln(w.xp, w.pos, P + h->enc_lng, P + h->enc_lnb, w.emb, tc ? w.in16 : nullptr, rows, HID, LN_EPS, s));
   h->launches += 3;
   const float* in = w.emb;
