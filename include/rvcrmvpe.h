@@ -53,7 +53,8 @@ int64_t rvcrmvpe_debug_read(rvcrmvpe_handle* h, const char* name, float* dst, in
 
 /* options: "tc" (default 1: the 3 x 3 convolutions with Cin % 64 == 0 and Cout % 128 == 0 - encoder levels 3-4, the intermediate
  * blocks, decoder levels 0-1 - as fp16-operand, fp32-accumulating implicit GEMMs on the tensor cores; 0: every layer in fp32),
- * "keep_inter" (0 / 1, default 0: test hook, see rvcrmvpe_debug_read). */
+ * "tma" (default 1; with tc: the convolutions with Cin % 64 == 0 read a channels-last fp16 copy of their input through tensor
+ * maps instead of gathering it per pixel - same arithmetic), "keep_inter" (0 / 1, default 0: test hook, see rvcrmvpe_debug_read). */
 int rvcrmvpe_set_option(rvcrmvpe_handle* h, const char* key, int64_t value);
 
 int64_t rvcrmvpe_last_launch_count(const rvcrmvpe_handle* h);

@@ -2,6 +2,7 @@
 // schedule of E2E(4, 1, (2, 2)) (rvc/lib/predictors/RMVPE.py:246-339) over the kernels of rmvpe_kernels.cu, mel front end and decode.
 #include <cuda_fp16.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -37,6 +38,12 @@ bool conv3x3_tc_supported(int Cin, int C0, int Cout);
 size_t conv3x3_tc_image_elems(int Cin, int Cout);
 void conv3x3_tc_pack_host(const float* w, int Cin, int Cout, __half* img);
 cudaError_t launch_conv3x3_tc(const ConvTcParams& p, cudaStream_t s);
+bool conv3x3_tma_supported(int Cin, int Cout);
+void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, __half* img);
+cudaError_t launch_rmvpe_to_nhwc16(const float* in0, const float* in1, int C0, int C, int B, int H, int W, __half* out, cudaStream_t s);
+cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const float* scale, const float* shift, const float* res, float* out32,
+                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, float* part, size_t part_floats, int* launches,
+                               cudaStream_t s);
 cudaError_t launch_convt2x(const float* in, const float* w, const float* scale, const float* shift, float* out, int B, int Cin, int Cout,
                            int H, int W, cudaStream_t s);
 cudaError_t launch_avgpool2(const float* in, float* out, size_t planes, int H, int W, cudaStream_t s);
@@ -82,7 +89,7 @@ constexpr int LEVELS = 5, INTERS = 4, BLOCKS = 4, C_BASE = 16, GRU_HID = 256, GR
 constexpr float BN_EPS = 1e-5f;
 
 // one convolution with its folded BatchNorm (or bias): offsets into the flat parameter array
-struct ConvW { size_t w = 0, scale = 0, shift = 0, img = 0; int cin = 0, cout = 0; bool has_scale = false, has_shift = false, has_img = false; };
+struct ConvW { size_t w = 0, scale = 0, shift = 0, img = 0, img2 = 0; int cin = 0, cout = 0; bool has_scale = false, has_shift = false, has_img = false, has_img2 = false; };
 // ConvBlockRes (RMVPE.py:13-57)
 struct Block { ConvW c1, c2, sc; bool shortcut = false; };
 
@@ -98,6 +105,11 @@ struct rvcrmvpe_handle {
   float* dev = nullptr;
   __half* dev16 = nullptr;
   bool keep_inter = false;
+  bool tma = true;           // with tc: 3 x 3 convolutions with Cin % 64 == 0 as TMA-fed implicit GEMMs (rmvpe_conv_tma.cu)
+  __half *t16 = nullptr, *y16[2] = {nullptr, nullptr};  // channels-last fp16 copies of the current forward (workspace)
+  int y16_cur = 0;
+  int T_ws = 0;              // frames of the current forward (sizes the fp16 buffers)
+  const float* y16_of = nullptr;  // the fp32 tensor whose copy is in y16[y16_cur] (valid between consecutive blocks of a level)
   float* part = nullptr;     // split-K scratch of the current forward (in the caller's workspace)
   size_t part_floats = 0;
   bool tc = true;            // those convolutions on the tensor cores (fp16 operands, fp32 accumulation); 0: all fp32
@@ -144,6 +156,12 @@ int load_conv_bn(rvcrmvpe_handle* h, const TM& tm, const std::string& conv, cons
     h->host16.resize(c.img + conv3x3_tc_image_elems(cin, cout));
     conv3x3_tc_pack_host(w->data, cin, cout, h->host16.data() + c.img);
     c.has_img = true;
+  }
+  if (pack_tc && ks == 3 && conv3x3_tma_supported(cin, cout)) {
+    c.img2 = (h->host16.size() + 127) / 128 * 128;
+    h->host16.resize(c.img2 + (size_t)9 * cout * cin);
+    conv3x3_tma_pack_host(w->data, cin, cout, h->host16.data() + c.img2);
+    c.has_img2 = true;
   }
   const rvcdec_tensor *g = tm.get(bn + ".weight", cout, &rc), *b = tm.get(bn + ".bias", cout, &rc), *mu = tm.get(bn + ".running_mean", cout, &rc),
                       *var = tm.get(bn + ".running_var", cout, &rc);
@@ -218,6 +236,7 @@ int rvcrmvpe_set_option(rvcrmvpe_handle* h, const char* key, int64_t value) {
   if (!h || !key) return mfail(RVCDEC_ERR_ARG, "null argument");
   if (!strcmp(key, "tc")) { h->tc = value != 0; return 0; }
   if (!strcmp(key, "keep_inter")) { h->keep_inter = value != 0; return 0; }
+  if (!strcmp(key, "tma")) { h->tma = value != 0; return 0; }
   return mfail(RVCDEC_ERR_ARG, "unknown option %s", key);
 }
 
@@ -319,6 +338,7 @@ struct MWs {
   float* buf[4];          // rotating activations, each B x 16 x T x 128 floats (the largest tensor of the U-Net)
   float* skip[LEVELS];    // encoder outputs kept for the decoder's concatenation
   float *feat, *gi, *gout, *inter, *part;
+  __half *t16, *y16a, *y16b;
   size_t bytes;
 };
 
@@ -333,6 +353,10 @@ MWs carve_m(void* base, int B, int T) {
   w.gi = take((size_t)B * T * 6 * GRU_HID);
   w.gout = take((size_t)B * T * 2 * GRU_HID);
   w.inter = take((size_t)B * 512 * (T / 32) * 4);
+  {  // three channels-last fp16 buffers, each large enough for the widest convolution input that takes the TMA path
+    const size_t halves = (size_t)B * (T + 2) * 130 * 32;
+    w.t16 = (__half*)take(halves / 2); w.y16a = (__half*)take(halves / 2); w.y16b = (__half*)take(halves / 2);
+  }
   w.part = take((size_t)16 * B * 256 * T);  // split-K partial sums: at most 16 splits of the largest layer that may split (128 ch x T/8 x 16)   // copy of the intermediate blocks' output (test hook, option keep_inter)
   w.bytes = off;
   return w;
@@ -342,6 +366,42 @@ MWs carve_m(void* base, int B, int T) {
 int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float* in1, int C0, int B, int H, int W, float* t1, float* t2,
               float* dst, cudaStream_t s) {
   const float* P = h->dev;
+  if (h->tc && h->tma && k.c1.has_img2 && k.c2.has_img2 && (in1 == nullptr || C0 % 8 == 0) &&
+      (size_t)B * (H + 2) * (W + 2) * (size_t)std::max(k.c1.cin, k.c1.cout) <= (size_t)B * (h->T_ws + 2) * 130 * 32) {
+    // both convolutions as TMA-fed implicit GEMMs over channels-last fp16 copies (rmvpe_conv_tma.cu)
+    const __half* x16;
+    if (in1 == nullptr && h->y16_of == in0) {
+      x16 = h->y16[h->y16_cur];  // left by the previous block's epilogue
+    } else {
+      h->y16_cur ^= 1;
+      MCK(launch_rmvpe_to_nhwc16(in0, in1, in1 ? C0 : k.c1.cin, k.c1.cin, B, H, W, h->y16[h->y16_cur], s)); ++h->launches;
+      x16 = h->y16[h->y16_cur];
+    }
+    int nl = 0;
+    cudaError_t e = launch_conv3x3_tma(x16, h->dev16 + k.c1.img2, P + k.c1.scale, P + k.c1.shift, nullptr, nullptr, h->t16, B, k.c1.cin, k.c1.cout, H, W,
+                                       1, h->part, h->part_floats, &nl, s);
+    if (e == cudaSuccess) {
+      h->launches += nl;
+      const float* res = in0;
+      if (k.shortcut) {
+        Conv2dParams q{};
+        q.in0 = in0; q.in1 = in1; q.C0 = C0; q.Cin = k.sc.cin; q.w = P + k.sc.w; q.shift = P + k.sc.shift;
+        q.out = t2; q.B = B; q.Cout = k.sc.cout; q.H = H; q.W = W;
+        MCK(launch_conv2d(q, 1, s)); ++h->launches;
+        res = t2;
+      }
+      __half* y16 = h->y16[h->y16_cur ^ 1];
+      MCK(launch_conv3x3_tma(h->t16, h->dev16 + k.c2.img2, P + k.c2.scale, P + k.c2.shift, res, dst, y16, B, k.c2.cin, k.c2.cout, H, W, 1, h->part,
+                             h->part_floats, &nl, s));
+      h->launches += nl;
+      h->y16_cur ^= 1;
+      h->y16_of = dst;
+      return 0;
+    }
+    if (e != cudaErrorNotSupported) MCK(e);
+    h->y16_of = nullptr;  // no tensor maps on this driver: the gathered kernels below
+  }
+  h->y16_of = nullptr;
   Conv2dParams p{};
   p.in0 = in0; p.in1 = in1; p.C0 = C0; p.Cin = k.c1.cin; p.w = P + k.c1.w; p.scale = P + k.c1.scale; p.shift = P + k.c1.shift;
   p.out = t1; p.B = B; p.Cout = k.c1.cout; p.H = H; p.W = W; p.relu = 1;
@@ -411,6 +471,8 @@ int rvcrmvpe_forward(rvcrmvpe_handle* h, const float* mel, float* hidden, void* 
   const float* P = h->dev;
   h->launches = 0;
   h->part = w.part;
+  h->T_ws = T;
+  h->t16 = w.t16; h->y16[0] = w.y16a; h->y16[1] = w.y16b; h->y16_cur = 0; h->y16_of = nullptr;
   h->part_floats = (size_t)16 * B * 256 * T;
   int rc;
   // mel (B, 128, T) -> (B, 1, T, 128), encoder input BatchNorm
@@ -425,6 +487,7 @@ int rvcrmvpe_forward(rvcrmvpe_handle* h, const float* mel, float* hidden, void* 
     if ((rc = run_blocks(h, h->enc[i], cur, nullptr, C, B, H, W, scratch, w.skip[i], s))) return rc;
     C = h->enc[i].back().c2.cout;
     MCK(launch_avgpool2(w.skip[i], scratch[0], (size_t)B * C, H, W, s)); ++h->launches;
+    h->y16_of = nullptr;  // scratch[0] now holds another tensor
     cur = scratch[0];
     H /= 2; W /= 2;
   }
@@ -452,6 +515,7 @@ int rvcrmvpe_forward(rvcrmvpe_handle* h, const float* mel, float* hidden, void* 
     for (int j = 0; j < 4; ++j) if (w.buf[j] != cur) fr[k++] = w.buf[j];
     const ConvW& u = h->up[i];
     MCK(launch_convt2x(cur, P + u.w, P + u.scale, P + u.shift, fr[0], B, u.cin, u.cout, H, W, s)); ++h->launches;
+    h->y16_of = nullptr;
     H *= 2; W *= 2; C = u.cout;
     // block 0 reads cat(fr[0], skip); internals fr[1], fr[2]; output -> cur (its old content, the level's input, is dead)
     if ((rc = run_block(h, h->dec[i][0], fr[0], w.skip[LEVELS - 1 - i], C, B, H, W, fr[1], fr[2], cur, s))) return rc;
