@@ -23,15 +23,19 @@
 namespace rvcdec {
 
 namespace ctm {
-constexpr int BM = 128, KB = 64, STAGES = 4;
-constexpr int A_TILE = BM * KB * 2;  // 16 KB
+constexpr int BM = 128, STAGES = 4;
 constexpr int THREADS = 192;         // warps 0-3 epilogue, 4 TMA producer, 5 MMA issuer
-template <int BN> struct Geo {
-  static constexpr int W_TILE = BN * KB * 2, STAGE = A_TILE + (W_TILE + 1023) / 1024 * 1024;
+// KB = channels per K step = min(Cin, 64): rows of 128 / 64 / 32 bytes, i.e. the 128- / 64- / 32-byte swizzle of TMA and UMMA
+template <int BN, int KB> struct Geo {
+  static constexpr int A_TILE = BM * KB * 2, W_TILE = BN * KB * 2, STAGE = A_TILE + (W_TILE + 1023) / 1024 * 1024;
   static constexpr int SMEM = 1024 + STAGES * STAGE + 8 * (2 * STAGES + 1) + 16;
+  static constexpr int MIN_CTAS = (KB == 64 && BN == 128) ? 1 : (KB == 64 ? 2 : 4);
 };
-__device__ __forceinline__ uint64_t sw128_desc(uint32_t addr) {
-  return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+// K-major operand tile written by TMA with the swizzle that matches its row length: 8-row atoms, 8 * row bytes apart
+template <int KB> __device__ __forceinline__ uint64_t sw_desc(uint32_t addr) {
+  constexpr uint64_t layout = KB == 64 ? 2 : (KB == 32 ? 4 : 6);  // SWIZZLE_128B / 64B / 32B
+  constexpr uint64_t sbo = 8 * KB * 2;
+  return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)1 << 16) | ((sbo >> 4) << 32) | ((uint64_t)1 << 46) | (layout << 61);
 }
 __device__ __forceinline__ void tma2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
@@ -50,10 +54,11 @@ struct ConvTmaParams {
   int ksplit;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(ctm::THREADS, 1) conv3x3_tma_kernel(const __grid_constant__ ConvTmaParams p) {
+template <int BN, int KB>
+__global__ void __launch_bounds__(ctm::THREADS, ctm::Geo<BN, KB>::MIN_CTAS) conv3x3_tma_kernel(const __grid_constant__ ConvTmaParams p) {
   using namespace ctm;
-  constexpr int STAGE = Geo<BN>::STAGE, W_TILE = Geo<BN>::W_TILE, OFF_BAR = STAGES * STAGE;
+  using G = Geo<BN, KB>;
+  constexpr int STAGE = G::STAGE, A_TILE = G::A_TILE, W_TILE = G::W_TILE, OFF_BAR = STAGES * STAGE;
   constexpr uint32_t TM_COLS = BN < 32 ? 32 : BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sg = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -101,7 +106,7 @@ __global__ void __launch_bounds__(ctm::THREADS, 1) conv3x3_tma_kernel(const __gr
       if (lane == 0) {
         const uint32_t sa = sb + s * STAGE, sw = sa + A_TILE;
 #pragma unroll
-        for (int ks = 0; ks < KB / 16; ++ks) tc_mma_f16(tm, sw128_desc(sa + ks * 32), sw128_desc(sw + ks * 32), idesc, (q | ks) ? 1u : 0u);
+        for (int ks = 0; ks < KB / 16; ++ks) tc_mma_f16(tm, sw_desc<KB>(sa + ks * 32), sw_desc<KB>(sw + ks * 32), idesc, (q | ks) ? 1u : 0u);
         tc_commit(empty0 + 8 * s);
         if (q == nk - 1) tc_commit(acc_full);
       }
@@ -248,7 +253,9 @@ __global__ void conv3x3_tma_finish_kernel(const float* __restrict__ part, int ks
   }
 }
 
-bool conv3x3_tma_supported(int Cin, int Cout) { return Cin % ctm::KB == 0 && (Cout == 32 || Cout == 64 || Cout % 128 == 0); }
+bool conv3x3_tma_supported(int Cin, int Cout) {
+  return (Cin == 16 || Cin == 32 || Cin % 64 == 0) && (Cout == 16 || Cout == 32 || Cout == 64 || Cout % 128 == 0);
+}
 
 // w (Cout, Cin, 3, 3) fp32 on the host -> [tap][Cout][Cin] fp16
 void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, __half* img) {
@@ -269,15 +276,16 @@ EncodeFn conv_encode_fn() {
   }();
   return fn;
 }
-bool map2d(const void* ptr, uint64_t inner, uint64_t rows, uint32_t box_rows, CUtensorMap* out) {
+bool map2d(const void* ptr, uint64_t inner, uint64_t rows, uint32_t kb, uint32_t box_rows, CUtensorMap* out) {
   EncodeFn fn = conv_encode_fn();
   if (!fn) return false;
   const cuuint64_t dims[2] = {inner, rows}, strides[1] = {inner * 2};
-  const cuuint32_t box[2] = {ctm::KB, box_rows}, es[2] = {1, 1};
-  return fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  const cuuint32_t box[2] = {kb, box_rows}, es[2] = {1, 1};
+  const CUtensorMapSwizzle sw = kb == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (kb == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+  return fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
-template <int BN>
+template <int BN, int KB>
 cudaError_t launch_n(ConvTmaParams& p, cudaStream_t s) {
   using namespace ctm;
   static bool attr_set[64] = {};
@@ -285,12 +293,12 @@ cudaError_t launch_n(ConvTmaParams& p, cudaStream_t s) {
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 64 && !attr_set[dev]) {
-    e = cudaFuncSetAttribute(conv3x3_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<BN>::SMEM);
+    e = cudaFuncSetAttribute(conv3x3_tma_kernel<BN, KB>, cudaFuncAttributeMaxDynamicSharedMemorySize, Geo<BN, KB>::SMEM);
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
   const long long R = (long long)p.B * (p.H + 2) * (p.W + 2);
-  conv3x3_tma_kernel<BN><<<dim3(p.Cout / BN, (unsigned)((R + BM - 1) / BM), p.ksplit), THREADS, Geo<BN>::SMEM, s>>>(p);
+  conv3x3_tma_kernel<BN, KB><<<dim3(p.Cout / BN, (unsigned)((R + BM - 1) / BM), p.ksplit), THREADS, Geo<BN, KB>::SMEM, s>>>(p);
   return cudaGetLastError();
 }
 }  // namespace
@@ -305,7 +313,8 @@ cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const flo
   const int BN = Cout >= 128 ? 128 : Cout;
   const long long R = (long long)B * (H + 2) * (W + 2);
   const long long ctas = (long long)(Cout / BN) * ((R + ctm::BM - 1) / ctm::BM);
-  const int nk = 9 * Cin / ctm::KB;
+  const int KBv = Cin >= 64 ? 64 : Cin;
+  const int nk = 9 * Cin / KBv;
   int sp = 1;
   if (part && ctas < 74 && nk >= 8) {
     sp = (int)((148 + ctas - 1) / ctas);
@@ -313,16 +322,22 @@ cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const flo
     if (sp > 16) sp = 16;
     if (sp < 2 || (size_t)sp * B * Cout * H * W > part_floats) sp = 1;
   }
-  if (!map2d(in16, (uint64_t)Cin, (uint64_t)B * (H + 2) * (W + 2), ctm::BM, &p.tmX) || !map2d(wimg, (uint64_t)Cin, (uint64_t)9 * Cout, (uint32_t)BN, &p.tmW))
+  if (!map2d(in16, (uint64_t)Cin, (uint64_t)B * (H + 2) * (W + 2), (uint32_t)KBv, ctm::BM, &p.tmX) ||
+      !map2d(wimg, (uint64_t)Cin, (uint64_t)9 * Cout, (uint32_t)KBv, (uint32_t)BN, &p.tmW))
     return cudaErrorNotSupported;
   p.scale = scale; p.shift = shift; p.res = res; p.out32 = out32; p.out16 = out16;
   p.B = B; p.Cin = Cin; p.Cout = Cout; p.H = H; p.W = W; p.relu = relu;
   p.part = sp > 1 ? part : nullptr; p.ksplit = sp;
   cudaError_t e = cudaErrorInvalidValue;
-  switch (BN) {
-    case 128: e = launch_n<128>(p, s); break;
-    case 64: e = launch_n<64>(p, s); break;
-    case 32: e = launch_n<32>(p, s); break;
+  switch (BN * 100 + KBv) {
+    case 12864: e = launch_n<128, 64>(p, s); break;
+    case 6464: e = launch_n<64, 64>(p, s); break;
+    case 6432: e = launch_n<64, 32>(p, s); break;
+    case 3264: e = launch_n<32, 64>(p, s); break;
+    case 3232: e = launch_n<32, 32>(p, s); break;
+    case 3216: e = launch_n<32, 16>(p, s); break;
+    case 1632: e = launch_n<16, 32>(p, s); break;
+    case 1616: e = launch_n<16, 16>(p, s); break;
   }
   if (launches) *launches = 1;
   if (e != cudaSuccess || sp == 1) return e;
