@@ -50,6 +50,7 @@ struct ConvTmaParams {
   float* out32;      // (B, Cout, H, W) or null
   __half* out16;     // padded channels-last (B, H + 2, W + 2, Cout) or null
   int B, Cin, Cout, H, W, relu;
+  int taps;      // 9 (3 x 3) or 1 (the 1 x 1 shortcut projection: centre tap only)
   float* part;   // split-K: raw partial sums [split][B][Cout][H W]; conv3x3_tma_finish_kernel reduces them and runs the epilogue
   int ksplit;
 };
@@ -67,7 +68,7 @@ __global__ void __launch_bounds__(ctm::THREADS, ctm::Geo<BN, KB>::MIN_CTAS) conv
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sg + OFF_BAR + 8 * (2 * STAGES + 1));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN, r0 = blockIdx.y * BM;
-  const int Hp = p.H + 2, Wp = p.W + 2, kcs = p.Cin / KB, nk_all = 9 * kcs, sp = blockIdx.z;
+  const int Hp = p.H + 2, Wp = p.W + 2, kcs = p.Cin / KB, nk_all = p.taps * kcs, sp = blockIdx.z;
   const int kbeg = (int)((long long)nk_all * sp / p.ksplit), nk = (int)((long long)nk_all * (sp + 1) / p.ksplit) - kbeg;  // this CTA's K steps
 
   if (threadIdx.x == 0) {
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(ctm::THREADS, ctm::Geo<BN, KB>::MIN_CTAS) conv
     if (lane == 0) {
       for (int q = 0; q < nk; ++q) {
         const int s = q % STAGES, tap = (kbeg + q) / kcs, kc = (kbeg + q) - tap * kcs;
-        const int dy = (tap * 11) >> 5, dx = tap - 3 * dy;  // tap / 3, tap % 3
+        const int dy = p.taps == 1 ? 1 : (tap * 11) >> 5, dx = p.taps == 1 ? 1 : tap - 3 * dy;  // tap / 3, tap % 3
         if (q >= STAGES) mbar_wait(empty0 + 8 * s, ((q / STAGES) - 1) & 1);
         const uint32_t sa = sb + s * STAGE, sw = sa + A_TILE;
         mbar_expect_tx(full0 + 8 * s, A_TILE + W_TILE);
@@ -257,11 +258,11 @@ bool conv3x3_tma_supported(int Cin, int Cout) {
   return (Cin == 16 || Cin == 32 || Cin % 64 == 0) && (Cout == 16 || Cout == 32 || Cout == 64 || Cout % 128 == 0);
 }
 
-// w (Cout, Cin, 3, 3) fp32 on the host -> [tap][Cout][Cin] fp16
-void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, __half* img) {
-  for (int tap = 0; tap < 9; ++tap)
+// w (Cout, Cin, k, k) fp32 on the host, k * k = taps (9 or 1) -> [tap][Cout][Cin] fp16
+void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, int taps, __half* img) {
+  for (int tap = 0; tap < taps; ++tap)
     for (int co = 0; co < Cout; ++co)
-      for (int ci = 0; ci < Cin; ++ci) img[((size_t)tap * Cout + co) * Cin + ci] = __float2half_rn(w[((size_t)co * Cin + ci) * 9 + tap]);
+      for (int ci = 0; ci < Cin; ++ci) img[((size_t)tap * Cout + co) * Cin + ci] = __float2half_rn(w[((size_t)co * Cin + ci) * taps + tap]);
 }
 
 namespace {
@@ -306,15 +307,15 @@ cudaError_t launch_n(ConvTmaParams& p, cudaStream_t s) {
 // in16: padded channels-last input (B, H + 2, W + 2, Cin); wimg: [9][Cout][Cin] fp16.  cudaErrorNotSupported: no tensor map -> caller falls back.
 // part / part_floats: scratch for split-K (used when the grid would leave most SMs idle: the deep levels), or null.
 cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const float* scale, const float* shift, const float* res, float* out32,
-                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, float* part, size_t part_floats, int* launches,
-                               cudaStream_t s) {
-  if (!conv3x3_tma_supported(Cin, Cout) || (!out32 && !out16)) return cudaErrorInvalidValue;
+                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, int taps, float* part, size_t part_floats,
+                               int* launches, cudaStream_t s) {
+  if (!conv3x3_tma_supported(Cin, Cout) || (!out32 && !out16) || (taps != 9 && taps != 1)) return cudaErrorInvalidValue;
   ConvTmaParams p;
   const int BN = Cout >= 128 ? 128 : Cout;
   const long long R = (long long)B * (H + 2) * (W + 2);
   const long long ctas = (long long)(Cout / BN) * ((R + ctm::BM - 1) / ctm::BM);
   const int KBv = Cin >= 64 ? 64 : Cin;
-  const int nk = 9 * Cin / KBv;
+  const int nk = taps * Cin / KBv;
   int sp = 1;
   if (part && ctas < 74 && nk >= 8) {
     sp = (int)((148 + ctas - 1) / ctas);
@@ -323,10 +324,10 @@ cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const flo
     if (sp < 2 || (size_t)sp * B * Cout * H * W > part_floats) sp = 1;
   }
   if (!map2d(in16, (uint64_t)Cin, (uint64_t)B * (H + 2) * (W + 2), (uint32_t)KBv, ctm::BM, &p.tmX) ||
-      !map2d(wimg, (uint64_t)Cin, (uint64_t)9 * Cout, (uint32_t)KBv, (uint32_t)BN, &p.tmW))
+      !map2d(wimg, (uint64_t)Cin, (uint64_t)taps * Cout, (uint32_t)KBv, (uint32_t)BN, &p.tmW))
     return cudaErrorNotSupported;
   p.scale = scale; p.shift = shift; p.res = res; p.out32 = out32; p.out16 = out16;
-  p.B = B; p.Cin = Cin; p.Cout = Cout; p.H = H; p.W = W; p.relu = relu;
+  p.B = B; p.Cin = Cin; p.Cout = Cout; p.H = H; p.W = W; p.relu = relu; p.taps = taps;
   p.part = sp > 1 ? part : nullptr; p.ksplit = sp;
   cudaError_t e = cudaErrorInvalidValue;
   switch (BN * 100 + KBv) {

@@ -39,11 +39,11 @@ size_t conv3x3_tc_image_elems(int Cin, int Cout);
 void conv3x3_tc_pack_host(const float* w, int Cin, int Cout, __half* img);
 cudaError_t launch_conv3x3_tc(const ConvTcParams& p, cudaStream_t s);
 bool conv3x3_tma_supported(int Cin, int Cout);
-void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, __half* img);
+void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, int taps, __half* img);
 cudaError_t launch_rmvpe_to_nhwc16(const float* in0, const float* in1, int C0, int C, int B, int H, int W, __half* out, cudaStream_t s);
 cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const float* scale, const float* shift, const float* res, float* out32,
-                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, float* part, size_t part_floats, int* launches,
-                               cudaStream_t s);
+                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, int taps, float* part, size_t part_floats,
+                               int* launches, cudaStream_t s);
 cudaError_t launch_convt2x(const float* in, const float* w, const float* scale, const float* shift, float* out, int B, int Cin, int Cout,
                            int H, int W, cudaStream_t s);
 cudaError_t launch_avgpool2(const float* in, float* out, size_t planes, int H, int W, cudaStream_t s);
@@ -160,7 +160,7 @@ int load_conv_bn(rvcrmvpe_handle* h, const TM& tm, const std::string& conv, cons
   if (pack_tc && ks == 3 && conv3x3_tma_supported(cin, cout)) {
     c.img2 = (h->host16.size() + 127) / 128 * 128;
     h->host16.resize(c.img2 + (size_t)9 * cout * cin);
-    conv3x3_tma_pack_host(w->data, cin, cout, h->host16.data() + c.img2);
+    conv3x3_tma_pack_host(w->data, cin, cout, 9, h->host16.data() + c.img2);
     c.has_img2 = true;
   }
   const rvcdec_tensor *g = tm.get(bn + ".weight", cout, &rc), *b = tm.get(bn + ".bias", cout, &rc), *mu = tm.get(bn + ".running_mean", cout, &rc),
@@ -189,6 +189,12 @@ int load_block(rvcrmvpe_handle* h, const TM& tm, const std::string& p, int cin, 
     blk.sc.w = push(h->host, w->data, (size_t)w->numel);
     blk.sc.shift = push(h->host, b->data, cout);
     blk.sc.has_shift = true;
+    if (conv3x3_tma_supported(cin, cout)) {  // the 1 x 1 projection through the same TMA kernel (one tap)
+      blk.sc.img2 = (h->host16.size() + 127) / 128 * 128;
+      h->host16.resize(blk.sc.img2 + (size_t)cout * cin);
+      conv3x3_tma_pack_host(w->data, cin, cout, 1, h->host16.data() + blk.sc.img2);
+      blk.sc.has_img2 = true;
+    }
   }
   return 0;
 }
@@ -379,11 +385,16 @@ int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float*
     }
     int nl = 0;
     cudaError_t e = launch_conv3x3_tma(x16, h->dev16 + k.c1.img2, P + k.c1.scale, P + k.c1.shift, nullptr, nullptr, h->t16, B, k.c1.cin, k.c1.cout, H, W,
-                                       1, h->part, h->part_floats, &nl, s);
+                                       1, 9, h->part, h->part_floats, &nl, s);
     if (e == cudaSuccess) {
       h->launches += nl;
       const float* res = in0;
-      if (k.shortcut) {
+      if (k.shortcut && k.sc.has_img2) {
+        MCK(launch_conv3x3_tma(x16, h->dev16 + k.sc.img2, nullptr, P + k.sc.shift, nullptr, t2, nullptr, B, k.sc.cin, k.sc.cout, H, W, 0, 1, nullptr, 0,
+                               &nl, s));
+        h->launches += nl;
+        res = t2;
+      } else if (k.shortcut) {
         Conv2dParams q{};
         q.in0 = in0; q.in1 = in1; q.C0 = C0; q.Cin = k.sc.cin; q.w = P + k.sc.w; q.shift = P + k.sc.shift;
         q.out = t2; q.B = B; q.Cout = k.sc.cout; q.H = H; q.W = W;
@@ -391,7 +402,7 @@ int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float*
         res = t2;
       }
       __half* y16 = h->y16[h->y16_cur ^ 1];
-      MCK(launch_conv3x3_tma(h->t16, h->dev16 + k.c2.img2, P + k.c2.scale, P + k.c2.shift, res, dst, y16, B, k.c2.cin, k.c2.cout, H, W, 1, h->part,
+      MCK(launch_conv3x3_tma(h->t16, h->dev16 + k.c2.img2, P + k.c2.scale, P + k.c2.shift, res, dst, y16, B, k.c2.cin, k.c2.cout, H, W, 1, 9, h->part,
                              h->part_floats, &nl, s));
       h->launches += nl;
       h->y16_cur ^= 1;
