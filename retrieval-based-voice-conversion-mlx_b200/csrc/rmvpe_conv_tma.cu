@@ -50,7 +50,9 @@ struct ConvTmaParams {
   float* out32;      // (B, Cout, H, W) or null
   __half* out16;     // padded channels-last (B, H + 2, W + 2, Cout) or null
   int B, Cin, Cout, H, W, relu;
-  int taps;      // 9 (3 x 3) or 1 (the 1 x 1 shortcut projection: centre tap only)
+  int taps;      // 9 (3 x 3), 1 (the 1 x 1 shortcut projection: centre tap only) or 4 (stride-2 transposed convolution, see up_cout)
+  int up_cout;   // taps == 4: Cout = 4 phases x up_cout channels; column (2 py + px) up_cout + co of input pixel (y, x) is output
+                 // pixel (2 y + py, 2 x + px) of channel co, fed by the input pixels (y + oy, x + ox), tap = 2 oy + ox
   float* part;   // split-K: raw partial sums [split][B][Cout][H W]; conv3x3_tma_finish_kernel reduces them and runs the epilogue
   int ksplit;
 };
@@ -93,7 +95,8 @@ __global__ void __launch_bounds__(ctm::THREADS, ctm::Geo<BN, KB>::MIN_CTAS) conv
         if (q >= STAGES) mbar_wait(empty0 + 8 * s, ((q / STAGES) - 1) & 1);
         const uint32_t sa = sb + s * STAGE, sw = sa + A_TILE;
         mbar_expect_tx(full0 + 8 * s, A_TILE + W_TILE);
-        tma2d(sa, &p.tmX, kc * KB, r0 + (dy - 1) * Wp + (dx - 1), full0 + 8 * s);
+        const int shift = p.taps == 4 ? (tap >> 1) * Wp + (tap & 1) : (dy - 1) * Wp + (dx - 1);
+        tma2d(sa, &p.tmX, kc * KB, r0 + shift, full0 + 8 * s);
         tma2d(sw, &p.tmW, kc * KB, tap * p.Cout + n0, full0 + 8 * s);
       }
     }
@@ -126,6 +129,19 @@ __global__ void __launch_bounds__(ctm::THREADS, ctm::Geo<BN, KB>::MIN_CTAS) conv
     const int HW = p.H * p.W, m = (yp - 1) * p.W + (xp - 1);
     const uint32_t tl = tm + ((uint32_t)(warp * 32) << 16);
     auto chunk = [&](int c0, const uint32_t* acc, int n) {  // n = 16 or 32 channels starting at n0 + c0
+      if (p.taps == 4) {  // transposed convolution: scatter the four phases into the (2 H, 2 W) fp32 tensor
+        if (inside) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            if (i >= n) break;
+            const int col = n0 + c0 + i, ph = col / p.up_cout, co = col - ph * p.up_cout;
+            float o = __uint_as_float(acc[i]) * (p.scale ? __ldg(p.scale + co) : 1.f) + (p.shift ? __ldg(p.shift + co) : 0.f);
+            if (p.relu) o = fmaxf(o, 0.f);
+            p.out32[(((size_t)b * p.up_cout + co) * (2 * p.H) + 2 * (yp - 1) + (ph >> 1)) * (2 * p.W) + 2 * (xp - 1) + (ph & 1)] = o;
+          }
+        }
+        return;
+      }
       if (p.part) {
         if (inside) {
 #pragma unroll
@@ -265,6 +281,19 @@ void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, int taps, __half* 
       for (int ci = 0; ci < Cin; ++ci) img[((size_t)tap * Cout + co) * Cin + ci] = __float2half_rn(w[((size_t)co * Cin + ci) * taps + tap]);
 }
 
+// ConvTranspose2d weight (Cin, Cout, 3, 3), stride 2, padding 1 -> [tap 4][phase 4 x Cout][Cin] fp16: tap = 2 oy + ox reads input pixel
+// (y + oy, x + ox); phase = 2 py + px writes output pixel (2 y + py, 2 x + px); kernel index k = p + 1 - 2 o (zero block if k < 0)
+void convt2x_tma_pack_host(const float* w, int Cin, int Cout, __half* img) {
+  for (int tap = 0; tap < 4; ++tap)
+    for (int ph = 0; ph < 4; ++ph) {
+      const int ky = (ph >> 1) + 1 - 2 * (tap >> 1), kx = (ph & 1) + 1 - 2 * (tap & 1);
+      for (int co = 0; co < Cout; ++co)
+        for (int ci = 0; ci < Cin; ++ci)
+          img[(((size_t)tap * 4 + ph) * Cout + co) * Cin + ci] =
+              __float2half_rn((ky < 0 || kx < 0) ? 0.f : w[(((size_t)ci * Cout + co) * 3 + ky) * 3 + kx]);
+    }
+}
+
 namespace {
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                              const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -307,9 +336,11 @@ cudaError_t launch_n(ConvTmaParams& p, cudaStream_t s) {
 // in16: padded channels-last input (B, H + 2, W + 2, Cin); wimg: [9][Cout][Cin] fp16.  cudaErrorNotSupported: no tensor map -> caller falls back.
 // part / part_floats: scratch for split-K (used when the grid would leave most SMs idle: the deep levels), or null.
 cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const float* scale, const float* shift, const float* res, float* out32,
-                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, int taps, float* part, size_t part_floats,
-                               int* launches, cudaStream_t s) {
-  if (!conv3x3_tma_supported(Cin, Cout) || (!out32 && !out16) || (taps != 9 && taps != 1)) return cudaErrorInvalidValue;
+                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, int taps, int up_cout, float* part,
+                               size_t part_floats, int* launches, cudaStream_t s) {
+  if (!conv3x3_tma_supported(Cin, Cout) || (!out32 && !out16) || (taps != 9 && taps != 1 && taps != 4)) return cudaErrorInvalidValue;
+  if (taps == 4 && (Cout != 4 * up_cout || !out32 || out16 || res)) return cudaErrorInvalidValue;
+  if (taps == 4) part = nullptr;
   ConvTmaParams p;
   const int BN = Cout >= 128 ? 128 : Cout;
   const long long R = (long long)B * (H + 2) * (W + 2);
@@ -327,7 +358,7 @@ cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const flo
       !map2d(wimg, (uint64_t)Cin, (uint64_t)taps * Cout, (uint32_t)KBv, (uint32_t)BN, &p.tmW))
     return cudaErrorNotSupported;
   p.scale = scale; p.shift = shift; p.res = res; p.out32 = out32; p.out16 = out16;
-  p.B = B; p.Cin = Cin; p.Cout = Cout; p.H = H; p.W = W; p.relu = relu; p.taps = taps;
+  p.B = B; p.Cin = Cin; p.Cout = Cout; p.H = H; p.W = W; p.relu = relu; p.taps = taps; p.up_cout = up_cout;
   p.part = sp > 1 ? part : nullptr; p.ksplit = sp;
   cudaError_t e = cudaErrorInvalidValue;
   switch (BN * 100 + KBv) {

@@ -40,10 +40,11 @@ void conv3x3_tc_pack_host(const float* w, int Cin, int Cout, __half* img);
 cudaError_t launch_conv3x3_tc(const ConvTcParams& p, cudaStream_t s);
 bool conv3x3_tma_supported(int Cin, int Cout);
 void conv3x3_tma_pack_host(const float* w, int Cin, int Cout, int taps, __half* img);
+void convt2x_tma_pack_host(const float* w, int Cin, int Cout, __half* img);
 cudaError_t launch_rmvpe_to_nhwc16(const float* in0, const float* in1, int C0, int C, int B, int H, int W, __half* out, cudaStream_t s);
 cudaError_t launch_conv3x3_tma(const __half* in16, const __half* wimg, const float* scale, const float* shift, const float* res, float* out32,
-                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, int taps, float* part, size_t part_floats,
-                               int* launches, cudaStream_t s);
+                               __half* out16, int B, int Cin, int Cout, int H, int W, int relu, int taps, int up_cout, float* part,
+                               size_t part_floats, int* launches, cudaStream_t s);
 cudaError_t launch_convt2x(const float* in, const float* w, const float* scale, const float* shift, float* out, int B, int Cin, int Cout,
                            int H, int W, cudaStream_t s);
 cudaError_t launch_avgpool2(const float* in, float* out, size_t planes, int H, int W, cudaStream_t s);
@@ -274,6 +275,13 @@ int rvcrmvpe_load_weights(rvcrmvpe_handle* h, const rvcdec_tensor* tensors, int3
     const std::string p = "unet.decoder.layers." + std::to_string(i);
     const int co = c / 2;
     if ((rc = load_conv_bn(h, tm, p + ".conv1.0", p + ".conv1.1", c, co, 3, h->up[i]))) return rc;  // ConvTranspose2d weight: (Cin, Cout, 3, 3)
+    if (conv3x3_tma_supported(c, 4 * co)) {  // the transposed convolution as a four-tap, four-phase GEMM (rmvpe_conv_tma.cu)
+      ConvW& u = h->up[i];
+      u.img2 = (h->host16.size() + 127) / 128 * 128;
+      h->host16.resize(u.img2 + (size_t)16 * co * c);
+      convt2x_tma_pack_host(h->host.data() + u.w, c, co, h->host16.data() + u.img2);
+      u.has_img2 = true;
+    }
     if ((rc = load_blocks(h, tm, p + ".conv2", 2 * co, co, h->dec[i]))) return rc;
     c = co;
   }
@@ -385,12 +393,12 @@ int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float*
     }
     int nl = 0;
     cudaError_t e = launch_conv3x3_tma(x16, h->dev16 + k.c1.img2, P + k.c1.scale, P + k.c1.shift, nullptr, nullptr, h->t16, B, k.c1.cin, k.c1.cout, H, W,
-                                       1, 9, h->part, h->part_floats, &nl, s);
+                                       1, 9, 0, h->part, h->part_floats, &nl, s);
     if (e == cudaSuccess) {
       h->launches += nl;
       const float* res = in0;
       if (k.shortcut && k.sc.has_img2) {
-        MCK(launch_conv3x3_tma(x16, h->dev16 + k.sc.img2, nullptr, P + k.sc.shift, nullptr, t2, nullptr, B, k.sc.cin, k.sc.cout, H, W, 0, 1, nullptr, 0,
+        MCK(launch_conv3x3_tma(x16, h->dev16 + k.sc.img2, nullptr, P + k.sc.shift, nullptr, t2, nullptr, B, k.sc.cin, k.sc.cout, H, W, 0, 1, 0, nullptr, 0,
                                &nl, s));
         h->launches += nl;
         res = t2;
@@ -402,7 +410,7 @@ int run_block(rvcrmvpe_handle* h, const Block& k, const float* in0, const float*
         res = t2;
       }
       __half* y16 = h->y16[h->y16_cur ^ 1];
-      MCK(launch_conv3x3_tma(h->t16, h->dev16 + k.c2.img2, P + k.c2.scale, P + k.c2.shift, res, dst, y16, B, k.c2.cin, k.c2.cout, H, W, 1, 9, h->part,
+      MCK(launch_conv3x3_tma(h->t16, h->dev16 + k.c2.img2, P + k.c2.scale, P + k.c2.shift, res, dst, y16, B, k.c2.cin, k.c2.cout, H, W, 1, 9, 0, h->part,
                              h->part_floats, &nl, s));
       h->launches += nl;
       h->y16_cur ^= 1;
@@ -525,7 +533,23 @@ int rvcrmvpe_forward(rvcrmvpe_handle* h, const float* mel, float* hidden, void* 
     float* fr[3]; int k = 0;
     for (int j = 0; j < 4; ++j) if (w.buf[j] != cur) fr[k++] = w.buf[j];
     const ConvW& u = h->up[i];
-    MCK(launch_convt2x(cur, P + u.w, P + u.scale, P + u.shift, fr[0], B, u.cin, u.cout, H, W, s)); ++h->launches;
+    bool up_done = false;
+    if (h->tc && h->tma && u.has_img2 && (size_t)(H + 2) * (W + 2) * u.cin <= (size_t)(T + 2) * 130 * 32) {
+      const __half* x16;
+      if (h->y16_of == cur) {
+        x16 = h->y16[h->y16_cur];
+      } else {
+        h->y16_cur ^= 1;
+        MCK(launch_rmvpe_to_nhwc16(cur, nullptr, u.cin, u.cin, B, H, W, h->y16[h->y16_cur], s)); ++h->launches;
+        x16 = h->y16[h->y16_cur];
+      }
+      int nl = 0;
+      cudaError_t e = launch_conv3x3_tma(x16, h->dev16 + u.img2, P + u.scale, P + u.shift, nullptr, fr[0], nullptr, B, u.cin, 4 * u.cout, H, W, 1, 4,
+                                         u.cout, nullptr, 0, &nl, s);
+      if (e == cudaSuccess) { h->launches += nl; up_done = true; }
+      else if (e != cudaErrorNotSupported) MCK(e);
+    }
+    if (!up_done) { MCK(launch_convt2x(cur, P + u.w, P + u.scale, P + u.shift, fr[0], B, u.cin, u.cout, H, W, s)); ++h->launches; }
     h->y16_of = nullptr;
     H *= 2; W *= 2; C = u.cout;
     // block 0 reads cat(fr[0], skip); internals fr[1], fr[2]; output -> cur (its old content, the level's input, is dead)
