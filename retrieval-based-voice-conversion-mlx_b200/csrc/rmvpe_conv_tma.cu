@@ -23,10 +23,13 @@
 namespace rvcdec {
 
 namespace ctm {
-constexpr int BM = 128, STAGES = 4;
+constexpr int BM = 128;
 constexpr int THREADS = 192;         // warps 0-3 epilogue, 4 TMA producer, 5 MMA issuer
 // KB = channels per K step = min(Cin, 64): rows of 128 / 64 / 32 bytes, i.e. the 128- / 64- / 32-byte swizzle of TMA and UMMA
+// A CTA of the shallow levels has only nine K steps (profiles/r2bo_*: ~8 us per CTA, the epilogue warps wait for the accumulator
+// 37 % of the time); keeping all nine steps in flight at once changed nothing measurable - what is left is per-CTA set-up.
 template <int BN, int KB> struct Geo {
+  static constexpr int STAGES = KB == 16 ? 9 : (KB == 32 ? 5 : 4);
   static constexpr int A_TILE = BM * KB * 2, W_TILE = BN * KB * 2, STAGE = A_TILE + (W_TILE + 1023) / 1024 * 1024;
   static constexpr int SMEM = 1024 + STAGES * STAGE + 8 * (2 * STAGES + 1) + 16;
   static constexpr int MIN_CTAS = (KB == 64 && BN == 128) ? 1 : (KB == 64 ? 2 : 4);
@@ -61,7 +64,7 @@ template <int BN, int KB>
 __global__ void __launch_bounds__(ctm::THREADS, ctm::Geo<BN, KB>::MIN_CTAS) conv3x3_tma_kernel(const __grid_constant__ ConvTmaParams p) {
   using namespace ctm;
   using G = Geo<BN, KB>;
-  constexpr int STAGE = G::STAGE, A_TILE = G::A_TILE, W_TILE = G::W_TILE, OFF_BAR = STAGES * STAGE;
+  constexpr int STAGES = G::STAGES, STAGE = G::STAGE, A_TILE = G::A_TILE, W_TILE = G::W_TILE, OFF_BAR = STAGES * STAGE;
   constexpr uint32_t TM_COLS = BN < 32 ? 32 : BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sg = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);

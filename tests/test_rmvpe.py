@@ -90,7 +90,7 @@ def test_mel_filterbank_and_stft_restatement():
 
 
 # salience (0..1) / tap tolerances: fp32 mode; tensor-core mode (deep 3 x 3 convolutions with fp16 operands)
-TOL = {0: dict(tap=1e-4, hidden=1e-5), 1: dict(tap=1e-3, hidden=1e-4)}
+TOL = {0: dict(tap=1e-4, hidden=1e-5), 1: dict(tap=3e-3, hidden=3e-4)}
 
 
 @pytest.mark.gpu
@@ -178,4 +178,4 @@ def test_predictor_pipeline_against_the_oracle():
     cents = float(np.abs(1200 * np.log2(f0_tc[voiced] / f0[voiced])).max()) if voiced.any() else 0.0
     record_parity({"test": "rmvpe_pipeline_tc_vs_fp32", "hidden_max_abs": e_hid_tc, "f0_max_cents": cents,
                    "voicing_flips": int(((f0 > 0) != (f0_tc > 0)).sum()), "frames": int(f0.shape[0])})
-    assert e_hid_tc <= 1e-4, e_hid_tc
+    assert e_hid_tc <= 3e-4, e_hid_tc
