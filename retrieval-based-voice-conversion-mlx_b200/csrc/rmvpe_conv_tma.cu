@@ -253,12 +253,20 @@ __global__ void conv3x3_tma_finish_kernel(const float* __restrict__ part, int ks
   if (yp >= 1 && yp <= H && xp >= 1 && xp <= W) {
     const int m = (yp - 1) * W + (xp - 1);
     const size_t n = (size_t)B * Cout * HW;
+    const size_t oi0 = ((size_t)b * Cout + g * 8) * HW + m;
+    float a8[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) a8[e] = 0.f;
+    for (int s = 0; s < ksplit; ++s) {  // splits outermost: the eight channels' loads of a split are in flight together
+      const float* ps = part + (size_t)s * n + oi0;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) a8[e] += __ldg(ps + (size_t)e * HW);
+    }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int co = g * 8 + e;
-      const size_t oi = ((size_t)b * Cout + co) * HW + m;
-      float a = 0.f;
-      for (int s = 0; s < ksplit; ++s) a += part[(size_t)s * n + oi];
+      const size_t oi = oi0 + (size_t)e * HW;
+      const float a = a8[e];
       float o = a * (scale ? __ldg(scale + co) : 1.f) + (shift ? __ldg(shift + co) : 0.f);
       if (relu) o = fmaxf(o, 0.f);
       if (res) o += res[oi];
