@@ -27,6 +27,7 @@ cudaError_t launch_hubert_feat0(const float* audio, size_t n, const float* w, co
 cudaError_t launch_hubert_posconv(const float* x, const float* wp, const float* bias, float* out, int B, int T, int C, cudaStream_t s);
 cudaError_t launch_hubert_attention(const float* qkv, float* ctx, __half* ctx16, int B, int T, int heads, cudaStream_t s);
 cudaError_t launch_hubert_att_tc(const __half* qkv16, __half* ctx16, int B, int T, int heads, cudaStream_t s);
+cudaError_t launch_hubert_att_tma(const __half* qkv16, __half* ctx16, int B, int T, int heads, cudaStream_t s);
 cudaError_t launch_posconv_tma(const __half* x16, const __half* wimg, const float* bias, float* out, int B, int T, int C, cudaStream_t s);
 cudaError_t launch_gemm_tma(const __half* A, size_t lda, size_t strideA, const __half* W, const float* bias, const float* R, float* C32, __half* C16,
                             size_t ldc, size_t strideC, int batch, int M, int N, int K, int act, cudaStream_t s);
@@ -405,7 +406,11 @@ int rvchubert_forward(rvchubert_handle* h, const float* audio, float* hidden, vo
     const LayerW& Lw = h->layer[i];
     const bool atc = tc && h->att_tc;
     HCK(linear(in, w.in16, HID, 0, Lw.wqkv, P + Lw.bqkv, nullptr, atc ? nullptr : w.qkv, atc ? w.qkv16 : nullptr, 3 * HID, 0, 1, M, 3 * HID, HID, 0));
-    if (atc) HCK(launch_hubert_att_tc(w.qkv16, w.ctx16, B, T, HEADS, s));
+    if (atc) {
+      cudaError_t ae = h->tma ? launch_hubert_att_tma(w.qkv16, w.ctx16, B, T, HEADS, s) : cudaErrorNotSupported;
+      if (ae == cudaErrorNotSupported) ae = launch_hubert_att_tc(w.qkv16, w.ctx16, B, T, HEADS, s);
+      HCK(ae);
+    }
     else HCK(launch_hubert_attention(w.qkv, tc ? nullptr : w.pos, tc ? w.ctx16 : nullptr, B, T, HEADS, s));
     HCK(linear(w.pos, w.ctx16, HID, 0, Lw.wo, P + Lw.bo, in, w.x1, nullptr, HID, 0, 1, M, HID, HID, 0));
     HCK(launch_hubert_ln(w.x1, nullptr, P + Lw.ln1g, P + Lw.ln1b, w.x1, tc ? w.x1_16 : nullptr, rows, HID, LN_EPS, s));
