@@ -179,3 +179,23 @@ def test_predictor_pipeline_against_the_oracle():
     record_parity({"test": "rmvpe_pipeline_tc_vs_fp32", "hidden_max_abs": e_hid_tc, "f0_max_cents": cents,
                    "voicing_flips": int(((f0 > 0) != (f0_tc > 0)).sum()), "frames": int(f0.shape[0])})
     assert e_hid_tc <= 3e-4, e_hid_tc
+
+
+@pytest.mark.gpu
+def test_long_clip_modes_agree():
+    """T = 1024 frames, B = 2: every convolution level has several tiles and the deep levels split K; the tensor-core modes
+    (TMA-fed, gathered) against the fp32 mode on the same weights."""
+    d = _golden()
+    dev = torch.device("cuda", 0)
+    m = _seeded_module(d).to(dev)
+    mel = (torch.randn(2, 128, 1024, generator=torch.Generator().manual_seed(9)) * 2 - 4).to(dev)
+    outs = {}
+    for name, (tc, tma) in {"fp32": (0, 0), "tma": (1, 1), "gathered": (1, 0)}.items():
+        m.set_option("tc", tc)
+        m.set_option("tma", tma)
+        outs[name] = m(mel).clone()
+    e_tma = float((outs["tma"] - outs["fp32"]).abs().max())
+    e_gat = float((outs["gathered"] - outs["fp32"]).abs().max())
+    record_parity({"test": "rmvpe_long_clip_modes", "frames": 1024, "tma_vs_fp32_max_abs": e_tma, "gathered_vs_fp32_max_abs": e_gat})
+    assert e_tma <= 3e-4 and e_gat <= 3e-4, (e_tma, e_gat)
+    assert e_tma > 0 and e_gat > 0   # the tensor-core paths did run
