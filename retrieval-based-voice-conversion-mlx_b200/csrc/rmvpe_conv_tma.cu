@@ -27,7 +27,8 @@ constexpr int BM = 128;
 constexpr int THREADS = 192;         // warps 0-3 epilogue, 4 TMA producer, 5 MMA issuer
 // KB = channels per K step = min(Cin, 64): rows of 128 / 64 / 32 bytes, i.e. the 128- / 64- / 32-byte swizzle of TMA and UMMA
 // A CTA of the shallow levels has only nine K steps (profiles/r2bo_*: ~8 us per CTA, the epilogue warps wait for the accumulator
-// 37 % of the time); keeping all nine steps in flight at once changed nothing measurable - what is left is per-CTA set-up.
+// 37 % of the time); keeping all nine steps in flight at once changed nothing measurable, and four pixel tiles per CTA made it
+// slower (5 s clip 2.8 -> 3.5 ms): the shallow levels want MORE CTAs in flight, not fewer set-ups.
 template <int BN, int KB> struct Geo {
   static constexpr int STAGES = KB == 16 ? 9 : (KB == 32 ? 5 : 4);
   static constexpr int A_TILE = BM * KB * 2, W_TILE = BN * KB * 2, STAGE = A_TILE + (W_TILE + 1023) / 1024 * 1024;
