@@ -28,12 +28,13 @@ constexpr int THREADS = 192;         // warps 0-3 epilogue, 4 TMA producer, 5 MM
 // KB = channels per K step = min(Cin, 64): rows of 128 / 64 / 32 bytes, i.e. the 128- / 64- / 32-byte swizzle of TMA and UMMA
 // A CTA of the shallow levels has only nine K steps (profiles/r2bo_*: ~8 us per CTA, the epilogue warps wait for the accumulator
 // 37 % of the time); keeping all nine steps in flight at once changed nothing measurable, and four pixel tiles per CTA made it
-// slower (5 s clip 2.8 -> 3.5 ms): the shallow levels want MORE CTAs in flight, not fewer set-ups.
+// slower (5 s clip 2.8 -> 3.5 ms): the shallow levels want MORE CTAs in flight, not fewer set-ups - six per SM instead of four
+// (56 registers, 30 KB of stages each) took 5 min of audio from 60.8 to 57.4 ms; eight do not fit the registers of tcgen05.ld.
 template <int BN, int KB> struct Geo {
-  static constexpr int STAGES = KB == 16 ? 9 : (KB == 32 ? 5 : 4);
+  static constexpr int STAGES = KB == 16 ? 6 : (KB == 32 ? 3 : 4);  // sized so that six CTAs of the shallow variants share an SM
   static constexpr int A_TILE = BM * KB * 2, W_TILE = BN * KB * 2, STAGE = A_TILE + (W_TILE + 1023) / 1024 * 1024;
   static constexpr int SMEM = 1024 + STAGES * STAGE + 8 * (2 * STAGES + 1) + 16;
-  static constexpr int MIN_CTAS = (KB == 64 && BN == 128) ? 1 : (KB == 64 ? 2 : 4);
+  static constexpr int MIN_CTAS = (KB == 64 && BN == 128) ? 1 : (KB == 64 ? 2 : 6);
 };
 // K-major operand tile written by TMA with the swizzle that matches its row length: 8-row atoms, 8 * row bytes apart
 template <int KB> __device__ __forceinline__ uint64_t sw_desc(uint32_t addr) {
