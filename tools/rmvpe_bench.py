@@ -47,6 +47,11 @@ def main():
         out[f"{secs}s"] = {"frames": int(f0.shape[0]), "infer_from_audio_s": min(ts), "audio_s_per_s": secs / min(ts),
                            "mel_ms": ev(lambda: p.mel_extractor(a)), "model_ms": ev(lambda: p.mel2hidden(mel)),
                            "decode_ms": ev(lambda: p.decode(hid[0])), "launches_model": p.model.last_launch_count}
+    # batched model call (the U-Net and the GRU clusters of different items run side by side): 8 x 30 s
+    B, T = 8, 3008
+    melb = torch.randn(B, 128, T, device=dev) * 2 - 4
+    ms = ev(lambda: p.model(melb))
+    out["batch_8x30s"] = {"B": B, "frames": T, "model_ms": ms, "audio_s_per_s": B * T / 100.0 / (ms * 1e-3)}
     print(json.dumps(out, indent=1))
 
 
