@@ -9,7 +9,8 @@ product path: file I/O, resampling, index retrieval, chunking of long clips and 
       -> net_g.infer (:367), crop of the padding (:527)
 
 Random weights (no network for checkpoints).  Host waveform in, host waveform out, wall clock.
-python tools/pipeline_bench.py [seconds] > gpurun_out/pipeline.json"""
+python tools/pipeline_bench.py [seconds] [batch] > gpurun_out/pipeline.json
+With batch > 1 the same clip is converted `batch` times in one pass (the throughput form: every stage takes a batch)."""
 import json
 import os
 import sys
@@ -36,6 +37,7 @@ def coarse_pitch(f0: torch.Tensor) -> torch.Tensor:
 
 def main():
     secs = float(sys.argv[1]) if len(sys.argv) > 1 else 13.5
+    NB = int(sys.argv[2]) if len(sys.argv) > 2 else 1
     dev = torch.device("cuda", 0)
     torch.manual_seed(1234)
     hubert = rvc_b200.HubertModelWithFinalProj().eval()
@@ -45,7 +47,7 @@ def main():
     n = int(secs * SR)
     t = np.arange(n) / SR
     audio = (0.4 * np.sin(2 * np.pi * (180 * t + 4 * np.sin(2 * np.pi * 4 * t))) + 0.02 * np.random.default_rng(0).standard_normal(n)).astype(np.float32)
-    sid = torch.zeros(1, dtype=torch.long, device=dev)
+    sid = torch.zeros(NB, dtype=torch.long, device=dev)
     stages = {}
 
     def convert(audio_np, record=False):
@@ -57,12 +59,12 @@ def main():
         t0 = time.perf_counter()
         audio_pad = np.pad(audio_np, (t_pad, t_pad), mode="reflect")                       # pipeline.py:458
         p_len = audio_pad.shape[0] // WINDOW
-        a = torch.from_numpy(audio_pad).to(dev, non_blocking=True).unsqueeze(0)
+        a = torch.from_numpy(audio_pad).to(dev, non_blocking=True).unsqueeze(0).expand(NB, -1).contiguous()
         mark("pad_h2d", t0)
         t0 = time.perf_counter()
         hidden = rmvpe.mel2hidden(rmvpe.mel_extractor(a))                                 # get_f0 (:200-246), RMVPE.py:497-513
-        f0 = rmvpe.decode(hidden[0], 0.03)[:p_len]
-        pitch, pitchf = coarse_pitch(f0).unsqueeze(0), f0.unsqueeze(0)                    # :282-291
+        f0 = torch.stack([rmvpe.decode(hidden[i], 0.03)[:p_len] for i in range(NB)])
+        pitch, pitchf = coarse_pitch(f0), f0                                              # :282-291
         mark("rmvpe_f0", t0)
         t0 = time.perf_counter()
         feats = hubert(a)["last_hidden_state"]                                            # :331 (v2: no final_proj)
@@ -71,9 +73,10 @@ def main():
         feats, pitch, pitchf = feats[:, :p].contiguous(), pitch[:, :p].contiguous(), pitchf[:, :p].contiguous()
         mark("hubert", t0)
         t0 = time.perf_counter()
-        lens = torch.tensor([p], device=dev).long()
-        out = net_g.infer(feats.float(), lens, pitch, pitchf.float(), sid)[0][0, 0]       # :367
-        y = out[t_pad_tgt:-t_pad_tgt].cpu().numpy()                                       # :527
+        lens = torch.full((NB,), p, device=dev).long()
+        out = net_g.infer(feats.float(), lens, pitch, pitchf.float(), sid)[0][:, 0]       # :367
+        y = out[:, t_pad_tgt:-t_pad_tgt].cpu().numpy()                                    # :527
+        y = y[0] if NB == 1 else y
         mark("net_g_infer_d2h", t0)
         return y
 
@@ -85,9 +88,9 @@ def main():
         y = convert(audio)
         ts.append(time.perf_counter() - t0)
     convert(audio, record=True)
-    assert np.isfinite(y).all() and abs(y.shape[0] - int(secs * TGT_SR)) <= 3 * 480, y.shape  # HuBERT yields 2 frames fewer than audio // 160, as in the reference
+    assert np.isfinite(y).all() and abs(y.shape[-1] - int(secs * TGT_SR)) <= 3 * 480, y.shape  # HuBERT yields 2 frames fewer than audio // 160, as in the reference
     best = min(ts)
-    print(json.dumps({"clip_seconds": secs, "output_samples": int(y.shape[0]), "pipeline_s": best, "realtime_factor": secs / best,
+    print(json.dumps({"clip_seconds": secs, "batch": NB, "output_samples": int(y.shape[-1]), "pipeline_s": best, "realtime_factor": NB * secs / best,
                       "stage_ms_with_syncs": stages,
                       "published_reference": {"mlx_s": 1.27, "pytorch_mps_s": 11.08, "hardware": "M3 Max", "source": "BASELINE.md / reference README.md:22-29"},
                       "data": "synthetic tone + noise, random weights"}, indent=1))
