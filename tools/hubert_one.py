@@ -1,4 +1,4 @@
-"""One 30 s forward of the HuBERT embedder (for an ncu launch list): python tools/hubert_one.py [seconds]"""
+"""One forward of the HuBERT embedder (for an ncu launch list): python tools/hubert_one.py [seconds] [batch]"""
 import os
 import sys
 
@@ -9,9 +9,10 @@ import torch  # noqa: E402
 import rvc_b200  # noqa: E402
 
 secs = float(sys.argv[1]) if len(sys.argv) > 1 else 30.0
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 torch.manual_seed(1)
 m = rvc_b200.HubertModelWithFinalProj().eval()
-a = (0.3 * torch.randn(1, int(secs * 16000))).cuda()
+a = (0.3 * torch.randn(B, int(secs * 16000))).cuda()
 m(a)
 torch.cuda.synchronize()
 y = m(a)["last_hidden_state"]
