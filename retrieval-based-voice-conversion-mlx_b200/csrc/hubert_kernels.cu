@@ -241,19 +241,23 @@ __global__ void __launch_bounds__(256) hubert_feat0_kernel(const float* __restri
     as[i] = p < n ? __ldg(a + p) : 0.f;
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < Cout; c += 256) {
-    float wv[F0K];
+  for (int c = 2 * threadIdx.x; c < Cout; c += 512) {  // two adjacent channels per thread: 4- / 8-byte stores, a warp writes 128 / 256 B
+    float w0[F0K], w1[F0K];
 #pragma unroll
-    for (int j = 0; j < F0K; ++j) wv[j] = __ldg(w + c * F0K + j);
-    const float sc = scale[(size_t)b * Cout + c], sh = shift[(size_t)b * Cout + c];
+    for (int j = 0; j < F0K; ++j) { w0[j] = __ldg(w + c * F0K + j); w1[j] = __ldg(w + (c + 1) * F0K + j); }
+    const float2 sc = *reinterpret_cast<const float2*>(scale + (size_t)b * Cout + c), sh = *reinterpret_cast<const float2*>(shift + (size_t)b * Cout + c);
     for (int tt = 0; tt < TT && t0 + tt < L0; ++tt) {
-      float y = 0.f;
+      float y0 = 0.f, y1 = 0.f;
 #pragma unroll
-      for (int j = 0; j < F0K; ++j) y = fmaf(wv[j], as[tt * F0S + j], y);
-      const float g = gelu_erf(fmaf(y, sc, sh));
+      for (int j = 0; j < F0K; ++j) {
+        const float av = as[tt * F0S + j];
+        y0 = fmaf(w0[j], av, y0);
+        y1 = fmaf(w1[j], av, y1);
+      }
+      const float g0 = gelu_erf(fmaf(y0, sc.x, sh.x)), g1 = gelu_erf(fmaf(y1, sc.y, sh.y));
       const size_t o = ((size_t)b * Lstride + t0 + tt) * Cout + c;
-      if (out) out[o] = g;
-      if (out16) out16[o] = __float2half_rn(g);
+      if (out) *reinterpret_cast<float2*>(out + o) = make_float2(g0, g1);
+      if (out16) *reinterpret_cast<__half2*>(out16 + o) = __floats2half2_rn(g0, g1);
     }
   }
 }
