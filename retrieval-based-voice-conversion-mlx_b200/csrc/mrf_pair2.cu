@@ -73,7 +73,6 @@ __device__ __forceinline__ uint32_t qpack2(float a, float b, bool bf16) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
-__device__ __forceinline__ float qlrelu(float v, float slope) { return fmaxf(v, v * slope); }
 // packed fp32x2 arithmetic (FADD2 / FMUL2): halves the epilogues' instruction count, which is what bounds them
 __device__ __forceinline__ uint64_t q2_pack(uint32_t lo, uint32_t hi) {
   uint64_t r;
