@@ -10,7 +10,9 @@ product path: file I/O, resampling, index retrieval, chunking of long clips and 
 
 Random weights (no network for checkpoints).  Host waveform in, host waveform out, wall clock.
 python tools/pipeline_bench.py [seconds] [batch] > gpurun_out/pipeline.json
-With batch > 1 the same clip is converted `batch` times in one pass (the throughput form: every stage takes a batch)."""
+With batch > 1 the same clip is converted `batch` times in one pass (the throughput form: every stage takes a batch).
+The f0 predictor and the embedder both read the waveform and nothing of each other: the tool runs them on two CUDA streams
+(the reference runs them one after the other; `sequential_pipeline_s` is that order here)."""
 import json
 import os
 import sys
@@ -50,7 +52,9 @@ def main():
     sid = torch.zeros(NB, dtype=torch.long, device=dev)
     stages = {}
 
-    def convert(audio_np, record=False):
+    s_f0, s_ft = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def convert(audio_np, record=False, overlap=True):
         def mark(name, t0):
             if record:
                 torch.cuda.synchronize()
@@ -61,17 +65,32 @@ def main():
         p_len = audio_pad.shape[0] // WINDOW
         a = torch.from_numpy(audio_pad).to(dev, non_blocking=True).unsqueeze(0).expand(NB, -1).contiguous()
         mark("pad_h2d", t0)
-        t0 = time.perf_counter()
-        hidden = rmvpe.mel2hidden(rmvpe.mel_extractor(a))                                 # get_f0 (:200-246), RMVPE.py:497-513
-        f0 = torch.stack([rmvpe.decode(hidden[i], 0.03)[:p_len] for i in range(NB)])
-        pitch, pitchf = coarse_pitch(f0), f0                                              # :282-291
-        mark("rmvpe_f0", t0)
-        t0 = time.perf_counter()
-        feats = hubert(a)["last_hidden_state"]                                            # :331 (v2: no final_proj)
-        feats = torch.nn.functional.interpolate(feats.permute(0, 2, 1), scale_factor=2).permute(0, 2, 1)  # :344
+        def f0_stage():
+            hidden = rmvpe.mel2hidden(rmvpe.mel_extractor(a))                             # get_f0 (:200-246), RMVPE.py:497-513
+            f0 = torch.stack([rmvpe.decode(hidden[i], 0.03)[:p_len] for i in range(NB)])
+            return coarse_pitch(f0), f0                                                   # :282-291
+
+        def feature_stage():
+            feats = hubert(a)["last_hidden_state"]                                        # :331 (v2: no final_proj)
+            return torch.nn.functional.interpolate(feats.permute(0, 2, 1), scale_factor=2).permute(0, 2, 1)  # :344
+
+        if overlap and not record:
+            cur = torch.cuda.current_stream(dev)
+            s_f0.wait_stream(cur); s_ft.wait_stream(cur)
+            with torch.cuda.stream(s_f0):
+                pitch, pitchf = f0_stage()
+            with torch.cuda.stream(s_ft):
+                feats = feature_stage()
+            cur.wait_stream(s_f0); cur.wait_stream(s_ft)
+        else:
+            t0 = time.perf_counter()
+            pitch, pitchf = f0_stage()
+            mark("rmvpe_f0", t0)
+            t0 = time.perf_counter()
+            feats = feature_stage()
+            mark("hubert", t0)
         p = min(audio_pad.shape[0] // WINDOW, feats.shape[1])                             # :348
         feats, pitch, pitchf = feats[:, :p].contiguous(), pitch[:, :p].contiguous(), pitchf[:, :p].contiguous()
-        mark("hubert", t0)
         t0 = time.perf_counter()
         lens = torch.full((NB,), p, device=dev).long()
         out = net_g.infer(feats.float(), lens, pitch, pitchf.float(), sid)[0][:, 0]       # :367
@@ -87,10 +106,16 @@ def main():
         t0 = time.perf_counter()
         y = convert(audio)
         ts.append(time.perf_counter() - t0)
+    seq = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        convert(audio, overlap=False)
+        seq.append(time.perf_counter() - t0)
     convert(audio, record=True)
     assert np.isfinite(y).all() and abs(y.shape[-1] - int(secs * TGT_SR)) <= 3 * 480, y.shape  # HuBERT yields 2 frames fewer than audio // 160, as in the reference
     best = min(ts)
     print(json.dumps({"clip_seconds": secs, "batch": NB, "output_samples": int(y.shape[-1]), "pipeline_s": best, "realtime_factor": NB * secs / best,
+                      "sequential_pipeline_s": min(seq),
                       "stage_ms_with_syncs": stages,
                       "published_reference": {"mlx_s": 1.27, "pytorch_mps_s": 11.08, "hardware": "M3 Max", "source": "BASELINE.md / reference README.md:22-29"},
                       "data": "synthetic tone + noise, random weights"}, indent=1))
