@@ -49,6 +49,7 @@ struct GemmTmaParams {
   int M, N, K, act, rows_per_item;  // rows_per_item: strideA / lda (row coordinate of item z = z * rows_per_item)
 };
 
+template <int BN>
 __global__ void __launch_bounds__(TM_THREADS, 2) gemm_tma_kernel(const __grid_constant__ GemmTmaParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sg = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -57,7 +58,7 @@ __global__ void __launch_bounds__(TM_THREADS, 2) gemm_tma_kernel(const __grid_co
   const uint32_t full0 = sb + OFF_BAR, empty0 = full0 + 8 * TM_STAGES, acc_full = empty0 + 8 * TM_STAGES, tmem_slot = acc_full + 8;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(sg + OFF_BAR + 8 * (2 * TM_STAGES + 1));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * TM_M, n0 = blockIdx.x * TM_N;
+  const int m0 = blockIdx.y * TM_M, n0 = blockIdx.x * BN;
   const int nk = p.K / TM_K;
 
   if (threadIdx.x == 0) {
@@ -82,7 +83,7 @@ __global__ void __launch_bounds__(TM_THREADS, 2) gemm_tma_kernel(const __grid_co
         const int s = kt % TM_STAGES;
         if (kt >= TM_STAGES) mbar_wait(empty0 + 8 * s, ((kt / TM_STAGES) - 1) & 1);
         const uint32_t sa = sb + s * 2 * TM_TILE, sw = sa + TM_TILE;
-        mbar_expect_tx(full0 + 8 * s, 2 * TM_TILE);
+        mbar_expect_tx(full0 + 8 * s, TM_TILE + BN * TM_K * 2);
         tma_load_2d(sa, &p.tmA, kt * TM_K, row0, full0 + 8 * s);
         tma_load_2d(sw, &p.tmW, kt * TM_K, n0, full0 + 8 * s);
       }
@@ -90,7 +91,7 @@ __global__ void __launch_bounds__(TM_THREADS, 2) gemm_tma_kernel(const __grid_co
     __syncwarp();
   } else if (warp == 5) {
     // ===================== MMA issuer =====================
-    const uint32_t idesc = make_idesc(ACT_F16, TM_N);
+    const uint32_t idesc = make_idesc(ACT_F16, BN);
     for (int kt = 0; kt < nk; ++kt) {
       const int s = kt % TM_STAGES;
       mbar_wait(full0 + 8 * s, (kt / TM_STAGES) & 1);
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(TM_THREADS, 2) gemm_tma_kernel(const __grid_co
     const size_t zoff = blockIdx.z * p.strideC;
     const uint32_t tl = tm + ((uint32_t)(warp * 32) << 16);
 #pragma unroll 1
-    for (int c = 0; c < TM_N / 32; ++c) {
+    for (int c = 0; c < BN / 32; ++c) {
       uint32_t r[32];
       tc_ld32(tl + c * 32, r);
       if (!ok) continue;
@@ -295,17 +296,17 @@ struct MapHash {
   size_t operator()(const MapKey& k) const { return (size_t)((uintptr_t)k.p * 1315423911u ^ k.pitch * 2654435761u ^ k.rows * 97 ^ k.k); }
 };
 // fp16 matrix of `rows` rows of `k` halves, `pitch` halves apart (pitch < k = overlapping rows); box 64 x 128, 128-byte swizzle
-bool tensor_map(const void* ptr, uint64_t pitch, uint64_t rows, uint64_t k, CUtensorMap* out) {
+bool tensor_map(const void* ptr, uint64_t pitch, uint64_t rows, uint64_t k, uint32_t box_rows, CUtensorMap* out) {
   static std::mutex mu;
   static std::unordered_map<MapKey, CUtensorMap, MapHash> cache;
-  const MapKey key{ptr, pitch, rows, k};
+  const MapKey key{ptr, pitch, rows, k * 1024 + box_rows};
   std::lock_guard<std::mutex> g(mu);
   auto it = cache.find(key);
   if (it != cache.end()) { *out = it->second; return true; }
   EncodeTiledFn fn = encode_fn();
   if (!fn) return false;
   const cuuint64_t dims[2] = {k, rows}, strides[1] = {pitch * 2};
-  const cuuint32_t box[2] = {TM_K, TM_M}, es[2] = {1, 1};
+  const cuuint32_t box[2] = {TM_K, box_rows}, es[2] = {1, 1};
   CUtensorMap m;
   if (fn(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -324,20 +325,24 @@ cudaError_t launch_gemm_tma(const __half* A, size_t lda, size_t strideA, const _
   GemmTmaParams p;
   const bool foldable = batch == 1 || (strideA % lda == 0);
   const uint64_t rows = (uint64_t)(batch - 1) * (foldable && batch > 1 ? strideA / lda : 0) + (uint64_t)M;
-  if (!foldable || !tensor_map(A, lda, rows, (uint64_t)K, &p.tmA) || !tensor_map(W, (uint64_t)K, (uint64_t)N, (uint64_t)K, &p.tmW))
+  // 64-column tiles where 128-column ones would leave half the SMs without a CTA (N = 768 at M = 1499: 72 CTAs)
+  const int bn = ((long long)(N / TM_N) * ((M + TM_M - 1) / TM_M) * batch < 100) ? 64 : TM_N;
+  if (!foldable || !tensor_map(A, lda, rows, (uint64_t)K, TM_M, &p.tmA) || !tensor_map(W, (uint64_t)K, (uint64_t)N, (uint64_t)K, (uint32_t)bn, &p.tmW))
     return launch_gemm_tc(A, lda, strideA, W, bias, R, C32, C16, ldc, strideC, batch, M, N, K, act, s);
   static bool attr_set[64] = {};
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   if (dev < 64 && !attr_set[dev]) {
-    e = cudaFuncSetAttribute(gemm_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TM_SMEM);
+    e = cudaFuncSetAttribute(gemm_tma_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, TM_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tma_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, TM_SMEM);
     if (e != cudaSuccess) return e;
     attr_set[dev] = true;
   }
   p.bias = bias; p.R = R; p.C32 = C32; p.C16 = C16; p.ldc = ldc; p.strideC = strideC;
   p.M = M; p.N = N; p.K = K; p.act = act; p.rows_per_item = batch > 1 ? (int)(strideA / lda) : 0;
-  gemm_tma_kernel<<<dim3(N / TM_N, (M + TM_M - 1) / TM_M, batch), TM_THREADS, TM_SMEM, s>>>(p);
+  if (bn == 64) gemm_tma_kernel<64><<<dim3(N / 64, (M + TM_M - 1) / TM_M, batch), TM_THREADS, TM_SMEM, s>>>(p);
+  else gemm_tma_kernel<128><<<dim3(N / TM_N, (M + TM_M - 1) / TM_M, batch), TM_THREADS, TM_SMEM, s>>>(p);
   return cudaGetLastError();
 }
 
